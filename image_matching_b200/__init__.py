@@ -1,0 +1,12 @@
+"""image_matching_b200: B200-native CKKS evaluation engine for the HyDia Sender hot path
+(n7koirala/image_matching approach 5). The compute lives in libhydia_b200.so (hand-written
+sm_100a CUDA behind the C ABI in include/hydia_b200.h); this package is the thin host mirror of
+the reference's Sender / OpenFHEWrapper / cc->Eval* surface. There is no CPU fallback."""
+from . import _lib
+from .client import Client, diagonal_pack, hydia_rotation_set, plaintext_normalize
+from .engine import Ciphertext, CryptoContext
+from .sender import DiagonalSender, Sender
+from . import openfhe_wrapper as OpenFHEWrapper
+
+__all__ = ["CryptoContext", "Ciphertext", "Client", "DiagonalSender", "Sender", "OpenFHEWrapper", "diagonal_pack",
+           "hydia_rotation_set", "plaintext_normalize"]

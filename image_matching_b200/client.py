@@ -1,0 +1,117 @@
+"""Synthetic client side over the C ABI (hx_client_*): KeyGen / EvalMultKeyGen / EvalRotateKeyGen
+(src/main.cpp:184-206), DiagonalEnroller packing + encryption (src/enroller/enroller_diag.cpp),
+DiagonalReceiver::encryptQuery (src/receiver/receiver_diag.cpp:13-26) and HersReceiver decisions
+(src/receiver/receiver_hers.cpp:26-54). Used by smoke / bench / tests to produce inputs; the
+Sender hot path never needs it."""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import List, Sequence
+
+import numpy as np
+
+from . import _lib
+from ._lib import F64P, I32P, check_int, check_ptr
+from .config import VECTOR_DIM
+from .engine import Ciphertext, CryptoContext
+
+
+def hydia_rotation_set(batch_size: int) -> List[int]:
+    """Rotation indices of src/main.cpp:195-206."""
+    rot = list(range(1, VECTOR_DIM))
+    i = VECTOR_DIM
+    while i < batch_size:
+        rot.append(i); i *= 2
+    i = 1
+    while i < batch_size:
+        rot.append(-i); i *= 2
+    return rot
+
+
+def plaintext_normalize(v: np.ndarray) -> np.ndarray:
+    """VectorUtils::plaintextNormalize (src/vector_utils.cpp)."""
+    n = np.linalg.norm(v, axis=-1, keepdims=True)
+    return v / np.where(n == 0, 1.0, n)
+
+
+def diagonal_pack(db: np.ndarray, batch: int) -> np.ndarray:
+    """DiagonalEnroller packing (enroller_diag.cpp:57-156): returns [G*512][batch] rows; row
+    g*512+d, slot j*512+r = normalize(db)[(g*(batch/512)+j)*512 + r][(r+d) mod 512]."""
+    dim = VECTOR_DIM
+    n = db.shape[0]
+    dbn = plaintext_normalize(db.astype(np.float64))
+    nmat = int(math.ceil(n / dim))
+    padded = np.zeros((nmat * dim, dim))
+    padded[:n] = dbn
+    mats = padded.reshape(nmat, dim, dim)
+    r = np.arange(dim)
+    # diagonals[m][d][r] = mats[m][r][(r+d) % dim]
+    diags = np.stack([mats[:, r, (r + d) % dim] for d in range(dim)], axis=1)   # [nmat][dim(d)][dim(r)]
+    per = batch // dim
+    G = int(math.ceil(nmat / per))
+    out = np.zeros((G * dim, batch))
+    for g in range(G):
+        for j in range(per):
+            m = g * per + j
+            if m < nmat:
+                out[g * dim:(g + 1) * dim, j * dim:(j + 1) * dim] = diags[m]
+    return out
+
+
+class Client:
+    def __init__(self, cc: CryptoContext, seed: int = 1):
+        self.cc = cc
+        self._lib = _lib.load()
+        self._h = check_ptr(self._lib.hx_client_create(cc._h, seed))
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            self._lib.hx_client_destroy(h)
+
+    def EvalMultKeyGen(self): check_int(self._lib.hx_client_gen_mult_key(self._h))
+    def EvalSumKeyGen(self): check_int(self._lib.hx_client_gen_sum_keys(self._h))
+    def EvalRotateKeyGen(self, rotations: Sequence[int]):
+        r = np.array(list(rotations), dtype=np.int32)
+        check_int(self._lib.hx_client_gen_rot_keys(self._h, r.ctypes.data_as(I32P), len(r)))
+
+    def encrypt(self, values) -> Ciphertext:
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        return Ciphertext(self.cc, self._lib.hx_client_encrypt(self._h, v.ctypes.data_as(F64P), len(v)))
+
+    def decrypt(self, ct: Ciphertext) -> np.ndarray:
+        out = np.empty(self.cc.N // 2, dtype=np.float64)
+        check_int(self._lib.hx_client_decrypt(self._h, ct._h, out.ctypes.data_as(F64P)))
+        return out
+
+    def secret(self) -> np.ndarray:
+        out = np.empty(self.cc.N, dtype=np.int8)
+        check_int(self._lib.hx_client_secret(self._h, out.ctypes.data_as(C.POINTER(C.c_int8))))
+        return out
+
+    # ---- Enroller / Receiver roles for approach 5
+    def enroll_diagonal(self, db: np.ndarray, first_block: int = 0) -> int:
+        """DiagonalEnroller::serializeDB: encrypt every packed row and keep it HBM resident."""
+        rows = diagonal_pack(db, self.cc.GetBatchSize())
+        for i, row in enumerate(rows):
+            v = np.ascontiguousarray(row)
+            check_int(self._lib.hx_client_enroll(self._h, first_block + i // VECTOR_DIM, i % VECTOR_DIM,
+                                                 v.ctypes.data_as(F64P), len(v)))
+        return len(rows) // VECTOR_DIM
+
+    def encryptQuery(self, query: np.ndarray) -> List[Ciphertext]:
+        """DiagonalReceiver::encryptQuery: normalise, tile batch/512 times, encrypt."""
+        q = plaintext_normalize(np.asarray(query, dtype=np.float64))
+        return [self.encrypt(np.tile(q, self.cc.GetBatchSize() // VECTOR_DIM))]
+
+    def decryptMembership(self, ct: Ciphertext) -> bool:
+        return bool(self.decrypt(ct)[0] >= 1.0)
+
+    def decryptIndex(self, cts: List[Ciphertext]) -> List[int]:
+        batch = self.cc.GetBatchSize()
+        out = []
+        for i, ct in enumerate(cts):
+            v = self.decrypt(ct)
+            out.extend(int(j + i * batch) for j in np.nonzero(v >= 1.0)[0])
+        return out

@@ -1,0 +1,195 @@
+// hx_capi.cu -- extern "C" boundary of libhydia_b200.so (declarations: include/hydia_b200.h).
+#include <cstring>
+
+#include "../../include/hydia_b200.h"
+#include "hx_client.h"
+#include "hx_engine.h"
+
+using namespace hx;
+
+struct hx_ctx { Engine* eng; };
+struct hx_ct { Ct ct; };
+struct hx_digits { std::shared_ptr<Engine::Digits> dg; };
+struct hx_client { Client* cl; };
+
+static thread_local std::string g_err;
+static void set_err(const std::exception& e) { g_err = e.what(); }
+
+#define HX_TRY_PTR(body)               \
+    try { body }                       \
+    catch (const std::exception& e) {  \
+        set_err(e);                    \
+        return nullptr;                \
+    }
+#define HX_TRY_INT(body)               \
+    try { body return 0; }             \
+    catch (const std::exception& e) {  \
+        set_err(e);                    \
+        return -1;                     \
+    }
+
+static hx_ct* wrap(const Ct& c) {
+    hx_ct* h = new hx_ct;
+    h->ct = c;
+    return h;
+}
+static void need(const void* p, const char* what) {
+    if (!p) throw std::runtime_error(std::string("null argument: ") + what);
+}
+
+extern "C" {
+
+const char* hx_last_error(void) { return g_err.c_str(); }
+int hx_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+hx_ctx* hx_ctx_create(int N, int L, int K, int dnum, const uint64_t* q, const uint64_t* p, const uint64_t* psi_q,
+                      const uint64_t* psi_p, int log2_scale, int device) {
+    HX_TRY_PTR(
+        need(q, "q"); need(p, "p"); need(psi_q, "psi_q"); need(psi_p, "psi_p");
+        int n = 0;
+        if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0)
+            throw std::runtime_error("no CUDA device: libhydia_b200 has no CPU fallback");
+        hx_ctx* c = new hx_ctx;
+        c->eng = new Engine(N, L, K, dnum, (const u64*)q, (const u64*)p, (const u64*)psi_q, (const u64*)psi_p, log2_scale, device);
+        return c;)
+}
+void hx_ctx_destroy(hx_ctx* ctx) {
+    if (!ctx) return;
+    delete ctx->eng;
+    delete ctx;
+}
+int hx_ctx_sync(hx_ctx* ctx) { HX_TRY_INT(need(ctx, "ctx"); ctx->eng->sync();) }
+uint64_t hx_ctx_launches(hx_ctx* ctx) { return ctx ? ctx->eng->launches : 0; }
+uint32_t hx_galois_for_rotation(hx_ctx* ctx, int rotation) { return ctx ? (uint32_t)ctx->eng->galois_for_rotation(rotation) : 0; }
+
+int hx_key_load_mult(hx_ctx* ctx, const uint64_t* a, const uint64_t* b) {
+    HX_TRY_INT(need(ctx, "ctx"); need(a, "a"); need(b, "b"); ctx->eng->load_mult_key((const u64*)a, (const u64*)b);)
+}
+int hx_key_load_auto(hx_ctx* ctx, uint32_t galois, const uint64_t* a, const uint64_t* b) {
+    HX_TRY_INT(need(ctx, "ctx"); need(a, "a"); need(b, "b"); ctx->eng->load_rot_key(galois, (const u64*)a, (const u64*)b);)
+}
+
+hx_ct* hx_ct_upload(hx_ctx* ctx, int ncomp, int nlimbs, const uint64_t* data, int level, int noise_deg) {
+    HX_TRY_PTR(
+        need(ctx, "ctx"); need(data, "data");
+        if (ncomp < 1 || ncomp > 3 || nlimbs < 1 || nlimbs > ctx->eng->L) throw std::runtime_error("hx_ct_upload: bad shape");
+        return wrap(ctx->eng->upload((const u64*)data, ncomp, nlimbs, level, noise_deg));)
+}
+int hx_ct_download(hx_ct* ct, uint64_t* data) { HX_TRY_INT(need(ct, "ct"); need(data, "data"); ct->ct->eng->download(ct->ct, (u64*)data);) }
+int hx_ct_info(hx_ct* ct, int* ncomp, int* nlimbs, int* level, int* noise_deg) {
+    HX_TRY_INT(
+        need(ct, "ct");
+        if (ncomp) *ncomp = ct->ct->ncomp;
+        if (nlimbs) *nlimbs = ct->ct->nl;
+        if (level) *level = ct->ct->level;
+        if (noise_deg) *noise_deg = ct->ct->deg;)
+}
+hx_ct* hx_ct_clone(hx_ct* ct) { HX_TRY_PTR(need(ct, "ct"); return wrap(ct->ct->eng->clone(ct->ct));) }
+void hx_ct_free(hx_ct* ct) { delete ct; }
+
+#define E(x) ((x)->ct->eng)
+hx_ct* hx_add(hx_ct* a, hx_ct* b) { HX_TRY_PTR(need(a, "a"); need(b, "b"); return wrap(E(a)->add(a->ct, b->ct));) }
+hx_ct* hx_sub(hx_ct* a, hx_ct* b) { HX_TRY_PTR(need(a, "a"); need(b, "b"); return wrap(E(a)->sub(a->ct, b->ct));) }
+hx_ct* hx_add_const(hx_ct* a, double c) { HX_TRY_PTR(need(a, "a"); return wrap(E(a)->add_const(a->ct, c));) }
+hx_ct* hx_mult_const(hx_ct* a, double c) { HX_TRY_PTR(need(a, "a"); return wrap(E(a)->mult_const(a->ct, c));) }
+hx_ct* hx_mult_norelin(hx_ct* a, hx_ct* b) { HX_TRY_PTR(need(a, "a"); need(b, "b"); return wrap(E(a)->mult_norelin(a->ct, b->ct));) }
+hx_ct* hx_relin(hx_ct* a) { HX_TRY_PTR(need(a, "a"); return wrap(E(a)->relinearize(a->ct));) }
+hx_ct* hx_mult(hx_ct* a, hx_ct* b) { HX_TRY_PTR(need(a, "a"); need(b, "b"); return wrap(E(a)->mult(a->ct, b->ct));) }
+hx_ct* hx_square(hx_ct* a) { HX_TRY_PTR(need(a, "a"); return wrap(E(a)->square(a->ct));) }
+hx_ct* hx_rescale(hx_ct* a) { HX_TRY_PTR(need(a, "a"); return wrap(E(a)->rescale(a->ct));) }
+hx_ct* hx_level_reduce(hx_ct* a, int levels) { HX_TRY_PTR(need(a, "a"); return wrap(E(a)->level_reduce(a->ct, levels));) }
+hx_ct* hx_rotate(hx_ct* a, int r) { HX_TRY_PTR(need(a, "a"); return wrap(E(a)->rotate(a->ct, r));) }
+hx_ct* hx_eval_sum(hx_ct* a, int n) { HX_TRY_PTR(need(a, "a"); return wrap(E(a)->eval_sum(a->ct, n));) }
+hx_ct* hx_add_many(hx_ct* const* cts, int n) {
+    HX_TRY_PTR(
+        need(cts, "cts");
+        if (n < 1) throw std::runtime_error("hx_add_many: empty input");
+        std::vector<Ct> v;
+        for (int i = 0; i < n; i++) { need(cts[i], "cts[i]"); v.push_back(cts[i]->ct); }
+        return wrap(v[0]->eng->add_many(v));)
+}
+hx_digits* hx_rot_precompute(hx_ct* a) {
+    HX_TRY_PTR(need(a, "a"); hx_digits* d = new hx_digits; d->dg = E(a)->fast_rotation_precompute(a->ct); return d;)
+}
+hx_ct* hx_rot_fast(hx_ct* a, int r, hx_digits* d) { HX_TRY_PTR(need(a, "a"); need(d, "digits"); return wrap(E(a)->fast_rotation(a->ct, r, d->dg));) }
+void hx_digits_free(hx_digits* d) { delete d; }
+hx_ct* hx_cheby_series(hx_ct* a, const double* coeffs, int n, double lo, double hi) {
+    HX_TRY_PTR(need(a, "a"); need(coeffs, "coeffs"); return wrap(E(a)->chebyshev_series(a->ct, std::vector<double>(coeffs, coeffs + n), lo, hi));)
+}
+hx_ct* hx_poly(hx_ct* a, const double* coeffs, int n) {
+    HX_TRY_PTR(need(a, "a"); need(coeffs, "coeffs"); return wrap(E(a)->eval_poly(a->ct, std::vector<double>(coeffs, coeffs + n)));)
+}
+hx_ct* hx_compare(hx_ct* a, double delta, int sign_depth) { HX_TRY_PTR(need(a, "a"); return wrap(E(a)->chebyshev_compare(a->ct, delta, sign_depth));) }
+
+int hx_db_register(hx_ctx* ctx, int block, int diag, const uint64_t* data) {
+    HX_TRY_INT(need(ctx, "ctx"); need(data, "data"); ctx->eng->db_register(block, diag, (const u64*)data);)
+}
+int hx_db_blocks(hx_ctx* ctx) { return ctx ? ctx->eng->db_blocks() : 0; }
+int hx_score_diag(hx_ctx* ctx, hx_ct* query, int ndiag, hx_ct** out, int max_out) {
+    try {
+        need(ctx, "ctx"); need(query, "query"); need(out, "out");
+        std::vector<Ct> s = ctx->eng->score_diag(query->ct, ndiag);
+        if ((int)s.size() > max_out) throw std::runtime_error("hx_score_diag: output array too small");
+        for (size_t i = 0; i < s.size(); i++) out[i] = wrap(s[i]);
+        return (int)s.size();
+    } catch (const std::exception& e) { set_err(e); return -1; }
+}
+hx_ct* hx_membership(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sign_depth) {
+    HX_TRY_PTR(need(ctx, "ctx"); need(query, "query"); return wrap(ctx->eng->membership(query->ct, ndiag, delta, sign_depth));)
+}
+int hx_index(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sign_depth, hx_ct** out, int max_out) {
+    try {
+        need(ctx, "ctx"); need(query, "query"); need(out, "out");
+        std::vector<Ct> s = ctx->eng->index(query->ct, ndiag, delta, sign_depth);
+        if ((int)s.size() > max_out) throw std::runtime_error("hx_index: output array too small");
+        for (size_t i = 0; i < s.size(); i++) out[i] = wrap(s[i]);
+        return (int)s.size();
+    } catch (const std::exception& e) { set_err(e); return -1; }
+}
+
+int hx_ntt(hx_ctx* ctx, uint64_t* data, int nbatch, const int* primes, int nprimes, int inverse) {
+    HX_TRY_INT(
+        need(ctx, "ctx"); need(data, "data"); need(primes, "primes");
+        Engine* e = ctx->eng;
+        std::lock_guard<std::recursive_mutex> g(e->mu);
+        size_t words = (size_t)nbatch * e->N;
+        u64* d = e->alloc_words(words);
+        HX_CUDA(cudaMemcpyAsync(d, data, words * sizeof(u64), cudaMemcpyHostToDevice, e->st));
+        e->ntt_limbs(d, nbatch, std::vector<int>(primes, primes + nprimes), inverse != 0);
+        HX_CUDA(cudaMemcpyAsync(data, d, words * sizeof(u64), cudaMemcpyDeviceToHost, e->st));
+        e->sync();
+        e->free_words(d);)
+}
+
+int hx_params_generate(int depth, int scale_bits, int first_mod_bits, int ring_dim, int num_large_digits, int* N, int* L, int* K,
+                       int* dnum, uint64_t* q, uint64_t* p, uint64_t* psi_q, uint64_t* psi_p) {
+    HX_TRY_INT(
+        ParamSet P = generate_params(depth, scale_bits, first_mod_bits, ring_dim, num_large_digits);
+        *N = P.N; *L = P.L; *K = P.K; *dnum = P.dnum;
+        for (int i = 0; i < P.L; i++) { q[i] = P.q[i]; psi_q[i] = P.psi_q[i]; }
+        for (int i = 0; i < P.K; i++) { p[i] = P.p[i]; psi_p[i] = P.psi_p[i]; })
+}
+
+hx_client* hx_client_create(hx_ctx* ctx, uint64_t seed) {
+    HX_TRY_PTR(need(ctx, "ctx"); hx_client* c = new hx_client; c->cl = new Client(ctx->eng, seed); return c;)
+}
+void hx_client_destroy(hx_client* c) {
+    if (!c) return;
+    delete c->cl;
+    delete c;
+}
+int hx_client_gen_mult_key(hx_client* c) { HX_TRY_INT(need(c, "client"); c->cl->gen_mult_key();) }
+int hx_client_gen_rot_keys(hx_client* c, const int* rotations, int n) { HX_TRY_INT(need(c, "client"); need(rotations, "rotations"); c->cl->gen_rot_keys(rotations, n);) }
+int hx_client_gen_sum_keys(hx_client* c) { HX_TRY_INT(need(c, "client"); c->cl->gen_sum_keys();) }
+hx_ct* hx_client_encrypt(hx_client* c, const double* values, int n) { HX_TRY_PTR(need(c, "client"); need(values, "values"); return wrap(c->cl->encrypt(values, n));) }
+int hx_client_enroll(hx_client* c, int block, int diag, const double* values, int n) {
+    HX_TRY_INT(need(c, "client"); need(values, "values"); c->cl->enroll(block, diag, values, n);)
+}
+int hx_client_decrypt(hx_client* c, hx_ct* ct, double* out) { HX_TRY_INT(need(c, "client"); need(ct, "ct"); need(out, "out"); c->cl->decrypt(ct->ct, out);) }
+int hx_client_secret(hx_client* c, int8_t* out) { HX_TRY_INT(need(c, "client"); need(out, "out"); c->cl->secret(out);) }
+
+}  // extern "C"

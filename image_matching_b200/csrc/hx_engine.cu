@@ -1,0 +1,538 @@
+// hx_engine.cu -- Engine: context tables, memory, keys, and the primitive evaluation ops.
+#include "hx_engine.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+namespace hx {
+
+// ------------------------------------------------------------------------------------------ CtObj
+CtObj::~CtObj() {
+    if (d && eng) eng->free_words(d);
+}
+u64* CtObj::comp(int c) const { return d + (size_t)c * comp_stride(); }
+size_t CtObj::comp_stride() const { return (size_t)nl * eng->N; }
+Engine::Digits::~Digits() {
+    if (d && eng) eng->free_words(d);
+}
+
+// ------------------------------------------------------------------------------------------ setup
+Engine::Engine(int N_, int L_, int K_, int dnum_, const u64* q, const u64* p, const u64* psi_q, const u64* psi_p, int scale_bits_,
+               int device_)
+    : N(N_), logN(ilog2(N_)), L(L_), K(K_), dnum(dnum_), scale_bits(scale_bits_), device(device_) {
+    if ((1 << logN) != N || N < 1024 || N > 65536) throw std::runtime_error("ring dimension must be a power of two in [2^10, 2^16]");
+    if (L + K > kMaxPrimes) throw std::runtime_error("too many RNS limbs");
+    alpha = (L + dnum - 1) / dnum;
+    if (alpha > 8) throw std::runtime_error("digit width > 8 limbs unsupported");
+    for (int i = 0; i < L; i++) { mods.push_back(q[i]); psis.push_back(psi_q[i]); }
+    for (int i = 0; i < K; i++) { mods.push_back(p[i]); psis.push_back(psi_p[i]); }
+    for (u64 m : mods)
+        if (m >> 60) throw std::runtime_error("moduli must be below 2^60");
+    HX_CUDA(cudaSetDevice(device));
+    HX_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    // keep freed blocks in the stream-ordered pool: op outputs are allocated per call
+    cudaMemPool_t pool;
+    HX_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+    unsigned long long thresh = ~0ull;
+    HX_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh));
+
+    const int np = L + K;
+    std::vector<PrimeConst> pcs(np);
+    std::vector<ulonglong2> twf((size_t)np * N), twi((size_t)np * N);
+    for (int i = 0; i < np; i++) {
+        u64 m = mods[i];
+        PrimeConst& c = pcs[i];
+        c.q = m;
+        u64 inv = 1;                       // Newton iteration for m^-1 mod 2^64
+        for (int it = 0; it < 6; it++) inv *= 2 - m * inv;
+        c.qinv_neg = (u64)0 - inv;
+        c.r1 = (u64)((((u128)1) << 64) % m);
+        c.r2 = mulmod(c.r1, c.r1, m);
+        c.mu64 = (u64)((((u128)1) << 64) / m);
+        c.ninv = invmod((u64)N % m, m);
+        c.ninv_sh = shoup(c.ninv, m);
+        c.pad = 0;
+        if (powmod(psis[i], (u64)N, m) != m - 1) throw std::runtime_error("psi is not a primitive 2N-th root of unity");
+        u64 psi_inv = invmod(psis[i], m);
+        u64 x = 1, y = 1;
+        for (int k = 0; k < N; k++) {
+            size_t r = (size_t)i * N + bitrev((u64)k, logN);
+            twf[r] = make_ulonglong2(x, shoup(x, m));
+            twi[r] = make_ulonglong2(y, shoup(y, m));
+            x = mulmod(x, psis[i], m);
+            y = mulmod(y, psi_inv, m);
+        }
+    }
+    HX_CUDA(cudaMalloc(&d_pc_, sizeof(PrimeConst) * np));
+    HX_CUDA(cudaMalloc(&d_twf_, sizeof(ulonglong2) * twf.size()));
+    HX_CUDA(cudaMalloc(&d_twi_, sizeof(ulonglong2) * twi.size()));
+    HX_CUDA(cudaMemcpy(d_pc_, pcs.data(), sizeof(PrimeConst) * np, cudaMemcpyHostToDevice));
+    HX_CUDA(cudaMemcpy(d_twf_, twf.data(), sizeof(ulonglong2) * twf.size(), cudaMemcpyHostToDevice));
+    HX_CUDA(cudaMemcpy(d_twi_, twi.data(), sizeof(ulonglong2) * twi.size(), cudaMemcpyHostToDevice));
+    T.N = N; T.logN = logN; T.nprimes = np; T.pc = d_pc_; T.tw_fwd = d_twf_; T.tw_inv = d_twi_;
+}
+
+Engine::~Engine() {
+    cudaSetDevice(device);
+    cudaStreamSynchronize(st);
+    for (auto& kv : modup_tabs_) cudaFree(kv.second);
+    for (auto& kv : moddown_tabs_) cudaFree(kv.second);
+    for (auto& kv : automaps_) cudaFree(kv.second);
+    for (auto& kv : rot_keys_) { cudaFree(kv.second.a); cudaFree(kv.second.b); }
+    if (have_mult_key_) { cudaFree(mult_key_.a); cudaFree(mult_key_.b); }
+    for (auto& kv : db_) cudaFree(kv.second.d);
+    for (void* p : owned_) cudaFree(p);
+    cudaFree(d_pc_); cudaFree(d_twf_); cudaFree(d_twi_);
+    cudaStreamDestroy(st);
+}
+
+// ------------------------------------------------------------------------------------------ memory
+u64* Engine::alloc_words(size_t words) {
+    void* p = nullptr;
+    HX_CUDA(cudaMallocAsync(&p, words * sizeof(u64), st));
+    return (u64*)p;
+}
+void Engine::free_words(u64* p) { cudaFreeAsync(p, st); }
+void Engine::sync() { HX_CUDA(cudaStreamSynchronize(st)); }
+
+Ct Engine::new_ct(int ncomp, int nl, int level, int deg) {
+    auto c = std::make_shared<CtObj>();
+    c->eng = this; c->ncomp = ncomp; c->nl = nl; c->level = level; c->deg = deg;
+    c->d = alloc_words((size_t)ncomp * nl * N);
+    return c;
+}
+Ct Engine::upload(const u64* host, int ncomp, int nl, int level, int deg) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    Ct c = new_ct(ncomp, nl, level, deg);
+    HX_CUDA(cudaMemcpyAsync(c->d, host, sizeof(u64) * (size_t)ncomp * nl * N, cudaMemcpyHostToDevice, st));
+    sync();
+    return c;
+}
+void Engine::download(const Ct& ct, u64* host) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    HX_CUDA(cudaMemcpyAsync(host, ct->d, sizeof(u64) * (size_t)ct->ncomp * ct->nl * N, cudaMemcpyDeviceToHost, st));
+    sync();
+}
+Ct Engine::clone(const Ct& a) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    Ct c = new_ct(a->ncomp, a->nl, a->level, a->deg);
+    HX_CUDA(cudaMemcpyAsync(c->d, a->d, sizeof(u64) * (size_t)a->ncomp * a->nl * N, cudaMemcpyDeviceToDevice, st));
+    return c;
+}
+
+// ------------------------------------------------------------------------------------------ helpers
+LimbMap Engine::limb_map(const std::vector<int>& primes) const {
+    LimbMap lm;
+    lm.period = (int)primes.size();
+    if (lm.period > kMaxPrimes) throw std::runtime_error("limb map too long");
+    for (int i = 0; i < lm.period; i++) lm.prime[i] = (short)primes[i];
+    return lm;
+}
+ScalarTable Engine::scalar_table(const std::vector<u64>& v) const {
+    ScalarTable s;
+    std::memset(&s, 0, sizeof(s));
+    for (size_t i = 0; i < v.size(); i++) {
+        s.v[i] = v[i] % mods[i];
+        s.sh[i] = shoup(s.v[i], mods[i]);
+    }
+    return s;
+}
+u64 Engine::P_mod(int i) const {
+    u64 r = 1;
+    for (int k = 0; k < K; k++) r = mulmod(r, mods[L + k] % mods[i], mods[i]);
+    return r;
+}
+void Engine::ntt_limbs(u64* data, int nbatch, const std::vector<int>& primes, bool inverse) {
+    launch_ntt(T, data, nbatch, limb_map(primes), inverse, st);
+    launches += (logN > 11) ? 2 : 1;
+}
+u64 Engine::galois_for_rotation(int r) const {
+    u64 m = 2ull * N;
+    if (r == 0) return 1;
+    u64 g = 5;
+    if (r < 0) {   // 5 has order N/2 in (Z/2N)*, so 5^-1 = 5^(N/2 - 1)
+        g = powmod(5, (u64)N / 2 - 1, m);
+        r = -r;
+    }
+    return powmod(g, (u64)r, m);
+}
+const u32* Engine::automap(u64 galois) {
+    auto it = automaps_.find(galois);
+    if (it != automaps_.end()) return it->second;
+    u32* m = nullptr;
+    HX_CUDA(cudaMalloc(&m, sizeof(u32) * N));
+    launch_automap(N, logN, galois, m, st);
+    launches++;
+    automaps_[galois] = m;
+    return m;
+}
+
+// ApproxSwitchCRTBasis tables: src/dst are prime indices.
+BaseConvTable* Engine::make_table(const std::vector<int>& src, const std::vector<int>& dst) {
+    BaseConvTable h;
+    std::memset(&h, 0, sizeof(h));
+    h.n_in = (int)src.size();
+    h.n_out = (int)dst.size();
+    for (int i = 0; i < h.n_in; i++) {
+        u64 qi = mods[src[i]];
+        h.src[i] = (short)src[i];
+        u64 hat = 1;
+        for (int k = 0; k < h.n_in; k++)
+            if (k != i) hat = mulmod(hat, mods[src[k]] % qi, qi);
+        h.hatinv[i] = invmod(hat, qi);
+        h.hatinv_sh[i] = shoup(h.hatinv[i], qi);
+        for (int j = 0; j < h.n_out; j++) {
+            u64 pj = mods[dst[j]];
+            u64 hm = 1;
+            for (int k = 0; k < h.n_in; k++)
+                if (k != i) hm = mulmod(hm, mods[src[k]] % pj, pj);
+            u64 r1 = (u64)((((u128)1) << 64) % pj);
+            h.mat[i * h.n_out + j] = mulmod(hm, r1, pj);   // Montgomery form
+        }
+    }
+    for (int j = 0; j < h.n_out; j++) h.dst[j] = (short)dst[j];
+    BaseConvTable* d = nullptr;
+    HX_CUDA(cudaMalloc(&d, sizeof(BaseConvTable)));
+    HX_CUDA(cudaMemcpy(d, &h, sizeof(BaseConvTable), cudaMemcpyHostToDevice));
+    return d;
+}
+const BaseConvTable* Engine::modup_table(int nl, int digit) {
+    auto key = std::make_pair(nl, digit);
+    auto it = modup_tabs_.find(key);
+    if (it != modup_tabs_.end()) return it->second;
+    int ndig = std::min((nl + alpha - 1) / alpha, dnum);
+    int lo = digit * alpha, hi = (digit == ndig - 1) ? nl : (digit + 1) * alpha;
+    std::vector<int> src, dst;
+    for (int i = lo; i < hi; i++) src.push_back(i);
+    for (int i = 0; i < nl; i++)
+        if (i < lo || i >= hi) dst.push_back(i);
+    for (int k = 0; k < K; k++) dst.push_back(L + k);
+    return modup_tabs_[key] = make_table(src, dst);
+}
+const BaseConvTable* Engine::moddown_table(int nl) {
+    auto it = moddown_tabs_.find(nl);
+    if (it != moddown_tabs_.end()) return it->second;
+    std::vector<int> src, dst;
+    for (int k = 0; k < K; k++) src.push_back(L + k);
+    for (int i = 0; i < nl; i++) dst.push_back(i);
+    return moddown_tabs_[nl] = make_table(src, dst);
+}
+
+// ------------------------------------------------------------------------------------------ keys
+static EvalKey upload_key(Engine& e, const u64* a, const u64* b) {
+    EvalKey k;
+    size_t words = (size_t)e.dnum * (e.L + e.K) * e.N;
+    HX_CUDA(cudaMalloc(&k.a, words * sizeof(u64)));
+    HX_CUDA(cudaMalloc(&k.b, words * sizeof(u64)));
+    HX_CUDA(cudaMemcpyAsync(k.a, a, words * sizeof(u64), cudaMemcpyHostToDevice, e.st));
+    HX_CUDA(cudaMemcpyAsync(k.b, b, words * sizeof(u64), cudaMemcpyHostToDevice, e.st));
+    std::vector<int> primes;
+    for (int i = 0; i < e.L + e.K; i++) primes.push_back(i);
+    LimbMap lm = e.limb_map(primes);
+    launch_to_mont(e.T, k.a, e.dnum * (e.L + e.K), lm, e.st);
+    launch_to_mont(e.T, k.b, e.dnum * (e.L + e.K), lm, e.st);
+    e.launches += 2;
+    e.sync();
+    return k;
+}
+void Engine::load_mult_key(const u64* a, const u64* b) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (have_mult_key_) { cudaFree(mult_key_.a); cudaFree(mult_key_.b); }
+    mult_key_ = upload_key(*this, a, b);
+    have_mult_key_ = true;
+}
+void Engine::load_rot_key(u64 galois, const u64* a, const u64* b) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    auto it = rot_keys_.find(galois);
+    if (it != rot_keys_.end()) { cudaFree(it->second.a); cudaFree(it->second.b); }
+    rot_keys_[galois] = upload_key(*this, a, b);
+}
+void Engine::adopt_rot_key(u64 galois, EvalKey k) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    auto it = rot_keys_.find(galois);
+    if (it != rot_keys_.end()) { cudaFree(it->second.a); cudaFree(it->second.b); }
+    rot_keys_[galois] = k;
+}
+void Engine::adopt_mult_key(EvalKey k) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (have_mult_key_) { cudaFree(mult_key_.a); cudaFree(mult_key_.b); }
+    mult_key_ = k;
+    have_mult_key_ = true;
+}
+const EvalKey& Engine::rot_key(u64 galois) const {
+    auto it = rot_keys_.find(galois);
+    if (it == rot_keys_.end()) throw std::runtime_error("EvalKey for Galois index " + std::to_string(galois) + " is not generated");
+    return it->second;
+}
+
+// ------------------------------------------------------------------------------------------ key switching
+// EvalKeySwitchPrecomputeCore (upstream keyswitch-hybrid.cpp; sender_diag.cpp:22): digit split +
+// ModUp. Returns [ndig][nl+K][N]; every digit holds its own limbs verbatim and the converted ones.
+u64* Engine::ks_precompute(const u64* c, int nl, int* ndig_out) {
+    int ndig = std::min((nl + alpha - 1) / alpha, dnum);
+    int ext = nl + K;
+    u64* digits = alloc_words((size_t)ndig * ext * N);
+    u64* scratch = alloc_words((size_t)alpha * N);
+    for (int j = 0; j < ndig; j++) {
+        int lo = j * alpha, hi = (j == ndig - 1) ? nl : (j + 1) * alpha, sz = hi - lo;
+        u64* dj = digits + (size_t)j * ext * N;
+        HX_CUDA(cudaMemcpyAsync(dj + (size_t)lo * N, c + (size_t)lo * N, sizeof(u64) * sz * N, cudaMemcpyDeviceToDevice, st));
+        HX_CUDA(cudaMemcpyAsync(scratch, c + (size_t)lo * N, sizeof(u64) * sz * N, cudaMemcpyDeviceToDevice, st));
+        std::vector<int> src;
+        for (int i = lo; i < hi; i++) src.push_back(i);
+        ntt_limbs(scratch, sz, src, true);
+        // converted limbs: Q-limbs below lo, Q-limbs from hi, then P. Written in two pieces around the own limbs.
+        const BaseConvTable* tab = modup_table(nl, j);
+        int n_out = nl - sz + K;
+        u64* compl_ = alloc_words((size_t)n_out * N);
+        launch_baseconv(T, tab, sz, n_out, scratch, 0, compl_, 0, 1, st);
+        launches++;
+        std::vector<int> dst;
+        for (int i = 0; i < nl; i++)
+            if (i < lo || i >= hi) dst.push_back(i);
+        for (int k = 0; k < K; k++) dst.push_back(L + k);
+        ntt_limbs(compl_, n_out, dst, false);
+        if (lo > 0) HX_CUDA(cudaMemcpyAsync(dj, compl_, sizeof(u64) * (size_t)lo * N, cudaMemcpyDeviceToDevice, st));
+        HX_CUDA(cudaMemcpyAsync(dj + (size_t)hi * N, compl_ + (size_t)lo * N, sizeof(u64) * (size_t)(n_out - lo) * N,
+                                cudaMemcpyDeviceToDevice, st));
+        free_words(compl_);
+    }
+    free_words(scratch);
+    *ndig_out = ndig;
+    return digits;
+}
+
+// EvalFastKeySwitchCoreExt + ApproxModDown for a batch of keys sharing one set of digits, fused
+// with the "+ c0" and the Galois gather of EvalFastRotation (sender_diag.cpp:25).
+void Engine::ks_core_batch(const u64* digits, int ndig, int nl, const std::vector<const EvalKey*>& keys, const u64* addend,
+                           int addend_comps, const std::vector<u64>& galois, u64* out, size_t out_bs) {
+    const int nb = (int)keys.size(), ext = nl + K;
+    std::vector<const u64*> ha(nb), hb(nb);
+    std::vector<const u32*> hm(nb, nullptr);
+    for (int i = 0; i < nb; i++) { ha[i] = keys[i]->a; hb[i] = keys[i]->b; }
+    if (!galois.empty())
+        for (int i = 0; i < nb; i++) hm[i] = automap(galois[i]);
+    // pointer tables (a | b | maps) in one device buffer
+    u64* ptrs = alloc_words((size_t)3 * nb);
+    HX_CUDA(cudaMemcpyAsync(ptrs, ha.data(), sizeof(u64) * nb, cudaMemcpyHostToDevice, st));
+    HX_CUDA(cudaMemcpyAsync(ptrs + nb, hb.data(), sizeof(u64) * nb, cudaMemcpyHostToDevice, st));
+    HX_CUDA(cudaMemcpyAsync(ptrs + 2 * nb, hm.data(), sizeof(u64) * nb, cudaMemcpyHostToDevice, st));
+    HX_CUDA(cudaStreamSynchronize(st));   // host vectors go out of scope; tables are tiny
+    size_t ct_bs = (size_t)2 * ext * N;
+    u64* ct = alloc_words(ct_bs * nb);
+    launch_ks_inner(T, digits, ndig, nl, L, K, (const u64* const*)ptrs, (const u64* const*)(ptrs + nb), ct, ct_bs, nb, st);
+    launches++;
+    // iNTT of the K P-limbs of both components, in place
+    std::vector<int> pm(ext, -1);
+    for (int k = 0; k < K; k++) pm[nl + k] = L + k;
+    ntt_limbs(ct, nb * 2 * ext, pm, true);
+    size_t conv_bs = (size_t)2 * nl * N;
+    u64* conv = alloc_words(conv_bs * nb);
+    launch_baseconv(T, moddown_table(nl), K, nl, ct + (size_t)nl * N, (size_t)ext * N, conv, (size_t)nl * N, nb * 2, st);
+    launches++;
+    std::vector<int> qm;
+    for (int i = 0; i < nl; i++) qm.push_back(i);
+    ntt_limbs(conv, nb * 2 * nl, qm, false);
+    std::vector<u64> pinv(nl);
+    for (int i = 0; i < nl; i++) pinv[i] = invmod(P_mod(i), mods[i]);
+    launch_moddown_finish(T, ct, ct_bs, conv, conv_bs, addend, addend_comps, galois.empty() ? nullptr : (const u32* const*)(ptrs + 2 * nb),
+                          out, out_bs, nl, scalar_table(pinv), nb, st);
+    launches++;
+    free_words(conv);
+    free_words(ct);
+    free_words(ptrs);
+}
+
+std::shared_ptr<Engine::Digits> Engine::fast_rotation_precompute(const Ct& a) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    auto dg = std::make_shared<Digits>();
+    dg->eng = this;
+    dg->nl = a->nl;
+    dg->d = ks_precompute(a->comp(1), a->nl, &dg->ndig);
+    return dg;
+}
+Ct Engine::fast_rotation(const Ct& a, int r, const std::shared_ptr<Digits>& dg) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (r == 0) return clone(a);
+    if (a->ncomp != 2 || dg->nl != a->nl) throw std::runtime_error("EvalFastRotation: digits do not match the ciphertext");
+    u64 k = galois_for_rotation(r);
+    Ct out = new_ct(2, a->nl, a->level, a->deg);
+    ks_core_batch(dg->d, dg->ndig, a->nl, {&rot_key(k)}, a->comp(0), 1, {k}, out->d, 0);
+    return out;
+}
+Ct Engine::automorphism(const Ct& a, u64 k) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (a->ncomp != 2) throw std::runtime_error("EvalAutomorphism needs a 2-component ciphertext");
+    int ndig;
+    u64* dg = ks_precompute(a->comp(1), a->nl, &ndig);
+    Ct out = new_ct(2, a->nl, a->level, a->deg);
+    ks_core_batch(dg, ndig, a->nl, {&rot_key(k)}, a->comp(0), 1, {k}, out->d, 0);
+    free_words(dg);
+    return out;
+}
+Ct Engine::rotate(const Ct& a, int r) {
+    if (r == 0) return clone(a);
+    return automorphism(a, galois_for_rotation(r));
+}
+Ct Engine::eval_sum(const Ct& a, int n) {
+    // EvalSum2nComplex: g = 5; ceil(log2 n) times { ct += sigma_g(ct); g = g^2 mod 2N }
+    u64 m = 2ull * N, gk = 5;
+    Ct out = a;
+    int rounds = 0;
+    while ((1 << rounds) < n) rounds++;
+    for (int i = 0; i < rounds; i++) {
+        out = add(out, automorphism(out, gk));
+        gk = mulmod(gk, gk, m);
+    }
+    return out;
+}
+Ct Engine::relinearize(const Ct& a) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (a->ncomp == 2) return clone(a);
+    if (a->ncomp != 3) throw std::runtime_error("Relinearize supports 3-component ciphertexts");
+    if (!have_mult_key_) throw std::runtime_error("EvalMultKey is not generated");
+    int ndig;
+    u64* dg = ks_precompute(a->comp(2), a->nl, &ndig);
+    Ct out = new_ct(2, a->nl, a->level, a->deg);
+    ks_core_batch(dg, ndig, a->nl, {&mult_key_}, a->d, 2, {}, out->d, 0);
+    free_words(dg);
+    return out;
+}
+
+// ------------------------------------------------------------------------------------------ leveled ops
+Ct Engine::level_reduce(const Ct& a, int levels) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (levels == 0) return a;
+    if (levels < 0 || levels >= a->nl) throw std::runtime_error("LevelReduce: not enough limbs");
+    int nl = a->nl - levels;
+    Ct out = new_ct(a->ncomp, nl, a->level + levels, a->deg);
+    for (int c = 0; c < a->ncomp; c++)
+        HX_CUDA(cudaMemcpyAsync(out->comp(c), a->comp(c), sizeof(u64) * (size_t)nl * N, cudaMemcpyDeviceToDevice, st));
+    return out;
+}
+void Engine::align(Ct& a, Ct& b) {   // FIXEDMANUAL AdjustLevelsInPlace: drop limbs of the fresher operand
+    if (a->nl > b->nl) a = level_reduce(a, a->nl - b->nl);
+    else if (b->nl > a->nl) b = level_reduce(b, b->nl - a->nl);
+}
+Ct Engine::add(const Ct& a_, const Ct& b_) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    Ct a = a_, b = b_;
+    align(a, b);
+    if (a->deg != b->deg) throw std::runtime_error("EvalAdd: noiseScaleDeg mismatch");
+    if (a->ncomp < b->ncomp) std::swap(a, b);
+    Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg);
+    launch_ew(T, EW_ADD, out->d, a->d, b->d, a->nl, b->ncomp, out->comp_stride(), a->comp_stride(), b->comp_stride(), st);
+    launches++;
+    for (int c = b->ncomp; c < a->ncomp; c++)
+        HX_CUDA(cudaMemcpyAsync(out->comp(c), a->comp(c), sizeof(u64) * a->comp_stride(), cudaMemcpyDeviceToDevice, st));
+    return out;
+}
+Ct Engine::sub(const Ct& a_, const Ct& b_) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    Ct a = a_, b = b_;
+    align(a, b);
+    if (a->deg != b->deg) throw std::runtime_error("EvalSub: noiseScaleDeg mismatch");
+    if (a->ncomp != b->ncomp) throw std::runtime_error("EvalSub: component count mismatch");
+    Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg);
+    launch_ew(T, EW_SUB, out->d, a->d, b->d, a->nl, a->ncomp, out->comp_stride(), a->comp_stride(), b->comp_stride(), st);
+    launches++;
+    return out;
+}
+Ct Engine::add_many(const std::vector<Ct>& v_) {
+    // EvalAddManyInPlace: for j = 1,2,4,..: for i = 0; i + j < n; i += 2j: v[i] += v[i+j]
+    std::vector<Ct> v = v_;
+    if (v.empty()) throw std::runtime_error("EvalAddMany: empty input");
+    for (size_t j = 1; j < v.size(); j *= 2)
+        for (size_t i = 0; i + j < v.size(); i += 2 * j) v[i] = add(v[i], v[i + j]);
+    return v[0];
+}
+// GetElementForEvalMult: (int128)(c * 2^scale_bits + 0.5), truncating cast, per-limb residue with sign fix-up.
+std::vector<u64> Engine::const_for_mult(double c, int nl) const {
+    double sc = std::ldexp(1.0, scale_bits);
+    __int128 large = (__int128)(c * sc + 0.5);
+    std::vector<u64> out(nl);
+    for (int i = 0; i < nl; i++) {
+        __int128 r = large % (__int128)mods[i];
+        if (r < 0) r += mods[i];
+        out[i] = (u64)r;
+    }
+    return out;
+}
+// GetElementForEvalAddOrSub: (uint64)(c*2^scale_bits + 0.5) * ((uint64)(2^scale_bits + 0.5))^(deg-1), c >= 0.
+std::vector<u64> Engine::const_for_add(double c, int nl, int deg) const {
+    double sc = std::ldexp(1.0, scale_bits);
+    u64 k = (u64)(c * sc + 0.5);
+    u64 isf = (u64)(sc + 0.5);
+    std::vector<u64> out(nl);
+    for (int i = 0; i < nl; i++) {
+        u64 v = k % mods[i];
+        for (int d = 1; d < deg; d++) v = mulmod(v, isf % mods[i], mods[i]);
+        out[i] = v;
+    }
+    return out;
+}
+Ct Engine::mult_const(const Ct& a, double c) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg + 1);
+    launch_mul_scalar(T, out->d, a->d, scalar_table(const_for_mult(c, a->nl)), a->nl, a->ncomp, out->comp_stride(), a->comp_stride(), st);
+    launches++;
+    return out;
+}
+Ct Engine::add_const(const Ct& a, double c) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    // the CryptoContext front end routes negative constants to EvalSub(ct, -c)
+    std::vector<u64> k = const_for_add(std::fabs(c), a->nl, a->deg);
+    if (c < 0)
+        for (int i = 0; i < a->nl; i++) k[i] = (mods[i] - k[i]) % mods[i];
+    Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg);
+    launch_add_scalar(T, out->d, a->d, scalar_table(k), a->nl, st);
+    launches++;
+    for (int cidx = 1; cidx < a->ncomp; cidx++)
+        HX_CUDA(cudaMemcpyAsync(out->comp(cidx), a->comp(cidx), sizeof(u64) * a->comp_stride(), cudaMemcpyDeviceToDevice, st));
+    return out;
+}
+Ct Engine::mult_norelin(const Ct& a_, const Ct& b_) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    Ct a = a_, b = b_;
+    align(a, b);
+    if (a->ncomp != 2 || b->ncomp != 2) throw std::runtime_error("EvalMultNoRelin supports 2-component inputs");
+    Ct out = new_ct(3, a->nl, a->level, a->deg + b->deg);
+    launch_tensor(T, out->d, a->d, a->comp_stride(), b->d, b->comp_stride(), a->nl, st);
+    launches++;
+    return out;
+}
+Ct Engine::mult(const Ct& a, const Ct& b) { return relinearize(mult_norelin(a, b)); }
+Ct Engine::square(const Ct& a) { return mult(a, a); }
+
+// DropLastElementAndScale (sender_diag.cpp:80).
+Ct Engine::rescale(const Ct& a) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    int nl = a->nl;
+    if (nl < 2) throw std::runtime_error("Rescale: no limb left to drop");
+    int nc = a->ncomp;
+    u64 ql = mods[nl - 1];
+    std::vector<u64> qlinv(nl - 1), neg(nl - 1);
+    for (int i = 0; i < nl - 1; i++) {
+        qlinv[i] = invmod(ql % mods[i], mods[i]);
+        neg[i] = (mods[i] - qlinv[i]) % mods[i];
+    }
+    u64* last = alloc_words((size_t)nc * N);
+    for (int c = 0; c < nc; c++)
+        HX_CUDA(cudaMemcpyAsync(last + (size_t)c * N, a->comp(c) + (size_t)(nl - 1) * N, sizeof(u64) * N, cudaMemcpyDeviceToDevice, st));
+    ntt_limbs(last, nc, {nl - 1}, true);
+    u64* tmp = alloc_words((size_t)nc * (nl - 1) * N);
+    launch_rescale_prep(T, last, N, tmp, (size_t)(nl - 1) * N, nl, scalar_table(neg), nc, st);
+    launches++;
+    std::vector<int> qm;
+    for (int i = 0; i < nl - 1; i++) qm.push_back(i);
+    ntt_limbs(tmp, nc * (nl - 1), qm, false);
+    Ct out = new_ct(nc, nl - 1, a->level + 1, a->deg - 1);
+    launch_rescale_finish(T, out->d, out->comp_stride(), a->d, a->comp_stride(), tmp, (size_t)(nl - 1) * N, nl, scalar_table(qlinv), nc, st);
+    launches++;
+    free_words(tmp);
+    free_words(last);
+    return out;
+}
+
+}  // namespace hx

@@ -1,0 +1,146 @@
+// hx_engine.h -- host-side CKKS evaluation engine over the sm_100a kernels (product code).
+// Mirrors the subset of lbcrypto::CryptoContext<DCRTPoly> the reference's Sender path calls
+// (SURVEY §8(b) B2); each method cites the reference call site it serves.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <map>
+#include <memory>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "hx_kernels.cuh"
+#include "hx_nt.h"
+
+namespace hx {
+
+#define HX_CUDA(call)                                                                                     \
+    do {                                                                                                  \
+        cudaError_t e_ = (call);                                                                          \
+        if (e_ != cudaSuccess)                                                                            \
+            throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(e_) + " at " #call); \
+    } while (0)
+
+class Engine;
+
+// Ciphertext<DCRTPoly>: ncomp components x nl limbs x N, EVALUATION form, device resident.
+struct CtObj {
+    Engine* eng = nullptr;
+    u64* d = nullptr;
+    int ncomp = 0, nl = 0;
+    int level = 0;      // GetLevel(): limbs dropped
+    int deg = 1;        // GetNoiseScaleDeg()
+    ~CtObj();
+    u64* comp(int c) const;
+    size_t comp_stride() const;
+};
+using Ct = std::shared_ptr<CtObj>;
+
+struct EvalKey {        // device, Montgomery form, [dnum][L+K][N] each
+    u64* a = nullptr;
+    u64* b = nullptr;
+};
+
+class Engine {
+public:
+    Engine(int N, int L, int K, int dnum, const u64* q, const u64* p, const u64* psi_q, const u64* psi_p, int scale_bits, int device);
+    ~Engine();
+
+    int N, logN, L, K, dnum, alpha, scale_bits, device;
+    std::vector<u64> mods, psis;     // Q then P
+    DevTables T{};
+    cudaStream_t st = nullptr;
+    std::recursive_mutex mu;         // the reference enters from up to 48 OpenMP threads
+    unsigned long long launches = 0; // kernels launched (bench "gpu_launches")
+
+    // ---- memory
+    u64* alloc_words(size_t words);
+    void free_words(u64* p);
+    Ct new_ct(int ncomp, int nl, int level, int deg);
+    Ct upload(const u64* host, int ncomp, int nl, int level, int deg);
+    void download(const Ct& ct, u64* host);
+    Ct clone(const Ct& ct);
+    void sync();
+
+    // ---- keys (plain-form host arrays [dnum][L+K][N], evaluation form, OpenFHE limb order)
+    void load_mult_key(const u64* a, const u64* b);
+    void load_rot_key(u64 galois, const u64* a, const u64* b);
+    void adopt_rot_key(u64 galois, EvalKey k);   // device-generated (client module)
+    void adopt_mult_key(EvalKey k);
+    bool has_rot_key(u64 galois) const { return rot_keys_.count(galois) != 0; }
+    u64 galois_for_rotation(int r) const;
+
+    // ---- primitive evaluation ops
+    Ct add(const Ct& a, const Ct& b);                       // EvalAdd / EvalAddInPlace (sender_diag.cpp:76)
+    Ct sub(const Ct& a, const Ct& b);                       // EvalSub
+    Ct add_const(const Ct& a, double c);                    // EvalAddInPlace(ct,double) (openFHE_wrapper.cpp:182)
+    Ct mult_const(const Ct& a, double c);                   // EvalMult(ct,double)
+    Ct mult_norelin(const Ct& a, const Ct& b);              // EvalMultNoRelin (sender_diag.cpp:93)
+    Ct relinearize(const Ct& a);                            // RelinearizeInPlace (sender_diag.cpp:79)
+    Ct mult(const Ct& a, const Ct& b);                      // EvalMult(ct,ct)
+    Ct square(const Ct& a);                                 // EvalSquare
+    Ct rescale(const Ct& a);                                // RescaleInPlace / ModReduceInPlace (sender_diag.cpp:80)
+    Ct level_reduce(const Ct& a, int levels);               // LevelReduceInPlace
+    Ct rotate(const Ct& a, int r);                          // EvalRotate (openFHE_wrapper.cpp:124)
+    Ct automorphism(const Ct& a, u64 galois);
+    Ct eval_sum(const Ct& a, int n);                        // EvalSum (sender_diag.cpp:47)
+    Ct add_many(const std::vector<Ct>& v);                  // EvalAddManyInPlace (sender_diag.cpp:46)
+    // hoisted rotations (sender_diag.cpp:22-26)
+    struct DbBlock { u64* d = nullptr; int ndiag = 0; };
+    struct Digits { u64* d = nullptr; int ndig = 0, nl = 0; Engine* eng = nullptr; ~Digits(); };
+    std::shared_ptr<Digits> fast_rotation_precompute(const Ct& a);
+    Ct fast_rotation(const Ct& a, int r, const std::shared_ptr<Digits>& dg);
+
+    // ---- PS evaluators (openFHE_wrapper.cpp:174,179)
+    Ct chebyshev_series(const Ct& x, const std::vector<double>& coeffs, double a, double b);
+    Ct eval_poly(const Ct& x, const std::vector<double>& coeffs);
+    Ct chebyshev_compare(const Ct& x, double delta, int sign_depth);   // openFHE_wrapper.cpp:143-185
+    Ct linear_wsum(const std::vector<Ct>& cts, const std::vector<double>& w);   // EvalLinearWSumMutable
+
+    // ---- fused HyDia path (sender_diag.cpp:12-94)
+    // database block g: 512 diagonal ciphertexts, kept HBM resident in Montgomery form
+    void db_register(int block, int diag, const u64* host_ct /*[2][L][N]*/);
+    void db_adopt(int block, u64* dev /*[ndiag][2][L][N], Montgomery form*/, int ndiag);
+    void db_store_device(int block, int diag, const u64* dev_ct /*[2][L][N], plain residues, device*/);
+    int db_blocks() const { return (int)db_.size(); }
+    std::vector<Ct> score_diag(const Ct& query, int ndiag);            // computeSimilarity
+    Ct membership(const Ct& query, int ndiag, double delta, int depth); // membershipScenario
+    std::vector<Ct> index(const Ct& query, int ndiag, double delta, int depth);   // indexScenario
+
+    // ---- building blocks exposed for parity tests
+    void ntt_limbs(u64* data, int nbatch, const std::vector<int>& primes, bool inverse);
+    u64* ks_precompute(const u64* c, int nl, int* ndig_out);               // digits [ndig][nl+K][N]
+    // key-switch core on precomputed digits for `nbatch` keys: out[b] = [2][nl][N] (+ optional addend/maps)
+    void ks_core_batch(const u64* digits, int ndig, int nl, const std::vector<const EvalKey*>& keys, const u64* addend, int addend_comps,
+                       const std::vector<u64>& galois /*empty = no permutation*/, u64* out, size_t out_bs);
+    const EvalKey& rot_key(u64 galois) const;
+    const u32* automap(u64 galois);
+    LimbMap limb_map(const std::vector<int>& primes) const;
+    ScalarTable scalar_table(const std::vector<u64>& v) const;   // v[i] mod q_i with Shoup quotients
+    u64 P_mod(int i) const;     // (prod P) mod q_i
+
+private:
+    const BaseConvTable* modup_table(int nl, int digit);
+    const BaseConvTable* moddown_table(int nl);
+    BaseConvTable* make_table(const std::vector<int>& src, const std::vector<int>& dst);
+    void align(Ct& a, Ct& b);
+    std::vector<u64> const_for_mult(double c, int nl) const;
+    std::vector<u64> const_for_add(double c, int nl, int deg) const;
+    Ct inner_cheb(const std::vector<double>& coeffs, int k, int m, std::vector<Ct>& T, std::vector<Ct>& T2);
+    Ct inner_poly(const std::vector<double>& coeffs, int k, int m, std::vector<Ct>& pw, std::vector<Ct>& pw2);
+
+    std::map<std::pair<int, int>, BaseConvTable*> modup_tabs_;
+    std::map<int, BaseConvTable*> moddown_tabs_;
+    std::map<u64, u32*> automaps_;
+    std::map<u64, EvalKey> rot_keys_;
+    EvalKey mult_key_;
+    bool have_mult_key_ = false;
+    std::map<int, DbBlock> db_;
+    PrimeConst* d_pc_ = nullptr;
+    ulonglong2 *d_twf_ = nullptr, *d_twi_ = nullptr;
+    std::vector<void*> owned_;   // device allocations released with the engine
+};
+
+}  // namespace hx

@@ -1,0 +1,101 @@
+// hx_hydia.cu -- the fused HyDia Sender path: what
+// DiagonalSender::computeSimilarity / membershipScenario / indexScenario
+// (/root/reference/src/sender/sender_diag.cpp:12-94) compute, with the database HBM-resident.
+#include "hx_engine.h"
+
+namespace hx {
+
+constexpr int kRotChunk = 32;   // hoisted rotations per key-switch batch (intermediates ~0.27 GB at N=2^15)
+
+// DB ciphertext `diag` of block `block` (serial/db_diagonal/index{block*512+diag}.bin in the
+// reference, sender_diag.cpp:87): stored in Montgomery form for the lazy MAC.
+static u64* db_slot(Engine& e, std::map<int, Engine::DbBlock>& db, int block, int diag) {
+    const int kDiag = 512;
+    if (diag < 0 || diag >= kDiag) throw std::runtime_error("db_register: diagonal index out of range");
+    Engine::DbBlock& b = db[block];
+    size_t ct_words = (size_t)2 * e.L * e.N;
+    if (!b.d) {
+        HX_CUDA(cudaMalloc(&b.d, sizeof(u64) * ct_words * kDiag));
+        HX_CUDA(cudaMemsetAsync(b.d, 0, sizeof(u64) * ct_words * kDiag, e.st));
+        b.ndiag = kDiag;
+    }
+    return b.d + ct_words * diag;
+}
+static void db_finish(Engine& e, u64* dst) {
+    std::vector<int> primes;
+    for (int i = 0; i < e.L; i++) primes.push_back(i);
+    launch_to_mont(e.T, dst, 2 * e.L, e.limb_map(primes), e.st);
+    e.launches++;
+}
+void Engine::db_register(int block, int diag, const u64* host_ct) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    u64* dst = db_slot(*this, db_, block, diag);
+    HX_CUDA(cudaMemcpyAsync(dst, host_ct, sizeof(u64) * (size_t)2 * L * N, cudaMemcpyHostToDevice, st));
+    db_finish(*this, dst);
+    sync();
+}
+void Engine::db_store_device(int block, int diag, const u64* dev_ct) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    u64* dst = db_slot(*this, db_, block, diag);
+    HX_CUDA(cudaMemcpyAsync(dst, dev_ct, sizeof(u64) * (size_t)2 * L * N, cudaMemcpyDeviceToDevice, st));
+    db_finish(*this, dst);
+}
+void Engine::db_adopt(int block, u64* dev, int ndiag) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    DbBlock& b = db_[block];
+    if (b.d) cudaFree(b.d);
+    b.d = dev;
+    b.ndiag = ndiag;
+}
+
+// computeSimilarity (sender_diag.cpp:12-33): hoisted rotations 1..ndiag-1 of the query
+// (EvalFastRotationPrecompute + EvalFastRotation), then per block the 512 tensor products, their
+// sum, one relinearisation and one rescale (computeSimilarityMatrix, :66-83).
+std::vector<Ct> Engine::score_diag(const Ct& query, int ndiag) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (query->ncomp != 2 || query->nl != L) throw std::runtime_error("score_diag: query must be a fresh 2-component ciphertext");
+    if (db_.empty()) throw std::runtime_error("score_diag: no database block registered");
+    const int nl = query->nl;
+    const size_t ct_words = (size_t)2 * nl * N;
+    u64* rotq = alloc_words(ct_words * ndiag);
+    HX_CUDA(cudaMemcpyAsync(rotq, query->d, sizeof(u64) * ct_words, cudaMemcpyDeviceToDevice, st));
+    int ndig;
+    u64* digits = ks_precompute(query->comp(1), nl, &ndig);
+    for (int d0 = 1; d0 < ndiag; d0 += kRotChunk) {
+        int d1 = std::min(ndiag, d0 + kRotChunk);
+        std::vector<const EvalKey*> keys;
+        std::vector<u64> gal;
+        for (int d = d0; d < d1; d++) {
+            u64 k = galois_for_rotation(d);
+            keys.push_back(&rot_key(k));
+            gal.push_back(k);
+        }
+        ks_core_batch(digits, ndig, nl, keys, query->comp(0), 1, gal, rotq + ct_words * d0, ct_words);
+    }
+    free_words(digits);
+    std::vector<Ct> scores;
+    for (auto& kv : db_) {
+        if (kv.second.ndiag < ndiag) throw std::runtime_error("score_diag: database block has fewer diagonals than requested");
+        Ct acc = new_ct(3, nl, query->level, query->deg + 1);
+        launch_diag_mac(T, rotq, kv.second.d, acc->d, ndiag, nl, st);
+        launches++;
+        scores.push_back(rescale(relinearize(acc)));
+    }
+    free_words(rotq);
+    return scores;
+}
+
+// indexScenario (sender_diag.cpp:52-63).
+std::vector<Ct> Engine::index(const Ct& query, int ndiag, double delta, int depth) {
+    std::vector<Ct> s = score_diag(query, ndiag);
+    for (auto& c : s) c = chebyshev_compare(c, delta, depth);
+    return s;
+}
+// membershipScenario (sender_diag.cpp:35-50).
+Ct Engine::membership(const Ct& query, int ndiag, double delta, int depth) {
+    std::vector<Ct> s = index(query, ndiag, delta, depth);
+    Ct m = add_many(s);
+    return eval_sum(m, N / 2);
+}
+
+}  // namespace hx

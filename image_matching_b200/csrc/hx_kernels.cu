@@ -1,0 +1,363 @@
+// hx_kernels.cu -- sm_100a kernels for the CKKS hot path other than the NTT (SURVEY §8 rows
+// P3-P8): approximate base conversion, key-switch inner product, ModDown epilogue with the Galois
+// gather, rescale, the elementwise family and the fused diagonal multiply-accumulate.
+// Every kernel is HBM/L2-streaming integer work: one thread owns two adjacent coefficients of a
+// limb (128-bit loads/stores), grid.y walks limbs, grid.z walks batch entries.
+#include "hx_kernels.cuh"
+
+namespace hx {
+
+constexpr int kThreads = 256;
+static inline unsigned blocks_for(int N) { return (unsigned)((N / 2 + kThreads - 1) / kThreads); }
+
+// ---------------------------------------------------------------------------------------------
+// ApproxSwitchCRTBasis (row P4/P5): out_j = ( sum_i [x_i * hatinv_i]_{q_i} * (Qhat_i mod p_j) ) mod p_j
+// hatinv as Shoup pairs; the matrix in Montgomery form so one REDC finishes each output.
+// Sum of n_in <= 8 products, each < 2^60 * p_j  ->  < p_j * 2^64, REDC precondition holds.
+__global__ void __launch_bounds__(kThreads) k_baseconv(DevTables T, const BaseConvTable* __restrict__ tab, int n_in, int n_out,
+                                                       const u64* __restrict__ in, size_t in_bs, u64* __restrict__ out, size_t out_bs) {
+    __shared__ u64 s_mat[8 * kMaxPrimes];
+    __shared__ u64 s_q[kMaxPrimes], s_qi[kMaxPrimes];
+    for (int i = threadIdx.x; i < n_in * n_out; i += blockDim.x) s_mat[i] = tab->mat[i];
+    for (int j = threadIdx.x; j < n_out; j += blockDim.x) {
+        PrimeConst pc = T.pc[tab->dst[j]];
+        s_q[j] = pc.q;
+        s_qi[j] = pc.qinv_neg;
+    }
+    __syncthreads();
+    int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    const u64* src = in + (size_t)blockIdx.z * in_bs + idx;
+    u64* dst = out + (size_t)blockIdx.z * out_bs + idx;
+    u64 y0[8], y1[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        if (i < n_in) {
+            ulonglong2 x = ldg128(src + (size_t)i * T.N);
+            u64 q = T.pc[tab->src[i]].q;
+            y0[i] = shoup_mul(x.x, tab->hatinv[i], tab->hatinv_sh[i], q);
+            y1[i] = shoup_mul(x.y, tab->hatinv[i], tab->hatinv_sh[i], q);
+        }
+    }
+    for (int j = 0; j < n_out; j++) {
+        u128d a0 = {0, 0}, a1 = {0, 0};
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            if (i < n_in) {
+                u64 m = s_mat[i * n_out + j];
+                acc_wide(a0, y0[i], m);
+                acc_wide(a1, y1[i], m);
+            }
+        }
+        ulonglong2 r;
+        r.x = redc(a0, s_q[j], s_qi[j]);
+        r.y = redc(a1, s_q[j], s_qi[j]);
+        st128(dst + (size_t)j * T.N, r);
+    }
+}
+
+void launch_baseconv(const DevTables& T, const BaseConvTable* tab, int n_in, int n_out, const u64* in, size_t in_bs,
+                     u64* out, size_t out_bs, int nbatch, cudaStream_t st) {
+    dim3 grid(blocks_for(T.N), 1, nbatch);
+    k_baseconv<<<grid, kThreads, 0, st>>>(T, tab, n_in, n_out, in, in_bs, out, out_bs);
+}
+
+// ---------------------------------------------------------------------------------------------
+// EvalFastKeySwitchCoreExt (row P5): c~0 = sum_j d_j (.) b_j ; c~1 = sum_j d_j (.) a_j over the
+// nl Q-limbs and K P-limbs.  Keys are streamed once from HBM (L1 no-allocate), digits are re-read
+// by every batch entry (hoisted rotations share them) and stay L2-resident.  Keys are stored in
+// Montgomery form, so each output is 3 wide MACs + one REDC (3*q^2 < q*2^64).
+__global__ void __launch_bounds__(kThreads) k_ks_inner(DevTables T, const u64* __restrict__ digits, int ndig, int nl, int L, int K,
+                                                       const u64* const* __restrict__ keyA, const u64* const* __restrict__ keyB,
+                                                       u64* __restrict__ out, size_t out_bs) {
+    int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    int i = blockIdx.y;                        // extended limb index 0..nl+K-1
+    int kl = i < nl ? i : i - nl + L;          // limb index inside the key / prime index
+    const PrimeConst pc = T.pc[kl];
+    const int ext = nl + K;
+    const u64* ka = keyA[blockIdx.z];
+    const u64* kb = keyB[blockIdx.z];
+    u128d b0 = {0, 0}, b1 = {0, 0}, a0 = {0, 0}, a1 = {0, 0};
+    for (int j = 0; j < ndig; j++) {
+        ulonglong2 d = ldg128(digits + ((size_t)j * ext + i) * T.N + idx);
+        size_t koff = ((size_t)j * (L + K) + kl) * T.N + idx;
+        ulonglong2 vb = ld_stream128(kb + koff);
+        ulonglong2 va = ld_stream128(ka + koff);
+        acc_wide(b0, d.x, vb.x);
+        acc_wide(b1, d.y, vb.y);
+        acc_wide(a0, d.x, va.x);
+        acc_wide(a1, d.y, va.y);
+    }
+    u64* o = out + (size_t)blockIdx.z * out_bs + (size_t)i * T.N + idx;
+    ulonglong2 r;
+    r.x = redc(b0, pc.q, pc.qinv_neg);
+    r.y = redc(b1, pc.q, pc.qinv_neg);
+    st128(o, r);
+    r.x = redc(a0, pc.q, pc.qinv_neg);
+    r.y = redc(a1, pc.q, pc.qinv_neg);
+    st128(o + (size_t)ext * T.N, r);
+}
+
+void launch_ks_inner(const DevTables& T, const u64* digits, int ndig, int nl, int L, int K, const u64* const* keyA,
+                     const u64* const* keyB, u64* out, size_t out_bs, int nbatch, cudaStream_t st) {
+    dim3 grid(blocks_for(T.N), nl + K, nbatch);
+    k_ks_inner<<<grid, kThreads, 0, st>>>(T, digits, ndig, nl, L, K, keyA, keyB, out, out_bs);
+}
+
+// ---------------------------------------------------------------------------------------------
+// ApproxModDown epilogue (row P5) fused with "+ c0" and the automorphism gather (row P3):
+//   out[i][j] = (ct[i][m] - conv[i][m]) * P^-1 + addend[i][m],  m = map[j]
+// grid.y = limb (nl), grid.z = batch*2 + component; addend ([comps][nl][N]) applies to components < addend_comps.
+__global__ void __launch_bounds__(kThreads) k_moddown_finish(DevTables T, const u64* __restrict__ ct, size_t ct_bs, const u64* __restrict__ conv,
+                                                             size_t conv_bs, const u64* __restrict__ addend, int addend_comps, const u32* const* __restrict__ maps,
+                                                             u64* __restrict__ out, size_t out_bs, int nl, int ext, ScalarTable pinv) {
+    int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    int i = blockIdx.y;
+    int batch = blockIdx.z >> 1, comp = blockIdx.z & 1;
+    const u64 q = T.pc[i].q;
+    const u64* c = ct + (size_t)batch * ct_bs + ((size_t)comp * ext + i) * T.N;
+    const u64* v = conv + (size_t)batch * conv_bs + ((size_t)comp * nl + i) * T.N;
+    const u64* ad = (addend != nullptr && comp < addend_comps) ? addend + ((size_t)comp * nl + i) * T.N : nullptr;
+    const u32* map = maps ? maps[batch] : nullptr;
+    u64 r[2];
+#pragma unroll
+    for (int e = 0; e < 2; e++) {
+        int m = map ? (int)map[idx + e] : idx + e;
+        u64 d = sub_mod(c[m], v[m], q);
+        d = shoup_mul(d, pinv.v[i], pinv.sh[i], q);
+        if (ad) d = add_mod(d, ad[m], q);
+        r[e] = d;
+    }
+    ulonglong2 o = {r[0], r[1]};
+    st128(out + (size_t)batch * out_bs + ((size_t)comp * nl + i) * T.N + idx, o);
+}
+
+void launch_moddown_finish(const DevTables& T, const u64* ct, size_t ct_bs, const u64* conv, size_t conv_bs, const u64* addend,
+                           int addend_comps, const u32* const* maps, u64* out, size_t out_bs, int nl, const ScalarTable& pinv, int nbatch,
+                           cudaStream_t st) {
+    dim3 grid(blocks_for(T.N), nl, nbatch * 2);
+    int ext = (int)(ct_bs / (2 * (size_t)T.N));   // ct batch entry = [2][ext][N]
+    k_moddown_finish<<<grid, kThreads, 0, st>>>(T, ct, ct_bs, conv, conv_bs, addend, addend_comps, maps, out, out_bs, nl, ext, pinv);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Elementwise family (row P8). grid.y = limb, grid.z = component.
+__global__ void __launch_bounds__(kThreads) k_ew(DevTables T, int op, u64* __restrict__ out, const u64* __restrict__ a, const u64* __restrict__ b,
+                                                 size_t cs_out, size_t cs_a, size_t cs_b) {
+    int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    int i = blockIdx.y;
+    const PrimeConst pc = T.pc[i];
+    size_t off = (size_t)i * T.N + idx;
+    ulonglong2 x = *reinterpret_cast<const ulonglong2*>(a + blockIdx.z * cs_a + off);
+    ulonglong2 y = *reinterpret_cast<const ulonglong2*>(b + blockIdx.z * cs_b + off);
+    ulonglong2 r;
+    if (op == EW_ADD) { r.x = add_mod(x.x, y.x, pc.q); r.y = add_mod(x.y, y.y, pc.q); }
+    else if (op == EW_SUB) { r.x = sub_mod(x.x, y.x, pc.q); r.y = sub_mod(x.y, y.y, pc.q); }
+    else { r.x = mulmod(x.x, y.x, pc); r.y = mulmod(x.y, y.y, pc); }
+    st128(out + blockIdx.z * cs_out + off, r);
+}
+void launch_ew(const DevTables& T, EwOp op, u64* out, const u64* a, const u64* b, int nl, int ncomp, size_t cs_out, size_t cs_a,
+               size_t cs_b, cudaStream_t st) {
+    dim3 grid(blocks_for(T.N), nl, ncomp);
+    k_ew<<<grid, kThreads, 0, st>>>(T, (int)op, out, a, b, cs_out, cs_a, cs_b);
+}
+
+__global__ void __launch_bounds__(kThreads) k_mul_scalar(DevTables T, u64* __restrict__ out, const u64* __restrict__ a, ScalarTable s,
+                                                         size_t cs_out, size_t cs_a) {
+    int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    int i = blockIdx.y;
+    const u64 q = T.pc[i].q;
+    size_t off = (size_t)i * T.N + idx;
+    ulonglong2 x = *reinterpret_cast<const ulonglong2*>(a + blockIdx.z * cs_a + off);
+    x.x = shoup_mul(x.x, s.v[i], s.sh[i], q);
+    x.y = shoup_mul(x.y, s.v[i], s.sh[i], q);
+    st128(out + blockIdx.z * cs_out + off, x);
+}
+void launch_mul_scalar(const DevTables& T, u64* out, const u64* a, const ScalarTable& s, int nl, int ncomp, size_t cs_out, size_t cs_a,
+                       cudaStream_t st) {
+    dim3 grid(blocks_for(T.N), nl, ncomp);
+    k_mul_scalar<<<grid, kThreads, 0, st>>>(T, out, a, s, cs_out, cs_a);
+}
+
+__global__ void __launch_bounds__(kThreads) k_add_scalar(DevTables T, u64* __restrict__ out, const u64* __restrict__ a, ScalarTable s) {
+    int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    int i = blockIdx.y;
+    const u64 q = T.pc[i].q;
+    size_t off = (size_t)i * T.N + idx;
+    ulonglong2 x = *reinterpret_cast<const ulonglong2*>(a + off);
+    x.x = add_mod(x.x, s.v[i], q);
+    x.y = add_mod(x.y, s.v[i], q);
+    st128(out + off, x);
+}
+void launch_add_scalar(const DevTables& T, u64* out, const u64* a, const ScalarTable& s, int nl, cudaStream_t st) {
+    dim3 grid(blocks_for(T.N), nl, 1);
+    k_add_scalar<<<grid, kThreads, 0, st>>>(T, out, a, s);
+}
+
+// EvalMultCore (row P6, single product): out = (a0*b0, a0*b1 + a1*b0, a1*b1).
+__global__ void __launch_bounds__(kThreads) k_tensor(DevTables T, u64* __restrict__ out, const u64* __restrict__ a, size_t cs_a,
+                                                     const u64* __restrict__ b, size_t cs_b, int nl) {
+    int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    int i = blockIdx.y;
+    const PrimeConst pc = T.pc[i];
+    size_t off = (size_t)i * T.N + idx;
+    ulonglong2 a0 = *reinterpret_cast<const ulonglong2*>(a + off);
+    ulonglong2 a1 = *reinterpret_cast<const ulonglong2*>(a + cs_a + off);
+    ulonglong2 b0 = *reinterpret_cast<const ulonglong2*>(b + off);
+    ulonglong2 b1 = *reinterpret_cast<const ulonglong2*>(b + cs_b + off);
+    size_t cs_o = (size_t)nl * T.N;
+    ulonglong2 r;
+    r.x = mulmod(a0.x, b0.x, pc); r.y = mulmod(a0.y, b0.y, pc);
+    st128(out + off, r);
+    r.x = add_mod(mulmod(a0.x, b1.x, pc), mulmod(a1.x, b0.x, pc), pc.q);
+    r.y = add_mod(mulmod(a0.y, b1.y, pc), mulmod(a1.y, b0.y, pc), pc.q);
+    st128(out + cs_o + off, r);
+    r.x = mulmod(a1.x, b1.x, pc); r.y = mulmod(a1.y, b1.y, pc);
+    st128(out + 2 * cs_o + off, r);
+}
+void launch_tensor(const DevTables& T, u64* out, const u64* a, size_t cs_a, const u64* b, size_t cs_b, int nl, cudaStream_t st) {
+    dim3 grid(blocks_for(T.N), nl, 1);
+    k_tensor<<<grid, kThreads, 0, st>>>(T, out, a, cs_a, b, cs_b, nl);
+}
+
+// AutomorphismTransform (row P3): out[l][j] = in[l][map[j]].
+__global__ void __launch_bounds__(kThreads) k_automorph(int N, u64* __restrict__ out, const u64* __restrict__ in, const u32* __restrict__ map) {
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= N) return;
+    size_t off = (size_t)blockIdx.y * N;
+    out[off + idx] = in[off + map[idx]];
+}
+void launch_automorph(const DevTables& T, u64* out, const u64* in, const u32* map, int nlimbs_total, cudaStream_t st) {
+    dim3 grid((T.N + kThreads - 1) / kThreads, nlimbs_total, 1);
+    k_automorph<<<grid, kThreads, 0, st>>>(T.N, out, in, map);
+}
+
+// PrecomputeAutoMap: map[brev(j)] = brev(((2j+1)*k mod 2N) >> 1).
+__global__ void k_automap(int N, int logN, u64 k, u32* __restrict__ map) {
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= N) return;
+    u64 m = (u64)N << 1;
+    u64 idx = ((((u64)j << 1) + 1) * k & (m - 1)) >> 1;
+    u32 jr = __brev((u32)j) >> (32 - logN);
+    u32 ir = __brev((u32)idx) >> (32 - logN);
+    map[jr] = ir;
+}
+void launch_automap(int N, int logN, u64 k, u32* map, cudaStream_t st) {
+    k_automap<<<(N + 255) / 256, 256, 0, st>>>(N, logN, k, map);
+}
+
+// x -> x * 2^64 mod q (Montgomery form) for keys / database blocks at load time.
+__global__ void __launch_bounds__(kThreads) k_to_mont(DevTables T, u64* __restrict__ data, LimbMap lm) {
+    int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    size_t b = (size_t)blockIdx.y + (size_t)blockIdx.z * gridDim.y;
+    const PrimeConst pc = T.pc[lm.prime[b % lm.period]];
+    u64* p = data + b * T.N + idx;
+    ulonglong2 x = *reinterpret_cast<ulonglong2*>(p);
+    x.x = redc(mul_wide(x.x, pc.r2), pc.q, pc.qinv_neg);
+    x.y = redc(mul_wide(x.y, pc.r2), pc.q, pc.qinv_neg);
+    st128(p, x);
+}
+void launch_to_mont(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, cudaStream_t st) {
+    // nbatch must be a multiple of lm.period; split so grid.y stays a multiple of the period
+    int per = lm.period;
+    int groups = nbatch / per;
+    dim3 grid(blocks_for(T.N), per, groups);
+    k_to_mont<<<grid, kThreads, 0, st>>>(T, data, lm);
+}
+
+// ---------------------------------------------------------------------------------------------
+// DropLastElementAndScale (row P7).
+// prep: tmp_i = centred_lift(last) * (-q_l^-1) mod q_i.  The centred lift of v > q_l/2 is v - q_l,
+// and q_l * (-q_l^-1) = -1, so the correction is simply "+1".
+__global__ void __launch_bounds__(kThreads) k_rescale_prep(DevTables T, const u64* __restrict__ last, size_t last_bs, u64* __restrict__ tmp,
+                                                           size_t tmp_bs, int nl, ScalarTable c) {
+    int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    int i = blockIdx.y;
+    const u64 q = T.pc[i].q;
+    const u64 half = T.pc[nl - 1].q >> 1;
+    ulonglong2 v = *reinterpret_cast<const ulonglong2*>(last + blockIdx.z * last_bs + idx);
+    ulonglong2 r;
+    r.x = shoup_mul(v.x, c.v[i], c.sh[i], q);
+    r.y = shoup_mul(v.y, c.v[i], c.sh[i], q);
+    if (v.x > half) r.x = add_mod(r.x, 1, q);
+    if (v.y > half) r.y = add_mod(r.y, 1, q);
+    st128(tmp + blockIdx.z * tmp_bs + (size_t)i * T.N + idx, r);
+}
+void launch_rescale_prep(const DevTables& T, const u64* last, size_t last_bs, u64* tmp, size_t tmp_bs, int nl,
+                         const ScalarTable& negqlinv, int nbatch, cudaStream_t st) {
+    dim3 grid(blocks_for(T.N), nl - 1, nbatch);
+    k_rescale_prep<<<grid, kThreads, 0, st>>>(T, last, last_bs, tmp, tmp_bs, nl, negqlinv);
+}
+__global__ void __launch_bounds__(kThreads) k_rescale_finish(DevTables T, u64* __restrict__ out, size_t out_bs, const u64* __restrict__ c, size_t c_bs,
+                                                             const u64* __restrict__ tmp, size_t tmp_bs, ScalarTable s) {
+    int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    int i = blockIdx.y;
+    const u64 q = T.pc[i].q;
+    size_t off = (size_t)i * T.N + idx;
+    ulonglong2 x = *reinterpret_cast<const ulonglong2*>(c + blockIdx.z * c_bs + off);
+    ulonglong2 t = *reinterpret_cast<const ulonglong2*>(tmp + blockIdx.z * tmp_bs + off);
+    x.x = add_mod(shoup_mul(x.x, s.v[i], s.sh[i], q), t.x, q);
+    x.y = add_mod(shoup_mul(x.y, s.v[i], s.sh[i], q), t.y, q);
+    st128(out + blockIdx.z * out_bs + off, x);
+}
+void launch_rescale_finish(const DevTables& T, u64* out, size_t out_bs, const u64* c, size_t c_bs, const u64* tmp, size_t tmp_bs,
+                           int nl, const ScalarTable& qlinv, int nbatch, cudaStream_t st) {
+    dim3 grid(blocks_for(T.N), nl - 1, nbatch);
+    k_rescale_finish<<<grid, kThreads, 0, st>>>(T, out, out_bs, c, c_bs, tmp, tmp_bs, qlinv);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Fused diagonal multiply-accumulate (row P6): sum over diagonals d of rotq[d] (x) db[d]
+// (sender_diag.cpp:70-77: 512 EvalMultNoRelin + 511 EvalAddInPlace).  The database block is in
+// Montgomery form; products are accumulated un-reduced in 128 bits and folded every kFold diagonals
+// (2*kFold*q^2 < 2^128 for q < 2^60), so the kernel does 4 wide MACs per 32 bytes streamed.
+constexpr int kFold = 64;
+__global__ void __launch_bounds__(kThreads) k_diag_mac(DevTables T, const u64* __restrict__ rotq, const u64* __restrict__ db,
+                                                       u64* __restrict__ out, int ndiag, int nl) {
+    int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    int i = blockIdx.y;
+    const PrimeConst pc = T.pc[i];
+    const size_t cs = (size_t)nl * T.N, ds = 2 * cs;
+    size_t off = (size_t)i * T.N + idx;
+    u64 r[3][2] = {{0, 0}, {0, 0}, {0, 0}};
+    for (int d0 = 0; d0 < ndiag; d0 += kFold) {
+        u128d acc[3][2] = {};
+        int d1 = min(ndiag, d0 + kFold);
+        for (int d = d0; d < d1; d++) {
+            const u64* qa = rotq + (size_t)d * ds + off;
+            const u64* da = db + (size_t)d * ds + off;
+            ulonglong2 a0 = ldg128(qa), a1 = ldg128(qa + cs);
+            ulonglong2 b0 = ld_stream128(da), b1 = ld_stream128(da + cs);
+            acc_wide(acc[0][0], a0.x, b0.x); acc_wide(acc[0][1], a0.y, b0.y);
+            acc_wide(acc[1][0], a0.x, b1.x); acc_wide(acc[1][1], a0.y, b1.y);
+            acc_wide(acc[1][0], a1.x, b0.x); acc_wide(acc[1][1], a1.y, b0.y);
+            acc_wide(acc[2][0], a1.x, b1.x); acc_wide(acc[2][1], a1.y, b1.y);
+        }
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+#pragma unroll
+            for (int e = 0; e < 2; e++)
+                r[c][e] = add_mod(r[c][e], redc(fold128(acc[c][e], pc.q, pc.mu64), pc.q, pc.qinv_neg), pc.q);
+    }
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        ulonglong2 o = {r[c][0], r[c][1]};
+        st128(out + (size_t)c * cs + off, o);
+    }
+}
+void launch_diag_mac(const DevTables& T, const u64* rotq, const u64* db, u64* out, int ndiag, int nl, cudaStream_t st) {
+    dim3 grid(blocks_for(T.N), nl, 1);
+    k_diag_mac<<<grid, kThreads, 0, st>>>(T, rotq, db, out, ndiag, nl);
+}
+
+}  // namespace hx

@@ -1,0 +1,77 @@
+// hx_kernels.cuh -- launch interface of the sm_100a kernels (definitions in hx_kernels.cu).
+// Polynomial data: uint64 limb-major [limb][N], EVALUATION form unless stated, canonical residues.
+#pragma once
+#include "hx_modarith.cuh"
+
+namespace hx {
+
+constexpr int kMaxPrimes = 40;       // L + K upper bound (approach 2 needs 19 + 6)
+constexpr int kMaxDigits = 4;
+
+// prime index of the b-th polynomial of a batch = prime[b % period]
+struct LimbMap {
+    int period;
+    short prime[kMaxPrimes];
+};
+
+struct DevTables {
+    int N, logN;
+    int nprimes;
+    const PrimeConst* pc;        // [nprimes]
+    const ulonglong2* tw_fwd;    // [nprimes][N]  {psi^brev(i), shoup}
+    const ulonglong2* tw_inv;    // [nprimes][N]  {psi^-brev(i), shoup}
+};
+
+// ---- NTT (row P2)
+void launch_ntt(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, bool inverse, cudaStream_t st);
+
+// ---- base conversion (rows P4, P5): coefficient-domain ApproxSwitchCRTBasis
+struct BaseConvTable {          // device-resident
+    int n_in, n_out;
+    short src[8];               // prime index of each source limb
+    short dst[kMaxPrimes];      // prime index of each target limb
+    u64 hatinv[8], hatinv_sh[8];           // (Q/q_i)^-1 mod q_i  (Shoup pair)
+    u64 mat[8 * kMaxPrimes];               // (Q/q_i) * 2^64 mod p_j  (Montgomery form), [i][j]
+};
+// in: [nbatch][n_in][N] (stride_in limbs between batches), out: [nbatch][n_out][N]
+void launch_baseconv(const DevTables& T, const BaseConvTable* tab, int n_in, int n_out, const u64* in, size_t in_batch_stride,
+                     u64* out, size_t out_batch_stride, int nbatch, cudaStream_t st);
+
+// ---- key-switch inner product (row P5): ct0/ct1[i] = sum_j digit_j[i] * keyB_j/keyA_j[i]
+// digits: [ndig][nl+K][N]; keys (Montgomery form): [dnum][L+K][N]; out0,out1: [nl+K][N] per batch entry.
+void launch_ks_inner(const DevTables& T, const u64* digits, int ndig, int nl, int L, int K,
+                     const u64* const* keyA, const u64* const* keyB, u64* out, size_t out_batch_stride,
+                     int nbatch, cudaStream_t st);
+
+// ---- ModDown epilogue (+ optional add of c0, + optional automorphism gather) (rows P3, P5)
+// out[i][j] = ( (ct[i][m] - conv[i][m]) * Pinv_i + (addend ? addend[i][m] : 0) ),  m = map ? map[j] : j
+struct ScalarTable { u64 v[kMaxPrimes]; u64 sh[kMaxPrimes]; };
+void launch_moddown_finish(const DevTables& T, const u64* ct, size_t ct_batch_stride, const u64* conv, size_t conv_batch_stride,
+                           const u64* addend, int addend_comps, const u32* const* maps, u64* out, size_t out_batch_stride, int nl,
+                           const ScalarTable& pinv, int nbatch, cudaStream_t st);
+
+// ---- elementwise family (row P8)
+enum EwOp { EW_ADD = 0, EW_SUB = 1, EW_MUL = 2 };
+void launch_ew(const DevTables& T, EwOp op, u64* out, const u64* a, const u64* b, int nl, int ncomp, size_t comp_stride_out,
+               size_t comp_stride_a, size_t comp_stride_b, cudaStream_t st);
+void launch_mul_scalar(const DevTables& T, u64* out, const u64* a, const ScalarTable& s, int nl, int ncomp, size_t cs_out, size_t cs_a, cudaStream_t st);
+void launch_add_scalar(const DevTables& T, u64* out, const u64* a, const ScalarTable& s, int nl, cudaStream_t st);
+// EvalMultCore: (a0*b0, a0*b1+a1*b0, a1*b1); a,b: [2][.][N] with component strides; out [3][nl][N]
+void launch_tensor(const DevTables& T, u64* out, const u64* a, size_t cs_a, const u64* b, size_t cs_b, int nl, cudaStream_t st);
+void launch_automorph(const DevTables& T, u64* out, const u64* in, const u32* map, int nlimbs_total, cudaStream_t st);
+void launch_automap(int N, int logN, u64 k, u32* map, cudaStream_t st);
+void launch_to_mont(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, cudaStream_t st);
+
+// ---- rescale (row P7)
+// last: [N] coefficient form of limb nl-1 ; tmp out: [nl-1][N] = lift(last)*(-q_l^-1) mod q_i
+void launch_rescale_prep(const DevTables& T, const u64* last, size_t last_batch_stride, u64* tmp, size_t tmp_batch_stride,
+                         int nl, const ScalarTable& negqlinv, int nbatch, cudaStream_t st);
+// out_i = c_i * qlinv_i + tmp_i
+void launch_rescale_finish(const DevTables& T, u64* out, size_t out_bs, const u64* c, size_t c_bs, const u64* tmp, size_t tmp_bs,
+                           int nl, const ScalarTable& qlinv, int nbatch, cudaStream_t st);
+
+// ---- fused diagonal multiply-accumulate (row P6)
+// rotq: [ndiag][2][nl][N]; db (Montgomery form): [ndiag][2][nl][N]; out: [3][nl][N] (overwritten)
+void launch_diag_mac(const DevTables& T, const u64* rotq, const u64* db, u64* out, int ndiag, int nl, cudaStream_t st);
+
+}  // namespace hx

@@ -1,0 +1,170 @@
+"""Host-side mirror of the lbcrypto::CryptoContext<DCRTPoly> subset the reference's Sender path
+uses, over the C ABI of libhydia_b200.so. Method names follow the reference's
+call sites (cc->EvalAdd, cc->EvalMultNoRelin, ...); "InPlace" variants return the new ciphertext."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from ._lib import F64P, I32P, U64P, VP, check_int, check_ptr
+
+
+def _u64p(a: np.ndarray):
+    assert a.dtype == np.uint64 and a.flags.c_contiguous
+    return a.ctypes.data_as(U64P)
+
+
+class Ciphertext:
+    """Ciphertext<DCRTPoly> handle (device resident)."""
+
+    def __init__(self, cc: "CryptoContext", handle):
+        self.cc = cc
+        self._h = check_ptr(handle)
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            _lib.load().hx_ct_free(h)
+
+    def info(self):
+        v = [C.c_int() for _ in range(4)]
+        check_int(_lib.load().hx_ct_info(self._h, *[C.byref(x) for x in v]))
+        return tuple(x.value for x in v)   # ncomp, nlimbs, level, noise_deg
+
+    ncomp = property(lambda s: s.info()[0])
+    nlimbs = property(lambda s: s.info()[1])
+    def GetLevel(self): return self.info()[2]
+    def GetNoiseScaleDeg(self): return self.info()[3]
+
+    def to_numpy(self) -> np.ndarray:
+        ncomp, nl, _, _ = self.info()
+        out = np.empty((ncomp, nl, self.cc.N), dtype=np.uint64)
+        check_int(_lib.load().hx_ct_download(self._h, _u64p(out)))
+        return out
+
+
+class CryptoContext:
+    """CryptoContext<DCRTPoly> for CKKS / FIXEDMANUAL / HYBRID (src/main.cpp:169-179)."""
+
+    def __init__(self, N: int, q: Sequence[int], p: Sequence[int], psi_q: Sequence[int], psi_p: Sequence[int],
+                 dnum: int, scale_bits: int = 45, device: int = 0):
+        self.N, self.L, self.K, self.dnum, self.scale_bits, self.device = N, len(q), len(p), dnum, scale_bits, device
+        self.q, self.p = list(q), list(p)
+        arr = lambda v: np.array([int(x) for x in v], dtype=np.uint64)
+        self._lib = _lib.load()
+        self._h = check_ptr(self._lib.hx_ctx_create(N, self.L, self.K, dnum, _u64p(arr(q)), _u64p(arr(p)), _u64p(arr(psi_q)),
+                                                    _u64p(arr(psi_p)), scale_bits, device))
+
+    @classmethod
+    def generate(cls, depth: int = 11, scale_bits: int = 45, first_mod_bits: int = 60, ring_dim: int = 0,
+                 num_large_digits: int = 0, device: int = 0) -> "CryptoContext":
+        """GenCryptoContext(HEStd_128_classic, depth, ScalingModSize 45, FIXEDMANUAL) (src/main.cpp:169-175)."""
+        lib = _lib.load()
+        N, L, K, d = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        q, p, sq, sp = (np.zeros(40, dtype=np.uint64) for _ in range(4))
+        check_int(lib.hx_params_generate(depth, scale_bits, first_mod_bits, ring_dim, num_large_digits, C.byref(N), C.byref(L),
+                                         C.byref(K), C.byref(d), _u64p(q), _u64p(p), _u64p(sq), _u64p(sp)))
+        return cls(N.value, q[:L.value].tolist(), p[:K.value].tolist(), sq[:L.value].tolist(), sp[:K.value].tolist(), d.value,
+                   scale_bits, device)
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            self._lib.hx_ctx_destroy(h)
+
+    # ---- getters the reference uses
+    def GetRingDimension(self) -> int: return self.N
+    def GetBatchSize(self) -> int: return self.N // 2
+    def sync(self): check_int(self._lib.hx_ctx_sync(self._h))
+    def launches(self) -> int: return int(self._lib.hx_ctx_launches(self._h))
+    def galois(self, rotation: int) -> int: return int(self._lib.hx_galois_for_rotation(self._h, rotation))
+
+    # ---- keys / ciphertext transport
+    def load_mult_key(self, a: np.ndarray, b: np.ndarray):
+        check_int(self._lib.hx_key_load_mult(self._h, _u64p(np.ascontiguousarray(a)), _u64p(np.ascontiguousarray(b))))
+
+    def load_auto_key(self, galois: int, a: np.ndarray, b: np.ndarray):
+        check_int(self._lib.hx_key_load_auto(self._h, galois, _u64p(np.ascontiguousarray(a)), _u64p(np.ascontiguousarray(b))))
+
+    def upload(self, data: np.ndarray, level: int = 0, noise_deg: int = 1) -> Ciphertext:
+        data = np.ascontiguousarray(data, dtype=np.uint64)
+        ncomp, nl, n = data.shape
+        assert n == self.N
+        return Ciphertext(self, self._lib.hx_ct_upload(self._h, ncomp, nl, _u64p(data), level, noise_deg))
+
+    def _ct(self, h) -> Ciphertext:
+        return Ciphertext(self, h)
+
+    # ---- evaluation (names as in the reference's cc-> calls)
+    def EvalAdd(self, a, b):
+        if isinstance(b, (int, float)):
+            return self._ct(self._lib.hx_add_const(a._h, float(b)))
+        return self._ct(self._lib.hx_add(a._h, b._h))
+    EvalAddInPlace = EvalAdd
+    def EvalSub(self, a, b):
+        if isinstance(b, (int, float)):
+            return self._ct(self._lib.hx_add_const(a._h, -float(b)))
+        return self._ct(self._lib.hx_sub(a._h, b._h))
+    def EvalMult(self, a, b):
+        if isinstance(b, (int, float)):
+            return self._ct(self._lib.hx_mult_const(a._h, float(b)))
+        return self._ct(self._lib.hx_mult(a._h, b._h))
+    def EvalMultNoRelin(self, a, b): return self._ct(self._lib.hx_mult_norelin(a._h, b._h))
+    def Relinearize(self, a): return self._ct(self._lib.hx_relin(a._h))
+    RelinearizeInPlace = Relinearize
+    def EvalSquare(self, a): return self._ct(self._lib.hx_square(a._h))
+    def Rescale(self, a): return self._ct(self._lib.hx_rescale(a._h))
+    RescaleInPlace = ModReduce = Rescale
+    def LevelReduce(self, a, levels=1): return self._ct(self._lib.hx_level_reduce(a._h, levels))
+    def EvalRotate(self, a, index): return self._ct(self._lib.hx_rotate(a._h, index))
+    def EvalSum(self, a, n): return self._ct(self._lib.hx_eval_sum(a._h, n))
+    def EvalAddMany(self, cts: List[Ciphertext]):
+        arr = (VP * len(cts))(*[c._h for c in cts])
+        return self._ct(self._lib.hx_add_many(arr, len(cts)))
+    EvalAddManyInPlace = EvalAddMany
+
+    class _Digits:
+        def __init__(self, lib, h):
+            self._lib, self._h = lib, check_ptr(h)
+        def __del__(self):
+            h, self._h = getattr(self, "_h", None), None
+            if h:
+                self._lib.hx_digits_free(h)
+
+    def EvalFastRotationPrecompute(self, a): return CryptoContext._Digits(self._lib, self._lib.hx_rot_precompute(a._h))
+    def EvalFastRotation(self, a, index, m, digits):
+        assert m == 2 * self.N
+        return self._ct(self._lib.hx_rot_fast(a._h, index, digits._h))
+
+    def EvalChebyshevSeries(self, a, coeffs, lo, hi):
+        c = np.ascontiguousarray(coeffs, dtype=np.float64)
+        return self._ct(self._lib.hx_cheby_series(a._h, c.ctypes.data_as(F64P), len(c), lo, hi))
+    def EvalPoly(self, a, coeffs):
+        c = np.ascontiguousarray(coeffs, dtype=np.float64)
+        return self._ct(self._lib.hx_poly(a._h, c.ctypes.data_as(F64P), len(c)))
+
+    # ---- fused HyDia entry points
+    def db_register(self, block: int, diag: int, data: np.ndarray):
+        check_int(self._lib.hx_db_register(self._h, block, diag, _u64p(np.ascontiguousarray(data, dtype=np.uint64))))
+    def db_blocks(self) -> int: return int(self._lib.hx_db_blocks(self._h))
+    def score_diag(self, query: Ciphertext, ndiag: int = 512) -> List[Ciphertext]:
+        out = (VP * 4096)()
+        n = check_int(self._lib.hx_score_diag(self._h, query._h, ndiag, out, 4096))
+        return [self._ct(out[i]) for i in range(n)]
+    def membership(self, query, ndiag=512, delta=0.44, depth=10) -> Ciphertext:
+        return self._ct(self._lib.hx_membership(self._h, query._h, ndiag, delta, depth))
+    def index(self, query, ndiag=512, delta=0.44, depth=10) -> List[Ciphertext]:
+        out = (VP * 4096)()
+        n = check_int(self._lib.hx_index(self._h, query._h, ndiag, delta, depth, out, 4096))
+        return [self._ct(out[i]) for i in range(n)]
+    def compare(self, a, delta=0.44, depth=10): return self._ct(self._lib.hx_compare(a._h, delta, depth))
+
+    # ---- parity-test hook
+    def ntt(self, data: np.ndarray, primes: Sequence[int], inverse: bool = False) -> np.ndarray:
+        out = np.ascontiguousarray(data, dtype=np.uint64).copy()
+        pr = np.array(list(primes), dtype=np.int32)
+        check_int(self._lib.hx_ntt(self._h, _u64p(out), out.shape[0], pr.ctypes.data_as(I32P), len(pr), 1 if inverse else 0))
+        return out

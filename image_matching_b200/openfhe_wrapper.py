@@ -1,0 +1,65 @@
+"""Mirror of the OpenFHEWrapper namespace (/root/reference/src/openFHE_wrapper.cpp,
+include/openFHE_wrapper.h) for the functions on the HyDia Sender path."""
+from __future__ import annotations
+
+import math
+import sys
+from typing import List
+
+from .engine import Ciphertext, CryptoContext
+
+# openFHE_wrapper.cpp:153-155 and :158-169
+DEPTH_TO_DEGREE = [-1, -1, -1, 5, 13, 27, 59, 119, 247, 495, 1007, 2031]
+F4_COEFS = [0.0, 315.0 / 128.0, 0.0, -420.0 / 128.0, 0.0, 378.0 / 128.0, 0.0, -180.0 / 128.0, 0.0, 35.0 / 128.0]
+
+
+def computeRequiredDepth(approach: int) -> int:
+    """openFHE_wrapper.cpp:6-44."""
+    from .config import ALPHA_DEPTH, COMP_DEPTH
+    return {1: 3 + COMP_DEPTH, 2: 6 + COMP_DEPTH + ALPHA_DEPTH, 3: 2 + COMP_DEPTH, 4: 1 + COMP_DEPTH, 5: 1 + COMP_DEPTH}[approach]
+
+
+def chebyshev_coefficients(func, a: float, b: float, degree: int) -> List[float]:
+    """What cc->EvalChebyshevFunction computes before the series evaluation
+    (OpenFHE EvalChebyshevCoefficients; call site openFHE_wrapper.cpp:174)."""
+    n = degree + 1
+    b_minus_a, b_plus_a = 0.5 * (b - a), 0.5 * (b + a)
+    pi_by_deg = math.pi / float(n)
+    pts = [func(math.cos(pi_by_deg * (i + 0.5)) * b_minus_a + b_plus_a) for i in range(n)]
+    mult = 2.0 / float(n)
+    out = []
+    for i in range(n):
+        s = 0.0
+        for j in range(n):
+            s += pts[j] * math.cos(pi_by_deg * i * (j + 0.5))
+        out.append(s * mult)
+    return out
+
+
+def chebyshevCompare(cc: CryptoContext, ctxt: Ciphertext, delta: float, signDepth: int) -> Ciphertext:
+    """OpenFHEWrapper::chebyshevCompare (openFHE_wrapper.cpp:143-185): x -> ~2 if x >= delta else ~0.
+    Issued as the reference does, one cc-> call per step (the C ABI also has the fused hx_compare)."""
+    if signDepth < 7 or signDepth > 15:
+        print("Error: chebshevCompare requires a depth parameter between 7 and 15", file=sys.stderr)
+        return ctxt
+    degree = DEPTH_TO_DEGREE[signDepth - 4]
+    coeffs = chebyshev_coefficients(lambda x: 1.0 if x >= delta else -1.0, -1.0, 1.0, degree)
+    ctxt = cc.EvalChebyshevSeries(ctxt, coeffs, -1.0, 1.0)
+    ctxt = cc.EvalPoly(ctxt, F4_COEFS)
+    return cc.EvalAdd(ctxt, 1.0)
+
+
+def binaryRotate(cc: CryptoContext, ctxt: Ciphertext, factor: int) -> Ciphertext:
+    """OpenFHEWrapper::binaryRotate (openFHE_wrapper.cpp:103-128): decompose into +-2^k rotations."""
+    batch = cc.GetBatchSize()
+    needed = []
+    while factor != 0:
+        sign = 1 if factor > 0 else -1
+        step = int(pow(2, round(math.log2(abs(factor)))))
+        cur = int(math.fmod(step * sign, batch))
+        if cur != 0:
+            needed.append(step * sign)
+        factor -= step * sign
+    for r in needed:
+        ctxt = cc.EvalRotate(ctxt, r)
+    return ctxt

@@ -1,0 +1,121 @@
+/*
+ * hydia_b200.h -- C ABI of libhydia_b200.so: the B200-native CKKS evaluation engine behind the
+ * HyDia Sender hot path (n7koirala/image_matching).  Plain pointers and sizes only; opaque handles.
+ *
+ * Every entry point names the reference interface it replaces (paths under /root/reference).
+ * The reference reaches all of them through lbcrypto::CryptoContext<DCRTPoly> (OpenFHE v1.2.3);
+ * INTEGRATION.md shows the C++ shim a maintainer adds so src/sender/ *.cpp and
+ * src/openFHE_wrapper.cpp call these instead.
+ *
+ * Conventions
+ *  - Polynomials are uint64 arrays, limb-major [component][limb][N], EVALUATION (NTT) form,
+ *    canonical residues, OpenFHE limb order (q_0..q_{L-1}, then p_0..p_{K-1} for keys).
+ *  - Functions returning a handle return NULL on error; functions returning int return 0 on
+ *    success and non-zero on error; hx_last_error() gives the message (thread-local).  OpenFHE
+ *    throws OpenFHEException in the same situations (missing key, level exhausted).
+ *  - Inputs are never consumed or modified ("InPlace" reference calls become: call, then rebind).
+ *  - All calls are thread-safe per context (the reference enters from up to 48 OpenMP threads,
+ *    include/config.h:21, e.g. src/sender/sender_diag.cpp:23-26).
+ */
+#ifndef HYDIA_B200_H
+#define HYDIA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct hx_ctx hx_ctx;        /* CryptoContext<DCRTPoly>            (include/sender.h:39) */
+typedef struct hx_ct hx_ct;          /* Ciphertext<DCRTPoly>                                      */
+typedef struct hx_digits hx_digits;  /* shared_ptr<vector<DCRTPoly>> from EvalFastRotationPrecompute */
+
+const char* hx_last_error(void);
+int hx_device_count(void);
+
+/* ---- context ----------------------------------------------------------------------------- */
+/* GenCryptoContext result (src/main.cpp:169-175): ring dimension, RNS chain and roots as OpenFHE
+ * generated them; dnum = number of hybrid key-switching digits. */
+hx_ctx* hx_ctx_create(int N, int L, int K, int dnum, const uint64_t* q, const uint64_t* p, const uint64_t* psi_q,
+                      const uint64_t* psi_p, int log2_scale, int device);
+void hx_ctx_destroy(hx_ctx* ctx);
+int hx_ctx_sync(hx_ctx* ctx);                       /* wait for all queued device work */
+uint64_t hx_ctx_launches(hx_ctx* ctx);              /* kernels launched so far (bench accounting) */
+/* FindAutomorphismIndex2nComplex: Galois element of a slot rotation (5^r or 5^-|r| mod 2N) */
+uint32_t hx_galois_for_rotation(hx_ctx* ctx, int rotation);
+
+/* ---- evaluation keys (src/main.cpp:188-206) ------------------------------------------------ */
+/* EvalKey a/b vectors, [dnum][L+K][N] each, plain residues; converted to the engine's layout. */
+int hx_key_load_mult(hx_ctx* ctx, const uint64_t* a, const uint64_t* b);                      /* EvalMultKeyGen */
+int hx_key_load_auto(hx_ctx* ctx, uint32_t galois, const uint64_t* a, const uint64_t* b);     /* EvalRotateKeyGen / EvalSumKeyGen */
+
+/* ---- ciphertexts --------------------------------------------------------------------------- */
+hx_ct* hx_ct_upload(hx_ctx* ctx, int ncomp, int nlimbs, const uint64_t* data, int level, int noise_deg);
+int hx_ct_download(hx_ct* ct, uint64_t* data);      /* data: [ncomp][nlimbs][N] */
+int hx_ct_info(hx_ct* ct, int* ncomp, int* nlimbs, int* level, int* noise_deg);
+hx_ct* hx_ct_clone(hx_ct* ct);
+void hx_ct_free(hx_ct* ct);
+
+/* ---- primitive evaluation ops (call sites: SURVEY.md section 8(b)) ---------------------------- */
+hx_ct* hx_add(hx_ct* a, hx_ct* b);                  /* EvalAdd / EvalAddInPlace   sender_diag.cpp:76 */
+hx_ct* hx_sub(hx_ct* a, hx_ct* b);                  /* EvalSub                                       */
+hx_ct* hx_add_const(hx_ct* a, double c);            /* EvalAddInPlace(ct,double)  openFHE_wrapper.cpp:182 */
+hx_ct* hx_mult_const(hx_ct* a, double c);           /* EvalMult(ct,double)                           */
+hx_ct* hx_mult_norelin(hx_ct* a, hx_ct* b);         /* EvalMultNoRelin            sender_diag.cpp:93 */
+hx_ct* hx_relin(hx_ct* a);                          /* RelinearizeInPlace         sender_diag.cpp:79 */
+hx_ct* hx_mult(hx_ct* a, hx_ct* b);                 /* EvalMult(ct,ct)            sender_hers.cpp:156 */
+hx_ct* hx_square(hx_ct* a);                         /* EvalSquare(InPlace)        sender_hers.cpp:124 */
+hx_ct* hx_rescale(hx_ct* a);                        /* RescaleInPlace             sender_diag.cpp:80 */
+hx_ct* hx_level_reduce(hx_ct* a, int levels);       /* LevelReduceInPlace                            */
+hx_ct* hx_rotate(hx_ct* a, int rotation);           /* EvalRotate                 openFHE_wrapper.cpp:124 */
+hx_ct* hx_eval_sum(hx_ct* a, int n);                /* EvalSum                    sender_diag.cpp:47 */
+hx_ct* hx_add_many(hx_ct* const* cts, int n);       /* EvalAddManyInPlace         sender_diag.cpp:46 */
+hx_digits* hx_rot_precompute(hx_ct* a);             /* EvalFastRotationPrecompute sender_diag.cpp:22 */
+hx_ct* hx_rot_fast(hx_ct* a, int rotation, hx_digits* digits);   /* EvalFastRotation sender_diag.cpp:25 */
+void hx_digits_free(hx_digits* d);
+/* EvalChebyshevSeries on precomputed coefficients / EvalPoly (openFHE_wrapper.cpp:174,179) */
+hx_ct* hx_cheby_series(hx_ct* a, const double* coeffs, int n, double lo, double hi);
+hx_ct* hx_poly(hx_ct* a, const double* coeffs, int n);
+/* OpenFHEWrapper::chebyshevCompare (openFHE_wrapper.cpp:143-185) */
+hx_ct* hx_compare(hx_ct* a, double delta, int sign_depth);
+
+/* ---- fused HyDia Sender path (src/sender/sender_diag.cpp) ---------------------------------- */
+/* Registers database ciphertext serial/db_diagonal/index{block*512+diag}.bin (sender_diag.cpp:87)
+ * as HBM resident; data: [2][L][N]. */
+int hx_db_register(hx_ctx* ctx, int block, int diag, const uint64_t* data);
+int hx_db_blocks(hx_ctx* ctx);
+/* DiagonalSender::computeSimilarity (sender_diag.cpp:12): one score ciphertext per block. */
+int hx_score_diag(hx_ctx* ctx, hx_ct* query, int ndiag, hx_ct** out, int max_out);
+/* DiagonalSender::membershipScenario (sender_diag.cpp:35) */
+hx_ct* hx_membership(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sign_depth);
+/* DiagonalSender::indexScenario (sender_diag.cpp:52) */
+int hx_index(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sign_depth, hx_ct** out, int max_out);
+
+/* ---- building blocks exposed for parity tests ---------------------------------------------- */
+/* DCRTPoly::SetFormat on a host buffer [nbatch][N]; primes[b % nprimes] = prime index of entry b */
+int hx_ntt(hx_ctx* ctx, uint64_t* data, int nbatch, const int* primes, int nprimes, int inverse);
+
+/* ---- synthetic client side (keys / inputs for smoke, bench and tests; not on the Sender path) */
+/* The parameter recipe of GenCryptoContext(HEStd_128_classic, depth, scale 2^45, FIXEDMANUAL)
+ * (src/main.cpp:169-175). ring_dim = 0 selects the smallest standard ring. Arrays sized >= 40. */
+int hx_params_generate(int depth, int scale_bits, int first_mod_bits, int ring_dim, int num_large_digits, int* N, int* L, int* K,
+                       int* dnum, uint64_t* q, uint64_t* p, uint64_t* psi_q, uint64_t* psi_p);
+typedef struct hx_client hx_client;  /* KeyGen + Enroller/Receiver crypto (src/main.cpp:184-206) */
+hx_client* hx_client_create(hx_ctx* ctx, uint64_t seed);
+void hx_client_destroy(hx_client* c);
+int hx_client_gen_mult_key(hx_client* c);                                   /* EvalMultKeyGen */
+int hx_client_gen_rot_keys(hx_client* c, const int* rotations, int n);      /* EvalRotateKeyGen */
+int hx_client_gen_sum_keys(hx_client* c);                                   /* EvalSumKeyGen  */
+/* MakeCKKSPackedPlaintext + Encrypt (openFHE_wrapper.cpp:74-77); values: up to N/2 reals */
+hx_ct* hx_client_encrypt(hx_client* c, const double* values, int n);
+/* Encrypt + register as database ciphertext (DiagonalEnroller::serializeDBThread, enroller_diag.cpp:158) */
+int hx_client_enroll(hx_client* c, int block, int diag, const double* values, int n);
+/* Decrypt + GetRealPackedValue (openFHE_wrapper.cpp:81-85); out: N/2 doubles */
+int hx_client_decrypt(hx_client* c, hx_ct* ct, double* out);
+/* secret key (ternary, N int8) for cross-checks against the CPU oracle in tests */
+int hx_client_secret(hx_client* c, int8_t* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HYDIA_B200_H */

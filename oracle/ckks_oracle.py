@@ -1123,3 +1123,112 @@ class PlainEval:
     def add_const(self, a, c): return PlainCt(a.v + c, a.level, a.deg)
     def rescale(self, a): return PlainCt(a.v, a.level + 1, a.deg - 1)
     def level_reduce(self, a, n): return PlainCt(a.v, a.level + n, a.deg)
+
+
+# ----------------------------------------------------------------------------- HyDia approach 5
+VECTOR_DIM = 512
+MATCH_THRESHOLD = 0.44
+COMP_DEPTH = 10
+
+
+def plaintext_normalize(v: np.ndarray) -> np.ndarray:
+    n = np.linalg.norm(v, axis=-1, keepdims=True)
+    return v / np.where(n == 0, 1.0, n)
+
+
+def diagonal_pack(db: np.ndarray, batch: int) -> np.ndarray:
+    """DiagonalEnroller::serializeDB packing (/root/reference/src/enroller/enroller_diag.cpp:12-53 via
+    splitIntoSquareMatrices :57-86, preprocessToDiagonalForm :99-115, concatenateRows :118-156),
+    written as the explicit loops of the reference."""
+    dim = VECTOR_DIM
+    dbn = plaintext_normalize(db.astype(np.float64))
+    nrows = int(math.ceil(db.shape[0] / dim)) * dim
+    mats = []
+    for i in range(0, nrows, dim):
+        sq = np.zeros((dim, dim))
+        hi = min(i + dim, db.shape[0])
+        if hi > i:
+            sq[:hi - i] = dbn[i:hi]
+        mats.append(sq)
+    diag_mats = []
+    for mtx in mats:
+        d = np.zeros((dim, dim))
+        for i in range(dim):
+            cols = (np.arange(dim) + i) % dim
+            d[i] = mtx[np.arange(dim), cols]
+        diag_mats.append(d)
+    per = batch // dim
+    nout = int(math.ceil(len(diag_mats) / per)) * dim
+    out = np.zeros((nout, batch))
+    for i in range(nout):
+        for j in range(per):
+            m = (i // dim) * per + j
+            if m < len(diag_mats):
+                out[i, j * dim:(j + 1) * dim] = diag_mats[m][i % dim]
+    return out
+
+
+def encrypt_query_diag(orc: Oracle, query: np.ndarray) -> Ct:
+    """DiagonalReceiver::encryptQuery (/root/reference/src/receiver/receiver_diag.cpp:13-26)."""
+    q = plaintext_normalize(np.asarray(query, dtype=np.float64))
+    return orc.encrypt(np.tile(q, orc.P.slots // VECTOR_DIM))
+
+
+def diag_compute_similarity(orc: Oracle, query: Ct, db_cts: List[Ct], ndiag: int = VECTOR_DIM) -> List[Ct]:
+    """DiagonalSender::computeSimilarity (/root/reference/src/sender/sender_diag.cpp:12-33) with
+    computeSimilarityMatrix (:66-83); db_cts[g*ndiag + d] stands for serial/db_diagonal/index*.bin."""
+    digits = orc.fast_rotation_precompute(query)
+    rot = [query] + [orc.fast_rotation(query, i, digits) for i in range(1, ndiag)]
+    scores = []
+    for g in range(len(db_cts) // ndiag):
+        acc = orc.mult_norelin(rot[0], db_cts[g * ndiag])
+        for i in range(1, ndiag):
+            acc = orc.add(acc, orc.mult_norelin(rot[i], db_cts[g * ndiag + i]))
+        scores.append(orc.rescale(orc.relinearize(acc)))
+    return scores
+
+
+def diag_index_scenario(orc: Oracle, query: Ct, db_cts: List[Ct], ndiag: int = VECTOR_DIM) -> List[Ct]:
+    """DiagonalSender::indexScenario (sender_diag.cpp:52-63)."""
+    return [chebyshev_compare(orc, s, MATCH_THRESHOLD, COMP_DEPTH) for s in diag_compute_similarity(orc, query, db_cts, ndiag)]
+
+
+def diag_membership_scenario(orc: Oracle, query: Ct, db_cts: List[Ct], ndiag: int = VECTOR_DIM) -> Ct:
+    """DiagonalSender::membershipScenario (sender_diag.cpp:35-50)."""
+    s = diag_index_scenario(orc, query, db_cts, ndiag)
+    return orc.eval_sum(orc.add_many(s), orc.P.slots)
+
+
+def decrypt_membership(orc: Oracle, ct: Ct) -> bool:
+    """HersReceiver::decryptMembership (/root/reference/src/receiver/receiver_hers.cpp:26-35)."""
+    return bool(orc.decrypt(ct)[0] >= 1.0)
+
+
+def decrypt_index(orc: Oracle, cts: List[Ct]) -> List[int]:
+    """HersReceiver::decryptIndex (receiver_hers.cpp:37-54)."""
+    out = []
+    for i, ct in enumerate(cts):
+        v = orc.decrypt(ct)
+        out.extend(int(j + i * orc.P.slots) for j in np.nonzero(v >= 1.0)[0])
+    return out
+
+
+def hydia_rotation_set(batch: int) -> List[int]:
+    """Rotation keys generated at /root/reference/src/main.cpp:195-206."""
+    rot = list(range(1, VECTOR_DIM))
+    i = VECTOR_DIM
+    while i < batch:
+        rot.append(i); i *= 2
+    i = 1
+    while i < batch:
+        rot.append(-i); i *= 2
+    return rot
+
+
+def read_dat(path: str):
+    """Dataset format of /root/reference/src/main.cpp:56-57, 216-230: n, query[512], db[n][512]."""
+    with open(path) as f:
+        tok = f.read().split()
+    n = int(tok[0])
+    vals = np.array(tok[1:], dtype=np.float64)
+    return n, vals[:VECTOR_DIM], vals[VECTOR_DIM:VECTOR_DIM + n * VECTOR_DIM].reshape(n, VECTOR_DIM)

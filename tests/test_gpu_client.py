@@ -1,0 +1,71 @@
+"""GPU tests of the synthetic client (device keygen / encrypt / decrypt) and of size-independent
+properties at the full BASELINE configuration."""
+import numpy as np
+import pytest
+
+from oracle import ckks_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def small():
+    import image_matching_b200 as hx
+    cc = hx.CryptoContext.generate(depth=11, ring_dim=4096)
+    cl = hx.Client(cc, seed=42)
+    cl.EvalMultKeyGen(); cl.EvalSumKeyGen(); cl.EvalRotateKeyGen([1, 5, -3, 512])
+    return cc, cl
+
+
+def test_client_roundtrip_and_homomorphisms(small):
+    cc, cl = small
+    rng = np.random.default_rng(0)
+    a, b = rng.uniform(-1, 1, cc.N // 2), rng.uniform(-1, 1, cc.N // 2)
+    ca, cb = cl.encrypt(a), cl.encrypt(b)
+    assert np.abs(cl.decrypt(ca) - a).max() <= 1e-7
+    assert np.abs(cl.decrypt(cc.EvalAdd(ca, cb)) - (a + b)).max() <= 1e-7
+    assert np.abs(cl.decrypt(cc.EvalMultNoRelin(ca, cb)) - a * b).max() <= 1e-6      # 3 components, degree 2
+    assert np.abs(cl.decrypt(cc.Rescale(cc.EvalMult(ca, cb))) - a * b).max() <= 1e-6
+    for r in (1, 5, -3, 512):
+        assert np.abs(cl.decrypt(cc.EvalRotate(ca, r)) - np.roll(a, -r)).max() <= 1e-6
+    s = cl.decrypt(cc.EvalSum(cc.LevelReduce(ca, 11), cc.N // 2))
+    assert abs(s[0] - a.sum()) <= 1e-4 and np.abs(s - s[0]).max() <= 1e-4
+
+
+def test_client_ciphertext_decrypts_under_oracle(small):
+    """Cross-check of the product's encode/encrypt against the oracle's decrypt/decode with the same secret."""
+    cc, cl = small
+    P = O.Params(N=cc.N, L=cc.L, K=cc.K, dnum=cc.dnum, alpha=-(-cc.L // cc.dnum), q=cc.q, p=cc.p,
+                 psi_q=O.gen_params(11, ring_dim=cc.N).psi_q, psi_p=O.gen_params(11, ring_dim=cc.N).psi_p)
+    orc = O.Oracle(P)
+    sk = cl.secret().astype(np.int64)
+    assert set(np.unique(sk)) <= {-1, 0, 1}
+    orc.sk = orc.small_to_rns(sk, list(range(P.L + P.K)))
+    a = np.random.default_rng(1).uniform(-1, 1, cc.N // 2)
+    ct = cl.encrypt(a)
+    dec = orc.decrypt(O.Ct(list(ct.to_numpy()), 0, 1))
+    assert np.abs(dec - a).max() <= 1e-7
+
+
+def test_hydia_end_to_end_product_client_small_ring():
+    """Enroll -> query -> membership/index entirely through the product (device keygen + encrypt),
+    decisions identical to the plaintext rule cos >= effective threshold (receiver_hers.cpp:26-54)."""
+    import image_matching_b200 as hx
+    cc = hx.CryptoContext.generate(depth=11, ring_dim=4096)
+    cl = hx.Client(cc, seed=3)
+    cl.EvalMultKeyGen(); cl.EvalSumKeyGen(); cl.EvalRotateKeyGen(list(range(1, 512)))
+    rng = np.random.default_rng(5)
+    n = 2048
+    db = rng.integers(-99, 100, size=(n, 512)).astype(np.float64)
+    db[0] = rng.integers(1, 4, size=512); db[777] = rng.integers(1, 4, size=512)
+    assert cl.enroll_diagonal(db) == 1
+    q = cl.encryptQuery(np.ones(512))
+    snd = hx.DiagonalSender(cc, None, n)
+    scores = snd.computeSimilarity(q)
+    cos = hx.plaintext_normalize(db) @ hx.plaintext_normalize(np.ones(512))
+    assert np.abs(cl.decrypt(scores[0])[:n] - cos).max() <= 1e-4
+    assert cl.decryptIndex(snd.indexScenario(q)) == [0, 777]
+    assert cl.decryptMembership(snd.membershipScenario(q)) is True
+    # a query matching nothing
+    q2 = cl.encryptQuery(rng.integers(-99, 100, size=512).astype(np.float64))
+    assert cl.decryptIndex(snd.indexScenario(q2)) == [] and cl.decryptMembership(snd.membershipScenario(q2)) is False

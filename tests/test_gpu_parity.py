@@ -1,0 +1,190 @@
+"""GPU parity tests: every CUDA op through the C ABI against the CPU oracle on the same keys and
+inputs, BIT-EXACT (integer residues), plus decrypted-level checks with stated tolerances."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import ckks_oracle as O
+from tests.helpers import make_gpu_context, make_oracle, same, up
+
+pytestmark = pytest.mark.gpu
+
+ROTS = [1, 2, 3, 7, 100, 511, -1, -2, -64, 512, 1024]
+
+
+@pytest.fixture(scope="module")
+def env():
+    orc = make_oracle(ring_dim=4096, depth=11, rotations=ROTS + [2 ** i for i in range(11)])
+    cc = make_gpu_context(orc)
+    rng = np.random.default_rng(7)
+    a, b = rng.uniform(-1, 1, orc.P.slots), rng.uniform(-1, 1, orc.P.slots)
+    ca, cb = orc.encrypt(a), orc.encrypt(b)
+    return dict(orc=orc, cc=cc, a=a, b=b, ca=ca, cb=cb, ga=up(cc, ca), gb=up(cc, cb))
+
+
+@pytest.mark.parametrize("logn", [10, 11, 12, 13, 14, 15, 16])
+def test_ntt_bit_exact(logn):
+    """Row P2: forward and inverse NTT of random limbs over Q and P primes, every ring size the
+    approaches use (2^15, 2^16) and the small test rings; also iNTT(NTT(x)) == x."""
+    N = 1 << logn
+    P = O.gen_params(3, ring_dim=N)
+    orc = O.Oracle(P)
+    import image_matching_b200 as hx
+    cc = hx.CryptoContext(P.N, P.q, P.p, P.psi_q, P.psi_p, P.dnum)
+    rng = np.random.default_rng(logn)
+    primes = list(range(P.L + P.K))
+    x = np.stack([rng.integers(0, orc.mods[i], size=N, dtype=np.uint64) for i in primes])
+    # edge values: 0, 1, q-1
+    x[:, 0] = 0; x[:, 1] = 1; x[:, 2] = np.array([m - 1 for m in orc.mods], dtype=np.uint64)
+    want = x.copy(); orc.ntt(want, primes)
+    got = cc.ntt(x, primes)
+    assert np.array_equal(got, want)
+    back = cc.ntt(got, primes, inverse=True)
+    assert np.array_equal(back, x)
+    wanti = x.copy(); orc.ntt(wanti, primes, inverse=True)
+    assert np.array_equal(cc.ntt(x, primes, inverse=True), wanti)
+    # batch with a repeating prime pattern longer than one period
+    xb = np.concatenate([x, x])
+    wb = np.concatenate([want, want])
+    assert np.array_equal(cc.ntt(xb, primes), wb)
+
+
+def test_elementwise_ops_bit_exact(env):
+    orc, cc, ca, cb, ga, gb = (env[k] for k in ("orc", "cc", "ca", "cb", "ga", "gb"))
+    assert same(cc.EvalAdd(ga, gb), orc.add(ca, cb))
+    assert same(cc.EvalSub(ga, gb), orc.sub(ca, cb))
+    for c in (0.25, -0.37, 1.0, 2.4609375, -3.28125, 1e-9, 0.0):
+        assert same(cc.EvalMult(ga, c), orc.mult_const(ca, c))
+        assert same(cc.EvalAdd(ga, c), orc.add_const(ca, c))
+    # constants on a degree-2 ciphertext use scale^2 (GetElementForEvalAddOrSub)
+    m2, g2 = orc.mult_const(ca, 0.5), cc.EvalMult(ga, 0.5)
+    assert same(cc.EvalAdd(g2, -1.0), orc.add_const(m2, -1.0))
+    assert same(cc.LevelReduce(ga, 3), orc.level_reduce(ca, 3))
+    # level alignment by dropping limbs (FIXEDMANUAL)
+    assert same(cc.EvalAdd(cc.LevelReduce(ga, 2), gb), orc.add(orc.level_reduce(ca, 2), cb))
+    assert same(cc.EvalAddMany([ga, gb, ga, gb, ga]), orc.add_many([ca, cb, ca, cb, ca]))
+
+
+def test_tensor_relin_rescale_bit_exact(env):
+    orc, cc, ca, cb, ga, gb = (env[k] for k in ("orc", "cc", "ca", "cb", "ga", "gb"))
+    t, gt = orc.mult_norelin(ca, cb), cc.EvalMultNoRelin(ga, gb)
+    assert same(gt, t)                                        # row P6
+    assert same(cc.EvalAdd(gt, gt), orc.add(t, t))            # 3-component add
+    r, gr = orc.relinearize(t), cc.Relinearize(gt)
+    assert same(gr, r)                                        # rows P4 + P5 (hybrid key switch, l = 12)
+    s, gs = orc.rescale(r), cc.Rescale(gr)
+    assert same(gs, s)                                        # row P7
+    assert same(cc.Rescale(gt), orc.rescale(t))               # rescale of a 3-component ciphertext
+    assert same(cc.EvalMult(ga, gb), r) and same(cc.EvalSquare(ga), orc.square(ca))
+    assert same(cc.Relinearize(ga), ca)                       # no-op on 2 components
+    dec = orc.decrypt(O.Ct(list(gs.to_numpy()), 1, 1))
+    assert np.abs(dec - env["a"] * env["b"]).max() <= 1e-6
+
+
+@pytest.mark.parametrize("drop", [0, 1, 3, 4, 7, 8, 10, 11])
+def test_key_switch_every_level_bit_exact(env, drop):
+    """Hybrid key switch at every digit shape: l = 12..1 limbs -> 3, 2 and 1 digits, ragged last digit."""
+    orc, cc, ca, cb, ga, gb = (env[k] for k in ("orc", "cc", "ca", "cb", "ga", "gb"))
+    la, lb = orc.level_reduce(ca, drop), orc.level_reduce(cb, drop)
+    xa, xb = cc.LevelReduce(ga, drop), cc.LevelReduce(gb, drop)
+    assert same(cc.EvalMult(xa, xb), orc.mult(la, lb))
+    assert same(cc.EvalRotate(xa, 7), orc.rotate(la, 7))
+    if la.nl >= 2:
+        assert same(cc.Rescale(cc.EvalMult(xa, xb)), orc.rescale(orc.mult(la, lb)))
+
+
+def test_rotations_bit_exact(env):
+    orc, cc, ca, ga = env["orc"], env["cc"], env["ca"], env["ga"]
+    for r in ROTS:
+        assert same(cc.EvalRotate(ga, r), orc.rotate(ca, r)), r            # rows P3 + P5
+    dg, gdg = orc.fast_rotation_precompute(ca), cc.EvalFastRotationPrecompute(ga)
+    for r in (0, 1, 3, 511, -64):
+        assert same(cc.EvalFastRotation(ga, r, 2 * orc.N, gdg), orc.fast_rotation(ca, r, dg)), r
+    low, glow = orc.level_reduce(ca, 11), cc.LevelReduce(ga, 11)
+    assert same(cc.EvalSum(glow, orc.P.slots), orc.eval_sum(low, orc.P.slots))
+    from image_matching_b200._lib import HxError
+    with pytest.raises(HxError, match="not generated"):                    # OpenFHE throws on a missing key
+        cc.EvalRotate(ga, 5)
+    with pytest.raises(HxError):
+        cc.Rescale(cc.LevelReduce(ga, 11))                                 # no limb left to drop
+
+
+def test_chebyshev_compare_bit_exact(env):
+    """Rows R4 + P9: the whole chebyshevCompare op DAG (Chebyshev-59 PS, f4 PS, +1) bit for bit,
+    through both the fused hx_compare and the reference-style per-call sequence."""
+    orc, cc = env["orc"], env["cc"]
+    x = np.random.default_rng(3).uniform(-0.3, 0.3, orc.P.slots)
+    x[:6] = [0.93, 0.47, 0.4542, 0.4540, 0.43, -0.9]
+    ct = orc.level_reduce(orc.encrypt(x), 1)
+    g = up(cc, ct)
+    want = orc.chebyshev_compare(ct, 0.44, 10)
+    got = cc.compare(g, 0.44, 10)
+    assert same(got, want)
+    import image_matching_b200 as hx
+    assert same(hx.OpenFHEWrapper.chebyshevCompare(cc, g, 0.44, 10), want)
+    dec = orc.decrypt(want)
+    ref = O.chebyshev_compare(O.PlainEval(), O.PlainCt(x)).v
+    assert np.abs(dec - ref).max() <= 1e-4
+    assert list(dec[:6] >= 1.0) == [True, True, True, False, False, False]
+
+
+def test_hydia_fused_path_bit_exact_small_ring(golden_dir):
+    """Rows R1-R6: fused score_diag / index / membership vs the oracle's per-op restatement of
+    sender_diag.cpp on a ragged database (1300 vectors -> 3 square blocks in one 2048-slot cipher
+    + a second, mostly empty cipher block), and vs the reference-style per-op DiagonalSender."""
+    import image_matching_b200 as hx
+    rots = list(range(1, 512)) + [2 ** i for i in range(11)]
+    orc = make_oracle(ring_dim=4096, depth=11, rotations=rots, seed=5)
+    cc = make_gpu_context(orc)
+    rng = np.random.default_rng(11)
+    n = 2300
+    db = rng.integers(-99, 100, size=(n, 512)).astype(np.float64)
+    q = np.ones(512)
+    db[0] = rng.integers(1, 4, size=512); db[n - 1] = rng.integers(1, 4, size=512)
+    rows = O.diagonal_pack(db, orc.P.slots)
+    assert rows.shape[0] == 1024
+    dbc = [orc.encrypt(r) for r in rows]
+    for i, c in enumerate(dbc):
+        cc.db_register(i // 512, i % 512, np.stack(c.c))
+    qc = O.encrypt_query_diag(orc, q)
+    gq = up(cc, qc)
+    want = O.diag_compute_similarity(orc, qc, dbc)
+    got = cc.score_diag(gq)
+    assert len(got) == 2 and all(same(g, w) for g, w in zip(got, want))
+    widx = [O.chebyshev_compare(orc, s) for s in want]
+    gidx = cc.index(gq)
+    assert all(same(g, w) for g, w in zip(gidx, widx))
+    wm = orc.eval_sum(orc.add_many(widx), orc.P.slots)
+    assert same(cc.membership(gq), wm)
+    # decisions (receiver_hers.cpp:26-54) and score accuracy (main_accuracy.cpp:360)
+    assert O.decrypt_index(orc, widx) == [0, n - 1] and O.decrypt_membership(orc, wm)
+    cos = O.plaintext_normalize(db) @ O.plaintext_normalize(q)
+    s = np.concatenate([orc.decrypt(O.Ct(list(g.to_numpy()), 1, 1)) for g in got])
+    assert np.abs(s[:n] - cos).max() <= 1e-4
+    # reference-style call sequence (511 EvalFastRotation, 512 EvalMultNoRelin, 511 EvalAdd ...), first block only
+    gdb = [up(cc, c) for c in dbc[:512]]
+    snd = hx.DiagonalSender(cc, None, 2048, fused=False, db_loader=lambda i: gdb[i])
+    per_op = snd.computeSimilarity([gq])
+    assert len(per_op) == 1 and same(per_op[0], want[0])
+
+
+def test_full_ring_ops_bit_exact():
+    """N = 2^15, 12 + 4 limbs (the configuration of configs[0..1]): key switch, rescale, hoisted
+    rotation and tensor product bit-exact vs the oracle at full size."""
+    orc = make_oracle(ring_dim=None, depth=11, rotations=[1, 300, -8])
+    assert orc.N == 32768
+    cc = make_gpu_context(orc)
+    rng = np.random.default_rng(9)
+    a, b = rng.uniform(-1, 1, orc.P.slots), rng.uniform(-1, 1, orc.P.slots)
+    ca, cb = orc.encrypt(a), orc.encrypt(b)
+    ga, gb = up(cc, ca), up(cc, cb)
+    t = orc.mult_norelin(ca, cb)
+    r = orc.relinearize(t)
+    gr = cc.Relinearize(cc.EvalMultNoRelin(ga, gb))
+    assert same(gr, r)
+    assert same(cc.Rescale(gr), orc.rescale(r))
+    dg, gdg = orc.fast_rotation_precompute(ca), cc.EvalFastRotationPrecompute(ga)
+    for rot in (1, 300):
+        assert same(cc.EvalFastRotation(ga, rot, 2 * orc.N, gdg), orc.fast_rotation(ca, rot, dg))
+    assert same(cc.EvalRotate(ga, -8), orc.rotate(ca, -8))

@@ -1,0 +1,113 @@
+"""CPU tests: the oracle against every known answer the reference holds for the path
+(SURVEY.md §8(c) items 1-4). No GPU, no product code."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import ckks_oracle as O
+
+
+def test_parameter_recipe_matches_reference_sizes():
+    # Appendix B / tools/figures/15IndexTotals.csv: approach 5 -> N = 2^15, L = 12, K = 4, dnum 3
+    P = O.gen_params(11)
+    assert (P.N, P.L, P.K, P.dnum, P.alpha) == (32768, 12, 4, 3, 4)
+    assert P.q[0] == 0xFFFFFFFFFFC0001              # largest 60-bit prime = 1 mod 2^16
+    assert all(x % (2 * P.N) == 1 for x in P.q + P.p)
+    assert len(set(P.q + P.p)) == 16
+    assert [x.bit_length() for x in P.q[1:]] == [46, 45] * 5 + [46]
+    # ciphertext bytes 2*L*N*8 = 6.29 MB, one evaluation key 2*dnum*(L+K)*N*8 = 25.17 MB
+    assert 2 * P.L * P.N * 8 == 6291456 and 2 * P.dnum * (P.L + P.K) * P.N * 8 == 25165824
+    for q, psi in zip(P.q + P.p, P.psi_q + P.psi_p):
+        assert pow(psi, P.N, q) == q - 1
+
+
+def test_ps_degrees():
+    assert O.compute_degrees_ps(59) == (4, 4)      # Chebyshev degree 59 (COMP_DEPTH 10 -> DEPTH_TO_DEGREE[6])
+    assert O.compute_degrees_ps(9) == (4, 2)       # f4, degree 9
+
+
+def test_compare_matches_signapprox_golden(golden_dir):
+    """tools/figures/signApprox.csv `combined` = chebyshevCompare(0.44, 10) as checked in by the authors."""
+    g = np.load(os.path.join(golden_dir, "signapprox.npz"))
+    out = O.chebyshev_compare(O.PlainEval(), O.PlainCt(g["input"]), 0.44, 10)
+    assert out.level == 10 and out.deg == 1            # COMP_DEPTH levels consumed
+    assert np.abs(out.v - g["combined"]).max() <= 1e-4  # 5.9e-5 measured
+    # effective decision threshold (>= 1.0, receiver_hers.cpp:30) sits between 0.4540 and 0.4542
+    x = g["input"]
+    assert np.all(out.v[x >= 0.4542][x[x >= 0.4542] <= 0.6] >= 1.0) and np.all(out.v[x <= 0.4540] < 1.0)
+
+
+def test_chebyshev_division_reconstructs():
+    rng = np.random.default_rng(0)
+    f = list(rng.normal(size=28)); g = [0.0] * 16 + [1.0]
+    q, r = O.long_div_cheb(f, g)
+    # evaluate both sides on a grid in the Chebyshev basis (q's free term is stored doubled)
+    xs = np.linspace(-1, 1, 33)
+    T = lambda c: np.polynomial.chebyshev.chebval(xs, c)
+    qq = list(q); qq[0] /= 2
+    assert np.allclose(T(f), T(qq) * T(g) + T(r), atol=1e-9)
+
+
+@pytest.fixture(scope="module")
+def small():
+    P = O.gen_params(11, ring_dim=2048)
+    orc = O.Oracle(P)
+    orc.keygen(3); orc.mult_keygen(); orc.rot_keygen([1, 2, 5, -1, -4, 512] + [2 ** i for i in range(10)])
+    return orc
+
+
+def test_encrypted_ops_small_ring(small):
+    orc = small
+    rng = np.random.default_rng(1)
+    a, b = rng.uniform(-1, 1, orc.P.slots), rng.uniform(-1, 1, orc.P.slots)
+    ca, cb = orc.encrypt(a), orc.encrypt(b)
+    assert np.abs(orc.decrypt(ca) - a).max() < 1e-7
+    assert np.abs(orc.decrypt(orc.rescale(orc.mult(ca, cb))) - a * b).max() < 1e-7
+    for r in (1, 5, -1, -4, 512):
+        assert np.abs(orc.decrypt(orc.rotate(ca, r)) - np.roll(a, -r)).max() < 1e-7
+    dg = orc.fast_rotation_precompute(ca)
+    fr, pr = orc.fast_rotation(ca, 2, dg), orc.rotate(ca, 2)
+    assert all(np.array_equal(x, y) for x, y in zip(fr.c, pr.c))      # hoisted == plain, bit for bit
+    s = orc.eval_sum(orc.level_reduce(ca, 10), orc.P.slots)
+    assert abs(orc.decrypt(s)[0] - a.sum()) < 1e-5
+    assert np.abs(orc.decrypt(orc.add_const(orc.mult_const(ca, -0.37), 0.25)) - (a * -0.37 + 0.25)).max() < 1e-7
+
+
+def test_encrypted_compare_small_ring(small):
+    orc = small
+    x = np.random.default_rng(2).uniform(-0.3, 0.3, orc.P.slots)
+    x[:4] = [0.93, 0.47, 0.43, -0.9]
+    ct = orc.level_reduce(orc.encrypt(x), 1)
+    out = orc.chebyshev_compare(ct)
+    assert out.nl == 1 and out.level == 11
+    ref = O.chebyshev_compare(O.PlainEval(), O.PlainCt(x)).v
+    dec = orc.decrypt(out)
+    assert np.abs(dec - ref).max() < 1e-4
+    assert dec[0] >= 1.0 and dec[1] >= 1.0 and dec[2] < 1.0 and dec[3] < 1.0
+
+
+@pytest.mark.slow
+def test_hydia_2_10_known_answer(golden_dir):
+    """run_artifact.sh:7-27 `./ImageMatching ../test/2_10.dat 5`: membership true, index [0]
+    (tools/gen_dataset.sh:66-72), scores within 1e-4 of plaintext cosine (main_accuracy.cpp:360).
+    Full parameters (N = 2^15, 12+4 limbs); ~2 minutes on 8 cores."""
+    g = np.load(os.path.join(golden_dir, "dat_2_10.npz"))
+    n, q, db = int(g["n"]), g["query"].astype(np.float64), g["db"].astype(np.float64)
+    P = O.gen_params(11)
+    orc = O.Oracle(P)
+    orc.keygen(1); orc.mult_keygen()
+    orc.rot_keygen(list(range(1, 512)) + [2 ** i for i in range(14)])   # rotations the path uses
+    rows = O.diagonal_pack(db, P.slots)
+    assert rows.shape == (512, 16384)
+    dbc = [orc.encrypt(r) for r in rows]
+    qc = O.encrypt_query_diag(orc, q)
+    scores = O.diag_compute_similarity(orc, qc, dbc)
+    cos = O.plaintext_normalize(db) @ O.plaintext_normalize(q)
+    s = orc.decrypt(scores[0])
+    assert np.abs(s[:n] - cos).max() <= 1e-4 and np.abs(s[n:]).max() <= 1e-4
+    assert abs(cos[0] - 0.92680) < 1e-5
+    idx = [O.chebyshev_compare(orc, x) for x in scores]
+    assert O.decrypt_index(orc, idx) == [0]
+    m = orc.eval_sum(orc.add_many(idx), P.slots)
+    assert O.decrypt_membership(orc, m) is True

@@ -6,7 +6,8 @@ from . import _lib
 from .client import Client, diagonal_pack, hydia_rotation_set, plaintext_normalize
 from .engine import Ciphertext, CryptoContext
 from .sender import DiagonalSender, Sender
+from .sharded import ShardedDiagonalSender, block_range
 from . import openfhe_wrapper as OpenFHEWrapper
 
-__all__ = ["CryptoContext", "Ciphertext", "Client", "DiagonalSender", "Sender", "OpenFHEWrapper", "diagonal_pack",
+__all__ = ["CryptoContext", "Ciphertext", "Client", "DiagonalSender", "Sender", "ShardedDiagonalSender", "block_range", "OpenFHEWrapper", "diagonal_pack",
            "hydia_rotation_set", "plaintext_normalize"]

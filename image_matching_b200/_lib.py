@@ -20,11 +20,20 @@ SIGNATURES = {
     "hx_ctx_destroy": (None, [VP]),
     "hx_ctx_sync": (C.c_int, [VP]),
     "hx_ctx_launches": (C.c_uint64, [VP]),
+    "hx_prof_kinds": (C.c_int, []),
+    "hx_prof_name": (C.c_char_p, [C.c_int]),
+    "hx_prof_enable": (C.c_int, [VP, C.c_int]),
+    "hx_prof_reset": (C.c_int, [VP]),
+    "hx_prof_read": (C.c_int, [VP, C.c_int, U64P, F64P, F64P]),
+    "hx_timer_start": (C.c_int, [VP]),
+    "hx_timer_stop": (C.c_int, [VP, F64P]),
     "hx_galois_for_rotation": (C.c_uint32, [VP, C.c_int]),
     "hx_key_load_mult": (C.c_int, [VP, U64P, U64P]),
     "hx_key_load_auto": (C.c_int, [VP, C.c_uint32, U64P, U64P]),
     "hx_ct_upload": (VP, [VP, C.c_int, C.c_int, U64P, C.c_int, C.c_int]),
     "hx_ct_download": (C.c_int, [VP, U64P]),
+    "hx_ct_upload_dev": (VP, [VP, C.c_int, C.c_int, VP, C.c_int, C.c_int]),
+    "hx_ct_download_dev": (C.c_int, [VP, VP]),
     "hx_ct_info": (C.c_int, [VP, I32P, I32P, I32P, I32P]),
     "hx_ct_clone": (VP, [VP]),
     "hx_ct_free": (None, [VP]),

@@ -100,6 +100,11 @@ class Client:
                                                  v.ctypes.data_as(F64P), len(v)))
         return len(rows) // VECTOR_DIM
 
+    def enroll_row(self, block: int, diag: int, row: np.ndarray):
+        """Encrypt one packed row as database ciphertext index{block*512+diag} (enroller_diag.cpp:158-166)."""
+        v = np.ascontiguousarray(row, dtype=np.float64)
+        check_int(self._lib.hx_client_enroll(self._h, block, diag, v.ctypes.data_as(F64P), len(v)))
+
     def encryptQuery(self, query: np.ndarray) -> List[Ciphertext]:
         """DiagonalReceiver::encryptQuery: normalise, tile batch/512 times, encrypt."""
         q = plaintext_normalize(np.asarray(query, dtype=np.float64))

@@ -7,7 +7,7 @@
 
 using namespace hx;
 
-struct hx_ctx { Engine* eng; };
+struct hx_ctx { std::shared_ptr<Engine> eng; };
 struct hx_ct { Ct ct; };
 struct hx_digits { std::shared_ptr<Engine::Digits> dg; };
 struct hx_client { Client* cl; };
@@ -54,16 +54,30 @@ hx_ctx* hx_ctx_create(int N, int L, int K, int dnum, const uint64_t* q, const ui
         if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0)
             throw std::runtime_error("no CUDA device: libhydia_b200 has no CPU fallback");
         hx_ctx* c = new hx_ctx;
-        c->eng = new Engine(N, L, K, dnum, (const u64*)q, (const u64*)p, (const u64*)psi_q, (const u64*)psi_p, log2_scale, device);
+        c->eng = std::make_shared<Engine>(N, L, K, dnum, (const u64*)q, (const u64*)p, (const u64*)psi_q, (const u64*)psi_p, log2_scale, device);
         return c;)
 }
 void hx_ctx_destroy(hx_ctx* ctx) {
     if (!ctx) return;
-    delete ctx->eng;
     delete ctx;
 }
 int hx_ctx_sync(hx_ctx* ctx) { HX_TRY_INT(need(ctx, "ctx"); ctx->eng->sync();) }
 uint64_t hx_ctx_launches(hx_ctx* ctx) { return ctx ? ctx->eng->launches : 0; }
+int hx_prof_kinds(void) { return PK_COUNT; }
+const char* hx_prof_name(int kind) { return prof_kind_name(kind); }
+int hx_prof_enable(hx_ctx* ctx, int mask) { HX_TRY_INT(need(ctx, "ctx"); ctx->eng->prof_enable((unsigned)mask);) }
+int hx_prof_reset(hx_ctx* ctx) { HX_TRY_INT(need(ctx, "ctx"); ctx->eng->prof_reset();) }
+int hx_prof_read(hx_ctx* ctx, int kind, uint64_t* launches, double* ms, double* bytes) {
+    HX_TRY_INT(
+        need(ctx, "ctx");
+        if (kind < 0 || kind >= PK_COUNT) throw std::runtime_error("hx_prof_read: bad kind");
+        ctx->eng->prof_collect();
+        if (launches) *launches = ctx->eng->prof_launches[kind];
+        if (ms) *ms = ctx->eng->prof_ms[kind];
+        if (bytes) *bytes = ctx->eng->prof_bytes[kind];)
+}
+int hx_timer_start(hx_ctx* ctx) { HX_TRY_INT(need(ctx, "ctx"); ctx->eng->timer_start();) }
+int hx_timer_stop(hx_ctx* ctx, double* ms) { HX_TRY_INT(need(ctx, "ctx"); need(ms, "ms"); *ms = ctx->eng->timer_stop_ms();) }
 uint32_t hx_galois_for_rotation(hx_ctx* ctx, int rotation) { return ctx ? (uint32_t)ctx->eng->galois_for_rotation(rotation) : 0; }
 
 int hx_key_load_mult(hx_ctx* ctx, const uint64_t* a, const uint64_t* b) {
@@ -78,6 +92,25 @@ hx_ct* hx_ct_upload(hx_ctx* ctx, int ncomp, int nlimbs, const uint64_t* data, in
         need(ctx, "ctx"); need(data, "data");
         if (ncomp < 1 || ncomp > 3 || nlimbs < 1 || nlimbs > ctx->eng->L) throw std::runtime_error("hx_ct_upload: bad shape");
         return wrap(ctx->eng->upload((const u64*)data, ncomp, nlimbs, level, noise_deg));)
+}
+hx_ct* hx_ct_upload_dev(hx_ctx* ctx, int ncomp, int nlimbs, const void* dev_data, int level, int noise_deg) {
+    HX_TRY_PTR(
+        need(ctx, "ctx"); need(dev_data, "dev_data");
+        if (ncomp < 1 || ncomp > 3 || nlimbs < 1 || nlimbs > ctx->eng->L) throw std::runtime_error("hx_ct_upload_dev: bad shape");
+        Engine* e = ctx->eng.get();
+        std::lock_guard<std::recursive_mutex> g(e->mu);
+        Ct c = e->new_ct(ncomp, nlimbs, level, noise_deg);
+        HX_CUDA(cudaMemcpyAsync(c->d, dev_data, sizeof(u64) * (size_t)ncomp * nlimbs * e->N, cudaMemcpyDeviceToDevice, e->st));
+        e->sync();
+        return wrap(c);)
+}
+int hx_ct_download_dev(hx_ct* ct, void* dev_data) {
+    HX_TRY_INT(
+        need(ct, "ct"); need(dev_data, "dev_data");
+        Engine* e = ct->ct->eng;
+        std::lock_guard<std::recursive_mutex> g(e->mu);
+        HX_CUDA(cudaMemcpyAsync(dev_data, ct->ct->d, sizeof(u64) * (size_t)ct->ct->ncomp * ct->ct->nl * e->N, cudaMemcpyDeviceToDevice, e->st));
+        e->sync();)
 }
 int hx_ct_download(hx_ct* ct, uint64_t* data) { HX_TRY_INT(need(ct, "ct"); need(data, "data"); ct->ct->eng->download(ct->ct, (u64*)data);) }
 int hx_ct_info(hx_ct* ct, int* ncomp, int* nlimbs, int* level, int* noise_deg) {
@@ -154,7 +187,7 @@ int hx_index(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sign_depth,
 int hx_ntt(hx_ctx* ctx, uint64_t* data, int nbatch, const int* primes, int nprimes, int inverse) {
     HX_TRY_INT(
         need(ctx, "ctx"); need(data, "data"); need(primes, "primes");
-        Engine* e = ctx->eng;
+        Engine* e = ctx->eng.get();
         std::lock_guard<std::recursive_mutex> g(e->mu);
         size_t words = (size_t)nbatch * e->N;
         u64* d = e->alloc_words(words);

@@ -128,7 +128,7 @@ static void fft_inplace(std::vector<std::complex<double>>& a, int sign) {
 }
 
 // ------------------------------------------------------------------------------------------ Client
-Client::Client(Engine* e, u64 seed_) : eng(e), seed(seed_) {
+Client::Client(std::shared_ptr<Engine> e, u64 seed_) : keep(e), eng(e.get()), seed(seed_) {
     std::lock_guard<std::recursive_mutex> g(eng->mu);
     const int N = eng->N, np = eng->L + eng->K;
     slot_idx.resize(N / 2);

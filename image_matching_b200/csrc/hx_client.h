@@ -8,7 +8,7 @@ namespace hx {
 
 class Client {
 public:
-    Client(Engine* e, u64 seed);
+    Client(std::shared_ptr<Engine> e, u64 seed);
     ~Client();
     void gen_mult_key();                          // EvalMultKeyGen      (src/main.cpp:188)
     void gen_rot_keys(const int* rot, int n);     // EvalRotateKeyGen    (src/main.cpp:206)
@@ -19,6 +19,7 @@ public:
     void secret(int8_t* out);
     std::vector<long long> encode(const double* values, int n) const;
 
+    std::shared_ptr<Engine> keep;
     Engine* eng;
     u64 seed;
 

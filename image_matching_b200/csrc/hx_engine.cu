@@ -83,8 +83,73 @@ Engine::~Engine() {
     if (have_mult_key_) { cudaFree(mult_key_.a); cudaFree(mult_key_.b); }
     for (auto& kv : db_) cudaFree(kv.second.d);
     for (void* p : owned_) cudaFree(p);
+    for (auto& r : prof_recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+    for (auto ev : prof_pool) cudaEventDestroy(ev);
+    if (timer_a) { cudaEventDestroy(timer_a); cudaEventDestroy(timer_b); }
     cudaFree(d_pc_); cudaFree(d_twf_); cudaFree(d_twi_);
     cudaStreamDestroy(st);
+}
+
+// ------------------------------------------------------------------------------------------ profiler
+const char* prof_kind_name(int kind) {
+    static const char* names[PK_COUNT] = {"ntt_fwd", "ntt_inv", "baseconv", "ks_inner", "moddown", "elementwise", "scalar", "tensor",
+                                          "automorph", "rescale", "diag_mac", "misc"};
+    return (kind >= 0 && kind < PK_COUNT) ? names[kind] : "?";
+}
+Engine::Scope::Scope(Engine* e_, int kind_, int nlaunch, double bytes) : e(e_), kind(kind_) {
+    e->launches += nlaunch;
+    e->prof_launches[kind] += nlaunch;
+    e->prof_bytes[kind] += bytes;
+    if (!((e->prof_on >> kind) & 1u)) return;
+    cudaEvent_t a;
+    auto grab = [&]() {
+        cudaEvent_t ev;
+        if (!e->prof_pool.empty()) { ev = e->prof_pool.back(); e->prof_pool.pop_back(); }
+        else cudaEventCreate(&ev);
+        return ev;
+    };
+    a = grab(); b = grab();
+    cudaEventRecord(a, e->st);
+    e->prof_recs.push_back({kind, a, b});
+}
+Engine::Scope::~Scope() {
+    if (b) cudaEventRecord(b, e->st);
+}
+void Engine::prof_enable(unsigned mask) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    prof_collect();
+    prof_on = mask;
+}
+void Engine::prof_collect() {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (prof_recs.empty()) return;
+    HX_CUDA(cudaStreamSynchronize(st));
+    for (auto& r : prof_recs) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) prof_ms[r.kind] += ms;
+        prof_pool.push_back(r.a);
+        prof_pool.push_back(r.b);
+    }
+    prof_recs.clear();
+}
+void Engine::prof_reset() {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    prof_collect();
+    for (int k = 0; k < PK_COUNT; k++) { prof_launches[k] = 0; prof_ms[k] = 0; prof_bytes[k] = 0; }
+}
+void Engine::timer_start() {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (!timer_a) { HX_CUDA(cudaEventCreate(&timer_a)); HX_CUDA(cudaEventCreate(&timer_b)); }
+    HX_CUDA(cudaEventRecord(timer_a, st));
+}
+double Engine::timer_stop_ms() {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (!timer_a) throw std::runtime_error("timer_stop without timer_start");
+    HX_CUDA(cudaEventRecord(timer_b, st));
+    HX_CUDA(cudaEventSynchronize(timer_b));
+    float ms = 0;
+    HX_CUDA(cudaEventElapsedTime(&ms, timer_a, timer_b));
+    return ms;
 }
 
 // ------------------------------------------------------------------------------------------ memory
@@ -98,7 +163,7 @@ void Engine::sync() { HX_CUDA(cudaStreamSynchronize(st)); }
 
 Ct Engine::new_ct(int ncomp, int nl, int level, int deg) {
     auto c = std::make_shared<CtObj>();
-    c->eng = this; c->ncomp = ncomp; c->nl = nl; c->level = level; c->deg = deg;
+    c->eng = this; c->keep = weak_from_this().lock(); c->ncomp = ncomp; c->nl = nl; c->level = level; c->deg = deg;
     c->d = alloc_words((size_t)ncomp * nl * N);
     return c;
 }
@@ -144,8 +209,10 @@ u64 Engine::P_mod(int i) const {
     return r;
 }
 void Engine::ntt_limbs(u64* data, int nbatch, const std::vector<int>& primes, bool inverse) {
+    int active = 0;
+    for (int b = 0; b < nbatch; b++) active += primes[b % primes.size()] >= 0;
+    Scope sc(this, inverse ? PK_NTT_INV : PK_NTT_FWD, (logN > 11) ? 2 : 1, 16.0 * N * active);
     launch_ntt(T, data, nbatch, limb_map(primes), inverse, st);
-    launches += (logN > 11) ? 2 : 1;
 }
 u64 Engine::galois_for_rotation(int r) const {
     u64 m = 2ull * N;
@@ -162,8 +229,7 @@ const u32* Engine::automap(u64 galois) {
     if (it != automaps_.end()) return it->second;
     u32* m = nullptr;
     HX_CUDA(cudaMalloc(&m, sizeof(u32) * N));
-    launch_automap(N, logN, galois, m, st);
-    launches++;
+    { Scope sc(this, PK_MISC, 1, 4.0 * N); launch_automap(N, logN, galois, m, st); }
     automaps_[galois] = m;
     return m;
 }
@@ -230,9 +296,11 @@ static EvalKey upload_key(Engine& e, const u64* a, const u64* b) {
     std::vector<int> primes;
     for (int i = 0; i < e.L + e.K; i++) primes.push_back(i);
     LimbMap lm = e.limb_map(primes);
-    launch_to_mont(e.T, k.a, e.dnum * (e.L + e.K), lm, e.st);
-    launch_to_mont(e.T, k.b, e.dnum * (e.L + e.K), lm, e.st);
-    e.launches += 2;
+    {
+        Engine::Scope sc(&e, PK_MISC, 2, 32.0 * words);
+        launch_to_mont(e.T, k.a, e.dnum * (e.L + e.K), lm, e.st);
+        launch_to_mont(e.T, k.b, e.dnum * (e.L + e.K), lm, e.st);
+    }
     e.sync();
     return k;
 }
@@ -286,8 +354,7 @@ u64* Engine::ks_precompute(const u64* c, int nl, int* ndig_out) {
         const BaseConvTable* tab = modup_table(nl, j);
         int n_out = nl - sz + K;
         u64* compl_ = alloc_words((size_t)n_out * N);
-        launch_baseconv(T, tab, sz, n_out, scratch, 0, compl_, 0, 1, st);
-        launches++;
+        { Scope sc(this, PK_BASECONV, 1, 8.0 * N * (sz + n_out)); launch_baseconv(T, tab, sz, n_out, scratch, 0, compl_, 0, 1, st); }
         std::vector<int> dst;
         for (int i = 0; i < nl; i++)
             if (i < lo || i >= hi) dst.push_back(i);
@@ -321,24 +388,30 @@ void Engine::ks_core_batch(const u64* digits, int ndig, int nl, const std::vecto
     HX_CUDA(cudaStreamSynchronize(st));   // host vectors go out of scope; tables are tiny
     size_t ct_bs = (size_t)2 * ext * N;
     u64* ct = alloc_words(ct_bs * nb);
-    launch_ks_inner(T, digits, ndig, nl, L, K, (const u64* const*)ptrs, (const u64* const*)(ptrs + nb), ct, ct_bs, nb, st);
-    launches++;
+    {   // algorithmic bytes: evk (a,b) streamed once per key, digits once per launch, outputs once
+        Scope sc(this, PK_KS_INNER, 1, 8.0 * N * ext * ((double)nb * 2 * ndig + ndig + (double)nb * 2));
+        launch_ks_inner(T, digits, ndig, nl, L, K, (const u64* const*)ptrs, (const u64* const*)(ptrs + nb), ct, ct_bs, nb, st);
+    }
     // iNTT of the K P-limbs of both components, in place
     std::vector<int> pm(ext, -1);
     for (int k = 0; k < K; k++) pm[nl + k] = L + k;
     ntt_limbs(ct, nb * 2 * ext, pm, true);
     size_t conv_bs = (size_t)2 * nl * N;
     u64* conv = alloc_words(conv_bs * nb);
-    launch_baseconv(T, moddown_table(nl), K, nl, ct + (size_t)nl * N, (size_t)ext * N, conv, (size_t)nl * N, nb * 2, st);
-    launches++;
+    {
+        Scope sc(this, PK_BASECONV, 1, 8.0 * N * (K + nl) * nb * 2);
+        launch_baseconv(T, moddown_table(nl), K, nl, ct + (size_t)nl * N, (size_t)ext * N, conv, (size_t)nl * N, nb * 2, st);
+    }
     std::vector<int> qm;
     for (int i = 0; i < nl; i++) qm.push_back(i);
     ntt_limbs(conv, nb * 2 * nl, qm, false);
     std::vector<u64> pinv(nl);
     for (int i = 0; i < nl; i++) pinv[i] = invmod(P_mod(i), mods[i]);
-    launch_moddown_finish(T, ct, ct_bs, conv, conv_bs, addend, addend_comps, galois.empty() ? nullptr : (const u32* const*)(ptrs + 2 * nb),
-                          out, out_bs, nl, scalar_table(pinv), nb, st);
-    launches++;
+    {
+        Scope sc(this, PK_MODDOWN, 1, 8.0 * N * nl * nb * (2 + 2 + 2 + (addend ? addend_comps : 0)));
+        launch_moddown_finish(T, ct, ct_bs, conv, conv_bs, addend, addend_comps, galois.empty() ? nullptr : (const u32* const*)(ptrs + 2 * nb),
+                              out, out_bs, nl, scalar_table(pinv), nb, st);
+    }
     free_words(conv);
     free_words(ct);
     free_words(ptrs);
@@ -348,6 +421,7 @@ std::shared_ptr<Engine::Digits> Engine::fast_rotation_precompute(const Ct& a) {
     std::lock_guard<std::recursive_mutex> g(mu);
     auto dg = std::make_shared<Digits>();
     dg->eng = this;
+    dg->keep = weak_from_this().lock();
     dg->nl = a->nl;
     dg->d = ks_precompute(a->comp(1), a->nl, &dg->ndig);
     return dg;
@@ -422,8 +496,7 @@ Ct Engine::add(const Ct& a_, const Ct& b_) {
     if (a->deg != b->deg) throw std::runtime_error("EvalAdd: noiseScaleDeg mismatch");
     if (a->ncomp < b->ncomp) std::swap(a, b);
     Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg);
-    launch_ew(T, EW_ADD, out->d, a->d, b->d, a->nl, b->ncomp, out->comp_stride(), a->comp_stride(), b->comp_stride(), st);
-    launches++;
+    { Scope sc(this, PK_EW, 1, 24.0 * N * a->nl * b->ncomp); launch_ew(T, EW_ADD, out->d, a->d, b->d, a->nl, b->ncomp, out->comp_stride(), a->comp_stride(), b->comp_stride(), st); }
     for (int c = b->ncomp; c < a->ncomp; c++)
         HX_CUDA(cudaMemcpyAsync(out->comp(c), a->comp(c), sizeof(u64) * a->comp_stride(), cudaMemcpyDeviceToDevice, st));
     return out;
@@ -435,8 +508,7 @@ Ct Engine::sub(const Ct& a_, const Ct& b_) {
     if (a->deg != b->deg) throw std::runtime_error("EvalSub: noiseScaleDeg mismatch");
     if (a->ncomp != b->ncomp) throw std::runtime_error("EvalSub: component count mismatch");
     Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg);
-    launch_ew(T, EW_SUB, out->d, a->d, b->d, a->nl, a->ncomp, out->comp_stride(), a->comp_stride(), b->comp_stride(), st);
-    launches++;
+    { Scope sc(this, PK_EW, 1, 24.0 * N * a->nl * a->ncomp); launch_ew(T, EW_SUB, out->d, a->d, b->d, a->nl, a->ncomp, out->comp_stride(), a->comp_stride(), b->comp_stride(), st); }
     return out;
 }
 Ct Engine::add_many(const std::vector<Ct>& v_) {
@@ -475,8 +547,7 @@ std::vector<u64> Engine::const_for_add(double c, int nl, int deg) const {
 Ct Engine::mult_const(const Ct& a, double c) {
     std::lock_guard<std::recursive_mutex> g(mu);
     Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg + 1);
-    launch_mul_scalar(T, out->d, a->d, scalar_table(const_for_mult(c, a->nl)), a->nl, a->ncomp, out->comp_stride(), a->comp_stride(), st);
-    launches++;
+    { Scope sc(this, PK_SCALAR, 1, 16.0 * N * a->nl * a->ncomp); launch_mul_scalar(T, out->d, a->d, scalar_table(const_for_mult(c, a->nl)), a->nl, a->ncomp, out->comp_stride(), a->comp_stride(), st); }
     return out;
 }
 Ct Engine::add_const(const Ct& a, double c) {
@@ -486,8 +557,7 @@ Ct Engine::add_const(const Ct& a, double c) {
     if (c < 0)
         for (int i = 0; i < a->nl; i++) k[i] = (mods[i] - k[i]) % mods[i];
     Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg);
-    launch_add_scalar(T, out->d, a->d, scalar_table(k), a->nl, st);
-    launches++;
+    { Scope sc(this, PK_SCALAR, 1, 16.0 * N * a->nl); launch_add_scalar(T, out->d, a->d, scalar_table(k), a->nl, st); }
     for (int cidx = 1; cidx < a->ncomp; cidx++)
         HX_CUDA(cudaMemcpyAsync(out->comp(cidx), a->comp(cidx), sizeof(u64) * a->comp_stride(), cudaMemcpyDeviceToDevice, st));
     return out;
@@ -498,8 +568,7 @@ Ct Engine::mult_norelin(const Ct& a_, const Ct& b_) {
     align(a, b);
     if (a->ncomp != 2 || b->ncomp != 2) throw std::runtime_error("EvalMultNoRelin supports 2-component inputs");
     Ct out = new_ct(3, a->nl, a->level, a->deg + b->deg);
-    launch_tensor(T, out->d, a->d, a->comp_stride(), b->d, b->comp_stride(), a->nl, st);
-    launches++;
+    { Scope sc(this, PK_TENSOR, 1, 8.0 * N * a->nl * 7); launch_tensor(T, out->d, a->d, a->comp_stride(), b->d, b->comp_stride(), a->nl, st); }
     return out;
 }
 Ct Engine::mult(const Ct& a, const Ct& b) { return relinearize(mult_norelin(a, b)); }
@@ -522,14 +591,12 @@ Ct Engine::rescale(const Ct& a) {
         HX_CUDA(cudaMemcpyAsync(last + (size_t)c * N, a->comp(c) + (size_t)(nl - 1) * N, sizeof(u64) * N, cudaMemcpyDeviceToDevice, st));
     ntt_limbs(last, nc, {nl - 1}, true);
     u64* tmp = alloc_words((size_t)nc * (nl - 1) * N);
-    launch_rescale_prep(T, last, N, tmp, (size_t)(nl - 1) * N, nl, scalar_table(neg), nc, st);
-    launches++;
+    { Scope sc(this, PK_RESCALE, 1, 8.0 * N * nc * nl); launch_rescale_prep(T, last, N, tmp, (size_t)(nl - 1) * N, nl, scalar_table(neg), nc, st); }
     std::vector<int> qm;
     for (int i = 0; i < nl - 1; i++) qm.push_back(i);
     ntt_limbs(tmp, nc * (nl - 1), qm, false);
     Ct out = new_ct(nc, nl - 1, a->level + 1, a->deg - 1);
-    launch_rescale_finish(T, out->d, out->comp_stride(), a->d, a->comp_stride(), tmp, (size_t)(nl - 1) * N, nl, scalar_table(qlinv), nc, st);
-    launches++;
+    { Scope sc(this, PK_RESCALE, 1, 24.0 * N * nc * (nl - 1)); launch_rescale_finish(T, out->d, out->comp_stride(), a->d, a->comp_stride(), tmp, (size_t)(nl - 1) * N, nl, scalar_table(qlinv), nc, st); }
     free_words(tmp);
     free_words(last);
     return out;

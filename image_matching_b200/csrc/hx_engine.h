@@ -25,9 +25,17 @@ namespace hx {
 
 class Engine;
 
+// Kernel families for launch accounting and the optional CUDA-event profiler (bench.py roofline).
+enum ProfKind {
+    PK_NTT_FWD = 0, PK_NTT_INV, PK_BASECONV, PK_KS_INNER, PK_MODDOWN, PK_EW, PK_SCALAR, PK_TENSOR, PK_AUTOMORPH,
+    PK_RESCALE, PK_DIAG_MAC, PK_MISC, PK_COUNT
+};
+const char* prof_kind_name(int kind);
+
 // Ciphertext<DCRTPoly>: ncomp components x nl limbs x N, EVALUATION form, device resident.
 struct CtObj {
     Engine* eng = nullptr;
+    std::shared_ptr<Engine> keep;   // a handle outliving hx_ctx_destroy keeps its engine alive
     u64* d = nullptr;
     int ncomp = 0, nl = 0;
     int level = 0;      // GetLevel(): limbs dropped
@@ -43,7 +51,7 @@ struct EvalKey {        // device, Montgomery form, [dnum][L+K][N] each
     u64* b = nullptr;
 };
 
-class Engine {
+class Engine : public std::enable_shared_from_this<Engine> {
 public:
     Engine(int N, int L, int K, int dnum, const u64* q, const u64* p, const u64* psi_q, const u64* psi_p, int scale_bits, int device);
     ~Engine();
@@ -54,6 +62,27 @@ public:
     cudaStream_t st = nullptr;
     std::recursive_mutex mu;         // the reference enters from up to 48 OpenMP threads
     unsigned long long launches = 0; // kernels launched (bench "gpu_launches")
+
+    // ---- launch accounting + optional CUDA-event profiler (events on `st`, the launching stream)
+    struct ProfRec { int kind; cudaEvent_t a, b; };
+    unsigned prof_on = 0;                    // bitmask of ProfKind families being timed
+    std::vector<ProfRec> prof_recs;
+    std::vector<cudaEvent_t> prof_pool;
+    unsigned long long prof_launches[PK_COUNT] = {};
+    double prof_ms[PK_COUNT] = {};
+    double prof_bytes[PK_COUNT] = {};        // algorithmic bytes (each operand read once, each result written once)
+    struct Scope {                           // RAII around the launch(es) of one kernel family
+        Engine* e; int kind; cudaEvent_t b = nullptr;
+        Scope(Engine* e, int kind, int nlaunch, double bytes);
+        ~Scope();
+    };
+    void prof_enable(unsigned mask);
+    void prof_reset();
+    void prof_collect();                     // sync + fold event pairs into prof_ms
+    // device timer for bench.py (events on `st`)
+    cudaEvent_t timer_a = nullptr, timer_b = nullptr;
+    void timer_start();
+    double timer_stop_ms();
 
     // ---- memory
     u64* alloc_words(size_t words);
@@ -89,7 +118,7 @@ public:
     Ct add_many(const std::vector<Ct>& v);                  // EvalAddManyInPlace (sender_diag.cpp:46)
     // hoisted rotations (sender_diag.cpp:22-26)
     struct DbBlock { u64* d = nullptr; int ndiag = 0; };
-    struct Digits { u64* d = nullptr; int ndig = 0, nl = 0; Engine* eng = nullptr; ~Digits(); };
+    struct Digits { u64* d = nullptr; int ndig = 0, nl = 0; Engine* eng = nullptr; std::shared_ptr<Engine> keep; ~Digits(); };
     std::shared_ptr<Digits> fast_rotation_precompute(const Ct& a);
     Ct fast_rotation(const Ct& a, int r, const std::shared_ptr<Digits>& dg);
 

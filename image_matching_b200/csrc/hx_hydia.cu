@@ -24,8 +24,8 @@ static u64* db_slot(Engine& e, std::map<int, Engine::DbBlock>& db, int block, in
 static void db_finish(Engine& e, u64* dst) {
     std::vector<int> primes;
     for (int i = 0; i < e.L; i++) primes.push_back(i);
+    Engine::Scope sc(&e, PK_MISC, 1, 32.0 * e.L * e.N);
     launch_to_mont(e.T, dst, 2 * e.L, e.limb_map(primes), e.st);
-    e.launches++;
 }
 void Engine::db_register(int block, int diag, const u64* host_ct) {
     std::lock_guard<std::recursive_mutex> g(mu);
@@ -77,8 +77,10 @@ std::vector<Ct> Engine::score_diag(const Ct& query, int ndiag) {
     for (auto& kv : db_) {
         if (kv.second.ndiag < ndiag) throw std::runtime_error("score_diag: database block has fewer diagonals than requested");
         Ct acc = new_ct(3, nl, query->level, query->deg + 1);
-        launch_diag_mac(T, rotq, kv.second.d, acc->d, ndiag, nl, st);
-        launches++;
+        {   // algorithmic bytes: the database block, read once; rotq is re-read per block
+            Scope sc(this, PK_DIAG_MAC, 1, 8.0 * N * nl * 2 * ndiag);
+            launch_diag_mac(T, rotq, kv.second.d, acc->d, ndiag, nl, st);
+        }
         scores.push_back(rescale(relinearize(acc)));
     }
     free_words(rotq);

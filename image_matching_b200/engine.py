@@ -39,6 +39,12 @@ class Ciphertext:
     def GetLevel(self): return self.info()[2]
     def GetNoiseScaleDeg(self): return self.info()[3]
 
+    def download_ptr(self, host_ptr: int):
+        check_int(_lib.load().hx_ct_download(self._h, C.cast(host_ptr, U64P)))
+
+    def download_dev(self, dev_ptr: int):
+        check_int(_lib.load().hx_ct_download_dev(self._h, VP(dev_ptr)))
+
     def to_numpy(self) -> np.ndarray:
         ncomp, nl, _, _ = self.info()
         out = np.empty((ncomp, nl, self.cc.N), dtype=np.uint64)
@@ -80,6 +86,27 @@ class CryptoContext:
     def GetBatchSize(self) -> int: return self.N // 2
     def sync(self): check_int(self._lib.hx_ctx_sync(self._h))
     def launches(self) -> int: return int(self._lib.hx_ctx_launches(self._h))
+    # ---- launch accounting / device timer (bench.py)
+    def prof_enable(self, kinds=None):
+        """Time the named kernel families with CUDA events on the launching stream (None = all, [] = off)."""
+        names = [self._lib.hx_prof_name(k).decode() for k in range(self._lib.hx_prof_kinds())]
+        mask = -1 if kinds is None else sum(1 << names.index(k) for k in kinds)
+        check_int(self._lib.hx_prof_enable(self._h, mask))
+    def prof_reset(self): check_int(self._lib.hx_prof_reset(self._h))
+    def prof_read(self) -> dict:
+        """{kernel family: {"launches", "ms", "bytes"}}; ms is filled only while the profiler is enabled."""
+        out = {}
+        for k in range(self._lib.hx_prof_kinds()):
+            n, ms, by = C.c_uint64(), C.c_double(), C.c_double()
+            check_int(self._lib.hx_prof_read(self._h, k, C.byref(n), C.byref(ms), C.byref(by)))
+            out[self._lib.hx_prof_name(k).decode()] = {"launches": int(n.value), "ms": ms.value, "bytes": by.value}
+        return out
+    def timer_start(self): check_int(self._lib.hx_timer_start(self._h))
+    def timer_stop(self) -> float:
+        ms = C.c_double()
+        check_int(self._lib.hx_timer_stop(self._h, C.byref(ms)))
+        return ms.value
+
     def galois(self, rotation: int) -> int: return int(self._lib.hx_galois_for_rotation(self._h, rotation))
 
     # ---- keys / ciphertext transport
@@ -94,6 +121,14 @@ class CryptoContext:
         ncomp, nl, n = data.shape
         assert n == self.N
         return Ciphertext(self, self._lib.hx_ct_upload(self._h, ncomp, nl, _u64p(data), level, noise_deg))
+
+    def upload_ptr(self, host_ptr: int, ncomp: int, nl: int, level: int = 0, noise_deg: int = 1) -> Ciphertext:
+        """hx_ct_upload from a raw HOST address (e.g. a pinned staging buffer)."""
+        return Ciphertext(self, self._lib.hx_ct_upload(self._h, ncomp, nl, C.cast(host_ptr, U64P), level, noise_deg))
+
+    def upload_dev(self, dev_ptr: int, ncomp: int, nl: int, level: int = 0, noise_deg: int = 1) -> Ciphertext:
+        """hx_ct_upload_dev from a DEVICE address on this context's GPU (NCCL staging buffer)."""
+        return Ciphertext(self, self._lib.hx_ct_upload_dev(self._h, ncomp, nl, VP(dev_ptr), level, noise_deg))
 
     def _ct(self, h) -> Ciphertext:
         return Ciphertext(self, h)
@@ -127,14 +162,14 @@ class CryptoContext:
     EvalAddManyInPlace = EvalAddMany
 
     class _Digits:
-        def __init__(self, lib, h):
-            self._lib, self._h = lib, check_ptr(h)
+        def __init__(self, lib, h, cc=None):
+            self._lib, self._h, self._cc = lib, check_ptr(h), cc
         def __del__(self):
             h, self._h = getattr(self, "_h", None), None
             if h:
                 self._lib.hx_digits_free(h)
 
-    def EvalFastRotationPrecompute(self, a): return CryptoContext._Digits(self._lib, self._lib.hx_rot_precompute(a._h))
+    def EvalFastRotationPrecompute(self, a): return CryptoContext._Digits(self._lib, self._lib.hx_rot_precompute(a._h), self)
     def EvalFastRotation(self, a, index, m, digits):
         assert m == 2 * self.N
         return self._ct(self._lib.hx_rot_fast(a._h, index, digits._h))

@@ -1,0 +1,117 @@
+"""Multi-GPU HyDia Sender: database blocks sharded over ranks, evaluation keys replicated, only the
+per-block result ciphertexts combined.  One process per GPU over torch.distributed
+(NCCL over NVLink on the GPU box; gloo in the CPU tests).
+
+The reference loops over blocks serially in one process (/root/reference/src/sender/sender_diag.cpp:28-30)
+and runs the compare in an OpenMP loop over blocks (:40-43, :57-60); here rank r owns the contiguous
+global blocks [r*B, (r+1)*B) so a decoded index stays j + g*slots (receiver_hers.cpp:46-49).
+
+Exchange steps (the only data-path collectives):
+  indexScenario      gather of the G result ciphertexts (2 x 1 limb each) to rank 0
+  membershipScenario local EvalAddMany, then SUM-reduce of the residues as int64 (world * q0 < 2^63),
+                     one mod-q0 fold, and EvalSum on rank 0.  Modular addition is associative, so the
+                     result is bit-identical to the reference's EvalAddManyInPlace tree over all G blocks.
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import numpy as np
+
+from .config import COMP_DEPTH, MATCH_THRESHOLD, VECTOR_DIM
+from .sender import Sender
+
+
+def block_range(rank: int, world: int, total_blocks: int):
+    """Contiguous block partition: the first (total % world) ranks own one block more."""
+    base, extra = divmod(total_blocks, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+class TorchTransport:
+    """Moves ciphertext residues between the engine and torch tensors on the same device."""
+
+    def __init__(self, cc, device):
+        import torch
+        self.cc, self.device, self.torch = cc, device, torch
+
+    def to_tensor(self, ct):
+        ncomp, nl, _, _ = ct.info()
+        t = self.torch.empty((ncomp, nl, self.cc.N), dtype=self.torch.int64, device=self.device)
+        ct.download_dev(t.data_ptr())
+        return t
+
+    def from_tensor(self, t, level: int, deg: int):
+        t = t.contiguous()
+        return self.cc.upload_dev(t.data_ptr(), t.shape[0], t.shape[1], level, deg)
+
+
+class ShardedDiagonalSender(Sender):
+    """DiagonalSender over `world` ranks. `cc` is this rank's context holding its local blocks
+    (registered as local block ids 0..B-1) and the full (replicated) key set."""
+
+    def __init__(self, cc, pk, numVectors: int, group=None, transport=None, device=None):
+        super().__init__(cc, pk, numVectors)
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.transport = transport or TorchTransport(cc, device)
+
+    # -- per-rank compute: identical to the single-GPU fused path on the local blocks
+    def computeSimilarity(self, queryCipher):
+        return self.cc.score_diag(queryCipher[0], VECTOR_DIM)
+
+    def _local_index(self, queryCipher):
+        return self.cc.index(queryCipher[0], VECTOR_DIM, MATCH_THRESHOLD, COMP_DEPTH)
+
+    def indexScenario(self, queryCipher) -> Optional[List]:
+        """Rank 0 returns the G result ciphertexts in global block order; other ranks return None."""
+        import torch
+        local = self._local_index(queryCipher)
+        meta = local[0].info() if local else None
+        stacked = torch.stack([self.transport.to_tensor(c) for c in local])          # [B][2][1][N]
+        if self.world == 1:
+            return local
+        counts = [block_range(r, self.world, self._total_blocks())[1] - block_range(r, self.world, self._total_blocks())[0]
+                  for r in range(self.world)]
+        bmax = max(counts)
+        if stacked.shape[0] < bmax:                                                   # pad ragged shards for the collective
+            pad = torch.zeros((bmax - stacked.shape[0],) + tuple(stacked.shape[1:]), dtype=stacked.dtype, device=stacked.device)
+            stacked = torch.cat([stacked, pad])
+        bufs = [torch.empty_like(stacked) for _ in range(self.world)] if self.rank == 0 else None
+        self.dist.gather(stacked, bufs, dst=0, group=self.group)
+        if self.rank != 0:
+            return None
+        out = []
+        for r in range(self.world):
+            for b in range(counts[r]):
+                out.append(self.transport.from_tensor(bufs[r][b], meta[2], meta[3]))
+        return out
+
+    def membershipScenario(self, queryCipher):
+        """Rank 0 returns the membership ciphertext; other ranks return None."""
+        cc = self.cc
+        local = self._local_index(queryCipher)
+        part = cc.EvalAddMany(local)
+        if self.world == 1:
+            return cc.EvalSum(part, cc.GetBatchSize())
+        _, _, level, deg = part.info()
+        t = self.transport.to_tensor(part)
+        self.dist.reduce(t, dst=0, op=self.dist.ReduceOp.SUM, group=self.group)
+        if self.rank != 0:
+            return None
+        t = fold_mod(t, cc.q[: t.shape[1]])
+        return cc.EvalSum(self.transport.from_tensor(t, level, deg), cc.GetBatchSize())
+
+    def _total_blocks(self) -> int:
+        import math
+        return int(math.ceil(float(self.numVectors) / float(self.cc.GetBatchSize())))
+
+
+def fold_mod(t, moduli):
+    """Residue-wise t mod q_i over the limb axis (axis 1) of an int64 [ncomp][nl][N] tensor of
+    un-reduced sums (each < world * q_i < 2^63)."""
+    import torch
+    q = torch.tensor([int(m) for m in moduli], dtype=torch.int64, device=t.device).view(1, -1, 1)
+    return torch.remainder(t, q)

@@ -41,6 +41,17 @@ hx_ctx* hx_ctx_create(int N, int L, int K, int dnum, const uint64_t* q, const ui
 void hx_ctx_destroy(hx_ctx* ctx);
 int hx_ctx_sync(hx_ctx* ctx);                       /* wait for all queued device work */
 uint64_t hx_ctx_launches(hx_ctx* ctx);              /* kernels launched so far (bench accounting) */
+/* Launch accounting and the optional CUDA-event profiler (events on the engine's launching stream).
+ * The reference has only wall-clock phase timers (src/main.cpp:342-347); these feed bench.py's
+ * roofline object.  kind in [0, hx_prof_kinds()). bytes = algorithmic bytes of the launches so far. */
+int hx_prof_kinds(void);
+const char* hx_prof_name(int kind);
+int hx_prof_enable(hx_ctx* ctx, int mask);   /* bit k times kernel family k; -1 = all; 0 = off */
+int hx_prof_reset(hx_ctx* ctx);
+int hx_prof_read(hx_ctx* ctx, int kind, uint64_t* launches, double* ms, double* bytes);
+/* device timer on the engine's stream: start records an event, stop records + waits, returns ms */
+int hx_timer_start(hx_ctx* ctx);
+int hx_timer_stop(hx_ctx* ctx, double* ms);
 /* FindAutomorphismIndex2nComplex: Galois element of a slot rotation (5^r or 5^-|r| mod 2N) */
 uint32_t hx_galois_for_rotation(hx_ctx* ctx, int rotation);
 
@@ -52,6 +63,9 @@ int hx_key_load_auto(hx_ctx* ctx, uint32_t galois, const uint64_t* a, const uint
 /* ---- ciphertexts --------------------------------------------------------------------------- */
 hx_ct* hx_ct_upload(hx_ctx* ctx, int ncomp, int nlimbs, const uint64_t* data, int level, int noise_deg);
 int hx_ct_download(hx_ct* ct, uint64_t* data);      /* data: [ncomp][nlimbs][N] */
+/* same, with DEVICE pointers on the context's GPU (NCCL staging buffers of the sharded sender) */
+hx_ct* hx_ct_upload_dev(hx_ctx* ctx, int ncomp, int nlimbs, const void* dev_data, int level, int noise_deg);
+int hx_ct_download_dev(hx_ct* ct, void* dev_data);
 int hx_ct_info(hx_ct* ct, int* ncomp, int* nlimbs, int* level, int* noise_deg);
 hx_ct* hx_ct_clone(hx_ct* ct);
 void hx_ct_free(hx_ct* ct);

@@ -34,6 +34,9 @@ def parse():
     ap.add_argument("--ring-dim", type=int, default=0, help="0 = the 128-bit ring of the reference (2^15)")
     ap.add_argument("--ndiag", type=int, default=512)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--rot-chunk", type=int, default=0, help="override the engine's hoisted-rotation batch size")
+    ap.add_argument("--ncu-range", action="store_true",
+                    help="run one extra step inside cudaProfilerStart/Stop (for ncu --profile-from-start off)")
     return ap.parse_args()
 
 
@@ -176,6 +179,8 @@ def run_b200(args):
 
     bpg, ndiag = args.blocks_per_gpu, args.ndiag
     cc = hx.CryptoContext.generate(depth=11, ring_dim=args.ring_dim, device=local)
+    if args.rot_chunk:
+        cc.set_option("rot_chunk", args.rot_chunk)
     slots = cc.GetBatchSize()
     total_blocks = bpg * world
     n_total = total_blocks * slots
@@ -279,6 +284,13 @@ def run_b200(args):
     ms_e2e, _ = timed(args.steps, True)
     sampler.stop_flag = True
     sampler.join(timeout=2)
+
+    if args.ncu_range:
+        fence()
+        torch.cuda.cudart().cudaProfilerStart()
+        step(q_res, False)
+        fence()
+        torch.cuda.cudart().cudaProfilerStop()
 
     # correctness of what was timed (outside the timed region): decisions as receiver_hers.cpp:26-54
     ok = True

@@ -63,6 +63,15 @@ void hx_ctx_destroy(hx_ctx* ctx) {
 }
 int hx_ctx_sync(hx_ctx* ctx) { HX_TRY_INT(need(ctx, "ctx"); ctx->eng->sync();) }
 uint64_t hx_ctx_launches(hx_ctx* ctx) { return ctx ? ctx->eng->launches : 0; }
+int hx_ctx_set_option(hx_ctx* ctx, const char* name, int value) {
+    HX_TRY_INT(
+        need(ctx, "ctx"); need(name, "name");
+        std::lock_guard<std::recursive_mutex> g(ctx->eng->mu);
+        std::string n(name);
+        if (n == "force_unfused") ctx->eng->force_unfused = value != 0;
+        else if (n == "rot_chunk") ctx->eng->rot_chunk = value;
+        else throw std::runtime_error("hx_ctx_set_option: unknown option " + n);)
+}
 int hx_prof_kinds(void) { return PK_COUNT; }
 const char* hx_prof_name(int kind) { return prof_kind_name(kind); }
 int hx_prof_enable(hx_ctx* ctx, int mask) { HX_TRY_INT(need(ctx, "ctx"); ctx->eng->prof_enable((unsigned)mask);) }

@@ -93,7 +93,7 @@ Engine::~Engine() {
 // ------------------------------------------------------------------------------------------ profiler
 const char* prof_kind_name(int kind) {
     static const char* names[PK_COUNT] = {"ntt_fwd", "ntt_inv", "baseconv", "ks_inner", "moddown", "elementwise", "scalar", "tensor",
-                                          "automorph", "rescale", "diag_mac", "misc"};
+                                          "automorph", "rescale", "diag_mac", "misc", "ks_fused"};
     return (kind >= 0 && kind < PK_COUNT) ? names[kind] : "?";
 }
 Engine::Scope::Scope(Engine* e_, int kind_, int nlaunch, double bytes) : e(e_), kind(kind_) {
@@ -248,6 +248,8 @@ BaseConvTable* Engine::make_table(const std::vector<int>& src, const std::vector
             if (k != i) hat = mulmod(hat, mods[src[k]] % qi, qi);
         h.hatinv[i] = invmod(hat, qi);
         h.hatinv_sh[i] = shoup(h.hatinv[i], qi);
+        h.hatinv_n[i] = mulmod(h.hatinv[i], invmod((u64)N % qi, qi), qi);
+        h.hatinv_n_sh[i] = shoup(h.hatinv_n[i], qi);
         for (int j = 0; j < h.n_out; j++) {
             u64 pj = mods[dst[j]];
             u64 hm = 1;
@@ -375,6 +377,37 @@ u64* Engine::ks_precompute(const u64* c, int nl, int* ndig_out) {
 void Engine::ks_core_batch(const u64* digits, int ndig, int nl, const std::vector<const EvalKey*>& keys, const u64* addend,
                            int addend_comps, const std::vector<u64>& galois, u64* out, size_t out_bs) {
     const int nb = (int)keys.size(), ext = nl + K;
+    std::vector<u64> pinv(nl);
+    for (int i = 0; i < nl; i++) pinv[i] = invmod(P_mod(i), mods[i]);
+    if (fused_ks_supported(logN) && !force_unfused) {
+        // fused pipeline (hx_fused.cu): the evaluation keys are read once, nothing of size 2 x (l+K) is stored
+        for (int b0 = 0; b0 < nb; b0 += kMaxKsBatch) {
+            const int n = std::min(kMaxKsBatch, nb - b0);
+            FusedKsArgs a;
+            a.digits = digits; a.ndig = ndig; a.nl = nl; a.L = L; a.K = K;
+            for (int i = 0; i < n; i++) {
+                a.keyA[i] = keys[b0 + i]->a;
+                a.keyB[i] = keys[b0 + i]->b;
+                a.galois[i] = galois.empty() ? 1u : (u32)galois[b0 + i];
+            }
+            a.tmpP = alloc_words((size_t)n * 2 * K * N);
+            a.conv = alloc_words((size_t)n * 2 * nl * N);
+            a.add0 = (addend && addend_comps >= 1) ? addend : nullptr;
+            a.add1 = (addend && addend_comps >= 2) ? addend + (size_t)nl * N : nullptr;
+            a.out = out + (size_t)b0 * out_bs;
+            a.out_bs = out_bs;
+            a.pinv = scalar_table(pinv);
+            {   // algorithmic bytes of one key switch after ModUp: evk once, digits once per launch,
+                // addend once, result once
+                Scope sc(this, PK_KS_FUSED, 3,
+                         8.0 * N * ((double)n * 2 * ndig * ext + (double)ndig * ext + (double)addend_comps * nl + (double)n * 2 * nl));
+                launch_fused_ks(T, a, moddown_table(nl), n, st);
+            }
+            free_words(a.conv);
+            free_words(a.tmpP);
+        }
+        return;
+    }
     std::vector<const u64*> ha(nb), hb(nb);
     std::vector<const u32*> hm(nb, nullptr);
     for (int i = 0; i < nb; i++) { ha[i] = keys[i]->a; hb[i] = keys[i]->b; }
@@ -405,8 +438,6 @@ void Engine::ks_core_batch(const u64* digits, int ndig, int nl, const std::vecto
     std::vector<int> qm;
     for (int i = 0; i < nl; i++) qm.push_back(i);
     ntt_limbs(conv, nb * 2 * nl, qm, false);
-    std::vector<u64> pinv(nl);
-    for (int i = 0; i < nl; i++) pinv[i] = invmod(P_mod(i), mods[i]);
     {
         Scope sc(this, PK_MODDOWN, 1, 8.0 * N * nl * nb * (2 + 2 + 2 + (addend ? addend_comps : 0)));
         launch_moddown_finish(T, ct, ct_bs, conv, conv_bs, addend, addend_comps, galois.empty() ? nullptr : (const u32* const*)(ptrs + 2 * nb),

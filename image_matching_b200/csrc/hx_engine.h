@@ -28,7 +28,7 @@ class Engine;
 // Kernel families for launch accounting and the optional CUDA-event profiler (bench.py roofline).
 enum ProfKind {
     PK_NTT_FWD = 0, PK_NTT_INV, PK_BASECONV, PK_KS_INNER, PK_MODDOWN, PK_EW, PK_SCALAR, PK_TENSOR, PK_AUTOMORPH,
-    PK_RESCALE, PK_DIAG_MAC, PK_MISC, PK_COUNT
+    PK_RESCALE, PK_DIAG_MAC, PK_MISC, PK_KS_FUSED, PK_COUNT
 };
 const char* prof_kind_name(int kind);
 
@@ -61,6 +61,8 @@ public:
     DevTables T{};
     cudaStream_t st = nullptr;
     std::recursive_mutex mu;         // the reference enters from up to 48 OpenMP threads
+    int rot_chunk = 8;               // hoisted rotations per fused key-switch batch (intermediates stay L2 resident)
+    bool force_unfused = false;      // tests: run the unfused reference kernels instead of hx_fused.cu
     unsigned long long launches = 0; // kernels launched (bench "gpu_launches")
 
     // ---- launch accounting + optional CUDA-event profiler (events on `st`, the launching stream)

@@ -5,7 +5,6 @@
 
 namespace hx {
 
-constexpr int kRotChunk = 32;   // hoisted rotations per key-switch batch (intermediates ~0.27 GB at N=2^15)
 
 // DB ciphertext `diag` of block `block` (serial/db_diagonal/index{block*512+diag}.bin in the
 // reference, sender_diag.cpp:87): stored in Montgomery form for the lazy MAC.
@@ -61,8 +60,9 @@ std::vector<Ct> Engine::score_diag(const Ct& query, int ndiag) {
     HX_CUDA(cudaMemcpyAsync(rotq, query->d, sizeof(u64) * ct_words, cudaMemcpyDeviceToDevice, st));
     int ndig;
     u64* digits = ks_precompute(query->comp(1), nl, &ndig);
-    for (int d0 = 1; d0 < ndiag; d0 += kRotChunk) {
-        int d1 = std::min(ndiag, d0 + kRotChunk);
+    const int chunk = std::max(1, std::min(rot_chunk, kMaxKsBatch));
+    for (int d0 = 1; d0 < ndiag; d0 += chunk) {
+        int d1 = std::min(ndiag, d0 + chunk);
         std::vector<const EvalKey*> keys;
         std::vector<u64> gal;
         for (int d = d0; d < d1; d++) {

@@ -8,6 +8,8 @@ namespace hx {
 constexpr int kMaxPrimes = 40;       // L + K upper bound (approach 2 needs 19 + 6)
 constexpr int kMaxDigits = 4;
 
+struct ScalarTable { u64 v[kMaxPrimes]; u64 sh[kMaxPrimes]; };   // per-limb constants with Shoup quotients
+
 // prime index of the b-th polynomial of a batch = prime[b % period]
 struct LimbMap {
     int period;
@@ -32,6 +34,7 @@ struct BaseConvTable {          // device-resident
     short dst[kMaxPrimes];      // prime index of each target limb
     u64 hatinv[8], hatinv_sh[8];           // (Q/q_i)^-1 mod q_i  (Shoup pair)
     u64 mat[8 * kMaxPrimes];               // (Q/q_i) * 2^64 mod p_j  (Montgomery form), [i][j]
+    u64 hatinv_n[8], hatinv_n_sh[8];       // hatinv * N^-1 mod q_i: folds the inverse transform's scaling (fused path)
 };
 // in: [nbatch][n_in][N] (stride_in limbs between batches), out: [nbatch][n_out][N]
 void launch_baseconv(const DevTables& T, const BaseConvTable* tab, int n_in, int n_out, const u64* in, size_t in_batch_stride,
@@ -45,10 +48,28 @@ void launch_ks_inner(const DevTables& T, const u64* digits, int ndig, int nl, in
 
 // ---- ModDown epilogue (+ optional add of c0, + optional automorphism gather) (rows P3, P5)
 // out[i][j] = ( (ct[i][m] - conv[i][m]) * Pinv_i + (addend ? addend[i][m] : 0) ),  m = map ? map[j] : j
-struct ScalarTable { u64 v[kMaxPrimes]; u64 sh[kMaxPrimes]; };
 void launch_moddown_finish(const DevTables& T, const u64* ct, size_t ct_batch_stride, const u64* conv, size_t conv_batch_stride,
                            const u64* addend, int addend_comps, const u32* const* maps, u64* out, size_t out_batch_stride, int nl,
                            const ScalarTable& pinv, int nbatch, cudaStream_t st);
+
+// ---- fused key switch (hx_fused.cu): rows P2-P5 in three launches per batch of keys
+constexpr int kMaxKsBatch = 32;
+struct FusedKsArgs {
+    const u64* digits;              // [ndig][nl+K][N] ModUp output (EvalKeySwitchPrecomputeCore)
+    int ndig, nl, L, K;
+    const u64* keyA[kMaxKsBatch];   // per batch entry: evk a / b, Montgomery form, [dnum][L+K][N]
+    const u64* keyB[kMaxKsBatch];
+    u32 galois[kMaxKsBatch];        // Galois element applied to the result (1 = none)
+    u64* tmpP;                      // scratch [nb][2][K][N]
+    u64* conv;                      // scratch [nb][2][nl][N]
+    const u64* add0;                // optional addend of component 0 / 1, [nl][N]
+    const u64* add1;
+    u64* out;                       // [nb] x out_bs, each [2][nl][N]
+    size_t out_bs;
+    ScalarTable pinv;               // P^-1 mod q_i
+};
+bool fused_ks_supported(int logN);
+void launch_fused_ks(const DevTables& T, const FusedKsArgs& a, const BaseConvTable* moddown, int nb, cudaStream_t st);
 
 // ---- elementwise family (row P8)
 enum EwOp { EW_ADD = 0, EW_SUB = 1, EW_MUL = 2 };

@@ -13,6 +13,7 @@
 // values stay in [0,4q) (forward) / [0,2q) (inverse) and are normalised to [0,q) on the way out,
 // so results are the canonical residues.
 #include "hx_kernels.cuh"
+#include "hx_ntt_tile.cuh"
 
 namespace hx {
 
@@ -207,6 +208,89 @@ __global__ void __launch_bounds__(kTile / kEPT) k_ntt_col(DevTables T, NttGeom g
     }
 }
 
+// ---- compile-time geometry kernels (N = 2^12 .. 2^16): grid (tiles per limb, nbatch) ----------
+template <int LOGN, bool kInverse>
+__global__ void __launch_bounds__(kTileThreads) k_ntt_row_t(const __grid_constant__ DevTables T, u64* __restrict__ data,
+                                                            const __grid_constant__ LimbMap lm) {
+    __shared__ u64 sm[kTileWords];
+    const int prime = lm.prime[blockIdx.y % lm.period];
+    if (prime < 0) return;                 // limb not part of this transform (block-uniform)
+    const PrimeConst pc = T.pc[prime];
+    const u64 q = pc.q, q2 = q << 1;
+    const int t = threadIdx.x, tile = blockIdx.x;
+    u64* limb = data + (size_t)blockIdx.y * T.N + (size_t)tile * kTileN;
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        const int e = (u * kTileThreads + t) * 2;
+        const ulonglong2 x = *reinterpret_cast<const ulonglong2*>(limb + e);
+        sm[tphys(e)] = x.x;
+        sm[tphys(e + 1)] = x.y;
+    }
+    __syncthreads();
+    if (!kInverse) {
+        fwd_row_pass<LOGN>(sm, t, tile, T.tw_fwd + (size_t)prime * T.N, q);
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int e = (u * kTileThreads + t) * 2;
+            ulonglong2 x;
+            x.x = csub(csub(sm[tphys(e)], q2), q);
+            x.y = csub(csub(sm[tphys(e + 1)], q2), q);
+            st128(limb + e, x);
+        }
+    } else {
+        inv_row_pass<LOGN>(sm, t, tile, T.tw_inv + (size_t)prime * T.N, q);
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int e = (u * kTileThreads + t) * 2;
+            ulonglong2 x = {sm[tphys(e)], sm[tphys(e + 1)]};   // [0,2q): the column pass finishes the transform
+            st128(limb + e, x);
+        }
+    }
+}
+template <int LOGN, bool kInverse>
+__global__ void __launch_bounds__(kTileThreads) k_ntt_col_t(const __grid_constant__ DevTables T, u64* __restrict__ data,
+                                                            const __grid_constant__ LimbMap lm) {
+    __shared__ u64 sm[kTileWords];
+    const int prime = lm.prime[blockIdx.y % lm.period];
+    if (prime < 0) return;
+    const PrimeConst pc = T.pc[prime];
+    const u64 q = pc.q;
+    const int t = threadIdx.x, tile = blockIdx.x;
+    u64* limb = data + (size_t)blockIdx.y * T.N;
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+        const int l = u * kTileThreads + t;
+        sm[tphys(l)] = limb[col_offset<LOGN>(tile, l)];
+    }
+    __syncthreads();
+    if (!kInverse) {
+        fwd_col_pass<LOGN>(sm, t, T.tw_fwd + (size_t)prime * T.N, q);
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            const int l = u * kTileThreads + t;
+            limb[col_offset<LOGN>(tile, l)] = sm[tphys(l)];   // [0,4q): the row pass normalises
+        }
+    } else {
+        inv_col_pass<LOGN>(sm, t, T.tw_inv + (size_t)prime * T.N, q);
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            const int l = u * kTileThreads + t;
+            limb[col_offset<LOGN>(tile, l)] = shoup_mul(sm[tphys(l)], pc.ninv, pc.ninv_sh, q);
+        }
+    }
+}
+template <int LOGN>
+static void launch_ntt_t(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, bool inverse, cudaStream_t st) {
+    dim3 grid(NttGeo<LOGN>::TILES, nbatch);
+    if (!inverse) {
+        k_ntt_col_t<LOGN, false><<<grid, kTileThreads, 0, st>>>(T, data, lm);
+        k_ntt_row_t<LOGN, false><<<grid, kTileThreads, 0, st>>>(T, data, lm);
+    } else {
+        k_ntt_row_t<LOGN, true><<<grid, kTileThreads, 0, st>>>(T, data, lm);
+        k_ntt_col_t<LOGN, true><<<grid, kTileThreads, 0, st>>>(T, data, lm);
+    }
+}
+
 static NttGeom make_geom(int logN) {
     NttGeom g;
     g.logN = logN;
@@ -221,6 +305,14 @@ static NttGeom make_geom(int logN) {
 
 void launch_ntt(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, bool inverse, cudaStream_t st) {
     if (nbatch <= 0) return;
+    switch (T.logN) {
+        case 12: return launch_ntt_t<12>(T, data, nbatch, lm, inverse, st);
+        case 13: return launch_ntt_t<13>(T, data, nbatch, lm, inverse, st);
+        case 14: return launch_ntt_t<14>(T, data, nbatch, lm, inverse, st);
+        case 15: return launch_ntt_t<15>(T, data, nbatch, lm, inverse, st);
+        case 16: return launch_ntt_t<16>(T, data, nbatch, lm, inverse, st);
+        default: break;
+    }
     NttGeom g = make_geom(T.logN);
     int threads = (1 << g.logT) / kEPT;
     dim3 grid_row(T.N >> g.logT, nbatch), grid_col(T.N >> g.logT, nbatch);

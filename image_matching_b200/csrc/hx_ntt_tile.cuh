@@ -1,0 +1,157 @@
+// hx_ntt_tile.cuh -- compile-time-geometry negacyclic NTT passes over 2048-element shared-memory
+// tiles, shared by the stand-alone NTT kernels and the fused key-switch kernels.
+//
+// Transform (same as OpenFHE's ChineseRemainderTransformFTT, reached from every key switch and
+// rescale of /root/reference/src/sender/sender_diag.cpp:25,79,80):
+//   forward : Cooley-Tukey, natural order in, bit-reversed out, stage s uses tw[2^s + group]
+//   inverse : Gentleman-Sande with psi^-1 twiddles, then N^-1
+// A limb of N = 2^LOGN words is viewed as 2^A rows x 2^B columns (A = LOGN/2):
+//   column pass = stages 0..A-1   on a tile of all 2^A rows x C = 2^(11-A) adjacent columns
+//   row pass    = stages A..LOGN-1 on a tile of D = 2^(11-B) whole rows = 2048 contiguous words
+// A thread owns 8 tile elements per round and runs up to 3 stages in registers (radix-8) between
+// shared-memory exchanges.  Harvey lazy butterflies on Shoup twiddles: forward values live in
+// [0,4q), inverse values in [0,2q); callers normalise on the way out.
+#pragma once
+#include "hx_modarith.cuh"
+
+namespace hx {
+
+constexpr int kLogTile = 11;
+constexpr int kTileN = 1 << kLogTile;          // 2048 elements
+constexpr int kTileThreads = kTileN / 8;       // 256 threads
+constexpr int kTileWords = kTileN + (kTileN >> 4) + 8;   // padded: 1 word per 16 against bank conflicts
+__device__ __forceinline__ int tphys(int e) { return e + (e >> 4); }
+
+template <int LOGN>
+struct NttGeo {
+    static_assert(LOGN >= 12 && LOGN <= 16, "tile NTT supports N = 2^12 .. 2^16");
+    static constexpr int A = LOGN / 2;
+    static constexpr int B = LOGN - A;
+    static constexpr int LOGC = kLogTile - A;      // columns per column-pass tile
+    static constexpr int LOGD = kLogTile - B;      // rows per row-pass tile
+    static constexpr int TILES = 1 << (LOGN - kLogTile);
+};
+
+__device__ __forceinline__ int insert_bits3(int t, int p) { return ((t >> p) << (p + 3)) | (t & ((1 << p) - 1)); }
+
+// ---- forward --------------------------------------------------------------------------------
+// One round of R consecutive forward stages.  SL0 = first local stage (local stage sl toggles
+// local bit 10-sl); S0 = the global stage of SL0; SHIFT0 = S0 - (stage at which `tileoff` has
+// weight 1) so that twiddle index = 2^s + (tileoff << (s - S0 + SHIFT0)) + local group.
+template <int SL0, int R, int S0, int SHIFT0>
+__device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q2) {
+    constexpr int p = kLogTile - SL0 - R;
+    const int base = insert_bits3(t, p);
+    u64 v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) v[k] = sm[tphys(base + (k << p))];
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+        const int kb = R - 1 - r;
+        const int b = p + kb;
+        const int s = S0 + r;
+        const ulonglong2* twp = tw + (1 << s) + (tileoff << (SHIFT0 + r)) + (base >> (b + 1));
+#pragma unroll
+        for (int h = 0; h < 4; h++) {
+            const int lowmask = (1 << kb) - 1;
+            const int k0 = ((h & ~lowmask) << 1) | (h & lowmask);
+            const int k1 = k0 | (1 << kb);
+            const ulonglong2 w = __ldg(twp + (k0 >> (kb + 1)));
+            u64 x = v[k0];
+            x = x >= q2 ? x - q2 : x;
+            const u64 y = shoup_lazy(v[k1], w.x, w.y, q);
+            v[k0] = x + y;
+            v[k1] = x - y + q2;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; k++) sm[tphys(base + (k << p))] = v[k];
+}
+
+// Local stages [SL, SL_END) forward; a __syncthreads() after every round.
+template <int SL, int SL_END, int S, int SHIFT>
+__device__ __forceinline__ void fwd_stages(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q2) {
+    if constexpr (SL < SL_END) {
+        constexpr int R = (SL_END - SL >= 3) ? 3 : (SL_END - SL);
+        fwd_round_ct<SL, R, S, SHIFT>(sm, t, tileoff, tw, q, q2);
+        __syncthreads();
+        fwd_stages<SL + R, SL_END, S + R, SHIFT + R>(sm, t, tileoff, tw, q, q2);
+    }
+}
+// column pass: global stages 0..A-1 = local stages 0..A-1, twiddle = 2^s + (row >> (A-s)); no tile offset
+template <int LOGN>
+__device__ __forceinline__ void fwd_col_pass(u64* sm, int t, const ulonglong2* __restrict__ tw, u64 q) {
+    fwd_stages<0, NttGeo<LOGN>::A, 0, 0>(sm, t, 0, tw, q, q << 1);
+}
+// row pass: global stages A..LOGN-1 = local stages LOGD..10; tile `tile` starts at row tile<<LOGD
+template <int LOGN>
+__device__ __forceinline__ void fwd_row_pass(u64* sm, int t, int tile, const ulonglong2* __restrict__ tw, u64 q) {
+    using G = NttGeo<LOGN>;
+    // at stage A a row index has weight 1 in the group number; local groups are numbered inside the tile
+    fwd_stages<G::LOGD, kLogTile, G::A, G::LOGD>(sm, t, tile, tw, q, q << 1);
+}
+
+// ---- inverse --------------------------------------------------------------------------------
+// One round of R consecutive inverse (Gentleman-Sande) stages: local stages SH-1, SH-2, .., SH-R.
+// S_TOP = global stage of local stage SH-1; SHIFT_TOP = shift of tileoff at that stage.
+template <int SH, int R, int S_TOP, int SHIFT_TOP>
+__device__ __forceinline__ void inv_round_ct(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q2) {
+    constexpr int p = kLogTile - SH;
+    const int base = insert_bits3(t, p);
+    u64 v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) v[k] = sm[tphys(base + (k << p))];
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+        const int kb = r;
+        const int b = p + kb;
+        const int s = S_TOP - r;
+        const ulonglong2* twp = tw + (1 << s) + (tileoff << (SHIFT_TOP - r)) + (base >> (b + 1));
+#pragma unroll
+        for (int h = 0; h < 4; h++) {
+            const int lowmask = (1 << kb) - 1;
+            const int k0 = ((h & ~lowmask) << 1) | (h & lowmask);
+            const int k1 = k0 | (1 << kb);
+            const ulonglong2 w = __ldg(twp + (k0 >> (kb + 1)));
+            const u64 x = v[k0], y = v[k1];
+            u64 s_ = x + y;
+            s_ = s_ >= q2 ? s_ - q2 : s_;
+            v[k0] = s_;
+            v[k1] = shoup_lazy(x - y + q2, w.x, w.y, q);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; k++) sm[tphys(base + (k << p))] = v[k];
+}
+// Local stages SH-1 .. SL (descending); remainder round first so the radix-8 rounds are aligned.
+template <int SL, int SH, int S_TOP, int SHIFT_TOP>
+__device__ __forceinline__ void inv_stages(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q2) {
+    if constexpr (SH > SL) {
+        constexpr int rem = (SH - SL) % 3;
+        constexpr int R = rem == 0 ? 3 : rem;
+        inv_round_ct<SH, R, S_TOP, SHIFT_TOP>(sm, t, tileoff, tw, q, q2);
+        __syncthreads();
+        inv_stages<SL, SH - R, S_TOP - R, SHIFT_TOP - R>(sm, t, tileoff, tw, q, q2);
+    }
+}
+template <int LOGN>
+__device__ __forceinline__ void inv_row_pass(u64* sm, int t, int tile, const ulonglong2* __restrict__ tw, u64 q) {
+    using G = NttGeo<LOGN>;
+    // top stage LOGN-1: shift of the tile offset there = LOGD + (LOGN-1-A) = 10
+    inv_stages<G::LOGD, kLogTile, LOGN - 1, kLogTile - 1>(sm, t, tile, tw, q, q << 1);
+}
+template <int LOGN>
+__device__ __forceinline__ void inv_col_pass(u64* sm, int t, const ulonglong2* __restrict__ tw, u64 q) {
+    using G = NttGeo<LOGN>;
+    inv_stages<0, G::A, G::A - 1, 16>(sm, t, 0, tw, q, q << 1);   // tile offset unused (0); 16 keeps shifts non-negative
+}
+
+// ---- tile addressing ------------------------------------------------------------------------
+// Column tile: local index l = r*C + c  <->  limb offset r*2^B + tile*C + c.
+template <int LOGN>
+__device__ __forceinline__ size_t col_offset(int tile, int l) {
+    using G = NttGeo<LOGN>;
+    return ((size_t)(l >> G::LOGC) << G::B) + ((size_t)tile << G::LOGC) + (l & ((1 << G::LOGC) - 1));
+}
+
+}  // namespace hx

@@ -25,6 +25,7 @@ Engine::Engine(int N_, int L_, int K_, int dnum_, const u64* q, const u64* p, co
     if (L + K > kMaxPrimes) throw std::runtime_error("too many RNS limbs");
     alpha = (L + dnum - 1) / dnum;
     if (alpha > 8) throw std::runtime_error("digit width > 8 limbs unsupported");
+    if (dnum < 1 || dnum > kMaxDigits) throw std::runtime_error("number of key-switching digits must be 1..4");
     for (int i = 0; i < L; i++) { mods.push_back(q[i]); psis.push_back(psi_q[i]); }
     for (int i = 0; i < K; i++) { mods.push_back(p[i]); psis.push_back(psi_p[i]); }
     for (u64 m : mods)
@@ -78,6 +79,7 @@ Engine::~Engine() {
     cudaStreamSynchronize(st);
     for (auto& kv : modup_tabs_) cudaFree(kv.second);
     for (auto& kv : moddown_tabs_) cudaFree(kv.second);
+    for (auto& kv : last_tabs_) cudaFree(kv.second);
     for (auto& kv : automaps_) cudaFree(kv.second);
     for (auto& kv : rot_keys_) { cudaFree(kv.second.a); cudaFree(kv.second.b); }
     if (have_mult_key_) { cudaFree(mult_key_.a); cudaFree(mult_key_.b); }
@@ -93,7 +95,7 @@ Engine::~Engine() {
 // ------------------------------------------------------------------------------------------ profiler
 const char* prof_kind_name(int kind) {
     static const char* names[PK_COUNT] = {"ntt_fwd", "ntt_inv", "baseconv", "ks_inner", "moddown", "elementwise", "scalar", "tensor",
-                                          "automorph", "rescale", "diag_mac", "misc", "ks_fused"};
+                                          "automorph", "rescale", "diag_mac", "misc", "ks_fused", "modup"};
     return (kind >= 0 && kind < PK_COUNT) ? names[kind] : "?";
 }
 Engine::Scope::Scope(Engine* e_, int kind_, int nlaunch, double bytes) : e(e_), kind(kind_) {
@@ -278,6 +280,11 @@ const BaseConvTable* Engine::modup_table(int nl, int digit) {
     for (int k = 0; k < K; k++) dst.push_back(L + k);
     return modup_tabs_[key] = make_table(src, dst);
 }
+const BaseConvTable* Engine::last_limb_table(int prime) {
+    auto it = last_tabs_.find(prime);
+    if (it != last_tabs_.end()) return it->second;
+    return last_tabs_[prime] = make_table({prime}, {});
+}
 const BaseConvTable* Engine::moddown_table(int nl) {
     auto it = moddown_tabs_.find(nl);
     if (it != moddown_tabs_.end()) return it->second;
@@ -343,6 +350,21 @@ u64* Engine::ks_precompute(const u64* c, int nl, int* ndig_out) {
     int ndig = std::min((nl + alpha - 1) / alpha, dnum);
     int ext = nl + K;
     u64* digits = alloc_words((size_t)ndig * ext * N);
+    if (fused_ks_supported(logN) && !force_unfused) {
+        ModUpArgs m;
+        m.c = c; m.c_bs = 0; m.nbatch = 1;
+        m.nl = nl; m.L = L; m.K = K; m.ndig = ndig; m.alpha = alpha;
+        for (int j = 0; j < ndig; j++) m.tabs[j] = modup_table(nl, j);
+        m.scratch = alloc_words((size_t)nl * N);
+        m.digits = digits;
+        {   // algorithmic bytes: input polynomial once, digits once
+            Scope sc(this, PK_MODUP, 2 + 2 * ndig, 8.0 * N * (nl + (double)ndig * ext));
+            launch_fused_modup(T, m, st);
+        }
+        free_words(m.scratch);
+        *ndig_out = ndig;
+        return digits;
+    }
     u64* scratch = alloc_words((size_t)alpha * N);
     for (int j = 0; j < ndig; j++) {
         int lo = j * alpha, hi = (j == ndig - 1) ? nl : (j + 1) * alpha, sz = hi - lo;
@@ -399,7 +421,7 @@ void Engine::ks_core_batch(const u64* digits, int ndig, int nl, const std::vecto
             a.pinv = scalar_table(pinv);
             {   // algorithmic bytes of one key switch after ModUp: evk once, digits once per launch,
                 // addend once, result once
-                Scope sc(this, PK_KS_FUSED, 3,
+                Scope sc(this, PK_KS_FUSED, 4,
                          8.0 * N * ((double)n * 2 * ndig * ext + (double)ndig * ext + (double)addend_comps * nl + (double)n * 2 * nl));
                 launch_fused_ks(T, a, moddown_table(nl), n, st);
             }
@@ -616,6 +638,24 @@ Ct Engine::rescale(const Ct& a) {
     for (int i = 0; i < nl - 1; i++) {
         qlinv[i] = invmod(ql % mods[i], mods[i]);
         neg[i] = (mods[i] - qlinv[i]) % mods[i];
+    }
+    if (fused_ks_supported(logN) && !force_unfused) {
+        RescaleArgs r;
+        r.c = a->d; r.c_bs = a->comp_stride(); r.ncomp = nc; r.nl = nl;
+        r.last_tab = last_limb_table(nl - 1);
+        r.last = alloc_words((size_t)nc * N);
+        r.tmp = alloc_words((size_t)nc * (nl - 1) * N);
+        Ct out = new_ct(nc, nl - 1, a->level + 1, a->deg - 1);
+        r.out = out->d; r.out_bs = out->comp_stride();
+        r.negqlinv = scalar_table(neg);
+        r.qlinv = scalar_table(qlinv);
+        {
+            Scope sc(this, PK_RESCALE, 4, 8.0 * N * nc * (nl + nl - 1));
+            launch_fused_rescale(T, r, st);
+        }
+        free_words(r.tmp);
+        free_words(r.last);
+        return out;
     }
     u64* last = alloc_words((size_t)nc * N);
     for (int c = 0; c < nc; c++)

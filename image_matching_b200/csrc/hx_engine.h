@@ -28,7 +28,7 @@ class Engine;
 // Kernel families for launch accounting and the optional CUDA-event profiler (bench.py roofline).
 enum ProfKind {
     PK_NTT_FWD = 0, PK_NTT_INV, PK_BASECONV, PK_KS_INNER, PK_MODDOWN, PK_EW, PK_SCALAR, PK_TENSOR, PK_AUTOMORPH,
-    PK_RESCALE, PK_DIAG_MAC, PK_MISC, PK_KS_FUSED, PK_COUNT
+    PK_RESCALE, PK_DIAG_MAC, PK_MISC, PK_KS_FUSED, PK_MODUP, PK_COUNT
 };
 const char* prof_kind_name(int kind);
 
@@ -61,7 +61,7 @@ public:
     DevTables T{};
     cudaStream_t st = nullptr;
     std::recursive_mutex mu;         // the reference enters from up to 48 OpenMP threads
-    int rot_chunk = 8;               // hoisted rotations per fused key-switch batch (intermediates stay L2 resident)
+    int rot_chunk = 32;              // hoisted rotations per fused key-switch batch (intermediates stay L2 resident)
     bool force_unfused = false;      // tests: run the unfused reference kernels instead of hx_fused.cu
     unsigned long long launches = 0; // kernels launched (bench "gpu_launches")
 
@@ -155,6 +155,7 @@ public:
 private:
     const BaseConvTable* modup_table(int nl, int digit);
     const BaseConvTable* moddown_table(int nl);
+    const BaseConvTable* last_limb_table(int prime);
     BaseConvTable* make_table(const std::vector<int>& src, const std::vector<int>& dst);
     void align(Ct& a, Ct& b);
     std::vector<u64> const_for_mult(double c, int nl) const;
@@ -164,6 +165,7 @@ private:
 
     std::map<std::pair<int, int>, BaseConvTable*> modup_tabs_;
     std::map<int, BaseConvTable*> moddown_tabs_;
+    std::map<int, BaseConvTable*> last_tabs_;
     std::map<u64, u32*> automaps_;
     std::map<u64, EvalKey> rot_keys_;
     EvalKey mult_key_;

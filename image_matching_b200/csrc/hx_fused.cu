@@ -1,13 +1,14 @@
 // hx_fused.cu -- fused hybrid key-switch pipeline for sm_100a:
 // EvalFastKeySwitchCoreExt + ApproxModDown + "+ c0" + automorphism of OpenFHE v1.2.3, as reached
 // from cc->EvalFastRotation (/root/reference/src/sender/sender_diag.cpp:25), RelinearizeInPlace
-// (:79) and EvalRotate (src/openFHE_wrapper.cpp:124), in THREE launches per batch of keys:
+// (:79) and EvalRotate (src/openFHE_wrapper.cpp:124), in FOUR launches per batch of keys, every
+// CTA owning one 2048-element tile of one limb (18 KB of shared memory, 3-4 CTAs per SM):
 //
-//   K1 k_ks_p_inner   P-limb inner product  sum_j d_j (.) evk_j  fused with the inverse row pass
-//   K2 k_conv_cols    inverse column pass of the P limbs -> P^-1/N^-1 scaling -> approximate base
-//                     conversion to the Q limbs -> forward column pass
-//   K3 k_ks_q_finish  forward row pass of the converted limbs, Q-limb inner product computed on the
-//                     fly, (ip - conv) * P^-1 + addend, written through the Galois permutation
+//   K1  k_ks_p_inner   P-limb inner product  sum_j d_j (.) evk_j  fused with the inverse row pass
+//   K2a k_inv_cols     inverse column pass of the P limbs, scaled by (P/p_k)^-1 * N^-1
+//   K2b k_conv_fwd_col approximate base conversion to one Q limb fused with its forward column pass
+//   K3  k_ks_q_finish  Q-limb inner product computed on the fly, forward row pass of the converted
+//                      limb, (ip - conv) * P^-1 + addend, written through the Galois permutation
 //
 // The evaluation key is streamed from HBM exactly once (its P limbs in K1, its Q limbs in K3); the
 // 2 x (l+K)-limb extended ciphertext of the textbook pipeline is never materialised.  The only
@@ -29,8 +30,8 @@ __device__ __forceinline__ u32 automap_at(u32 J, u32 g) {
 
 // ---------------------------------------------------------------------------------------------
 // K1: grid (TILES, 2*K, nb).  out: tmpP[b][comp][k][N], values in [0,2q), inverse row pass done.
-template <int LOGN>
-__global__ void __launch_bounds__(kTileThreads) k_ks_p_inner(const __grid_constant__ DevTables T, const __grid_constant__ FusedKsArgs a) {
+template <int LOGN, int NDIG>
+__global__ void __launch_bounds__(kTileThreads, 3) k_ks_p_inner(const __grid_constant__ DevTables T, const __grid_constant__ FusedKsArgs a) {
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, tile = blockIdx.x;
     const int k = blockIdx.y >> 1, comp = blockIdx.y & 1, b = blockIdx.z;
@@ -43,7 +44,8 @@ __global__ void __launch_bounds__(kTileThreads) k_ks_p_inner(const __grid_consta
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
         u128d a0 = {0, 0}, a1 = {0, 0};
-        for (int j = 0; j < a.ndig; j++) {
+#pragma unroll
+        for (int j = 0; j < NDIG; j++) {
             const ulonglong2 d = ldg128(dig + j * dstride + e);
             const ulonglong2 kv = ld_stream128(key + j * kstride + e);
             acc_wide(a0, d.x, kv.x);
@@ -64,70 +66,73 @@ __global__ void __launch_bounds__(kTileThreads) k_ks_p_inner(const __grid_consta
 }
 
 // ---------------------------------------------------------------------------------------------
-// K2: grid (TILES, nbatch).  in : [nbatch][n_in][N]  row-pass-inverted limbs in [0,2q)
-//                            out: [nbatch][n_out][N] column-pass-forwarded limbs in [0,4q)
-// dynamic shared memory: (n_in + 1) tiles.  hatinv_n = (Qhat_i^-1 * N^-1) mod q_i folds the N^-1 of
-// the inverse transform into the first multiplication of ApproxSwitchCRTBasis.
+// K2a: grid (TILES, n_in, nbatch), in place on [nbatch][n_in][N]: inverse column pass, then
+// x * hatinv_n  (hatinv_n = (Qhat_k^-1 * N^-1) mod q_k folds the N^-1 of the inverse transform into
+// the first multiplication of ApproxSwitchCRTBasis).  Output canonical, coefficient order.
 template <int LOGN>
-__global__ void __launch_bounds__(kTileThreads) k_conv_cols(DevTables T, const BaseConvTable* __restrict__ tab, const u64* __restrict__ in,
-                                                            size_t in_bs, u64* __restrict__ out, size_t out_bs) {
-    extern __shared__ u64 smd[];
-    const int t = threadIdx.x, tile = blockIdx.x;
+__global__ void __launch_bounds__(kTileThreads, 3) k_inv_cols(const __grid_constant__ DevTables T, const BaseConvTable* __restrict__ tab,
+                                                              u64* __restrict__ data, size_t bs) {
+    __shared__ u64 sm[kTileWords];
+    const int t = threadIdx.x, tile = blockIdx.x, k = blockIdx.y;
+    const int prime = tab->src[k];
+    const u64 q = T.pc[prime].q;
+    u64* limb = data + (size_t)blockIdx.z * bs + (size_t)k * T.N;
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+        const int l = u * kTileThreads + t;
+        sm[tphys(l)] = limb[col_offset<LOGN>(tile, l)];
+    }
+    __syncthreads();
+    inv_col_pass<LOGN>(sm, t, T.tw_inv + (size_t)prime * T.N, q);
+    const u64 h = tab->hatinv_n[k], hs = tab->hatinv_n_sh[k];
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+        const int l = u * kTileThreads + t;
+        limb[col_offset<LOGN>(tile, l)] = shoup_mul(sm[tphys(l)], h, hs, q);
+    }
+}
+
+// K2b: grid (TILES, n_out, nbatch).  in: [nbatch][n_in][N] scaled coefficients (K2a);
+// out: [nbatch][n_out][N], forward column pass done, values lazy (see fwd_round_ct).
+template <int LOGN>
+__global__ void __launch_bounds__(kTileThreads, 3) k_conv_fwd_col(const __grid_constant__ DevTables T, const BaseConvTable* __restrict__ tab,
+                                                                  const u64* __restrict__ in, size_t in_bs, u64* __restrict__ out, size_t out_bs,
+                                                                  int ext_nl, int L) {
+    __shared__ u64 sm[kTileWords];
+    const int t = threadIdx.x, tile = blockIdx.x, j = blockIdx.y;
     const int n_in = tab->n_in, n_out = tab->n_out;
-    const u64* src = in + (size_t)blockIdx.y * in_bs;
-    u64* dst = out + (size_t)blockIdx.y * out_bs;
+    const int prime = tab->dst[j];
+    const PrimeConst pc = T.pc[prime];
+    const u64* src = in + (size_t)blockIdx.z * in_bs;
+    u128d acc[8];
+#pragma unroll
+    for (int u = 0; u < 8; u++) acc[u] = {0, 0};
     for (int k = 0; k < n_in; k++) {
-        u64* s = smd + (size_t)k * kTileWords;
+        const u64 m = tab->mat[k * n_out + j];
 #pragma unroll
-        for (int u = 0; u < 8; u++) {
-            const int l = u * kTileThreads + t;
-            s[tphys(l)] = src[(size_t)k * T.N + col_offset<LOGN>(tile, l)];
-        }
+        for (int u = 0; u < 8; u++)
+            acc_wide(acc[u], __ldg(src + (size_t)k * T.N + col_offset<LOGN>(tile, u * kTileThreads + t)), m);
     }
+#pragma unroll
+    for (int u = 0; u < 8; u++) sm[tphys(u * kTileThreads + t)] = redc(acc[u], pc.q, pc.qinv_neg);
     __syncthreads();
-    for (int k = 0; k < n_in; k++) {
-        const int prime = tab->src[k];
-        const u64 q = T.pc[prime].q;
-        u64* s = smd + (size_t)k * kTileWords;
-        inv_col_pass<LOGN>(s, t, T.tw_inv + (size_t)prime * T.N, q);
-        const u64 h = tab->hatinv_n[k], hs = tab->hatinv_n_sh[k];
+    fwd_col_pass<LOGN>(sm, t, T.tw_fwd + (size_t)prime * T.N, pc.q);
+    // ext_nl >= 0 (ModUp): the output is a digit in extended-basis order (Q limbs 0..nl-1, then P); else limb j
+    const int pos = ext_nl < 0 ? j : (prime < L ? prime : ext_nl + prime - L);
+    u64* dst = out + (size_t)blockIdx.z * out_bs + (size_t)pos * T.N;
 #pragma unroll
-        for (int u = 0; u < 8; u++) {
-            const int l = tphys(u * kTileThreads + t);
-            s[l] = shoup_mul(s[l], h, hs, q);
-        }
-    }
-    __syncthreads();
-    u64* so = smd + (size_t)n_in * kTileWords;
-    for (int j = 0; j < n_out; j++) {
-        const int prime = tab->dst[j];
-        const PrimeConst pc = T.pc[prime];
-        u128d acc[8];
-#pragma unroll
-        for (int u = 0; u < 8; u++) acc[u] = {0, 0};
-        for (int k = 0; k < n_in; k++) {
-            const u64 m = tab->mat[k * n_out + j];
-            const u64* s = smd + (size_t)k * kTileWords;
-#pragma unroll
-            for (int u = 0; u < 8; u++) acc_wide(acc[u], s[tphys(u * kTileThreads + t)], m);
-        }
-#pragma unroll
-        for (int u = 0; u < 8; u++) so[tphys(u * kTileThreads + t)] = redc(acc[u], pc.q, pc.qinv_neg);
-        __syncthreads();
-        fwd_col_pass<LOGN>(so, t, T.tw_fwd + (size_t)prime * T.N, pc.q);
-#pragma unroll
-        for (int u = 0; u < 8; u++) {
-            const int l = u * kTileThreads + t;
-            dst[(size_t)j * T.N + col_offset<LOGN>(tile, l)] = so[tphys(l)];
-        }
-        __syncthreads();
+    for (int u = 0; u < 8; u++) {
+        const int l = u * kTileThreads + t;
+        dst[col_offset<LOGN>(tile, l)] = sm[tphys(l)];
     }
 }
 
 // ---------------------------------------------------------------------------------------------
 // K3: grid (TILES, 2*nl, nb).  out[b][comp][i][J] = ((ip - conv) * P^-1 + addend)[map_g(J)]
-template <int LOGN>
-__global__ void __launch_bounds__(kTileThreads) k_ks_q_finish(const __grid_constant__ DevTables T, const __grid_constant__ FusedKsArgs a) {
+// All global loads (converted tile, digits, key limbs) are issued before the transform so the
+// memory phase of one CTA overlaps the butterfly phase of its neighbours on the SM.
+template <int LOGN, int NDIG>
+__global__ void __launch_bounds__(kTileThreads, 3) k_ks_q_finish(const __grid_constant__ DevTables T, const __grid_constant__ FusedKsArgs a) {
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, otile = blockIdx.x;
     const int i = blockIdx.y >> 1, comp = blockIdx.y & 1, b = blockIdx.z;
@@ -135,37 +140,42 @@ __global__ void __launch_bounds__(kTileThreads) k_ks_q_finish(const __grid_const
     // tiles map to tiles under the automorphism (the low bits of the natural index map among themselves)
     const int tile = (int)(automap_at<LOGN>((u32)otile << kLogTile, g) >> kLogTile);
     const PrimeConst pc = T.pc[i];
-    const u64 q = pc.q, q2 = q << 1;
+    const u64 q = pc.q;
+    const bool lazy = lazy_ok(q);
     const size_t toff = (size_t)tile * kTileN;
     const u64* cv = a.conv + (((size_t)b * 2 + comp) * a.nl + i) * T.N + toff;
+    const u64* key = (comp == 0 ? a.keyB[b] : a.keyA[b]) + (size_t)i * T.N + toff;
+    const u64* dig = a.digits + (size_t)i * T.N + toff;
+    const size_t kstride = (size_t)(a.L + a.K) * T.N, dstride = (size_t)(a.nl + a.K) * T.N;
+    u64 ip[8];
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
         const ulonglong2 x = ldg128(cv + e);
         sm[tphys(e)] = x.x;
         sm[tphys(e + 1)] = x.y;
-    }
-    __syncthreads();
-    fwd_row_pass<LOGN>(sm, t, tile, T.tw_fwd + (size_t)i * T.N, q);
-    const u64* key = (comp == 0 ? a.keyB[b] : a.keyA[b]) + (size_t)i * T.N + toff;
-    const u64* dig = a.digits + (size_t)i * T.N + toff;
-    const u64* add = (comp == 0 ? a.add0 : a.add1);
-    if (add) add += (size_t)i * T.N + toff;
-    const size_t kstride = (size_t)(a.L + a.K) * T.N, dstride = (size_t)(a.nl + a.K) * T.N;
-    const u64 pinv = a.pinv.v[i], pinv_sh = a.pinv.sh[i];
-#pragma unroll
-    for (int u = 0; u < 4; u++) {
-        const int e = (u * kTileThreads + t) * 2;
         u128d a0 = {0, 0}, a1 = {0, 0};
-        for (int j = 0; j < a.ndig; j++) {
+#pragma unroll
+        for (int j = 0; j < NDIG; j++) {
             const ulonglong2 d = ldg128(dig + j * dstride + e);
             const ulonglong2 kv = ld_stream128(key + j * kstride + e);
             acc_wide(a0, d.x, kv.x);
             acc_wide(a1, d.y, kv.y);
         }
-        const u64 c0 = csub(csub(sm[tphys(e)], q2), q), c1 = csub(csub(sm[tphys(e + 1)], q2), q);
-        u64 r0 = shoup_mul(sub_mod(redc(a0, q, pc.qinv_neg), c0, q), pinv, pinv_sh, q);
-        u64 r1 = shoup_mul(sub_mod(redc(a1, q, pc.qinv_neg), c1, q), pinv, pinv_sh, q);
+        ip[2 * u] = redc(a0, q, pc.qinv_neg);
+        ip[2 * u + 1] = redc(a1, q, pc.qinv_neg);
+    }
+    __syncthreads();
+    fwd_row_pass<LOGN>(sm, t, tile, T.tw_fwd + (size_t)i * T.N, q);
+    const u64* add = (comp == 0 ? a.add0 : a.add1);
+    if (add) add += (size_t)i * T.N + toff;
+    const u64 pinv = a.pinv.v[i], pinv_sh = a.pinv.sh[i];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        const int e = (u * kTileThreads + t) * 2;
+        const u64 c0 = fwd_normalize(sm[tphys(e)], q, pc.mu64, lazy), c1 = fwd_normalize(sm[tphys(e + 1)], q, pc.mu64, lazy);
+        u64 r0 = shoup_mul(sub_mod(ip[2 * u], c0, q), pinv, pinv_sh, q);
+        u64 r1 = shoup_mul(sub_mod(ip[2 * u + 1], c1, q), pinv, pinv_sh, q);
         if (add) {
             const ulonglong2 ad = ldg128(add + e);
             r0 = add_mod(r0, ad.x, q);
@@ -187,18 +197,201 @@ __global__ void __launch_bounds__(kTileThreads) k_ks_q_finish(const __grid_const
     }
 }
 
+template <int LOGN, int NDIG>
+static void launch_fused_tn(const DevTables& T, const FusedKsArgs& a, const BaseConvTable* moddown, int nb, cudaStream_t st) {
+    using G = NttGeo<LOGN>;
+    k_ks_p_inner<LOGN, NDIG><<<dim3(G::TILES, 2 * a.K, nb), kTileThreads, 0, st>>>(T, a);
+    k_inv_cols<LOGN><<<dim3(G::TILES, a.K, nb * 2), kTileThreads, 0, st>>>(T, moddown, a.tmpP, (size_t)a.K * T.N);
+    k_conv_fwd_col<LOGN><<<dim3(G::TILES, a.nl, nb * 2), kTileThreads, 0, st>>>(T, moddown, a.tmpP, (size_t)a.K * T.N, a.conv, (size_t)a.nl * T.N, -1, 0);
+    k_ks_q_finish<LOGN, NDIG><<<dim3(G::TILES, 2 * a.nl, nb), kTileThreads, 0, st>>>(T, a);
+}
 template <int LOGN>
 static void launch_fused_t(const DevTables& T, const FusedKsArgs& a, const BaseConvTable* moddown, int nb, cudaStream_t st) {
-    using G = NttGeo<LOGN>;
-    k_ks_p_inner<LOGN><<<dim3(G::TILES, 2 * a.K, nb), kTileThreads, 0, st>>>(T, a);
-    const size_t smem = (size_t)(a.K + 1) * kTileWords * sizeof(u64);
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(k_conv_cols<LOGN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 9 * kTileWords * (int)sizeof(u64));
-        attr_set = true;
+    switch (a.ndig) {
+        case 1: launch_fused_tn<LOGN, 1>(T, a, moddown, nb, st); break;
+        case 2: launch_fused_tn<LOGN, 2>(T, a, moddown, nb, st); break;
+        case 3: launch_fused_tn<LOGN, 3>(T, a, moddown, nb, st); break;
+        case 4: launch_fused_tn<LOGN, 4>(T, a, moddown, nb, st); break;
+        default: break;
     }
-    k_conv_cols<LOGN><<<dim3(G::TILES, nb * 2), kTileThreads, smem, st>>>(T, moddown, a.tmpP, (size_t)a.K * T.N, a.conv, (size_t)a.nl * T.N);
-    k_ks_q_finish<LOGN><<<dim3(G::TILES, 2 * a.nl, nb), kTileThreads, 0, st>>>(T, a);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Fused ModUp (EvalKeySwitchPrecomputeCore, sender_diag.cpp:22) and rescale (DropLastElementAndScale,
+// sender_diag.cpp:80) are built from the same tile passes.
+
+// Inverse row pass, out of place: grid (TILES, nlimbs, nbatch); limb y of batch z is read at
+// in + z*in_bs + y*N and written to out + z*out_bs + y*N; prime index = prime0 + y.  Values [0,2q).
+template <int LOGN>
+__global__ void __launch_bounds__(kTileThreads, 3) k_inv_rows(const __grid_constant__ DevTables T, const u64* __restrict__ in, size_t in_bs,
+                                                              u64* __restrict__ out, size_t out_bs, int prime0) {
+    __shared__ u64 sm[kTileWords];
+    const int t = threadIdx.x, tile = blockIdx.x, prime = prime0 + blockIdx.y;
+    const u64 q = T.pc[prime].q;
+    const u64* src = in + (size_t)blockIdx.z * in_bs + (size_t)blockIdx.y * T.N + (size_t)tile * kTileN;
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        const int e = (u * kTileThreads + t) * 2;
+        const ulonglong2 x = ldg128(src + e);
+        sm[tphys(e)] = x.x;
+        sm[tphys(e + 1)] = x.y;
+    }
+    __syncthreads();
+    inv_row_pass<LOGN>(sm, t, tile, T.tw_inv + (size_t)prime * T.N, q);
+    u64* dst = out + (size_t)blockIdx.z * out_bs + (size_t)blockIdx.y * T.N + (size_t)tile * kTileN;
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        const int e = (u * kTileThreads + t) * 2;
+        ulonglong2 x = {sm[tphys(e)], sm[tphys(e + 1)]};
+        st128(dst + e, x);
+    }
+}
+
+// ModUp tail: grid (TILES, ext, ndig*nbatch).  Limb y of digit d: own limbs [lo,hi) are copied from the
+// input polynomial, the converted limbs get their forward row pass (in place) and are normalised.
+template <int LOGN>
+__global__ void __launch_bounds__(kTileThreads, 3) k_modup_rows(const __grid_constant__ DevTables T, u64* __restrict__ digits, const u64* __restrict__ c,
+                                                                size_t c_bs, int ndig, int nl, int L, int alpha) {
+    __shared__ u64 sm[kTileWords];
+    const int t = threadIdx.x, tile = blockIdx.x, y = blockIdx.y;
+    const int d = blockIdx.z % ndig, bz = blockIdx.z / ndig;
+    const int ext = gridDim.y;
+    const int lo = d * alpha, hi = (d == ndig - 1) ? nl : (d + 1) * alpha;
+    u64* limb = digits + ((size_t)blockIdx.z * ext + y) * T.N + (size_t)tile * kTileN;
+    if (y >= lo && y < hi) {
+        const u64* src = c + (size_t)bz * c_bs + (size_t)y * T.N + (size_t)tile * kTileN;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int e = (u * kTileThreads + t) * 2;
+            st128(limb + e, ldg128(src + e));
+        }
+        return;
+    }
+    const int prime = y < nl ? y : L + (y - nl);
+    const PrimeConst pc = T.pc[prime];
+    const u64 q = pc.q;
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        const int e = (u * kTileThreads + t) * 2;
+        const ulonglong2 x = *reinterpret_cast<const ulonglong2*>(limb + e);
+        sm[tphys(e)] = x.x;
+        sm[tphys(e + 1)] = x.y;
+    }
+    __syncthreads();
+    fwd_row_pass<LOGN>(sm, t, tile, T.tw_fwd + (size_t)prime * T.N, q);
+    const bool lazy = lazy_ok(q);
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        const int e = (u * kTileThreads + t) * 2;
+        ulonglong2 x = {fwd_normalize(sm[tphys(e)], q, pc.mu64, lazy), fwd_normalize(sm[tphys(e + 1)], q, pc.mu64, lazy)};
+        st128(limb + e, x);
+    }
+}
+
+// Rescale, column stage: grid (TILES, nl-1, nbatch).  last: [nbatch][N] coefficients of the dropped limb
+// (canonical, K2a with a 1x0 table does inverse columns + N^-1); tmp_i = lift(last) * (-q_l^-1) mod q_i
+// (centred lift: v > q_l/2 means v - q_l, and q_l * (-q_l^-1) = -1, hence the "+1"), forward column pass.
+template <int LOGN>
+__global__ void __launch_bounds__(kTileThreads, 3) k_rescale_cols(const __grid_constant__ DevTables T, const u64* __restrict__ last, size_t last_bs,
+                                                                  u64* __restrict__ tmp, size_t tmp_bs, int nl, const __grid_constant__ ScalarTable negqlinv) {
+    __shared__ u64 sm[kTileWords];
+    const int t = threadIdx.x, tile = blockIdx.x, i = blockIdx.y;
+    const u64 q = T.pc[i].q, half = T.pc[nl - 1].q >> 1;
+    const u64* src = last + (size_t)blockIdx.z * last_bs;
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+        const int l = u * kTileThreads + t;
+        const u64 v = __ldg(src + col_offset<LOGN>(tile, l));
+        u64 r = shoup_mul(v, negqlinv.v[i], negqlinv.sh[i], q);
+        if (v > half) r = add_mod(r, 1, q);
+        sm[tphys(l)] = r;
+    }
+    __syncthreads();
+    fwd_col_pass<LOGN>(sm, t, T.tw_fwd + (size_t)i * T.N, q);
+    u64* dst = tmp + (size_t)blockIdx.z * tmp_bs + (size_t)i * T.N;
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+        const int l = u * kTileThreads + t;
+        dst[col_offset<LOGN>(tile, l)] = sm[tphys(l)];
+    }
+}
+// Rescale, row stage: out_i = c_i * q_l^-1 + NTT(tmp_i).  grid (TILES, nl-1, nbatch).
+template <int LOGN>
+__global__ void __launch_bounds__(kTileThreads, 3) k_rescale_rows(const __grid_constant__ DevTables T, u64* __restrict__ out, size_t out_bs,
+                                                                  const u64* __restrict__ c, size_t c_bs, const u64* __restrict__ tmp, size_t tmp_bs,
+                                                                  const __grid_constant__ ScalarTable qlinv) {
+    __shared__ u64 sm[kTileWords];
+    const int t = threadIdx.x, tile = blockIdx.x, i = blockIdx.y;
+    const PrimeConst pc = T.pc[i];
+    const u64 q = pc.q;
+    const size_t off = (size_t)i * T.N + (size_t)tile * kTileN;
+    const u64* src = tmp + (size_t)blockIdx.z * tmp_bs + off;
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        const int e = (u * kTileThreads + t) * 2;
+        const ulonglong2 x = ldg128(src + e);
+        sm[tphys(e)] = x.x;
+        sm[tphys(e + 1)] = x.y;
+    }
+    __syncthreads();
+    fwd_row_pass<LOGN>(sm, t, tile, T.tw_fwd + (size_t)i * T.N, q);
+    const bool lazy = lazy_ok(q);
+    const u64* cs = c + (size_t)blockIdx.z * c_bs + off;
+    u64* dst = out + (size_t)blockIdx.z * out_bs + off;
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        const int e = (u * kTileThreads + t) * 2;
+        const ulonglong2 x = ldg128(cs + e);
+        ulonglong2 r;
+        r.x = add_mod(shoup_mul(x.x, qlinv.v[i], qlinv.sh[i], q), fwd_normalize(sm[tphys(e)], q, pc.mu64, lazy), q);
+        r.y = add_mod(shoup_mul(x.y, qlinv.v[i], qlinv.sh[i], q), fwd_normalize(sm[tphys(e + 1)], q, pc.mu64, lazy), q);
+        st128(dst + e, r);
+    }
+}
+
+template <int LOGN>
+static void modup_t(const DevTables& T, const ModUpArgs& m, cudaStream_t st) {
+    using G = NttGeo<LOGN>;
+    const int ext = m.nl + m.K;
+    k_inv_rows<LOGN><<<dim3(G::TILES, m.nl, m.nbatch), kTileThreads, 0, st>>>(T, m.c, m.c_bs, m.scratch, (size_t)m.nl * T.N, 0);
+    for (int d = 0; d < m.ndig; d++) {
+        const int lo = d * m.alpha, hi = (d == m.ndig - 1) ? m.nl : (d + 1) * m.alpha, sz = hi - lo;
+        k_inv_cols<LOGN><<<dim3(G::TILES, sz, m.nbatch), kTileThreads, 0, st>>>(T, m.tabs[d], m.scratch + (size_t)lo * T.N, (size_t)m.nl * T.N);
+        k_conv_fwd_col<LOGN><<<dim3(G::TILES, ext - sz, m.nbatch), kTileThreads, 0, st>>>(
+            T, m.tabs[d], m.scratch + (size_t)lo * T.N, (size_t)m.nl * T.N, m.digits + (size_t)d * ext * T.N, (size_t)m.ndig * ext * T.N, m.nl, m.L);
+    }
+    k_modup_rows<LOGN><<<dim3(G::TILES, ext, m.ndig * m.nbatch), kTileThreads, 0, st>>>(T, m.digits, m.c, m.c_bs, m.ndig, m.nl, m.L, m.alpha);
+}
+void launch_fused_modup(const DevTables& T, const ModUpArgs& m, cudaStream_t st) {
+    switch (T.logN) {
+        case 12: modup_t<12>(T, m, st); break;
+        case 13: modup_t<13>(T, m, st); break;
+        case 14: modup_t<14>(T, m, st); break;
+        case 15: modup_t<15>(T, m, st); break;
+        case 16: modup_t<16>(T, m, st); break;
+        default: break;
+    }
+}
+
+template <int LOGN>
+static void rescale_t(const DevTables& T, const RescaleArgs& r, cudaStream_t st) {
+    using G = NttGeo<LOGN>;
+    const int nl = r.nl;
+    // dropped limb of every component -> coefficients (inverse rows, then inverse columns * N^-1 via the 1-limb table)
+    k_inv_rows<LOGN><<<dim3(G::TILES, 1, r.ncomp), kTileThreads, 0, st>>>(T, r.c + (size_t)(nl - 1) * T.N, r.c_bs, r.last, (size_t)T.N, nl - 1);
+    k_inv_cols<LOGN><<<dim3(G::TILES, 1, r.ncomp), kTileThreads, 0, st>>>(T, r.last_tab, r.last, (size_t)T.N);
+    k_rescale_cols<LOGN><<<dim3(G::TILES, nl - 1, r.ncomp), kTileThreads, 0, st>>>(T, r.last, (size_t)T.N, r.tmp, (size_t)(nl - 1) * T.N, nl, r.negqlinv);
+    k_rescale_rows<LOGN><<<dim3(G::TILES, nl - 1, r.ncomp), kTileThreads, 0, st>>>(T, r.out, r.out_bs, r.c, r.c_bs, r.tmp, (size_t)(nl - 1) * T.N, r.qlinv);
+}
+void launch_fused_rescale(const DevTables& T, const RescaleArgs& r, cudaStream_t st) {
+    switch (T.logN) {
+        case 12: rescale_t<12>(T, r, st); break;
+        case 13: rescale_t<13>(T, r, st); break;
+        case 14: rescale_t<14>(T, r, st); break;
+        case 15: rescale_t<15>(T, r, st); break;
+        case 16: rescale_t<16>(T, r, st); break;
+        default: break;
+    }
 }
 
 bool fused_ks_supported(int logN) { return logN >= 12 && logN <= 16; }

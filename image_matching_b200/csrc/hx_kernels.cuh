@@ -71,6 +71,26 @@ struct FusedKsArgs {
 bool fused_ks_supported(int logN);
 void launch_fused_ks(const DevTables& T, const FusedKsArgs& a, const BaseConvTable* moddown, int nb, cudaStream_t st);
 
+// fused ModUp: c [nbatch] x c_bs, each [nl][N]  ->  digits [nbatch][ndig][nl+K][N]
+struct ModUpArgs {
+    const u64* c; size_t c_bs; int nbatch;
+    int nl, L, K, ndig, alpha;
+    const BaseConvTable* tabs[kMaxDigits];   // per digit: own limbs -> complement (Q then P)
+    u64* scratch;                            // [nbatch][nl][N]
+    u64* digits;
+};
+void launch_fused_modup(const DevTables& T, const ModUpArgs& m, cudaStream_t st);
+// fused rescale: c [ncomp] x c_bs, each [nl][N]  ->  out [ncomp] x out_bs, each [nl-1][N]
+struct RescaleArgs {
+    const u64* c; size_t c_bs; int ncomp, nl;
+    const BaseConvTable* last_tab;           // 1-limb table of prime nl-1 (hatinv_n = N^-1)
+    u64* last;                               // scratch [ncomp][N]
+    u64* tmp;                                // scratch [ncomp][nl-1][N]
+    u64* out; size_t out_bs;
+    ScalarTable negqlinv, qlinv;
+};
+void launch_fused_rescale(const DevTables& T, const RescaleArgs& r, cudaStream_t st);
+
 // ---- elementwise family (row P8)
 enum EwOp { EW_ADD = 0, EW_SUB = 1, EW_MUL = 2 };
 void launch_ew(const DevTables& T, EwOp op, u64* out, const u64* a, const u64* b, int nl, int ncomp, size_t comp_stride_out,

@@ -216,7 +216,7 @@ __global__ void __launch_bounds__(kTileThreads) k_ntt_row_t(const __grid_constan
     const int prime = lm.prime[blockIdx.y % lm.period];
     if (prime < 0) return;                 // limb not part of this transform (block-uniform)
     const PrimeConst pc = T.pc[prime];
-    const u64 q = pc.q, q2 = q << 1;
+    const u64 q = pc.q;
     const int t = threadIdx.x, tile = blockIdx.x;
     u64* limb = data + (size_t)blockIdx.y * T.N + (size_t)tile * kTileN;
 #pragma unroll
@@ -233,8 +233,8 @@ __global__ void __launch_bounds__(kTileThreads) k_ntt_row_t(const __grid_constan
         for (int u = 0; u < 4; u++) {
             const int e = (u * kTileThreads + t) * 2;
             ulonglong2 x;
-            x.x = csub(csub(sm[tphys(e)], q2), q);
-            x.y = csub(csub(sm[tphys(e + 1)], q2), q);
+            x.x = fwd_normalize(sm[tphys(e)], q, pc.mu64, lazy_ok(q));
+            x.y = fwd_normalize(sm[tphys(e + 1)], q, pc.mu64, lazy_ok(q));
             st128(limb + e, x);
         }
     } else {

@@ -38,7 +38,9 @@ __device__ __forceinline__ int insert_bits3(int t, int p) { return ((t >> p) << 
 // One round of R consecutive forward stages.  SL0 = first local stage (local stage sl toggles
 // local bit 10-sl); S0 = the global stage of SL0; SHIFT0 = S0 - (stage at which `tileoff` has
 // weight 1) so that twiddle index = 2^s + (tileoff << (s - S0 + SHIFT0)) + local group.
-template <int SL0, int R, int S0, int SHIFT0>
+// LAZY (moduli below 2^50 only): no conditional subtraction at all -- a value grows by at most 2q
+// per stage, so 16 stages from a canonical input stay below 33q < 2^56; the caller reduces once.
+template <int SL0, int R, int S0, int SHIFT0, bool LAZY>
 __device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q2) {
     constexpr int p = kLogTile - SL0 - R;
     const int base = insert_bits3(t, p);
@@ -58,7 +60,7 @@ __device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const 
             const int k1 = k0 | (1 << kb);
             const ulonglong2 w = __ldg(twp + (k0 >> (kb + 1)));
             u64 x = v[k0];
-            x = x >= q2 ? x - q2 : x;
+            if (!LAZY) x = x >= q2 ? x - q2 : x;
             const u64 y = shoup_lazy(v[k1], w.x, w.y, q);
             v[k0] = x + y;
             v[k1] = x - y + q2;
@@ -69,26 +71,34 @@ __device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const 
 }
 
 // Local stages [SL, SL_END) forward; a __syncthreads() after every round.
-template <int SL, int SL_END, int S, int SHIFT>
+template <int SL, int SL_END, int S, int SHIFT, bool LAZY>
 __device__ __forceinline__ void fwd_stages(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q2) {
     if constexpr (SL < SL_END) {
         constexpr int R = (SL_END - SL >= 3) ? 3 : (SL_END - SL);
-        fwd_round_ct<SL, R, S, SHIFT>(sm, t, tileoff, tw, q, q2);
+        fwd_round_ct<SL, R, S, SHIFT, LAZY>(sm, t, tileoff, tw, q, q2);
         __syncthreads();
-        fwd_stages<SL + R, SL_END, S + R, SHIFT + R>(sm, t, tileoff, tw, q, q2);
+        fwd_stages<SL + R, SL_END, S + R, SHIFT + R, LAZY>(sm, t, tileoff, tw, q, q2);
     }
+}
+// moduli for which the LAZY forward passes are valid (block-uniform test on the limb's prime)
+__device__ __forceinline__ bool lazy_ok(u64 q) { return (q >> 50) == 0; }
+// any forward-pass value (lazy or not) -> canonical residue
+__device__ __forceinline__ u64 fwd_normalize(u64 x, u64 q, u64 mu64, bool lazy) {
+    return lazy ? reduce64(x, q, mu64) : csub(csub(x, q << 1), q);
 }
 // column pass: global stages 0..A-1 = local stages 0..A-1, twiddle = 2^s + (row >> (A-s)); no tile offset
 template <int LOGN>
 __device__ __forceinline__ void fwd_col_pass(u64* sm, int t, const ulonglong2* __restrict__ tw, u64 q) {
-    fwd_stages<0, NttGeo<LOGN>::A, 0, 0>(sm, t, 0, tw, q, q << 1);
+    if (lazy_ok(q)) fwd_stages<0, NttGeo<LOGN>::A, 0, 0, true>(sm, t, 0, tw, q, q << 1);
+    else fwd_stages<0, NttGeo<LOGN>::A, 0, 0, false>(sm, t, 0, tw, q, q << 1);
 }
 // row pass: global stages A..LOGN-1 = local stages LOGD..10; tile `tile` starts at row tile<<LOGD
 template <int LOGN>
 __device__ __forceinline__ void fwd_row_pass(u64* sm, int t, int tile, const ulonglong2* __restrict__ tw, u64 q) {
     using G = NttGeo<LOGN>;
     // at stage A a row index has weight 1 in the group number; local groups are numbered inside the tile
-    fwd_stages<G::LOGD, kLogTile, G::A, G::LOGD>(sm, t, tile, tw, q, q << 1);
+    if (lazy_ok(q)) fwd_stages<G::LOGD, kLogTile, G::A, G::LOGD, true>(sm, t, tile, tw, q, q << 1);
+    else fwd_stages<G::LOGD, kLogTile, G::A, G::LOGD, false>(sm, t, tile, tw, q, q << 1);
 }
 
 // ---- inverse --------------------------------------------------------------------------------

@@ -188,3 +188,35 @@ def test_full_ring_ops_bit_exact():
     for rot in (1, 300):
         assert same(cc.EvalFastRotation(ga, rot, 2 * orc.N, gdg), orc.fast_rotation(ca, rot, dg))
     assert same(cc.EvalRotate(ga, -8), orc.rotate(ca, -8))
+
+
+@pytest.mark.parametrize("ring", [4096, 8192, 16384, 65536])
+def test_fused_pipeline_equals_unfused_kernels(ring):
+    """The fused key-switch / ModUp / rescale pipeline (hx_fused.cu) against the unfused one-op-per-kernel path
+    (hx_kernels.cu) on the product's own keys, at every tile geometry (N = 2^12 .. 2^16), all digit shapes."""
+    import image_matching_b200 as hx
+    cc = hx.CryptoContext.generate(depth=11, ring_dim=ring)
+    cl = hx.Client(cc, seed=ring)
+    cl.EvalMultKeyGen(); cl.EvalRotateKeyGen([1, -3, 37])
+    rng = np.random.default_rng(ring)
+    ca, cb = cl.encrypt(rng.uniform(-1, 1, ring // 2)), cl.encrypt(rng.uniform(-1, 1, ring // 2))
+
+    def run():
+        outs = []
+        for drop in (0, 3, 7, 8, 10, 11):
+            xa, xb = cc.LevelReduce(ca, drop), cc.LevelReduce(cb, drop)
+            m = cc.EvalMult(xa, xb)
+            outs += [m, cc.EvalRotate(xa, 37), cc.EvalRotate(m, -3)]
+            if drop < 11:
+                outs += [cc.Rescale(m), cc.Rescale(cc.EvalMultNoRelin(xa, xb))]
+        dg = cc.EvalFastRotationPrecompute(ca)
+        outs += [cc.EvalFastRotation(ca, 1, 2 * ring, dg), cc.EvalFastRotation(ca, -3, 2 * ring, dg)]
+        return [o.to_numpy() for o in outs]
+
+    fused = run()
+    cc.set_option("force_unfused", 1)
+    plain = run()
+    cc.set_option("force_unfused", 0)
+    assert len(fused) == len(plain)
+    for f, p in zip(fused, plain):
+        assert np.array_equal(f, p)

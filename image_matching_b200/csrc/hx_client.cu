@@ -205,8 +205,7 @@ EvalKey Client::ks_keygen(const u64* s_old, const u64* s_new) {
         k_ksgen_b<<<grid1(N, np), kCT, 0, eng->st>>>(eng->T, bj, aj, e, s_new, s_old, eng->scalar_table(fac));
         eng->free_words(e);
     }
-    launch_to_mont(eng->T, k.a, eng->dnum * np, lm, eng->st);
-    launch_to_mont(eng->T, k.b, eng->dnum * np, lm, eng->st);
+    eng->finish_key(k);
     return k;
 }
 void Client::gen_mult_key() {

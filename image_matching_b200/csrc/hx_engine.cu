@@ -237,7 +237,7 @@ const u32* Engine::automap(u64 galois) {
 }
 
 // ApproxSwitchCRTBasis tables: src/dst are prime indices.
-BaseConvTable* Engine::make_table(const std::vector<int>& src, const std::vector<int>& dst) {
+BaseConvTable* Engine::make_table(const std::vector<int>& src, const std::vector<int>& dst, const std::vector<u64>* out_scale) {
     BaseConvTable h;
     std::memset(&h, 0, sizeof(h));
     h.n_in = (int)src.size();
@@ -258,6 +258,7 @@ BaseConvTable* Engine::make_table(const std::vector<int>& src, const std::vector
             for (int k = 0; k < h.n_in; k++)
                 if (k != i) hm = mulmod(hm, mods[src[k]] % pj, pj);
             u64 r1 = (u64)((((u128)1) << 64) % pj);
+            if (out_scale) hm = mulmod(hm, (*out_scale)[j] % pj, pj);
             h.mat[i * h.n_out + j] = mulmod(hm, r1, pj);   // Montgomery form
         }
     }
@@ -291,7 +292,9 @@ const BaseConvTable* Engine::moddown_table(int nl) {
     std::vector<int> src, dst;
     for (int k = 0; k < K; k++) src.push_back(L + k);
     for (int i = 0; i < nl; i++) dst.push_back(i);
-    return moddown_tabs_[nl] = make_table(src, dst);
+    std::vector<u64> pinv(nl);
+    for (int i = 0; i < nl; i++) pinv[i] = invmod(P_mod(i), mods[i]);
+    return moddown_tabs_[nl] = make_table(src, dst, &pinv);   // ApproxModDown's final * P^-1 folded into the matrix
 }
 
 // ------------------------------------------------------------------------------------------ keys
@@ -302,16 +305,25 @@ static EvalKey upload_key(Engine& e, const u64* a, const u64* b) {
     HX_CUDA(cudaMalloc(&k.b, words * sizeof(u64)));
     HX_CUDA(cudaMemcpyAsync(k.a, a, words * sizeof(u64), cudaMemcpyHostToDevice, e.st));
     HX_CUDA(cudaMemcpyAsync(k.b, b, words * sizeof(u64), cudaMemcpyHostToDevice, e.st));
-    std::vector<int> primes;
-    for (int i = 0; i < e.L + e.K; i++) primes.push_back(i);
-    LimbMap lm = e.limb_map(primes);
-    {
-        Engine::Scope sc(&e, PK_MISC, 2, 32.0 * words);
-        launch_to_mont(e.T, k.a, e.dnum * (e.L + e.K), lm, e.st);
-        launch_to_mont(e.T, k.b, e.dnum * (e.L + e.K), lm, e.st);
-    }
+    e.finish_key(k);
     e.sync();
     return k;
+}
+// Engine-internal key form: Montgomery residues, Q limbs pre-multiplied by P^-1 (so ModDown's last
+// multiplication disappears from the key-switch kernels).  Input: plain residues, [dnum][L+K][N].
+void Engine::finish_key(EvalKey& k) {
+    std::vector<int> primes;
+    for (int i = 0; i < L + K; i++) primes.push_back(i);
+    LimbMap lm = limb_map(primes);
+    std::vector<u64> pinv(L);
+    for (int i = 0; i < L; i++) pinv[i] = invmod(P_mod(i), mods[i]);
+    ScalarTable ps = scalar_table(pinv);
+    const size_t ds = (size_t)(L + K) * N;
+    Scope sc(this, PK_MISC, 4, 64.0 * dnum * (L + K) * N);
+    launch_to_mont(T, k.a, dnum * (L + K), lm, st);
+    launch_to_mont(T, k.b, dnum * (L + K), lm, st);
+    launch_mul_scalar(T, k.a, k.a, ps, L, dnum, ds, ds, st);
+    launch_mul_scalar(T, k.b, k.b, ps, L, dnum, ds, ds, st);
 }
 void Engine::load_mult_key(const u64* a, const u64* b) {
     std::lock_guard<std::recursive_mutex> g(mu);
@@ -399,8 +411,6 @@ u64* Engine::ks_precompute(const u64* c, int nl, int* ndig_out) {
 void Engine::ks_core_batch(const u64* digits, int ndig, int nl, const std::vector<const EvalKey*>& keys, const u64* addend,
                            int addend_comps, const std::vector<u64>& galois, u64* out, size_t out_bs) {
     const int nb = (int)keys.size(), ext = nl + K;
-    std::vector<u64> pinv(nl);
-    for (int i = 0; i < nl; i++) pinv[i] = invmod(P_mod(i), mods[i]);
     if (fused_ks_supported(logN) && !force_unfused) {
         // fused pipeline (hx_fused.cu): the evaluation keys are read once, nothing of size 2 x (l+K) is stored
         for (int b0 = 0; b0 < nb; b0 += kMaxKsBatch) {
@@ -418,7 +428,6 @@ void Engine::ks_core_batch(const u64* digits, int ndig, int nl, const std::vecto
             a.add1 = (addend && addend_comps >= 2) ? addend + (size_t)nl * N : nullptr;
             a.out = out + (size_t)b0 * out_bs;
             a.out_bs = out_bs;
-            a.pinv = scalar_table(pinv);
             {   // algorithmic bytes of one key switch after ModUp: evk once, digits once per launch,
                 // addend once, result once
                 Scope sc(this, PK_KS_FUSED, 4,
@@ -463,7 +472,7 @@ void Engine::ks_core_batch(const u64* digits, int ndig, int nl, const std::vecto
     {
         Scope sc(this, PK_MODDOWN, 1, 8.0 * N * nl * nb * (2 + 2 + 2 + (addend ? addend_comps : 0)));
         launch_moddown_finish(T, ct, ct_bs, conv, conv_bs, addend, addend_comps, galois.empty() ? nullptr : (const u32* const*)(ptrs + 2 * nb),
-                              out, out_bs, nl, scalar_table(pinv), nb, st);
+                              out, out_bs, nl, nb, st);
     }
     free_words(conv);
     free_words(ct);

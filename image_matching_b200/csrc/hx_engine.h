@@ -100,6 +100,7 @@ public:
     void load_rot_key(u64 galois, const u64* a, const u64* b);
     void adopt_rot_key(u64 galois, EvalKey k);   // device-generated (client module)
     void adopt_mult_key(EvalKey k);
+    void finish_key(EvalKey& k);                 // plain residues -> engine-internal key form (in place)
     bool has_rot_key(u64 galois) const { return rot_keys_.count(galois) != 0; }
     u64 galois_for_rotation(int r) const;
 
@@ -156,7 +157,7 @@ private:
     const BaseConvTable* modup_table(int nl, int digit);
     const BaseConvTable* moddown_table(int nl);
     const BaseConvTable* last_limb_table(int prime);
-    BaseConvTable* make_table(const std::vector<int>& src, const std::vector<int>& dst);
+    BaseConvTable* make_table(const std::vector<int>& src, const std::vector<int>& dst, const std::vector<u64>* out_scale = nullptr);
     void align(Ct& a, Ct& b);
     std::vector<u64> const_for_mult(double c, int nl) const;
     std::vector<u64> const_for_add(double c, int nl, int deg) const;

@@ -17,6 +17,9 @@
 #include "hx_kernels.cuh"
 #include "hx_ntt_tile.cuh"
 
+#ifndef HX_MINB
+#define HX_MINB 3
+#endif
 namespace hx {
 
 // PrecomputeAutoMap on the fly: position J (bit-reversed order) of the output reads position
@@ -29,9 +32,9 @@ __device__ __forceinline__ u32 automap_at(u32 J, u32 g) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// K1: grid (TILES, 2*K, nb).  out: tmpP[b][comp][k][N], values in [0,2q), inverse row pass done.
+// K1: grid (TILES, 2*K, nb).  out: tmpP[b][comp][k][N], values in [0,4q), inverse row pass done.
 template <int LOGN, int NDIG>
-__global__ void __launch_bounds__(kTileThreads, 3) k_ks_p_inner(const __grid_constant__ DevTables T, const __grid_constant__ FusedKsArgs a) {
+__global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_p_inner(const __grid_constant__ DevTables T, const __grid_constant__ FusedKsArgs a) {
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, tile = blockIdx.x;
     const int k = blockIdx.y >> 1, comp = blockIdx.y & 1, b = blockIdx.z;
@@ -70,7 +73,7 @@ __global__ void __launch_bounds__(kTileThreads, 3) k_ks_p_inner(const __grid_con
 // x * hatinv_n  (hatinv_n = (Qhat_k^-1 * N^-1) mod q_k folds the N^-1 of the inverse transform into
 // the first multiplication of ApproxSwitchCRTBasis).  Output canonical, coefficient order.
 template <int LOGN>
-__global__ void __launch_bounds__(kTileThreads, 3) k_inv_cols(const __grid_constant__ DevTables T, const BaseConvTable* __restrict__ tab,
+__global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_cols(const __grid_constant__ DevTables T, const BaseConvTable* __restrict__ tab,
                                                               u64* __restrict__ data, size_t bs) {
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, tile = blockIdx.x, k = blockIdx.y;
@@ -95,7 +98,7 @@ __global__ void __launch_bounds__(kTileThreads, 3) k_inv_cols(const __grid_const
 // K2b: grid (TILES, n_out, nbatch).  in: [nbatch][n_in][N] scaled coefficients (K2a);
 // out: [nbatch][n_out][N], forward column pass done, values lazy (see fwd_round_ct).
 template <int LOGN>
-__global__ void __launch_bounds__(kTileThreads, 3) k_conv_fwd_col(const __grid_constant__ DevTables T, const BaseConvTable* __restrict__ tab,
+__global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __grid_constant__ DevTables T, const BaseConvTable* __restrict__ tab,
                                                                   const u64* __restrict__ in, size_t in_bs, u64* __restrict__ out, size_t out_bs,
                                                                   int ext_nl, int L) {
     __shared__ u64 sm[kTileWords];
@@ -128,11 +131,11 @@ __global__ void __launch_bounds__(kTileThreads, 3) k_conv_fwd_col(const __grid_c
 }
 
 // ---------------------------------------------------------------------------------------------
-// K3: grid (TILES, 2*nl, nb).  out[b][comp][i][J] = ((ip - conv) * P^-1 + addend)[map_g(J)]
+// K3: grid (TILES, 2*nl, nb).  out[b][comp][i][J] = (ip' - conv' + addend)[map_g(J)]  (ip', conv' carry the factor P^-1)
 // All global loads (converted tile, digits, key limbs) are issued before the transform so the
 // memory phase of one CTA overlaps the butterfly phase of its neighbours on the SM.
 template <int LOGN, int NDIG>
-__global__ void __launch_bounds__(kTileThreads, 3) k_ks_q_finish(const __grid_constant__ DevTables T, const __grid_constant__ FusedKsArgs a) {
+__global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __grid_constant__ DevTables T, const __grid_constant__ FusedKsArgs a) {
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, otile = blockIdx.x;
     const int i = blockIdx.y >> 1, comp = blockIdx.y & 1, b = blockIdx.z;
@@ -169,13 +172,13 @@ __global__ void __launch_bounds__(kTileThreads, 3) k_ks_q_finish(const __grid_co
     fwd_row_pass<LOGN>(sm, t, tile, T.tw_fwd + (size_t)i * T.N, q);
     const u64* add = (comp == 0 ? a.add0 : a.add1);
     if (add) add += (size_t)i * T.N + toff;
-    const u64 pinv = a.pinv.v[i], pinv_sh = a.pinv.sh[i];
+    // P^-1 is folded into the evaluation keys' Q limbs and into the ModDown conversion matrix at load time
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
         const u64 c0 = fwd_normalize(sm[tphys(e)], q, pc.mu64, lazy), c1 = fwd_normalize(sm[tphys(e + 1)], q, pc.mu64, lazy);
-        u64 r0 = shoup_mul(sub_mod(ip[2 * u], c0, q), pinv, pinv_sh, q);
-        u64 r1 = shoup_mul(sub_mod(ip[2 * u + 1], c1, q), pinv, pinv_sh, q);
+        u64 r0 = sub_mod(ip[2 * u], c0, q);
+        u64 r1 = sub_mod(ip[2 * u + 1], c1, q);
         if (add) {
             const ulonglong2 ad = ldg128(add + e);
             r0 = add_mod(r0, ad.x, q);
@@ -223,7 +226,7 @@ static void launch_fused_t(const DevTables& T, const FusedKsArgs& a, const BaseC
 // Inverse row pass, out of place: grid (TILES, nlimbs, nbatch); limb y of batch z is read at
 // in + z*in_bs + y*N and written to out + z*out_bs + y*N; prime index = prime0 + y.  Values [0,2q).
 template <int LOGN>
-__global__ void __launch_bounds__(kTileThreads, 3) k_inv_rows(const __grid_constant__ DevTables T, const u64* __restrict__ in, size_t in_bs,
+__global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_rows(const __grid_constant__ DevTables T, const u64* __restrict__ in, size_t in_bs,
                                                               u64* __restrict__ out, size_t out_bs, int prime0) {
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, tile = blockIdx.x, prime = prime0 + blockIdx.y;
@@ -250,7 +253,7 @@ __global__ void __launch_bounds__(kTileThreads, 3) k_inv_rows(const __grid_const
 // ModUp tail: grid (TILES, ext, ndig*nbatch).  Limb y of digit d: own limbs [lo,hi) are copied from the
 // input polynomial, the converted limbs get their forward row pass (in place) and are normalised.
 template <int LOGN>
-__global__ void __launch_bounds__(kTileThreads, 3) k_modup_rows(const __grid_constant__ DevTables T, u64* __restrict__ digits, const u64* __restrict__ c,
+__global__ void __launch_bounds__(kTileThreads, HX_MINB) k_modup_rows(const __grid_constant__ DevTables T, u64* __restrict__ digits, const u64* __restrict__ c,
                                                                 size_t c_bs, int ndig, int nl, int L, int alpha) {
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, tile = blockIdx.x, y = blockIdx.y;
@@ -292,7 +295,7 @@ __global__ void __launch_bounds__(kTileThreads, 3) k_modup_rows(const __grid_con
 // (canonical, K2a with a 1x0 table does inverse columns + N^-1); tmp_i = lift(last) * (-q_l^-1) mod q_i
 // (centred lift: v > q_l/2 means v - q_l, and q_l * (-q_l^-1) = -1, hence the "+1"), forward column pass.
 template <int LOGN>
-__global__ void __launch_bounds__(kTileThreads, 3) k_rescale_cols(const __grid_constant__ DevTables T, const u64* __restrict__ last, size_t last_bs,
+__global__ void __launch_bounds__(kTileThreads, HX_MINB) k_rescale_cols(const __grid_constant__ DevTables T, const u64* __restrict__ last, size_t last_bs,
                                                                   u64* __restrict__ tmp, size_t tmp_bs, int nl, const __grid_constant__ ScalarTable negqlinv) {
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, tile = blockIdx.x, i = blockIdx.y;
@@ -317,7 +320,7 @@ __global__ void __launch_bounds__(kTileThreads, 3) k_rescale_cols(const __grid_c
 }
 // Rescale, row stage: out_i = c_i * q_l^-1 + NTT(tmp_i).  grid (TILES, nl-1, nbatch).
 template <int LOGN>
-__global__ void __launch_bounds__(kTileThreads, 3) k_rescale_rows(const __grid_constant__ DevTables T, u64* __restrict__ out, size_t out_bs,
+__global__ void __launch_bounds__(kTileThreads, HX_MINB) k_rescale_rows(const __grid_constant__ DevTables T, u64* __restrict__ out, size_t out_bs,
                                                                   const u64* __restrict__ c, size_t c_bs, const u64* __restrict__ tmp, size_t tmp_bs,
                                                                   const __grid_constant__ ScalarTable qlinv) {
     __shared__ u64 sm[kTileWords];

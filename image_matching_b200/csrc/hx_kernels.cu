@@ -107,11 +107,11 @@ void launch_ks_inner(const DevTables& T, const u64* digits, int ndig, int nl, in
 
 // ---------------------------------------------------------------------------------------------
 // ApproxModDown epilogue (row P5) fused with "+ c0" and the automorphism gather (row P3):
-//   out[i][j] = (ct[i][m] - conv[i][m]) * P^-1 + addend[i][m],  m = map[j]
+//   out[i][j] = ct'[i][m] - conv'[i][m] + addend[i][m],  m = map[j]   (keys and conversion matrix carry P^-1)
 // grid.y = limb (nl), grid.z = batch*2 + component; addend ([comps][nl][N]) applies to components < addend_comps.
 __global__ void __launch_bounds__(kThreads) k_moddown_finish(DevTables T, const u64* __restrict__ ct, size_t ct_bs, const u64* __restrict__ conv,
                                                              size_t conv_bs, const u64* __restrict__ addend, int addend_comps, const u32* const* __restrict__ maps,
-                                                             u64* __restrict__ out, size_t out_bs, int nl, int ext, ScalarTable pinv) {
+                                                             u64* __restrict__ out, size_t out_bs, int nl, int ext) {
     int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (idx >= T.N) return;
     int i = blockIdx.y;
@@ -126,7 +126,6 @@ __global__ void __launch_bounds__(kThreads) k_moddown_finish(DevTables T, const 
     for (int e = 0; e < 2; e++) {
         int m = map ? (int)map[idx + e] : idx + e;
         u64 d = sub_mod(c[m], v[m], q);
-        d = shoup_mul(d, pinv.v[i], pinv.sh[i], q);
         if (ad) d = add_mod(d, ad[m], q);
         r[e] = d;
     }
@@ -135,11 +134,11 @@ __global__ void __launch_bounds__(kThreads) k_moddown_finish(DevTables T, const 
 }
 
 void launch_moddown_finish(const DevTables& T, const u64* ct, size_t ct_bs, const u64* conv, size_t conv_bs, const u64* addend,
-                           int addend_comps, const u32* const* maps, u64* out, size_t out_bs, int nl, const ScalarTable& pinv, int nbatch,
+                           int addend_comps, const u32* const* maps, u64* out, size_t out_bs, int nl, int nbatch,
                            cudaStream_t st) {
     dim3 grid(blocks_for(T.N), nl, nbatch * 2);
     int ext = (int)(ct_bs / (2 * (size_t)T.N));   // ct batch entry = [2][ext][N]
-    k_moddown_finish<<<grid, kThreads, 0, st>>>(T, ct, ct_bs, conv, conv_bs, addend, addend_comps, maps, out, out_bs, nl, ext, pinv);
+    k_moddown_finish<<<grid, kThreads, 0, st>>>(T, ct, ct_bs, conv, conv_bs, addend, addend_comps, maps, out, out_bs, nl, ext);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -50,7 +50,7 @@ void launch_ks_inner(const DevTables& T, const u64* digits, int ndig, int nl, in
 // out[i][j] = ( (ct[i][m] - conv[i][m]) * Pinv_i + (addend ? addend[i][m] : 0) ),  m = map ? map[j] : j
 void launch_moddown_finish(const DevTables& T, const u64* ct, size_t ct_batch_stride, const u64* conv, size_t conv_batch_stride,
                            const u64* addend, int addend_comps, const u32* const* maps, u64* out, size_t out_batch_stride, int nl,
-                           const ScalarTable& pinv, int nbatch, cudaStream_t st);
+                           int nbatch, cudaStream_t st);
 
 // ---- fused key switch (hx_fused.cu): rows P2-P5 in three launches per batch of keys
 constexpr int kMaxKsBatch = 32;
@@ -66,7 +66,6 @@ struct FusedKsArgs {
     const u64* add1;
     u64* out;                       // [nb] x out_bs, each [2][nl][N]
     size_t out_bs;
-    ScalarTable pinv;               // P^-1 mod q_i
 };
 bool fused_ks_supported(int logN);
 void launch_fused_ks(const DevTables& T, const FusedKsArgs& a, const BaseConvTable* moddown, int nb, cudaStream_t st);

@@ -49,6 +49,15 @@ __device__ __forceinline__ u64 shoup_lazy(u64 a, u64 w, u64 wsh, u64 q) {
     return a * w - hi * q;
 }
 __device__ __forceinline__ u64 shoup_mul(u64 a, u64 w, u64 wsh, u64 q) { return csub(shoup_lazy(a, w, wsh, q), q); }
+// Cheaper lazy product for the NTT butterflies: the quotient estimate drops a_lo*wsh_lo and the carries
+// of the two cross terms, so it is hi, hi-1 or hi-2 and the result lies in [0,4q) (still a*w mod q).
+// Three IMAD.WIDE instead of four and no carry chain (measured 14.4 vs 16.4 issue slots, tools/microbench2.cu).
+__device__ __forceinline__ u64 umulhi_approx(u64 a, u64 b) {
+    const u32 a0 = (u32)a, a1 = (u32)(a >> 32), b0 = (u32)b, b1 = (u32)(b >> 32);
+    const u64 s1 = (u64)a0 * b1, s2 = (u64)a1 * b0;
+    return (u64)a1 * b1 + ((s1 >> 32) + (s2 >> 32));
+}
+__device__ __forceinline__ u64 shoup_lazy4(u64 a, u64 w, u64 wsh, u64 q) { return a * w - umulhi_approx(a, wsh) * q; }
 
 // Montgomery REDC: T = hi*2^64 + lo < q*2^64  ->  T * 2^-64 mod q in [0,q).
 __device__ __forceinline__ u64 redc(u128d t, u64 q, u64 qinv_neg) {

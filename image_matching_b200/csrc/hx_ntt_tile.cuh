@@ -9,8 +9,9 @@
 //   column pass = stages 0..A-1   on a tile of all 2^A rows x C = 2^(11-A) adjacent columns
 //   row pass    = stages A..LOGN-1 on a tile of D = 2^(11-B) whole rows = 2048 contiguous words
 // A thread owns 8 tile elements per round and runs up to 3 stages in registers (radix-8) between
-// shared-memory exchanges.  Harvey lazy butterflies on Shoup twiddles: forward values live in
-// [0,4q), inverse values in [0,2q); callers normalise on the way out.
+// shared-memory exchanges.  Harvey lazy butterflies on Shoup twiddles with the approximate quotient
+// of shoup_lazy4 (product in [0,4q)): forward values live in [0,8q), inverse values in [0,4q)
+// (q < 2^60, so 8q fits a word); callers normalise on the way out.
 #pragma once
 #include "hx_modarith.cuh"
 
@@ -38,10 +39,10 @@ __device__ __forceinline__ int insert_bits3(int t, int p) { return ((t >> p) << 
 // One round of R consecutive forward stages.  SL0 = first local stage (local stage sl toggles
 // local bit 10-sl); S0 = the global stage of SL0; SHIFT0 = S0 - (stage at which `tileoff` has
 // weight 1) so that twiddle index = 2^s + (tileoff << (s - S0 + SHIFT0)) + local group.
-// LAZY (moduli below 2^50 only): no conditional subtraction at all -- a value grows by at most 2q
-// per stage, so 16 stages from a canonical input stay below 33q < 2^56; the caller reduces once.
+// LAZY (moduli below 2^50 only): no conditional subtraction at all -- a value grows by at most 4q
+// per stage, so 16 stages from a canonical input stay below 65q < 2^57; the caller reduces once.
 template <int SL0, int R, int S0, int SHIFT0, bool LAZY>
-__device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q2) {
+__device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
     constexpr int p = kLogTile - SL0 - R;
     const int base = insert_bits3(t, p);
     u64 v[8];
@@ -60,10 +61,10 @@ __device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const 
             const int k1 = k0 | (1 << kb);
             const ulonglong2 w = __ldg(twp + (k0 >> (kb + 1)));
             u64 x = v[k0];
-            if (!LAZY) x = x >= q2 ? x - q2 : x;
-            const u64 y = shoup_lazy(v[k1], w.x, w.y, q);
+            if (!LAZY) x = x >= q4 ? x - q4 : x;
+            const u64 y = shoup_lazy4(v[k1], w.x, w.y, q);
             v[k0] = x + y;
-            v[k1] = x - y + q2;
+            v[k1] = x - y + q4;
         }
     }
 #pragma unroll
@@ -72,40 +73,40 @@ __device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const 
 
 // Local stages [SL, SL_END) forward; a __syncthreads() after every round.
 template <int SL, int SL_END, int S, int SHIFT, bool LAZY>
-__device__ __forceinline__ void fwd_stages(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q2) {
+__device__ __forceinline__ void fwd_stages(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
     if constexpr (SL < SL_END) {
         constexpr int R = (SL_END - SL >= 3) ? 3 : (SL_END - SL);
-        fwd_round_ct<SL, R, S, SHIFT, LAZY>(sm, t, tileoff, tw, q, q2);
+        fwd_round_ct<SL, R, S, SHIFT, LAZY>(sm, t, tileoff, tw, q, q4);
         __syncthreads();
-        fwd_stages<SL + R, SL_END, S + R, SHIFT + R, LAZY>(sm, t, tileoff, tw, q, q2);
+        fwd_stages<SL + R, SL_END, S + R, SHIFT + R, LAZY>(sm, t, tileoff, tw, q, q4);
     }
 }
 // moduli for which the LAZY forward passes are valid (block-uniform test on the limb's prime)
 __device__ __forceinline__ bool lazy_ok(u64 q) { return (q >> 50) == 0; }
 // any forward-pass value (lazy or not) -> canonical residue
 __device__ __forceinline__ u64 fwd_normalize(u64 x, u64 q, u64 mu64, bool lazy) {
-    return lazy ? reduce64(x, q, mu64) : csub(csub(x, q << 1), q);
+    return lazy ? reduce64(x, q, mu64) : csub(csub(csub(x, q << 2), q << 1), q);
 }
 // column pass: global stages 0..A-1 = local stages 0..A-1, twiddle = 2^s + (row >> (A-s)); no tile offset
 template <int LOGN>
 __device__ __forceinline__ void fwd_col_pass(u64* sm, int t, const ulonglong2* __restrict__ tw, u64 q) {
-    if (lazy_ok(q)) fwd_stages<0, NttGeo<LOGN>::A, 0, 0, true>(sm, t, 0, tw, q, q << 1);
-    else fwd_stages<0, NttGeo<LOGN>::A, 0, 0, false>(sm, t, 0, tw, q, q << 1);
+    if (lazy_ok(q)) fwd_stages<0, NttGeo<LOGN>::A, 0, 0, true>(sm, t, 0, tw, q, q << 2);
+    else fwd_stages<0, NttGeo<LOGN>::A, 0, 0, false>(sm, t, 0, tw, q, q << 2);
 }
 // row pass: global stages A..LOGN-1 = local stages LOGD..10; tile `tile` starts at row tile<<LOGD
 template <int LOGN>
 __device__ __forceinline__ void fwd_row_pass(u64* sm, int t, int tile, const ulonglong2* __restrict__ tw, u64 q) {
     using G = NttGeo<LOGN>;
     // at stage A a row index has weight 1 in the group number; local groups are numbered inside the tile
-    if (lazy_ok(q)) fwd_stages<G::LOGD, kLogTile, G::A, G::LOGD, true>(sm, t, tile, tw, q, q << 1);
-    else fwd_stages<G::LOGD, kLogTile, G::A, G::LOGD, false>(sm, t, tile, tw, q, q << 1);
+    if (lazy_ok(q)) fwd_stages<G::LOGD, kLogTile, G::A, G::LOGD, true>(sm, t, tile, tw, q, q << 2);
+    else fwd_stages<G::LOGD, kLogTile, G::A, G::LOGD, false>(sm, t, tile, tw, q, q << 2);
 }
 
 // ---- inverse --------------------------------------------------------------------------------
 // One round of R consecutive inverse (Gentleman-Sande) stages: local stages SH-1, SH-2, .., SH-R.
 // S_TOP = global stage of local stage SH-1; SHIFT_TOP = shift of tileoff at that stage.
 template <int SH, int R, int S_TOP, int SHIFT_TOP>
-__device__ __forceinline__ void inv_round_ct(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q2) {
+__device__ __forceinline__ void inv_round_ct(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
     constexpr int p = kLogTile - SH;
     const int base = insert_bits3(t, p);
     u64 v[8];
@@ -125,9 +126,9 @@ __device__ __forceinline__ void inv_round_ct(u64* sm, int t, int tileoff, const 
             const ulonglong2 w = __ldg(twp + (k0 >> (kb + 1)));
             const u64 x = v[k0], y = v[k1];
             u64 s_ = x + y;
-            s_ = s_ >= q2 ? s_ - q2 : s_;
+            s_ = s_ >= q4 ? s_ - q4 : s_;
             v[k0] = s_;
-            v[k1] = shoup_lazy(x - y + q2, w.x, w.y, q);
+            v[k1] = shoup_lazy4(x - y + q4, w.x, w.y, q);
         }
     }
 #pragma unroll
@@ -135,25 +136,25 @@ __device__ __forceinline__ void inv_round_ct(u64* sm, int t, int tileoff, const 
 }
 // Local stages SH-1 .. SL (descending); remainder round first so the radix-8 rounds are aligned.
 template <int SL, int SH, int S_TOP, int SHIFT_TOP>
-__device__ __forceinline__ void inv_stages(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q2) {
+__device__ __forceinline__ void inv_stages(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
     if constexpr (SH > SL) {
         constexpr int rem = (SH - SL) % 3;
         constexpr int R = rem == 0 ? 3 : rem;
-        inv_round_ct<SH, R, S_TOP, SHIFT_TOP>(sm, t, tileoff, tw, q, q2);
+        inv_round_ct<SH, R, S_TOP, SHIFT_TOP>(sm, t, tileoff, tw, q, q4);
         __syncthreads();
-        inv_stages<SL, SH - R, S_TOP - R, SHIFT_TOP - R>(sm, t, tileoff, tw, q, q2);
+        inv_stages<SL, SH - R, S_TOP - R, SHIFT_TOP - R>(sm, t, tileoff, tw, q, q4);
     }
 }
 template <int LOGN>
 __device__ __forceinline__ void inv_row_pass(u64* sm, int t, int tile, const ulonglong2* __restrict__ tw, u64 q) {
     using G = NttGeo<LOGN>;
     // top stage LOGN-1: shift of the tile offset there = LOGD + (LOGN-1-A) = 10
-    inv_stages<G::LOGD, kLogTile, LOGN - 1, kLogTile - 1>(sm, t, tile, tw, q, q << 1);
+    inv_stages<G::LOGD, kLogTile, LOGN - 1, kLogTile - 1>(sm, t, tile, tw, q, q << 2);
 }
 template <int LOGN>
 __device__ __forceinline__ void inv_col_pass(u64* sm, int t, const ulonglong2* __restrict__ tw, u64 q) {
     using G = NttGeo<LOGN>;
-    inv_stages<0, G::A, G::A - 1, 16>(sm, t, 0, tw, q, q << 1);   // tile offset unused (0); 16 keeps shifts non-negative
+    inv_stages<0, G::A, G::A - 1, 16>(sm, t, 0, tw, q, q << 2);   // tile offset unused (0); 16 keeps shifts non-negative
 }
 
 // ---- tile addressing ------------------------------------------------------------------------

@@ -41,6 +41,7 @@ Engine::Engine(int N_, int L_, int K_, int dnum_, const u64* q, const u64* p, co
     const int np = L + K;
     std::vector<PrimeConst> pcs(np);
     std::vector<ulonglong2> twf((size_t)np * N), twi((size_t)np * N);
+    std::vector<double2> twd((size_t)np * N);
     for (int i = 0; i < np; i++) {
         u64 m = mods[i];
         PrimeConst& c = pcs[i];
@@ -53,7 +54,7 @@ Engine::Engine(int N_, int L_, int K_, int dnum_, const u64* q, const u64* p, co
         c.mu64 = (u64)((((u128)1) << 64) / m);
         c.ninv = invmod((u64)N % m, m);
         c.ninv_sh = shoup(c.ninv, m);
-        c.pad = 0;
+        c.qinv_d = 1.0 / (double)m;
         if (powmod(psis[i], (u64)N, m) != m - 1) throw std::runtime_error("psi is not a primitive 2N-th root of unity");
         u64 psi_inv = invmod(psis[i], m);
         u64 x = 1, y = 1;
@@ -61,6 +62,7 @@ Engine::Engine(int N_, int L_, int K_, int dnum_, const u64* q, const u64* p, co
             size_t r = (size_t)i * N + bitrev((u64)k, logN);
             twf[r] = make_ulonglong2(x, shoup(x, m));
             twi[r] = make_ulonglong2(y, shoup(y, m));
+            twd[r] = make_double2((double)x, (double)x / (double)m);   // exact / correctly rounded when m < 2^53
             x = mulmod(x, psis[i], m);
             y = mulmod(y, psi_inv, m);
         }
@@ -68,10 +70,12 @@ Engine::Engine(int N_, int L_, int K_, int dnum_, const u64* q, const u64* p, co
     HX_CUDA(cudaMalloc(&d_pc_, sizeof(PrimeConst) * np));
     HX_CUDA(cudaMalloc(&d_twf_, sizeof(ulonglong2) * twf.size()));
     HX_CUDA(cudaMalloc(&d_twi_, sizeof(ulonglong2) * twi.size()));
+    HX_CUDA(cudaMalloc(&d_twd_, sizeof(double2) * twd.size()));
+    HX_CUDA(cudaMemcpy(d_twd_, twd.data(), sizeof(double2) * twd.size(), cudaMemcpyHostToDevice));
     HX_CUDA(cudaMemcpy(d_pc_, pcs.data(), sizeof(PrimeConst) * np, cudaMemcpyHostToDevice));
     HX_CUDA(cudaMemcpy(d_twf_, twf.data(), sizeof(ulonglong2) * twf.size(), cudaMemcpyHostToDevice));
     HX_CUDA(cudaMemcpy(d_twi_, twi.data(), sizeof(ulonglong2) * twi.size(), cudaMemcpyHostToDevice));
-    T.N = N; T.logN = logN; T.nprimes = np; T.pc = d_pc_; T.tw_fwd = d_twf_; T.tw_inv = d_twi_;
+    T.N = N; T.logN = logN; T.nprimes = np; T.pc = d_pc_; T.tw_fwd = d_twf_; T.tw_inv = d_twi_; T.tw_fwd_d = d_twd_;
 }
 
 Engine::~Engine() {
@@ -88,7 +92,7 @@ Engine::~Engine() {
     for (auto& r : prof_recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
     for (auto ev : prof_pool) cudaEventDestroy(ev);
     if (timer_a) { cudaEventDestroy(timer_a); cudaEventDestroy(timer_b); }
-    cudaFree(d_pc_); cudaFree(d_twf_); cudaFree(d_twi_);
+    cudaFree(d_pc_); cudaFree(d_twf_); cudaFree(d_twi_); cudaFree(d_twd_);
     cudaStreamDestroy(st);
 }
 

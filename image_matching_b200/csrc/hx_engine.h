@@ -174,6 +174,7 @@ private:
     std::map<int, DbBlock> db_;
     PrimeConst* d_pc_ = nullptr;
     ulonglong2 *d_twf_ = nullptr, *d_twi_ = nullptr;
+    double2* d_twd_ = nullptr;
     std::vector<void*> owned_;   // device allocations released with the engine
 };
 

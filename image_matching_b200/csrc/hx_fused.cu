@@ -117,9 +117,9 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
             acc_wide(acc[u], __ldg(src + (size_t)k * T.N + col_offset<LOGN>(tile, u * kTileThreads + t)), m);
     }
 #pragma unroll
-    for (int u = 0; u < 8; u++) sm[tphys(u * kTileThreads + t)] = redc(acc[u], pc.q, pc.qinv_neg);
+    for (int u = 0; u < 8; u++) sm[tphys(u * kTileThreads + t)] = fwd_encode(redc(acc[u], pc.q, pc.qinv_neg), fp_ok(pc.q));
     __syncthreads();
-    fwd_col_pass<LOGN>(sm, t, T.tw_fwd + (size_t)prime * T.N, pc.q);
+    fwd_col_pass<LOGN>(sm, t, T, prime, pc.q);
     // ext_nl >= 0 (ModUp): the output is a digit in extended-basis order (Q limbs 0..nl-1, then P); else limb j
     const int pos = ext_nl < 0 ? j : (prime < L ? prime : ext_nl + prime - L);
     u64* dst = out + (size_t)blockIdx.z * out_bs + (size_t)pos * T.N;
@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __g
     const int tile = (int)(automap_at<LOGN>((u32)otile << kLogTile, g) >> kLogTile);
     const PrimeConst pc = T.pc[i];
     const u64 q = pc.q;
-    const bool lazy = lazy_ok(q);
+    const bool fp = fp_ok(q);
     const size_t toff = (size_t)tile * kTileN;
     const u64* cv = a.conv + (((size_t)b * 2 + comp) * a.nl + i) * T.N + toff;
     const u64* key = (comp == 0 ? a.keyB[b] : a.keyA[b]) + (size_t)i * T.N + toff;
@@ -169,14 +169,14 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __g
         ip[2 * u + 1] = redc(a1, q, pc.qinv_neg);
     }
     __syncthreads();
-    fwd_row_pass<LOGN>(sm, t, tile, T.tw_fwd + (size_t)i * T.N, q);
+    fwd_row_pass<LOGN>(sm, t, tile, T, i, q);
     const u64* add = (comp == 0 ? a.add0 : a.add1);
     if (add) add += (size_t)i * T.N + toff;
     // P^-1 is folded into the evaluation keys' Q limbs and into the ModDown conversion matrix at load time
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
-        const u64 c0 = fwd_normalize(sm[tphys(e)], q, pc.mu64, lazy), c1 = fwd_normalize(sm[tphys(e + 1)], q, pc.mu64, lazy);
+        const u64 c0 = fwd_normalize(sm[tphys(e)], pc, fp), c1 = fwd_normalize(sm[tphys(e + 1)], pc, fp);
         u64 r0 = sub_mod(ip[2 * u], c0, q);
         u64 r1 = sub_mod(ip[2 * u + 1], c1, q);
         if (add) {
@@ -281,12 +281,12 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_modup_rows(const __gr
         sm[tphys(e + 1)] = x.y;
     }
     __syncthreads();
-    fwd_row_pass<LOGN>(sm, t, tile, T.tw_fwd + (size_t)prime * T.N, q);
-    const bool lazy = lazy_ok(q);
+    fwd_row_pass<LOGN>(sm, t, tile, T, prime, q);
+    const bool fp = fp_ok(q);
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
-        ulonglong2 x = {fwd_normalize(sm[tphys(e)], q, pc.mu64, lazy), fwd_normalize(sm[tphys(e + 1)], q, pc.mu64, lazy)};
+        ulonglong2 x = {fwd_normalize(sm[tphys(e)], pc, fp), fwd_normalize(sm[tphys(e + 1)], pc, fp)};
         st128(limb + e, x);
     }
 }
@@ -307,10 +307,10 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_rescale_cols(const __
         const u64 v = __ldg(src + col_offset<LOGN>(tile, l));
         u64 r = shoup_mul(v, negqlinv.v[i], negqlinv.sh[i], q);
         if (v > half) r = add_mod(r, 1, q);
-        sm[tphys(l)] = r;
+        sm[tphys(l)] = fwd_encode(r, fp_ok(q));
     }
     __syncthreads();
-    fwd_col_pass<LOGN>(sm, t, T.tw_fwd + (size_t)i * T.N, q);
+    fwd_col_pass<LOGN>(sm, t, T, i, q);
     u64* dst = tmp + (size_t)blockIdx.z * tmp_bs + (size_t)i * T.N;
 #pragma unroll
     for (int u = 0; u < 8; u++) {
@@ -337,8 +337,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_rescale_rows(const __
         sm[tphys(e + 1)] = x.y;
     }
     __syncthreads();
-    fwd_row_pass<LOGN>(sm, t, tile, T.tw_fwd + (size_t)i * T.N, q);
-    const bool lazy = lazy_ok(q);
+    fwd_row_pass<LOGN>(sm, t, tile, T, i, q);
+    const bool fp = fp_ok(q);
     const u64* cs = c + (size_t)blockIdx.z * c_bs + off;
     u64* dst = out + (size_t)blockIdx.z * out_bs + off;
 #pragma unroll
@@ -346,8 +346,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_rescale_rows(const __
         const int e = (u * kTileThreads + t) * 2;
         const ulonglong2 x = ldg128(cs + e);
         ulonglong2 r;
-        r.x = add_mod(shoup_mul(x.x, qlinv.v[i], qlinv.sh[i], q), fwd_normalize(sm[tphys(e)], q, pc.mu64, lazy), q);
-        r.y = add_mod(shoup_mul(x.y, qlinv.v[i], qlinv.sh[i], q), fwd_normalize(sm[tphys(e + 1)], q, pc.mu64, lazy), q);
+        r.x = add_mod(shoup_mul(x.x, qlinv.v[i], qlinv.sh[i], q), fwd_normalize(sm[tphys(e)], pc, fp), q);
+        r.y = add_mod(shoup_mul(x.y, qlinv.v[i], qlinv.sh[i], q), fwd_normalize(sm[tphys(e + 1)], pc, fp), q);
         st128(dst + e, r);
     }
 }

@@ -22,6 +22,7 @@ struct DevTables {
     const PrimeConst* pc;        // [nprimes]
     const ulonglong2* tw_fwd;    // [nprimes][N]  {psi^brev(i), shoup}
     const ulonglong2* tw_inv;    // [nprimes][N]  {psi^-brev(i), shoup}
+    const double2* tw_fwd_d;     // [nprimes][N]  {psi^brev(i), psi^brev(i)/q} as doubles (used for primes below 2^46)
 };
 
 // ---- NTT (row P2)

@@ -26,7 +26,7 @@ struct PrimeConst {
     u64 mu64;     // floor(2^64 / q)  (reduce an arbitrary 64-bit word)
     u64 ninv;     // N^-1 mod q
     u64 ninv_sh;  // Shoup quotient of ninv
-    u64 pad;
+    double qinv_d; // 1/q rounded to double (FP64 NTT back end, primes below 2^46)
 };
 
 __device__ __forceinline__ u128d mul_wide(u64 a, u64 b) {

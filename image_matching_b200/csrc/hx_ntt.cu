@@ -228,13 +228,13 @@ __global__ void __launch_bounds__(kTileThreads) k_ntt_row_t(const __grid_constan
     }
     __syncthreads();
     if (!kInverse) {
-        fwd_row_pass<LOGN>(sm, t, tile, T.tw_fwd + (size_t)prime * T.N, q);
+        fwd_row_pass<LOGN>(sm, t, tile, T, prime, q);
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             const int e = (u * kTileThreads + t) * 2;
             ulonglong2 x;
-            x.x = fwd_normalize(sm[tphys(e)], q, pc.mu64, lazy_ok(q));
-            x.y = fwd_normalize(sm[tphys(e + 1)], q, pc.mu64, lazy_ok(q));
+            x.x = fwd_normalize(sm[tphys(e)], pc, fp_ok(q));
+            x.y = fwd_normalize(sm[tphys(e + 1)], pc, fp_ok(q));
             st128(limb + e, x);
         }
     } else {
@@ -260,11 +260,12 @@ __global__ void __launch_bounds__(kTileThreads) k_ntt_col_t(const __grid_constan
 #pragma unroll
     for (int u = 0; u < 8; u++) {
         const int l = u * kTileThreads + t;
-        sm[tphys(l)] = limb[col_offset<LOGN>(tile, l)];
+        const u64 x = limb[col_offset<LOGN>(tile, l)];
+        sm[tphys(l)] = kInverse ? x : fwd_encode(x, fp_ok(q));
     }
     __syncthreads();
     if (!kInverse) {
-        fwd_col_pass<LOGN>(sm, t, T.tw_fwd + (size_t)prime * T.N, q);
+        fwd_col_pass<LOGN>(sm, t, T, prime, q);
 #pragma unroll
         for (int u = 0; u < 8; u++) {
             const int l = u * kTileThreads + t;

@@ -36,12 +36,45 @@ struct NttGeo {
 __device__ __forceinline__ int insert_bits3(int t, int p) { return ((t >> p) << (p + 3)) | (t & ((1 << p) - 1)); }
 
 // ---- forward --------------------------------------------------------------------------------
+// Two arithmetic back ends, chosen per prime (block-uniform):
+//  * integer (any q < 2^60): Harvey butterflies on Shoup twiddles, values in [0,8q);
+//  * FP64 (q < 2^46, i.e. the 45-bit scaling primes = 11 of the 12 Q limbs of approaches 4/5): values are
+//    exact integers held in doubles, CENTRED and lazy.  y*w mod q = y*w - rint(y*(w/q))*q is evaluated
+//    exactly with an error-free product (h = y*w rounded, l = fma(y,w,-h)) and two more FMAs, 8 DP
+//    instructions per butterfly against ~40 integer instructions; |result| <= 0.58q, so a value grows by
+//    at most 0.58q per stage: 16 stages from a canonical input stay below 10.3q < 2^50 and the pass needs
+//    no comparison or conditional subtraction at all.  All intermediate integers are < 2^53, so every
+//    operation is exact and the canonical output is bit-identical to the integer path.
+// Between the column and the row pass the words in shared/global memory are "pass-internal": lazy
+// integers (integer back end) or double bit patterns (FP64 back end).  fwd_encode() makes them from
+// canonical residues, fwd_normalize() turns them back.
+__device__ __forceinline__ bool fp_ok(u64 q) { return (q >> 46) == 0; }
+constexpr double kMagic52 = 4503599627370496.0;          // 2^52
+constexpr double kMagicRint = 6755399441055744.0;        // 1.5 * 2^52: x + M - M = rint(x) for |x| < 2^51
+// exact for 0 <= x < 2^52
+__device__ __forceinline__ double u64_to_double_small(u64 x) {
+    return __dsub_rn(__longlong_as_double((long long)(x | 0x4330000000000000ull)), kMagic52);
+}
+__device__ __forceinline__ u64 fwd_encode(u64 x, bool fp) {
+    return fp ? (u64)__double_as_longlong(u64_to_double_small(x)) : x;
+}
+// any forward-pass word -> canonical residue
+__device__ __forceinline__ u64 fwd_normalize(u64 x, const PrimeConst& pc, bool fp) {
+    if (fp) {
+        const double v = __longlong_as_double((long long)x), qd = u64_to_double_small(pc.q);
+        const double c = __dsub_rn(__fma_rn(v, pc.qinv_d, kMagicRint), kMagicRint);
+        double r = __fma_rn(-c, qd, v);                   // in [-q/2 - 1, q/2 + 1], exact
+        if (r < 0.0) r = __dadd_rn(r, qd);
+        return (u64)__double_as_longlong(__dadd_rn(r, kMagic52)) & 0x000FFFFFFFFFFFFFull;
+    }
+    const u64 q = pc.q;
+    return csub(csub(csub(x, q << 2), q << 1), q);
+}
+
 // One round of R consecutive forward stages.  SL0 = first local stage (local stage sl toggles
 // local bit 10-sl); S0 = the global stage of SL0; SHIFT0 = S0 - (stage at which `tileoff` has
 // weight 1) so that twiddle index = 2^s + (tileoff << (s - S0 + SHIFT0)) + local group.
-// LAZY (moduli below 2^50 only): no conditional subtraction at all -- a value grows by at most 4q
-// per stage, so 16 stages from a canonical input stay below 65q < 2^57; the caller reduces once.
-template <int SL0, int R, int S0, int SHIFT0, bool LAZY>
+template <int SL0, int R, int S0, int SHIFT0>
 __device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
     constexpr int p = kLogTile - SL0 - R;
     const int base = insert_bits3(t, p);
@@ -61,7 +94,7 @@ __device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const 
             const int k1 = k0 | (1 << kb);
             const ulonglong2 w = __ldg(twp + (k0 >> (kb + 1)));
             u64 x = v[k0];
-            if (!LAZY) x = x >= q4 ? x - q4 : x;
+            x = x >= q4 ? x - q4 : x;
             const u64 y = shoup_lazy4(v[k1], w.x, w.y, q);
             v[k0] = x + y;
             v[k1] = x - y + q4;
@@ -70,36 +103,73 @@ __device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const 
 #pragma unroll
     for (int k = 0; k < 8; k++) sm[tphys(base + (k << p))] = v[k];
 }
+// FP64 back end of the same round: tw = {w, w/q} as doubles.
+template <int SL0, int R, int S0, int SHIFT0>
+__device__ __forceinline__ void fwd_round_fp(double* sm, int t, int tileoff, const double2* __restrict__ tw, double q) {
+    constexpr int p = kLogTile - SL0 - R;
+    const int base = insert_bits3(t, p);
+    double v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) v[k] = sm[tphys(base + (k << p))];
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+        const int kb = R - 1 - r;
+        const int b = p + kb;
+        const int s = S0 + r;
+        const double2* twp = tw + (1 << s) + (tileoff << (SHIFT0 + r)) + (base >> (b + 1));
+#pragma unroll
+        for (int h = 0; h < 4; h++) {
+            const int lowmask = (1 << kb) - 1;
+            const int k0 = ((h & ~lowmask) << 1) | (h & lowmask);
+            const int k1 = k0 | (1 << kb);
+            const double2 w = __ldg(twp + (k0 >> (kb + 1)));
+            const double y = v[k1];
+            const double c = __dsub_rn(__fma_rn(y, w.y, kMagicRint), kMagicRint);   // rint(y * w/q)
+            const double hi = __dmul_rn(y, w.x);
+            const double lo = __fma_rn(y, w.x, -hi);                               // y*w = hi + lo exactly
+            const double m = __dadd_rn(__fma_rn(-c, q, hi), lo);                   // y*w - c*q, |m| <= 0.58 q
+            const double x = v[k0];
+            v[k0] = __dadd_rn(x, m);
+            v[k1] = __dsub_rn(x, m);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; k++) sm[tphys(base + (k << p))] = v[k];
+}
 
 // Local stages [SL, SL_END) forward; a __syncthreads() after every round.
-template <int SL, int SL_END, int S, int SHIFT, bool LAZY>
+template <int SL, int SL_END, int S, int SHIFT>
 __device__ __forceinline__ void fwd_stages(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
     if constexpr (SL < SL_END) {
         constexpr int R = (SL_END - SL >= 3) ? 3 : (SL_END - SL);
-        fwd_round_ct<SL, R, S, SHIFT, LAZY>(sm, t, tileoff, tw, q, q4);
+        fwd_round_ct<SL, R, S, SHIFT>(sm, t, tileoff, tw, q, q4);
         __syncthreads();
-        fwd_stages<SL + R, SL_END, S + R, SHIFT + R, LAZY>(sm, t, tileoff, tw, q, q4);
+        fwd_stages<SL + R, SL_END, S + R, SHIFT + R>(sm, t, tileoff, tw, q, q4);
     }
 }
-// moduli for which the LAZY forward passes are valid (block-uniform test on the limb's prime)
-__device__ __forceinline__ bool lazy_ok(u64 q) { return (q >> 50) == 0; }
-// any forward-pass value (lazy or not) -> canonical residue
-__device__ __forceinline__ u64 fwd_normalize(u64 x, u64 q, u64 mu64, bool lazy) {
-    return lazy ? reduce64(x, q, mu64) : csub(csub(csub(x, q << 2), q << 1), q);
+template <int SL, int SL_END, int S, int SHIFT>
+__device__ __forceinline__ void fwd_stages_fp(double* sm, int t, int tileoff, const double2* __restrict__ tw, double q) {
+    if constexpr (SL < SL_END) {
+        constexpr int R = (SL_END - SL >= 3) ? 3 : (SL_END - SL);
+        fwd_round_fp<SL, R, S, SHIFT>(sm, t, tileoff, tw, q);
+        __syncthreads();
+        fwd_stages_fp<SL + R, SL_END, S + R, SHIFT + R>(sm, t, tileoff, tw, q);
+    }
 }
-// column pass: global stages 0..A-1 = local stages 0..A-1, twiddle = 2^s + (row >> (A-s)); no tile offset
-template <int LOGN>
-__device__ __forceinline__ void fwd_col_pass(u64* sm, int t, const ulonglong2* __restrict__ tw, u64 q) {
-    if (lazy_ok(q)) fwd_stages<0, NttGeo<LOGN>::A, 0, 0, true>(sm, t, 0, tw, q, q << 2);
-    else fwd_stages<0, NttGeo<LOGN>::A, 0, 0, false>(sm, t, 0, tw, q, q << 2);
+// column pass: global stages 0..A-1 = local stages 0..A-1, twiddle = 2^s + (row >> (A-s)); no tile offset.
+// Shared memory holds pass-internal words (fwd_encode of canonical residues) on entry.
+template <int LOGN, class Tables>
+__device__ __forceinline__ void fwd_col_pass(u64* sm, int t, const Tables& T, int prime, u64 q) {
+    if (fp_ok(q)) fwd_stages_fp<0, NttGeo<LOGN>::A, 0, 0>(reinterpret_cast<double*>(sm), t, 0, T.tw_fwd_d + (size_t)prime * T.N, u64_to_double_small(q));
+    else fwd_stages<0, NttGeo<LOGN>::A, 0, 0>(sm, t, 0, T.tw_fwd + (size_t)prime * T.N, q, q << 2);
 }
 // row pass: global stages A..LOGN-1 = local stages LOGD..10; tile `tile` starts at row tile<<LOGD
-template <int LOGN>
-__device__ __forceinline__ void fwd_row_pass(u64* sm, int t, int tile, const ulonglong2* __restrict__ tw, u64 q) {
+template <int LOGN, class Tables>
+__device__ __forceinline__ void fwd_row_pass(u64* sm, int t, int tile, const Tables& T, int prime, u64 q) {
     using G = NttGeo<LOGN>;
     // at stage A a row index has weight 1 in the group number; local groups are numbered inside the tile
-    if (lazy_ok(q)) fwd_stages<G::LOGD, kLogTile, G::A, G::LOGD, true>(sm, t, tile, tw, q, q << 2);
-    else fwd_stages<G::LOGD, kLogTile, G::A, G::LOGD, false>(sm, t, tile, tw, q, q << 2);
+    if (fp_ok(q)) fwd_stages_fp<G::LOGD, kLogTile, G::A, G::LOGD>(reinterpret_cast<double*>(sm), t, tile, T.tw_fwd_d + (size_t)prime * T.N, u64_to_double_small(q));
+    else fwd_stages<G::LOGD, kLogTile, G::A, G::LOGD>(sm, t, tile, T.tw_fwd + (size_t)prime * T.N, q, q << 2);
 }
 
 // ---- inverse --------------------------------------------------------------------------------

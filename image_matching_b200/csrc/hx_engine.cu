@@ -167,11 +167,34 @@ u64* Engine::alloc_words(size_t words) {
 void Engine::free_words(u64* p) { cudaFreeAsync(p, st); }
 void Engine::sync() { HX_CUDA(cudaStreamSynchronize(st)); }
 
-Ct Engine::new_ct(int ncomp, int nl, int level, int deg) {
+Ct Engine::new_ct(int ncomp, int nl, int level, int deg, int nb) {
     auto c = std::make_shared<CtObj>();
-    c->eng = this; c->keep = weak_from_this().lock(); c->ncomp = ncomp; c->nl = nl; c->level = level; c->deg = deg;
-    c->d = alloc_words((size_t)ncomp * nl * N);
+    c->eng = this; c->keep = weak_from_this().lock(); c->ncomp = ncomp; c->nl = nl; c->level = level; c->deg = deg; c->nb = nb;
+    c->d = alloc_words((size_t)nb * ncomp * nl * N);
     return c;
+}
+Ct Engine::stack(const std::vector<Ct>& v) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (v.empty()) throw std::runtime_error("stack: empty input");
+    const Ct& f = v[0];
+    Ct out = new_ct(f->ncomp, f->nl, f->level, f->deg, (int)v.size());
+    for (size_t i = 0; i < v.size(); i++) {
+        if (v[i]->nb != 1 || v[i]->ncomp != f->ncomp || v[i]->nl != f->nl || v[i]->deg != f->deg)
+            throw std::runtime_error("stack: ciphertexts differ in shape");
+        HX_CUDA(cudaMemcpyAsync(out->d + i * out->batch_stride(), v[i]->d, sizeof(u64) * out->batch_stride(), cudaMemcpyDeviceToDevice, st));
+    }
+    return out;
+}
+std::vector<Ct> Engine::unstack(const Ct& a) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    std::vector<Ct> out;
+    if (a->nb == 1) { out.push_back(a); return out; }
+    for (int i = 0; i < a->nb; i++) {
+        Ct c = new_ct(a->ncomp, a->nl, a->level, a->deg);
+        HX_CUDA(cudaMemcpyAsync(c->d, a->d + (size_t)i * a->batch_stride(), sizeof(u64) * a->batch_stride(), cudaMemcpyDeviceToDevice, st));
+        out.push_back(c);
+    }
+    return out;
 }
 Ct Engine::upload(const u64* host, int ncomp, int nl, int level, int deg) {
     std::lock_guard<std::recursive_mutex> g(mu);
@@ -182,13 +205,13 @@ Ct Engine::upload(const u64* host, int ncomp, int nl, int level, int deg) {
 }
 void Engine::download(const Ct& ct, u64* host) {
     std::lock_guard<std::recursive_mutex> g(mu);
-    HX_CUDA(cudaMemcpyAsync(host, ct->d, sizeof(u64) * (size_t)ct->ncomp * ct->nl * N, cudaMemcpyDeviceToHost, st));
+    HX_CUDA(cudaMemcpyAsync(host, ct->d, sizeof(u64) * (size_t)ct->nb * ct->ncomp * ct->nl * N, cudaMemcpyDeviceToHost, st));
     sync();
 }
 Ct Engine::clone(const Ct& a) {
     std::lock_guard<std::recursive_mutex> g(mu);
-    Ct c = new_ct(a->ncomp, a->nl, a->level, a->deg);
-    HX_CUDA(cudaMemcpyAsync(c->d, a->d, sizeof(u64) * (size_t)a->ncomp * a->nl * N, cudaMemcpyDeviceToDevice, st));
+    Ct c = new_ct(a->ncomp, a->nl, a->level, a->deg, a->nb);
+    HX_CUDA(cudaMemcpyAsync(c->d, a->d, sizeof(u64) * (size_t)a->nb * a->ncomp * a->nl * N, cudaMemcpyDeviceToDevice, st));
     return c;
 }
 
@@ -362,25 +385,26 @@ const EvalKey& Engine::rot_key(u64 galois) const {
 // ------------------------------------------------------------------------------------------ key switching
 // EvalKeySwitchPrecomputeCore (upstream keyswitch-hybrid.cpp; sender_diag.cpp:22): digit split +
 // ModUp. Returns [ndig][nl+K][N]; every digit holds its own limbs verbatim and the converted ones.
-u64* Engine::ks_precompute(const u64* c, int nl, int* ndig_out) {
+u64* Engine::ks_precompute(const u64* c, int nl, int* ndig_out, int nbatch, size_t c_bs) {
     int ndig = std::min((nl + alpha - 1) / alpha, dnum);
     int ext = nl + K;
-    u64* digits = alloc_words((size_t)ndig * ext * N);
+    u64* digits = alloc_words((size_t)nbatch * ndig * ext * N);
     if (fused_ks_supported(logN) && !force_unfused) {
         ModUpArgs m;
-        m.c = c; m.c_bs = 0; m.nbatch = 1;
+        m.c = c; m.c_bs = c_bs; m.nbatch = nbatch;
         m.nl = nl; m.L = L; m.K = K; m.ndig = ndig; m.alpha = alpha;
         for (int j = 0; j < ndig; j++) m.tabs[j] = modup_table(nl, j);
-        m.scratch = alloc_words((size_t)nl * N);
+        m.scratch = alloc_words((size_t)nbatch * nl * N);
         m.digits = digits;
         {   // algorithmic bytes: input polynomial once, digits once
-            Scope sc(this, PK_MODUP, 2 + 2 * ndig, 8.0 * N * (nl + (double)ndig * ext));
+            Scope sc(this, PK_MODUP, 2 + 2 * ndig, 8.0 * N * nbatch * (nl + (double)ndig * ext));
             launch_fused_modup(T, m, st);
         }
         free_words(m.scratch);
         *ndig_out = ndig;
         return digits;
     }
+    if (nbatch != 1) throw std::runtime_error("batched key switching needs the fused pipeline");
     u64* scratch = alloc_words((size_t)alpha * N);
     for (int j = 0; j < ndig; j++) {
         int lo = j * alpha, hi = (j == ndig - 1) ? nl : (j + 1) * alpha, sz = hi - lo;
@@ -413,14 +437,15 @@ u64* Engine::ks_precompute(const u64* c, int nl, int* ndig_out) {
 // EvalFastKeySwitchCoreExt + ApproxModDown for a batch of keys sharing one set of digits, fused
 // with the "+ c0" and the Galois gather of EvalFastRotation (sender_diag.cpp:25).
 void Engine::ks_core_batch(const u64* digits, int ndig, int nl, const std::vector<const EvalKey*>& keys, const u64* addend,
-                           int addend_comps, const std::vector<u64>& galois, u64* out, size_t out_bs) {
+                           int addend_comps, const std::vector<u64>& galois, u64* out, size_t out_bs, size_t digits_bs, size_t addend_bs) {
     const int nb = (int)keys.size(), ext = nl + K;
     if (fused_ks_supported(logN) && !force_unfused) {
         // fused pipeline (hx_fused.cu): the evaluation keys are read once, nothing of size 2 x (l+K) is stored
         for (int b0 = 0; b0 < nb; b0 += kMaxKsBatch) {
             const int n = std::min(kMaxKsBatch, nb - b0);
             FusedKsArgs a;
-            a.digits = digits; a.ndig = ndig; a.nl = nl; a.L = L; a.K = K;
+            a.digits = digits + (size_t)b0 * digits_bs; a.ndig = ndig; a.nl = nl; a.L = L; a.K = K;
+            a.digits_bs = digits_bs; a.add_bs = addend_bs;
             for (int i = 0; i < n; i++) {
                 a.keyA[i] = keys[b0 + i]->a;
                 a.keyB[i] = keys[b0 + i]->b;
@@ -428,14 +453,15 @@ void Engine::ks_core_batch(const u64* digits, int ndig, int nl, const std::vecto
             }
             a.tmpP = alloc_words((size_t)n * 2 * K * N);
             a.conv = alloc_words((size_t)n * 2 * nl * N);
-            a.add0 = (addend && addend_comps >= 1) ? addend : nullptr;
-            a.add1 = (addend && addend_comps >= 2) ? addend + (size_t)nl * N : nullptr;
+            const u64* ad = addend ? addend + (size_t)b0 * addend_bs : nullptr;
+            a.add0 = (ad && addend_comps >= 1) ? ad : nullptr;
+            a.add1 = (ad && addend_comps >= 2) ? ad + (size_t)nl * N : nullptr;
             a.out = out + (size_t)b0 * out_bs;
             a.out_bs = out_bs;
             {   // algorithmic bytes of one key switch after ModUp: evk once, digits once per launch,
                 // addend once, result once
                 Scope sc(this, PK_KS_FUSED, 4,
-                         8.0 * N * ((double)n * 2 * ndig * ext + (double)ndig * ext + (double)addend_comps * nl + (double)n * 2 * nl));
+                         8.0 * N * ((double)n * 2 * ndig * ext + (double)(digits_bs ? n : 1) * ndig * ext + (double)(addend_bs ? n : 1) * addend_comps * nl + (double)n * 2 * nl));
                 launch_fused_ks(T, a, moddown_table(nl), n, st);
             }
             free_words(a.conv);
@@ -443,6 +469,7 @@ void Engine::ks_core_batch(const u64* digits, int ndig, int nl, const std::vecto
         }
         return;
     }
+    if (digits_bs || addend_bs) throw std::runtime_error("batched key switching needs the fused pipeline");
     std::vector<const u64*> ha(nb), hb(nb);
     std::vector<const u32*> hm(nb, nullptr);
     for (int i = 0; i < nb; i++) { ha[i] = keys[i]->a; hb[i] = keys[i]->b; }
@@ -503,7 +530,7 @@ Ct Engine::fast_rotation(const Ct& a, int r, const std::shared_ptr<Digits>& dg) 
 }
 Ct Engine::automorphism(const Ct& a, u64 k) {
     std::lock_guard<std::recursive_mutex> g(mu);
-    if (a->ncomp != 2) throw std::runtime_error("EvalAutomorphism needs a 2-component ciphertext");
+    if (a->ncomp != 2 || a->nb != 1) throw std::runtime_error("EvalAutomorphism needs a single 2-component ciphertext");
     int ndig;
     u64* dg = ks_precompute(a->comp(1), a->nl, &ndig);
     Ct out = new_ct(2, a->nl, a->level, a->deg);
@@ -533,9 +560,10 @@ Ct Engine::relinearize(const Ct& a) {
     if (a->ncomp != 3) throw std::runtime_error("Relinearize supports 3-component ciphertexts");
     if (!have_mult_key_) throw std::runtime_error("EvalMultKey is not generated");
     int ndig;
-    u64* dg = ks_precompute(a->comp(2), a->nl, &ndig);
-    Ct out = new_ct(2, a->nl, a->level, a->deg);
-    ks_core_batch(dg, ndig, a->nl, {&mult_key_}, a->d, 2, {}, out->d, 0);
+    u64* dg = ks_precompute(a->comp(2), a->nl, &ndig, a->nb, a->batch_stride());
+    Ct out = new_ct(2, a->nl, a->level, a->deg, a->nb);
+    std::vector<const EvalKey*> keys(a->nb, &mult_key_);
+    ks_core_batch(dg, ndig, a->nl, keys, a->d, 2, {}, out->d, out->batch_stride(), a->nb > 1 ? (size_t)ndig * (a->nl + K) * N : 0, a->nb > 1 ? a->batch_stride() : 0);
     free_words(dg);
     return out;
 }
@@ -546,9 +574,9 @@ Ct Engine::level_reduce(const Ct& a, int levels) {
     if (levels == 0) return a;
     if (levels < 0 || levels >= a->nl) throw std::runtime_error("LevelReduce: not enough limbs");
     int nl = a->nl - levels;
-    Ct out = new_ct(a->ncomp, nl, a->level + levels, a->deg);
-    for (int c = 0; c < a->ncomp; c++)
-        HX_CUDA(cudaMemcpyAsync(out->comp(c), a->comp(c), sizeof(u64) * (size_t)nl * N, cudaMemcpyDeviceToDevice, st));
+    Ct out = new_ct(a->ncomp, nl, a->level + levels, a->deg, a->nb);
+    HX_CUDA(cudaMemcpy2DAsync(out->d, sizeof(u64) * out->comp_stride(), a->d, sizeof(u64) * a->comp_stride(), sizeof(u64) * (size_t)nl * N,
+                              (size_t)a->comps_total(), cudaMemcpyDeviceToDevice, st));
     return out;
 }
 void Engine::align(Ct& a, Ct& b) {   // FIXEDMANUAL AdjustLevelsInPlace: drop limbs of the fresher operand
@@ -560,9 +588,12 @@ Ct Engine::add(const Ct& a_, const Ct& b_) {
     Ct a = a_, b = b_;
     align(a, b);
     if (a->deg != b->deg) throw std::runtime_error("EvalAdd: noiseScaleDeg mismatch");
+    if (a->nb != b->nb) throw std::runtime_error("EvalAdd: batch size mismatch");
     if (a->ncomp < b->ncomp) std::swap(a, b);
-    Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg);
-    { Scope sc(this, PK_EW, 1, 24.0 * N * a->nl * b->ncomp); launch_ew(T, EW_ADD, out->d, a->d, b->d, a->nl, b->ncomp, out->comp_stride(), a->comp_stride(), b->comp_stride(), st); }
+    if (a->nb > 1 && a->ncomp != b->ncomp) throw std::runtime_error("EvalAdd: batched operands must have equal component counts");
+    Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg, a->nb);
+    const int nc = a->nb > 1 ? a->comps_total() : b->ncomp;
+    { Scope sc(this, PK_EW, 1, 24.0 * N * a->nl * nc); launch_ew(T, EW_ADD, out->d, a->d, b->d, a->nl, nc, out->comp_stride(), a->comp_stride(), b->comp_stride(), st); }
     for (int c = b->ncomp; c < a->ncomp; c++)
         HX_CUDA(cudaMemcpyAsync(out->comp(c), a->comp(c), sizeof(u64) * a->comp_stride(), cudaMemcpyDeviceToDevice, st));
     return out;
@@ -572,9 +603,9 @@ Ct Engine::sub(const Ct& a_, const Ct& b_) {
     Ct a = a_, b = b_;
     align(a, b);
     if (a->deg != b->deg) throw std::runtime_error("EvalSub: noiseScaleDeg mismatch");
-    if (a->ncomp != b->ncomp) throw std::runtime_error("EvalSub: component count mismatch");
-    Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg);
-    { Scope sc(this, PK_EW, 1, 24.0 * N * a->nl * a->ncomp); launch_ew(T, EW_SUB, out->d, a->d, b->d, a->nl, a->ncomp, out->comp_stride(), a->comp_stride(), b->comp_stride(), st); }
+    if (a->ncomp != b->ncomp || a->nb != b->nb) throw std::runtime_error("EvalSub: component or batch count mismatch");
+    Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg, a->nb);
+    { Scope sc(this, PK_EW, 1, 24.0 * N * a->nl * a->comps_total()); launch_ew(T, EW_SUB, out->d, a->d, b->d, a->nl, a->comps_total(), out->comp_stride(), a->comp_stride(), b->comp_stride(), st); }
     return out;
 }
 Ct Engine::add_many(const std::vector<Ct>& v_) {
@@ -612,8 +643,8 @@ std::vector<u64> Engine::const_for_add(double c, int nl, int deg) const {
 }
 Ct Engine::mult_const(const Ct& a, double c) {
     std::lock_guard<std::recursive_mutex> g(mu);
-    Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg + 1);
-    { Scope sc(this, PK_SCALAR, 1, 16.0 * N * a->nl * a->ncomp); launch_mul_scalar(T, out->d, a->d, scalar_table(const_for_mult(c, a->nl)), a->nl, a->ncomp, out->comp_stride(), a->comp_stride(), st); }
+    Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg + 1, a->nb);
+    { Scope sc(this, PK_SCALAR, 1, 16.0 * N * a->nl * a->comps_total()); launch_mul_scalar(T, out->d, a->d, scalar_table(const_for_mult(c, a->nl)), a->nl, a->comps_total(), out->comp_stride(), a->comp_stride(), st); }
     return out;
 }
 Ct Engine::add_const(const Ct& a, double c) {
@@ -622,10 +653,11 @@ Ct Engine::add_const(const Ct& a, double c) {
     std::vector<u64> k = const_for_add(std::fabs(c), a->nl, a->deg);
     if (c < 0)
         for (int i = 0; i < a->nl; i++) k[i] = (mods[i] - k[i]) % mods[i];
-    Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg);
-    { Scope sc(this, PK_SCALAR, 1, 16.0 * N * a->nl); launch_add_scalar(T, out->d, a->d, scalar_table(k), a->nl, st); }
-    for (int cidx = 1; cidx < a->ncomp; cidx++)
-        HX_CUDA(cudaMemcpyAsync(out->comp(cidx), a->comp(cidx), sizeof(u64) * a->comp_stride(), cudaMemcpyDeviceToDevice, st));
+    Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg, a->nb);
+    { Scope sc(this, PK_SCALAR, 1, 16.0 * N * a->nl * a->nb); launch_add_scalar(T, out->d, a->d, scalar_table(k), a->nl, a->nb, a->batch_stride(), st); }
+    if (a->ncomp > 1)   // components 1.. of every batch entry are copied unchanged
+        HX_CUDA(cudaMemcpy2DAsync(out->comp(1), sizeof(u64) * a->batch_stride(), a->comp(1), sizeof(u64) * a->batch_stride(),
+                                  sizeof(u64) * (size_t)(a->ncomp - 1) * a->comp_stride(), (size_t)a->nb, cudaMemcpyDeviceToDevice, st));
     return out;
 }
 Ct Engine::mult_norelin(const Ct& a_, const Ct& b_) {
@@ -633,8 +665,9 @@ Ct Engine::mult_norelin(const Ct& a_, const Ct& b_) {
     Ct a = a_, b = b_;
     align(a, b);
     if (a->ncomp != 2 || b->ncomp != 2) throw std::runtime_error("EvalMultNoRelin supports 2-component inputs");
-    Ct out = new_ct(3, a->nl, a->level, a->deg + b->deg);
-    { Scope sc(this, PK_TENSOR, 1, 8.0 * N * a->nl * 7); launch_tensor(T, out->d, a->d, a->comp_stride(), b->d, b->comp_stride(), a->nl, st); }
+    if (a->nb != b->nb) throw std::runtime_error("EvalMultNoRelin: batch size mismatch");
+    Ct out = new_ct(3, a->nl, a->level, a->deg + b->deg, a->nb);
+    { Scope sc(this, PK_TENSOR, 1, 8.0 * N * a->nl * 7 * a->nb); launch_tensor(T, out->d, a->d, a->comp_stride(), b->d, b->comp_stride(), a->nl, a->nb, st); }
     return out;
 }
 Ct Engine::mult(const Ct& a, const Ct& b) { return relinearize(mult_norelin(a, b)); }
@@ -645,7 +678,7 @@ Ct Engine::rescale(const Ct& a) {
     std::lock_guard<std::recursive_mutex> g(mu);
     int nl = a->nl;
     if (nl < 2) throw std::runtime_error("Rescale: no limb left to drop");
-    int nc = a->ncomp;
+    int nc = a->comps_total();   // batch entries are independent components for DropLastElementAndScale
     u64 ql = mods[nl - 1];
     std::vector<u64> qlinv(nl - 1), neg(nl - 1);
     for (int i = 0; i < nl - 1; i++) {
@@ -658,7 +691,7 @@ Ct Engine::rescale(const Ct& a) {
         r.last_tab = last_limb_table(nl - 1);
         r.last = alloc_words((size_t)nc * N);
         r.tmp = alloc_words((size_t)nc * (nl - 1) * N);
-        Ct out = new_ct(nc, nl - 1, a->level + 1, a->deg - 1);
+        Ct out = new_ct(a->ncomp, nl - 1, a->level + 1, a->deg - 1, a->nb);
         r.out = out->d; r.out_bs = out->comp_stride();
         r.negqlinv = scalar_table(neg);
         r.qlinv = scalar_table(qlinv);
@@ -670,6 +703,7 @@ Ct Engine::rescale(const Ct& a) {
         free_words(r.last);
         return out;
     }
+    if (a->nb != 1) throw std::runtime_error("batched rescale needs the fused pipeline");
     u64* last = alloc_words((size_t)nc * N);
     for (int c = 0; c < nc; c++)
         HX_CUDA(cudaMemcpyAsync(last + (size_t)c * N, a->comp(c) + (size_t)(nl - 1) * N, sizeof(u64) * N, cudaMemcpyDeviceToDevice, st));

@@ -33,16 +33,23 @@ enum ProfKind {
 const char* prof_kind_name(int kind);
 
 // Ciphertext<DCRTPoly>: ncomp components x nl limbs x N, EVALUATION form, device resident.
+// nb > 1: a BATCH of nb ciphertexts of identical shape/level/degree, contiguous [nb][ncomp][nl][N].  Every
+// leveled op treats the batch entries independently with the same constants and keys in ONE launch per
+// kernel; the HyDia path uses it to run the compare chain of all database blocks of a GPU together
+// (the reference does the same chain per block in an OpenMP loop, sender_diag.cpp:40-43).
 struct CtObj {
     Engine* eng = nullptr;
     std::shared_ptr<Engine> keep;   // a handle outliving hx_ctx_destroy keeps its engine alive
     u64* d = nullptr;
     int ncomp = 0, nl = 0;
+    int nb = 1;         // batch entries
     int level = 0;      // GetLevel(): limbs dropped
     int deg = 1;        // GetNoiseScaleDeg()
     ~CtObj();
     u64* comp(int c) const;
     size_t comp_stride() const;
+    size_t batch_stride() const { return (size_t)ncomp * comp_stride(); }
+    int comps_total() const { return nb * ncomp; }
 };
 using Ct = std::shared_ptr<CtObj>;
 
@@ -63,6 +70,7 @@ public:
     std::recursive_mutex mu;         // the reference enters from up to 48 OpenMP threads
     int rot_chunk = 32;              // hoisted rotations per fused key-switch batch (intermediates stay L2 resident)
     bool force_unfused = false;      // tests: run the unfused reference kernels instead of hx_fused.cu
+    bool batch_blocks = true;        // HyDia path: relinearise/rescale/compare all blocks as one batch
     unsigned long long launches = 0; // kernels launched (bench "gpu_launches")
 
     // ---- launch accounting + optional CUDA-event profiler (events on `st`, the launching stream)
@@ -89,7 +97,9 @@ public:
     // ---- memory
     u64* alloc_words(size_t words);
     void free_words(u64* p);
-    Ct new_ct(int ncomp, int nl, int level, int deg);
+    Ct new_ct(int ncomp, int nl, int level, int deg, int nb = 1);
+    Ct stack(const std::vector<Ct>& v);            // nb = v.size() batch from single ciphertexts (copies)
+    std::vector<Ct> unstack(const Ct& a);          // batch -> single ciphertexts (copies)
     Ct upload(const u64* host, int ncomp, int nl, int level, int deg);
     void download(const Ct& ct, u64* host);
     Ct clone(const Ct& ct);
@@ -138,15 +148,18 @@ public:
     void db_store_device(int block, int diag, const u64* dev_ct /*[2][L][N], plain residues, device*/);
     int db_blocks() const { return (int)db_.size(); }
     std::vector<Ct> score_diag(const Ct& query, int ndiag);            // computeSimilarity
+    std::vector<Ct> score_diag_batched(const Ct& query, int ndiag);    // same, blocks kept as batches of <= 32
     Ct membership(const Ct& query, int ndiag, double delta, int depth); // membershipScenario
     std::vector<Ct> index(const Ct& query, int ndiag, double delta, int depth);   // indexScenario
 
     // ---- building blocks exposed for parity tests
     void ntt_limbs(u64* data, int nbatch, const std::vector<int>& primes, bool inverse);
-    u64* ks_precompute(const u64* c, int nl, int* ndig_out);               // digits [ndig][nl+K][N]
+    // digits [nbatch][ndig][nl+K][N]; input polynomials c + b*c_bs
+    u64* ks_precompute(const u64* c, int nl, int* ndig_out, int nbatch = 1, size_t c_bs = 0);
     // key-switch core on precomputed digits for `nbatch` keys: out[b] = [2][nl][N] (+ optional addend/maps)
     void ks_core_batch(const u64* digits, int ndig, int nl, const std::vector<const EvalKey*>& keys, const u64* addend, int addend_comps,
-                       const std::vector<u64>& galois /*empty = no permutation*/, u64* out, size_t out_bs);
+                       const std::vector<u64>& galois /*empty = no permutation*/, u64* out, size_t out_bs,
+                       size_t digits_bs = 0 /*0: all entries share the digits*/, size_t addend_bs = 0);
     const EvalKey& rot_key(u64 galois) const;
     const u32* automap(u64 galois);
     LimbMap limb_map(const std::vector<int>& primes) const;

@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_p_inner(const __gr
     const int prime = a.L + k, dl = a.nl + k, ext = a.nl + a.K;
     const PrimeConst pc = T.pc[prime];
     const u64* key = (comp == 0 ? a.keyB[b] : a.keyA[b]) + (size_t)prime * T.N + (size_t)tile * kTileN;
-    const u64* dig = a.digits + (size_t)dl * T.N + (size_t)tile * kTileN;
+    const u64* dig = a.digits + (size_t)b * a.digits_bs + (size_t)dl * T.N + (size_t)tile * kTileN;
     const size_t kstride = (size_t)(a.L + a.K) * T.N, dstride = (size_t)ext * T.N;
 #pragma unroll
     for (int u = 0; u < 4; u++) {
@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __g
     const size_t toff = (size_t)tile * kTileN;
     const u64* cv = a.conv + (((size_t)b * 2 + comp) * a.nl + i) * T.N + toff;
     const u64* key = (comp == 0 ? a.keyB[b] : a.keyA[b]) + (size_t)i * T.N + toff;
-    const u64* dig = a.digits + (size_t)i * T.N + toff;
+    const u64* dig = a.digits + (size_t)b * a.digits_bs + (size_t)i * T.N + toff;
     const size_t kstride = (size_t)(a.L + a.K) * T.N, dstride = (size_t)(a.nl + a.K) * T.N;
     u64 ip[8];
 #pragma unroll
@@ -171,7 +171,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __g
     __syncthreads();
     fwd_row_pass<LOGN>(sm, t, tile, T, i, q);
     const u64* add = (comp == 0 ? a.add0 : a.add1);
-    if (add) add += (size_t)i * T.N + toff;
+    if (add) add += (size_t)b * a.add_bs + (size_t)i * T.N + toff;
     // P^-1 is folded into the evaluation keys' Q limbs and into the ModDown conversion matrix at load time
 #pragma unroll
     for (int u = 0; u < 4; u++) {

@@ -50,7 +50,7 @@ void Engine::db_adopt(int block, u64* dev, int ndiag) {
 // computeSimilarity (sender_diag.cpp:12-33): hoisted rotations 1..ndiag-1 of the query
 // (EvalFastRotationPrecompute + EvalFastRotation), then per block the 512 tensor products, their
 // sum, one relinearisation and one rescale (computeSimilarityMatrix, :66-83).
-std::vector<Ct> Engine::score_diag(const Ct& query, int ndiag) {
+std::vector<Ct> Engine::score_diag_batched(const Ct& query, int ndiag) {
     std::lock_guard<std::recursive_mutex> g(mu);
     if (query->ncomp != 2 || query->nl != L) throw std::runtime_error("score_diag: query must be a fresh 2-component ciphertext");
     if (db_.empty()) throw std::runtime_error("score_diag: no database block registered");
@@ -73,25 +73,42 @@ std::vector<Ct> Engine::score_diag(const Ct& query, int ndiag) {
         ks_core_batch(digits, ndig, nl, keys, query->comp(0), 1, gal, rotq + ct_words * d0, ct_words);
     }
     free_words(digits);
-    std::vector<Ct> scores;
+    // all blocks of this GPU in one launch each: diagonal MAC (the rotated query is fetched from HBM once
+    // for all of them), relinearisation and rescale on the batch [G][3][nl][N]
+    std::vector<const u64*> blocks;
     for (auto& kv : db_) {
         if (kv.second.ndiag < ndiag) throw std::runtime_error("score_diag: database block has fewer diagonals than requested");
-        Ct acc = new_ct(3, nl, query->level, query->deg + 1);
-        {   // algorithmic bytes: the database block, read once; rotq is re-read per block
-            Scope sc(this, PK_DIAG_MAC, 1, 8.0 * N * nl * 2 * ndiag);
-            launch_diag_mac(T, rotq, kv.second.d, acc->d, ndiag, nl, st);
+        blocks.push_back(kv.second.d);
+    }
+    std::vector<Ct> parts;
+    const int group = (batch_blocks && !force_unfused && fused_ks_supported(logN)) ? std::min(kMaxKsBatch, kMaxDbBlocks) : 1;
+    for (size_t g0 = 0; g0 < blocks.size(); g0 += group) {
+        const int g = (int)std::min((size_t)group, blocks.size() - g0);
+        DbBlockPtrs ptrs;
+        for (int i = 0; i < g; i++) ptrs.p[i] = blocks[g0 + i];
+        Ct acc = new_ct(3, nl, query->level, query->deg + 1, g);
+        {   // algorithmic bytes: the database blocks, read once; rotq is shared by the launch
+            Scope sc(this, PK_DIAG_MAC, 1, 8.0 * N * nl * 2 * ndiag * g);
+            launch_diag_mac(T, rotq, ptrs, g, acc->d, ndiag, nl, st);
         }
-        scores.push_back(rescale(relinearize(acc)));
+        parts.push_back(rescale(relinearize(acc)));
     }
     free_words(rotq);
-    return scores;
+    return parts;
+}
+std::vector<Ct> Engine::score_diag(const Ct& query, int ndiag) {
+    std::vector<Ct> out;
+    for (auto& p : score_diag_batched(query, ndiag))
+        for (auto& c : unstack(p)) out.push_back(c);
+    return out;
 }
 
-// indexScenario (sender_diag.cpp:52-63).
+// indexScenario (sender_diag.cpp:52-63): the compare chain runs once per batch of blocks.
 std::vector<Ct> Engine::index(const Ct& query, int ndiag, double delta, int depth) {
-    std::vector<Ct> s = score_diag(query, ndiag);
-    for (auto& c : s) c = chebyshev_compare(c, delta, depth);
-    return s;
+    std::vector<Ct> out;
+    for (auto& p : score_diag_batched(query, ndiag))
+        for (auto& c : unstack(chebyshev_compare(p, delta, depth))) out.push_back(c);
+    return out;
 }
 // membershipScenario (sender_diag.cpp:35-50).
 Ct Engine::membership(const Ct& query, int ndiag, double delta, int depth) {

@@ -182,20 +182,20 @@ void launch_mul_scalar(const DevTables& T, u64* out, const u64* a, const ScalarT
     k_mul_scalar<<<grid, kThreads, 0, st>>>(T, out, a, s, cs_out, cs_a);
 }
 
-__global__ void __launch_bounds__(kThreads) k_add_scalar(DevTables T, u64* __restrict__ out, const u64* __restrict__ a, ScalarTable s) {
+__global__ void __launch_bounds__(kThreads) k_add_scalar(DevTables T, u64* __restrict__ out, const u64* __restrict__ a, ScalarTable s, size_t bs) {
     int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (idx >= T.N) return;
     int i = blockIdx.y;
     const u64 q = T.pc[i].q;
-    size_t off = (size_t)i * T.N + idx;
+    size_t off = (size_t)blockIdx.z * bs + (size_t)i * T.N + idx;
     ulonglong2 x = *reinterpret_cast<const ulonglong2*>(a + off);
     x.x = add_mod(x.x, s.v[i], q);
     x.y = add_mod(x.y, s.v[i], q);
     st128(out + off, x);
 }
-void launch_add_scalar(const DevTables& T, u64* out, const u64* a, const ScalarTable& s, int nl, cudaStream_t st) {
-    dim3 grid(blocks_for(T.N), nl, 1);
-    k_add_scalar<<<grid, kThreads, 0, st>>>(T, out, a, s);
+void launch_add_scalar(const DevTables& T, u64* out, const u64* a, const ScalarTable& s, int nl, int nbatch, size_t batch_stride, cudaStream_t st) {
+    dim3 grid(blocks_for(T.N), nl, nbatch);
+    k_add_scalar<<<grid, kThreads, 0, st>>>(T, out, a, s, batch_stride);
 }
 
 // EvalMultCore (row P6, single product): out = (a0*b0, a0*b1 + a1*b0, a1*b1).
@@ -206,6 +206,7 @@ __global__ void __launch_bounds__(kThreads) k_tensor(DevTables T, u64* __restric
     int i = blockIdx.y;
     const PrimeConst pc = T.pc[i];
     size_t off = (size_t)i * T.N + idx;
+    a += (size_t)blockIdx.z * 2 * cs_a; b += (size_t)blockIdx.z * 2 * cs_b; out += (size_t)blockIdx.z * 3 * nl * T.N;   // batch entries are contiguous ciphertexts
     ulonglong2 a0 = *reinterpret_cast<const ulonglong2*>(a + off);
     ulonglong2 a1 = *reinterpret_cast<const ulonglong2*>(a + cs_a + off);
     ulonglong2 b0 = *reinterpret_cast<const ulonglong2*>(b + off);
@@ -220,8 +221,8 @@ __global__ void __launch_bounds__(kThreads) k_tensor(DevTables T, u64* __restric
     r.x = mulmod(a1.x, b1.x, pc); r.y = mulmod(a1.y, b1.y, pc);
     st128(out + 2 * cs_o + off, r);
 }
-void launch_tensor(const DevTables& T, u64* out, const u64* a, size_t cs_a, const u64* b, size_t cs_b, int nl, cudaStream_t st) {
-    dim3 grid(blocks_for(T.N), nl, 1);
+void launch_tensor(const DevTables& T, u64* out, const u64* a, size_t cs_a, const u64* b, size_t cs_b, int nl, int nbatch, cudaStream_t st) {
+    dim3 grid(blocks_for(T.N), nl, nbatch);
     k_tensor<<<grid, kThreads, 0, st>>>(T, out, a, cs_a, b, cs_b, nl);
 }
 
@@ -320,11 +321,13 @@ void launch_rescale_finish(const DevTables& T, u64* out, size_t out_bs, const u6
 // Montgomery form; products are accumulated un-reduced in 128 bits and folded every kFold diagonals
 // (2*kFold*q^2 < 2^128 for q < 2^60), so the kernel does 4 wide MACs per 32 bytes streamed.
 constexpr int kFold = 64;
-__global__ void __launch_bounds__(kThreads) k_diag_mac(DevTables T, const u64* __restrict__ rotq, const u64* __restrict__ db,
+__global__ void __launch_bounds__(kThreads) k_diag_mac(DevTables T, const u64* __restrict__ rotq, const __grid_constant__ DbBlockPtrs dbs,
                                                        u64* __restrict__ out, int ndiag, int nl) {
-    int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    int idx = (blockIdx.y * blockDim.x + threadIdx.x) * 2;
     if (idx >= T.N) return;
-    int i = blockIdx.y;
+    int i = blockIdx.z;
+    const u64* __restrict__ db = dbs.p[blockIdx.x];
+    out += (size_t)blockIdx.x * 3 * nl * T.N;
     const PrimeConst pc = T.pc[i];
     const size_t cs = (size_t)nl * T.N, ds = 2 * cs;
     size_t off = (size_t)i * T.N + idx;
@@ -354,9 +357,9 @@ __global__ void __launch_bounds__(kThreads) k_diag_mac(DevTables T, const u64* _
         st128(out + (size_t)c * cs + off, o);
     }
 }
-void launch_diag_mac(const DevTables& T, const u64* rotq, const u64* db, u64* out, int ndiag, int nl, cudaStream_t st) {
-    dim3 grid(blocks_for(T.N), nl, 1);
-    k_diag_mac<<<grid, kThreads, 0, st>>>(T, rotq, db, out, ndiag, nl);
+void launch_diag_mac(const DevTables& T, const u64* rotq, const DbBlockPtrs& dbs, int nblocks, u64* out, int ndiag, int nl, cudaStream_t st) {
+    dim3 grid(nblocks, blocks_for(T.N), nl);
+    k_diag_mac<<<grid, kThreads, 0, st>>>(T, rotq, dbs, out, ndiag, nl);
 }
 
 }  // namespace hx

@@ -65,6 +65,8 @@ struct FusedKsArgs {
     u64* conv;                      // scratch [nb][2][nl][N]
     const u64* add0;                // optional addend of component 0 / 1, [nl][N]
     const u64* add1;
+    size_t digits_bs = 0;           // words between the digit sets of consecutive batch entries (0 = shared: hoisted rotations)
+    size_t add_bs = 0;              // words between the addends of consecutive batch entries (0 = shared)
     u64* out;                       // [nb] x out_bs, each [2][nl][N]
     size_t out_bs;
 };
@@ -96,9 +98,11 @@ enum EwOp { EW_ADD = 0, EW_SUB = 1, EW_MUL = 2 };
 void launch_ew(const DevTables& T, EwOp op, u64* out, const u64* a, const u64* b, int nl, int ncomp, size_t comp_stride_out,
                size_t comp_stride_a, size_t comp_stride_b, cudaStream_t st);
 void launch_mul_scalar(const DevTables& T, u64* out, const u64* a, const ScalarTable& s, int nl, int ncomp, size_t cs_out, size_t cs_a, cudaStream_t st);
-void launch_add_scalar(const DevTables& T, u64* out, const u64* a, const ScalarTable& s, int nl, cudaStream_t st);
+// adds s to component 0 of `nbatch` ciphertexts lying batch_stride words apart
+void launch_add_scalar(const DevTables& T, u64* out, const u64* a, const ScalarTable& s, int nl, int nbatch, size_t batch_stride, cudaStream_t st);
 // EvalMultCore: (a0*b0, a0*b1+a1*b0, a1*b1); a,b: [2][.][N] with component strides; out [3][nl][N]
-void launch_tensor(const DevTables& T, u64* out, const u64* a, size_t cs_a, const u64* b, size_t cs_b, int nl, cudaStream_t st);
+// batch entry z: a + z*2*cs_a, b + z*2*cs_b (contiguous 2-component ciphertexts), out + z*3*nl*N
+void launch_tensor(const DevTables& T, u64* out, const u64* a, size_t cs_a, const u64* b, size_t cs_b, int nl, int nbatch, cudaStream_t st);
 void launch_automorph(const DevTables& T, u64* out, const u64* in, const u32* map, int nlimbs_total, cudaStream_t st);
 void launch_automap(int N, int logN, u64 k, u32* map, cudaStream_t st);
 void launch_to_mont(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, cudaStream_t st);
@@ -112,7 +116,11 @@ void launch_rescale_finish(const DevTables& T, u64* out, size_t out_bs, const u6
                            int nl, const ScalarTable& qlinv, int nbatch, cudaStream_t st);
 
 // ---- fused diagonal multiply-accumulate (row P6)
-// rotq: [ndiag][2][nl][N]; db (Montgomery form): [ndiag][2][nl][N]; out: [3][nl][N] (overwritten)
-void launch_diag_mac(const DevTables& T, const u64* rotq, const u64* db, u64* out, int ndiag, int nl, cudaStream_t st);
+// rotq: [ndiag][2][nl][N]; dbs.p[g] (Montgomery form): [ndiag][2][nl][N]; out: [nblocks][3][nl][N] (overwritten).
+// All blocks of one launch share the rotated query: the block index is the fastest grid dimension, so the
+// CTAs reading the same rotq tile are co-resident and every rotq line is fetched from HBM once per launch.
+constexpr int kMaxDbBlocks = 64;
+struct DbBlockPtrs { const u64* p[kMaxDbBlocks]; };
+void launch_diag_mac(const DevTables& T, const u64* rotq, const DbBlockPtrs& dbs, int nblocks, u64* out, int ndiag, int nl, cudaStream_t st);
 
 }  // namespace hx

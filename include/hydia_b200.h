@@ -42,7 +42,9 @@ void hx_ctx_destroy(hx_ctx* ctx);
 int hx_ctx_sync(hx_ctx* ctx);                       /* wait for all queued device work */
 uint64_t hx_ctx_launches(hx_ctx* ctx);              /* kernels launched so far (bench accounting) */
 /* Engine tuning / test switches: "rot_chunk" (hoisted rotations per key-switch batch),
- * "force_unfused" (1 = run the unfused reference kernels instead of the fused key-switch pipeline). */
+ * "force_unfused" (1 = run the unfused reference kernels instead of the fused key-switch pipeline),
+ * "batch_blocks" (default 1: the fused HyDia entries relinearise / rescale / compare all database blocks of
+ * this GPU as one batch; 0 = one chain per block). */
 int hx_ctx_set_option(hx_ctx* ctx, const char* name, int value);
 /* Launch accounting and the optional CUDA-event profiler (events on the engine's launching stream).
  * The reference has only wall-clock phase timers (src/main.cpp:342-347); these feed bench.py's

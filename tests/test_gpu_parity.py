@@ -157,6 +157,10 @@ def test_hydia_fused_path_bit_exact_small_ring(golden_dir):
     assert all(same(g, w) for g, w in zip(gidx, widx))
     wm = orc.eval_sum(orc.add_many(widx), orc.P.slots)
     assert same(cc.membership(gq), wm)
+    # the two blocks above went through ONE batched relinearise / rescale / compare chain; per-block chain must agree
+    cc.set_option("batch_blocks", 0)
+    assert all(same(g, w) for g, w in zip(cc.index(gq), widx))
+    cc.set_option("batch_blocks", 1)
     # decisions (receiver_hers.cpp:26-54) and score accuracy (main_accuracy.cpp:360)
     assert O.decrypt_index(orc, widx) == [0, n - 1] and O.decrypt_membership(orc, wm)
     cos = O.plaintext_normalize(db) @ O.plaintext_normalize(q)

@@ -24,7 +24,7 @@ Engine::Engine(int N_, int L_, int K_, int dnum_, const u64* q, const u64* p, co
     if ((1 << logN) != N || N < 1024 || N > 65536) throw std::runtime_error("ring dimension must be a power of two in [2^10, 2^16]");
     if (L + K > kMaxPrimes) throw std::runtime_error("too many RNS limbs");
     alpha = (L + dnum - 1) / dnum;
-    if (alpha > 8) throw std::runtime_error("digit width > 8 limbs unsupported");
+    if (alpha > 7 || K > 7) throw std::runtime_error("digit width or P basis above 7 limbs unsupported (carry-free MAC bound)");
     if (dnum < 1 || dnum > kMaxDigits) throw std::runtime_error("number of key-switching digits must be 1..4");
     for (int i = 0; i < L; i++) { mods.push_back(q[i]); psis.push_back(psi_q[i]); }
     for (int i = 0; i < K; i++) { mods.push_back(p[i]); psis.push_back(psi_p[i]); }
@@ -287,6 +287,7 @@ BaseConvTable* Engine::make_table(const std::vector<int>& src, const std::vector
             u64 r1 = (u64)((((u128)1) << 64) % pj);
             if (out_scale) hm = mulmod(hm, (*out_scale)[j] % pj, pj);
             h.mat[i * h.n_out + j] = mulmod(hm, r1, pj);   // Montgomery form
+            h.mat30[i * h.n_out + j] = split30(h.mat[i * h.n_out + j]);
         }
     }
     for (int j = 0; j < h.n_out; j++) h.dst[j] = (short)dst[j];
@@ -346,11 +347,13 @@ void Engine::finish_key(EvalKey& k) {
     for (int i = 0; i < L; i++) pinv[i] = invmod(P_mod(i), mods[i]);
     ScalarTable ps = scalar_table(pinv);
     const size_t ds = (size_t)(L + K) * N;
-    Scope sc(this, PK_MISC, 4, 64.0 * dnum * (L + K) * N);
+    Scope sc(this, PK_MISC, 6, 96.0 * dnum * (L + K) * N);
     launch_to_mont(T, k.a, dnum * (L + K), lm, st);
     launch_to_mont(T, k.b, dnum * (L + K), lm, st);
     launch_mul_scalar(T, k.a, k.a, ps, L, dnum, ds, ds, st);
     launch_mul_scalar(T, k.b, k.b, ps, L, dnum, ds, ds, st);
+    launch_split30(k.a, (size_t)dnum * ds, st);   // 30-bit halves for the carry-free inner product
+    launch_split30(k.b, (size_t)dnum * ds, st);
 }
 void Engine::load_mult_key(const u64* a, const u64* b) {
     std::lock_guard<std::recursive_mutex> g(mu);

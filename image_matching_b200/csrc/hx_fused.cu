@@ -22,6 +22,10 @@
 #endif
 namespace hx {
 
+constexpr unsigned kTileBytes = kTileN * sizeof(u64);                                   // 16 KB
+constexpr unsigned kStageOff = (kTileWords * sizeof(u64) + 127u) & ~127u;              // staged key tiles start here
+constexpr unsigned ks_smem_bytes(int ndig) { return kStageOff + ndig * kTileBytes + 16; }
+
 // PrecomputeAutoMap on the fly: position J (bit-reversed order) of the output reads position
 // brev(((2*brev(J)+1)*g mod 2N) >> 1) of the input.
 template <int LOGN>
@@ -35,7 +39,10 @@ __device__ __forceinline__ u32 automap_at(u32 J, u32 g) {
 // K1: grid (TILES, 2*K, nb).  out: tmpP[b][comp][k][N], values in [0,4q), inverse row pass done.
 template <int LOGN, int NDIG>
 __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_p_inner(const __grid_constant__ DevTables T, const __grid_constant__ FusedKsArgs a) {
-    __shared__ u64 sm[kTileWords];
+    extern __shared__ __align__(128) unsigned char smraw[];
+    u64* sm = reinterpret_cast<u64*>(smraw);
+    u64* kst = reinterpret_cast<u64*>(smraw + kStageOff);
+    u64* mbar = reinterpret_cast<u64*>(smraw + kStageOff + NDIG * kTileBytes);
     const int t = threadIdx.x, tile = blockIdx.x;
     const int k = blockIdx.y >> 1, comp = blockIdx.y & 1, b = blockIdx.z;
     const int prime = a.L + k, dl = a.nl + k, ext = a.nl + a.K;
@@ -43,19 +50,27 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_p_inner(const __gr
     const u64* key = (comp == 0 ? a.keyB[b] : a.keyA[b]) + (size_t)prime * T.N + (size_t)tile * kTileN;
     const u64* dig = a.digits + (size_t)b * a.digits_bs + (size_t)dl * T.N + (size_t)tile * kTileN;
     const size_t kstride = (size_t)(a.L + a.K) * T.N, dstride = (size_t)ext * T.N;
+    if (t == 0) {   // key tiles by TMA bulk copy (see k_ks_q_finish)
+        mbar_init(mbar, 1);
+        mbar_expect_tx(mbar, NDIG * kTileBytes);
+#pragma unroll
+        for (int j = 0; j < NDIG; j++) bulk_g2s(kst + j * kTileN, key + j * kstride, kTileBytes, mbar);
+    }
+    __syncthreads();
+    mbar_wait(mbar, 0);
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
-        u128d a0 = {0, 0}, a1 = {0, 0};
+        acc3 a0 = {0, 0, 0}, a1 = {0, 0, 0};
 #pragma unroll
         for (int j = 0; j < NDIG; j++) {
             const ulonglong2 d = ldg128(dig + j * dstride + e);
-            const ulonglong2 kv = ld_stream128(key + j * kstride + e);
-            acc_wide(a0, d.x, kv.x);
-            acc_wide(a1, d.y, kv.y);
+            const ulonglong2 kv = *reinterpret_cast<const ulonglong2*>(kst + j * kTileN + e);
+            mac30(a0, d.x, kv.x);
+            mac30(a1, d.y, kv.y);
         }
-        sm[tphys(e)] = redc(a0, pc.q, pc.qinv_neg);
-        sm[tphys(e + 1)] = redc(a1, pc.q, pc.qinv_neg);
+        sm[tphys(e)] = redc(fold30(a0), pc.q, pc.qinv_neg);
+        sm[tphys(e + 1)] = redc(fold30(a1), pc.q, pc.qinv_neg);
     }
     __syncthreads();
     inv_row_pass<LOGN>(sm, t, tile, T.tw_inv + (size_t)prime * T.N, pc.q);
@@ -107,17 +122,17 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
     const int prime = tab->dst[j];
     const PrimeConst pc = T.pc[prime];
     const u64* src = in + (size_t)blockIdx.z * in_bs;
-    u128d acc[8];
+    acc3 acc[8];
 #pragma unroll
-    for (int u = 0; u < 8; u++) acc[u] = {0, 0};
-    for (int k = 0; k < n_in; k++) {
-        const u64 m = tab->mat[k * n_out + j];
+    for (int u = 0; u < 8; u++) acc[u] = {0, 0, 0};
+    for (int k = 0; k < n_in; k++) {   // n_in <= 7 (digit width / number of P limbs)
+        const u64 m = tab->mat30[k * n_out + j];
 #pragma unroll
         for (int u = 0; u < 8; u++)
-            acc_wide(acc[u], __ldg(src + (size_t)k * T.N + col_offset<LOGN>(tile, u * kTileThreads + t)), m);
+            mac30(acc[u], __ldg(src + (size_t)k * T.N + col_offset<LOGN>(tile, u * kTileThreads + t)), m);
     }
 #pragma unroll
-    for (int u = 0; u < 8; u++) sm[tphys(u * kTileThreads + t)] = fwd_encode(redc(acc[u], pc.q, pc.qinv_neg), fp_ok(pc.q));
+    for (int u = 0; u < 8; u++) sm[tphys(u * kTileThreads + t)] = fwd_encode(redc(fold30(acc[u]), pc.q, pc.qinv_neg), fp_ok(pc.q));
     __syncthreads();
     fwd_col_pass<LOGN>(sm, t, T, prime, pc.q);
     // ext_nl >= 0 (ModUp): the output is a digit in extended-basis order (Q limbs 0..nl-1, then P); else limb j
@@ -136,7 +151,10 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
 // memory phase of one CTA overlaps the butterfly phase of its neighbours on the SM.
 template <int LOGN, int NDIG>
 __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __grid_constant__ DevTables T, const __grid_constant__ FusedKsArgs a) {
-    __shared__ u64 sm[kTileWords];
+    extern __shared__ __align__(128) unsigned char smraw[];
+    u64* sm = reinterpret_cast<u64*>(smraw);                       // work tile
+    u64* kst = reinterpret_cast<u64*>(smraw + kStageOff);           // NDIG staged key tiles (TMA)
+    u64* mbar = reinterpret_cast<u64*>(smraw + kStageOff + NDIG * kTileBytes);
     const int t = threadIdx.x, otile = blockIdx.x;
     const int i = blockIdx.y >> 1, comp = blockIdx.y & 1, b = blockIdx.z;
     const u32 g = a.galois[b];
@@ -150,35 +168,42 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __g
     const u64* key = (comp == 0 ? a.keyB[b] : a.keyA[b]) + (size_t)i * T.N + toff;
     const u64* dig = a.digits + (size_t)b * a.digits_bs + (size_t)i * T.N + toff;
     const size_t kstride = (size_t)(a.L + a.K) * T.N, dstride = (size_t)(a.nl + a.K) * T.N;
-    u64 ip[8];
+    // the key tiles of this CTA (NDIG x 16 KB, each contiguous) are fetched by TMA bulk copies into shared
+    // memory while the converted tile is loaded and transformed: 48 KB in flight per CTA without holding
+    // registers, and the inner product reads its keys at shared-memory latency
+    if (t == 0) {
+        mbar_init(mbar, 1);
+        mbar_expect_tx(mbar, NDIG * kTileBytes);
+#pragma unroll
+        for (int j = 0; j < NDIG; j++) bulk_g2s(kst + j * kTileN, key + j * kstride, kTileBytes, mbar);
+    }
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
         const ulonglong2 x = ldg128(cv + e);
         sm[tphys(e)] = x.x;
         sm[tphys(e + 1)] = x.y;
-        u128d a0 = {0, 0}, a1 = {0, 0};
-#pragma unroll
-        for (int j = 0; j < NDIG; j++) {
-            const ulonglong2 d = ldg128(dig + j * dstride + e);
-            const ulonglong2 kv = ld_stream128(key + j * kstride + e);
-            acc_wide(a0, d.x, kv.x);
-            acc_wide(a1, d.y, kv.y);
-        }
-        ip[2 * u] = redc(a0, q, pc.qinv_neg);
-        ip[2 * u + 1] = redc(a1, q, pc.qinv_neg);
     }
     __syncthreads();
     fwd_row_pass<LOGN>(sm, t, tile, T, i, q);
     const u64* add = (comp == 0 ? a.add0 : a.add1);
     if (add) add += (size_t)b * a.add_bs + (size_t)i * T.N + toff;
     // P^-1 is folded into the evaluation keys' Q limbs and into the ModDown conversion matrix at load time
+    mbar_wait(mbar, 0);
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
+        acc3 a0 = {0, 0, 0}, a1 = {0, 0, 0};
+#pragma unroll
+        for (int j = 0; j < NDIG; j++) {
+            const ulonglong2 d = ldg128(dig + j * dstride + e);
+            const ulonglong2 kv = *reinterpret_cast<const ulonglong2*>(kst + j * kTileN + e);
+            mac30(a0, d.x, kv.x);
+            mac30(a1, d.y, kv.y);
+        }
         const u64 c0 = fwd_normalize(sm[tphys(e)], pc, fp), c1 = fwd_normalize(sm[tphys(e + 1)], pc, fp);
-        u64 r0 = sub_mod(ip[2 * u], c0, q);
-        u64 r1 = sub_mod(ip[2 * u + 1], c1, q);
+        u64 r0 = sub_mod(redc(fold30(a0), q, pc.qinv_neg), c0, q);
+        u64 r1 = sub_mod(redc(fold30(a1), q, pc.qinv_neg), c1, q);
         if (add) {
             const ulonglong2 ad = ldg128(add + e);
             r0 = add_mod(r0, ad.x, q);
@@ -203,10 +228,16 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __g
 template <int LOGN, int NDIG>
 static void launch_fused_tn(const DevTables& T, const FusedKsArgs& a, const BaseConvTable* moddown, int nb, cudaStream_t st) {
     using G = NttGeo<LOGN>;
-    k_ks_p_inner<LOGN, NDIG><<<dim3(G::TILES, 2 * a.K, nb), kTileThreads, 0, st>>>(T, a);
+    static bool attr_done = false;   // > 48 KB of dynamic shared memory needs the opt-in, once per instantiation
+    if (!attr_done) {
+        cudaFuncSetAttribute(k_ks_p_inner<LOGN, NDIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ks_smem_bytes(NDIG));
+        cudaFuncSetAttribute(k_ks_q_finish<LOGN, NDIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ks_smem_bytes(NDIG));
+        attr_done = true;
+    }
+    k_ks_p_inner<LOGN, NDIG><<<dim3(G::TILES, 2 * a.K, nb), kTileThreads, ks_smem_bytes(NDIG), st>>>(T, a);
     k_inv_cols<LOGN><<<dim3(G::TILES, a.K, nb * 2), kTileThreads, 0, st>>>(T, moddown, a.tmpP, (size_t)a.K * T.N);
     k_conv_fwd_col<LOGN><<<dim3(G::TILES, a.nl, nb * 2), kTileThreads, 0, st>>>(T, moddown, a.tmpP, (size_t)a.K * T.N, a.conv, (size_t)a.nl * T.N, -1, 0);
-    k_ks_q_finish<LOGN, NDIG><<<dim3(G::TILES, 2 * a.nl, nb), kTileThreads, 0, st>>>(T, a);
+    k_ks_q_finish<LOGN, NDIG><<<dim3(G::TILES, 2 * a.nl, nb), kTileThreads, ks_smem_bytes(NDIG), st>>>(T, a);
 }
 template <int LOGN>
 static void launch_fused_t(const DevTables& T, const FusedKsArgs& a, const BaseConvTable* moddown, int nb, cudaStream_t st) {

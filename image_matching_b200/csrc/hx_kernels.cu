@@ -84,6 +84,7 @@ __global__ void __launch_bounds__(kThreads) k_ks_inner(DevTables T, const u64* _
         size_t koff = ((size_t)j * (L + K) + kl) * T.N + idx;
         ulonglong2 vb = ld_stream128(kb + koff);
         ulonglong2 va = ld_stream128(ka + koff);
+        vb.x = unsplit30(vb.x); vb.y = unsplit30(vb.y); va.x = unsplit30(va.x); va.y = unsplit30(va.y);   // keys are stored split (fused path)
         acc_wide(b0, d.x, vb.x);
         acc_wide(b1, d.y, vb.y);
         acc_wide(a0, d.x, va.x);
@@ -263,6 +264,16 @@ __global__ void __launch_bounds__(kThreads) k_to_mont(DevTables T, u64* __restri
     x.x = redc(mul_wide(x.x, pc.r2), pc.q, pc.qinv_neg);
     x.y = redc(mul_wide(x.y, pc.r2), pc.q, pc.qinv_neg);
     st128(p, x);
+}
+__global__ void __launch_bounds__(kThreads) k_split30(u64* __restrict__ data, size_t words) {
+    size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (i >= words) return;
+    ulonglong2 x = *reinterpret_cast<ulonglong2*>(data + i);
+    x.x = split30(x.x); x.y = split30(x.y);
+    st128(data + i, x);
+}
+void launch_split30(u64* data, size_t words, cudaStream_t st) {
+    k_split30<<<(unsigned)((words / 2 + kThreads - 1) / kThreads), kThreads, 0, st>>>(data, words);
 }
 void launch_to_mont(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, cudaStream_t st) {
     // nbatch must be a multiple of lm.period; split so grid.y stays a multiple of the period

@@ -36,6 +36,7 @@ struct BaseConvTable {          // device-resident
     u64 hatinv[8], hatinv_sh[8];           // (Q/q_i)^-1 mod q_i  (Shoup pair)
     u64 mat[8 * kMaxPrimes];               // (Q/q_i) * 2^64 mod p_j  (Montgomery form), [i][j]
     u64 hatinv_n[8], hatinv_n_sh[8];       // hatinv * N^-1 mod q_i: folds the inverse transform's scaling (fused path)
+    u64 mat30[8 * kMaxPrimes];             // mat, pre-split into 30-bit halves (split30) for the carry-free MAC
 };
 // in: [nbatch][n_in][N] (stride_in limbs between batches), out: [nbatch][n_out][N]
 void launch_baseconv(const DevTables& T, const BaseConvTable* tab, int n_in, int n_out, const u64* in, size_t in_batch_stride,
@@ -106,6 +107,8 @@ void launch_tensor(const DevTables& T, u64* out, const u64* a, size_t cs_a, cons
 void launch_automorph(const DevTables& T, u64* out, const u64* in, const u32* map, int nlimbs_total, cudaStream_t st);
 void launch_automap(int N, int logN, u64 k, u32* map, cudaStream_t st);
 void launch_to_mont(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, cudaStream_t st);
+// in place: x -> split30(x) (engine-internal key form, see hx_modarith.cuh)
+void launch_split30(u64* data, size_t words, cudaStream_t st);
 
 // ---- rescale (row P7)
 // last: [N] coefficient form of limb nl-1 ; tmp out: [nl-1][N] = lift(last)*(-q_l^-1) mod q_i

@@ -59,6 +59,40 @@ __device__ __forceinline__ u64 umulhi_approx(u64 a, u64 b) {
 }
 __device__ __forceinline__ u64 shoup_lazy4(u64 a, u64 w, u64 wsh, u64 q) { return a * w - umulhi_approx(a, wsh) * q; }
 
+// ---- carry-free lazy multiply-accumulate on 30-bit halves ----------------------------------------
+// x = x1*2^30 + x0 with x0, x1 < 2^30 (any x < 2^60).  A product x*y is the three columns
+//   lo = x0*y0,  mid = x0*y1 + x1*y0,  hi = x1*y1      (x*y = lo + mid*2^30 + hi*2^60)
+// each column is one or two IMAD.WIDE.U32 with a 64-bit addend and never overflows while at most 7
+// products are accumulated (mid < 2*7*2^60 < 2^64): 4 multiplier-pipe instructions per product and no
+// carry chain, against ~12 for a 64x64->128 multiply-accumulate.  Long-lived operands (evaluation keys,
+// conversion matrices) are stored pre-split as (x1 << 32) | x0, so only the streaming operand is split.
+struct acc3 { u64 lo, mid, hi; };
+constexpr u32 kMask30 = 0x3FFFFFFFu;
+__device__ __host__ __forceinline__ u64 split30(u64 x) { return ((x >> 30) << 32) | (x & kMask30); }
+__device__ __host__ __forceinline__ u64 unsplit30(u64 s) { return ((s >> 32) << 30) | (s & 0xFFFFFFFFull); }
+__device__ __forceinline__ u64 madw(u32 a, u32 b, u64 c) {
+    u64 d;
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(d) : "r"(a), "r"(b), "l"(c));
+    return d;
+}
+// acc += x * y ; x plain (< 2^60), ys = split30(y)
+__device__ __forceinline__ void mac30(acc3& a, u64 x, u64 ys) {
+    const u32 x0 = (u32)x & kMask30, x1 = (u32)(x >> 30);
+    const u32 y0 = (u32)ys, y1 = (u32)(ys >> 32);
+    a.lo = madw(x0, y0, a.lo);
+    a.mid = madw(x0, y1, a.mid);
+    a.mid = madw(x1, y0, a.mid);
+    a.hi = madw(x1, y1, a.hi);
+}
+// the accumulated value as a 128-bit integer
+__device__ __forceinline__ u128d fold30(const acc3& a) {
+    u128d t;
+    const u64 m_lo = a.mid << 30, m_hi = a.mid >> 34, h_lo = a.hi << 60, h_hi = a.hi >> 4;
+    asm("add.cc.u64 %0, %2, %3;\n\taddc.u64 %1, %4, %5;" : "=l"(t.lo), "=l"(t.hi) : "l"(a.lo), "l"(m_lo), "l"(m_hi), "l"(h_hi));
+    asm("add.cc.u64 %0, %0, %2;\n\taddc.u64 %1, %1, 0;" : "+l"(t.lo), "+l"(t.hi) : "l"(h_lo));
+    return t;
+}
+
 // Montgomery REDC: T = hi*2^64 + lo < q*2^64  ->  T * 2^-64 mod q in [0,q).
 __device__ __forceinline__ u64 redc(u128d t, u64 q, u64 qinv_neg) {
     u64 m = t.lo * qinv_neg;
@@ -94,6 +128,31 @@ __device__ __forceinline__ ulonglong2 ld_stream128(const u64* p) {
     ulonglong2 v;
     asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
     return v;
+}
+// Asynchronous HBM -> L2 prefetch of `bytes` (multiple of 16) contiguous bytes at a 16-byte aligned address.
+__device__ __forceinline__ void l2_prefetch(const void* p, unsigned bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+// ---- TMA bulk copy global -> shared, completion on an mbarrier (sm_90+; SASS UBLKCP) -----------------
+__device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(u64* bar, u32 arrivals) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(arrivals) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(u64* bar, u32 bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// bytes: multiple of 16; both addresses 16-byte aligned
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, u32 bytes, u64* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u64* bar, u32 parity) {
+    u32 done;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    } while (!done);
 }
 __device__ __forceinline__ void st128(u64* p, ulonglong2 v) { *reinterpret_cast<ulonglong2*>(p) = v; }
 

@@ -400,7 +400,7 @@ u64* Engine::ks_precompute(const u64* c, int nl, int* ndig_out, int nbatch, size
         m.scratch = alloc_words((size_t)nbatch * nl * N);
         m.digits = digits;
         {   // algorithmic bytes: input polynomial once, digits once
-            Scope sc(this, PK_MODUP, 2 + 2 * ndig, 8.0 * N * nbatch * (nl + (double)ndig * ext));
+            Scope sc(this, PK_MODUP, 4, 8.0 * N * nbatch * (nl + (double)ndig * ext));
             launch_fused_modup(T, m, st);
         }
         free_words(m.scratch);

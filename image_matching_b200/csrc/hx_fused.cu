@@ -84,17 +84,35 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_p_inner(const __gr
 }
 
 // ---------------------------------------------------------------------------------------------
+// Conversion tables of one launch: a single table (ModDown, rescale) or the per-digit tables of a ModUp,
+// whose digits then share ONE launch of each stage (grid.y runs over the limbs / targets of all digits).
+struct TabSet {
+    const BaseConvTable* t[kMaxDigits];
+    int ndig;
+    int alpha;                 // source limbs per digit (inverse-column stage: digit of limb y = min(y / alpha, ndig - 1))
+    int ystart[kMaxDigits + 1]; // conversion stage: targets of digit d are grid.y in [ystart[d], ystart[d+1])
+    size_t in_off[kMaxDigits];  // conversion stage: words added to the input / output pointer for digit d
+    size_t out_off[kMaxDigits];
+};
+static TabSet single_table(const BaseConvTable* tab) {
+    TabSet s{};
+    s.t[0] = tab; s.ndig = 1; s.alpha = 1 << 20; s.ystart[0] = 0; s.ystart[1] = 1 << 20;
+    return s;
+}
+
 // K2a: grid (TILES, n_in, nbatch), in place on [nbatch][n_in][N]: inverse column pass, then
 // x * hatinv_n  (hatinv_n = (Qhat_k^-1 * N^-1) mod q_k folds the N^-1 of the inverse transform into
 // the first multiplication of ApproxSwitchCRTBasis).  Output canonical, coefficient order.
 template <int LOGN>
-__global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_cols(const __grid_constant__ DevTables T, const BaseConvTable* __restrict__ tab,
+__global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_cols(const __grid_constant__ DevTables T, const __grid_constant__ TabSet ts,
                                                               u64* __restrict__ data, size_t bs) {
     __shared__ u64 sm[kTileWords];
-    const int t = threadIdx.x, tile = blockIdx.x, k = blockIdx.y;
+    const int t = threadIdx.x, tile = blockIdx.x;
+    const int dgt = min((int)blockIdx.y / ts.alpha, ts.ndig - 1), k = blockIdx.y - dgt * ts.alpha;
+    const BaseConvTable* __restrict__ tab = ts.t[dgt];
     const int prime = tab->src[k];
     const u64 q = T.pc[prime].q;
-    u64* limb = data + (size_t)blockIdx.z * bs + (size_t)k * T.N;
+    u64* limb = data + (size_t)blockIdx.z * bs + (size_t)blockIdx.y * T.N;
 #pragma unroll
     for (int u = 0; u < 8; u++) {
         const int l = u * kTileThreads + t;
@@ -110,39 +128,78 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_cols(const __grid
     }
 }
 
-// K2b: grid (TILES, n_out, nbatch).  in: [nbatch][n_in][N] scaled coefficients (K2a);
-// out: [nbatch][n_out][N], forward column pass done, values lazy (see fwd_round_ct).
+// K2b: grid (TILES, ceil(targets / jgroup), nbatch).  in: [nbatch][n_in][N] scaled coefficients (K2a);
+// out: [nbatch][n_out][N], forward column pass done, values pass-internal (see fwd_encode).
+// The n_in source column tiles are staged into shared memory once per CTA by cp.async (all of them in
+// flight together, no registers held) and converted to `jgroup` target limbs from there: a large batch
+// re-reads the sources from L2 n_out / jgroup times instead of n_out times.
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
+}
 template <int LOGN>
-__global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __grid_constant__ DevTables T, const BaseConvTable* __restrict__ tab,
+__global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __grid_constant__ DevTables T, const __grid_constant__ TabSet ts,
                                                                   const u64* __restrict__ in, size_t in_bs, u64* __restrict__ out, size_t out_bs,
-                                                                  int ext_nl, int L) {
-    __shared__ u64 sm[kTileWords];
-    const int t = threadIdx.x, tile = blockIdx.x, j = blockIdx.y;
+                                                                  int ext_nl, int L, int jgroup) {
+    using G = NttGeo<LOGN>;
+    extern __shared__ __align__(128) unsigned char smraw[];
+    u64* sm = reinterpret_cast<u64*>(smraw);
+    u64* stage = reinterpret_cast<u64*>(smraw + kStageOff);          // [n_in][2048], local index r*C + c
+    const int t = threadIdx.x, tile = blockIdx.x;
+    int dgt = 0;
+    while (dgt + 1 < ts.ndig && (int)blockIdx.y >= ts.ystart[dgt + 1]) dgt++;
+    const BaseConvTable* __restrict__ tab = ts.t[dgt];
+    in += ts.in_off[dgt];
+    out += ts.out_off[dgt];
     const int n_in = tab->n_in, n_out = tab->n_out;
-    const int prime = tab->dst[j];
-    const PrimeConst pc = T.pc[prime];
-    const u64* src = in + (size_t)blockIdx.z * in_bs;
-    acc3 acc[8];
+    const int j0 = (blockIdx.y - ts.ystart[dgt]) * jgroup, j1 = min(n_out, j0 + jgroup);
+    const u64* src = in + (size_t)blockIdx.z * in_bs + ((size_t)tile << G::LOGC);
+    constexpr int kSegs = (1 << G::LOGC) / 2;                         // 16-byte chunks per tile row
+    for (int k = 0; k < n_in; k++) {
 #pragma unroll
-    for (int u = 0; u < 8; u++) acc[u] = {0, 0, 0};
-    for (int k = 0; k < n_in; k++) {   // n_in <= 7 (digit width / number of P limbs)
-        const u64 m = tab->mat30[k * n_out + j];
-#pragma unroll
-        for (int u = 0; u < 8; u++)
-            mac30(acc[u], __ldg(src + (size_t)k * T.N + col_offset<LOGN>(tile, u * kTileThreads + t)), m);
+        for (int i = 0; i < 4; i++) {
+            const int ch = i * kTileThreads + t, r = ch / kSegs, sg = ch % kSegs;
+            cp_async16(stage + k * kTileN + (r << G::LOGC) + sg * 2, src + (size_t)k * T.N + ((size_t)r << G::B) + sg * 2);
+        }
     }
-#pragma unroll
-    for (int u = 0; u < 8; u++) sm[tphys(u * kTileThreads + t)] = fwd_encode(redc(fold30(acc[u]), pc.q, pc.qinv_neg), fp_ok(pc.q));
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
     __syncthreads();
-    fwd_col_pass<LOGN>(sm, t, T, prime, pc.q);
-    // ext_nl >= 0 (ModUp): the output is a digit in extended-basis order (Q limbs 0..nl-1, then P); else limb j
-    const int pos = ext_nl < 0 ? j : (prime < L ? prime : ext_nl + prime - L);
-    u64* dst = out + (size_t)blockIdx.z * out_bs + (size_t)pos * T.N;
+    for (int j = j0; j < j1; j++) {
+        const int prime = tab->dst[j];
+        const PrimeConst pc = T.pc[prime];
+        acc3 acc[8];
 #pragma unroll
-    for (int u = 0; u < 8; u++) {
-        const int l = u * kTileThreads + t;
-        dst[col_offset<LOGN>(tile, l)] = sm[tphys(l)];
+        for (int u = 0; u < 8; u++) acc[u] = {0, 0, 0};
+        for (int k = 0; k < n_in; k++) {   // n_in <= 7 (digit width / number of P limbs)
+            const u64 m = tab->mat30[k * n_out + j];
+#pragma unroll
+            for (int u = 0; u < 8; u++) mac30(acc[u], stage[k * kTileN + u * kTileThreads + t], m);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; u++) sm[tphys(u * kTileThreads + t)] = fwd_encode(redc(fold30(acc[u]), pc.q, pc.qinv_neg), fp_ok(pc.q));
+        __syncthreads();
+        fwd_col_pass<LOGN>(sm, t, T, prime, pc.q);
+        // ext_nl >= 0 (ModUp): the output is a digit in extended-basis order (Q limbs 0..nl-1, then P); else limb j
+        const int pos = ext_nl < 0 ? j : (prime < L ? prime : ext_nl + prime - L);
+        u64* dst = out + (size_t)blockIdx.z * out_bs + (size_t)pos * T.N;
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            const int l = u * kTileThreads + t;
+            dst[col_offset<LOGN>(tile, l)] = sm[tphys(l)];
+        }
+        __syncthreads();   // the work tile is reused by the next target limb
     }
+}
+// launch helper: dynamic shared memory = work tile + n_in staged source tiles
+template <int LOGN>
+static void launch_conv_fwd_col(const DevTables& T, const TabSet& ts, int max_n_in, int ny, int nbatch, const u64* in, size_t in_bs, u64* out,
+                                size_t out_bs, int ext_nl, int L, int jgroup, cudaStream_t st) {
+    static int attr_bytes = 0;
+    const int bytes = (int)(kStageOff + max_n_in * kTileBytes);
+    if (bytes > attr_bytes) {
+        cudaFuncSetAttribute(k_conv_fwd_col<LOGN>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        attr_bytes = bytes;
+    }
+    k_conv_fwd_col<LOGN><<<dim3(NttGeo<LOGN>::TILES, ny, nbatch), kTileThreads, bytes, st>>>(T, ts, in, in_bs, out, out_bs, ext_nl, L, jgroup);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -235,8 +292,11 @@ static void launch_fused_tn(const DevTables& T, const FusedKsArgs& a, const Base
         attr_done = true;
     }
     k_ks_p_inner<LOGN, NDIG><<<dim3(G::TILES, 2 * a.K, nb), kTileThreads, ks_smem_bytes(NDIG), st>>>(T, a);
-    k_inv_cols<LOGN><<<dim3(G::TILES, a.K, nb * 2), kTileThreads, 0, st>>>(T, moddown, a.tmpP, (size_t)a.K * T.N);
-    k_conv_fwd_col<LOGN><<<dim3(G::TILES, a.nl, nb * 2), kTileThreads, 0, st>>>(T, moddown, a.tmpP, (size_t)a.K * T.N, a.conv, (size_t)a.nl * T.N, -1, 0);
+    const TabSet ts = single_table(moddown);
+    k_inv_cols<LOGN><<<dim3(G::TILES, a.K, nb * 2), kTileThreads, 0, st>>>(T, ts, a.tmpP, (size_t)a.K * T.N);
+    // large batches: 4 target limbs per CTA share one staging of the K source tiles
+    const int jg = (nb * 2 >= 16) ? 4 : 1;
+    launch_conv_fwd_col<LOGN>(T, ts, a.K, (a.nl + jg - 1) / jg, nb * 2, a.tmpP, (size_t)a.K * T.N, a.conv, (size_t)a.nl * T.N, -1, 0, jg, st);
     k_ks_q_finish<LOGN, NDIG><<<dim3(G::TILES, 2 * a.nl, nb), kTileThreads, ks_smem_bytes(NDIG), st>>>(T, a);
 }
 template <int LOGN>
@@ -388,12 +448,20 @@ static void modup_t(const DevTables& T, const ModUpArgs& m, cudaStream_t st) {
     using G = NttGeo<LOGN>;
     const int ext = m.nl + m.K;
     k_inv_rows<LOGN><<<dim3(G::TILES, m.nl, m.nbatch), kTileThreads, 0, st>>>(T, m.c, m.c_bs, m.scratch, (size_t)m.nl * T.N, 0);
+    // all digits in one launch per stage: inverse columns of the nl source limbs, then every digit's
+    // conversion to its complement limbs fused with their forward column pass
+    TabSet ts{};
+    ts.ndig = m.ndig; ts.alpha = m.alpha; ts.ystart[0] = 0;
     for (int d = 0; d < m.ndig; d++) {
         const int lo = d * m.alpha, hi = (d == m.ndig - 1) ? m.nl : (d + 1) * m.alpha, sz = hi - lo;
-        k_inv_cols<LOGN><<<dim3(G::TILES, sz, m.nbatch), kTileThreads, 0, st>>>(T, m.tabs[d], m.scratch + (size_t)lo * T.N, (size_t)m.nl * T.N);
-        k_conv_fwd_col<LOGN><<<dim3(G::TILES, ext - sz, m.nbatch), kTileThreads, 0, st>>>(
-            T, m.tabs[d], m.scratch + (size_t)lo * T.N, (size_t)m.nl * T.N, m.digits + (size_t)d * ext * T.N, (size_t)m.ndig * ext * T.N, m.nl, m.L);
+        ts.t[d] = m.tabs[d];
+        ts.ystart[d + 1] = ts.ystart[d] + (ext - sz);
+        ts.in_off[d] = (size_t)lo * T.N;
+        ts.out_off[d] = (size_t)d * ext * T.N;
     }
+    k_inv_cols<LOGN><<<dim3(G::TILES, m.nl, m.nbatch), kTileThreads, 0, st>>>(T, ts, m.scratch, (size_t)m.nl * T.N);
+    launch_conv_fwd_col<LOGN>(T, ts, m.alpha, ts.ystart[m.ndig], m.nbatch,
+                              m.scratch, (size_t)m.nl * T.N, m.digits, (size_t)m.ndig * ext * T.N, m.nl, m.L, 1, st);
     k_modup_rows<LOGN><<<dim3(G::TILES, ext, m.ndig * m.nbatch), kTileThreads, 0, st>>>(T, m.digits, m.c, m.c_bs, m.ndig, m.nl, m.L, m.alpha);
 }
 void launch_fused_modup(const DevTables& T, const ModUpArgs& m, cudaStream_t st) {
@@ -413,7 +481,7 @@ static void rescale_t(const DevTables& T, const RescaleArgs& r, cudaStream_t st)
     const int nl = r.nl;
     // dropped limb of every component -> coefficients (inverse rows, then inverse columns * N^-1 via the 1-limb table)
     k_inv_rows<LOGN><<<dim3(G::TILES, 1, r.ncomp), kTileThreads, 0, st>>>(T, r.c + (size_t)(nl - 1) * T.N, r.c_bs, r.last, (size_t)T.N, nl - 1);
-    k_inv_cols<LOGN><<<dim3(G::TILES, 1, r.ncomp), kTileThreads, 0, st>>>(T, r.last_tab, r.last, (size_t)T.N);
+    k_inv_cols<LOGN><<<dim3(G::TILES, 1, r.ncomp), kTileThreads, 0, st>>>(T, single_table(r.last_tab), r.last, (size_t)T.N);
     k_rescale_cols<LOGN><<<dim3(G::TILES, nl - 1, r.ncomp), kTileThreads, 0, st>>>(T, r.last, (size_t)T.N, r.tmp, (size_t)(nl - 1) * T.N, nl, r.negqlinv);
     k_rescale_rows<LOGN><<<dim3(G::TILES, nl - 1, r.ncomp), kTileThreads, 0, st>>>(T, r.out, r.out_bs, r.c, r.c_bs, r.tmp, (size_t)(nl - 1) * T.N, r.qlinv);
 }

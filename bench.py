@@ -314,8 +314,15 @@ def run_b200(args):
         peak = float(peaks.get("hbm_gbs", 0)) or 6500.0
         peak_src = "MEASURED_PEAKS.json hbm_gbs" if peaks.get("hbm_gbs") else "fallback 6500 GB/s (B200_PROFILING.md)"
         d = prof[dominant]
-        avg_ms = d["ms"] / max(1, d["launches"])
-        achieved = (d["bytes"] / max(1, d["launches"])) / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+        traffic = None
+        try:   # ncu --set full DRAM bytes per launch of this kernel family (captured once per change, see profiles/)
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json"))).get(dominant, {}).get("traffic_bytes_per_launch")
+        except Exception:
+            pass
+        # a "launch" of a fused family is its group of kernels (4 for the key switch, ModUp and rescale)
+        groups = max(1, d["launches"] // {"ks_hoisted": 4, "ks_fused": 4, "modup": 4, "rescale": 4}.get(dominant, 1))
+        avg_ms = d["ms"] / groups
+        achieved = (d["bytes"] / groups) / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
         sec = ms_total / args.steps / 1e3
         sec_e2e = ms_e2e / args.steps / 1e3
         line = {"metric": METRIC, "value": sec, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -325,8 +332,8 @@ def run_b200(args):
                         "d2h_bytes_per_step": (total_blocks + 1) * res_words * 8},
                 "gpu_launches": launches, "clocks": sampler.result(), "results_ok": bool(ok),
                 "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                             "launches": d["launches"], "avg_launch_ms": avg_ms, "share_of_step": d["ms"] / ms_total,
+                             "frac": achieved / peak, "traffic": traffic, "algorithmic_bytes_per_launch": d["bytes"] / groups, "peak_source": peak_src,
+                             "launches": groups, "kernels": d["launches"], "avg_launch_ms": avg_ms, "share_of_step": d["ms"] / ms_total,
                              "warmup_profile_ms": {k: round(v["ms"], 3) for k, v in prof_all.items() if v["launches"]}}}
         if not args.no_cpu_baseline and world == 1:
             v, desc, cores = cpu_port_latency(args.ring_dim, ndiag, total_blocks, n_rot_sample=96)

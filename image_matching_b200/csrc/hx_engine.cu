@@ -99,7 +99,7 @@ Engine::~Engine() {
 // ------------------------------------------------------------------------------------------ profiler
 const char* prof_kind_name(int kind) {
     static const char* names[PK_COUNT] = {"ntt_fwd", "ntt_inv", "baseconv", "ks_inner", "moddown", "elementwise", "scalar", "tensor",
-                                          "automorph", "rescale", "diag_mac", "misc", "ks_fused", "modup"};
+                                          "automorph", "rescale", "diag_mac", "misc", "ks_fused", "modup", "ks_hoisted"};
     return (kind >= 0 && kind < PK_COUNT) ? names[kind] : "?";
 }
 Engine::Scope::Scope(Engine* e_, int kind_, int nlaunch, double bytes) : e(e_), kind(kind_) {
@@ -463,7 +463,7 @@ void Engine::ks_core_batch(const u64* digits, int ndig, int nl, const std::vecto
             a.out_bs = out_bs;
             {   // algorithmic bytes of one key switch after ModUp: evk once, digits once per launch,
                 // addend once, result once
-                Scope sc(this, PK_KS_FUSED, 4,
+                Scope sc(this, ks_kind, 4,
                          8.0 * N * ((double)n * 2 * ndig * ext + (double)(digits_bs ? n : 1) * ndig * ext + (double)(addend_bs ? n : 1) * addend_comps * nl + (double)n * 2 * nl));
                 launch_fused_ks(T, a, moddown_table(nl), n, st);
             }

@@ -28,7 +28,7 @@ class Engine;
 // Kernel families for launch accounting and the optional CUDA-event profiler (bench.py roofline).
 enum ProfKind {
     PK_NTT_FWD = 0, PK_NTT_INV, PK_BASECONV, PK_KS_INNER, PK_MODDOWN, PK_EW, PK_SCALAR, PK_TENSOR, PK_AUTOMORPH,
-    PK_RESCALE, PK_DIAG_MAC, PK_MISC, PK_KS_FUSED, PK_MODUP, PK_COUNT
+    PK_RESCALE, PK_DIAG_MAC, PK_MISC, PK_KS_FUSED, PK_MODUP, PK_KS_HOISTED, PK_COUNT
 };
 const char* prof_kind_name(int kind);
 
@@ -70,6 +70,7 @@ public:
     std::recursive_mutex mu;         // the reference enters from up to 48 OpenMP threads
     int rot_chunk = 32;              // hoisted rotations per fused key-switch batch (intermediates stay L2 resident)
     bool force_unfused = false;      // tests: run the unfused reference kernels instead of hx_fused.cu
+    int ks_kind = PK_KS_FUSED;       // profiler family of the next fused key switches (score_diag books its hoisted rotations separately)
     bool batch_blocks = true;        // HyDia path: relinearise/rescale/compare all blocks as one batch
     unsigned long long launches = 0; // kernels launched (bench "gpu_launches")
 

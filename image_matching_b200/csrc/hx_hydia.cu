@@ -61,6 +61,7 @@ std::vector<Ct> Engine::score_diag_batched(const Ct& query, int ndiag) {
     int ndig;
     u64* digits = ks_precompute(query->comp(1), nl, &ndig);
     const int chunk = std::max(1, std::min(rot_chunk, kMaxKsBatch));
+    ks_kind = PK_KS_HOISTED;
     for (int d0 = 1; d0 < ndiag; d0 += chunk) {
         int d1 = std::min(ndiag, d0 + chunk);
         std::vector<const EvalKey*> keys;
@@ -72,6 +73,7 @@ std::vector<Ct> Engine::score_diag_batched(const Ct& query, int ndiag) {
         }
         ks_core_batch(digits, ndig, nl, keys, query->comp(0), 1, gal, rotq + ct_words * d0, ct_words);
     }
+    ks_kind = PK_KS_FUSED;
     free_words(digits);
     // all blocks of this GPU in one launch each: diagonal MAC (the rotated query is fetched from HBM once
     // for all of them), relinearisation and rescale on the batch [G][3][nl][N]

@@ -62,6 +62,8 @@ SIGNATURES = {
     "hx_score_diag": (C.c_int, [VP, VP, C.c_int, C.POINTER(VP), C.c_int]),
     "hx_membership": (VP, [VP, VP, C.c_int, C.c_double, C.c_int]),
     "hx_index": (C.c_int, [VP, VP, C.c_int, C.c_double, C.c_int, C.POINTER(VP), C.c_int]),
+    "hx_score_hers": (C.c_int, [VP, C.POINTER(VP), C.c_int, C.POINTER(VP), C.c_int]),
+    "hx_compare_many": (C.c_int, [VP, C.POINTER(VP), C.c_int, C.c_double, C.c_int, C.POINTER(VP)]),
     "hx_ntt": (C.c_int, [VP, U64P, C.c_int, I32P, C.c_int, C.c_int]),
     "hx_params_generate": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, I32P, I32P, I32P, I32P, U64P, U64P, U64P, U64P]),
     "hx_client_create": (VP, [VP, C.c_uint64]),

@@ -59,6 +59,17 @@ def diagonal_pack(db: np.ndarray, batch: int) -> np.ndarray:
     return out
 
 
+def hers_pack(db: np.ndarray, batch: int) -> np.ndarray:
+    """HersEnroller packing (enroller_hers.cpp:14-36, 106-121): [matrices][dim][batch]; matrix m, column j, slot k =
+    normalize(db)[m*batch + k][j]; rows beyond the database stay zero."""
+    n, dim = db.shape
+    dbn = plaintext_normalize(db.astype(np.float64))
+    nmat = int(math.ceil(n / batch))
+    padded = np.zeros((nmat * batch, dim))
+    padded[:n] = dbn
+    return np.ascontiguousarray(padded.reshape(nmat, batch, dim).transpose(0, 2, 1))
+
+
 class Client:
     def __init__(self, cc: CryptoContext, seed: int = 1):
         self.cc = cc
@@ -109,6 +120,20 @@ class Client:
         """DiagonalReceiver::encryptQuery: normalise, tile batch/512 times, encrypt."""
         q = plaintext_normalize(np.asarray(query, dtype=np.float64))
         return [self.encrypt(np.tile(q, self.cc.GetBatchSize() // VECTOR_DIM))]
+
+    # ---- Enroller / Receiver roles for approach 4 (HERS)
+    def enroll_hers(self, db: np.ndarray) -> int:
+        """HersEnroller::serializeDB: column j of matrix m -> database ciphertext matrix{m}/index{j}, HBM resident."""
+        packed = hers_pack(db, self.cc.GetBatchSize())
+        for m in range(packed.shape[0]):
+            for j in range(packed.shape[1]):
+                self.enroll_row(m, j, packed[m, j])
+        return packed.shape[0]
+
+    def encryptQueryHers(self, query: np.ndarray) -> List[Ciphertext]:
+        """HersReceiver::encryptQuery (receiver_hers.cpp:13-24, 56-61): one ciphertext per coordinate, all slots equal."""
+        q = plaintext_normalize(np.asarray(query, dtype=np.float64))
+        return [self.encrypt(np.full(self.cc.GetBatchSize(), v)) for v in q]
 
     def decryptMembership(self, ct: Ciphertext) -> bool:
         return bool(self.decrypt(ct)[0] >= 1.0)

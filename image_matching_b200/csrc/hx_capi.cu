@@ -184,6 +184,27 @@ int hx_score_diag(hx_ctx* ctx, hx_ct* query, int ndiag, hx_ct** out, int max_out
 hx_ct* hx_membership(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sign_depth) {
     HX_TRY_PTR(need(ctx, "ctx"); need(query, "query"); return wrap(ctx->eng->membership(query->ct, ndiag, delta, sign_depth));)
 }
+int hx_score_hers(hx_ctx* ctx, hx_ct* const* query, int nquery, hx_ct** out, int max_out) {
+    try {
+        need(ctx, "ctx"); need(query, "query"); need(out, "out");
+        std::vector<Ct> q;
+        for (int i = 0; i < nquery; i++) { need(query[i], "query[i]"); q.push_back(query[i]->ct); }
+        std::vector<Ct> s = ctx->eng->score_hers(q);
+        if ((int)s.size() > max_out) throw std::runtime_error("hx_score_hers: output array too small");
+        for (size_t i = 0; i < s.size(); i++) out[i] = wrap(s[i]);
+        return (int)s.size();
+    } catch (const std::exception& e) { set_err(e); return -1; }
+}
+int hx_compare_many(hx_ctx* ctx, hx_ct* const* in, int n, double delta, int sign_depth, hx_ct** out) {
+    try {
+        need(ctx, "ctx"); need(in, "in"); need(out, "out");
+        std::vector<Ct> v;
+        for (int i = 0; i < n; i++) { need(in[i], "in[i]"); v.push_back(in[i]->ct); }
+        std::vector<Ct> s = ctx->eng->compare_many(v, delta, sign_depth);
+        for (size_t i = 0; i < s.size(); i++) out[i] = wrap(s[i]);
+        return 0;
+    } catch (const std::exception& e) { set_err(e); return -1; }
+}
 int hx_index(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sign_depth, hx_ct** out, int max_out) {
     try {
         need(ctx, "ctx"); need(query, "query"); need(out, "out");

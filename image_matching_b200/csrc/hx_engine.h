@@ -152,6 +152,11 @@ public:
     std::vector<Ct> score_diag_batched(const Ct& query, int ndiag);    // same, blocks kept as batches of <= 32
     Ct membership(const Ct& query, int ndiag, double delta, int depth); // membershipScenario
     std::vector<Ct> index(const Ct& query, int ndiag, double delta, int depth);   // indexScenario
+    // ---- HERS (approach 4) scoring, sender_hers.cpp:13-98: query = one ciphertext per coordinate, database matrix m =
+    // registered block m (index j = "diagonal" j).  One score ciphertext per matrix.
+    std::vector<Ct> score_hers(const std::vector<Ct>& query);
+    // chebyshevCompare of many ciphertexts of one shape as batches (the OpenMP loops of sender_*.cpp over scoreCipher)
+    std::vector<Ct> compare_many(const std::vector<Ct>& cts, double delta, int depth);
 
     // ---- building blocks exposed for parity tests
     void ntt_limbs(u64* data, int nbatch, const std::vector<int>& primes, bool inverse);

@@ -119,4 +119,59 @@ Ct Engine::membership(const Ct& query, int ndiag, double delta, int depth) {
     return eval_sum(m, N / 2);
 }
 
+// HersSender::computeSimilarity (sender_hers.cpp:13-26, 61-98): per matrix, sum over the coordinates i of
+// Rescale(Relinearize(EvalMultNoRelin(query[i], db[matrix][i]))).  The coordinates run in batches of 32: one
+// tensor-product launch against the HBM-resident database, one batched relinearisation (same EvalMultKey, 32
+// digit sets), one batched rescale, one modular sum over the batch.  Modular addition is associative and
+// commutative, so the result equals the reference's sequential EvalAddInPlace chain bit for bit.
+std::vector<Ct> Engine::score_hers(const std::vector<Ct>& query) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (query.empty()) throw std::runtime_error("score_hers: empty query");
+    if (db_.empty()) throw std::runtime_error("score_hers: no database matrix registered");
+    const int dim = (int)query.size(), nl = query[0]->nl;
+    for (auto& q : query)
+        if (q->ncomp != 2 || q->nl != nl || q->nb != 1 || q->deg != query[0]->deg) throw std::runtime_error("score_hers: query ciphertexts differ in shape");
+    if (nl != L) throw std::runtime_error("score_hers: query must be fresh (database ciphertexts are stored at full level)");
+    if (!(fused_ks_supported(logN) && !force_unfused)) throw std::runtime_error("score_hers needs the fused pipeline");
+    const size_t cs = (size_t)nl * N;
+    std::vector<Ct> out;
+    for (auto& kv : db_) {
+        if (kv.second.ndiag < dim) throw std::runtime_error("score_hers: database matrix has fewer columns than the query");
+        Ct acc = new_ct(2, nl - 1, query[0]->level + 1, query[0]->deg + 1 - 1);
+        for (int i0 = 0; i0 < dim; i0 += kMaxKsBatch) {
+            const int n = std::min(kMaxKsBatch, dim - i0);
+            CtPtrs ap;
+            for (int i = 0; i < n; i++) ap.p[i] = query[i0 + i]->d;
+            Ct t = new_ct(3, nl, query[0]->level, query[0]->deg + 1, n);
+            {   // algorithmic bytes: database ciphertexts once, query ciphertexts once, products once
+                Scope sc(this, PK_TENSOR, 1, 8.0 * N * nl * n * (2 + 2 + 3));
+                launch_tensor_db(T, t->d, ap, cs, kv.second.d + (size_t)i0 * 2 * cs, cs, nl, n, st);
+            }
+            Ct r = rescale(relinearize(t));
+            {
+                Scope sc(this, PK_EW, 1, 8.0 * N * r->nl * 2 * (n + 1));
+                launch_batch_sum(T, acc->d, r->d, r->nl, 2, n, i0 != 0, st);
+            }
+        }
+        out.push_back(acc);
+    }
+    return out;
+}
+
+std::vector<Ct> Engine::compare_many(const std::vector<Ct>& cts, double delta, int depth) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    std::vector<Ct> out;
+    const bool batch = batch_blocks && !force_unfused && fused_ks_supported(logN);
+    for (size_t i0 = 0; i0 < cts.size(); i0 += kMaxKsBatch) {
+        const size_t n = std::min((size_t)kMaxKsBatch, cts.size() - i0);
+        std::vector<Ct> part(cts.begin() + i0, cts.begin() + i0 + n);
+        if (batch && n > 1) {
+            for (auto& c : unstack(chebyshev_compare(stack(part), delta, depth))) out.push_back(c);
+        } else {
+            for (auto& c : part) out.push_back(chebyshev_compare(c, delta, depth));
+        }
+    }
+    return out;
+}
+
 }  // namespace hx

@@ -227,6 +227,53 @@ void launch_tensor(const DevTables& T, u64* out, const u64* a, size_t cs_a, cons
     k_tensor<<<grid, kThreads, 0, st>>>(T, out, a, cs_a, b, cs_b, nl);
 }
 
+// EvalMultCore against database ciphertexts kept in Montgomery form: one REDC per output word.
+__global__ void __launch_bounds__(kThreads) k_tensor_db(DevTables T, u64* __restrict__ out, const __grid_constant__ CtPtrs ap, size_t cs_a,
+                                                        const u64* __restrict__ db, size_t cs_b, int nl) {
+    int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    int i = blockIdx.y;
+    const PrimeConst pc = T.pc[i];
+    size_t off = (size_t)i * T.N + idx;
+    const u64* a = ap.p[blockIdx.z];
+    const u64* b = db + (size_t)blockIdx.z * 2 * cs_b;
+    out += (size_t)blockIdx.z * 3 * nl * T.N;
+    const ulonglong2 a0 = ldg128(a + off), a1 = ldg128(a + cs_a + off);
+    const ulonglong2 b0 = ld_stream128(b + off), b1 = ld_stream128(b + cs_b + off);
+    size_t cs_o = (size_t)nl * T.N;
+    ulonglong2 r;
+    r.x = mont_mul(a0.x, b0.x, pc.q, pc.qinv_neg); r.y = mont_mul(a0.y, b0.y, pc.q, pc.qinv_neg);
+    st128(out + off, r);
+    u128d m0 = mul_wide(a0.x, b1.x), m1 = mul_wide(a0.y, b1.y);     // 2 q^2 < q 2^64: one REDC for the cross term
+    acc_wide(m0, a1.x, b0.x); acc_wide(m1, a1.y, b0.y);
+    r.x = redc(m0, pc.q, pc.qinv_neg); r.y = redc(m1, pc.q, pc.qinv_neg);
+    st128(out + cs_o + off, r);
+    r.x = mont_mul(a1.x, b1.x, pc.q, pc.qinv_neg); r.y = mont_mul(a1.y, b1.y, pc.q, pc.qinv_neg);
+    st128(out + 2 * cs_o + off, r);
+}
+void launch_tensor_db(const DevTables& T, u64* out, const CtPtrs& a, size_t cs_a, const u64* db, size_t cs_b, int nl, int nbatch, cudaStream_t st) {
+    dim3 grid(blocks_for(T.N), nl, nbatch);
+    k_tensor_db<<<grid, kThreads, 0, st>>>(T, out, a, cs_a, db, cs_b, nl);
+}
+__global__ void __launch_bounds__(kThreads) k_batch_sum(DevTables T, u64* __restrict__ acc, const u64* __restrict__ in, int nl, size_t bs, int nbatch,
+                                                        int accumulate) {
+    int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    const u64 q = T.pc[blockIdx.y % nl].q;
+    size_t off = (size_t)blockIdx.y * T.N + idx;
+    ulonglong2 s = accumulate ? *reinterpret_cast<const ulonglong2*>(acc + off) : make_ulonglong2(0, 0);
+    for (int z = 0; z < nbatch; z++) {
+        const ulonglong2 x = ldg128(in + (size_t)z * bs + off);
+        s.x = add_mod(s.x, x.x, q);
+        s.y = add_mod(s.y, x.y, q);
+    }
+    st128(acc + off, s);
+}
+void launch_batch_sum(const DevTables& T, u64* acc, const u64* in, int nl, int ncomp, int nbatch, int accumulate, cudaStream_t st) {
+    dim3 grid(blocks_for(T.N), nl * ncomp, 1);
+    k_batch_sum<<<grid, kThreads, 0, st>>>(T, acc, in, nl, (size_t)ncomp * nl * T.N, nbatch, accumulate);
+}
+
 // AutomorphismTransform (row P3): out[l][j] = in[l][map[j]].
 __global__ void __launch_bounds__(kThreads) k_automorph(int N, u64* __restrict__ out, const u64* __restrict__ in, const u32* __restrict__ map) {
     int idx = blockIdx.x * blockDim.x + threadIdx.x;

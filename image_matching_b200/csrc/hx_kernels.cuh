@@ -104,6 +104,14 @@ void launch_add_scalar(const DevTables& T, u64* out, const u64* a, const ScalarT
 // EvalMultCore: (a0*b0, a0*b1+a1*b0, a1*b1); a,b: [2][.][N] with component strides; out [3][nl][N]
 // batch entry z: a + z*2*cs_a, b + z*2*cs_b (contiguous 2-component ciphertexts), out + z*3*nl*N
 void launch_tensor(const DevTables& T, u64* out, const u64* a, size_t cs_a, const u64* b, size_t cs_b, int nl, int nbatch, cudaStream_t st);
+// EvalMultNoRelin of nbatch (query, database) pairs (row R7, sender_hers.cpp:61-98): query ciphertext z = a.p[z]
+// ([2][nl_a][N], plain residues, component stride cs_a), database ciphertext z = db + z*2*cs_b (Montgomery form,
+// as registered by hx_db_register); out [nbatch][3][nl][N].
+struct CtPtrs { const u64* p[kMaxKsBatch]; };
+void launch_tensor_db(const DevTables& T, u64* out, const CtPtrs& a, size_t cs_a, const u64* db, size_t cs_b, int nl, int nbatch, cudaStream_t st);
+// acc[c][i][n] (+)= sum_z in[z][c][i][n] mod q_i over the nbatch entries of a batched ciphertext; ncl = ncomp*nl limbs
+// per entry, limb y has prime index y % nl.  accumulate = 0 overwrites acc.
+void launch_batch_sum(const DevTables& T, u64* acc, const u64* in, int nl, int ncomp, int nbatch, int accumulate, cudaStream_t st);
 void launch_automorph(const DevTables& T, u64* out, const u64* in, const u32* map, int nlimbs_total, cudaStream_t st);
 void launch_automap(int N, int logN, u64 k, u32* map, cudaStream_t st);
 void launch_to_mont(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, cudaStream_t st);

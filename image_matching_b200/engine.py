@@ -198,6 +198,18 @@ class CryptoContext:
         n = check_int(self._lib.hx_index(self._h, query._h, ndiag, delta, depth, out, 4096))
         return [self._ct(out[i]) for i in range(n)]
     def compare(self, a, delta=0.44, depth=10): return self._ct(self._lib.hx_compare(a._h, delta, depth))
+    def compare_many(self, cts: Sequence[Ciphertext], delta=0.44, depth=10) -> List[Ciphertext]:
+        """chebyshevCompare of every ciphertext of the list through one batched chain (hx_compare_many)."""
+        n = len(cts)
+        inp, out = (VP * n)(*[c._h for c in cts]), (VP * n)()
+        check_int(self._lib.hx_compare_many(self._h, inp, n, delta, depth, out))
+        return [self._ct(out[i]) for i in range(n)]
+    def score_hers(self, query: Sequence[Ciphertext]) -> List[Ciphertext]:
+        """HersSender::computeSimilarity on the registered database matrices (hx_score_hers)."""
+        n = len(query)
+        inp, out = (VP * n)(*[c._h for c in query]), (VP * 4096)()
+        m = check_int(self._lib.hx_score_hers(self._h, inp, n, out, 4096))
+        return [self._ct(out[i]) for i in range(m)]
 
     # ---- parity-test hook
     def ntt(self, data: np.ndarray, primes: Sequence[int], inverse: bool = False) -> np.ndarray:

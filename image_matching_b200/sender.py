@@ -1,5 +1,6 @@
-"""Mirror of the Sender class surface (/root/reference/include/sender.h:19-43) for approach 5:
-DiagonalSender (/root/reference/src/sender/sender_diag.cpp). Two code paths with identical
+"""Mirror of the Sender class surface (/root/reference/include/sender.h:19-43): DiagonalSender (approach 5,
+/root/reference/src/sender/sender_diag.cpp) and HersSender (approach 4, src/sender/sender_hers.cpp).
+DiagonalSender: Two code paths with identical
 results: `fused=True` (default) uses the fused C-ABI entry points; `fused=False` issues the same
 per-op call sequence as the reference (511 EvalFastRotation, 512 EvalMultNoRelin, 511 EvalAdd...)."""
 from __future__ import annotations
@@ -81,3 +82,50 @@ class DiagonalSender(Sender):
             return cc.index(queryCipher[0], VECTOR_DIM, MATCH_THRESHOLD, COMP_DEPTH)
         score = self.computeSimilarity(queryCipher)
         return [OpenFHEWrapper.chebyshevCompare(cc, s, MATCH_THRESHOLD, COMP_DEPTH) for s in score]
+
+
+class HersSender(Sender):
+    """sender_hers.cpp (approach 4). queryCipher = VECTOR_DIM ciphertexts, one per
+    coordinate (HersReceiver::encryptQuery); database matrix m, column j = serial/db_hers/matrix{m}/index{j}.bin,
+    registered with cc.db_register(m, j, ...) / client.enroll_hers. `fused=False` issues the reference's per-op
+    call sequence (EvalMultNoRelin, RelinearizeInPlace, RescaleInPlace per column, then the EvalAddInPlace chain)
+    through `db_loader(matrix, index)`."""
+
+    def __init__(self, cc: CryptoContext, pk, numVectors: int, fused: bool = True,
+                 db_loader: Optional[Callable[[int, int], Ciphertext]] = None):
+        super().__init__(cc, pk, numVectors)
+        self.fused, self.db_loader = fused, db_loader
+
+    def computeSimilarity(self, queryCipher):
+        cc = self.cc
+        if self.fused:
+            return cc.score_hers(queryCipher)
+        ciphersNeeded = int(math.ceil(float(self.numVectors) / float(cc.GetBatchSize())))
+        return [self.computeSimilarityHelper(i, queryCipher) for i in range(ciphersNeeded)]
+
+    def computeSimilarityHelper(self, matrixIndex: int, queryCipher) -> Ciphertext:
+        cc = self.cc
+        score = []
+        for i in range(len(queryCipher)):
+            s = self.computeSimilaritySerial(matrixIndex, i, queryCipher[i])
+            s = cc.RelinearizeInPlace(s)
+            score.append(cc.RescaleInPlace(s))
+        for i in range(1, len(score)):
+            score[0] = cc.EvalAddInPlace(score[0], score[i])
+        return score[0]
+
+    def computeSimilaritySerial(self, matrix: int, index: int, queryCipher: Ciphertext) -> Ciphertext:
+        return self.cc.EvalMultNoRelin(queryCipher, self.db_loader(matrix, index))
+
+    def _compare(self, score):
+        if self.fused:
+            return self.cc.compare_many(score, MATCH_THRESHOLD, COMP_DEPTH)
+        return [OpenFHEWrapper.chebyshevCompare(self.cc, s, MATCH_THRESHOLD, COMP_DEPTH) for s in score]
+
+    def indexScenario(self, queryCipher):
+        return self._compare(self.computeSimilarity(queryCipher))
+
+    def membershipScenario(self, queryCipher):
+        cc = self.cc
+        m = cc.EvalAddManyInPlace(self._compare(self.computeSimilarity(queryCipher)))
+        return cc.EvalSum(m, cc.GetBatchSize())

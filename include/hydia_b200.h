@@ -110,6 +110,16 @@ hx_ct* hx_membership(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sig
 /* DiagonalSender::indexScenario (sender_diag.cpp:52) */
 int hx_index(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sign_depth, hx_ct** out, int max_out);
 
+/* ---- other senders ------------------------------------------------- */
+/* HersSender::computeSimilarity (src/sender/sender_hers.cpp:13-26, 61-98): query = nquery ciphertexts, one per
+ * coordinate (HersReceiver::encryptQuery, src/receiver/receiver_hers.cpp:13-24); database matrix m, column j =
+ * serial/db_hers/matrix{m}/index{j}.bin, registered with hx_db_register(ctx, m, j, data).  Per matrix:
+ * sum_j Rescale(Relinearize(EvalMultNoRelin(query[j], db[m][j]))).  Returns the number of matrices. */
+int hx_score_hers(hx_ctx* ctx, hx_ct* const* query, int nquery, hx_ct** out, int max_out);
+/* OpenFHEWrapper::chebyshevCompare over a vector of score ciphertexts (the "#pragma omp parallel for" loops of
+ * sender_hers.cpp:33-36, sender_diag.cpp:40-43, ...): all n inputs go through one batched chain. out: n handles. */
+int hx_compare_many(hx_ctx* ctx, hx_ct* const* in, int n, double delta, int sign_depth, hx_ct** out);
+
 /* ---- building blocks exposed for parity tests ---------------------------------------------- */
 /* DCRTPoly::SetFormat on a host buffer [nbatch][N]; primes[b % nprimes] = prime index of entry b */
 int hx_ntt(hx_ctx* ctx, uint64_t* data, int nbatch, const int* primes, int nprimes, int inverse);

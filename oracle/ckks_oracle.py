@@ -1199,6 +1199,52 @@ def diag_membership_scenario(orc: Oracle, query: Ct, db_cts: List[Ct], ndiag: in
     return orc.eval_sum(orc.add_many(s), orc.P.slots)
 
 
+# ---- approach 4 (HERS), SURVEY.md section 8 row R7 ---------------------------------------------------
+def hers_pack(db: np.ndarray, batch: int) -> np.ndarray:
+    """HersEnroller::serializeDB packing (/root/reference/src/enroller/enroller_hers.cpp:14-36 normalisation,
+    :106-121 serializeDBThread), written as the reference's loops: out[matrix][index][k % batch] =
+    normalize(db)[k][index] for k in [matrix*batch, (matrix+1)*batch)."""
+    n, dim = db.shape
+    dbn = plaintext_normalize(db.astype(np.float64))
+    nmat = int(math.ceil(n / batch))
+    out = np.zeros((nmat, dim, batch))
+    for m in range(nmat):
+        for index in range(dim):
+            for k in range(m * batch, min((m + 1) * batch, n)):
+                out[m, index, k % batch] = dbn[k][index]
+    return out
+
+
+def encrypt_query_hers(orc: Oracle, query: np.ndarray) -> List[Ct]:
+    """HersReceiver::encryptQuery (/root/reference/src/receiver/receiver_hers.cpp:13-24) with encryptQueryThread
+    (:56-61): one ciphertext per coordinate, every slot holding that coordinate of the normalised query."""
+    q = plaintext_normalize(np.asarray(query, dtype=np.float64))
+    return [orc.encrypt(np.full(orc.P.slots, v)) for v in q]
+
+
+def hers_compute_similarity(orc: Oracle, query: List[Ct], db_cts: List[List[Ct]]) -> List[Ct]:
+    """HersSender::computeSimilarity (/root/reference/src/sender/sender_hers.cpp:13-26) with computeSimilarityHelper
+    (:61-84: EvalMultNoRelin, RelinearizeInPlace, RescaleInPlace per column, then the EvalAddInPlace chain);
+    db_cts[m][i] stands for serial/db_hers/matrix{m}/index{i}.bin (:88-98)."""
+    out = []
+    for mat in db_cts:
+        score = [orc.rescale(orc.relinearize(orc.mult_norelin(query[i], mat[i]))) for i in range(len(query))]
+        for i in range(1, len(score)):
+            score[0] = orc.add(score[0], score[i])
+        out.append(score[0])
+    return out
+
+
+def hers_index_scenario(orc: Oracle, query: List[Ct], db_cts: List[List[Ct]]) -> List[Ct]:
+    """HersSender::indexScenario (sender_hers.cpp:29-40)."""
+    return [chebyshev_compare(orc, s, MATCH_THRESHOLD, COMP_DEPTH) for s in hers_compute_similarity(orc, query, db_cts)]
+
+
+def hers_membership_scenario(orc: Oracle, query: List[Ct], db_cts: List[List[Ct]]) -> Ct:
+    """HersSender::membershipScenario (sender_hers.cpp:43-57)."""
+    return orc.eval_sum(orc.add_many(hers_index_scenario(orc, query, db_cts)), orc.P.slots)
+
+
 def decrypt_membership(orc: Oracle, ct: Ct) -> bool:
     """HersReceiver::decryptMembership (/root/reference/src/receiver/receiver_hers.cpp:26-35)."""
     return bool(orc.decrypt(ct)[0] >= 1.0)

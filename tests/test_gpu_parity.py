@@ -224,3 +224,45 @@ def test_fused_pipeline_equals_unfused_kernels(ring):
     assert len(fused) == len(plain)
     for f, p in zip(fused, plain):
         assert np.array_equal(f, p)
+
+
+def test_hers_sender_bit_exact_small_ring():
+    """Row R7: HersSender (approach 4) -- fused score_hers + batched compare vs the oracle's restatement of
+    sender_hers.cpp, on a ragged database spanning two matrices (2048 slots each), 40 coordinates so the
+    32-wide key-switch batches see a full and a partial chunk; and vs the reference-style per-op call sequence."""
+    import image_matching_b200 as hx
+    dim, n = 40, 2500
+    orc = make_oracle(ring_dim=4096, depth=11, rotations=[2 ** i for i in range(11)], seed=7)
+    cc = make_gpu_context(orc)
+    rng = np.random.default_rng(21)
+    db = rng.integers(-99, 100, size=(n, dim)).astype(np.float64)
+    q = rng.integers(1, 4, size=dim).astype(np.float64)
+    c0 = O.plaintext_normalize(db) @ O.plaintext_normalize(q)
+    db[c0 > 0.3] *= -1.0                      # keep every unplanted cosine well below the 0.44 threshold
+    db[3] = q; db[n - 1] = 2 * q
+    packed = O.hers_pack(db, orc.P.slots)
+    assert packed.shape == (2, dim, orc.P.slots)
+    assert np.array_equal(packed, hx.hers_pack(db, orc.P.slots))
+    dbc = [[orc.encrypt(packed[m, j]) for j in range(dim)] for m in range(2)]
+    for m in range(2):
+        for j in range(dim):
+            cc.db_register(m, j, np.stack(dbc[m][j].c))
+    qc = O.encrypt_query_hers(orc, q)
+    gq = [up(cc, c) for c in qc]
+    want = O.hers_compute_similarity(orc, qc, dbc)
+    snd = hx.HersSender(cc, None, n)
+    got = snd.computeSimilarity(gq)
+    assert len(got) == 2 and all(same(g, w) for g, w in zip(got, want))
+    widx = [O.chebyshev_compare(orc, s) for s in want]
+    gidx = snd.indexScenario(gq)
+    assert all(same(g, w) for g, w in zip(gidx, widx))
+    wm = orc.eval_sum(orc.add_many(widx), orc.P.slots)
+    assert same(snd.membershipScenario(gq), wm)
+    assert O.decrypt_index(orc, widx) == [3, n - 1] and O.decrypt_membership(orc, wm)
+    cos = O.plaintext_normalize(db) @ O.plaintext_normalize(q)
+    s = np.concatenate([orc.decrypt(w) for w in want])
+    assert np.abs(s[:n] - cos).max() <= 1e-4
+    # reference-style call sequence on the first matrix
+    gdb = [up(cc, c) for c in dbc[0]]
+    per_op = hx.HersSender(cc, None, orc.P.slots, fused=False, db_loader=lambda m, i: gdb[i]).computeSimilarity(gq)
+    assert len(per_op) == 1 and same(per_op[0], want[0])

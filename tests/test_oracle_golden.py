@@ -111,3 +111,28 @@ def test_hydia_2_10_known_answer(golden_dir):
     assert O.decrypt_index(orc, idx) == [0]
     m = orc.eval_sum(orc.add_many(idx), P.slots)
     assert O.decrypt_membership(orc, m) is True
+
+
+def test_hers_restatement_small_ring():
+    """Row R7 on the CPU oracle: HersSender scores equal the plaintext cosines to 1e-4 (the tolerance of
+    /root/reference/src/main_accuracy.cpp:354-364) and the receiver decisions are the planted matches."""
+    dim, n = 8, 300
+    orc = O.Oracle(O.gen_params(11, ring_dim=4096))
+    orc.keygen(3)
+    orc.mult_keygen()
+    orc.rot_keygen([2 ** i for i in range(11)])
+    rng = np.random.default_rng(4)
+    db = rng.integers(-99, 100, size=(n, dim)).astype(np.float64)
+    q = rng.integers(1, 4, size=dim).astype(np.float64)
+    c0 = O.plaintext_normalize(db) @ O.plaintext_normalize(q)
+    db[c0 > 0.3] *= -1.0                      # keep every unplanted cosine well below the 0.44 threshold
+    db[17] = 3 * q
+    packed = O.hers_pack(db, orc.P.slots)
+    dbc = [[orc.encrypt(packed[m, j]) for j in range(dim)] for m in range(packed.shape[0])]
+    qc = O.encrypt_query_hers(orc, q)
+    scores = O.hers_compute_similarity(orc, qc, dbc)
+    cos = O.plaintext_normalize(db) @ O.plaintext_normalize(q)
+    assert np.abs(orc.decrypt(scores[0])[:n] - cos).max() <= 1e-4
+    idx = O.hers_index_scenario(orc, qc, dbc)
+    assert O.decrypt_index(orc, idx) == [17]
+    assert O.decrypt_membership(orc, orc.eval_sum(orc.add_many(idx), orc.P.slots))

@@ -70,11 +70,38 @@ def hers_pack(db: np.ndarray, batch: int) -> np.ndarray:
     return np.ascontiguousarray(padded.reshape(nmat, batch, dim).transpose(0, 2, 1))
 
 
+def base_pack(db: np.ndarray, batch: int) -> np.ndarray:
+    """BaseEnroller::serializeDB packing (enroller_base.cpp:36-56): [numBatches][batch]; row i = normalised vectors
+    i*(batch/dim) .. (i+1)*(batch/dim)-1, one after the other."""
+    n, dim = db.shape
+    per = batch // dim
+    dbn = plaintext_normalize(db.astype(np.float64))
+    nb = int(math.ceil(n / per))
+    padded = np.zeros((nb * per, dim))
+    padded[:n] = dbn
+    return np.ascontiguousarray(padded.reshape(nb, per * dim))
+
+
+def blind_pack(db: np.ndarray, batch: int, chunk: int) -> np.ndarray:
+    """BlindEnroller::serializeDB packing (enroller_blind.cpp:40-90): [matrices][dim/chunk][batch]; matrix m, chunk c,
+    slots i*chunk..(i+1)*chunk-1 = normalize(db)[m*(batch/chunk) + i][c*chunk:(c+1)*chunk]."""
+    n, dim = db.shape
+    per = batch // chunk
+    dbn = plaintext_normalize(db.astype(np.float64))
+    nmat = int(math.ceil(n / per))
+    padded = np.zeros((nmat * per, dim))
+    padded[:n] = dbn
+    x = padded.reshape(nmat, per, dim // chunk, chunk)           # [m][i][c][k]
+    return np.ascontiguousarray(x.transpose(0, 2, 1, 3).reshape(nmat, dim // chunk, per * chunk))
+
+
 class Client:
     def __init__(self, cc: CryptoContext, seed: int = 1):
         self.cc = cc
         self._lib = _lib.load()
         self._h = check_ptr(self._lib.hx_client_create(cc._h, seed))
+        if getattr(cc, "encoder", None) is None:
+            cc.encoder = self.MakeCKKSPackedPlaintext
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
@@ -86,6 +113,12 @@ class Client:
     def EvalRotateKeyGen(self, rotations: Sequence[int]):
         r = np.array(list(rotations), dtype=np.int32)
         check_int(self._lib.hx_client_gen_rot_keys(self._h, r.ctypes.data_as(I32P), len(r)))
+
+    def MakeCKKSPackedPlaintext(self, values) -> np.ndarray:
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        out = np.empty((self.cc.L, self.cc.N), dtype=np.uint64)
+        check_int(self._lib.hx_client_encode(self._h, v.ctypes.data_as(F64P), len(v), out.ctypes.data_as(_lib.U64P)))
+        return out
 
     def encrypt(self, values) -> Ciphertext:
         v = np.ascontiguousarray(values, dtype=np.float64)
@@ -134,6 +167,27 @@ class Client:
         """HersReceiver::encryptQuery (receiver_hers.cpp:13-24, 56-61): one ciphertext per coordinate, all slots equal."""
         q = plaintext_normalize(np.asarray(query, dtype=np.float64))
         return [self.encrypt(np.full(self.cc.GetBatchSize(), v)) for v in q]
+
+    # ---- Receiver roles for approaches 1 and 3
+    def encryptQueryBase(self, query: np.ndarray) -> List[Ciphertext]:
+        """BaseReceiver::encryptQuery (receiver_base.cpp:13-26): normalise, tile over the slots."""
+        q = plaintext_normalize(np.asarray(query, dtype=np.float64))
+        return [self.encrypt(np.tile(q, self.cc.GetBatchSize() // len(q)))]
+
+    def encryptQueryBlind(self, query: np.ndarray, chunk: int) -> List[Ciphertext]:
+        """BlindReceiver::encryptQuery (receiver_blind.cpp:13-27, 58-70): chunk c of the query tiled over the slots."""
+        q = plaintext_normalize(np.asarray(query, dtype=np.float64))
+        return [self.encrypt(np.tile(q[c:c + chunk], self.cc.GetBatchSize() // chunk)) for c in range(0, len(q), chunk)]
+
+    def decryptIndexBlind(self, cts: List[Ciphertext], chunk: int) -> List[int]:
+        """BlindReceiver::decryptIndex (receiver_blind.cpp:29-54): undo the slot order of compressCiphers."""
+        batch = self.cc.GetBatchSize()
+        per = batch // chunk
+        out = []
+        for i, ct in enumerate(cts):
+            v = self.decrypt(ct)
+            out.extend(int(i * batch + j // chunk + (j % chunk) * per) for j in np.nonzero(v >= 1.0)[0])
+        return out
 
     def decryptMembership(self, ct: Ciphertext) -> bool:
         return bool(self.decrypt(ct)[0] >= 1.0)

@@ -184,6 +184,12 @@ int hx_score_diag(hx_ctx* ctx, hx_ct* query, int ndiag, hx_ct** out, int max_out
 hx_ct* hx_membership(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sign_depth) {
     HX_TRY_PTR(need(ctx, "ctx"); need(query, "query"); return wrap(ctx->eng->membership(query->ct, ndiag, delta, sign_depth));)
 }
+hx_ct* hx_mult_plain(hx_ct* a, const uint64_t* pt, int nlimbs) {
+    HX_TRY_PTR(need(a, "a"); need(pt, "pt"); return wrap(a->ct->eng->mult_plain(a->ct, (const u64*)pt, nlimbs));)
+}
+hx_ct* hx_inner_product(hx_ct* a, hx_ct* b, int n) {
+    HX_TRY_PTR(need(a, "a"); need(b, "b"); return wrap(a->ct->eng->inner_product(a->ct, b->ct, n));)
+}
 int hx_score_hers(hx_ctx* ctx, hx_ct* const* query, int nquery, hx_ct** out, int max_out) {
     try {
         need(ctx, "ctx"); need(query, "query"); need(out, "out");
@@ -250,6 +256,9 @@ int hx_client_gen_mult_key(hx_client* c) { HX_TRY_INT(need(c, "client"); c->cl->
 int hx_client_gen_rot_keys(hx_client* c, const int* rotations, int n) { HX_TRY_INT(need(c, "client"); need(rotations, "rotations"); c->cl->gen_rot_keys(rotations, n);) }
 int hx_client_gen_sum_keys(hx_client* c) { HX_TRY_INT(need(c, "client"); c->cl->gen_sum_keys();) }
 hx_ct* hx_client_encrypt(hx_client* c, const double* values, int n) { HX_TRY_PTR(need(c, "client"); need(values, "values"); return wrap(c->cl->encrypt(values, n));) }
+int hx_client_encode(hx_client* c, const double* values, int n, uint64_t* out) {
+    HX_TRY_INT(need(c, "client"); need(values, "values"); need(out, "out"); c->cl->encode_rns(values, n, (u64*)out);)
+}
 int hx_client_enroll(hx_client* c, int block, int diag, const double* values, int n) {
     HX_TRY_INT(need(c, "client"); need(values, "values"); c->cl->enroll(block, diag, values, n);)
 }

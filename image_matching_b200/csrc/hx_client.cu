@@ -260,6 +260,22 @@ std::vector<long long> Client::encode(const double* values, int n) const {
     return out;
 }
 
+void Client::encode_rns(const double* values, int n, u64* host_out) {
+    std::lock_guard<std::recursive_mutex> g(eng->mu);
+    const int N = eng->N, L = eng->L;
+    std::vector<long long> coeffs = encode(values, n);
+    long long* d_small = (long long*)eng->alloc_words(N);
+    HX_CUDA(cudaMemcpyAsync(d_small, coeffs.data(), sizeof(long long) * N, cudaMemcpyHostToDevice, eng->st));
+    std::vector<int> qs;
+    for (int i = 0; i < L; i++) qs.push_back(i);
+    u64* m = eng->alloc_words((size_t)L * N);
+    k_small_to_rns<<<grid1(N, L), kCT, 0, eng->st>>>(eng->T, m, d_small, eng->limb_map(qs));
+    eng->ntt_limbs(m, L, qs, false);
+    HX_CUDA(cudaMemcpyAsync(host_out, m, sizeof(u64) * (size_t)L * N, cudaMemcpyDeviceToHost, eng->st));
+    HX_CUDA(cudaStreamSynchronize(eng->st));
+    eng->free_words(m); eng->free_words((u64*)d_small);
+}
+
 Ct Client::encrypt(const double* values, int n) {
     std::lock_guard<std::recursive_mutex> g(eng->mu);
     const int N = eng->N, L = eng->L;

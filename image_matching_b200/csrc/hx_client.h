@@ -18,6 +18,7 @@ public:
     void decrypt(const Ct& ct, double* out);      // decryptToVector     (src/openFHE_wrapper.cpp:81)
     void secret(int8_t* out);
     std::vector<long long> encode(const double* values, int n) const;
+    void encode_rns(const double* values, int n, u64* host_out);   // MakeCKKSPackedPlaintext: [L][N], evaluation form
 
     std::shared_ptr<Engine> keep;
     Engine* eng;

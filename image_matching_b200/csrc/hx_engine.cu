@@ -674,6 +674,19 @@ Ct Engine::mult_norelin(const Ct& a_, const Ct& b_) {
     return out;
 }
 Ct Engine::mult(const Ct& a, const Ct& b) { return relinearize(mult_norelin(a, b)); }
+Ct Engine::mult_plain(const Ct& a, const u64* host_pt, int nlimbs) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (nlimbs < a->nl) throw std::runtime_error("EvalMult(ct, Plaintext): plaintext has fewer limbs than the ciphertext");
+    // the plaintext was encoded at level 0; a ciphertext at a lower level uses its first nl limbs (same integer polynomial)
+    u64* pt = alloc_words((size_t)a->nl * N);
+    HX_CUDA(cudaMemcpyAsync(pt, host_pt, sizeof(u64) * (size_t)a->nl * N, cudaMemcpyHostToDevice, st));
+    Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg + 1, a->nb);
+    { Scope sc(this, PK_EW, 1, 8.0 * N * a->nl * (2 * a->comps_total() + 1)); launch_ew(T, EW_MUL, out->d, a->d, pt, a->nl, a->comps_total(), out->comp_stride(), a->comp_stride(), 0, st); }
+    HX_CUDA(cudaStreamSynchronize(st));   // the caller's host buffer may go away
+    free_words(pt);
+    return out;
+}
+Ct Engine::inner_product(const Ct& a, const Ct& b, int n) { return eval_sum(mult(a, b), n); }
 Ct Engine::square(const Ct& a) { return mult(a, a); }
 
 // DropLastElementAndScale (sender_diag.cpp:80).

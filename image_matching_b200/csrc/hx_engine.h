@@ -124,6 +124,9 @@ public:
     Ct relinearize(const Ct& a);                            // RelinearizeInPlace (sender_diag.cpp:79)
     Ct mult(const Ct& a, const Ct& b);                      // EvalMult(ct,ct)
     Ct square(const Ct& a);                                 // EvalSquare
+    // EvalMult(ct, Plaintext) (openFHE_wrapper.cpp:235,244,289): pt = encoded plaintext, host, [nlimbs][N], evaluation form
+    Ct mult_plain(const Ct& a, const u64* host_pt, int nlimbs);
+    Ct inner_product(const Ct& a, const Ct& b, int n);      // EvalInnerProduct (sender_base.cpp:93) = EvalSum(EvalMult(a,b), n)
     Ct rescale(const Ct& a);                                // RescaleInPlace / ModReduceInPlace (sender_diag.cpp:80)
     Ct level_reduce(const Ct& a, int levels);               // LevelReduceInPlace
     Ct rotate(const Ct& a, int r);                          // EvalRotate (openFHE_wrapper.cpp:124)

@@ -148,6 +148,9 @@ class CryptoContext:
     def EvalMult(self, a, b):
         if isinstance(b, (int, float)):
             return self._ct(self._lib.hx_mult_const(a._h, float(b)))
+        if isinstance(b, np.ndarray):   # Plaintext = encoded limbs [nlimbs][N] (MakeCKKSPackedPlaintext)
+            pt = np.ascontiguousarray(b, dtype=np.uint64)
+            return self._ct(self._lib.hx_mult_plain(a._h, _u64p(pt), pt.shape[0]))
         return self._ct(self._lib.hx_mult(a._h, b._h))
     def EvalMultNoRelin(self, a, b): return self._ct(self._lib.hx_mult_norelin(a._h, b._h))
     def Relinearize(self, a): return self._ct(self._lib.hx_relin(a._h))
@@ -158,6 +161,13 @@ class CryptoContext:
     def LevelReduce(self, a, levels=1): return self._ct(self._lib.hx_level_reduce(a._h, levels))
     def EvalRotate(self, a, index): return self._ct(self._lib.hx_rotate(a._h, index))
     def EvalSum(self, a, n): return self._ct(self._lib.hx_eval_sum(a._h, n))
+    def EvalInnerProduct(self, a, b, n): return self._ct(self._lib.hx_inner_product(a._h, b._h, n))
+    def MakeCKKSPackedPlaintext(self, values) -> np.ndarray:
+        """Encoded plaintext [L][N] (evaluation form). Encoding is client-side work: `encoder` is set by Client (or by a test
+        to the oracle's encoder so both sides multiply by the same polynomial)."""
+        if getattr(self, "encoder", None) is None:
+            raise RuntimeError("MakeCKKSPackedPlaintext: no encoder attached (create a Client or set cc.encoder)")
+        return self.encoder(values)
     def EvalAddMany(self, cts: List[Ciphertext]):
         arr = (VP * len(cts))(*[c._h for c in cts])
         return self._ct(self._lib.hx_add_many(arr, len(cts)))

@@ -63,3 +63,80 @@ def binaryRotate(cc: CryptoContext, ctxt: Ciphertext, factor: int) -> Ciphertext
     for r in needed:
         ctxt = cc.EvalRotate(ctxt, r)
     return ctxt
+
+
+def generateMergeMask(cc: CryptoContext, dimension: int, segmentLength: int):
+    """OpenFHEWrapper::generateMergeMask (openFHE_wrapper.cpp:253-271): segments of ones every dimension*segmentLength slots."""
+    batch = cc.GetBatchSize()
+    mask = [0.0] * batch
+    if segmentLength > batch // dimension:
+        print("Mask generation index error", file=sys.stderr)
+        return cc.MakeCKKSPackedPlaintext(mask)
+    i = 0
+    while i < batch:
+        for k in range(i, min(batch, i + segmentLength)):
+            mask[k] = 1.0
+        i += dimension * segmentLength
+    return cc.MakeCKKSPackedPlaintext(mask)
+
+
+def mergeSingleCipher(cc: CryptoContext, ctxt: Ciphertext, dimension: int) -> Ciphertext:
+    """OpenFHEWrapper::mergeSingleCipher (openFHE_wrapper.cpp:221-249): packs every dimension-th slot to the front."""
+    batch = cc.GetBatchSize()
+    outputSize = batch // dimension
+    paddingSize = 1
+    rotationFactor = dimension - 1
+    i = 1
+    while i < outputSize:
+        if i >= paddingSize:
+            ctxt = cc.EvalMult(ctxt, generateMergeMask(cc, dimension, i))
+            ctxt = cc.RelinearizeInPlace(ctxt)
+            ctxt = cc.RescaleInPlace(ctxt)
+            paddingSize = i * dimension
+        ctxt = cc.EvalAddInPlace(ctxt, binaryRotate(cc, ctxt, rotationFactor * i))
+        i *= 2
+    ctxt = cc.EvalMult(ctxt, generateMergeMask(cc, dimension, outputSize))
+    ctxt = cc.RelinearizeInPlace(ctxt)
+    return cc.RescaleInPlace(ctxt)
+
+
+def mergeCiphers(cc: CryptoContext, ctxts: List[Ciphertext], dimension: int) -> List[Ciphertext]:
+    """OpenFHEWrapper::mergeCiphers (openFHE_wrapper.cpp:189-217)."""
+    batch = cc.GetBatchSize()
+    elementsPerCipher = batch // dimension
+    outputSize = elementsPerCipher * len(ctxts)
+    neededCiphers = int(math.ceil(float(outputSize) / float(batch)))
+    ctxts = [mergeSingleCipher(cc, c, dimension) for c in ctxts]
+    merged: List[Ciphertext] = [None] * neededCiphers
+    for i, c in enumerate(ctxts):
+        outputCipher = (elementsPerCipher * i) // batch
+        outputSlot = (elementsPerCipher * i) % batch
+        if outputSlot == 0:
+            merged[outputCipher] = c
+        else:
+            merged[outputCipher] = cc.EvalAddInPlace(merged[outputCipher], binaryRotate(cc, c, -outputSlot))
+    return merged
+
+
+def compressCiphers(cc: CryptoContext, ctxts: List[Ciphertext], dimension: int) -> List[Ciphertext]:
+    """OpenFHEWrapper::compressCiphers (openFHE_wrapper.cpp:273-312): keeps the dimension-th slots, not in order."""
+    batch = cc.GetBatchSize()
+    ciphersNeeded = int(math.ceil(float(len(ctxts)) / float(dimension)))
+    maskVec = [0.0] * batch
+    for i in range(0, batch, dimension):
+        maskVec[i] = 1.0
+    maskPtxt = cc.MakeCKKSPackedPlaintext(maskVec)
+    out = []
+    for c in ctxts:
+        c = cc.EvalMult(c, maskPtxt)
+        c = cc.RelinearizeInPlace(c)
+        out.append(cc.RescaleInPlace(c))
+    compressed: List[Ciphertext] = [None] * ciphersNeeded
+    for i, c in enumerate(out):
+        rotFactor = -(i % dimension)
+        outputSlot = i // dimension
+        if rotFactor == 0:
+            compressed[outputSlot] = c
+        else:
+            compressed[outputSlot] = cc.EvalAddInPlace(compressed[outputSlot], binaryRotate(cc, c, rotFactor))
+    return compressed

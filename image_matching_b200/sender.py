@@ -129,3 +129,63 @@ class HersSender(Sender):
         cc = self.cc
         m = cc.EvalAddManyInPlace(self._compare(self.computeSimilarity(queryCipher)))
         return cc.EvalSum(m, cc.GetBatchSize())
+
+
+class BaseSender(HersSender):
+    """sender_base.cpp (approach 1, literature baseline). queryCipher[0] = the normalised
+    query tiled over the slots (BaseReceiver::encryptQuery); database ciphertext i = serial/db_baseline/batch{i}.bin =
+    batch/dim consecutive vectors (`db_loader(i)`). Per database ciphertext: EvalInnerProduct(q, db, dim), Relinearize,
+    Rescale; then OpenFHEWrapper::mergeCiphers packs the scores. `dim` is VECTOR_DIM in the reference."""
+
+    def __init__(self, cc: CryptoContext, pk, numVectors: int, db_loader: Callable[[int], Ciphertext], dim: int = VECTOR_DIM):
+        super().__init__(cc, pk, numVectors, fused=True)
+        self.db_loader, self.dim = db_loader, dim
+
+    def computeSimilarity(self, queryCipher):
+        cc = self.cc
+        vectorsPerBatch = cc.GetBatchSize() // self.dim
+        numBatches = int(math.ceil(float(self.numVectors) / float(vectorsPerBatch)))
+        similarity = [self.computeSimilarityThread(queryCipher[0], i) for i in range(numBatches)]
+        return OpenFHEWrapper.mergeCiphers(cc, similarity, self.dim)
+
+    def computeSimilarityThread(self, queryCipher: Ciphertext, databaseIndex: int) -> Ciphertext:
+        cc = self.cc
+        s = cc.EvalInnerProduct(queryCipher, self.db_loader(databaseIndex), self.dim)
+        s = cc.RelinearizeInPlace(s)
+        return cc.RescaleInPlace(s)
+
+
+class BlindSender(HersSender):
+    """sender_blind.cpp (approach 3, Blind-Match). queryCipher[i] = chunk i of the query tiled
+    over the slots (BlindReceiver::encryptQuery); database ciphertext (matrix m, chunk offset j) =
+    serial/db_blind/matrix{m}/batch{j}.bin (`db_loader(m, j)`). `dim` / `chunk` are VECTOR_DIM / CHUNK_LEN in the reference."""
+
+    def __init__(self, cc: CryptoContext, pk, numVectors: int, db_loader: Callable[[int, int], Ciphertext],
+                 dim: int = VECTOR_DIM, chunk: int = 0):
+        super().__init__(cc, pk, numVectors, fused=True)
+        from .config import CHUNK_LEN
+        self.db_loader, self.dim, self.chunk = db_loader, dim, chunk or CHUNK_LEN
+
+    def computeSimilarity(self, queryCipher):
+        cc = self.cc
+        chunksPerBatch = cc.GetBatchSize() // self.chunk
+        numMatrices = int(math.ceil(float(self.numVectors) / float(chunksPerBatch)))
+        score = [self.computeSimilarityMatrix(queryCipher, self.chunk, i) for i in range(numMatrices)]
+        return OpenFHEWrapper.compressCiphers(cc, score, self.chunk)
+
+    def computeSimilarityMatrix(self, queryCipher, chunkLength: int, matrix: int) -> Ciphertext:
+        cc = self.cc
+        chunksPerVector = self.dim // chunkLength
+        m = [self.computeSimilaritySerial(queryCipher[i], matrix, i * chunkLength) for i in range(chunksPerVector)]
+        for i in range(1, chunksPerVector):
+            m[0] = cc.EvalAddInPlace(m[0], m[i])
+        m[0] = cc.RelinearizeInPlace(m[0])
+        m[0] = cc.RescaleInPlace(m[0])
+        r = 1
+        while r < chunkLength:
+            m[0] = cc.EvalAddInPlace(m[0], OpenFHEWrapper.binaryRotate(cc, m[0], r))
+            r *= 2
+        return m[0]
+
+    def computeSimilaritySerial(self, queryCipher: Ciphertext, matrix: int, index: int) -> Ciphertext:
+        return self.cc.EvalMultNoRelin(queryCipher, self.db_loader(matrix, index))

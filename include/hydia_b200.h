@@ -84,6 +84,10 @@ hx_ct* hx_mult_norelin(hx_ct* a, hx_ct* b);         /* EvalMultNoRelin          
 hx_ct* hx_relin(hx_ct* a);                          /* RelinearizeInPlace         sender_diag.cpp:79 */
 hx_ct* hx_mult(hx_ct* a, hx_ct* b);                 /* EvalMult(ct,ct)            sender_hers.cpp:156 */
 hx_ct* hx_square(hx_ct* a);                         /* EvalSquare(InPlace)        sender_hers.cpp:124 */
+/* EvalMult(ct, Plaintext) (openFHE_wrapper.cpp:235,244,289; sender_hers.cpp:110): pt = the encoded plaintext of
+ * MakeCKKSPackedPlaintext, [nlimbs][N] evaluation form, nlimbs >= limbs of a (the first ones are used). */
+hx_ct* hx_mult_plain(hx_ct* a, const uint64_t* pt, int nlimbs);
+hx_ct* hx_inner_product(hx_ct* a, hx_ct* b, int n); /* EvalInnerProduct           sender_base.cpp:93  */
 hx_ct* hx_rescale(hx_ct* a);                        /* RescaleInPlace             sender_diag.cpp:80 */
 hx_ct* hx_level_reduce(hx_ct* a, int levels);       /* LevelReduceInPlace                            */
 hx_ct* hx_rotate(hx_ct* a, int rotation);           /* EvalRotate                 openFHE_wrapper.cpp:124 */
@@ -137,6 +141,8 @@ int hx_client_gen_rot_keys(hx_client* c, const int* rotations, int n);      /* E
 int hx_client_gen_sum_keys(hx_client* c);                                   /* EvalSumKeyGen  */
 /* MakeCKKSPackedPlaintext + Encrypt (openFHE_wrapper.cpp:74-77); values: up to N/2 reals */
 hx_ct* hx_client_encrypt(hx_client* c, const double* values, int n);
+/* MakeCKKSPackedPlaintext (openFHE_wrapper.cpp:75, :257-271 masks): out = [L][N] residues, evaluation form */
+int hx_client_encode(hx_client* c, const double* values, int n, uint64_t* out);
 /* Encrypt + register as database ciphertext (DiagonalEnroller::serializeDBThread, enroller_diag.cpp:158) */
 int hx_client_enroll(hx_client* c, int block, int diag, const double* values, int n);
 /* Decrypt + GetRealPackedValue (openFHE_wrapper.cpp:81-85); out: N/2 doubles */

@@ -670,6 +670,17 @@ class Oracle:
         """cc->EvalMult(ct, ct): EvalMultCore + relinearisation, no rescale."""
         return self.relinearize(self.mult_norelin(a, b))
 
+    def mult_plain(self, ct: Ct, pt: np.ndarray) -> Ct:
+        """EvalMult(ct, Plaintext) (openFHE_wrapper.cpp:235,244,289): pt = encode() output at level 0; a ciphertext at a
+        lower level uses the plaintext's first nl limbs (LevelReduce of the plaintext); noiseScaleDeg adds up."""
+        nl = ct.nl
+        mods = self.qmods(nl)
+        return Ct([self.pmul(c, np.ascontiguousarray(pt[:nl]), mods) for c in ct.c], ct.level, ct.deg + 1)
+
+    def inner_product(self, a: Ct, b: Ct, n: int) -> Ct:
+        """EvalInnerProduct (sender_base.cpp:93): EvalSum(EvalMult(a, b), n) (upstream base-advancedshe.cpp)."""
+        return self.eval_sum(self.mult(a, b), n)
+
     def square(self, a: Ct) -> Ct:
         """cc->EvalSquare: same residues as EvalMult(a, a)."""
         return self.mult(a, a)
@@ -1243,6 +1254,165 @@ def hers_index_scenario(orc: Oracle, query: List[Ct], db_cts: List[List[Ct]]) ->
 def hers_membership_scenario(orc: Oracle, query: List[Ct], db_cts: List[List[Ct]]) -> Ct:
     """HersSender::membershipScenario (sender_hers.cpp:43-57)."""
     return orc.eval_sum(orc.add_many(hers_index_scenario(orc, query, db_cts)), orc.P.slots)
+
+
+# ---- OpenFHEWrapper helpers used by approaches 1 and 3 (SURVEY.md section 8 rows R8-R10) ---------------------
+def binary_rotate(orc: Oracle, ct: Ct, factor: int) -> Ct:
+    """OpenFHEWrapper::binaryRotate (/root/reference/src/openFHE_wrapper.cpp:103-128)."""
+    batch = orc.P.slots
+    needed = []
+    while factor != 0:
+        sign = factor // abs(factor)
+        counter = int(pow(2, round(math.log2(abs(factor)))))
+        cur = int(math.fmod(counter * sign, batch))
+        if cur != 0:
+            needed.append(counter * sign)
+        factor -= counter * sign
+    for r in needed:
+        ct = orc.rotate(ct, r)
+    return ct
+
+
+def generate_merge_mask(orc: Oracle, dimension: int, segment: int) -> np.ndarray:
+    """OpenFHEWrapper::generateMergeMask (openFHE_wrapper.cpp:253-271)."""
+    batch = orc.P.slots
+    mask = np.zeros(batch)
+    if segment > batch // dimension:
+        return orc.encode(mask)
+    i = 0
+    while i < batch:
+        mask[i:i + segment] = 1.0
+        i += dimension * segment
+    return orc.encode(mask)
+
+
+def merge_single_cipher(orc: Oracle, ct: Ct, dimension: int) -> Ct:
+    """OpenFHEWrapper::mergeSingleCipher (openFHE_wrapper.cpp:221-249)."""
+    output_size = orc.P.slots // dimension
+    padding, rot = 1, dimension - 1
+    i = 1
+    while i < output_size:
+        if i >= padding:
+            ct = orc.rescale(orc.relinearize(orc.mult_plain(ct, generate_merge_mask(orc, dimension, i))))
+            padding = i * dimension
+        ct = orc.add(ct, binary_rotate(orc, ct, rot * i))
+        i *= 2
+    return orc.rescale(orc.relinearize(orc.mult_plain(ct, generate_merge_mask(orc, dimension, output_size))))
+
+
+def merge_ciphers(orc: Oracle, cts: List[Ct], dimension: int) -> List[Ct]:
+    """OpenFHEWrapper::mergeCiphers (openFHE_wrapper.cpp:189-217)."""
+    batch = orc.P.slots
+    per = batch // dimension
+    needed = int(math.ceil(per * len(cts) / batch))
+    cts = [merge_single_cipher(orc, c, dimension) for c in cts]
+    merged: List[Optional[Ct]] = [None] * needed
+    for i, c in enumerate(cts):
+        oc, slot = (per * i) // batch, (per * i) % batch
+        merged[oc] = c if slot == 0 else orc.add(merged[oc], binary_rotate(orc, c, -slot))
+    return merged
+
+
+def compress_ciphers(orc: Oracle, cts: List[Ct], dimension: int) -> List[Ct]:
+    """OpenFHEWrapper::compressCiphers (openFHE_wrapper.cpp:273-312)."""
+    batch = orc.P.slots
+    needed = int(math.ceil(len(cts) / dimension))
+    mask = np.zeros(batch)
+    mask[::dimension] = 1.0
+    pt = orc.encode(mask)
+    cts = [orc.rescale(orc.relinearize(orc.mult_plain(c, pt))) for c in cts]
+    out: List[Optional[Ct]] = [None] * needed
+    for i, c in enumerate(cts):
+        rot, slot = -(i % dimension), i // dimension
+        out[slot] = c if rot == 0 else orc.add(out[slot], binary_rotate(orc, c, rot))
+    return out
+
+
+# ---- approach 1 (literature baseline), row R9 ----------------------------------------------------------
+def base_pack(db: np.ndarray, batch: int) -> np.ndarray:
+    """BaseEnroller::serializeDB packing (/root/reference/src/enroller/enroller_base.cpp:36-56), as the reference's loops."""
+    n, dim = db.shape
+    per = batch // dim
+    dbn = plaintext_normalize(db.astype(np.float64))
+    nb = int(math.ceil(n / per))
+    out = np.zeros((nb, batch))
+    for i in range(nb):
+        for j in range(min(per, n - i * per)):
+            out[i, j * dim:(j + 1) * dim] = dbn[j + i * per]
+    return out
+
+
+def encrypt_query_base(orc: Oracle, query: np.ndarray) -> List[Ct]:
+    """BaseReceiver::encryptQuery (/root/reference/src/receiver/receiver_base.cpp:13-26)."""
+    q = plaintext_normalize(np.asarray(query, dtype=np.float64))
+    batch = np.zeros(orc.P.slots)
+    for i in range(0, orc.P.slots, len(q)):
+        batch[i:i + len(q)] = q
+    return [orc.encrypt(batch)]
+
+
+def base_compute_similarity(orc: Oracle, query: List[Ct], db_cts: List[Ct], dim: int = VECTOR_DIM) -> List[Ct]:
+    """BaseSender::computeSimilarity (/root/reference/src/sender/sender_base.cpp:13-27) with computeSimilarityThread
+    (:84-98: EvalInnerProduct, RelinearizeInPlace, RescaleInPlace) and OpenFHEWrapper::mergeCiphers."""
+    sim = [orc.rescale(orc.relinearize(orc.inner_product(query[0], d, dim))) for d in db_cts]
+    return merge_ciphers(orc, sim, dim)
+
+
+# ---- approach 3 (Blind-Match), row R8 --------------------------------------------------------------------
+def blind_pack(db: np.ndarray, batch: int, chunk: int) -> np.ndarray:
+    """BlindEnroller::serializeDB packing (/root/reference/src/enroller/enroller_blind.cpp:40-90), as the reference's loops:
+    out[matrix][index/chunk][i*chunk : (i+1)*chunk] = normalize(db)[i + matrix*chunksPerBatch][index : index+chunk]."""
+    n, dim = db.shape
+    per = batch // chunk
+    dbn = plaintext_normalize(db.astype(np.float64))
+    nmat = int(math.ceil(n / per))
+    out = np.zeros((nmat, dim // chunk, batch))
+    for m in range(nmat):
+        remaining = n - m * per
+        for index in range(0, dim, chunk):
+            for i in range(min(per, remaining)):
+                out[m, index // chunk, i * chunk:(i + 1) * chunk] = dbn[i + m * per][index:index + chunk]
+    return out
+
+
+def encrypt_query_blind(orc: Oracle, query: np.ndarray, chunk: int) -> List[Ct]:
+    """BlindReceiver::encryptQuery (/root/reference/src/receiver/receiver_blind.cpp:13-27) with encryptQueryThread (:58-70)."""
+    q = plaintext_normalize(np.asarray(query, dtype=np.float64))
+    out = []
+    for index in range(0, len(q), chunk):
+        v = np.zeros(orc.P.slots)
+        for i in range(0, orc.P.slots, chunk):
+            v[i:i + chunk] = q[index:index + chunk]
+        out.append(orc.encrypt(v))
+    return out
+
+
+def blind_compute_similarity(orc: Oracle, query: List[Ct], db_cts: List[List[Ct]], chunk: int) -> List[Ct]:
+    """BlindSender::computeSimilarity (/root/reference/src/sender/sender_blind.cpp:43-57) with computeSimilarityMatrix
+    (:59-83) and computeSimilaritySerial (:85-94); db_cts[m][c] stands for serial/db_blind/matrix{m}/batch{c*chunk}.bin."""
+    scores = []
+    for mat in db_cts:
+        m = [orc.mult_norelin(query[i], mat[i]) for i in range(len(query))]
+        for i in range(1, len(m)):
+            m[0] = orc.add(m[0], m[i])
+        acc = orc.rescale(orc.relinearize(m[0]))
+        r = 1
+        while r < chunk:
+            acc = orc.add(acc, binary_rotate(orc, acc, r))
+            r *= 2
+        scores.append(acc)
+    return compress_ciphers(orc, scores, chunk)
+
+
+def blind_decrypt_index(orc: Oracle, cts: List[Ct], chunk: int) -> List[int]:
+    """BlindReceiver::decryptIndex (receiver_blind.cpp:29-54)."""
+    batch = orc.P.slots
+    per = batch // chunk
+    out = []
+    for i, ct in enumerate(cts):
+        v = orc.decrypt(ct)
+        out.extend(int(i * batch + j // chunk + (j % chunk) * per) for j in np.nonzero(v >= 1.0)[0])
+    return out
 
 
 def decrypt_membership(orc: Oracle, ct: Ct) -> bool:

@@ -266,3 +266,90 @@ def test_hers_sender_bit_exact_small_ring():
     gdb = [up(cc, c) for c in dbc[0]]
     per_op = hx.HersSender(cc, None, orc.P.slots, fused=False, db_loader=lambda m, i: gdb[i]).computeSimilarity(gq)
     assert len(per_op) == 1 and same(per_op[0], want[0])
+
+
+def _pm_pow2(slots):
+    return [s * (1 << k) for k in range(int(np.log2(slots))) for s in (1, -1)]
+
+
+def test_base_sender_bit_exact_small_ring():
+    """Row R9 (+R10): BaseSender (approach 1) through the per-op C ABI -- EvalInnerProduct, EvalMult(ct, Plaintext) masks,
+    binaryRotate, mergeCiphers -- bit-exact vs the oracle's restatement, then compare + decisions."""
+    import image_matching_b200 as hx
+    dim, n = 64, 80
+    orc = make_oracle(ring_dim=4096, depth=13, rotations=_pm_pow2(2048), seed=5)
+    cc = make_gpu_context(orc)
+    cc.encoder = orc.encode                    # both sides multiply by the same encoded masks
+    rng = np.random.default_rng(6)
+    db = rng.integers(-99, 100, size=(n, dim)).astype(np.float64)
+    q = rng.integers(1, 4, size=dim).astype(np.float64)
+    c0 = O.plaintext_normalize(db) @ O.plaintext_normalize(q)
+    db[c0 > 0.3] *= -1.0
+    db[41] = 2 * q
+    packed = O.base_pack(db, orc.P.slots)
+    assert np.array_equal(packed, hx.base_pack(db, orc.P.slots))
+    dbc = [orc.encrypt(r) for r in packed]
+    gdb = [up(cc, c) for c in dbc]
+    qc = O.encrypt_query_base(orc, q)
+    gq = [up(cc, qc[0])]
+    want = O.base_compute_similarity(orc, qc, dbc, dim)
+    snd = hx.BaseSender(cc, None, n, db_loader=lambda i: gdb[i], dim=dim)
+    got = snd.computeSimilarity(gq)
+    assert len(got) == len(want) == 1 and same(got[0], want[0])
+    widx = [O.chebyshev_compare(orc, w) for w in want]
+    gidx = snd.indexScenario(gq)
+    assert all(same(g, w) for g, w in zip(gidx, widx))
+    assert O.decrypt_index(orc, widx) == [41]
+    assert same(snd.membershipScenario(gq), orc.eval_sum(orc.add_many(widx), orc.P.slots))
+
+
+def test_blind_sender_bit_exact_small_ring():
+    """Row R8: BlindSender (approach 3) -- chunked EvalMultNoRelin, rotate-and-sum, compressCiphers -- bit-exact vs the oracle."""
+    import image_matching_b200 as hx
+    dim, chunk, n = 64, 16, 200
+    orc = make_oracle(ring_dim=4096, depth=12, rotations=_pm_pow2(2048), seed=8)
+    cc = make_gpu_context(orc)
+    cc.encoder = orc.encode
+    rng = np.random.default_rng(9)
+    db = rng.integers(-99, 100, size=(n, dim)).astype(np.float64)
+    q = rng.integers(1, 4, size=dim).astype(np.float64)
+    c0 = O.plaintext_normalize(db) @ O.plaintext_normalize(q)
+    db[c0 > 0.3] *= -1.0
+    db[5] = q; db[150] = 3 * q
+    packed = O.blind_pack(db, orc.P.slots, chunk)
+    assert np.array_equal(packed, hx.blind_pack(db, orc.P.slots, chunk))
+    dbc = [[orc.encrypt(packed[m, c]) for c in range(packed.shape[1])] for m in range(packed.shape[0])]
+    gdb = [[up(cc, c) for c in row] for row in dbc]
+    qc = O.encrypt_query_blind(orc, q, chunk)
+    gq = [up(cc, c) for c in qc]
+    want = O.blind_compute_similarity(orc, qc, dbc, chunk)
+    snd = hx.BlindSender(cc, None, n, db_loader=lambda m, j: gdb[m][j // chunk], dim=dim, chunk=chunk)
+    got = snd.computeSimilarity(gq)
+    assert len(got) == len(want) == 1 and same(got[0], want[0])
+    widx = [O.chebyshev_compare(orc, w) for w in want]
+    assert all(same(g, w) for g, w in zip(snd.indexScenario(gq), widx))
+    assert sorted(O.blind_decrypt_index(orc, widx, chunk)) == [5, 150]
+
+
+def test_client_masks_and_roles_for_approaches_1_and_3():
+    """The product's own client (hx_client_encode = MakeCKKSPackedPlaintext, encryptQueryBase/Blind, decryptIndexBlind):
+    BaseSender and BlindSender end to end on the product's keys, decisions checked against the planted matches."""
+    import image_matching_b200 as hx
+    dim, chunk, n = 64, 16, 200
+    cc = hx.CryptoContext.generate(depth=13, ring_dim=4096)
+    cl = hx.Client(cc, seed=3)
+    cl.EvalMultKeyGen(); cl.EvalRotateKeyGen(_pm_pow2(cc.GetBatchSize()))
+    rng = np.random.default_rng(2)
+    db = rng.integers(-99, 100, size=(n, dim)).astype(np.float64)
+    q = rng.integers(1, 4, size=dim).astype(np.float64)
+    c0 = hx.plaintext_normalize(db) @ hx.plaintext_normalize(q)
+    db[c0 > 0.3] *= -1.0
+    db[7] = q; db[199] = 2 * q
+    bdb = [cl.encrypt(r) for r in hx.base_pack(db, cc.GetBatchSize())]
+    base = hx.BaseSender(cc, None, n, db_loader=lambda i: bdb[i], dim=dim)
+    assert cl.decryptIndex(base.indexScenario(cl.encryptQueryBase(q))) == [7, 199]
+    pk = hx.blind_pack(db, cc.GetBatchSize(), chunk)
+    kdb = [[cl.encrypt(pk[m, c]) for c in range(pk.shape[1])] for m in range(pk.shape[0])]
+    blind = hx.BlindSender(cc, None, n, db_loader=lambda m, j: kdb[m][j // chunk], dim=dim, chunk=chunk)
+    assert sorted(cl.decryptIndexBlind(blind.indexScenario(cl.encryptQueryBlind(q, chunk)), chunk)) == [7, 199]
+    assert cl.decryptMembership(blind.membershipScenario(cl.encryptQueryBlind(q, chunk)))

@@ -136,3 +136,62 @@ def test_hers_restatement_small_ring():
     idx = O.hers_index_scenario(orc, qc, dbc)
     assert O.decrypt_index(orc, idx) == [17]
     assert O.decrypt_membership(orc, orc.eval_sum(orc.add_many(idx), orc.P.slots))
+
+
+def _pm_pow2_rotations(slots):
+    return [s * (1 << k) for k in range(int(np.log2(slots))) for s in (1, -1)]
+
+
+def test_base_restatement_small_ring():
+    """Row R9 on the CPU oracle: BaseSender (EvalInnerProduct + mergeCiphers) gives the plaintext cosines, packed
+    consecutively, to 1e-4; index decisions are the planted matches."""
+    dim, n = 64, 80
+    orc = O.Oracle(O.gen_params(13, ring_dim=4096))
+    orc.keygen(5)
+    orc.mult_keygen()
+    orc.rot_keygen(_pm_pow2_rotations(orc.P.slots))
+    rng = np.random.default_rng(6)
+    db = rng.integers(-99, 100, size=(n, dim)).astype(np.float64)
+    q = rng.integers(1, 4, size=dim).astype(np.float64)
+    c0 = O.plaintext_normalize(db) @ O.plaintext_normalize(q)
+    db[c0 > 0.3] *= -1.0
+    db[41] = 2 * q
+    dbc = [orc.encrypt(r) for r in O.base_pack(db, orc.P.slots)]
+    assert len(dbc) == 3
+    qc = O.encrypt_query_base(orc, q)
+    merged = O.base_compute_similarity(orc, qc, dbc, dim)
+    assert len(merged) == 1
+    cos = O.plaintext_normalize(db) @ O.plaintext_normalize(q)
+    assert np.abs(orc.decrypt(merged[0])[:n] - cos).max() <= 1e-4
+    idx = [O.chebyshev_compare(orc, m) for m in merged]
+    assert O.decrypt_index(orc, idx) == [41]
+
+
+def test_blind_restatement_small_ring():
+    """Row R8 on the CPU oracle: BlindSender (chunked products, rotate-and-sum, compressCiphers) + BlindReceiver::decryptIndex."""
+    dim, chunk, n = 64, 16, 200
+    orc = O.Oracle(O.gen_params(12, ring_dim=4096))
+    orc.keygen(8)
+    orc.mult_keygen()
+    orc.rot_keygen(_pm_pow2_rotations(orc.P.slots))
+    rng = np.random.default_rng(9)
+    db = rng.integers(-99, 100, size=(n, dim)).astype(np.float64)
+    q = rng.integers(1, 4, size=dim).astype(np.float64)
+    c0 = O.plaintext_normalize(db) @ O.plaintext_normalize(q)
+    db[c0 > 0.3] *= -1.0
+    db[5] = q; db[150] = 3 * q
+    packed = O.blind_pack(db, orc.P.slots, chunk)
+    assert packed.shape == (2, 4, orc.P.slots)
+    dbc = [[orc.encrypt(packed[m, c]) for c in range(packed.shape[1])] for m in range(packed.shape[0])]
+    qc = O.encrypt_query_blind(orc, q, chunk)
+    comp = O.blind_compute_similarity(orc, qc, dbc, chunk)
+    assert len(comp) == 1
+    # slot j of the compressed cipher holds the score of vector j // chunk + (j % chunk) * (slots // chunk)
+    cos = O.plaintext_normalize(db) @ O.plaintext_normalize(q)
+    dec = orc.decrypt(comp[0])
+    per = orc.P.slots // chunk
+    for v in (5, 150, 17):
+        m, i = divmod(v, per)
+        assert abs(dec[i * chunk + m] - cos[v]) <= 1e-4
+    idx = [O.chebyshev_compare(orc, c) for c in comp]
+    assert sorted(O.blind_decrypt_index(orc, idx, chunk)) == [5, 150]

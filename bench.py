@@ -22,6 +22,18 @@ if ROOT not in sys.path:
 
 METRIC = "encrypted_match_latency_membership_plus_index"
 UNIT = "s"
+# BASELINE.md "HyDia, approach 5": published Sender compute seconds (membership, index) per DB size on a 48-thread
+# Xeon Gold 5412U (tools/figures/approach5.csv) -- other hardware, not re-measured; vs_baseline = value / (m + i)
+PUBLISHED_APPROACH5 = {1 << 14: (4.518783, 4.175511), 1 << 15: (6.155975, 5.85484), 1 << 16: (9.560245, 9.011757),
+                       1 << 17: (16.00675, 15.46935), 1 << 18: (28.72538, 27.62988), 1 << 19: (53.24866, 49.70151),
+                       1 << 20: (102.411, 96.52172)}
+
+
+def vs_published(args, seconds):
+    if args.ring_dim or args.ndiag != 512:
+        return None
+    pub = PUBLISHED_APPROACH5.get(args.blocks_per_gpu * args.gpus * 16384)
+    return seconds / sum(pub) if pub else None
 
 
 def parse():
@@ -142,7 +154,7 @@ def run_reference(args):
             args.warmup = 1   # one untimed pass is enough to page the library in; keeps the run to minutes
     v = float(np.mean(vals))
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": len(vals),
-            "warmup": args.warmup, "ms_per_step": v * 1e3, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
+            "warmup": args.warmup, "ms_per_step": v * 1e3, "higher_is_better": False, "scaling": "weak", "vs_baseline": vs_published(args, v),
             "dtype": "u64", "data": "synthetic", "config": workload_config(args),
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
@@ -326,7 +338,7 @@ def run_b200(args):
         sec = ms_total / args.steps / 1e3
         sec_e2e = ms_e2e / args.steps / 1e3
         line = {"metric": METRIC, "value": sec, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": sec * 1e3, "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
+                "ms_per_step": sec * 1e3, "higher_is_better": False, "scaling": "weak", "vs_baseline": vs_published(args, sec), "dtype": "u64",
                 "data": "synthetic", "config": workload_config(args),
                 "e2e": {"value": sec_e2e, "unit": UNIT, "h2d_bytes_per_step": ct_words * 8,
                         "d2h_bytes_per_step": (total_blocks + 1) * res_words * 8},

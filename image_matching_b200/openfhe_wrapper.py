@@ -68,6 +68,9 @@ def binaryRotate(cc: CryptoContext, ctxt: Ciphertext, factor: int) -> Ciphertext
 def generateMergeMask(cc: CryptoContext, dimension: int, segmentLength: int):
     """OpenFHEWrapper::generateMergeMask (openFHE_wrapper.cpp:253-271): segments of ones every dimension*segmentLength slots."""
     batch = cc.GetBatchSize()
+    cache = cc.__dict__.setdefault("_merge_masks", {})      # the same (dimension, segment) always encodes to the same plaintext
+    if (dimension, segmentLength) in cache:
+        return cache[(dimension, segmentLength)]
     mask = [0.0] * batch
     if segmentLength > batch // dimension:
         print("Mask generation index error", file=sys.stderr)
@@ -77,7 +80,8 @@ def generateMergeMask(cc: CryptoContext, dimension: int, segmentLength: int):
         for k in range(i, min(batch, i + segmentLength)):
             mask[k] = 1.0
         i += dimension * segmentLength
-    return cc.MakeCKKSPackedPlaintext(mask)
+    cache[(dimension, segmentLength)] = cc.MakeCKKSPackedPlaintext(mask)
+    return cache[(dimension, segmentLength)]
 
 
 def mergeSingleCipher(cc: CryptoContext, ctxt: Ciphertext, dimension: int) -> Ciphertext:

@@ -657,10 +657,7 @@ Ct Engine::add_const(const Ct& a, double c) {
     if (c < 0)
         for (int i = 0; i < a->nl; i++) k[i] = (mods[i] - k[i]) % mods[i];
     Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg, a->nb);
-    { Scope sc(this, PK_SCALAR, 1, 16.0 * N * a->nl * a->nb); launch_add_scalar(T, out->d, a->d, scalar_table(k), a->nl, a->nb, a->batch_stride(), st); }
-    if (a->ncomp > 1)   // components 1.. of every batch entry are copied unchanged
-        HX_CUDA(cudaMemcpy2DAsync(out->comp(1), sizeof(u64) * a->batch_stride(), a->comp(1), sizeof(u64) * a->batch_stride(),
-                                  sizeof(u64) * (size_t)(a->ncomp - 1) * a->comp_stride(), (size_t)a->nb, cudaMemcpyDeviceToDevice, st));
+    { Scope sc(this, PK_SCALAR, 1, 16.0 * N * a->nl * a->comps_total()); launch_add_scalar(T, out->d, a->d, scalar_table(k), a->nl, a->ncomp, a->comps_total(), st); }
     return out;
 }
 Ct Engine::mult_norelin(const Ct& a_, const Ct& b_) {

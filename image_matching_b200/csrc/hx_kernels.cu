@@ -183,20 +183,43 @@ void launch_mul_scalar(const DevTables& T, u64* out, const u64* a, const ScalarT
     k_mul_scalar<<<grid, kThreads, 0, st>>>(T, out, a, s, cs_out, cs_a);
 }
 
-__global__ void __launch_bounds__(kThreads) k_add_scalar(DevTables T, u64* __restrict__ out, const u64* __restrict__ a, ScalarTable s, size_t bs) {
+__global__ void __launch_bounds__(kThreads) k_add_scalar(DevTables T, u64* __restrict__ out, const u64* __restrict__ a, ScalarTable s, int ncomp) {
     int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (idx >= T.N) return;
     int i = blockIdx.y;
     const u64 q = T.pc[i].q;
-    size_t off = (size_t)blockIdx.z * bs + (size_t)i * T.N + idx;
+    size_t off = ((size_t)blockIdx.z * gridDim.y + i) * T.N + idx;
     ulonglong2 x = *reinterpret_cast<const ulonglong2*>(a + off);
-    x.x = add_mod(x.x, s.v[i], q);
-    x.y = add_mod(x.y, s.v[i], q);
+    if (blockIdx.z % ncomp == 0) {   // the constant goes to component 0; the other components are copied
+        x.x = add_mod(x.x, s.v[i], q);
+        x.y = add_mod(x.y, s.v[i], q);
+    }
     st128(out + off, x);
 }
-void launch_add_scalar(const DevTables& T, u64* out, const u64* a, const ScalarTable& s, int nl, int nbatch, size_t batch_stride, cudaStream_t st) {
-    dim3 grid(blocks_for(T.N), nl, nbatch);
-    k_add_scalar<<<grid, kThreads, 0, st>>>(T, out, a, s, batch_stride);
+void launch_add_scalar(const DevTables& T, u64* out, const u64* a, const ScalarTable& s, int nl, int ncomp, int ncomps_total, cudaStream_t st) {
+    dim3 grid(blocks_for(T.N), nl, ncomps_total);
+    k_add_scalar<<<grid, kThreads, 0, st>>>(T, out, a, s, ncomp);
+}
+
+__global__ void __launch_bounds__(kThreads) k_wsum(DevTables T, u64* __restrict__ out, const __grid_constant__ WsumArgs a) {
+    int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    const int i = blockIdx.y;
+    const u64 q = T.pc[i].q;
+    const size_t off = ((size_t)blockIdx.z * gridDim.y + i) * T.N + idx;
+    ulonglong2 acc = ldg128(a.p[0] + off);
+    acc.x = shoup_mul(acc.x, a.v[0][i], a.sh[0][i], q);
+    acc.y = shoup_mul(acc.y, a.v[0][i], a.sh[0][i], q);
+    for (int t = 1; t < a.n; t++) {
+        const ulonglong2 x = ldg128(a.p[t] + off);
+        acc.x = add_mod(acc.x, shoup_mul(x.x, a.v[t][i], a.sh[t][i], q), q);
+        acc.y = add_mod(acc.y, shoup_mul(x.y, a.v[t][i], a.sh[t][i], q), q);
+    }
+    st128(out + off, acc);
+}
+void launch_wsum(const DevTables& T, u64* out, const WsumArgs& a, int nl, int ncomps_total, cudaStream_t st) {
+    dim3 grid(blocks_for(T.N), nl, ncomps_total);
+    k_wsum<<<grid, kThreads, 0, st>>>(T, out, a);
 }
 
 // EvalMultCore (row P6, single product): out = (a0*b0, a0*b1 + a1*b0, a1*b1).

@@ -99,8 +99,12 @@ enum EwOp { EW_ADD = 0, EW_SUB = 1, EW_MUL = 2 };
 void launch_ew(const DevTables& T, EwOp op, u64* out, const u64* a, const u64* b, int nl, int ncomp, size_t comp_stride_out,
                size_t comp_stride_a, size_t comp_stride_b, cudaStream_t st);
 void launch_mul_scalar(const DevTables& T, u64* out, const u64* a, const ScalarTable& s, int nl, int ncomp, size_t cs_out, size_t cs_a, cudaStream_t st);
-// adds s to component 0 of `nbatch` ciphertexts lying batch_stride words apart
-void launch_add_scalar(const DevTables& T, u64* out, const u64* a, const ScalarTable& s, int nl, int nbatch, size_t batch_stride, cudaStream_t st);
+// out = a with s added to component 0 of every ciphertext: ncomps_total = nbatch*ncomp contiguous components of nl limbs
+void launch_add_scalar(const DevTables& T, u64* out, const u64* a, const ScalarTable& s, int nl, int ncomp, int ncomps_total, cudaStream_t st);
+// EvalLinearWSum core: out = sum_t w_t * ct_t over n <= 8 ciphertexts of one shape (ncomps_total contiguous components of nl limbs)
+constexpr int kMaxWsum = 8;
+struct WsumArgs { const u64* p[kMaxWsum]; int n; u64 v[kMaxWsum][kMaxPrimes]; u64 sh[kMaxWsum][kMaxPrimes]; };
+void launch_wsum(const DevTables& T, u64* out, const WsumArgs& a, int nl, int ncomps_total, cudaStream_t st);
 // EvalMultCore: (a0*b0, a0*b1+a1*b0, a1*b1); a,b: [2][.][N] with component strides; out [3][nl][N]
 // batch entry z: a + z*2*cs_a, b + z*2*cs_b (contiguous 2-component ciphertexts), out + z*3*nl*N
 void launch_tensor(const DevTables& T, u64* out, const u64* a, size_t cs_a, const u64* b, size_t cs_b, int nl, int nbatch, cudaStream_t st);

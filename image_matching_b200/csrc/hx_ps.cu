@@ -157,6 +157,22 @@ Split ps_split(const Vec& coeffs, int k, int m, bool cheb) {
 
 // EvalLinearWSumMutable: sum_i w_i * ct_i, then one ModReduce.
 Ct Engine::linear_wsum(const std::vector<Ct>& cts, const std::vector<double>& w) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    bool same = cts.size() <= (size_t)kMaxWsum;
+    for (auto& c : cts) same = same && c->nl == cts[0]->nl && c->ncomp == cts[0]->ncomp && c->nb == cts[0]->nb && c->deg == cts[0]->deg;
+    if (same) {   // one launch: sum_t w_t * ct_t (modular addition is associative: same bits as the add chain below)
+        const Ct& f = cts[0];
+        WsumArgs a;
+        a.n = (int)cts.size();
+        for (int t = 0; t < a.n; t++) {
+            a.p[t] = cts[t]->d;
+            ScalarTable s = scalar_table(const_for_mult(w[t], f->nl));
+            for (int i = 0; i < f->nl; i++) { a.v[t][i] = s.v[i]; a.sh[t][i] = s.sh[i]; }
+        }
+        Ct acc = new_ct(f->ncomp, f->nl, f->level, f->deg + 1, f->nb);
+        { Scope sc(this, PK_SCALAR, 1, 8.0 * N * f->nl * f->comps_total() * (a.n + 1)); launch_wsum(T, acc->d, a, f->nl, f->comps_total(), st); }
+        return rescale(acc);
+    }
     Ct acc = mult_const(cts[0], w[0]);
     for (size_t i = 1; i < cts.size(); i++) acc = add(acc, mult_const(cts[i], w[i]));
     return rescale(acc);

@@ -215,6 +215,39 @@ Ct Engine::clone(const Ct& a) {
     return c;
 }
 
+Ct Engine::concat(const std::vector<Ct>& v) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (v.empty()) throw std::runtime_error("concat: empty input");
+    const Ct& f = v[0];
+    int nb = 0;
+    for (auto& c : v) {
+        if (c->ncomp != f->ncomp || c->nl != f->nl || c->deg != f->deg) throw std::runtime_error("concat: ciphertexts differ in shape");
+        nb += c->nb;
+    }
+    Ct out = new_ct(f->ncomp, f->nl, f->level, f->deg, nb);
+    size_t off = 0;
+    for (auto& c : v) {
+        const size_t words = (size_t)c->nb * c->batch_stride();
+        HX_CUDA(cudaMemcpyAsync(out->d + off, c->d, sizeof(u64) * words, cudaMemcpyDeviceToDevice, st));
+        off += words;
+    }
+    return out;
+}
+std::vector<Ct> Engine::split(const Ct& a, int parts) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (parts <= 0 || a->nb % parts) throw std::runtime_error("split: batch size is not a multiple of the number of parts");
+    std::vector<Ct> out;
+    if (parts == 1) { out.push_back(a); return out; }
+    const int nb = a->nb / parts;
+    for (int i = 0; i < parts; i++) {
+        Ct c = new_ct(a->ncomp, a->nl, a->level, a->deg, nb);
+        const size_t words = (size_t)nb * a->batch_stride();
+        HX_CUDA(cudaMemcpyAsync(c->d, a->d + (size_t)i * words, sizeof(u64) * words, cudaMemcpyDeviceToDevice, st));
+        out.push_back(c);
+    }
+    return out;
+}
+
 // ------------------------------------------------------------------------------------------ helpers
 LimbMap Engine::limb_map(const std::vector<int>& primes) const {
     LimbMap lm;

@@ -101,6 +101,8 @@ public:
     Ct new_ct(int ncomp, int nl, int level, int deg, int nb = 1);
     Ct stack(const std::vector<Ct>& v);            // nb = v.size() batch from single ciphertexts (copies)
     std::vector<Ct> unstack(const Ct& a);          // batch -> single ciphertexts (copies)
+    Ct concat(const std::vector<Ct>& v);           // batches of one shape -> one batch (entries in order; copies)
+    std::vector<Ct> split(const Ct& a, int parts); // inverse of concat for equal-sized parts
     Ct upload(const u64* host, int ncomp, int nl, int level, int deg);
     void download(const Ct& ct, u64* host);
     Ct clone(const Ct& ct);
@@ -185,6 +187,11 @@ private:
     std::vector<u64> const_for_add(double c, int nl, int deg) const;
     Ct inner_cheb(const std::vector<double>& coeffs, int k, int m, std::vector<Ct>& T, std::vector<Ct>& T2);
     Ct inner_poly(const std::vector<double>& coeffs, int k, int m, std::vector<Ct>& pw, std::vector<Ct>& pw2);
+    // InnerEvalChebyshevPS / InnerEvalPolyPS of several coefficient vectors at the same recursion level m, evaluated level by
+    // level: the independent ciphertext products of one tree level run as ONE batched mult + rescale (same operations on the
+    // same operands as the recursion, hence the same bits)
+    std::vector<Ct> inner_ps_many(const std::vector<std::vector<double>>& roots, int k, int m, std::vector<Ct>& basis,
+                                  std::vector<Ct>& basis2, bool cheb);
 
     std::map<std::pair<int, int>, BaseConvTable*> modup_tabs_;
     std::map<int, BaseConvTable*> moddown_tabs_;

@@ -6,6 +6,8 @@
 // rounded constant feeds integer polynomial arithmetic.
 #include <cmath>
 
+#include <functional>
+
 #include "hx_engine.h"
 
 namespace hx {
@@ -195,45 +197,96 @@ static Ct eval_c(Engine& e, Ct (Engine::*wsum)(const std::vector<Ct>&, const std
     return e.add_const(cu, half ? c[0] / 2 : c[0]);
 }
 
-// InnerEvalChebyshevPS.
-Ct Engine::inner_cheb(const std::vector<double>& coeffs, int k, int m, std::vector<Ct>& T, std::vector<Ct>& T2) {
-    Split sp = ps_split(coeffs, k, m, true);
-    Ct cu = eval_c(*this, &Engine::linear_wsum, T, sp.c, true);
-    Ct qu, su;
-    if (degree_of(sp.q) > k) {
-        qu = inner_cheb(sp.q, k, m - 1, T, T2);
-    } else {
-        Vec qc = resized(sp.q, k);
-        int dq = degree_of(qc);
-        Ct sum = T[k - 1];
-        for (int i = 0; i < std::log2(sp.q.back()); i++) sum = add(sum, sum);
-        if (dq > 0) {
-            std::vector<Ct> cts(T.begin(), T.begin() + dq);
-            Vec w(sp.q.begin() + 1, sp.q.begin() + 1 + dq);
-            qu = add(linear_wsum(cts, w), sum);
-        } else {
-            qu = sum;
+// InnerEvalChebyshevPS / InnerEvalPolyPS, level-synchronous (see hx_engine.h).  A node computes
+//   cu = c(basis) ; qu, su = child result or leaf polynomial ; out = Rescale((basis2[m-1] + cu) * qu) + su
+// exactly as the upstream recursion does; only the order of independent operations differs.
+std::vector<Ct> Engine::inner_ps_many(const std::vector<Vec>& roots, int k, int m0, std::vector<Ct>& B, std::vector<Ct>& B2, bool cheb) {
+    struct Node { Split sp; int m, depth, qchild = -1, schild = -1; Ct out; };
+    std::vector<Node> nodes;
+    std::function<int(const Vec&, int, int)> build = [&](const Vec& c, int m, int depth) -> int {
+        Node n;
+        n.sp = ps_split(c, k, m, cheb);
+        n.m = m; n.depth = depth;
+        const int id = (int)nodes.size();
+        nodes.push_back(n);
+        if (degree_of(nodes[id].sp.q) > k) { int ch = build(nodes[id].sp.q, m - 1, depth + 1); nodes[id].qchild = ch; }
+        if (degree_of(nodes[id].sp.s2) > k) { int ch = build(nodes[id].sp.s2, m - 1, depth + 1); nodes[id].schild = ch; }
+        return id;
+    };
+    std::vector<int> root_ids;
+    for (auto& r : roots) root_ids.push_back(build(r, m0, 0));
+    int maxd = 0;
+    for (auto& n : nodes) maxd = std::max(maxd, n.depth);
+    auto leaf_q = [&](const Split& sp) -> Ct {
+        Ct qu;
+        if (cheb) {
+            Vec qc = resized(sp.q, k);
+            int dq = degree_of(qc);
+            Ct sum = B[k - 1];
+            for (int i = 0; i < std::log2(sp.q.back()); i++) sum = add(sum, sum);
+            if (dq > 0) {
+                std::vector<Ct> cts(B.begin(), B.begin() + dq);
+                Vec w(sp.q.begin() + 1, sp.q.begin() + 1 + dq);
+                qu = add(linear_wsum(cts, w), sum);
+            } else {
+                qu = sum;
+            }
+            return add_const(qu, sp.q.front() / 2);
         }
-        qu = add_const(qu, sp.q.front() / 2);
-    }
-    if (degree_of(sp.s2) > k) {
-        su = inner_cheb(sp.s2, k, m - 1, T, T2);
-    } else {
+        Vec vc = resized(sp.q, k);
+        int dv = degree_of(vc);
+        if (dv > 0) {
+            std::vector<Ct> cts(B.begin(), B.begin() + dv);
+            Vec w(sp.q.begin() + 1, sp.q.begin() + 1 + dv);
+            qu = add(linear_wsum(cts, w), B[k - 1]);
+        } else {
+            qu = B[k - 1];
+        }
+        return add_const(qu, sp.q.front());
+    };
+    auto leaf_s = [&](const Split& sp) -> Ct {
         Vec sc = resized(sp.s2, k);
         int ds = degree_of(sc);
+        Ct su;
         if (ds > 0) {
-            std::vector<Ct> cts(T.begin(), T.begin() + ds);
+            std::vector<Ct> cts(B.begin(), B.begin() + ds);
             Vec w(sp.s2.begin() + 1, sp.s2.begin() + 1 + ds);
-            su = add(linear_wsum(cts, w), T[k - 1]);
+            su = add(linear_wsum(cts, w), B[k - 1]);
         } else {
-            su = T[k - 1];
+            su = B[k - 1];
         }
-        su = add_const(su, sp.s2.front() / 2);
-        su = level_reduce(su, 1);
+        su = add_const(su, cheb ? sp.s2.front() / 2 : sp.s2.front());
+        return cheb ? level_reduce(su, 1) : su;
+    };
+    for (int d = maxd; d >= 0; d--) {
+        std::vector<int> ids;
+        for (int i = 0; i < (int)nodes.size(); i++)
+            if (nodes[i].depth == d) ids.push_back(i);
+        std::vector<Ct> res(ids.size()), qu(ids.size()), su(ids.size());
+        for (size_t j = 0; j < ids.size(); j++) {
+            Node& n = nodes[ids[j]];
+            Ct cu = eval_c(*this, &Engine::linear_wsum, B, n.sp.c, cheb);
+            qu[j] = n.qchild >= 0 ? nodes[n.qchild].out : leaf_q(n.sp);
+            su[j] = n.schild >= 0 ? nodes[n.schild].out : leaf_s(n.sp);
+            res[j] = cu ? add(B2[n.m - 1], cu) : add_const(B2[n.m - 1], cheb ? n.sp.c.front() / 2 : n.sp.c.front());
+        }
+        bool same = ids.size() > 1 && batch_blocks && !force_unfused && fused_ks_supported(logN);
+        for (size_t j = 1; j < ids.size() && same; j++)
+            same = res[j]->nl == res[0]->nl && res[j]->deg == res[0]->deg && res[j]->nb == res[0]->nb && res[j]->ncomp == res[0]->ncomp &&
+                   qu[j]->nl == qu[0]->nl && qu[j]->deg == qu[0]->deg && qu[j]->nb == qu[0]->nb && qu[j]->ncomp == qu[0]->ncomp;
+        if (same) {
+            std::vector<Ct> prod = split(rescale(mult(concat(res), concat(qu))), (int)ids.size());
+            for (size_t j = 0; j < ids.size(); j++) nodes[ids[j]].out = add(prod[j], su[j]);
+        } else {
+            for (size_t j = 0; j < ids.size(); j++) nodes[ids[j]].out = add(rescale(mult(res[j], qu[j])), su[j]);
+        }
     }
-    Ct res = cu ? add(T2[m - 1], cu) : add_const(T2[m - 1], sp.c.front() / 2);
-    res = rescale(mult(res, qu));
-    return add(res, su);
+    std::vector<Ct> out;
+    for (int id : root_ids) out.push_back(nodes[id].out);
+    return out;
+}
+Ct Engine::inner_cheb(const std::vector<double>& coeffs, int k, int m, std::vector<Ct>& T, std::vector<Ct>& T2) {
+    return inner_ps_many({coeffs}, k, m, T, T2, true)[0];
 }
 
 // EvalChebyshevSeriesPS (cc->EvalChebyshevFunction, openFHE_wrapper.cpp:174).
@@ -281,7 +334,11 @@ Ct Engine::chebyshev_series(const Ct& x, const std::vector<double>& coefficients
     Ct cu = eval_c(*this, &Engine::linear_wsum, T, sp.c, true);
     if (cu) cu = level_reduce(cu, T2[m - 1]->level - cu->level);
     Ct qu, su;
-    if (degree_of(sp.q) > k) {
+    std::vector<Ct> both;
+    if (degree_of(sp.q) > k && degree_of(sp.s2) > k) both = inner_ps_many({sp.q, sp.s2}, k, m - 1, T, T2, true);
+    if (!both.empty()) {
+        qu = both[0];
+    } else if (degree_of(sp.q) > k) {
         qu = inner_cheb(sp.q, k, m - 1, T, T2);
     } else {
         Vec qc = resized(sp.q, k);
@@ -296,7 +353,9 @@ Ct Engine::chebyshev_series(const Ct& x, const std::vector<double>& coefficients
         }
         qu = add_const(qu, sp.q.front() / 2);
     }
-    if (degree_of(sp.s2) > k) {
+    if (!both.empty()) {
+        su = both[1];
+    } else if (degree_of(sp.s2) > k) {
         su = inner_cheb(sp.s2, k, m - 1, T, T2);
     } else {
         Vec sc = resized(sp.s2, k);
@@ -318,26 +377,7 @@ Ct Engine::chebyshev_series(const Ct& x, const std::vector<double>& coefficients
 
 // InnerEvalPolyPS.
 Ct Engine::inner_poly(const std::vector<double>& coeffs, int k, int m, std::vector<Ct>& pw, std::vector<Ct>& pw2) {
-    Split sp = ps_split(coeffs, k, m, false);
-    Ct cu = eval_c(*this, &Engine::linear_wsum, pw, sp.c, false);
-    auto leaf = [&](const Vec& v) -> Ct {
-        if (degree_of(v) > k) return inner_poly(v, k, m - 1, pw, pw2);
-        Vec vc = resized(v, k);
-        int dv = degree_of(vc);
-        Ct out;
-        if (dv > 0) {
-            std::vector<Ct> cts(pw.begin(), pw.begin() + dv);
-            Vec w(v.begin() + 1, v.begin() + 1 + dv);
-            out = add(linear_wsum(cts, w), pw[k - 1]);
-        } else {
-            out = pw[k - 1];
-        }
-        return add_const(out, v.front());
-    };
-    Ct qu = leaf(sp.q), su = leaf(sp.s2);
-    Ct res = cu ? add(pw2[m - 1], cu) : add_const(pw2[m - 1], sp.c.front());
-    res = rescale(mult(res, qu));
-    return add(res, su);
+    return inner_ps_many({coeffs}, k, m, pw, pw2, false)[0];
 }
 
 // EvalPolyPS (cc->EvalPoly, openFHE_wrapper.cpp:179).

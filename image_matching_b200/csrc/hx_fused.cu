@@ -44,6 +44,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_p_inner(const __gr
     u64* kst = reinterpret_cast<u64*>(smraw + kStageOff);
     u64* mbar = reinterpret_cast<u64*>(smraw + kStageOff + NDIG * kTileBytes);
     const int t = threadIdx.x, tile = blockIdx.x;
+    u64* const smp = sm + tphys(2 * t);   // this thread's element pairs: smp[u * kPairStep + {0,1}]
+    u64* const smw = sm + tphys(t);       // this thread's single words:  smw[u * kWordStep]
     const int k = blockIdx.y >> 1, comp = blockIdx.y & 1, b = blockIdx.z;
     const int prime = a.L + k, dl = a.nl + k, ext = a.nl + a.K;
     const PrimeConst pc = T.pc[prime];
@@ -69,8 +71,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_p_inner(const __gr
             mac30(a0, d.x, kv.x);
             mac30(a1, d.y, kv.y);
         }
-        sm[tphys(e)] = redc(fold30(a0), pc.q, pc.qinv_neg);
-        sm[tphys(e + 1)] = redc(fold30(a1), pc.q, pc.qinv_neg);
+        smp[u * kPairStep] = redc(fold30(a0), pc.q, pc.qinv_neg);
+        smp[u * kPairStep + 1] = redc(fold30(a1), pc.q, pc.qinv_neg);
     }
     __syncthreads();
     inv_row_pass<LOGN>(sm, t, tile, T.tw_inv + (size_t)prime * T.N, pc.q);
@@ -78,7 +80,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_p_inner(const __gr
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
-        ulonglong2 x = {sm[tphys(e)], sm[tphys(e + 1)]};
+        ulonglong2 x = {smp[u * kPairStep], smp[u * kPairStep + 1]};
         st128(o + e, x);
     }
 }
@@ -108,6 +110,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_cols(const __grid
                                                               u64* __restrict__ data, size_t bs) {
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, tile = blockIdx.x;
+    u64* const smp = sm + tphys(2 * t);   // this thread's element pairs: smp[u * kPairStep + {0,1}]
+    u64* const smw = sm + tphys(t);       // this thread's single words:  smw[u * kWordStep]
     const int dgt = min((int)blockIdx.y / ts.alpha, ts.ndig - 1), k = blockIdx.y - dgt * ts.alpha;
     const BaseConvTable* __restrict__ tab = ts.t[dgt];
     const int prime = tab->src[k];
@@ -116,7 +120,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_cols(const __grid
 #pragma unroll
     for (int u = 0; u < 8; u++) {
         const int l = u * kTileThreads + t;
-        sm[tphys(l)] = limb[col_offset<LOGN>(tile, l)];
+        smw[u * kWordStep] = limb[col_offset<LOGN>(tile, l)];
     }
     __syncthreads();
     inv_col_pass<LOGN>(sm, t, T.tw_inv + (size_t)prime * T.N, q);
@@ -124,7 +128,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_cols(const __grid
 #pragma unroll
     for (int u = 0; u < 8; u++) {
         const int l = u * kTileThreads + t;
-        limb[col_offset<LOGN>(tile, l)] = shoup_mul(sm[tphys(l)], h, hs, q);
+        limb[col_offset<LOGN>(tile, l)] = shoup_mul(smw[u * kWordStep], h, hs, q);
     }
 }
 
@@ -145,6 +149,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
     u64* sm = reinterpret_cast<u64*>(smraw);
     u64* stage = reinterpret_cast<u64*>(smraw + kStageOff);          // [n_in][2048], local index r*C + c
     const int t = threadIdx.x, tile = blockIdx.x;
+    u64* const smp = sm + tphys(2 * t);   // this thread's element pairs: smp[u * kPairStep + {0,1}]
+    u64* const smw = sm + tphys(t);       // this thread's single words:  smw[u * kWordStep]
     int dgt = 0;
     while (dgt + 1 < ts.ndig && (int)blockIdx.y >= ts.ystart[dgt + 1]) dgt++;
     const BaseConvTable* __restrict__ tab = ts.t[dgt];
@@ -175,7 +181,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
             for (int u = 0; u < 8; u++) mac30(acc[u], stage[k * kTileN + u * kTileThreads + t], m);
         }
 #pragma unroll
-        for (int u = 0; u < 8; u++) sm[tphys(u * kTileThreads + t)] = fwd_encode(redc(fold30(acc[u]), pc.q, pc.qinv_neg), fp_ok(pc.q));
+        for (int u = 0; u < 8; u++) smw[u * kWordStep] = fwd_encode(redc(fold30(acc[u]), pc.q, pc.qinv_neg), fp_ok(pc.q));
         __syncthreads();
         fwd_col_pass<LOGN>(sm, t, T, prime, pc.q);
         // ext_nl >= 0 (ModUp): the output is a digit in extended-basis order (Q limbs 0..nl-1, then P); else limb j
@@ -184,7 +190,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
 #pragma unroll
         for (int u = 0; u < 8; u++) {
             const int l = u * kTileThreads + t;
-            dst[col_offset<LOGN>(tile, l)] = sm[tphys(l)];
+            dst[col_offset<LOGN>(tile, l)] = smw[u * kWordStep];
         }
         __syncthreads();   // the work tile is reused by the next target limb
     }
@@ -213,6 +219,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __g
     u64* kst = reinterpret_cast<u64*>(smraw + kStageOff);           // NDIG staged key tiles (TMA)
     u64* mbar = reinterpret_cast<u64*>(smraw + kStageOff + NDIG * kTileBytes);
     const int t = threadIdx.x, otile = blockIdx.x;
+    u64* const smp = sm + tphys(2 * t);   // this thread's element pairs: smp[u * kPairStep + {0,1}]
+    u64* const smw = sm + tphys(t);       // this thread's single words:  smw[u * kWordStep]
     const int i = blockIdx.y >> 1, comp = blockIdx.y & 1, b = blockIdx.z;
     const u32 g = a.galois[b];
     // tiles map to tiles under the automorphism (the low bits of the natural index map among themselves)
@@ -238,8 +246,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __g
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
         const ulonglong2 x = ldg128(cv + e);
-        sm[tphys(e)] = x.x;
-        sm[tphys(e + 1)] = x.y;
+        smp[u * kPairStep] = x.x;
+        smp[u * kPairStep + 1] = x.y;
     }
     __syncthreads();
     fwd_row_pass<LOGN>(sm, t, tile, T, i, q);
@@ -258,7 +266,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __g
             mac30(a0, d.x, kv.x);
             mac30(a1, d.y, kv.y);
         }
-        const u64 c0 = fwd_normalize(sm[tphys(e)], pc, fp), c1 = fwd_normalize(sm[tphys(e + 1)], pc, fp);
+        const u64 c0 = fwd_normalize(smp[u * kPairStep], pc, fp), c1 = fwd_normalize(smp[u * kPairStep + 1], pc, fp);
         u64 r0 = sub_mod(redc(fold30(a0), q, pc.qinv_neg), c0, q);
         u64 r1 = sub_mod(redc(fold30(a1), q, pc.qinv_neg), c1, q);
         if (add) {
@@ -266,8 +274,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __g
             r0 = add_mod(r0, ad.x, q);
             r1 = add_mod(r1, ad.y, q);
         }
-        sm[tphys(e)] = r0;
-        sm[tphys(e + 1)] = r1;
+        smp[u * kPairStep] = r0;
+        smp[u * kPairStep + 1] = r1;
     }
     __syncthreads();
     u64* o = a.out + (size_t)b * a.out_bs + ((size_t)comp * a.nl + i) * T.N + (size_t)otile * kTileN;
@@ -321,14 +329,16 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_rows(const __grid
                                                               u64* __restrict__ out, size_t out_bs, int prime0) {
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, tile = blockIdx.x, prime = prime0 + blockIdx.y;
+    u64* const smp = sm + tphys(2 * t);   // this thread's element pairs: smp[u * kPairStep + {0,1}]
+    u64* const smw = sm + tphys(t);       // this thread's single words:  smw[u * kWordStep]
     const u64 q = T.pc[prime].q;
     const u64* src = in + (size_t)blockIdx.z * in_bs + (size_t)blockIdx.y * T.N + (size_t)tile * kTileN;
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
         const ulonglong2 x = ldg128(src + e);
-        sm[tphys(e)] = x.x;
-        sm[tphys(e + 1)] = x.y;
+        smp[u * kPairStep] = x.x;
+        smp[u * kPairStep + 1] = x.y;
     }
     __syncthreads();
     inv_row_pass<LOGN>(sm, t, tile, T.tw_inv + (size_t)prime * T.N, q);
@@ -336,7 +346,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_rows(const __grid
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
-        ulonglong2 x = {sm[tphys(e)], sm[tphys(e + 1)]};
+        ulonglong2 x = {smp[u * kPairStep], smp[u * kPairStep + 1]};
         st128(dst + e, x);
     }
 }
@@ -348,6 +358,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_modup_rows(const __gr
                                                                 size_t c_bs, int ndig, int nl, int L, int alpha) {
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, tile = blockIdx.x, y = blockIdx.y;
+    u64* const smp = sm + tphys(2 * t);   // this thread's element pairs: smp[u * kPairStep + {0,1}]
+    u64* const smw = sm + tphys(t);       // this thread's single words:  smw[u * kWordStep]
     const int d = blockIdx.z % ndig, bz = blockIdx.z / ndig;
     const int ext = gridDim.y;
     const int lo = d * alpha, hi = (d == ndig - 1) ? nl : (d + 1) * alpha;
@@ -368,8 +380,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_modup_rows(const __gr
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
         const ulonglong2 x = *reinterpret_cast<const ulonglong2*>(limb + e);
-        sm[tphys(e)] = x.x;
-        sm[tphys(e + 1)] = x.y;
+        smp[u * kPairStep] = x.x;
+        smp[u * kPairStep + 1] = x.y;
     }
     __syncthreads();
     fwd_row_pass<LOGN>(sm, t, tile, T, prime, q);
@@ -377,7 +389,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_modup_rows(const __gr
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
-        ulonglong2 x = {fwd_normalize(sm[tphys(e)], pc, fp), fwd_normalize(sm[tphys(e + 1)], pc, fp)};
+        ulonglong2 x = {fwd_normalize(smp[u * kPairStep], pc, fp), fwd_normalize(smp[u * kPairStep + 1], pc, fp)};
         st128(limb + e, x);
     }
 }
@@ -390,6 +402,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_rescale_cols(const __
                                                                   u64* __restrict__ tmp, size_t tmp_bs, int nl, const __grid_constant__ ScalarTable negqlinv) {
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, tile = blockIdx.x, i = blockIdx.y;
+    u64* const smp = sm + tphys(2 * t);   // this thread's element pairs: smp[u * kPairStep + {0,1}]
+    u64* const smw = sm + tphys(t);       // this thread's single words:  smw[u * kWordStep]
     const u64 q = T.pc[i].q, half = T.pc[nl - 1].q >> 1;
     const u64* src = last + (size_t)blockIdx.z * last_bs;
 #pragma unroll
@@ -398,7 +412,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_rescale_cols(const __
         const u64 v = __ldg(src + col_offset<LOGN>(tile, l));
         u64 r = shoup_mul(v, negqlinv.v[i], negqlinv.sh[i], q);
         if (v > half) r = add_mod(r, 1, q);
-        sm[tphys(l)] = fwd_encode(r, fp_ok(q));
+        smw[u * kWordStep] = fwd_encode(r, fp_ok(q));
     }
     __syncthreads();
     fwd_col_pass<LOGN>(sm, t, T, i, q);
@@ -406,7 +420,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_rescale_cols(const __
 #pragma unroll
     for (int u = 0; u < 8; u++) {
         const int l = u * kTileThreads + t;
-        dst[col_offset<LOGN>(tile, l)] = sm[tphys(l)];
+        dst[col_offset<LOGN>(tile, l)] = smw[u * kWordStep];
     }
 }
 // Rescale, row stage: out_i = c_i * q_l^-1 + NTT(tmp_i).  grid (TILES, nl-1, nbatch).
@@ -416,6 +430,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_rescale_rows(const __
                                                                   const __grid_constant__ ScalarTable qlinv) {
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, tile = blockIdx.x, i = blockIdx.y;
+    u64* const smp = sm + tphys(2 * t);   // this thread's element pairs: smp[u * kPairStep + {0,1}]
+    u64* const smw = sm + tphys(t);       // this thread's single words:  smw[u * kWordStep]
     const PrimeConst pc = T.pc[i];
     const u64 q = pc.q;
     const size_t off = (size_t)i * T.N + (size_t)tile * kTileN;
@@ -424,8 +440,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_rescale_rows(const __
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
         const ulonglong2 x = ldg128(src + e);
-        sm[tphys(e)] = x.x;
-        sm[tphys(e + 1)] = x.y;
+        smp[u * kPairStep] = x.x;
+        smp[u * kPairStep + 1] = x.y;
     }
     __syncthreads();
     fwd_row_pass<LOGN>(sm, t, tile, T, i, q);
@@ -437,8 +453,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_rescale_rows(const __
         const int e = (u * kTileThreads + t) * 2;
         const ulonglong2 x = ldg128(cs + e);
         ulonglong2 r;
-        r.x = add_mod(shoup_mul(x.x, qlinv.v[i], qlinv.sh[i], q), fwd_normalize(sm[tphys(e)], pc, fp), q);
-        r.y = add_mod(shoup_mul(x.y, qlinv.v[i], qlinv.sh[i], q), fwd_normalize(sm[tphys(e + 1)], pc, fp), q);
+        r.x = add_mod(shoup_mul(x.x, qlinv.v[i], qlinv.sh[i], q), fwd_normalize(smp[u * kPairStep], pc, fp), q);
+        r.y = add_mod(shoup_mul(x.y, qlinv.v[i], qlinv.sh[i], q), fwd_normalize(smp[u * kPairStep + 1], pc, fp), q);
         st128(dst + e, r);
     }
 }

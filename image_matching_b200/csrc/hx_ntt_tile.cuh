@@ -22,6 +22,14 @@ constexpr int kTileN = 1 << kLogTile;          // 2048 elements
 constexpr int kTileThreads = kTileN / 8;       // 256 threads
 constexpr int kTileWords = kTileN + (kTileN >> 4) + 8;   // padded: 1 word per 16 against bank conflicts
 __device__ __forceinline__ int tphys(int e) { return e + (e >> 4); }
+// Compile-time offsets of the padded layout (verified exhaustively): with base = insert_bits3(t, p),
+//   tphys(base + (k << p)) == tphys(base) + toff(k, p)            (the 8 elements a thread owns in a round)
+//   tphys((u*256 + t)*2 + j) == tphys(2t) + u*kPairStep + j        (128-bit load/store loops)
+//   tphys(u*256 + t)        == tphys(t)  + u*kWordStep             (column-tile loops)
+// so a thread computes one padded address per phase and the rest are immediate offsets.
+__host__ __device__ constexpr int toff(int k, int p) { return (k << p) + ((k << p) >> 4); }
+constexpr int kPairStep = 2 * kTileThreads + (2 * kTileThreads >> 4);   // 544
+constexpr int kWordStep = kTileThreads + (kTileThreads >> 4);           // 272
 
 template <int LOGN>
 struct NttGeo {
@@ -78,9 +86,10 @@ template <int SL0, int R, int S0, int SHIFT0>
 __device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
     constexpr int p = kLogTile - SL0 - R;
     const int base = insert_bits3(t, p);
+    u64* const sp = sm + tphys(base);
     u64 v[8];
 #pragma unroll
-    for (int k = 0; k < 8; k++) v[k] = sm[tphys(base + (k << p))];
+    for (int k = 0; k < 8; k++) v[k] = sp[toff(k, p)];
 #pragma unroll
     for (int r = 0; r < R; r++) {
         const int kb = R - 1 - r;
@@ -101,16 +110,17 @@ __device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const 
         }
     }
 #pragma unroll
-    for (int k = 0; k < 8; k++) sm[tphys(base + (k << p))] = v[k];
+    for (int k = 0; k < 8; k++) sp[toff(k, p)] = v[k];
 }
 // FP64 back end of the same round: tw = {w, w/q} as doubles.
 template <int SL0, int R, int S0, int SHIFT0>
 __device__ __forceinline__ void fwd_round_fp(double* sm, int t, int tileoff, const double2* __restrict__ tw, double q) {
     constexpr int p = kLogTile - SL0 - R;
     const int base = insert_bits3(t, p);
+    double* const sp = sm + tphys(base);
     double v[8];
 #pragma unroll
-    for (int k = 0; k < 8; k++) v[k] = sm[tphys(base + (k << p))];
+    for (int k = 0; k < 8; k++) v[k] = sp[toff(k, p)];
 #pragma unroll
     for (int r = 0; r < R; r++) {
         const int kb = R - 1 - r;
@@ -134,7 +144,7 @@ __device__ __forceinline__ void fwd_round_fp(double* sm, int t, int tileoff, con
         }
     }
 #pragma unroll
-    for (int k = 0; k < 8; k++) sm[tphys(base + (k << p))] = v[k];
+    for (int k = 0; k < 8; k++) sp[toff(k, p)] = v[k];
 }
 
 // Local stages [SL, SL_END) forward; a __syncthreads() after every round.
@@ -179,9 +189,10 @@ template <int SH, int R, int S_TOP, int SHIFT_TOP>
 __device__ __forceinline__ void inv_round_ct(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
     constexpr int p = kLogTile - SH;
     const int base = insert_bits3(t, p);
+    u64* const sp = sm + tphys(base);
     u64 v[8];
 #pragma unroll
-    for (int k = 0; k < 8; k++) v[k] = sm[tphys(base + (k << p))];
+    for (int k = 0; k < 8; k++) v[k] = sp[toff(k, p)];
 #pragma unroll
     for (int r = 0; r < R; r++) {
         const int kb = r;
@@ -202,7 +213,7 @@ __device__ __forceinline__ void inv_round_ct(u64* sm, int t, int tileoff, const 
         }
     }
 #pragma unroll
-    for (int k = 0; k < 8; k++) sm[tphys(base + (k << p))] = v[k];
+    for (int k = 0; k < 8; k++) sp[toff(k, p)] = v[k];
 }
 // Local stages SH-1 .. SL (descending); remainder round first so the radix-8 rounds are aligned.
 template <int SL, int SH, int S_TOP, int SHIFT_TOP>

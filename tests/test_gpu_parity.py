@@ -353,3 +353,24 @@ def test_client_masks_and_roles_for_approaches_1_and_3():
     blind = hx.BlindSender(cc, None, n, db_loader=lambda m, j: kdb[m][j // chunk], dim=dim, chunk=chunk)
     assert sorted(cl.decryptIndexBlind(blind.indexScenario(cl.encryptQueryBlind(q, chunk)), chunk)) == [7, 199]
     assert cl.decryptMembership(blind.membershipScenario(cl.encryptQueryBlind(q, chunk)))
+
+
+def test_hydia_fused_path_bit_exact_full_ring():
+    """configs[1] geometry (N = 2^15, 12 + 4 limbs, the tile geometry and launch shapes bench.py runs): 63 hoisted rotations in
+    two key-switch batches, the diagonal MAC, relinearise, rescale and the whole compare chain, bit-exact vs the oracle."""
+    ndiag = 64
+    orc = make_oracle(ring_dim=None, depth=11, rotations=list(range(1, ndiag)) + [2 ** i for i in range(14)], seed=9)
+    assert orc.N == 32768 and orc.P.L == 12 and orc.P.K == 4
+    cc = make_gpu_context(orc)
+    rng = np.random.default_rng(31)
+    dbc = [orc.encrypt(rng.uniform(-0.1, 0.1, orc.P.slots)) for _ in range(ndiag)]
+    for d, c in enumerate(dbc):
+        cc.db_register(0, d, np.stack(c.c))
+    qc = orc.encrypt(rng.uniform(-0.1, 0.1, orc.P.slots))
+    gq = up(cc, qc)
+    want = O.diag_compute_similarity(orc, qc, dbc, ndiag)
+    got = cc.score_diag(gq, ndiag)
+    assert len(got) == 1 and same(got[0], want[0])
+    widx = [O.chebyshev_compare(orc, s) for s in want]
+    assert same(cc.index(gq, ndiag)[0], widx[0])
+    assert same(cc.membership(gq, ndiag), orc.eval_sum(orc.add_many(widx), orc.P.slots))

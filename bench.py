@@ -47,6 +47,7 @@ def parse():
     ap.add_argument("--ndiag", type=int, default=512)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--rot-chunk", type=int, default=0, help="override the engine's hoisted-rotation batch size")
+    ap.add_argument("--rot-streams", type=int, default=0, help="override the number of streams the hoisted-rotation batches use")
     ap.add_argument("--ncu-range", action="store_true",
                     help="run one extra step inside cudaProfilerStart/Stop (for ncu --profile-from-start off)")
     return ap.parse_args()
@@ -193,6 +194,8 @@ def run_b200(args):
     cc = hx.CryptoContext.generate(depth=11, ring_dim=args.ring_dim, device=local)
     if args.rot_chunk:
         cc.set_option("rot_chunk", args.rot_chunk)
+    if args.rot_streams:
+        cc.set_option("rot_streams", args.rot_streams)
     slots = cc.GetBatchSize()
     total_blocks = bpg * world
     n_total = total_blocks * slots

@@ -106,7 +106,7 @@ Engine::Scope::Scope(Engine* e_, int kind_, int nlaunch, double bytes) : e(e_), 
     e->launches += nlaunch;
     e->prof_launches[kind] += nlaunch;
     e->prof_bytes[kind] += bytes;
-    if (!((e->prof_on >> kind) & 1u)) return;
+    if (!((e->prof_on >> kind) & 1u) || e->prof_no_events) return;
     cudaEvent_t a;
     auto grab = [&]() {
         cudaEvent_t ev;

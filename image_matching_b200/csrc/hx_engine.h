@@ -68,6 +68,9 @@ public:
     DevTables T{};
     cudaStream_t st = nullptr;
     std::recursive_mutex mu;         // the reference enters from up to 48 OpenMP threads
+    int rot_streams = 2;             // hoisted-rotation batches are issued round-robin on this many streams (1 = the engine stream only)
+    cudaStream_t aux_streams[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t aux_events[4] = {nullptr, nullptr, nullptr, nullptr};
     int rot_chunk = 32;              // hoisted rotations per fused key-switch batch (intermediates stay L2 resident)
     bool force_unfused = false;      // tests: run the unfused reference kernels instead of hx_fused.cu
     int ks_kind = PK_KS_FUSED;       // profiler family of the next fused key switches (score_diag books its hoisted rotations separately)
@@ -76,6 +79,7 @@ public:
 
     // ---- launch accounting + optional CUDA-event profiler (events on `st`, the launching stream)
     struct ProfRec { int kind; cudaEvent_t a, b; };
+    bool prof_no_events = false;             // inside a section timed as a whole (multi-stream hoisted rotations)
     unsigned prof_on = 0;                    // bitmask of ProfKind families being timed
     std::vector<ProfRec> prof_recs;
     std::vector<cudaEvent_t> prof_pool;

@@ -62,8 +62,26 @@ std::vector<Ct> Engine::score_diag_batched(const Ct& query, int ndiag) {
     u64* digits = ks_precompute(query->comp(1), nl, &ndig);
     const int chunk = std::max(1, std::min(rot_chunk, kMaxKsBatch));
     ks_kind = PK_KS_HOISTED;
-    for (int d0 = 1; d0 < ndiag; d0 += chunk) {
+    // Independent batches may run on several streams so that the tail of one batch's kernels overlaps the next batch
+    // (smaller batches keep their intermediates in L2).  Stream s > 0 waits for the digits, the engine stream waits for all.
+    const int ns = rot_streams;
+    cudaStream_t main_st = st;
+    // profiler: the whole section is timed as one span on the engine stream (its batches overlap across streams);
+    // the per-batch scopes inside only book launches and algorithmic bytes
+    std::unique_ptr<Scope> span(new Scope(this, PK_KS_HOISTED, 0, 0.0));
+    prof_no_events = true;
+    if (ns > 1) {
+        for (int s = 0; s < ns - 1; s++)
+            if (!aux_streams[s]) HX_CUDA(cudaStreamCreateWithFlags(&aux_streams[s], cudaStreamNonBlocking));
+        for (int s = 0; s < 4; s++)
+            if (!aux_events[s]) HX_CUDA(cudaEventCreateWithFlags(&aux_events[s], cudaEventDisableTiming));
+        HX_CUDA(cudaEventRecord(aux_events[3], main_st));
+        for (int s = 0; s < ns - 1; s++) HX_CUDA(cudaStreamWaitEvent(aux_streams[s], aux_events[3], 0));
+    }
+    int turn = 0;
+    for (int d0 = 1; d0 < ndiag; d0 += chunk, turn++) {
         int d1 = std::min(ndiag, d0 + chunk);
+        st = (ns > 1 && turn % ns) ? aux_streams[turn % ns - 1] : main_st;
         std::vector<const EvalKey*> keys;
         std::vector<u64> gal;
         for (int d = d0; d < d1; d++) {
@@ -73,6 +91,14 @@ std::vector<Ct> Engine::score_diag_batched(const Ct& query, int ndiag) {
         }
         ks_core_batch(digits, ndig, nl, keys, query->comp(0), 1, gal, rotq + ct_words * d0, ct_words);
     }
+    st = main_st;
+    if (ns > 1)
+        for (int s = 0; s < ns - 1; s++) {
+            HX_CUDA(cudaEventRecord(aux_events[s], aux_streams[s]));
+            HX_CUDA(cudaStreamWaitEvent(main_st, aux_events[s], 0));
+        }
+    prof_no_events = false;
+    span.reset();
     ks_kind = PK_KS_FUSED;
     free_words(digits);
     // all blocks of this GPU in one launch each: diagonal MAC (the rotated query is fetched from HBM once

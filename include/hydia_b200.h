@@ -41,7 +41,8 @@ hx_ctx* hx_ctx_create(int N, int L, int K, int dnum, const uint64_t* q, const ui
 void hx_ctx_destroy(hx_ctx* ctx);
 int hx_ctx_sync(hx_ctx* ctx);                       /* wait for all queued device work */
 uint64_t hx_ctx_launches(hx_ctx* ctx);              /* kernels launched so far (bench accounting) */
-/* Engine tuning / test switches: "rot_chunk" (hoisted rotations per key-switch batch),
+/* Engine tuning / test switches: "rot_chunk" (hoisted rotations per key-switch batch), "rot_streams" (streams the
+ * independent batches are issued on, default 2: the tail of one batch overlaps the head of the next),
  * "force_unfused" (1 = run the unfused reference kernels instead of the fused key-switch pipeline),
  * "batch_blocks" (default 1: the fused HyDia entries relinearise / rescale / compare all database blocks of
  * this GPU as one batch; 0 = one chain per block). */

@@ -374,3 +374,27 @@ def test_hydia_fused_path_bit_exact_full_ring():
     widx = [O.chebyshev_compare(orc, s) for s in want]
     assert same(cc.index(gq, ndiag)[0], widx[0])
     assert same(cc.membership(gq, ndiag), orc.eval_sum(orc.add_many(widx), orc.P.slots))
+
+
+def test_error_behaviour_matches_openfhe_exceptions():
+    """OpenFHE throws on a missing evaluation key, on an exhausted modulus chain and on mismatched noiseScaleDeg; the
+    reference never catches. The C ABI reports the same situations as errors instead of computing garbage."""
+    import image_matching_b200 as hx
+    from image_matching_b200._lib import HxError
+    orc = make_oracle(ring_dim=4096, depth=2, rotations=[1], seed=2)
+    cc = make_gpu_context(orc)
+    ct = up(cc, orc.encrypt(np.linspace(-1, 1, orc.P.slots)))
+    with pytest.raises(HxError, match="Galois"):
+        cc.EvalRotate(ct, 5)                                   # EvalAutomorphismKey not generated
+    with pytest.raises(HxError):
+        cc.score_diag(ct, 8)                                   # no database registered
+    low = cc.Rescale(cc.Rescale(cc.EvalMult(cc.EvalMult(ct, 0.5), 0.5)))
+    assert low.nlimbs == 1
+    with pytest.raises(HxError, match="limb"):
+        cc.Rescale(cc.EvalMult(low, 0.5))                      # level exhausted
+    with pytest.raises(HxError, match="noiseScaleDeg"):
+        cc.EvalAdd(ct, cc.EvalMult(ct, 0.5))                   # FIXEDMANUAL: operands must be rescaled by the caller
+    fresh = hx.CryptoContext(orc.P.N, orc.P.q, orc.P.p, orc.P.psi_q, orc.P.psi_p, orc.P.dnum, orc.P.scale_bits, 0)
+    sq = fresh.EvalMultNoRelin(fresh.upload(np.stack(orc.encrypt([0.5]).c), 0, 1), fresh.upload(np.stack(orc.encrypt([0.5]).c), 0, 1))
+    with pytest.raises(HxError, match="EvalMultKey"):
+        fresh.Relinearize(sq)                                  # EvalMultKey not generated

@@ -62,6 +62,8 @@ SIGNATURES = {
     "hx_score_diag": (C.c_int, [VP, VP, C.c_int, C.POINTER(VP), C.c_int]),
     "hx_membership": (VP, [VP, VP, C.c_int, C.c_double, C.c_int]),
     "hx_index": (C.c_int, [VP, VP, C.c_int, C.c_double, C.c_int, C.POINTER(VP), C.c_int]),
+    "hx_ct_stack": (VP, [C.POINTER(VP), C.c_int]),
+    "hx_ct_unstack": (C.c_int, [VP, C.POINTER(VP), C.c_int]),
     "hx_mult_plain": (VP, [VP, U64P, C.c_int]),
     "hx_inner_product": (VP, [VP, VP, C.c_int]),
     "hx_client_encode": (C.c_int, [VP, F64P, C.c_int, U64P]),

@@ -118,12 +118,17 @@ hx_ct* hx_ct_upload_dev(hx_ctx* ctx, int ncomp, int nlimbs, const void* dev_data
 int hx_ct_download_dev(hx_ct* ct, void* dev_data) {
     HX_TRY_INT(
         need(ct, "ct"); need(dev_data, "dev_data");
+        if (ct->ct->nb != 1) throw std::runtime_error("hx_ct_download_dev: batched ciphertext (hx_ct_unstack it first)");
         Engine* e = ct->ct->eng;
         std::lock_guard<std::recursive_mutex> g(e->mu);
         HX_CUDA(cudaMemcpyAsync(dev_data, ct->ct->d, sizeof(u64) * (size_t)ct->ct->ncomp * ct->ct->nl * e->N, cudaMemcpyDeviceToDevice, e->st));
         e->sync();)
 }
-int hx_ct_download(hx_ct* ct, uint64_t* data) { HX_TRY_INT(need(ct, "ct"); need(data, "data"); ct->ct->eng->download(ct->ct, (u64*)data);) }
+int hx_ct_download(hx_ct* ct, uint64_t* data) {
+    HX_TRY_INT(need(ct, "ct"); need(data, "data");
+               if (ct->ct->nb != 1) throw std::runtime_error("hx_ct_download: batched ciphertext (hx_ct_unstack it first)");
+               ct->ct->eng->download(ct->ct, (u64*)data);)
+}
 int hx_ct_info(hx_ct* ct, int* ncomp, int* nlimbs, int* level, int* noise_deg) {
     HX_TRY_INT(
         need(ct, "ct");
@@ -184,6 +189,20 @@ int hx_score_diag(hx_ctx* ctx, hx_ct* query, int ndiag, hx_ct** out, int max_out
 }
 hx_ct* hx_membership(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sign_depth) {
     HX_TRY_PTR(need(ctx, "ctx"); need(query, "query"); return wrap(ctx->eng->membership(query->ct, ndiag, delta, sign_depth));)
+}
+hx_ct* hx_ct_stack(hx_ct* const* cts, int n) {
+    HX_TRY_PTR(need(cts, "cts"); if (n <= 0) throw std::runtime_error("hx_ct_stack: empty input");
+               std::vector<Ct> v; for (int i = 0; i < n; i++) { need(cts[i], "cts[i]"); v.push_back(cts[i]->ct); }
+               return wrap(v[0]->eng->concat(v));)
+}
+int hx_ct_unstack(hx_ct* ct, hx_ct** out, int max_out) {
+    try {
+        need(ct, "ct"); need(out, "out");
+        if (ct->ct->nb > max_out) throw std::runtime_error("hx_ct_unstack: output array too small");
+        std::vector<Ct> v = ct->ct->eng->split(ct->ct, ct->ct->nb);
+        for (size_t i = 0; i < v.size(); i++) out[i] = wrap(v[i]);
+        return (int)v.size();
+    } catch (const std::exception& e) { set_err(e); return -1; }
 }
 hx_ct* hx_mult_plain(hx_ct* a, const uint64_t* pt, int nlimbs) {
     HX_TRY_PTR(need(a, "a"); need(pt, "pt"); return wrap(a->ct->eng->mult_plain(a->ct, (const u64*)pt, nlimbs));)

@@ -552,6 +552,7 @@ std::shared_ptr<Engine::Digits> Engine::fast_rotation_precompute(const Ct& a) {
     dg->eng = this;
     dg->keep = weak_from_this().lock();
     dg->nl = a->nl;
+    dg->fused = fused_ks_supported(logN) && !force_unfused;
     dg->d = ks_precompute(a->comp(1), a->nl, &dg->ndig);
     return dg;
 }
@@ -559,6 +560,7 @@ Ct Engine::fast_rotation(const Ct& a, int r, const std::shared_ptr<Digits>& dg) 
     std::lock_guard<std::recursive_mutex> g(mu);
     if (r == 0) return clone(a);
     if (a->ncomp != 2 || dg->nl != a->nl) throw std::runtime_error("EvalFastRotation: digits do not match the ciphertext");
+    if (dg->fused != (fused_ks_supported(logN) && !force_unfused)) throw std::runtime_error("EvalFastRotation: digits were precomputed by the other key-switch pipeline");
     u64 k = galois_for_rotation(r);
     Ct out = new_ct(2, a->nl, a->level, a->deg);
     ks_core_batch(dg->d, dg->ndig, a->nl, {&rot_key(k)}, a->comp(0), 1, {k}, out->d, 0);
@@ -566,11 +568,21 @@ Ct Engine::fast_rotation(const Ct& a, int r, const std::shared_ptr<Digits>& dg) 
 }
 Ct Engine::automorphism(const Ct& a, u64 k) {
     std::lock_guard<std::recursive_mutex> g(mu);
-    if (a->ncomp != 2 || a->nb != 1) throw std::runtime_error("EvalAutomorphism needs a single 2-component ciphertext");
+    if (a->ncomp != 2) throw std::runtime_error("EvalAutomorphism needs 2-component ciphertexts");
     int ndig;
-    u64* dg = ks_precompute(a->comp(1), a->nl, &ndig);
-    Ct out = new_ct(2, a->nl, a->level, a->deg);
-    ks_core_batch(dg, ndig, a->nl, {&rot_key(k)}, a->comp(0), 1, {k}, out->d, 0);
+    if (a->nb == 1) {
+        u64* dg = ks_precompute(a->comp(1), a->nl, &ndig);
+        Ct out = new_ct(2, a->nl, a->level, a->deg);
+        ks_core_batch(dg, ndig, a->nl, {&rot_key(k)}, a->comp(0), 1, {k}, out->d, 0);
+        free_words(dg);
+        return out;
+    }
+    // a batch: every entry gets its own ModUp, all share the key and the Galois element
+    u64* dg = ks_precompute(a->comp(1), a->nl, &ndig, a->nb, a->batch_stride());
+    Ct out = new_ct(2, a->nl, a->level, a->deg, a->nb);
+    std::vector<const EvalKey*> keys(a->nb, &rot_key(k));
+    std::vector<u64> gal(a->nb, k);
+    ks_core_batch(dg, ndig, a->nl, keys, a->comp(0), 1, gal, out->d, out->batch_stride(), (size_t)ndig * (a->nl + K) * N, a->batch_stride());
     free_words(dg);
     return out;
 }
@@ -698,9 +710,10 @@ Ct Engine::mult_norelin(const Ct& a_, const Ct& b_) {
     Ct a = a_, b = b_;
     align(a, b);
     if (a->ncomp != 2 || b->ncomp != 2) throw std::runtime_error("EvalMultNoRelin supports 2-component inputs");
-    if (a->nb != b->nb) throw std::runtime_error("EvalMultNoRelin: batch size mismatch");
-    Ct out = new_ct(3, a->nl, a->level, a->deg + b->deg, a->nb);
-    { Scope sc(this, PK_TENSOR, 1, 8.0 * N * a->nl * 7 * a->nb); launch_tensor(T, out->d, a->d, a->comp_stride(), b->d, b->comp_stride(), a->nl, a->nb, st); }
+    if (a->nb != b->nb && a->nb != 1 && b->nb != 1) throw std::runtime_error("EvalMultNoRelin: batch size mismatch");
+    const int nb = std::max(a->nb, b->nb);   // a single ciphertext is broadcast against a batch
+    Ct out = new_ct(3, a->nl, a->level, a->deg + b->deg, nb);
+    { Scope sc(this, PK_TENSOR, 1, 8.0 * N * a->nl * 7 * nb); launch_tensor(T, out->d, a->d, a->comp_stride(), a->nb == 1 && nb > 1, b->d, b->comp_stride(), b->nb == 1 && nb > 1, a->nl, nb, st); }
     return out;
 }
 Ct Engine::mult(const Ct& a, const Ct& b) { return relinearize(mult_norelin(a, b)); }

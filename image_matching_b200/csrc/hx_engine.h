@@ -141,7 +141,8 @@ public:
     Ct add_many(const std::vector<Ct>& v);                  // EvalAddManyInPlace (sender_diag.cpp:46)
     // hoisted rotations (sender_diag.cpp:22-26)
     struct DbBlock { u64* d = nullptr; int ndiag = 0; };
-    struct Digits { u64* d = nullptr; int ndig = 0, nl = 0; Engine* eng = nullptr; std::shared_ptr<Engine> keep; ~Digits(); };
+    struct Digits { u64* d = nullptr; int ndig = 0, nl = 0; bool fused = false;   // fused ModUp stores 30-bit-split words
+                    Engine* eng = nullptr; std::shared_ptr<Engine> keep; ~Digits(); };
     std::shared_ptr<Digits> fast_rotation_precompute(const Ct& a);
     Ct fast_rotation(const Ct& a, int r, const std::shared_ptr<Digits>& dg);
 

@@ -68,8 +68,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_p_inner(const __gr
         for (int j = 0; j < NDIG; j++) {
             const ulonglong2 d = ldg128(dig + j * dstride + e);
             const ulonglong2 kv = *reinterpret_cast<const ulonglong2*>(kst + j * kTileN + e);
-            mac30(a0, d.x, kv.x);
-            mac30(a1, d.y, kv.y);
+            mac30ss(a0, d.x, kv.x);
+            mac30ss(a1, d.y, kv.y);
         }
         smp[u * kPairStep] = redc(fold30(a0), pc.q, pc.qinv_neg);
         smp[u * kPairStep + 1] = redc(fold30(a1), pc.q, pc.qinv_neg);
@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_cols(const __grid
 #pragma unroll
     for (int u = 0; u < 8; u++) {
         const int l = u * kTileThreads + t;
-        limb[col_offset<LOGN>(tile, l)] = shoup_mul(smw[u * kWordStep], h, hs, q);
+        limb[col_offset<LOGN>(tile, l)] = split30(shoup_mul(smw[u * kWordStep], h, hs, q));   // conversion source, stored split
     }
 }
 
@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
         for (int k = 0; k < n_in; k++) {   // n_in <= 7 (digit width / number of P limbs)
             const u64 m = tab->mat30[k * n_out + j];
 #pragma unroll
-            for (int u = 0; u < 8; u++) mac30(acc[u], stage[k * kTileN + u * kTileThreads + t], m);
+            for (int u = 0; u < 8; u++) mac30ss(acc[u], stage[k * kTileN + u * kTileThreads + t], m);
         }
 #pragma unroll
         for (int u = 0; u < 8; u++) smw[u * kWordStep] = fwd_encode(redc(fold30(acc[u]), pc.q, pc.qinv_neg), fp_ok(pc.q));
@@ -263,8 +263,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __g
         for (int j = 0; j < NDIG; j++) {
             const ulonglong2 d = ldg128(dig + j * dstride + e);
             const ulonglong2 kv = *reinterpret_cast<const ulonglong2*>(kst + j * kTileN + e);
-            mac30(a0, d.x, kv.x);
-            mac30(a1, d.y, kv.y);
+            mac30ss(a0, d.x, kv.x);
+            mac30ss(a1, d.y, kv.y);
         }
         const u64 c0 = fwd_normalize(smp[u * kPairStep], pc, fp), c1 = fwd_normalize(smp[u * kPairStep + 1], pc, fp);
         u64 r0 = sub_mod(redc(fold30(a0), q, pc.qinv_neg), c0, q);
@@ -369,7 +369,9 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_modup_rows(const __gr
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             const int e = (u * kTileThreads + t) * 2;
-            st128(limb + e, ldg128(src + e));
+            ulonglong2 x = ldg128(src + e);
+            x.x = split30(x.x); x.y = split30(x.y);
+            st128(limb + e, x);
         }
         return;
     }
@@ -389,8 +391,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_modup_rows(const __gr
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
-        ulonglong2 x = {fwd_normalize(smp[u * kPairStep], pc, fp), fwd_normalize(smp[u * kPairStep + 1], pc, fp)};
-        st128(limb + e, x);
+        ulonglong2 x = {split30(fwd_normalize(smp[u * kPairStep], pc, fp)), split30(fwd_normalize(smp[u * kPairStep + 1], pc, fp))};
+        st128(limb + e, x);   // digits are stored split: the key-switch inner products multiply without unpacking
     }
 }
 
@@ -409,7 +411,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_rescale_cols(const __
 #pragma unroll
     for (int u = 0; u < 8; u++) {
         const int l = u * kTileThreads + t;
-        const u64 v = __ldg(src + col_offset<LOGN>(tile, l));
+        const u64 v = unsplit30(__ldg(src + col_offset<LOGN>(tile, l)));   // k_inv_cols stores split words
         u64 r = shoup_mul(v, negqlinv.v[i], negqlinv.sh[i], q);
         if (v > half) r = add_mod(r, 1, q);
         smw[u * kWordStep] = fwd_encode(r, fp_ok(q));

@@ -224,13 +224,15 @@ void launch_wsum(const DevTables& T, u64* out, const WsumArgs& a, int nl, int nc
 
 // EvalMultCore (row P6, single product): out = (a0*b0, a0*b1 + a1*b0, a1*b1).
 __global__ void __launch_bounds__(kThreads) k_tensor(DevTables T, u64* __restrict__ out, const u64* __restrict__ a, size_t cs_a,
-                                                     const u64* __restrict__ b, size_t cs_b, int nl) {
+                                                     const u64* __restrict__ b, size_t cs_b, int nl, int bca, int bcb) {
     int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (idx >= T.N) return;
     int i = blockIdx.y;
     const PrimeConst pc = T.pc[i];
     size_t off = (size_t)i * T.N + idx;
-    a += (size_t)blockIdx.z * 2 * cs_a; b += (size_t)blockIdx.z * 2 * cs_b; out += (size_t)blockIdx.z * 3 * nl * T.N;   // batch entries are contiguous ciphertexts
+    if (!bca) a += (size_t)blockIdx.z * 2 * cs_a;
+    if (!bcb) b += (size_t)blockIdx.z * 2 * cs_b;
+    out += (size_t)blockIdx.z * 3 * nl * T.N;   // batch entries are contiguous ciphertexts
     ulonglong2 a0 = *reinterpret_cast<const ulonglong2*>(a + off);
     ulonglong2 a1 = *reinterpret_cast<const ulonglong2*>(a + cs_a + off);
     ulonglong2 b0 = *reinterpret_cast<const ulonglong2*>(b + off);
@@ -245,9 +247,9 @@ __global__ void __launch_bounds__(kThreads) k_tensor(DevTables T, u64* __restric
     r.x = mulmod(a1.x, b1.x, pc); r.y = mulmod(a1.y, b1.y, pc);
     st128(out + 2 * cs_o + off, r);
 }
-void launch_tensor(const DevTables& T, u64* out, const u64* a, size_t cs_a, const u64* b, size_t cs_b, int nl, int nbatch, cudaStream_t st) {
+void launch_tensor(const DevTables& T, u64* out, const u64* a, size_t cs_a, bool bcast_a, const u64* b, size_t cs_b, bool bcast_b, int nl, int nbatch, cudaStream_t st) {
     dim3 grid(blocks_for(T.N), nl, nbatch);
-    k_tensor<<<grid, kThreads, 0, st>>>(T, out, a, cs_a, b, cs_b, nl);
+    k_tensor<<<grid, kThreads, 0, st>>>(T, out, a, cs_a, b, cs_b, nl, bcast_a ? 1 : 0, bcast_b ? 1 : 0);
 }
 
 // EvalMultCore against database ciphertexts kept in Montgomery form: one REDC per output word.

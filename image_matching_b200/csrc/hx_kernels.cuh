@@ -107,7 +107,8 @@ struct WsumArgs { const u64* p[kMaxWsum]; int n; u64 v[kMaxWsum][kMaxPrimes]; u6
 void launch_wsum(const DevTables& T, u64* out, const WsumArgs& a, int nl, int ncomps_total, cudaStream_t st);
 // EvalMultCore: (a0*b0, a0*b1+a1*b0, a1*b1); a,b: [2][.][N] with component strides; out [3][nl][N]
 // batch entry z: a + z*2*cs_a, b + z*2*cs_b (contiguous 2-component ciphertexts), out + z*3*nl*N
-void launch_tensor(const DevTables& T, u64* out, const u64* a, size_t cs_a, const u64* b, size_t cs_b, int nl, int nbatch, cudaStream_t st);
+// bcast_a / bcast_b: that operand is ONE ciphertext used by every batch entry
+void launch_tensor(const DevTables& T, u64* out, const u64* a, size_t cs_a, bool bcast_a, const u64* b, size_t cs_b, bool bcast_b, int nl, int nbatch, cudaStream_t st);
 // EvalMultNoRelin of nbatch (query, database) pairs (row R7, sender_hers.cpp:61-98): query ciphertext z = a.p[z]
 // ([2][nl_a][N], plain residues, component stride cs_a), database ciphertext z = db + z*2*cs_b (Montgomery form,
 // as registered by hx_db_register); out [nbatch][3][nl][N].

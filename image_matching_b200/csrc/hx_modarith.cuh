@@ -84,6 +84,14 @@ __device__ __forceinline__ void mac30(acc3& a, u64 x, u64 ys) {
     a.mid = madw(x1, y0, a.mid);
     a.hi = madw(x1, y1, a.hi);
 }
+// acc += x * y with both operands stored split (xs = split30(x), ys = split30(y)): no unpacking instructions at all
+__device__ __forceinline__ void mac30ss(acc3& a, u64 xs, u64 ys) {
+    const u32 x0 = (u32)xs, x1 = (u32)(xs >> 32), y0 = (u32)ys, y1 = (u32)(ys >> 32);
+    a.lo = madw(x0, y0, a.lo);
+    a.mid = madw(x0, y1, a.mid);
+    a.mid = madw(x1, y0, a.mid);
+    a.hi = madw(x1, y1, a.hi);
+}
 // the accumulated value as a 128-bit integer
 __device__ __forceinline__ u128d fold30(const acc3& a) {
     u128d t;

@@ -208,6 +208,14 @@ class CryptoContext:
         n = check_int(self._lib.hx_index(self._h, query._h, ndiag, delta, depth, out, 4096))
         return [self._ct(out[i]) for i in range(n)]
     def compare(self, a, delta=0.44, depth=10): return self._ct(self._lib.hx_compare(a._h, delta, depth))
+    def stack(self, cts: Sequence[Ciphertext]) -> Ciphertext:
+        """n ciphertexts of one shape -> one batched handle (hx_ct_stack); every Eval* call then works on all entries at once."""
+        n = len(cts)
+        return self._ct(self._lib.hx_ct_stack((VP * n)(*[c._h for c in cts]), n))
+    def unstack(self, ct: Ciphertext) -> List[Ciphertext]:
+        out = (VP * 65536)()
+        n = check_int(self._lib.hx_ct_unstack(ct._h, out, 65536))
+        return [self._ct(out[i]) for i in range(n)]
     def compare_many(self, cts: Sequence[Ciphertext], delta=0.44, depth=10) -> List[Ciphertext]:
         """chebyshevCompare of every ciphertext of the list through one batched chain (hx_compare_many)."""
         n = len(cts)

@@ -104,13 +104,17 @@ def mergeSingleCipher(cc: CryptoContext, ctxt: Ciphertext, dimension: int) -> Ci
     return cc.RescaleInPlace(ctxt)
 
 
-def mergeCiphers(cc: CryptoContext, ctxts: List[Ciphertext], dimension: int) -> List[Ciphertext]:
-    """OpenFHEWrapper::mergeCiphers (openFHE_wrapper.cpp:189-217)."""
+def mergeCiphers(cc: CryptoContext, ctxts: List[Ciphertext], dimension: int, batched: bool = False) -> List[Ciphertext]:
+    """OpenFHEWrapper::mergeCiphers (openFHE_wrapper.cpp:189-217). batched=True runs the per-cipher mergeSingleCipher
+    loop (the reference's "#pragma omp parallel for", :199-202) as ONE batched ciphertext: same operations per entry."""
     batch = cc.GetBatchSize()
     elementsPerCipher = batch // dimension
     outputSize = elementsPerCipher * len(ctxts)
     neededCiphers = int(math.ceil(float(outputSize) / float(batch)))
-    ctxts = [mergeSingleCipher(cc, c, dimension) for c in ctxts]
+    if batched and len(ctxts) > 1:
+        ctxts = cc.unstack(mergeSingleCipher(cc, cc.stack(ctxts), dimension))
+    else:
+        ctxts = [mergeSingleCipher(cc, c, dimension) for c in ctxts]
     merged: List[Ciphertext] = [None] * neededCiphers
     for i, c in enumerate(ctxts):
         outputCipher = (elementsPerCipher * i) // batch
@@ -122,8 +126,9 @@ def mergeCiphers(cc: CryptoContext, ctxts: List[Ciphertext], dimension: int) -> 
     return merged
 
 
-def compressCiphers(cc: CryptoContext, ctxts: List[Ciphertext], dimension: int) -> List[Ciphertext]:
-    """OpenFHEWrapper::compressCiphers (openFHE_wrapper.cpp:273-312): keeps the dimension-th slots, not in order."""
+def compressCiphers(cc: CryptoContext, ctxts: List[Ciphertext], dimension: int, batched: bool = False) -> List[Ciphertext]:
+    """OpenFHEWrapper::compressCiphers (openFHE_wrapper.cpp:273-312): keeps the dimension-th slots, not in order.
+    batched=True runs the masking loop (:287-292) on one batched ciphertext."""
     batch = cc.GetBatchSize()
     ciphersNeeded = int(math.ceil(float(len(ctxts)) / float(dimension)))
     maskVec = [0.0] * batch
@@ -131,6 +136,11 @@ def compressCiphers(cc: CryptoContext, ctxts: List[Ciphertext], dimension: int) 
         maskVec[i] = 1.0
     maskPtxt = cc.MakeCKKSPackedPlaintext(maskVec)
     out = []
+    if batched and len(ctxts) > 1:
+        c = cc.EvalMult(cc.stack(ctxts), maskPtxt)
+        c = cc.RelinearizeInPlace(c)
+        out = cc.unstack(cc.RescaleInPlace(c))
+        ctxts = []
     for c in ctxts:
         c = cc.EvalMult(c, maskPtxt)
         c = cc.RelinearizeInPlace(c)

@@ -137,14 +137,23 @@ class BaseSender(HersSender):
     batch/dim consecutive vectors (`db_loader(i)`). Per database ciphertext: EvalInnerProduct(q, db, dim), Relinearize,
     Rescale; then OpenFHEWrapper::mergeCiphers packs the scores. `dim` is VECTOR_DIM in the reference."""
 
-    def __init__(self, cc: CryptoContext, pk, numVectors: int, db_loader: Callable[[int], Ciphertext], dim: int = VECTOR_DIM):
+    def __init__(self, cc: CryptoContext, pk, numVectors: int, db_loader: Callable[[int], Ciphertext], dim: int = VECTOR_DIM,
+                 batched: bool = True):
         super().__init__(cc, pk, numVectors, fused=True)
-        self.db_loader, self.dim = db_loader, dim
+        self.db_loader, self.dim, self.batched, self._db = db_loader, dim, batched, None
 
     def computeSimilarity(self, queryCipher):
+        """batched=True: the "embarrassingly parallel" loop over database ciphertexts (sender_base.cpp:20-24) and the per-cipher
+        merge run as one batched ciphertext (the database batch is stacked once and stays HBM resident)."""
         cc = self.cc
         vectorsPerBatch = cc.GetBatchSize() // self.dim
         numBatches = int(math.ceil(float(self.numVectors) / float(vectorsPerBatch)))
+        if self.batched and numBatches > 1:
+            if self._db is None:
+                self._db = cc.stack([self.db_loader(i) for i in range(numBatches)])
+            s = cc.EvalInnerProduct(queryCipher[0], self._db, self.dim)
+            s = cc.RescaleInPlace(cc.RelinearizeInPlace(s))
+            return OpenFHEWrapper.mergeCiphers(cc, cc.unstack(s), self.dim, batched=True)
         similarity = [self.computeSimilarityThread(queryCipher[0], i) for i in range(numBatches)]
         return OpenFHEWrapper.mergeCiphers(cc, similarity, self.dim)
 
@@ -161,15 +170,29 @@ class BlindSender(HersSender):
     serial/db_blind/matrix{m}/batch{j}.bin (`db_loader(m, j)`). `dim` / `chunk` are VECTOR_DIM / CHUNK_LEN in the reference."""
 
     def __init__(self, cc: CryptoContext, pk, numVectors: int, db_loader: Callable[[int, int], Ciphertext],
-                 dim: int = VECTOR_DIM, chunk: int = 0):
+                 dim: int = VECTOR_DIM, chunk: int = 0, batched: bool = True):
         super().__init__(cc, pk, numVectors, fused=True)
         from .config import CHUNK_LEN
-        self.db_loader, self.dim, self.chunk = db_loader, dim, chunk or CHUNK_LEN
+        self.db_loader, self.dim, self.chunk, self.batched, self._db = db_loader, dim, chunk or CHUNK_LEN, batched, None
 
     def computeSimilarity(self, queryCipher):
+        """batched=True: the loop over matrices (sender_blind.cpp:52-54) runs as one batched ciphertext per query chunk."""
         cc = self.cc
         chunksPerBatch = cc.GetBatchSize() // self.chunk
         numMatrices = int(math.ceil(float(self.numVectors) / float(chunksPerBatch)))
+        if self.batched and numMatrices > 1:
+            chunksPerVector = self.dim // self.chunk
+            if self._db is None:
+                self._db = [cc.stack([self.db_loader(m, c * self.chunk) for m in range(numMatrices)]) for c in range(chunksPerVector)]
+            m0 = cc.EvalMultNoRelin(queryCipher[0], self._db[0])
+            for c in range(1, chunksPerVector):
+                m0 = cc.EvalAddInPlace(m0, cc.EvalMultNoRelin(queryCipher[c], self._db[c]))
+            m0 = cc.RescaleInPlace(cc.RelinearizeInPlace(m0))
+            r = 1
+            while r < self.chunk:
+                m0 = cc.EvalAddInPlace(m0, OpenFHEWrapper.binaryRotate(cc, m0, r))
+                r *= 2
+            return OpenFHEWrapper.compressCiphers(cc, cc.unstack(m0), self.chunk, batched=True)
         score = [self.computeSimilarityMatrix(queryCipher, self.chunk, i) for i in range(numMatrices)]
         return OpenFHEWrapper.compressCiphers(cc, score, self.chunk)
 

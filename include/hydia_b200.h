@@ -115,6 +115,14 @@ hx_ct* hx_membership(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sig
 /* DiagonalSender::indexScenario (sender_diag.cpp:52) */
 int hx_index(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sign_depth, hx_ct** out, int max_out);
 
+/* ---- batched ciphertexts ---------------------------------------------------------------------------------- */
+/* A batch is n ciphertexts of one shape and level behind one handle. Every evaluation entry above accepts a batch and
+ * applies the operation to each entry with the same constants / plaintext / keys in one launch per kernel
+ * (a single ciphertext multiplied with a batch is broadcast). This is how the "#pragma omp parallel for" loops over
+ * ciphertexts in src/sender/ *.cpp and src/openFHE_wrapper.cpp:199-202, 287-292 map onto the GPU. */
+hx_ct* hx_ct_stack(hx_ct* const* cts, int n);            /* copies; inputs stay valid */
+int hx_ct_unstack(hx_ct* ct, hx_ct** out, int max_out);  /* returns the number of entries */
+
 /* ---- other senders ------------------------------------------------- */
 /* HersSender::computeSimilarity (src/sender/sender_hers.cpp:13-26, 61-98): query = nquery ciphertexts, one per
  * coordinate (HersReceiver::encryptQuery, src/receiver/receiver_hers.cpp:13-24); database matrix m, column j =

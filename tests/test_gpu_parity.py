@@ -103,7 +103,15 @@ def test_rotations_bit_exact(env):
         assert same(cc.EvalFastRotation(ga, r, 2 * orc.N, gdg), orc.fast_rotation(ca, r, dg)), r
     low, glow = orc.level_reduce(ca, 11), cc.LevelReduce(ga, 11)
     assert same(cc.EvalSum(glow, orc.P.slots), orc.eval_sum(low, orc.P.slots))
+    cb, gb = env["cb"], env["gb"]
+    both = cc.stack([ga, gb])                                              # batched ciphertext: same op on every entry
+    r0, r1 = cc.unstack(cc.EvalRotate(both, 3))
+    assert same(r0, orc.rotate(ca, 3)) and same(r1, orc.rotate(cb, 3))
+    m0, m1 = cc.unstack(cc.Rescale(cc.EvalMult(ga, both)))                 # single ciphertext broadcast over the batch
+    assert same(m0, orc.rescale(orc.mult(ca, ca))) and same(m1, orc.rescale(orc.mult(ca, cb)))
     from image_matching_b200._lib import HxError
+    with pytest.raises(HxError):
+        both.to_numpy()                                                    # entries are downloaded one by one
     with pytest.raises(HxError, match="not generated"):                    # OpenFHE throws on a missing key
         cc.EvalRotate(ga, 5)
     with pytest.raises(HxError):
@@ -296,6 +304,8 @@ def test_base_sender_bit_exact_small_ring():
     snd = hx.BaseSender(cc, None, n, db_loader=lambda i: gdb[i], dim=dim)
     got = snd.computeSimilarity(gq)
     assert len(got) == len(want) == 1 and same(got[0], want[0])
+    per_op = hx.BaseSender(cc, None, n, db_loader=lambda i: gdb[i], dim=dim, batched=False).computeSimilarity(gq)
+    assert same(per_op[0], want[0])                 # one ciphertext at a time, as the reference loops
     widx = [O.chebyshev_compare(orc, w) for w in want]
     gidx = snd.indexScenario(gq)
     assert all(same(g, w) for g, w in zip(gidx, widx))
@@ -328,6 +338,8 @@ def test_blind_sender_bit_exact_small_ring():
     assert len(got) == len(want) == 1 and same(got[0], want[0])
     widx = [O.chebyshev_compare(orc, w) for w in want]
     assert all(same(g, w) for g, w in zip(snd.indexScenario(gq), widx))
+    per_op = hx.BlindSender(cc, None, n, db_loader=lambda m, j: gdb[m][j // chunk], dim=dim, chunk=chunk, batched=False).computeSimilarity(gq)
+    assert same(per_op[0], want[0])
     assert sorted(O.blind_decrypt_index(orc, widx, chunk)) == [5, 150]
 
 

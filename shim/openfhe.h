@@ -1,0 +1,479 @@
+// shim/openfhe.h -- the subset of OpenFHE v1.2.3's `lbcrypto` namespace that n7koirala/image_matching's
+// sources name (every `cc->`, `Serial::`, `parameters.` and getter under src/),
+// implemented over the C ABI of libhydia_b200.so (include/hydia_b200.h).  With this directory ahead of
+// OpenFHE on the include path the reference's src/**/*.cpp compile UNMODIFIED and every evaluation call of the
+// Sender runs as sm_100a kernels; shim/Makefile builds the reference's own `ImageMatching` that way.
+//
+// What maps where
+//   CryptoContext<DCRTPoly>   -> hx_ctx   (+ the hx_client that stands for KeyGen / Encrypt / Decrypt)
+//   Ciphertext<DCRTPoly>      -> shared_ptr to a mutable object owning one hx_ct ("...InPlace" swaps the handle
+//                                inside the pointee, so aliases observe the update as they do with OpenFHE)
+//   Plaintext                 -> the packed reals; encoded to RNS (hx_client_encode) when a ciphertext is multiplied by it
+//   Serial::SerializeToFile / DeserializeFromFile for ciphertexts -> a path -> handle table in HBM
+//       (the enrollers "write" serial/db_*/...bin, the senders "read" them inside their hot loops,
+//       src/sender/sender_diag.cpp:87-91: no disk I/O, no parsing, the database stays device resident)
+//   context / key serialisation -> accepted and ignored (keys live in HBM next to the context)
+// Errors: the C ABI's NULL / non-zero returns are re-thrown as lbcrypto::OpenFHEException, which is what the
+// reference (never catching) would see from OpenFHE.  Thread safety: the library serialises callers per context,
+// so the reference's "#pragma omp parallel for" loops are safe as they stand.
+#pragma once
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <complex>
+#include <cstdint>
+#include <cstdlib>
+#include <fstream>
+#include <functional>
+#include <iostream>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <numeric>
+#include <sstream>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "hydia_b200.h"
+
+namespace lbcrypto {
+
+class OpenFHEException : public std::runtime_error {
+public:
+    explicit OpenFHEException(const std::string& what) : std::runtime_error(what) {}
+};
+
+namespace shim {
+inline void check(int rc, const char* where) {
+    if (rc != 0) throw OpenFHEException(std::string(where) + ": " + hx_last_error());
+}
+template <class P>
+inline P* check(P* p, const char* where) {
+    if (!p) throw OpenFHEException(std::string(where) + ": " + hx_last_error());
+    return p;
+}
+// The engine and the client that stands for the key holder; outlives every ciphertext that points at it.
+struct Backend {
+    hx_ctx* ctx = nullptr;
+    hx_client* client = nullptr;
+    int N = 0, L = 0, K = 0, dnum = 0, scale_bits = 0;
+    bool sync_every_call = false;
+    ~Backend() {
+        if (client) hx_client_destroy(client);
+        if (ctx) hx_ctx_destroy(ctx);
+    }
+};
+}  // namespace shim
+
+// ---- enums and tags (src/main.cpp:170-179) ---------------------------------------------------------------------
+enum SecurityLevel { HEStd_128_classic, HEStd_192_classic, HEStd_256_classic, HEStd_NotSet };
+enum ScalingTechnique { FIXEDMANUAL, FIXEDAUTO, FLEXIBLEAUTO, FLEXIBLEAUTOEXT, NORESCALE };
+enum KeySwitchTechnique { INVALID_KS_TECH, BV, HYBRID };
+enum PKESchemeFeature { PKE = 0x01, KEYSWITCH = 0x02, PRE = 0x04, LEVELEDSHE = 0x08, ADVANCEDSHE = 0x10, MULTIPARTY = 0x20, FHE = 0x40 };
+struct SerType {
+    struct SERBINARY {};
+    struct SERJSON {};
+    static constexpr SERBINARY BINARY{};
+    static constexpr SERJSON JSON{};
+};
+
+// Only ever named as the element type, and inside shared_ptr<vector<DCRTPoly>> (src/sender/sender_diag.cpp:22) where it
+// carries the ModUp digits of EvalFastRotationPrecompute.
+class DCRTPoly {
+public:
+    std::shared_ptr<hx_digits> digits;
+};
+
+// ---- CCParams<CryptoContextCKKSRNS> (src/main.cpp:169-173, src/openFHE_wrapper.cpp:50-58) ---------------------------
+class CryptoContextCKKSRNS {};
+template <class Scheme>
+class CCParams;
+template <>
+class CCParams<CryptoContextCKKSRNS> {
+public:
+    void SetSecurityLevel(SecurityLevel s) { security_ = s; }
+    void SetMultiplicativeDepth(uint32_t d) { depth_ = d; }
+    void SetScalingModSize(uint32_t b) { scaling_bits_ = b; }
+    void SetFirstModSize(uint32_t b) { first_bits_ = b; }
+    void SetScalingTechnique(ScalingTechnique t) { technique_ = t; }
+    void SetRingDim(uint32_t n) { ring_dim_ = n; }
+    void SetBatchSize(uint32_t b) { batch_ = b; }
+    void SetNumLargeDigits(uint32_t d) { num_large_digits_ = d; }
+    void SetKeySwitchTechnique(KeySwitchTechnique k) { ks_ = k; }
+    SecurityLevel GetSecurityLevel() const { return security_; }
+    uint32_t GetMultiplicativeDepth() const { return depth_; }
+    uint32_t GetScalingModSize() const { return scaling_bits_; }
+    uint32_t GetFirstModSize() const { return first_bits_; }
+    ScalingTechnique GetScalingTechnique() const { return technique_; }
+    uint32_t GetRingDim() const { return ring_dim_; }
+    uint32_t GetBatchSize() const { return batch_; }
+    uint32_t GetNumLargeDigits() const { return num_large_digits_; }
+    KeySwitchTechnique GetKeySwitchTechnique() const { return ks_; }
+    double GetNoiseEstimate() const { return 0; }
+    friend std::ostream& operator<<(std::ostream& os, const CCParams& p) {
+        return os << "scheme: CKKSRNS; multiplicativeDepth: " << p.depth_ << "; scalingModSize: " << p.scaling_bits_
+                  << "; firstModSize: " << p.first_bits_ << "; ringDim: " << p.ring_dim_ << "; scalTech: " << int(p.technique_)
+                  << "; ksTech: HYBRID; numLargeDigits: " << p.num_large_digits_ << "; securityLevel: " << int(p.security_);
+    }
+
+private:
+    SecurityLevel security_ = HEStd_128_classic;
+    ScalingTechnique technique_ = FLEXIBLEAUTOEXT;
+    KeySwitchTechnique ks_ = HYBRID;
+    uint32_t depth_ = 1, scaling_bits_ = 50, first_bits_ = 60, ring_dim_ = 0, batch_ = 0, num_large_digits_ = 0;
+};
+
+class EncodingParamsImpl {
+public:
+    explicit EncodingParamsImpl(uint32_t batch = 0) : batch_(batch) {}
+    uint32_t GetBatchSize() const { return batch_; }
+    friend std::ostream& operator<<(std::ostream& os, const std::shared_ptr<EncodingParamsImpl>& p) {
+        return p ? os << "[batch=" << p->batch_ << "]" : os << "[null]";
+    }
+
+private:
+    uint32_t batch_;
+};
+using EncodingParams = std::shared_ptr<EncodingParamsImpl>;
+
+// ---- keys: tokens, the material lives with the backend's client -----------------------------------------------------------
+template <class Element>
+struct PublicKeyImpl {
+    std::shared_ptr<shim::Backend> be;
+};
+template <class Element>
+struct PrivateKeyImpl {
+    std::shared_ptr<shim::Backend> be;
+};
+template <class Element>
+using PublicKey = std::shared_ptr<PublicKeyImpl<Element>>;
+template <class Element>
+using PrivateKey = std::shared_ptr<PrivateKeyImpl<Element>>;
+template <class Element>
+struct KeyPair {
+    PublicKey<Element> publicKey;
+    PrivateKey<Element> secretKey;
+    bool good() const { return publicKey && secretKey; }
+};
+
+// ---- Plaintext ---------------------------------------------------------------------------------------------------------
+class PlaintextImpl {
+public:
+    explicit PlaintextImpl(std::vector<double> v = {}) : values_(std::move(v)) {}
+    const std::vector<double>& GetRealPackedValue() const { return values_; }
+    std::vector<std::complex<double>> GetCKKSPackedValue() const { return {values_.begin(), values_.end()}; }
+    void SetLength(size_t n) { values_.resize(n); }
+    size_t GetLength() const { return values_.size(); }
+    double GetLogPrecision() const { return 0; }
+    friend std::ostream& operator<<(std::ostream& os, const std::shared_ptr<PlaintextImpl>& p) {
+        os << "(";
+        if (p)
+            for (double v : p->values_) os << v << ", ";
+        return os << ")";
+    }
+    // [L][N] evaluation-form residues of MakeCKKSPackedPlaintext, built on first use by EvalMult(ct, Plaintext)
+    const std::vector<uint64_t>& rns(const shim::Backend& be) const {
+        std::lock_guard<std::mutex> g(mu_);
+        if (rns_.empty()) {
+            rns_.resize(size_t(be.L) * be.N);
+            shim::check(hx_client_encode(be.client, values_.data(), int(values_.size()), rns_.data()), "MakeCKKSPackedPlaintext");
+        }
+        return rns_;
+    }
+
+private:
+    std::vector<double> values_;
+    mutable std::vector<uint64_t> rns_;
+    mutable std::mutex mu_;
+};
+using Plaintext = std::shared_ptr<PlaintextImpl>;
+using ConstPlaintext = std::shared_ptr<const PlaintextImpl>;
+
+// ---- Ciphertext --------------------------------------------------------------------------------------------------------
+template <class Element>
+class CiphertextImpl {
+public:
+    CiphertextImpl(std::shared_ptr<shim::Backend> be, hx_ct* h) : be_(std::move(be)), h_(h) {}
+    CiphertextImpl(const CiphertextImpl&) = delete;
+    CiphertextImpl& operator=(const CiphertextImpl&) = delete;
+    ~CiphertextImpl() { hx_ct_free(h_); }
+    hx_ct* handle() const { return h_; }
+    void reset(hx_ct* h) {      // "...InPlace": the pointee changes, every alias sees it
+        hx_ct_free(h_);
+        h_ = h;
+        if (be_->sync_every_call) shim::check(hx_ctx_sync(be_->ctx), "InPlace");
+    }
+    const std::shared_ptr<shim::Backend>& backend() const { return be_; }
+    // getters of src/openFHE_wrapper.cpp:65-68
+    size_t GetSlots() const { return size_t(be_->N / 2); }
+    size_t GetLevel() const { return size_t(info(2)); }
+    size_t GetNoiseScaleDeg() const { return size_t(info(3)); }
+    double GetScalingFactor() const { return std::pow(std::ldexp(1.0, be_->scale_bits), double(info(3))); }
+    EncodingParams GetEncodingParameters() const { return std::make_shared<EncodingParamsImpl>(uint32_t(be_->N / 2)); }
+    size_t NumberCiphertextElements() const { return size_t(info(0)); }
+
+private:
+    int info(int which) const {
+        int v[4] = {0, 0, 0, 0};
+        shim::check(hx_ct_info(h_, &v[0], &v[1], &v[2], &v[3]), "Ciphertext getter");
+        return v[which];
+    }
+    std::shared_ptr<shim::Backend> be_;
+    hx_ct* h_;
+};
+template <class Element>
+using Ciphertext = std::shared_ptr<CiphertextImpl<Element>>;
+template <class Element>
+using ConstCiphertext = std::shared_ptr<const CiphertextImpl<Element>>;
+
+struct DecryptResult {
+    bool isValid = true;
+    size_t messageLength = 0;
+};
+
+// ---- CryptoContext -----------------------------------------------------------------------------------------------------
+template <class Element>
+class CryptoContextImpl {
+    using CT = Ciphertext<Element>;
+
+public:
+    explicit CryptoContextImpl(std::shared_ptr<shim::Backend> be) : be_(std::move(be)) {}
+
+    // called through a null CryptoContext at src/main.cpp:112-114: static, and there is no global key store to clear
+    static void ClearEvalMultKeys() {}
+    static void ClearEvalAutomorphismKeys() {}
+    static void ClearEvalSumKeys() {}
+
+    void Enable(PKESchemeFeature) {}
+    void Enable(uint32_t) {}
+    EncodingParams GetEncodingParams() const { return std::make_shared<EncodingParamsImpl>(uint32_t(be_->N / 2)); }
+    uint32_t GetRingDimension() const { return uint32_t(be_->N); }
+    uint32_t GetCyclotomicOrder() const { return uint32_t(2 * be_->N); }
+    const std::shared_ptr<shim::Backend>& backend() const { return be_; }
+
+    // -- client side (src/main.cpp:184-206, src/openFHE_wrapper.cpp:74-85): hx_client_*
+    KeyPair<Element> KeyGen() {
+        if (!be_->client) {
+            const char* s = std::getenv("HYDIA_SEED");
+            be_->client = shim::check(hx_client_create(be_->ctx, s ? std::strtoull(s, nullptr, 10) : 1), "KeyGen");
+        }
+        KeyPair<Element> kp;
+        kp.publicKey = std::make_shared<PublicKeyImpl<Element>>(PublicKeyImpl<Element>{be_});
+        kp.secretKey = std::make_shared<PrivateKeyImpl<Element>>(PrivateKeyImpl<Element>{be_});
+        return kp;
+    }
+    void EvalMultKeyGen(const PrivateKey<Element>&) { shim::check(hx_client_gen_mult_key(client()), "EvalMultKeyGen"); }
+    void EvalSumKeyGen(const PrivateKey<Element>&) { shim::check(hx_client_gen_sum_keys(client()), "EvalSumKeyGen"); }
+    void EvalRotateKeyGen(const PrivateKey<Element>&, const std::vector<int32_t>& rotations) {
+        shim::check(hx_client_gen_rot_keys(client(), rotations.data(), int(rotations.size())), "EvalRotateKeyGen");
+    }
+    Plaintext MakeCKKSPackedPlaintext(const std::vector<double>& values, size_t = 1, uint32_t = 0, const std::shared_ptr<void>& = nullptr,
+                                      uint32_t = 0) const {
+        if (values.size() > size_t(be_->N / 2)) throw OpenFHEException("MakeCKKSPackedPlaintext: more values than slots");
+        return std::make_shared<PlaintextImpl>(values);
+    }
+    CT Encrypt(const PublicKey<Element>&, const Plaintext& pt) const {
+        const std::vector<double>& v = pt->GetRealPackedValue();
+        return wrap(hx_client_encrypt(client(), v.data(), int(v.size())), "Encrypt");
+    }
+    CT Encrypt(const Plaintext& pt, const PublicKey<Element>& pk) const { return Encrypt(pk, pt); }
+    DecryptResult Decrypt(const PrivateKey<Element>&, const CT& ct, Plaintext* out) const {
+        std::vector<double> v(size_t(be_->N / 2));
+        shim::check(hx_client_decrypt(client(), ct->handle(), v.data()), "Decrypt");
+        *out = std::make_shared<PlaintextImpl>(std::move(v));
+        return DecryptResult{true, size_t(be_->N / 2)};
+    }
+    DecryptResult Decrypt(const CT& ct, const PrivateKey<Element>& sk, Plaintext* out) const { return Decrypt(sk, ct, out); }
+
+    // -- evaluation (the Sender's calls); each is one C-ABI entry
+    CT EvalAdd(const CT& a, const CT& b) const { return wrap(hx_add(a->handle(), b->handle()), "EvalAdd"); }
+    CT EvalAdd(const CT& a, double c) const { return wrap(hx_add_const(a->handle(), c), "EvalAdd"); }
+    void EvalAddInPlace(CT& a, const CT& b) const { a->reset(shim::check(hx_add(a->handle(), b->handle()), "EvalAddInPlace")); }
+    void EvalAddInPlace(CT& a, double c) const { a->reset(shim::check(hx_add_const(a->handle(), c), "EvalAddInPlace")); }
+    CT EvalSub(const CT& a, const CT& b) const { return wrap(hx_sub(a->handle(), b->handle()), "EvalSub"); }
+    CT EvalSub(const CT& a, double c) const { return wrap(hx_add_const(a->handle(), -c), "EvalSub"); }
+    void EvalSubInPlace(CT& a, const CT& b) const { a->reset(shim::check(hx_sub(a->handle(), b->handle()), "EvalSubInPlace")); }
+    CT EvalMult(const CT& a, const CT& b) const { return wrap(hx_mult(a->handle(), b->handle()), "EvalMult"); }
+    CT EvalMult(const CT& a, double c) const { return wrap(hx_mult_const(a->handle(), c), "EvalMult"); }
+    CT EvalMult(double c, const CT& a) const { return EvalMult(a, c); }
+    CT EvalMult(const CT& a, const Plaintext& pt) const {
+        return wrap(hx_mult_plain(a->handle(), pt->rns(*be_).data(), be_->L), "EvalMult(ct, Plaintext)");
+    }
+    CT EvalMult(const Plaintext& pt, const CT& a) const { return EvalMult(a, pt); }
+    CT EvalMultNoRelin(const CT& a, const CT& b) const { return wrap(hx_mult_norelin(a->handle(), b->handle()), "EvalMultNoRelin"); }
+    CT Relinearize(const CT& a) const { return wrap(hx_relin(a->handle()), "Relinearize"); }
+    void RelinearizeInPlace(CT& a) const { a->reset(shim::check(hx_relin(a->handle()), "RelinearizeInPlace")); }
+    CT Rescale(const CT& a) const { return wrap(hx_rescale(a->handle()), "Rescale"); }
+    void RescaleInPlace(CT& a) const { a->reset(shim::check(hx_rescale(a->handle()), "RescaleInPlace")); }
+    CT ModReduce(const CT& a) const { return Rescale(a); }
+    void ModReduceInPlace(CT& a) const { RescaleInPlace(a); }
+    CT LevelReduce(const CT& a, const std::shared_ptr<void>&, size_t levels = 1) const {
+        return wrap(hx_level_reduce(a->handle(), int(levels)), "LevelReduce");
+    }
+    void LevelReduceInPlace(CT& a, const std::shared_ptr<void>&, size_t levels = 1) const {
+        a->reset(shim::check(hx_level_reduce(a->handle(), int(levels)), "LevelReduceInPlace"));
+    }
+    CT EvalSquare(const CT& a) const { return wrap(hx_square(a->handle()), "EvalSquare"); }
+    void EvalSquareInPlace(CT& a) const { a = EvalSquare(a); }          // OpenFHE rebinds the pointer here
+    CT EvalRotate(const CT& a, int32_t index) const { return wrap(hx_rotate(a->handle(), index), "EvalRotate"); }
+    CT EvalAtIndex(const CT& a, int32_t index) const { return EvalRotate(a, index); }
+    CT EvalSum(const CT& a, uint32_t batch) const { return wrap(hx_eval_sum(a->handle(), int(batch)), "EvalSum"); }
+    CT EvalInnerProduct(const CT& a, const CT& b, uint32_t batch) const {
+        return wrap(hx_inner_product(a->handle(), b->handle(), int(batch)), "EvalInnerProduct");
+    }
+    CT EvalAddMany(const std::vector<CT>& v) const {
+        std::vector<hx_ct*> h;
+        for (const CT& c : v) h.push_back(c->handle());
+        return wrap(hx_add_many(h.data(), int(h.size())), "EvalAddMany");
+    }
+    CT EvalAddManyInPlace(std::vector<CT>& v) const {                   // the sum lands in v[0], as OpenFHE's tree leaves it
+        std::vector<hx_ct*> h;
+        for (const CT& c : v) h.push_back(c->handle());
+        v[0]->reset(shim::check(hx_add_many(h.data(), int(h.size())), "EvalAddManyInPlace"));
+        return v[0];
+    }
+    std::shared_ptr<std::vector<Element>> EvalFastRotationPrecompute(const CT& a) const {
+        hx_digits* d = shim::check(hx_rot_precompute(a->handle()), "EvalFastRotationPrecompute");
+        auto out = std::make_shared<std::vector<Element>>(1);
+        (*out)[0].digits = std::shared_ptr<hx_digits>(d, [be = be_](hx_digits* p) { hx_digits_free(p); });
+        return out;
+    }
+    CT EvalFastRotation(const CT& a, uint32_t index, uint32_t cyclotomic_order, const std::shared_ptr<std::vector<Element>>& digits) const {
+        if (cyclotomic_order != uint32_t(2 * be_->N)) throw OpenFHEException("EvalFastRotation: cyclotomic order is not 2N");
+        if (!digits || digits->empty() || !(*digits)[0].digits) throw OpenFHEException("EvalFastRotation: no precomputed digits");
+        return wrap(hx_rot_fast(a->handle(), int(index), (*digits)[0].digits.get()), "EvalFastRotation");
+    }
+    // EvalChebyshevCoefficients (interpolation at the Chebyshev nodes) then EvalChebyshevSeries (Paterson-Stockmeyer on the device)
+    CT EvalChebyshevFunction(const std::function<double(double)>& func, const CT& a, double lo, double hi, uint32_t degree) const {
+        return EvalChebyshevSeries(a, ChebyshevCoefficients(func, lo, hi, degree), lo, hi);
+    }
+    CT EvalChebyshevSeries(const CT& a, const std::vector<double>& coeffs, double lo, double hi) const {
+        return wrap(hx_cheby_series(a->handle(), coeffs.data(), int(coeffs.size()), lo, hi), "EvalChebyshevSeries");
+    }
+    CT EvalPoly(const CT& a, const std::vector<double>& coeffs) const {
+        return wrap(hx_poly(a->handle(), coeffs.data(), int(coeffs.size())), "EvalPoly");
+    }
+    static std::vector<double> ChebyshevCoefficients(const std::function<double(double)>& func, double lo, double hi, uint32_t degree) {
+        const size_t n = size_t(degree) + 1;
+        const double half_span = 0.5 * (hi - lo), mid = 0.5 * (hi + lo), step = M_PI / double(n);
+        std::vector<double> at_node(n), coeffs(n);
+        for (size_t i = 0; i < n; i++) at_node[i] = func(std::cos(step * (double(i) + 0.5)) * half_span + mid);
+        const double norm = 2.0 / double(n);
+        for (size_t i = 0; i < n; i++) {
+            double s = 0.0;
+            for (size_t j = 0; j < n; j++) s += at_node[j] * std::cos(step * double(i) * (double(j) + 0.5));
+            coeffs[i] = s * norm;
+        }
+        return coeffs;
+    }
+
+    // -- key (de)serialisation (src/main.cpp:124-165, 251-285): the keys never leave HBM
+    template <class ST> bool SerializeEvalMultKey(std::ostream& os, const ST&, const std::string& = "") const { return marker(os); }
+    template <class ST> bool SerializeEvalSumKey(std::ostream& os, const ST&, const std::string& = "") const { return marker(os); }
+    template <class ST> bool SerializeEvalAutomorphismKey(std::ostream& os, const ST&, const std::string& = "") const { return marker(os); }
+    template <class ST> bool DeserializeEvalMultKey(std::istream& is, const ST&) const { return is.good(); }
+    template <class ST> bool DeserializeEvalSumKey(std::istream& is, const ST&) const { return is.good(); }
+    template <class ST> bool DeserializeEvalAutomorphismKey(std::istream& is, const ST&) const { return is.good(); }
+
+private:
+    static bool marker(std::ostream& os) {
+        os << "hydia-b200: evaluation keys are resident in HBM\n";
+        return os.good();
+    }
+    hx_client* client() const {
+        if (!be_->client) throw OpenFHEException("no key pair: call KeyGen first");
+        return be_->client;
+    }
+    // Device work is queued asynchronously and completes in order; a result is waited for when it is read (Decrypt). With
+    // HYDIA_SYNC_EVERY_CALL=1 every evaluation call returns only when its result is complete, as OpenFHE's do, so that the
+    // reference's wall-clock timers around sender->...Scenario() (src/main.cpp:342-347, 361-366) see the device time.
+    CT wrap(hx_ct* h, const char* where) const {
+        CT out = std::make_shared<CiphertextImpl<Element>>(be_, shim::check(h, where));
+        if (be_->sync_every_call) shim::check(hx_ctx_sync(be_->ctx), where);
+        return out;
+    }
+    std::shared_ptr<shim::Backend> be_;
+};
+template <class Element>
+using CryptoContext = std::shared_ptr<CryptoContextImpl<Element>>;
+
+template <class Element>
+class CryptoContextFactory {
+public:
+    static void ReleaseAllContexts() {}
+};
+
+// GenCryptoContext(HEStd_128_classic, depth, ScalingModSize, FIXEDMANUAL) (src/main.cpp:169-175): the parameter recipe is
+// hx_params_generate; HYDIA_DEVICE picks the GPU.
+inline CryptoContext<DCRTPoly> GenCryptoContext(const CCParams<CryptoContextCKKSRNS>& p) {
+    if (p.GetScalingTechnique() != FIXEDMANUAL) throw OpenFHEException("GenCryptoContext: only FIXEDMANUAL is implemented");
+    if (p.GetKeySwitchTechnique() != HYBRID) throw OpenFHEException("GenCryptoContext: only HYBRID key switching is implemented");
+    auto be = std::make_shared<shim::Backend>();
+    uint64_t q[40], pp[40], psi_q[40], psi_p[40];
+    shim::check(hx_params_generate(int(p.GetMultiplicativeDepth()), int(p.GetScalingModSize()), int(p.GetFirstModSize()), int(p.GetRingDim()),
+                                   int(p.GetNumLargeDigits()), &be->N, &be->L, &be->K, &be->dnum, q, pp, psi_q, psi_p),
+                "GenCryptoContext");
+    be->scale_bits = int(p.GetScalingModSize());
+    const char* dev = std::getenv("HYDIA_DEVICE");
+    be->ctx = shim::check(hx_ctx_create(be->N, be->L, be->K, be->dnum, q, pp, psi_q, psi_p, be->scale_bits, dev ? std::atoi(dev) : 0), "GenCryptoContext");
+    const char* sync = std::getenv("HYDIA_SYNC_EVERY_CALL");
+    be->sync_every_call = sync && std::atoi(sync) != 0;
+    return std::make_shared<CryptoContextImpl<DCRTPoly>>(be);
+}
+
+// ---- Serial ------------------------------------------------------------------------------------------------------------
+namespace Serial {
+namespace detail {
+// path -> ciphertext. Deliberately never destroyed: handles must not be released after the CUDA runtime has shut down.
+inline std::map<std::string, Ciphertext<DCRTPoly>>& table() {
+    static auto* t = new std::map<std::string, Ciphertext<DCRTPoly>>();
+    return *t;
+}
+inline std::mutex& table_mutex() {
+    static auto* m = new std::mutex();
+    return *m;
+}
+}  // namespace detail
+
+// Enrollers (src/enroller/enroller_diag.cpp:158-164, enroller_hers.cpp:116-121, ...): the ciphertext becomes database entry
+// `path`, resident in HBM. A private copy is kept so later "...InPlace" calls on the caller's object cannot touch it.
+template <class ST>
+bool SerializeToFile(const std::string& path, const Ciphertext<DCRTPoly>& ct, const ST&) {
+    if (!ct) return false;
+    hx_ct* copy = hx_ct_clone(ct->handle());
+    if (!copy) return false;
+    auto entry = std::make_shared<CiphertextImpl<DCRTPoly>>(ct->backend(), copy);
+    std::lock_guard<std::mutex> g(detail::table_mutex());
+    detail::table()[path] = entry;
+    return true;
+}
+// Senders (src/sender/sender_diag.cpp:87-91 and the like): the handle registered under `path`; false when nothing was enrolled
+// there, which the reference reports on cerr and carries on from.
+template <class ST>
+bool DeserializeFromFile(const std::string& path, Ciphertext<DCRTPoly>& ct, const ST&) {
+    std::lock_guard<std::mutex> g(detail::table_mutex());
+    auto it = detail::table().find(path);
+    if (it == detail::table().end()) return false;
+    ct = it->second;
+    return true;
+}
+// Context and key pair (src/main.cpp:122-134, 246-249): nothing to move, the objects are process resident.
+template <class ST> bool SerializeToFile(const std::string&, const CryptoContext<DCRTPoly>& cc, const ST&) { return bool(cc); }
+template <class ST> bool SerializeToFile(const std::string&, const PublicKey<DCRTPoly>& k, const ST&) { return bool(k); }
+template <class ST> bool SerializeToFile(const std::string&, const PrivateKey<DCRTPoly>& k, const ST&) { return bool(k); }
+template <class ST> bool DeserializeFromFile(const std::string&, CryptoContext<DCRTPoly>&, const ST&) { return false; }
+template <class ST> bool DeserializeFromFile(const std::string&, PublicKey<DCRTPoly>&, const ST&) { return false; }
+template <class ST> bool DeserializeFromFile(const std::string&, PrivateKey<DCRTPoly>&, const ST&) { return false; }
+}  // namespace Serial
+
+// OpenFHE prints vectors as "[ a b c ]" (src/main.cpp:388-389 streams the index results this way).
+template <class T>
+std::ostream& operator<<(std::ostream& os, const std::vector<T>& v) {
+    os << "[";
+    for (const T& x : v) os << " " << x;
+    return os << " ]";
+}
+
+}  // namespace lbcrypto

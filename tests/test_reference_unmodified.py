@@ -1,0 +1,149 @@
+"""The reference's own executable -- src/main.cpp and every translation unit CMakeLists.txt:60-80 links, compiled UNMODIFIED
+from /root/reference against shim/openfhe.h + libhydia_b200.so (shim/Makefile -> shim/_ref/ImageMatching) -- run as
+run_artifact.sh:7-27 runs it: `ImageMatching <dataset> <approach>`.  The dataset is the reference's shipped smoke file
+test/2_10.dat (tests/golden/dat_2_10.npz, written back in main.cpp:56-57,216-230's text format); the known answer is
+membership true / index [0].  Enroller, Receiver, Sender and OpenFHEWrapper are the reference's
+code; every lbcrypto call underneath them is the C ABI."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(ROOT, "shim", "_ref", "ImageMatching")
+needs_exe = pytest.mark.skipif(not os.path.exists(EXE), reason="shim/_ref/ImageMatching not built (make -C shim needs /root/reference)")
+
+
+def write_dataset(path, n=None, dim=512):
+    z = np.load(os.path.join(ROOT, "tests", "golden", "dat_2_10.npz"))
+    db, q = z["db"].astype(np.int64), z["query"].astype(np.int64)
+    if n is not None:
+        db = db[:n]
+    with open(path, "w") as f:
+        f.write(f"{len(db)}\n" + " ".join(map(str, q[:dim])) + "\n")
+        for row in db:
+            f.write(" ".join(map(str, row[:dim])) + "\n")
+    return len(db)
+
+
+def run_reference(tmp_path, approach, n=None, timeout=900, env=None):
+    data = tmp_path / "data.dat"
+    write_dataset(str(data), n)
+    for d in ("serial/db_diagonal", "serial/db_hers", "serial/db_blind", "serial/db_base"):
+        os.makedirs(tmp_path / d, exist_ok=True)
+    return subprocess.run([EXE, str(data), str(approach)], cwd=str(tmp_path), capture_output=True, text=True, timeout=timeout,
+                          env=dict(os.environ, **(env or {})))
+
+
+@needs_exe
+def test_shim_binary_has_no_cpu_fallback(tmp_path):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by the gpu tests")
+    r = run_reference(tmp_path, 5, n=4, timeout=120)
+    assert r.returncode != 0 and "no CUDA device" in r.stderr
+
+
+def test_shim_header_covers_every_lbcrypto_name_the_reference_uses():
+    """Every cc-> method, Serial:: function and CCParams setter named in SURVEY.md section 8(b) B2 is declared by the shim."""
+    text = open(os.path.join(ROOT, "shim", "openfhe.h")).read()
+    names = ["EvalFastRotationPrecompute", "EvalFastRotation", "EvalMultNoRelin", "EvalAddInPlace", "EvalAdd", "RelinearizeInPlace",
+             "RescaleInPlace", "EvalMult", "EvalSquareInPlace", "EvalRotate", "EvalSum", "EvalInnerProduct", "EvalAddManyInPlace",
+             "EvalChebyshevFunction", "EvalPoly", "GenCryptoContext", "Enable", "KeyGen", "EvalMultKeyGen", "EvalSumKeyGen",
+             "EvalRotateKeyGen", "MakeCKKSPackedPlaintext", "Encrypt", "Decrypt", "GetRealPackedValue", "GetEncodingParams",
+             "GetBatchSize", "GetRingDimension", "GetSlots", "GetNoiseScaleDeg", "GetScalingFactor", "GetLevel", "GetEncodingParameters",
+             "ClearEvalMultKeys", "ClearEvalAutomorphismKeys", "ReleaseAllContexts", "SerializeToFile", "DeserializeFromFile",
+             "SerializeEvalMultKey", "SerializeEvalSumKey", "SerializeEvalAutomorphismKey", "DeserializeEvalMultKey",
+             "DeserializeEvalSumKey", "DeserializeEvalAutomorphismKey", "SetSecurityLevel", "SetMultiplicativeDepth",
+             "SetScalingModSize", "SetScalingTechnique", "GetNoiseEstimate", "GetScalingModSize", "GetMultiplicativeDepth",
+             "HEStd_128_classic", "FIXEDMANUAL", "PKE", "KEYSWITCH", "LEVELEDSHE", "ADVANCEDSHE", "BINARY"]
+    missing = [n for n in names if not re.search(r"\b" + n + r"\b", text)]
+    assert not missing, missing
+    for h in ("ciphertext-ser.h", "cryptocontext-ser.h", "key/key-ser.h", "scheme/ckksrns/ckksrns-ser.h"):   # main.cpp:30-33
+        assert os.path.exists(os.path.join(ROOT, "shim", h)), h
+
+
+def parse(stdout):
+    mem = re.search(r"Membership scenario:\s*(\w+)", stdout)
+    idx = re.search(r"Index scenario:\s*\[([^\]]*)\]", stdout)
+    assert mem and idx, stdout[-2000:]
+    return mem.group(1), [int(t) for t in idx.group(1).split()]
+
+
+@needs_exe
+@pytest.mark.gpu
+@pytest.mark.timeout(1500)
+def test_reference_main_unmodified_approach5_2_10(tmp_path):
+    """BASELINE configs[0]: `./ImageMatching test/2_10.dat 5` -> true / [0]."""
+    r = run_reference(tmp_path, 5)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    assert "cannot deserialize" not in r.stderr
+    assert parse(r.stdout) == ("true", [0])
+    print(r.stdout)
+
+
+@needs_exe
+@pytest.mark.gpu
+@pytest.mark.timeout(1500)
+@pytest.mark.parametrize("approach", [1, 3, 4])
+def test_reference_main_unmodified_other_approaches(tmp_path, approach):
+    """Baseline (1), Blind-Match (3) and HERS (4) through the reference's own enroller / receiver / sender classes on the same
+    dataset: rows R7-R10 reached from unmodified reference code."""
+    r = run_reference(tmp_path, approach)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    assert parse(r.stdout) == ("true", [0])
+
+
+@needs_exe
+@pytest.mark.gpu
+@pytest.mark.timeout(1500)
+def test_reference_timers_with_synchronous_calls(tmp_path):
+    """HYDIA_SYNC_EVERY_CALL=1: each evaluation call completes before it returns (OpenFHE's semantics), so the latencies the
+    reference prints and appends to latency.csv (main.cpp:342-372) are device-complete times of its own per-op call sequence."""
+    r = run_reference(tmp_path, 5, env={"HYDIA_SYNC_EVERY_CALL": "1"})
+    assert r.returncode == 0 and parse(r.stdout) == ("true", [0])
+    t = [float(x) for x in re.findall(r"Computing \w+ scenario\.\.\. done \(([0-9.e+-]+)s\)", r.stdout)]
+    assert len(t) == 2
+    row = open(tmp_path / "latency.csv").read().strip().split(",")
+    assert row[0] == "Diagonal" and row[1] == "1024" and "true" in row
+    print("reference-timed, unmodified per-op sender on B200: membership %.3f s (first call: includes warm-up), index %.3f s" % (t[0], t[1]))
+
+
+ACC = os.path.join(ROOT, "shim", "_ref", "ImageMatchingAccuracy")
+
+
+@pytest.mark.skipif(not os.path.exists(ACC), reason="shim/_ref/ImageMatchingAccuracy not built")
+@pytest.mark.gpu
+@pytest.mark.timeout(1500)
+def test_reference_accuracy_main_unmodified_two_blocks(tmp_path):
+    """src/main_accuracy.cpp unmodified, on a synthetic dataset in the FRGC file layout it hard-codes (../test/frgc2-*.dat/txt,
+    main_accuracy.cpp:45,73,84,91): 20000 vectors = two 16384-slot blocks of approach 5, subjects with several near-identical
+    vectors each.  Its own tally must show the encrypted decisions equal to the plaintext-cosine decisions (:386-421)."""
+    rng = np.random.default_rng(3)
+    n, dim, nsubj = 20000, 512, 4000
+    centers = rng.integers(-99, 100, size=(nsubj, dim)).astype(np.float64)
+    subj = np.arange(n) % nsubj
+    db = np.rint(centers[subj] + rng.normal(0, 12, size=(n, dim)))
+    db[db[:, 0] == 0, 0] = 1                                    # main_accuracy.cpp:232 treats a leading 0 as a read error
+    qsubj = rng.choice(nsubj, size=50, replace=False)
+    queries = np.rint(centers[qsubj] + rng.normal(0, 12, size=(50, dim)))
+    (tmp_path / "test").mkdir()
+    (tmp_path / "build" / "serial" / "db_diagonal").mkdir(parents=True)
+    with open(tmp_path / "test" / "frgc2-db.dat", "w") as f:
+        f.write(f"{n}\n")
+        np.savetxt(f, db, fmt="%d")
+    np.savetxt(tmp_path / "test" / "frgc2-query.dat", queries, fmt="%d")
+    np.savetxt(tmp_path / "test" / "frgc2-qid.txt", qsubj, fmt="%d")
+    ids = np.full(44228, 10 ** 6, dtype=np.int64)
+    ids[:n] = subj
+    np.savetxt(tmp_path / "test" / "frgc2-dbid.txt", ids, fmt="%d")
+    r = subprocess.run([ACC, "7", "5"], cwd=str(tmp_path / "build"), capture_output=True, text=True, timeout=1200)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    tally = {k: (int(a), int(b)) for k, a, b in
+             re.findall(r"Encrypted (true positives|false negatives|true negatives|false positives):\s*(\d+)\s*Unencrypted [a-z ]+:\s*(\d+)", r.stdout)}
+    assert len(tally) == 4, r.stdout[-1500:]
+    assert all(a == b for a, b in tally.values()), tally            # encrypted decisions == plaintext decisions
+    assert tally["true positives"][0] == n // nsubj and tally["false positives"][0] == 0
+    assert sum(a for a, _ in tally.values()) == n

@@ -30,6 +30,7 @@ def main():
     ap.add_argument("--log2n", type=int, default=14)
     ap.add_argument("--ring-dim", type=int, default=0)
     ap.add_argument("--steps", type=int, default=1)
+    ap.add_argument("--profile", action="store_true", help="extra pass with per-kernel-family device times and phase wall clocks")
     a = ap.parse_args()
     import image_matching_b200 as hx
     from image_matching_b200 import OpenFHEWrapper
@@ -78,6 +79,14 @@ def main():
     cc.sync()
     ms = cc.timer_stop() / a.steps
     wall = (time.perf_counter() - w0) / a.steps
+    if a.profile:
+        cc.prof_reset(); cc.prof_enable(None)
+        p0 = time.perf_counter(); sc = snd.computeSimilarity(qc); cc.sync(); p1 = time.perf_counter()
+        from image_matching_b200.config import MATCH_THRESHOLD, COMP_DEPTH
+        [OpenFHEWrapper.chebyshevCompare(cc, s, MATCH_THRESHOLD, COMP_DEPTH) for s in sc]; cc.sync(); p2 = time.perf_counter()
+        fam = {k: (v["launches"], round(v["ms"], 2)) for k, v in cc.prof_read().items() if v["launches"]}
+        cc.prof_enable([])
+        print(json.dumps({"similarity_s": p1 - p0, "compare_s": p2 - p1, "outputs": len(sc), "families": fam}), flush=True)
     got = decode(idx)
     ok = (got == matches) and cl.decryptMembership(mem)
     print(json.dumps({"approach": a.approach, "n": n, "ring_dim": cc.N, "limbs": f"{cc.L}+{cc.K}", "depth": depth, "workload": work,

@@ -62,6 +62,12 @@ SIGNATURES = {
     "hx_score_diag": (C.c_int, [VP, VP, C.c_int, C.POINTER(VP), C.c_int]),
     "hx_membership": (VP, [VP, VP, C.c_int, C.c_double, C.c_int]),
     "hx_index": (C.c_int, [VP, VP, C.c_int, C.c_double, C.c_int, C.POINTER(VP), C.c_int]),
+    "hx_db_register_ct": (C.c_int, [VP, C.c_int, C.c_int, VP]),
+    "hx_db_get": (VP, [VP, C.c_int, C.c_int]),
+    "hx_rot_fast_all": (VP, [VP, C.c_int]),
+    "hx_rotset_get": (VP, [VP, C.c_int]),
+    "hx_rotset_free": (None, [VP]),
+    "hx_score_blocks": (C.c_int, [VP, I32P, C.c_int, C.POINTER(VP)]),
     "hx_ct_stack": (VP, [C.POINTER(VP), C.c_int]),
     "hx_ct_unstack": (C.c_int, [VP, C.POINTER(VP), C.c_int]),
     "hx_mult_plain": (VP, [VP, U64P, C.c_int]),

@@ -11,6 +11,7 @@ struct hx_ctx { std::shared_ptr<Engine> eng; };
 struct hx_ct { Ct ct; };
 struct hx_digits { std::shared_ptr<Engine::Digits> dg; };
 struct hx_client { Client* cl; };
+struct hx_rotset { std::shared_ptr<Engine::RotSet> rs; };
 
 static thread_local std::string g_err;
 static void set_err(const std::exception& e) { g_err = e.what(); }
@@ -178,6 +179,25 @@ int hx_db_register(hx_ctx* ctx, int block, int diag, const uint64_t* data) {
     HX_TRY_INT(need(ctx, "ctx"); need(data, "data"); ctx->eng->db_register(block, diag, (const u64*)data);)
 }
 int hx_db_blocks(hx_ctx* ctx) { return ctx ? ctx->eng->db_blocks() : 0; }
+int hx_db_register_ct(hx_ctx* ctx, int block, int diag, hx_ct* ct) {
+    HX_TRY_INT(need(ctx, "ctx"); need(ct, "ct");
+               if (ct->ct->eng != ctx->eng.get() || ct->ct->ncomp != 2 || ct->ct->nl != ctx->eng->L || ct->ct->nb != 1)
+                   throw std::runtime_error("hx_db_register_ct: a fresh 2-component ciphertext of this context is required");
+               ctx->eng->db_store_device(block, diag, ct->ct->d);)
+}
+hx_ct* hx_db_get(hx_ctx* ctx, int block, int diag) { HX_TRY_PTR(need(ctx, "ctx"); return wrap(ctx->eng->db_entry(block, diag));) }
+hx_rotset* hx_rot_fast_all(hx_ct* query, int ndiag) {
+    HX_TRY_PTR(need(query, "query"); hx_rotset* r = new hx_rotset; r->rs = query->ct->eng->rotate_hoisted_all(query->ct, ndiag); return r;)
+}
+hx_ct* hx_rotset_get(hx_rotset* r, int i) { HX_TRY_PTR(need(r, "rotset"); return wrap(r->rs->eng->rotset_entry(*r->rs, i));) }
+void hx_rotset_free(hx_rotset* r) { delete r; }
+int hx_score_blocks(hx_rotset* r, const int* blocks, int nblocks, hx_ct** out) {
+    HX_TRY_INT(need(r, "rotset"); need(blocks, "blocks"); need(out, "out");
+               Engine* e = r->rs->eng;
+               int k = 0;
+               for (auto& part : e->score_rotset(*r->rs, std::vector<int>(blocks, blocks + nblocks)))
+                   for (auto& c : e->unstack(part)) out[k++] = wrap(c);)
+}
 int hx_score_diag(hx_ctx* ctx, hx_ct* query, int ndiag, hx_ct** out, int max_out) {
     try {
         need(ctx, "ctx"); need(query, "query"); need(out, "out");

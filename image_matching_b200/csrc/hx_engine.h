@@ -158,6 +158,14 @@ public:
     void db_adopt(int block, u64* dev /*[ndiag][2][L][N], Montgomery form*/, int ndiag);
     void db_store_device(int block, int diag, const u64* dev_ct /*[2][L][N], plain residues, device*/);
     int db_blocks() const { return (int)db_.size(); }
+    // rotations 0..ndiag-1 of the query (entry 0 = the query), hoisted and batched, as one [ndiag][2][L][N] buffer
+    struct RotSet { u64* rotq = nullptr; int ndiag = 0, nl = 0, level = 0, deg = 0;
+                    Engine* eng = nullptr; std::shared_ptr<Engine> keep; ~RotSet(); };
+    std::shared_ptr<RotSet> rotate_hoisted_all(const Ct& query, int ndiag);   // sender_diag.cpp:20-26
+    Ct rotset_entry(const RotSet& rs, int i);                                 // one rotated query as a ciphertext (copy)
+    // computeSimilarityMatrix (sender_diag.cpp:66-83) for the named blocks against one rotation set, as batches of <= 32
+    std::vector<Ct> score_rotset(const RotSet& rs, const std::vector<int>& blocks);
+    Ct db_entry(int block, int diag);                                         // plain-residue copy of a stored database ciphertext
     std::vector<Ct> score_diag(const Ct& query, int ndiag);            // computeSimilarity
     std::vector<Ct> score_diag_batched(const Ct& query, int ndiag);    // same, blocks kept as batches of <= 32
     Ct membership(const Ct& query, int ndiag, double delta, int depth); // membershipScenario

@@ -50,13 +50,20 @@ void Engine::db_adopt(int block, u64* dev, int ndiag) {
 // computeSimilarity (sender_diag.cpp:12-33): hoisted rotations 1..ndiag-1 of the query
 // (EvalFastRotationPrecompute + EvalFastRotation), then per block the 512 tensor products, their
 // sum, one relinearisation and one rescale (computeSimilarityMatrix, :66-83).
-std::vector<Ct> Engine::score_diag_batched(const Ct& query, int ndiag) {
+Engine::RotSet::~RotSet() {
+    if (rotq && eng) eng->free_words(rotq);
+}
+std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_all(const Ct& query, int ndiag) {
     std::lock_guard<std::recursive_mutex> g(mu);
-    if (query->ncomp != 2 || query->nl != L) throw std::runtime_error("score_diag: query must be a fresh 2-component ciphertext");
-    if (db_.empty()) throw std::runtime_error("score_diag: no database block registered");
+    if (query->ncomp != 2 || query->nl != L || query->nb != 1) throw std::runtime_error("score_diag: query must be a fresh 2-component ciphertext");
+    if (ndiag < 1) throw std::runtime_error("score_diag: ndiag must be positive");
     const int nl = query->nl;
     const size_t ct_words = (size_t)2 * nl * N;
-    u64* rotq = alloc_words(ct_words * ndiag);
+    auto rs = std::make_shared<RotSet>();
+    rs->eng = this;
+    rs->keep = weak_from_this().lock();
+    rs->ndiag = ndiag; rs->nl = nl; rs->level = query->level; rs->deg = query->deg;
+    u64* rotq = rs->rotq = alloc_words(ct_words * ndiag);
     HX_CUDA(cudaMemcpyAsync(rotq, query->d, sizeof(u64) * ct_words, cudaMemcpyDeviceToDevice, st));
     int ndig;
     u64* digits = ks_precompute(query->comp(1), nl, &ndig);
@@ -101,12 +108,41 @@ std::vector<Ct> Engine::score_diag_batched(const Ct& query, int ndiag) {
     span.reset();
     ks_kind = PK_KS_FUSED;
     free_words(digits);
+    return rs;
+}
+Ct Engine::rotset_entry(const RotSet& rs, int i) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (i < 0 || i >= rs.ndiag) throw std::runtime_error("rotset_entry: index out of range");
+    Ct c = new_ct(2, rs.nl, rs.level, rs.deg);
+    const size_t ct_words = (size_t)2 * rs.nl * N;
+    HX_CUDA(cudaMemcpyAsync(c->d, rs.rotq + ct_words * i, sizeof(u64) * ct_words, cudaMemcpyDeviceToDevice, st));
+    return c;
+}
+Ct Engine::db_entry(int block, int diag) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    auto it = db_.find(block);
+    if (it == db_.end() || diag < 0 || diag >= it->second.ndiag) throw std::runtime_error("db_entry: no such database ciphertext");
+    Ct c = new_ct(2, L, 0, 1);
+    const size_t ct_words = (size_t)2 * L * N;
+    HX_CUDA(cudaMemcpyAsync(c->d, it->second.d + ct_words * diag, sizeof(u64) * ct_words, cudaMemcpyDeviceToDevice, st));
+    std::vector<int> primes;
+    for (int i = 0; i < L; i++) primes.push_back(i);
+    Scope sc(this, PK_MISC, 1, 32.0 * L * N);
+    launch_to_mont(T, c->d, 2 * L, limb_map(primes), st, true);
+    return c;
+}
+std::vector<Ct> Engine::score_rotset(const RotSet& rs, const std::vector<int>& block_ids) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    const int nl = rs.nl, ndiag = rs.ndiag;
+    const u64* rotq = rs.rotq;
     // all blocks of this GPU in one launch each: diagonal MAC (the rotated query is fetched from HBM once
     // for all of them), relinearisation and rescale on the batch [G][3][nl][N]
     std::vector<const u64*> blocks;
-    for (auto& kv : db_) {
-        if (kv.second.ndiag < ndiag) throw std::runtime_error("score_diag: database block has fewer diagonals than requested");
-        blocks.push_back(kv.second.d);
+    for (int id : block_ids) {
+        auto it = db_.find(id);
+        if (it == db_.end()) throw std::runtime_error("score_diag: database block not registered");
+        if (it->second.ndiag < ndiag) throw std::runtime_error("score_diag: database block has fewer diagonals than requested");
+        blocks.push_back(it->second.d);
     }
     std::vector<Ct> parts;
     const int group = (batch_blocks && !force_unfused && fused_ks_supported(logN)) ? std::min(kMaxKsBatch, kMaxDbBlocks) : 1;
@@ -114,15 +150,22 @@ std::vector<Ct> Engine::score_diag_batched(const Ct& query, int ndiag) {
         const int g = (int)std::min((size_t)group, blocks.size() - g0);
         DbBlockPtrs ptrs;
         for (int i = 0; i < g; i++) ptrs.p[i] = blocks[g0 + i];
-        Ct acc = new_ct(3, nl, query->level, query->deg + 1, g);
+        Ct acc = new_ct(3, nl, rs.level, rs.deg + 1, g);
         {   // algorithmic bytes: the database blocks, read once; rotq is shared by the launch
             Scope sc(this, PK_DIAG_MAC, 1, 8.0 * N * nl * 2 * ndiag * g);
             launch_diag_mac(T, rotq, ptrs, g, acc->d, ndiag, nl, st);
         }
         parts.push_back(rescale(relinearize(acc)));
     }
-    free_words(rotq);
     return parts;
+}
+std::vector<Ct> Engine::score_diag_batched(const Ct& query, int ndiag) {
+    std::lock_guard<std::recursive_mutex> g(mu);
+    if (db_.empty()) throw std::runtime_error("score_diag: no database block registered");
+    std::shared_ptr<RotSet> rs = rotate_hoisted_all(query, ndiag);
+    std::vector<int> ids;
+    for (auto& kv : db_) ids.push_back(kv.first);
+    return score_rotset(*rs, ids);
 }
 std::vector<Ct> Engine::score_diag(const Ct& query, int ndiag) {
     std::vector<Ct> out;

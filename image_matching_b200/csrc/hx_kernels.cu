@@ -326,15 +326,16 @@ void launch_automap(int N, int logN, u64 k, u32* map, cudaStream_t st) {
 }
 
 // x -> x * 2^64 mod q (Montgomery form) for keys / database blocks at load time.
-__global__ void __launch_bounds__(kThreads) k_to_mont(DevTables T, u64* __restrict__ data, LimbMap lm) {
+__global__ void __launch_bounds__(kThreads) k_to_mont(DevTables T, u64* __restrict__ data, LimbMap lm, bool inverse) {
     int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (idx >= T.N) return;
     size_t b = (size_t)blockIdx.y + (size_t)blockIdx.z * gridDim.y;
     const PrimeConst pc = T.pc[lm.prime[b % lm.period]];
     u64* p = data + b * T.N + idx;
     ulonglong2 x = *reinterpret_cast<ulonglong2*>(p);
-    x.x = redc(mul_wide(x.x, pc.r2), pc.q, pc.qinv_neg);
-    x.y = redc(mul_wide(x.y, pc.r2), pc.q, pc.qinv_neg);
+    const u64 f = inverse ? 1ull : pc.r2;          // inverse: x * 2^-64, back to plain residues
+    x.x = redc(mul_wide(x.x, f), pc.q, pc.qinv_neg);
+    x.y = redc(mul_wide(x.y, f), pc.q, pc.qinv_neg);
     st128(p, x);
 }
 __global__ void __launch_bounds__(kThreads) k_split30(u64* __restrict__ data, size_t words) {
@@ -347,12 +348,12 @@ __global__ void __launch_bounds__(kThreads) k_split30(u64* __restrict__ data, si
 void launch_split30(u64* data, size_t words, cudaStream_t st) {
     k_split30<<<(unsigned)((words / 2 + kThreads - 1) / kThreads), kThreads, 0, st>>>(data, words);
 }
-void launch_to_mont(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, cudaStream_t st) {
+void launch_to_mont(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, cudaStream_t st, bool inverse) {
     // nbatch must be a multiple of lm.period; split so grid.y stays a multiple of the period
     int per = lm.period;
     int groups = nbatch / per;
     dim3 grid(blocks_for(T.N), per, groups);
-    k_to_mont<<<grid, kThreads, 0, st>>>(T, data, lm);
+    k_to_mont<<<grid, kThreads, 0, st>>>(T, data, lm, inverse);
 }
 
 // ---------------------------------------------------------------------------------------------

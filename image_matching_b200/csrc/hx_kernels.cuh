@@ -119,7 +119,7 @@ void launch_tensor_db(const DevTables& T, u64* out, const CtPtrs& a, size_t cs_a
 void launch_batch_sum(const DevTables& T, u64* acc, const u64* in, int nl, int ncomp, int nbatch, int accumulate, cudaStream_t st);
 void launch_automorph(const DevTables& T, u64* out, const u64* in, const u32* map, int nlimbs_total, cudaStream_t st);
 void launch_automap(int N, int logN, u64 k, u32* map, cudaStream_t st);
-void launch_to_mont(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, cudaStream_t st);
+void launch_to_mont(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, cudaStream_t st, bool inverse = false);
 // in place: x -> split30(x) (engine-internal key form, see hx_modarith.cuh)
 void launch_split30(u64* data, size_t words, cudaStream_t st);
 

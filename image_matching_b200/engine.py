@@ -208,6 +208,19 @@ class CryptoContext:
         n = check_int(self._lib.hx_index(self._h, query._h, ndiag, delta, depth, out, 4096))
         return [self._ct(out[i]) for i in range(n)]
     def compare(self, a, delta=0.44, depth=10): return self._ct(self._lib.hx_compare(a._h, delta, depth))
+    # the fused path in two steps (what shim/openfhe.h's deferred layer calls)
+    def db_register_ct(self, block: int, diag: int, ct: Ciphertext): check_int(self._lib.hx_db_register_ct(self._h, block, diag, ct._h))
+    def db_get(self, block: int, diag: int) -> Ciphertext: return self._ct(self._lib.hx_db_get(self._h, block, diag))
+    def score_blocks(self, query: Ciphertext, ndiag: int, blocks: Sequence[int], rotations: Sequence[int] = ()):
+        """hx_rot_fast_all + hx_score_blocks (+ hx_rotset_get for the listed rotations): ([score per block], [rotated queries])."""
+        rs = check_ptr(self._lib.hx_rot_fast_all(query._h, ndiag))
+        try:
+            b = np.array(list(blocks), dtype=np.int32)
+            out = (VP * len(b))()
+            check_int(self._lib.hx_score_blocks(rs, b.ctypes.data_as(_lib.I32P), len(b), out))
+            return [self._ct(out[i]) for i in range(len(b))], [self._ct(self._lib.hx_rotset_get(rs, int(r))) for r in rotations]
+        finally:
+            self._lib.hx_rotset_free(rs)
     def stack(self, cts: Sequence[Ciphertext]) -> Ciphertext:
         """n ciphertexts of one shape -> one batched handle (hx_ct_stack); every Eval* call then works on all entries at once."""
         n = len(cts)

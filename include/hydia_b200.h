@@ -115,6 +115,19 @@ hx_ct* hx_membership(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sig
 /* DiagonalSender::indexScenario (sender_diag.cpp:52) */
 int hx_index(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sign_depth, hx_ct** out, int max_out);
 
+/* The same path in two steps, for callers that hold the database as ciphertext handles and score blocks one at a time
+ * (the deferred-execution layer of shim/openfhe.h): hx_rot_fast_all = sender_diag.cpp:20-26 (rotations 0..ndiag-1 of the
+ * query, hoisted, batched; entry 0 is the query), hx_score_blocks = computeSimilarityMatrix (sender_diag.cpp:66-83) for the
+ * listed blocks against that set (out: one ciphertext per block). hx_db_register_ct stores a device-resident ciphertext as
+ * serial/db_diagonal/index{block*512+diag}.bin; hx_db_get returns a plain copy of a stored one. */
+typedef struct hx_rotset hx_rotset;
+int hx_db_register_ct(hx_ctx* ctx, int block, int diag, hx_ct* ct);
+hx_ct* hx_db_get(hx_ctx* ctx, int block, int diag);
+hx_rotset* hx_rot_fast_all(hx_ct* query, int ndiag);
+hx_ct* hx_rotset_get(hx_rotset* r, int i);
+void hx_rotset_free(hx_rotset* r);
+int hx_score_blocks(hx_rotset* r, const int* blocks, int nblocks, hx_ct** out);
+
 /* ---- batched ciphertexts ---------------------------------------------------------------------------------- */
 /* A batch is n ciphertexts of one shape and level behind one handle. Every evaluation entry above accepts a batch and
  * applies the operation to each entry with the same constants / plaintext / keys in one launch per kernel

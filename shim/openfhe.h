@@ -13,16 +13,24 @@
 //       (the enrollers "write" serial/db_*/...bin, the senders "read" them inside their hot loops,
 //       src/sender/sender_diag.cpp:87-91: no disk I/O, no parsing, the database stays device resident)
 //   context / key serialisation -> accepted and ignored (keys live in HBM next to the context)
+// Deferred execution: the DiagonalSender's call pattern -- EvalFastRotationPrecompute, 511 x
+// EvalFastRotation, per block 512 x (DeserializeFromFile + EvalMultNoRelin), 511 x EvalAddInPlace, RelinearizeInPlace,
+// RescaleInPlace (src/sender/sender_diag.cpp:20-33, 66-94) -- is recorded instead of executed, and when a block score is first
+// read all recorded blocks run through the fused entries (hx_rot_fast_all + hx_score_blocks: batched hoisted rotations, one
+// diagonal multiply-accumulate over all blocks, batched relinearise + rescale). Any other use of a recorded ciphertext
+// executes its recipe call by call, so the results are the per-op results bit for bit either way.
 // Errors: the C ABI's NULL / non-zero returns are re-thrown as lbcrypto::OpenFHEException, which is what the
 // reference (never catching) would see from OpenFHE.  Thread safety: the library serialises callers per context,
 // so the reference's "#pragma omp parallel for" loops are safe as they stand.
 #pragma once
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <complex>
 #include <cstdint>
+#include <cstdio>
 #include <cstdlib>
 #include <fstream>
 #include <functional>
@@ -60,6 +68,7 @@ struct Backend {
     hx_client* client = nullptr;
     int N = 0, L = 0, K = 0, dnum = 0, scale_bits = 0;
     bool sync_every_call = false;
+    bool deferred = true;     // HYDIA_DEFERRED=0: every call is issued as it comes (pure per-op path)
     ~Backend() {
         if (client) hx_client_destroy(client);
         if (ctx) hx_ctx_destroy(ctx);
@@ -81,9 +90,12 @@ struct SerType {
 
 // Only ever named as the element type, and inside shared_ptr<vector<DCRTPoly>> (src/sender/sender_diag.cpp:22) where it
 // carries the ModUp digits of EvalFastRotationPrecompute.
+namespace shim {
+struct Hoist;
+}
 class DCRTPoly {
 public:
-    std::shared_ptr<hx_digits> digits;
+    std::shared_ptr<shim::Hoist> hoist;
 };
 
 // ---- CCParams<CryptoContextCKKSRNS> (src/main.cpp:169-173, src/openFHE_wrapper.cpp:50-58) ---------------------------
@@ -191,42 +203,157 @@ private:
 using Plaintext = std::shared_ptr<PlaintextImpl>;
 using ConstPlaintext = std::shared_ptr<const PlaintextImpl>;
 
-// ---- Ciphertext --------------------------------------------------------------------------------------------------------
-template <class Element>
-class CiphertextImpl {
-public:
-    CiphertextImpl(std::shared_ptr<shim::Backend> be, hx_ct* h) : be_(std::move(be)), h_(h) {}
-    CiphertextImpl(const CiphertextImpl&) = delete;
-    CiphertextImpl& operator=(const CiphertextImpl&) = delete;
-    ~CiphertextImpl() { hx_ct_free(h_); }
-    hx_ct* handle() const { return h_; }
-    void reset(hx_ct* h) {      // "...InPlace": the pointee changes, every alias sees it
-        hx_ct_free(h_);
-        h_ = h;
-        if (be_->sync_every_call) shim::check(hx_ctx_sync(be_->ctx), "InPlace");
+// ---- the pointee of a Ciphertext: a device handle, or the recipe that produces one -------------------------------------
+namespace shim {
+inline std::recursive_mutex& lazy_mutex() {
+    static auto* m = new std::recursive_mutex();
+    return *m;
+}
+struct Node;
+// One EvalFastRotationPrecompute: the digits, a private copy of the hoisted query, and the block scores waiting for it.
+struct Hoist {
+    std::shared_ptr<Backend> be;
+    hx_digits* digits = nullptr;
+    hx_ct* query = nullptr;
+    const void* query_obj = nullptr;     // identity of the caller's ciphertext object at precompute time
+    uint64_t query_version = 0;
+    std::vector<std::weak_ptr<Node>> pending;
+    ~Hoist() {
+        hx_digits_free(digits);
+        hx_ct_free(query);
     }
-    const std::shared_ptr<shim::Backend>& backend() const { return be_; }
-    // getters of src/openFHE_wrapper.cpp:65-68
-    size_t GetSlots() const { return size_t(be_->N / 2); }
-    size_t GetLevel() const { return size_t(info(2)); }
-    size_t GetNoiseScaleDeg() const { return size_t(info(3)); }
-    double GetScalingFactor() const { return std::pow(std::ldexp(1.0, be_->scale_bits), double(info(3))); }
-    EncodingParams GetEncodingParameters() const { return std::make_shared<EncodingParamsImpl>(uint32_t(be_->N / 2)); }
-    size_t NumberCiphertextElements() const { return size_t(info(0)); }
+};
+struct Node {
+    enum Kind { READY, DB, ROT, PROD, SUM, SUM_RELIN, SCORE };
+    Node(std::shared_ptr<Backend> b, hx_ct* handle) : be(std::move(b)), h(handle) {}
+    Node(const Node&) = delete;
+    Node& operator=(const Node&) = delete;
+    virtual ~Node() { hx_ct_free(h.load()); }
+
+    hx_ct* get() {                       // the value; a recorded recipe runs now
+        hx_ct* p = h.load(std::memory_order_acquire);
+        return p ? p : materialise();
+    }
+    void set(hx_ct* p) {                 // "...InPlace": the pointee changes, every alias sees it
+        std::lock_guard<std::recursive_mutex> g(lazy_mutex());
+        hx_ct_free(h.exchange(p));
+        kind = READY;
+        hoist.reset();
+        terms.clear();
+        db_block = db_diag = -1;
+        version++;
+        if (be->sync_every_call) check(hx_ctx_sync(be->ctx), "InPlace");
+    }
+    bool recorded() const { return h.load(std::memory_order_acquire) == nullptr; }
+
+    std::shared_ptr<Backend> be;
+    std::atomic<hx_ct*> h;
+    Kind kind = READY;
+    std::shared_ptr<Hoist> hoist;                  // ROT / PROD / SUM / SUM_RELIN / SCORE
+    int rot = 0, block = -1, diag = -1, ndiag = 0; // ROT: rot; PROD: rot, block, diag; SUM..: block; SCORE: block, ndiag
+    std::vector<std::pair<int, int>> terms;        // SUM / SUM_RELIN: (rotation, diagonal) of every product
+    int db_block = -1, db_diag = -1;               // database ciphertext serial/db_diagonal/index{db_block*512+db_diag}.bin
+    uint64_t version = 0;
+    std::weak_ptr<Hoist> last_hoist;               // set on a query by EvalFastRotationPrecompute
 
 private:
-    int info(int which) const {
+    hx_ct* product(int r, int d) const {
+        hx_ct* a = r == 0 ? hoist->query : check(hx_rot_fast(hoist->query, r, hoist->digits), "EvalFastRotation");
+        hx_ct* b = check(hx_db_get(be->ctx, block, d), "database ciphertext");
+        hx_ct* p = hx_mult_norelin(a, b);
+        if (r != 0) hx_ct_free(a);
+        hx_ct_free(b);
+        return check(p, "EvalMultNoRelin");
+    }
+    void score_pending() {               // every recorded block score of this hoist, through the fused entries
+        std::shared_ptr<Hoist> H = hoist;
+        std::vector<std::shared_ptr<Node>> nodes;
+        std::vector<int> blocks;
+        for (auto& w : H->pending)
+            if (std::shared_ptr<Node> n = w.lock())
+                if (n->kind == SCORE && n->recorded() && n->hoist == H && n->ndiag == ndiag) {
+                    nodes.push_back(n);
+                    blocks.push_back(n->block);
+                }
+        if (std::find_if(nodes.begin(), nodes.end(), [this](const std::shared_ptr<Node>& n) { return n.get() == this; }) == nodes.end())
+            throw OpenFHEException("deferred score: ciphertext is not registered with its hoist");
+        hx_rotset* rs = check(hx_rot_fast_all(H->query, ndiag), "EvalFastRotation (hoisted, batched)");
+        std::vector<hx_ct*> out(nodes.size(), nullptr);
+        int rc = hx_score_blocks(rs, blocks.data(), int(blocks.size()), out.data());
+        hx_rotset_free(rs);
+        check(rc, "EvalMultNoRelin / EvalAddInPlace / Relinearize / Rescale (fused)");
+        for (size_t i = 0; i < nodes.size(); i++) {
+            nodes[i]->h.store(out[i], std::memory_order_release);
+            nodes[i]->kind = READY;
+        }
+        H->pending.clear();
+    }
+    hx_ct* materialise() {
+        std::lock_guard<std::recursive_mutex> g(lazy_mutex());
+        if (hx_ct* p = h.load(std::memory_order_acquire)) return p;
+        hx_ct* out = nullptr;
+        switch (kind) {
+            case DB: out = check(hx_db_get(be->ctx, db_block, db_diag), "database ciphertext"); break;
+            case ROT: out = check(hx_rot_fast(hoist->query, rot, hoist->digits), "EvalFastRotation"); break;
+            case PROD: out = product(rot, diag); break;
+            case SUM:
+            case SUM_RELIN:
+                out = product(terms[0].first, terms[0].second);
+                for (size_t t = 1; t < terms.size(); t++) {
+                    hx_ct* p = product(terms[t].first, terms[t].second);
+                    hx_ct* sum = hx_add(out, p);
+                    hx_ct_free(p);
+                    hx_ct_free(out);
+                    out = check(sum, "EvalAddInPlace");
+                }
+                if (kind == SUM_RELIN) {
+                    hx_ct* r = hx_relin(out);
+                    hx_ct_free(out);
+                    out = check(r, "RelinearizeInPlace");
+                }
+                break;
+            case SCORE:
+                score_pending();
+                out = h.load(std::memory_order_acquire);
+                break;
+            default: throw OpenFHEException("ciphertext without a value");
+        }
+        h.store(out, std::memory_order_release);
+        kind = READY;
+        hoist.reset();
+        terms.clear();
+        return out;
+    }
+};
+}  // namespace shim
+
+// ---- Ciphertext --------------------------------------------------------------------------------------------------------
+template <class Element>
+class CiphertextImpl : public shim::Node {
+public:
+    CiphertextImpl(std::shared_ptr<shim::Backend> be, hx_ct* h) : shim::Node(std::move(be), h) {}
+    hx_ct* handle() { return get(); }
+    void reset(hx_ct* h) { set(h); }
+    const std::shared_ptr<shim::Backend>& backend() const { return be; }
+    // getters of src/openFHE_wrapper.cpp:65-68
+    size_t GetSlots() const { return size_t(be->N / 2); }
+    size_t GetLevel() { return size_t(info(2)); }
+    size_t GetNoiseScaleDeg() { return size_t(info(3)); }
+    double GetScalingFactor() { return std::pow(std::ldexp(1.0, be->scale_bits), double(info(3))); }
+    EncodingParams GetEncodingParameters() const { return std::make_shared<EncodingParamsImpl>(uint32_t(be->N / 2)); }
+    size_t NumberCiphertextElements() { return size_t(info(0)); }
+
+private:
+    int info(int which) {
         int v[4] = {0, 0, 0, 0};
-        shim::check(hx_ct_info(h_, &v[0], &v[1], &v[2], &v[3]), "Ciphertext getter");
+        shim::check(hx_ct_info(get(), &v[0], &v[1], &v[2], &v[3]), "Ciphertext getter");
         return v[which];
     }
-    std::shared_ptr<shim::Backend> be_;
-    hx_ct* h_;
 };
 template <class Element>
 using Ciphertext = std::shared_ptr<CiphertextImpl<Element>>;
 template <class Element>
-using ConstCiphertext = std::shared_ptr<const CiphertextImpl<Element>>;
+using ConstCiphertext = std::shared_ptr<CiphertextImpl<Element>>;
 
 struct DecryptResult {
     bool isValid = true;
@@ -290,7 +417,22 @@ public:
     // -- evaluation (the Sender's calls); each is one C-ABI entry
     CT EvalAdd(const CT& a, const CT& b) const { return wrap(hx_add(a->handle(), b->handle()), "EvalAdd"); }
     CT EvalAdd(const CT& a, double c) const { return wrap(hx_add_const(a->handle(), c), "EvalAdd"); }
-    void EvalAddInPlace(CT& a, const CT& b) const { a->reset(shim::check(hx_add(a->handle(), b->handle()), "EvalAddInPlace")); }
+    void EvalAddInPlace(CT& a, const CT& b) const {
+        {   // recorded: product (+ product)* of one hoist against one database block (sender_diag.cpp:75-77)
+            std::lock_guard<std::recursive_mutex> g(shim::lazy_mutex());
+            if (a->recorded() && b->recorded() && (a->kind == shim::Node::PROD || a->kind == shim::Node::SUM) && b->kind == shim::Node::PROD &&
+                a->hoist == b->hoist && a->block == b->block) {
+                if (a->kind == shim::Node::PROD) {
+                    a->terms.assign(1, std::make_pair(a->rot, a->diag));
+                    a->kind = shim::Node::SUM;
+                }
+                a->terms.emplace_back(b->rot, b->diag);
+                a->version++;
+                return;
+            }
+        }
+        a->reset(shim::check(hx_add(a->handle(), b->handle()), "EvalAddInPlace"));
+    }
     void EvalAddInPlace(CT& a, double c) const { a->reset(shim::check(hx_add_const(a->handle(), c), "EvalAddInPlace")); }
     CT EvalSub(const CT& a, const CT& b) const { return wrap(hx_sub(a->handle(), b->handle()), "EvalSub"); }
     CT EvalSub(const CT& a, double c) const { return wrap(hx_add_const(a->handle(), -c), "EvalSub"); }
@@ -302,11 +444,63 @@ public:
         return wrap(hx_mult_plain(a->handle(), pt->rns(*be_).data(), be_->L), "EvalMult(ct, Plaintext)");
     }
     CT EvalMult(const Plaintext& pt, const CT& a) const { return EvalMult(a, pt); }
-    CT EvalMultNoRelin(const CT& a, const CT& b) const { return wrap(hx_mult_norelin(a->handle(), b->handle()), "EvalMultNoRelin"); }
+    CT EvalMultNoRelin(const CT& a, const CT& b) const {
+        if (be_->deferred && b->db_block >= 0) {   // rotation r of a hoisted query x database ciphertext (sender_diag.cpp:93)
+            std::lock_guard<std::recursive_mutex> g(shim::lazy_mutex());
+            std::shared_ptr<shim::Hoist> H;
+            int rot = -1;
+            if (a->recorded() && a->kind == shim::Node::ROT) {
+                H = a->hoist;
+                rot = a->rot;
+            } else if (!a->recorded()) {           // rotatedQueryCipher[0] = queryCipher[0] (sender_diag.cpp:21)
+                H = a->last_hoist.lock();
+                if (H && H->query_obj == a.get() && H->query_version == a->version) rot = 0;
+            }
+            if (H && rot >= 0) {
+                CT out = std::make_shared<CiphertextImpl<Element>>(be_, nullptr);
+                out->kind = shim::Node::PROD;
+                out->hoist = H;
+                out->rot = rot;
+                out->block = b->db_block;
+                out->diag = b->db_diag;
+                return out;
+            }
+        }
+        return wrap(hx_mult_norelin(a->handle(), b->handle()), "EvalMultNoRelin");
+    }
     CT Relinearize(const CT& a) const { return wrap(hx_relin(a->handle()), "Relinearize"); }
-    void RelinearizeInPlace(CT& a) const { a->reset(shim::check(hx_relin(a->handle()), "RelinearizeInPlace")); }
+    void RelinearizeInPlace(CT& a) const {
+        {
+            std::lock_guard<std::recursive_mutex> g(shim::lazy_mutex());
+            if (a->recorded() && a->kind == shim::Node::SUM) {
+                a->kind = shim::Node::SUM_RELIN;
+                a->version++;
+                return;
+            }
+        }
+        a->reset(shim::check(hx_relin(a->handle()), "RelinearizeInPlace"));
+    }
     CT Rescale(const CT& a) const { return wrap(hx_rescale(a->handle()), "Rescale"); }
-    void RescaleInPlace(CT& a) const { a->reset(shim::check(hx_rescale(a->handle()), "RescaleInPlace")); }
+    void RescaleInPlace(CT& a) const {
+        {   // a complete block: rotation i x diagonal i for i = 0..n-1, summed, relinearised (computeSimilarityMatrix, :66-83)
+            std::lock_guard<std::recursive_mutex> g(shim::lazy_mutex());
+            if (a->recorded() && a->kind == shim::Node::SUM_RELIN) {
+                std::vector<std::pair<int, int>> t = a->terms;
+                std::sort(t.begin(), t.end());
+                bool complete = !t.empty();
+                for (size_t i = 0; i < t.size() && complete; i++) complete = t[i].first == int(i) && t[i].second == int(i);
+                if (complete) {
+                    a->kind = shim::Node::SCORE;
+                    a->ndiag = int(t.size());
+                    a->terms.clear();
+                    a->version++;
+                    a->hoist->pending.push_back(a);
+                    return;
+                }
+            }
+        }
+        a->reset(shim::check(hx_rescale(a->handle()), "RescaleInPlace"));
+    }
     CT ModReduce(const CT& a) const { return Rescale(a); }
     void ModReduceInPlace(CT& a) const { RescaleInPlace(a); }
     CT LevelReduce(const CT& a, const std::shared_ptr<void>&, size_t levels = 1) const {
@@ -335,15 +529,35 @@ public:
         return v[0];
     }
     std::shared_ptr<std::vector<Element>> EvalFastRotationPrecompute(const CT& a) const {
-        hx_digits* d = shim::check(hx_rot_precompute(a->handle()), "EvalFastRotationPrecompute");
+        auto H = std::make_shared<shim::Hoist>();
+        H->be = be_;
+        H->digits = shim::check(hx_rot_precompute(a->handle()), "EvalFastRotationPrecompute");
+        H->query = shim::check(hx_ct_clone(a->handle()), "EvalFastRotationPrecompute");
+        {
+            std::lock_guard<std::recursive_mutex> g(shim::lazy_mutex());
+            H->query_obj = a.get();
+            H->query_version = a->version;
+            a->last_hoist = H;
+        }
         auto out = std::make_shared<std::vector<Element>>(1);
-        (*out)[0].digits = std::shared_ptr<hx_digits>(d, [be = be_](hx_digits* p) { hx_digits_free(p); });
+        (*out)[0].hoist = H;
         return out;
     }
     CT EvalFastRotation(const CT& a, uint32_t index, uint32_t cyclotomic_order, const std::shared_ptr<std::vector<Element>>& digits) const {
         if (cyclotomic_order != uint32_t(2 * be_->N)) throw OpenFHEException("EvalFastRotation: cyclotomic order is not 2N");
-        if (!digits || digits->empty() || !(*digits)[0].digits) throw OpenFHEException("EvalFastRotation: no precomputed digits");
-        return wrap(hx_rot_fast(a->handle(), int(index), (*digits)[0].digits.get()), "EvalFastRotation");
+        if (!digits || digits->empty() || !(*digits)[0].hoist) throw OpenFHEException("EvalFastRotation: no precomputed digits");
+        const std::shared_ptr<shim::Hoist>& H = (*digits)[0].hoist;
+        if (be_->deferred && index != 0) {
+            std::lock_guard<std::recursive_mutex> g(shim::lazy_mutex());
+            if (H->query_obj == a.get() && H->query_version == a->version) {     // the hoisted ciphertext itself: record
+                CT out = std::make_shared<CiphertextImpl<Element>>(be_, nullptr);
+                out->kind = shim::Node::ROT;
+                out->hoist = H;
+                out->rot = int(index);
+                return out;
+            }
+        }
+        return wrap(hx_rot_fast(a->handle(), int(index), H->digits), "EvalFastRotation");
     }
     // EvalChebyshevCoefficients (interpolation at the Chebyshev nodes) then EvalChebyshevSeries (Paterson-Stockmeyer on the device)
     CT EvalChebyshevFunction(const std::function<double(double)>& func, const CT& a, double lo, double hi, uint32_t degree) const {
@@ -420,6 +634,8 @@ inline CryptoContext<DCRTPoly> GenCryptoContext(const CCParams<CryptoContextCKKS
     be->ctx = shim::check(hx_ctx_create(be->N, be->L, be->K, be->dnum, q, pp, psi_q, psi_p, be->scale_bits, dev ? std::atoi(dev) : 0), "GenCryptoContext");
     const char* sync = std::getenv("HYDIA_SYNC_EVERY_CALL");
     be->sync_every_call = sync && std::atoi(sync) != 0;
+    const char* deferred = std::getenv("HYDIA_DEFERRED");
+    be->deferred = !deferred || std::atoi(deferred) != 0;
     return std::make_shared<CryptoContextImpl<DCRTPoly>>(be);
 }
 
@@ -442,9 +658,21 @@ inline std::mutex& table_mutex() {
 template <class ST>
 bool SerializeToFile(const std::string& path, const Ciphertext<DCRTPoly>& ct, const ST&) {
     if (!ct) return false;
-    hx_ct* copy = hx_ct_clone(ct->handle());
-    if (!copy) return false;
-    auto entry = std::make_shared<CiphertextImpl<DCRTPoly>>(ct->backend(), copy);
+    std::shared_ptr<CiphertextImpl<DCRTPoly>> entry;
+    int index = -1, consumed = 0;
+    // serial/db_diagonal/index{block*512+diag}.bin (enroller_diag.cpp:159): goes into the engine's database store, which is what
+    // the fused scoring reads; the table entry is a recipe for a plain copy, used only if a caller touches the ciphertext itself
+    if (std::sscanf(path.c_str(), "serial/db_diagonal/index%d.bin%n", &index, &consumed) == 1 && size_t(consumed) == path.size() && index >= 0 &&
+        hx_db_register_ct(ct->backend()->ctx, index / 512, index % 512, ct->handle()) == 0) {
+        entry = std::make_shared<CiphertextImpl<DCRTPoly>>(ct->backend(), nullptr);
+        entry->kind = shim::Node::DB;
+        entry->db_block = index / 512;
+        entry->db_diag = index % 512;
+    } else {
+        hx_ct* copy = hx_ct_clone(ct->handle());
+        if (!copy) return false;
+        entry = std::make_shared<CiphertextImpl<DCRTPoly>>(ct->backend(), copy);
+    }
     std::lock_guard<std::mutex> g(detail::table_mutex());
     detail::table()[path] = entry;
     return true;

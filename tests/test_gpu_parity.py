@@ -179,6 +179,13 @@ def test_hydia_fused_path_bit_exact_small_ring(golden_dir):
     snd = hx.DiagonalSender(cc, None, 2048, fused=False, db_loader=lambda i: gdb[i])
     per_op = snd.computeSimilarity([gq])
     assert len(per_op) == 1 and same(per_op[0], want[0])
+    # the same path in two steps (what shim/openfhe.h's deferred layer calls): database ciphertexts handed over as device
+    # handles, rotations once, blocks scored against the rotation set in any order; stored ciphertexts read back unchanged
+    cc.db_register_ct(2, 7, gdb[7])
+    assert np.array_equal(cc.db_get(2, 7).to_numpy(), gdb[7].to_numpy()) and same(cc.db_get(1, 3), dbc[512 + 3])
+    scores, rotated = cc.score_blocks(gq, 512, [1, 0], rotations=[0, 1, 300])
+    assert same(scores[0], want[1]) and same(scores[1], want[0])
+    assert all(same(r, orc.rotate(qc, k)) for r, k in zip(rotated, (0, 1, 300)))
 
 
 def test_full_ring_ops_bit_exact():

@@ -108,7 +108,11 @@ def test_reference_timers_with_synchronous_calls(tmp_path):
     assert len(t) == 2
     row = open(tmp_path / "latency.csv").read().strip().split(",")
     assert row[0] == "Diagonal" and row[1] == "1024" and "true" in row
-    print("reference-timed, unmodified per-op sender on B200: membership %.3f s (first call: includes warm-up), index %.3f s" % (t[0], t[1]))
+    print("reference-timed, unmodified sender on B200 (deferred layer -> fused kernels): membership %.3f s (first call: includes warm-up), index %.3f s" % (t[0], t[1]))
+    r2 = run_reference(tmp_path, 5, env={"HYDIA_SYNC_EVERY_CALL": "1", "HYDIA_DEFERRED": "0"})
+    assert r2.returncode == 0 and parse(r2.stdout) == ("true", [0])
+    t2 = [float(x) for x in re.findall(r"Computing \w+ scenario\.\.\. done \(([0-9.e+-]+)s\)", r2.stdout)]
+    print("same with HYDIA_DEFERRED=0 (every call issued as it comes): membership %.3f s, index %.3f s" % (t2[0], t2[1]))
 
 
 ACC = os.path.join(ROOT, "shim", "_ref", "ImageMatchingAccuracy")

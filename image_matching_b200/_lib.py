@@ -74,6 +74,7 @@ SIGNATURES = {
     "hx_inner_product": (VP, [VP, VP, C.c_int]),
     "hx_client_encode": (C.c_int, [VP, F64P, C.c_int, U64P]),
     "hx_score_hers": (C.c_int, [VP, C.POINTER(VP), C.c_int, C.POINTER(VP), C.c_int]),
+    "hx_score_hers_blocks": (C.c_int, [VP, C.POINTER(VP), C.c_int, I32P, C.c_int, C.POINTER(VP)]),
     "hx_compare_many": (C.c_int, [VP, C.POINTER(VP), C.c_int, C.c_double, C.c_int, C.POINTER(VP)]),
     "hx_ntt": (C.c_int, [VP, U64P, C.c_int, I32P, C.c_int, C.c_int]),
     "hx_params_generate": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, I32P, I32P, I32P, I32P, U64P, U64P, U64P, U64P]),

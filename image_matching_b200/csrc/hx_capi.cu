@@ -210,6 +210,14 @@ int hx_score_diag(hx_ctx* ctx, hx_ct* query, int ndiag, hx_ct** out, int max_out
 hx_ct* hx_membership(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sign_depth) {
     HX_TRY_PTR(need(ctx, "ctx"); need(query, "query"); return wrap(ctx->eng->membership(query->ct, ndiag, delta, sign_depth));)
 }
+int hx_score_hers_blocks(hx_ctx* ctx, hx_ct* const* query, int nquery, const int* matrices, int nmatrices, hx_ct** out) {
+    HX_TRY_INT(need(ctx, "ctx"); need(query, "query"); need(matrices, "matrices"); need(out, "out");
+               std::vector<Ct> q;
+               for (int i = 0; i < nquery; i++) { need(query[i], "query[i]"); q.push_back(query[i]->ct); }
+               std::vector<int> ids(matrices, matrices + nmatrices);
+               std::vector<Ct> s = ctx->eng->score_hers(q, &ids);
+               for (size_t i = 0; i < s.size(); i++) out[i] = wrap(s[i]);)
+}
 hx_ct* hx_ct_stack(hx_ct* const* cts, int n) {
     HX_TRY_PTR(need(cts, "cts"); if (n <= 0) throw std::runtime_error("hx_ct_stack: empty input");
                std::vector<Ct> v; for (int i = 0; i < n; i++) { need(cts[i], "cts[i]"); v.push_back(cts[i]->ct); }

@@ -172,7 +172,7 @@ public:
     std::vector<Ct> index(const Ct& query, int ndiag, double delta, int depth);   // indexScenario
     // ---- HERS (approach 4) scoring, sender_hers.cpp:13-98: query = one ciphertext per coordinate, database matrix m =
     // registered block m (index j = "diagonal" j).  One score ciphertext per matrix.
-    std::vector<Ct> score_hers(const std::vector<Ct>& query);
+    std::vector<Ct> score_hers(const std::vector<Ct>& query, const std::vector<int>* matrices = nullptr /*null: all registered*/);
     // chebyshevCompare of many ciphertexts of one shape as batches (the OpenMP loops of sender_*.cpp over scoreCipher)
     std::vector<Ct> compare_many(const std::vector<Ct>& cts, double delta, int depth);
 

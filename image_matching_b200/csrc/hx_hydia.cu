@@ -193,7 +193,7 @@ Ct Engine::membership(const Ct& query, int ndiag, double delta, int depth) {
 // tensor-product launch against the HBM-resident database, one batched relinearisation (same EvalMultKey, 32
 // digit sets), one batched rescale, one modular sum over the batch.  Modular addition is associative and
 // commutative, so the result equals the reference's sequential EvalAddInPlace chain bit for bit.
-std::vector<Ct> Engine::score_hers(const std::vector<Ct>& query) {
+std::vector<Ct> Engine::score_hers(const std::vector<Ct>& query, const std::vector<int>* matrices) {
     std::lock_guard<std::recursive_mutex> g(mu);
     if (query.empty()) throw std::runtime_error("score_hers: empty query");
     if (db_.empty()) throw std::runtime_error("score_hers: no database matrix registered");
@@ -204,7 +204,17 @@ std::vector<Ct> Engine::score_hers(const std::vector<Ct>& query) {
     if (!(fused_ks_supported(logN) && !force_unfused)) throw std::runtime_error("score_hers needs the fused pipeline");
     const size_t cs = (size_t)nl * N;
     std::vector<Ct> out;
-    for (auto& kv : db_) {
+    std::vector<std::pair<int, DbBlock>> todo;
+    if (matrices) {
+        for (int id : *matrices) {
+            auto it = db_.find(id);
+            if (it == db_.end()) throw std::runtime_error("score_hers: database matrix not registered");
+            todo.emplace_back(it->first, it->second);
+        }
+    } else {
+        for (auto& kv : db_) todo.emplace_back(kv.first, kv.second);
+    }
+    for (auto& kv : todo) {
         if (kv.second.ndiag < dim) throw std::runtime_error("score_hers: database matrix has fewer columns than the query");
         Ct acc = new_ct(2, nl - 1, query[0]->level + 1, query[0]->deg + 1 - 1);
         for (int i0 = 0; i0 < dim; i0 += kMaxKsBatch) {

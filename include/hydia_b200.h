@@ -142,6 +142,8 @@ int hx_ct_unstack(hx_ct* ct, hx_ct** out, int max_out);  /* returns the number o
  * serial/db_hers/matrix{m}/index{j}.bin, registered with hx_db_register(ctx, m, j, data).  Per matrix:
  * sum_j Rescale(Relinearize(EvalMultNoRelin(query[j], db[m][j]))).  Returns the number of matrices. */
 int hx_score_hers(hx_ctx* ctx, hx_ct* const* query, int nquery, hx_ct** out, int max_out);
+/* same for the listed matrices only (computeSimilarityHelper, sender_hers.cpp:61-86); out: nmatrices handles */
+int hx_score_hers_blocks(hx_ctx* ctx, hx_ct* const* query, int nquery, const int* matrices, int nmatrices, hx_ct** out);
 /* OpenFHEWrapper::chebyshevCompare over a vector of score ciphertexts (the "#pragma omp parallel for" loops of
  * sender_hers.cpp:33-36, sender_diag.cpp:40-43, ...): all n inputs go through one batched chain. out: n handles. */
 int hx_compare_many(hx_ctx* ctx, hx_ct* const* in, int n, double delta, int sign_depth, hx_ct** out);

@@ -224,7 +224,13 @@ struct Hoist {
     }
 };
 struct Node {
-    enum Kind { READY, DB, ROT, PROD, SUM, SUM_RELIN, SCORE };
+    enum Kind { READY, DB, ROT, PROD, SUM, SUM_RELIN, SCORE,      // DiagonalSender (approach 5)
+                HPROD, HPROD_RELIN, HTERM, HSUM };                // HersSender (approach 4)
+    struct HersTerm {                  // Rescale(Relinearize(EvalMultNoRelin(query, database[block][diag])))
+        std::shared_ptr<Node> query;
+        uint64_t query_version;
+        int diag;
+    };
     Node(std::shared_ptr<Backend> b, hx_ct* handle) : be(std::move(b)), h(handle) {}
     Node(const Node&) = delete;
     Node& operator=(const Node&) = delete;
@@ -240,7 +246,9 @@ struct Node {
         kind = READY;
         hoist.reset();
         terms.clear();
+        hterms.clear();
         db_block = db_diag = -1;
+        db_layout = 0;
         version++;
         if (be->sync_every_call) check(hx_ctx_sync(be->ctx), "InPlace");
     }
@@ -252,7 +260,9 @@ struct Node {
     std::shared_ptr<Hoist> hoist;                  // ROT / PROD / SUM / SUM_RELIN / SCORE
     int rot = 0, block = -1, diag = -1, ndiag = 0; // ROT: rot; PROD: rot, block, diag; SUM..: block; SCORE: block, ndiag
     std::vector<std::pair<int, int>> terms;        // SUM / SUM_RELIN: (rotation, diagonal) of every product
-    int db_block = -1, db_diag = -1;               // database ciphertext serial/db_diagonal/index{db_block*512+db_diag}.bin
+    std::vector<HersTerm> hterms;                  // HPROD..HSUM: the recorded products of one database matrix (block)
+    int db_block = -1, db_diag = -1;               // database ciphertext: serial/db_diagonal/index{db_block*512+db_diag}.bin (layout 1)
+    int db_layout = 0;                             //                   or serial/db_hers/matrix{db_block}/index{db_diag}.bin (layout 2)
     uint64_t version = 0;
     std::weak_ptr<Hoist> last_hoist;               // set on a query by EvalFastRotationPrecompute
 
@@ -288,6 +298,50 @@ private:
         }
         H->pending.clear();
     }
+    // HersSender::computeSimilarityHelper (sender_hers.cpp:61-86). A complete matrix (column i of the query against
+    // database column i, i = 0..n-1) goes through hx_score_hers_blocks; anything else runs term by term.
+    hx_ct* hers() {
+        for (const HersTerm& t : hterms)
+            if (t.query->version != t.query_version) throw OpenFHEException("deferred HERS score: a query ciphertext changed after it was recorded");
+        if (kind == HSUM) {
+            std::vector<HersTerm> t = hterms;
+            std::sort(t.begin(), t.end(), [](const HersTerm& a, const HersTerm& b) { return a.diag < b.diag; });
+            bool complete = true;
+            for (size_t i = 0; i < t.size() && complete; i++) complete = t[i].diag == int(i);
+            if (complete) {
+                std::vector<hx_ct*> q;
+                for (const HersTerm& x : t) q.push_back(x.query->get());
+                hx_ct* out = nullptr;
+                if (hx_score_hers_blocks(be->ctx, q.data(), int(q.size()), &block, 1, &out) == 0) return out;
+            }
+        }
+        hx_ct* acc = nullptr;
+        for (const HersTerm& t : hterms) {
+            hx_ct* b = check(hx_db_get(be->ctx, block, t.diag), "database ciphertext");
+            hx_ct* p = hx_mult_norelin(t.query->get(), b);
+            hx_ct_free(b);
+            check(p, "EvalMultNoRelin");
+            if (kind != HPROD) {
+                hx_ct* r = hx_relin(p);
+                hx_ct_free(p);
+                p = check(r, "RelinearizeInPlace");
+            }
+            if (kind == HTERM || kind == HSUM) {
+                hx_ct* r = hx_rescale(p);
+                hx_ct_free(p);
+                p = check(r, "RescaleInPlace");
+            }
+            if (!acc) {
+                acc = p;
+            } else {
+                hx_ct* sum = hx_add(acc, p);
+                hx_ct_free(acc);
+                hx_ct_free(p);
+                acc = check(sum, "EvalAddInPlace");
+            }
+        }
+        return acc;
+    }
     hx_ct* materialise() {
         std::lock_guard<std::recursive_mutex> g(lazy_mutex());
         if (hx_ct* p = h.load(std::memory_order_acquire)) return p;
@@ -316,12 +370,17 @@ private:
                 score_pending();
                 out = h.load(std::memory_order_acquire);
                 break;
+            case HPROD:
+            case HPROD_RELIN:
+            case HTERM:
+            case HSUM: out = hers(); break;
             default: throw OpenFHEException("ciphertext without a value");
         }
         h.store(out, std::memory_order_release);
         kind = READY;
         hoist.reset();
         terms.clear();
+        hterms.clear();
         return out;
     }
 };
@@ -420,6 +479,13 @@ public:
     void EvalAddInPlace(CT& a, const CT& b) const {
         {   // recorded: product (+ product)* of one hoist against one database block (sender_diag.cpp:75-77)
             std::lock_guard<std::recursive_mutex> g(shim::lazy_mutex());
+            if (a->recorded() && b->recorded() && (a->kind == shim::Node::HTERM || a->kind == shim::Node::HSUM) && b->kind == shim::Node::HTERM &&
+                a->block == b->block) {                       // sender_hers.cpp:75-77
+                a->hterms.push_back(b->hterms[0]);
+                a->kind = shim::Node::HSUM;
+                a->version++;
+                return;
+            }
             if (a->recorded() && b->recorded() && (a->kind == shim::Node::PROD || a->kind == shim::Node::SUM) && b->kind == shim::Node::PROD &&
                 a->hoist == b->hoist && a->block == b->block) {
                 if (a->kind == shim::Node::PROD) {
@@ -445,7 +511,15 @@ public:
     }
     CT EvalMult(const Plaintext& pt, const CT& a) const { return EvalMult(a, pt); }
     CT EvalMultNoRelin(const CT& a, const CT& b) const {
-        if (be_->deferred && b->db_block >= 0) {   // rotation r of a hoisted query x database ciphertext (sender_diag.cpp:93)
+        if (be_->deferred && b->db_layout == 2 && !a->recorded()) {   // query column x database column (sender_hers.cpp:97)
+            std::lock_guard<std::recursive_mutex> g(shim::lazy_mutex());
+            CT out = std::make_shared<CiphertextImpl<Element>>(be_, nullptr);
+            out->kind = shim::Node::HPROD;
+            out->block = b->db_block;
+            out->hterms.push_back(shim::Node::HersTerm{a, a->version, b->db_diag});
+            return out;
+        }
+        if (be_->deferred && b->db_layout == 1) {   // rotation r of a hoisted query x database ciphertext (sender_diag.cpp:93)
             std::lock_guard<std::recursive_mutex> g(shim::lazy_mutex());
             std::shared_ptr<shim::Hoist> H;
             int rot = -1;
@@ -472,8 +546,8 @@ public:
     void RelinearizeInPlace(CT& a) const {
         {
             std::lock_guard<std::recursive_mutex> g(shim::lazy_mutex());
-            if (a->recorded() && a->kind == shim::Node::SUM) {
-                a->kind = shim::Node::SUM_RELIN;
+            if (a->recorded() && (a->kind == shim::Node::SUM || a->kind == shim::Node::HPROD)) {
+                a->kind = a->kind == shim::Node::SUM ? shim::Node::SUM_RELIN : shim::Node::HPROD_RELIN;
                 a->version++;
                 return;
             }
@@ -484,6 +558,11 @@ public:
     void RescaleInPlace(CT& a) const {
         {   // a complete block: rotation i x diagonal i for i = 0..n-1, summed, relinearised (computeSimilarityMatrix, :66-83)
             std::lock_guard<std::recursive_mutex> g(shim::lazy_mutex());
+            if (a->recorded() && a->kind == shim::Node::HPROD_RELIN) {
+                a->kind = shim::Node::HTERM;
+                a->version++;
+                return;
+            }
             if (a->recorded() && a->kind == shim::Node::SUM_RELIN) {
                 std::vector<std::pair<int, int>> t = a->terms;
                 std::sort(t.begin(), t.end());
@@ -659,7 +738,7 @@ template <class ST>
 bool SerializeToFile(const std::string& path, const Ciphertext<DCRTPoly>& ct, const ST&) {
     if (!ct) return false;
     std::shared_ptr<CiphertextImpl<DCRTPoly>> entry;
-    int index = -1, consumed = 0;
+    int index = -1, matrix = -1, consumed = 0;
     // serial/db_diagonal/index{block*512+diag}.bin (enroller_diag.cpp:159): goes into the engine's database store, which is what
     // the fused scoring reads; the table entry is a recipe for a plain copy, used only if a caller touches the ciphertext itself
     if (std::sscanf(path.c_str(), "serial/db_diagonal/index%d.bin%n", &index, &consumed) == 1 && size_t(consumed) == path.size() && index >= 0 &&
@@ -668,6 +747,15 @@ bool SerializeToFile(const std::string& path, const Ciphertext<DCRTPoly>& ct, co
         entry->kind = shim::Node::DB;
         entry->db_block = index / 512;
         entry->db_diag = index % 512;
+        entry->db_layout = 1;
+    } else if (std::sscanf(path.c_str(), "serial/db_hers/matrix%d/index%d.bin%n", &matrix, &index, &consumed) == 2 &&
+               size_t(consumed) == path.size() && matrix >= 0 && index >= 0 && index < 512 &&
+               hx_db_register_ct(ct->backend()->ctx, matrix, index, ct->handle()) == 0) {     // enroller_hers.cpp:116-121
+        entry = std::make_shared<CiphertextImpl<DCRTPoly>>(ct->backend(), nullptr);
+        entry->kind = shim::Node::DB;
+        entry->db_block = matrix;
+        entry->db_diag = index;
+        entry->db_layout = 2;
     } else {
         hx_ct* copy = hx_ct_clone(ct->handle());
         if (!copy) return false;

@@ -151,3 +151,16 @@ def test_reference_accuracy_main_unmodified_two_blocks(tmp_path):
     assert all(a == b for a, b in tally.values()), tally            # encrypted decisions == plaintext decisions
     assert tally["true positives"][0] == n // nsubj and tally["false positives"][0] == 0
     assert sum(a for a, _ in tally.values()) == n
+
+
+SELF = os.path.join(ROOT, "shim", "_ref", "shim_deferred_parity")
+
+
+@pytest.mark.skipif(not os.path.exists(SELF), reason="shim/_ref/shim_deferred_parity not built (make -C shim selftest)")
+@pytest.mark.gpu
+@pytest.mark.timeout(600)
+def test_deferred_layer_is_bit_identical_to_call_by_call_execution():
+    """tests/cpp/shim_deferred_parity.cpp: the DiagonalSender / HersSender call patterns and their fall-backs through the shim,
+    layer on vs HYDIA_DEFERRED=0, every output ciphertext compared word for word."""
+    r = subprocess.run([SELF], capture_output=True, text=True, timeout=500)
+    assert r.returncode == 0 and r.stdout.startswith("OK"), (r.stdout[-800:], r.stderr[-800:])

@@ -69,6 +69,7 @@ struct Backend {
     int N = 0, L = 0, K = 0, dnum = 0, scale_bits = 0;
     bool sync_every_call = false;
     bool deferred = true;     // HYDIA_DEFERRED=0: every call is issued as it comes (pure per-op path)
+    bool chains = true;       // HYDIA_DEFERRED=2 (default unless calls are synchronous): compare chains are recorded and batched too
     ~Backend() {
         if (client) hx_client_destroy(client);
         if (ctx) hx_ctx_destroy(ctx);
@@ -225,7 +226,14 @@ struct Hoist {
 };
 struct Node {
     enum Kind { READY, DB, ROT, PROD, SUM, SUM_RELIN, SCORE,      // DiagonalSender (approach 5)
-                HPROD, HPROD_RELIN, HTERM, HSUM };                // HersSender (approach 4)
+                HPROD, HPROD_RELIN, HTERM, HSUM,                  // HersSender (approach 4)
+                CHAIN };                                          // EvalChebyshevFunction / EvalPoly / + constant on one input
+    struct UnaryOp {                   // one step of OpenFHEWrapper::chebyshevCompare (openFHE_wrapper.cpp:174-182)
+        enum Type { CHEB, POLY, ADDC } type;
+        std::vector<double> coeffs;
+        double lo = 0, hi = 0, c = 0;
+        bool operator==(const UnaryOp& o) const { return type == o.type && coeffs == o.coeffs && lo == o.lo && hi == o.hi && c == o.c; }
+    };
     struct HersTerm {                  // Rescale(Relinearize(EvalMultNoRelin(query, database[block][diag])))
         std::shared_ptr<Node> query;
         uint64_t query_version;
@@ -247,6 +255,8 @@ struct Node {
         hoist.reset();
         terms.clear();
         hterms.clear();
+        src.reset();
+        ops.clear();
         db_block = db_diag = -1;
         db_layout = 0;
         version++;
@@ -260,6 +270,13 @@ struct Node {
     std::shared_ptr<Hoist> hoist;                  // ROT / PROD / SUM / SUM_RELIN / SCORE
     int rot = 0, block = -1, diag = -1, ndiag = 0; // ROT: rot; PROD: rot, block, diag; SUM..: block; SCORE: block, ndiag
     std::vector<std::pair<int, int>> terms;        // SUM / SUM_RELIN: (rotation, diagonal) of every product
+    std::shared_ptr<Node> src;                     // CHAIN: the input, and the steps applied to it
+    uint64_t src_version = 0;
+    std::vector<UnaryOp> ops;
+    static std::vector<std::weak_ptr<Node>>& chains() {      // every recorded chain (never destroyed, see Serial::detail::table)
+        static auto* v = new std::vector<std::weak_ptr<Node>>();
+        return *v;
+    }
     std::vector<HersTerm> hterms;                  // HPROD..HSUM: the recorded products of one database matrix (block)
     int db_block = -1, db_diag = -1;               // database ciphertext: serial/db_diagonal/index{db_block*512+db_diag}.bin (layout 1)
     int db_layout = 0;                             //                   or serial/db_hers/matrix{db_block}/index{db_diag}.bin (layout 2)
@@ -297,6 +314,71 @@ private:
             nodes[i]->kind = READY;
         }
         H->pending.clear();
+    }
+    // The compare loops of the senders ("#pragma omp parallel for" over scoreCipher, sender_diag.cpp:40-43, sender_hers.cpp:33-36)
+    // apply one chain of steps to many ciphertexts of one shape. All recorded chains with the same steps run as ONE batched
+    // ciphertext (hx_ct_stack, the steps, hx_ct_unstack): the same operations per entry, so the same bits.
+    static hx_ct* apply(hx_ct* in, const std::vector<UnaryOp>& steps) {
+        hx_ct* cur = in;
+        for (const UnaryOp& op : steps) {
+            hx_ct* next = op.type == UnaryOp::CHEB   ? hx_cheby_series(cur, op.coeffs.data(), int(op.coeffs.size()), op.lo, op.hi)
+                          : op.type == UnaryOp::POLY ? hx_poly(cur, op.coeffs.data(), int(op.coeffs.size()))
+                                                     : hx_add_const(cur, op.c);
+            if (cur != in) hx_ct_free(cur);
+            cur = check(next, op.type == UnaryOp::CHEB ? "EvalChebyshevFunction" : op.type == UnaryOp::POLY ? "EvalPoly" : "EvalAddInPlace");
+        }
+        return cur == in ? check(hx_ct_clone(in), "clone") : cur;
+    }
+    void chain() {
+        constexpr size_t kMaxBatch = 32;
+        std::vector<std::weak_ptr<Node>>& reg = chains();
+        std::vector<std::shared_ptr<Node>> group;
+        std::vector<std::weak_ptr<Node>> keep;
+        for (auto& w : reg)
+            if (std::shared_ptr<Node> n = w.lock())
+                if (n->kind == CHAIN && n->recorded()) {
+                    if (n.get() != this && n->be == be && n->ops == ops && group.size() + 1 < kMaxBatch) group.push_back(n);
+                    else if (n.get() != this) keep.push_back(w);
+                }
+        reg.swap(keep);
+        auto shape = [](hx_ct* c) {
+            int v[4] = {0, 0, 0, 0};
+            check(hx_ct_info(c, &v[0], &v[1], &v[2], &v[3]), "Ciphertext getter");
+            return std::vector<int>(v, v + 4);
+        };
+        if (src->version != src_version) throw OpenFHEException("deferred chain: the input ciphertext changed after it was recorded");
+        hx_ct* mine = src->get();
+        const std::vector<int> want = shape(mine);
+        std::vector<Node*> nodes{this};
+        std::vector<hx_ct*> in{mine};
+        std::vector<std::shared_ptr<Node>> alive;        // keeps the siblings alive while their results are produced
+        for (auto& n : group) {
+            if (n->src->version != n->src_version) { reg.push_back(n); continue; }
+            hx_ct* x = n->src->get();
+            if (shape(x) != want) { reg.push_back(n); continue; }
+            nodes.push_back(n.get());
+            in.push_back(x);
+            alive.push_back(n);
+        }
+        std::vector<hx_ct*> out(nodes.size(), nullptr);
+        if (nodes.size() == 1) {
+            out[0] = apply(mine, ops);
+        } else {
+            hx_ct* batch = check(hx_ct_stack(in.data(), int(in.size())), "batch");
+            hx_ct* res = apply(batch, ops);
+            hx_ct_free(batch);
+            int n = hx_ct_unstack(res, out.data(), int(out.size()));
+            hx_ct_free(res);
+            if (n != int(out.size())) throw OpenFHEException(std::string("batched chain: ") + hx_last_error());
+        }
+        for (size_t i = 0; i < nodes.size(); i++) {
+            nodes[i]->h.store(out[i], std::memory_order_release);
+            if (nodes[i] != this) {
+                nodes[i]->kind = READY;
+                nodes[i]->src.reset();
+                nodes[i]->ops.clear();
+            }
+        }
     }
     // HersSender::computeSimilarityHelper (sender_hers.cpp:61-86). A complete matrix (column i of the query against
     // database column i, i = 0..n-1) goes through hx_score_hers_blocks; anything else runs term by term.
@@ -374,6 +456,10 @@ private:
             case HPROD_RELIN:
             case HTERM:
             case HSUM: out = hers(); break;
+            case CHAIN:
+                chain();
+                out = h.load(std::memory_order_acquire);
+                break;
             default: throw OpenFHEException("ciphertext without a value");
         }
         h.store(out, std::memory_order_release);
@@ -381,6 +467,8 @@ private:
         hoist.reset();
         terms.clear();
         hterms.clear();
+        src.reset();
+        ops.clear();
         return out;
     }
 };
@@ -499,7 +587,20 @@ public:
         }
         a->reset(shim::check(hx_add(a->handle(), b->handle()), "EvalAddInPlace"));
     }
-    void EvalAddInPlace(CT& a, double c) const { a->reset(shim::check(hx_add_const(a->handle(), c), "EvalAddInPlace")); }
+    void EvalAddInPlace(CT& a, double c) const {
+        {
+            std::lock_guard<std::recursive_mutex> g(shim::lazy_mutex());
+            if (a->recorded() && a->kind == shim::Node::CHAIN) {
+                shim::Node::UnaryOp op;
+                op.type = shim::Node::UnaryOp::ADDC;
+                op.c = c;
+                a->ops.push_back(op);
+                a->version++;
+                return;
+            }
+        }
+        a->reset(shim::check(hx_add_const(a->handle(), c), "EvalAddInPlace"));
+    }
     CT EvalSub(const CT& a, const CT& b) const { return wrap(hx_sub(a->handle(), b->handle()), "EvalSub"); }
     CT EvalSub(const CT& a, double c) const { return wrap(hx_add_const(a->handle(), -c), "EvalSub"); }
     void EvalSubInPlace(CT& a, const CT& b) const { a->reset(shim::check(hx_sub(a->handle(), b->handle()), "EvalSubInPlace")); }
@@ -643,9 +744,23 @@ public:
         return EvalChebyshevSeries(a, ChebyshevCoefficients(func, lo, hi, degree), lo, hi);
     }
     CT EvalChebyshevSeries(const CT& a, const std::vector<double>& coeffs, double lo, double hi) const {
+        if (be_->chains) {
+            shim::Node::UnaryOp op;
+            op.type = shim::Node::UnaryOp::CHEB;
+            op.coeffs = coeffs;
+            op.lo = lo;
+            op.hi = hi;
+            return chain(a, op);
+        }
         return wrap(hx_cheby_series(a->handle(), coeffs.data(), int(coeffs.size()), lo, hi), "EvalChebyshevSeries");
     }
     CT EvalPoly(const CT& a, const std::vector<double>& coeffs) const {
+        if (be_->chains) {
+            shim::Node::UnaryOp op;
+            op.type = shim::Node::UnaryOp::POLY;
+            op.coeffs = coeffs;
+            return chain(a, op);
+        }
         return wrap(hx_poly(a->handle(), coeffs.data(), int(coeffs.size())), "EvalPoly");
     }
     static std::vector<double> ChebyshevCoefficients(const std::function<double(double)>& func, double lo, double hi, uint32_t degree) {
@@ -671,6 +786,23 @@ public:
     template <class ST> bool DeserializeEvalAutomorphismKey(std::istream& is, const ST&) const { return is.good(); }
 
 private:
+    // a new recorded ciphertext = `a` followed by one more step (a's own steps are copied when `a` is still a recorded chain)
+    CT chain(const CT& a, const shim::Node::UnaryOp& op) const {
+        std::lock_guard<std::recursive_mutex> g(shim::lazy_mutex());
+        CT out = std::make_shared<CiphertextImpl<Element>>(be_, nullptr);
+        out->kind = shim::Node::CHAIN;
+        if (a->recorded() && a->kind == shim::Node::CHAIN) {
+            out->src = a->src;
+            out->src_version = a->src_version;
+            out->ops = a->ops;
+        } else {
+            out->src = a;
+            out->src_version = a->version;
+        }
+        out->ops.push_back(op);
+        shim::Node::chains().push_back(out);
+        return out;
+    }
     static bool marker(std::ostream& os) {
         os << "hydia-b200: evaluation keys are resident in HBM\n";
         return os.good();
@@ -715,6 +847,10 @@ inline CryptoContext<DCRTPoly> GenCryptoContext(const CCParams<CryptoContextCKKS
     be->sync_every_call = sync && std::atoi(sync) != 0;
     const char* deferred = std::getenv("HYDIA_DEFERRED");
     be->deferred = !deferred || std::atoi(deferred) != 0;
+    // A recorded compare chain may leave the sender's scenario function unevaluated (indexScenario returns its outputs) and
+    // complete when the receiver reads it; with synchronous calls that would move work out of the reference's timers, so
+    // chains are then recorded only on request (HYDIA_DEFERRED=2).
+    be->chains = be->deferred && (deferred ? std::atoi(deferred) >= 2 : !be->sync_every_call);
     return std::make_shared<CryptoContextImpl<DCRTPoly>>(be);
 }
 

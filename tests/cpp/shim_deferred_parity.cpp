@@ -22,7 +22,7 @@ static std::vector<uint64_t> bits(const CT& c) {
 }
 
 static std::vector<std::vector<uint64_t>> run(bool deferred) {
-    setenv("HYDIA_DEFERRED", deferred ? "1" : "0", 1);
+    setenv("HYDIA_DEFERRED", deferred ? "2" : "0", 1);
     const int ndiag = 8, nblocks = 2, ncols = 6;
     CCParams<CryptoContextCKKSRNS> params;
     params.SetSecurityLevel(HEStd_128_classic);
@@ -73,6 +73,19 @@ static std::vector<std::vector<uint64_t>> run(bool deferred) {
             cc->RelinearizeInPlace(s[0]);
             cc->RescaleInPlace(s[0]);
             scores.push_back(s[0]);
+        }
+        if (skip < 0) {      // the compare loop of sender_diag.cpp:40-43 over both block scores (recorded chains -> one batch)
+            std::vector<CT> cmp;
+            for (const CT& sc : scores) {
+                CT c = cc->EvalChebyshevFunction([](double x) -> double { return x >= 0.44 ? 1 : -1; }, sc, -1, 1, 59);
+                c = cc->EvalPoly(c, {0.0, 315.0 / 128.0, 0.0, -420.0 / 128.0, 0.0, 378.0 / 128.0, 0.0, -180.0 / 128.0, 0.0, 35.0 / 128.0});
+                cc->EvalAddInPlace(c, 1.0);
+                cmp.push_back(c);
+            }
+            out.push_back(bits(cmp[1]));
+            out.push_back(bits(cmp[0]));
+            CT lone = cc->EvalPoly(scores[0], {0.5, 0.25, 0.125, 0.0, 0.03, 0.0, 0.01});      // a chain of its own kind: runs alone
+            out.push_back(bits(lone));
         }
         out.push_back(bits(scores[1]));
         out.push_back(bits(scores[0]));

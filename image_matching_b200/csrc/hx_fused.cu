@@ -58,6 +58,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_p_inner(const __gr
 #pragma unroll
         for (int j = 0; j < NDIG; j++) bulk_g2s(kst + j * kTileN, key + j * kstride, kTileBytes, mbar);
     }
+    pdl_wait();      // the evaluation keys above are static; everything below reads the previous kernels' output
     __syncthreads();
     mbar_wait(mbar, 0);
 #pragma unroll
@@ -108,6 +109,7 @@ static TabSet single_table(const BaseConvTable* tab) {
 template <int LOGN>
 __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_cols(const __grid_constant__ DevTables T, const __grid_constant__ TabSet ts,
                                                               u64* __restrict__ data, size_t bs) {
+    pdl_wait();
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, tile = blockIdx.x;
     u64* const smp = sm + tphys(2 * t);   // this thread's element pairs: smp[u * kPairStep + {0,1}]
@@ -144,6 +146,7 @@ template <int LOGN>
 __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __grid_constant__ DevTables T, const __grid_constant__ TabSet ts,
                                                                   const u64* __restrict__ in, size_t in_bs, u64* __restrict__ out, size_t out_bs,
                                                                   int ext_nl, int L, int jgroup) {
+    pdl_wait();
     using G = NttGeo<LOGN>;
     extern __shared__ __align__(128) unsigned char smraw[];
     u64* sm = reinterpret_cast<u64*>(smraw);
@@ -205,7 +208,7 @@ static void launch_conv_fwd_col(const DevTables& T, const TabSet& ts, int max_n_
         cudaFuncSetAttribute(k_conv_fwd_col<LOGN>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
         attr_bytes = bytes;
     }
-    k_conv_fwd_col<LOGN><<<dim3(NttGeo<LOGN>::TILES, ny, nbatch), kTileThreads, bytes, st>>>(T, ts, in, in_bs, out, out_bs, ext_nl, L, jgroup);
+    launch_pdl(k_conv_fwd_col<LOGN>, dim3(NttGeo<LOGN>::TILES, ny, nbatch), dim3(kTileThreads), bytes, st, T, ts, in, in_bs, out, out_bs, ext_nl, L, jgroup);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -242,6 +245,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __g
 #pragma unroll
         for (int j = 0; j < NDIG; j++) bulk_g2s(kst + j * kTileN, key + j * kstride, kTileBytes, mbar);
     }
+    pdl_wait();      // the evaluation keys above are static; everything below reads the previous kernels' output
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
@@ -299,13 +303,13 @@ static void launch_fused_tn(const DevTables& T, const FusedKsArgs& a, const Base
         cudaFuncSetAttribute(k_ks_q_finish<LOGN, NDIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ks_smem_bytes(NDIG));
         attr_done = true;
     }
-    k_ks_p_inner<LOGN, NDIG><<<dim3(G::TILES, 2 * a.K, nb), kTileThreads, ks_smem_bytes(NDIG), st>>>(T, a);
+    launch_pdl(k_ks_p_inner<LOGN, NDIG>, dim3(G::TILES, 2 * a.K, nb), dim3(kTileThreads), ks_smem_bytes(NDIG), st, T, a);
     const TabSet ts = single_table(moddown);
-    k_inv_cols<LOGN><<<dim3(G::TILES, a.K, nb * 2), kTileThreads, 0, st>>>(T, ts, a.tmpP, (size_t)a.K * T.N);
+    launch_pdl(k_inv_cols<LOGN>, dim3(G::TILES, a.K, nb * 2), dim3(kTileThreads), 0, st, T, ts, a.tmpP, (size_t)a.K * T.N);
     // large batches: 4 target limbs per CTA share one staging of the K source tiles
     const int jg = (nb * 2 >= 16) ? 4 : 1;
     launch_conv_fwd_col<LOGN>(T, ts, a.K, (a.nl + jg - 1) / jg, nb * 2, a.tmpP, (size_t)a.K * T.N, a.conv, (size_t)a.nl * T.N, -1, 0, jg, st);
-    k_ks_q_finish<LOGN, NDIG><<<dim3(G::TILES, 2 * a.nl, nb), kTileThreads, ks_smem_bytes(NDIG), st>>>(T, a);
+    launch_pdl(k_ks_q_finish<LOGN, NDIG>, dim3(G::TILES, 2 * a.nl, nb), dim3(kTileThreads), ks_smem_bytes(NDIG), st, T, a);
 }
 template <int LOGN>
 static void launch_fused_t(const DevTables& T, const FusedKsArgs& a, const BaseConvTable* moddown, int nb, cudaStream_t st) {
@@ -327,6 +331,7 @@ static void launch_fused_t(const DevTables& T, const FusedKsArgs& a, const BaseC
 template <int LOGN>
 __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_rows(const __grid_constant__ DevTables T, const u64* __restrict__ in, size_t in_bs,
                                                               u64* __restrict__ out, size_t out_bs, int prime0) {
+    pdl_wait();
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, tile = blockIdx.x, prime = prime0 + blockIdx.y;
     u64* const smp = sm + tphys(2 * t);   // this thread's element pairs: smp[u * kPairStep + {0,1}]
@@ -356,6 +361,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_rows(const __grid
 template <int LOGN>
 __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_modup_rows(const __grid_constant__ DevTables T, u64* __restrict__ digits, const u64* __restrict__ c,
                                                                 size_t c_bs, int ndig, int nl, int L, int alpha) {
+    pdl_wait();
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, tile = blockIdx.x, y = blockIdx.y;
     u64* const smp = sm + tphys(2 * t);   // this thread's element pairs: smp[u * kPairStep + {0,1}]
@@ -402,6 +408,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_modup_rows(const __gr
 template <int LOGN>
 __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_rescale_cols(const __grid_constant__ DevTables T, const u64* __restrict__ last, size_t last_bs,
                                                                   u64* __restrict__ tmp, size_t tmp_bs, int nl, const __grid_constant__ ScalarTable negqlinv) {
+    pdl_wait();
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, tile = blockIdx.x, i = blockIdx.y;
     u64* const smp = sm + tphys(2 * t);   // this thread's element pairs: smp[u * kPairStep + {0,1}]
@@ -430,6 +437,7 @@ template <int LOGN>
 __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_rescale_rows(const __grid_constant__ DevTables T, u64* __restrict__ out, size_t out_bs,
                                                                   const u64* __restrict__ c, size_t c_bs, const u64* __restrict__ tmp, size_t tmp_bs,
                                                                   const __grid_constant__ ScalarTable qlinv) {
+    pdl_wait();
     __shared__ u64 sm[kTileWords];
     const int t = threadIdx.x, tile = blockIdx.x, i = blockIdx.y;
     u64* const smp = sm + tphys(2 * t);   // this thread's element pairs: smp[u * kPairStep + {0,1}]
@@ -465,7 +473,7 @@ template <int LOGN>
 static void modup_t(const DevTables& T, const ModUpArgs& m, cudaStream_t st) {
     using G = NttGeo<LOGN>;
     const int ext = m.nl + m.K;
-    k_inv_rows<LOGN><<<dim3(G::TILES, m.nl, m.nbatch), kTileThreads, 0, st>>>(T, m.c, m.c_bs, m.scratch, (size_t)m.nl * T.N, 0);
+    launch_pdl(k_inv_rows<LOGN>, dim3(G::TILES, m.nl, m.nbatch), dim3(kTileThreads), 0, st, T, m.c, m.c_bs, m.scratch, (size_t)m.nl * T.N, 0);
     // all digits in one launch per stage: inverse columns of the nl source limbs, then every digit's
     // conversion to its complement limbs fused with their forward column pass
     TabSet ts{};
@@ -477,10 +485,10 @@ static void modup_t(const DevTables& T, const ModUpArgs& m, cudaStream_t st) {
         ts.in_off[d] = (size_t)lo * T.N;
         ts.out_off[d] = (size_t)d * ext * T.N;
     }
-    k_inv_cols<LOGN><<<dim3(G::TILES, m.nl, m.nbatch), kTileThreads, 0, st>>>(T, ts, m.scratch, (size_t)m.nl * T.N);
+    launch_pdl(k_inv_cols<LOGN>, dim3(G::TILES, m.nl, m.nbatch), dim3(kTileThreads), 0, st, T, ts, m.scratch, (size_t)m.nl * T.N);
     launch_conv_fwd_col<LOGN>(T, ts, m.alpha, ts.ystart[m.ndig], m.nbatch,
                               m.scratch, (size_t)m.nl * T.N, m.digits, (size_t)m.ndig * ext * T.N, m.nl, m.L, 1, st);
-    k_modup_rows<LOGN><<<dim3(G::TILES, ext, m.ndig * m.nbatch), kTileThreads, 0, st>>>(T, m.digits, m.c, m.c_bs, m.ndig, m.nl, m.L, m.alpha);
+    launch_pdl(k_modup_rows<LOGN>, dim3(G::TILES, ext, m.ndig * m.nbatch), dim3(kTileThreads), 0, st, T, m.digits, m.c, m.c_bs, m.ndig, m.nl, m.L, m.alpha);
 }
 void launch_fused_modup(const DevTables& T, const ModUpArgs& m, cudaStream_t st) {
     switch (T.logN) {
@@ -498,10 +506,10 @@ static void rescale_t(const DevTables& T, const RescaleArgs& r, cudaStream_t st)
     using G = NttGeo<LOGN>;
     const int nl = r.nl;
     // dropped limb of every component -> coefficients (inverse rows, then inverse columns * N^-1 via the 1-limb table)
-    k_inv_rows<LOGN><<<dim3(G::TILES, 1, r.ncomp), kTileThreads, 0, st>>>(T, r.c + (size_t)(nl - 1) * T.N, r.c_bs, r.last, (size_t)T.N, nl - 1);
-    k_inv_cols<LOGN><<<dim3(G::TILES, 1, r.ncomp), kTileThreads, 0, st>>>(T, single_table(r.last_tab), r.last, (size_t)T.N);
-    k_rescale_cols<LOGN><<<dim3(G::TILES, nl - 1, r.ncomp), kTileThreads, 0, st>>>(T, r.last, (size_t)T.N, r.tmp, (size_t)(nl - 1) * T.N, nl, r.negqlinv);
-    k_rescale_rows<LOGN><<<dim3(G::TILES, nl - 1, r.ncomp), kTileThreads, 0, st>>>(T, r.out, r.out_bs, r.c, r.c_bs, r.tmp, (size_t)(nl - 1) * T.N, r.qlinv);
+    launch_pdl(k_inv_rows<LOGN>, dim3(G::TILES, 1, r.ncomp), dim3(kTileThreads), 0, st, T, r.c + (size_t)(nl - 1) * T.N, r.c_bs, r.last, (size_t)T.N, nl - 1);
+    launch_pdl(k_inv_cols<LOGN>, dim3(G::TILES, 1, r.ncomp), dim3(kTileThreads), 0, st, T, single_table(r.last_tab), r.last, (size_t)T.N);
+    launch_pdl(k_rescale_cols<LOGN>, dim3(G::TILES, nl - 1, r.ncomp), dim3(kTileThreads), 0, st, T, r.last, (size_t)T.N, r.tmp, (size_t)(nl - 1) * T.N, nl, r.negqlinv);
+    launch_pdl(k_rescale_rows<LOGN>, dim3(G::TILES, nl - 1, r.ncomp), dim3(kTileThreads), 0, st, T, r.out, r.out_bs, r.c, r.c_bs, r.tmp, (size_t)(nl - 1) * T.N, r.qlinv);
 }
 void launch_fused_rescale(const DevTables& T, const RescaleArgs& r, cudaStream_t st) {
     switch (T.logN) {

@@ -146,6 +146,7 @@ void launch_moddown_finish(const DevTables& T, const u64* ct, size_t ct_bs, cons
 // Elementwise family (row P8). grid.y = limb, grid.z = component.
 __global__ void __launch_bounds__(kThreads) k_ew(DevTables T, int op, u64* __restrict__ out, const u64* __restrict__ a, const u64* __restrict__ b,
                                                  size_t cs_out, size_t cs_a, size_t cs_b) {
+    pdl_wait();
     int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (idx >= T.N) return;
     int i = blockIdx.y;
@@ -162,11 +163,12 @@ __global__ void __launch_bounds__(kThreads) k_ew(DevTables T, int op, u64* __res
 void launch_ew(const DevTables& T, EwOp op, u64* out, const u64* a, const u64* b, int nl, int ncomp, size_t cs_out, size_t cs_a,
                size_t cs_b, cudaStream_t st) {
     dim3 grid(blocks_for(T.N), nl, ncomp);
-    k_ew<<<grid, kThreads, 0, st>>>(T, (int)op, out, a, b, cs_out, cs_a, cs_b);
+    launch_pdl(k_ew, grid, dim3(kThreads), 0, st, T, (int)op, out, a, b, cs_out, cs_a, cs_b);
 }
 
 __global__ void __launch_bounds__(kThreads) k_mul_scalar(DevTables T, u64* __restrict__ out, const u64* __restrict__ a, ScalarTable s,
                                                          size_t cs_out, size_t cs_a) {
+    pdl_wait();
     int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (idx >= T.N) return;
     int i = blockIdx.y;
@@ -180,10 +182,11 @@ __global__ void __launch_bounds__(kThreads) k_mul_scalar(DevTables T, u64* __res
 void launch_mul_scalar(const DevTables& T, u64* out, const u64* a, const ScalarTable& s, int nl, int ncomp, size_t cs_out, size_t cs_a,
                        cudaStream_t st) {
     dim3 grid(blocks_for(T.N), nl, ncomp);
-    k_mul_scalar<<<grid, kThreads, 0, st>>>(T, out, a, s, cs_out, cs_a);
+    launch_pdl(k_mul_scalar, grid, dim3(kThreads), 0, st, T, out, a, s, cs_out, cs_a);
 }
 
 __global__ void __launch_bounds__(kThreads) k_add_scalar(DevTables T, u64* __restrict__ out, const u64* __restrict__ a, ScalarTable s, int ncomp) {
+    pdl_wait();
     int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (idx >= T.N) return;
     int i = blockIdx.y;
@@ -198,10 +201,11 @@ __global__ void __launch_bounds__(kThreads) k_add_scalar(DevTables T, u64* __res
 }
 void launch_add_scalar(const DevTables& T, u64* out, const u64* a, const ScalarTable& s, int nl, int ncomp, int ncomps_total, cudaStream_t st) {
     dim3 grid(blocks_for(T.N), nl, ncomps_total);
-    k_add_scalar<<<grid, kThreads, 0, st>>>(T, out, a, s, ncomp);
+    launch_pdl(k_add_scalar, grid, dim3(kThreads), 0, st, T, out, a, s, ncomp);
 }
 
 __global__ void __launch_bounds__(kThreads) k_wsum(DevTables T, u64* __restrict__ out, const __grid_constant__ WsumArgs a) {
+    pdl_wait();
     int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (idx >= T.N) return;
     const int i = blockIdx.y;
@@ -219,12 +223,13 @@ __global__ void __launch_bounds__(kThreads) k_wsum(DevTables T, u64* __restrict_
 }
 void launch_wsum(const DevTables& T, u64* out, const WsumArgs& a, int nl, int ncomps_total, cudaStream_t st) {
     dim3 grid(blocks_for(T.N), nl, ncomps_total);
-    k_wsum<<<grid, kThreads, 0, st>>>(T, out, a);
+    launch_pdl(k_wsum, grid, dim3(kThreads), 0, st, T, out, a);
 }
 
 // EvalMultCore (row P6, single product): out = (a0*b0, a0*b1 + a1*b0, a1*b1).
 __global__ void __launch_bounds__(kThreads) k_tensor(DevTables T, u64* __restrict__ out, const u64* __restrict__ a, size_t cs_a,
                                                      const u64* __restrict__ b, size_t cs_b, int nl, int bca, int bcb) {
+    pdl_wait();
     int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (idx >= T.N) return;
     int i = blockIdx.y;
@@ -249,12 +254,13 @@ __global__ void __launch_bounds__(kThreads) k_tensor(DevTables T, u64* __restric
 }
 void launch_tensor(const DevTables& T, u64* out, const u64* a, size_t cs_a, bool bcast_a, const u64* b, size_t cs_b, bool bcast_b, int nl, int nbatch, cudaStream_t st) {
     dim3 grid(blocks_for(T.N), nl, nbatch);
-    k_tensor<<<grid, kThreads, 0, st>>>(T, out, a, cs_a, b, cs_b, nl, bcast_a ? 1 : 0, bcast_b ? 1 : 0);
+    launch_pdl(k_tensor, grid, dim3(kThreads), 0, st, T, out, a, cs_a, b, cs_b, nl, bcast_a ? 1 : 0, bcast_b ? 1 : 0);
 }
 
 // EvalMultCore against database ciphertexts kept in Montgomery form: one REDC per output word.
 __global__ void __launch_bounds__(kThreads) k_tensor_db(DevTables T, u64* __restrict__ out, const __grid_constant__ CtPtrs ap, size_t cs_a,
                                                         const u64* __restrict__ db, size_t cs_b, int nl) {
+    pdl_wait();
     int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (idx >= T.N) return;
     int i = blockIdx.y;
@@ -278,10 +284,11 @@ __global__ void __launch_bounds__(kThreads) k_tensor_db(DevTables T, u64* __rest
 }
 void launch_tensor_db(const DevTables& T, u64* out, const CtPtrs& a, size_t cs_a, const u64* db, size_t cs_b, int nl, int nbatch, cudaStream_t st) {
     dim3 grid(blocks_for(T.N), nl, nbatch);
-    k_tensor_db<<<grid, kThreads, 0, st>>>(T, out, a, cs_a, db, cs_b, nl);
+    launch_pdl(k_tensor_db, grid, dim3(kThreads), 0, st, T, out, a, cs_a, db, cs_b, nl);
 }
 __global__ void __launch_bounds__(kThreads) k_batch_sum(DevTables T, u64* __restrict__ acc, const u64* __restrict__ in, int nl, size_t bs, int nbatch,
                                                         int accumulate) {
+    pdl_wait();
     int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (idx >= T.N) return;
     const u64 q = T.pc[blockIdx.y % nl].q;
@@ -296,7 +303,7 @@ __global__ void __launch_bounds__(kThreads) k_batch_sum(DevTables T, u64* __rest
 }
 void launch_batch_sum(const DevTables& T, u64* acc, const u64* in, int nl, int ncomp, int nbatch, int accumulate, cudaStream_t st) {
     dim3 grid(blocks_for(T.N), nl * ncomp, 1);
-    k_batch_sum<<<grid, kThreads, 0, st>>>(T, acc, in, nl, (size_t)ncomp * nl * T.N, nbatch, accumulate);
+    launch_pdl(k_batch_sum, grid, dim3(kThreads), 0, st, T, acc, in, nl, (size_t)ncomp * nl * T.N, nbatch, accumulate);
 }
 
 // AutomorphismTransform (row P3): out[l][j] = in[l][map[j]].
@@ -428,6 +435,7 @@ __device__ __forceinline__ u128d fold23(const cols3& c) {      // lo + mid * 2^2
 template <int NB>
 __global__ void __launch_bounds__(kThreads, 2) k_diag_mac(DevTables T, const u64* __restrict__ rotq, const __grid_constant__ DbBlockPtrs dbs,
                                                           u64* __restrict__ out, int ndiag, int nl, int nblocks) {
+    pdl_wait();
     int idx = (blockIdx.y * blockDim.x + threadIdx.x) * 2;
     if (idx >= T.N) return;
     const int i = blockIdx.z, g0 = blockIdx.x * NB;
@@ -510,7 +518,7 @@ __global__ void __launch_bounds__(kThreads, 2) k_diag_mac(DevTables T, const u64
 void launch_diag_mac(const DevTables& T, const u64* rotq, const DbBlockPtrs& dbs, int nblocks, u64* out, int ndiag, int nl, cudaStream_t st) {
     // one block per CTA: NB = 2 (rotated query loaded once for two blocks) measured slower, 13.1 vs 11.9 ms for 8 blocks x 2 scenarios
     dim3 grid(nblocks, blocks_for(T.N), nl);
-    k_diag_mac<1><<<grid, kThreads, 0, st>>>(T, rotq, dbs, out, ndiag, nl, nblocks);
+    launch_pdl(k_diag_mac<1>, grid, dim3(kThreads), 0, st, T, rotq, dbs, out, ndiag, nl, nblocks);
 }
 
 }  // namespace hx

@@ -1,6 +1,9 @@
 // hx_kernels.cuh -- launch interface of the sm_100a kernels (definitions in hx_kernels.cu).
 // Polynomial data: uint64 limb-major [limb][N], EVALUATION form unless stated, canonical residues.
 #pragma once
+#include <stdexcept>
+#include <string>
+#include <utility>
 #include "hx_modarith.cuh"
 
 namespace hx {
@@ -119,6 +122,23 @@ void launch_tensor_db(const DevTables& T, u64* out, const CtPtrs& a, size_t cs_a
 void launch_batch_sum(const DevTables& T, u64* acc, const u64* in, int nl, int ncomp, int nbatch, int accumulate, cudaStream_t st);
 void launch_automorph(const DevTables& T, u64* out, const u64* in, const u32* map, int nlimbs_total, cudaStream_t st);
 void launch_automap(int N, int logN, u64 k, u32* map, cudaStream_t st);
+// Launch with programmatic stream serialization (the kernel's first statement must be pdl_wait()): hides the launch and
+// block-scheduling latency between the ~1000 small dependent kernels of a step.
+template <class... KArgs, class... Args>
+inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+    if (e != cudaSuccess) throw std::runtime_error(std::string("kernel launch failed: ") + cudaGetErrorString(e));
+}
 void launch_to_mont(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, cudaStream_t st, bool inverse = false);
 // in place: x -> split30(x) (engine-internal key form, see hx_modarith.cuh)
 void launch_split30(u64* data, size_t words, cudaStream_t st);

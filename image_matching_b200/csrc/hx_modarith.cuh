@@ -137,6 +137,11 @@ __device__ __forceinline__ ulonglong2 ld_stream128(const u64* p) {
     asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
     return v;
 }
+// Programmatic dependent launch: a kernel launched with launch_pdl() may be scheduled while the previous kernel of its stream is
+// draining; it must not touch that kernel's output before this returns (full completion + memory flush of the predecessor).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// (An early "griddepcontrol.launch_dependents" at the top of every kernel was tried and gave wrong results in chains of three
+// or more dependent kernels, so the trigger is left implicit: the dependent is scheduled as this kernel's CTAs exit.)
 // Asynchronous HBM -> L2 prefetch of `bytes` (multiple of 16) contiguous bytes at a 16-byte aligned address.
 __device__ __forceinline__ void l2_prefetch(const void* p, unsigned bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");

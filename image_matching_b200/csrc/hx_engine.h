@@ -198,6 +198,7 @@ private:
     void align(Ct& a, Ct& b);
     std::vector<u64> const_for_mult(double c, int nl) const;
     std::vector<u64> const_for_add(double c, int nl, int deg) const;
+    std::pair<Ct, Ct> two_products(Ct a0, Ct b0, Ct a1, Ct b1, bool twice);
     Ct inner_cheb(const std::vector<double>& coeffs, int k, int m, std::vector<Ct>& T, std::vector<Ct>& T2);
     Ct inner_poly(const std::vector<double>& coeffs, int k, int m, std::vector<Ct>& pw, std::vector<Ct>& pw2);
     // InnerEvalChebyshevPS / InnerEvalPolyPS of several coefficient vectors at the same recursion level m, evaluated level by

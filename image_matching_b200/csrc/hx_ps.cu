@@ -290,6 +290,24 @@ Ct Engine::inner_cheb(const std::vector<double>& coeffs, int k, int m, std::vect
 }
 
 // EvalChebyshevSeriesPS (cc->EvalChebyshevFunction, openFHE_wrapper.cpp:174).
+// Rescale(f * a0 * b0) and Rescale(f * a1 * b1) (f = 2: the Chebyshev doubling) for two independent products whose operands sit
+// at one level: ONE batched multiply / relinearise / rescale instead of two chains of ~14 dependent launches each. Per entry the
+// operations and operands are those of the sequential code, hence the same bits.
+std::pair<Ct, Ct> Engine::two_products(Ct a0, Ct b0, Ct a1, Ct b1, bool twice) {
+    align(a0, b0);
+    align(a1, b1);
+    auto one = [&](const Ct& a, const Ct& b) {
+        Ct p = mult(a, b);
+        return rescale(twice ? add(p, p) : p);
+    };
+    auto shape_eq = [](const Ct& u, const Ct& v) { return u->nl == v->nl && u->deg == v->deg && u->nb == v->nb && u->ncomp == v->ncomp && u->level == v->level; };
+    if (!(batch_blocks && !force_unfused && fused_ks_supported(logN) && shape_eq(a0, a1) && shape_eq(b0, b1) && a0->ncomp == 2 && b0->ncomp == 2))
+        return {one(a0, b0), one(a1, b1)};
+    Ct p = mult(concat({a0, a1}), concat({b0, b1}));
+    std::vector<Ct> r = split(rescale(twice ? add(p, p) : p), 2);
+    return {r[0], r[1]};
+}
+
 Ct Engine::chebyshev_series(const Ct& x, const std::vector<double>& coefficients, double a, double b) {
     std::lock_guard<std::recursive_mutex> g(mu);
     int n = degree_of(coefficients);
@@ -310,6 +328,11 @@ Ct Engine::chebyshev_series(const Ct& x, const std::vector<double>& coefficients
         if (!(i & (i - 1)) || i % 2 == 0) {
             Ct sq = square(T[i / 2 - 1]);
             T[i - 1] = add_const(rescale(add(sq, sq)), -1.0);
+        } else if (i + 1 <= k) {      // T_i = 2 T_(i-1)/2 T_(i+1)/2 - T_1 and T_(i+1) = 2 T_(i+1)/2 ^2 - 1 depend on earlier terms only
+            auto pr = two_products(T[i / 2 - 1], T[i / 2], T[(i + 1) / 2 - 1], T[(i + 1) / 2 - 1], true);
+            T[i - 1] = sub(pr.first, y);
+            T[i] = add_const(pr.second, -1.0);
+            i++;
         } else {
             Ct prod = mult(T[i / 2 - 1], T[i / 2]);
             T[i - 1] = sub(rescale(add(prod, prod)), y);
@@ -318,14 +341,20 @@ Ct Engine::chebyshev_series(const Ct& x, const std::vector<double>& coefficients
     for (int i = 1; i < k; i++) T[i - 1] = level_reduce(T[i - 1], T[k - 1]->level - T[i - 1]->level);
     std::vector<Ct> T2(m);
     T2[0] = T.back();
-    for (int i = 1; i < m; i++) {
-        Ct sq = square(T2[i - 1]);
-        T2[i] = add_const(rescale(add(sq, sq)), -1.0);
-    }
     Ct T2km1 = T2[0];
+    if (m > 1) {
+        Ct sq = square(T2[0]);
+        T2[1] = add_const(rescale(add(sq, sq)), -1.0);
+    }
     for (int i = 1; i < m; i++) {
-        Ct prod = mult(T2km1, T2[i]);
-        T2km1 = sub(rescale(add(prod, prod)), T2[0]);
+        if (i + 1 < m) {              // T2[i+1] = 2 T2[i]^2 - 1 and the next T2km1 = 2 T2km1 T2[i] - T2[0] are independent
+            auto pr = two_products(T2[i], T2[i], T2km1, T2[i], true);
+            T2[i + 1] = add_const(pr.first, -1.0);
+            T2km1 = sub(pr.second, T2[0]);
+        } else {
+            Ct prod = mult(T2km1, T2[i]);
+            T2km1 = sub(rescale(add(prod, prod)), T2[0]);
+        }
     }
     int k2m2k = k * (1 << (m - 1)) - k;
     f2.resize(2 * k2m2k + k + 1, 0.0);
@@ -408,6 +437,15 @@ Ct Engine::eval_poly(const Ct& x, const std::vector<double>& coefficients) {
     for (int i = 2; i <= k; i++) {
         if (!(i & (i - 1))) {
             pw[i - 1] = rescale(square(pw[i / 2 - 1]));
+        } else if (need[i - 1] && i + 1 <= k && !((i + 1) & i) && (i + 1) / 2 < i) {
+            // x^i = x^p2 * x^rem and x^(i+1) = (x^((i+1)/2))^2 are independent of each other
+            int p2 = 1 << (int)std::floor(std::log2(i));
+            int rem = i % p2;
+            pw[rem - 1] = level_reduce(pw[rem - 1], pw[p2 - 1]->level - pw[rem - 1]->level);
+            auto pr = two_products(pw[p2 - 1], pw[rem - 1], pw[(i + 1) / 2 - 1], pw[(i + 1) / 2 - 1], false);
+            pw[i - 1] = pr.first;
+            pw[i] = pr.second;
+            i++;
         } else if (need[i - 1]) {
             int p2 = 1 << (int)std::floor(std::log2(i));
             int rem = i % p2;

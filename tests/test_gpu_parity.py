@@ -417,3 +417,15 @@ def test_error_behaviour_matches_openfhe_exceptions():
     sq = fresh.EvalMultNoRelin(fresh.upload(np.stack(orc.encrypt([0.5]).c), 0, 1), fresh.upload(np.stack(orc.encrypt([0.5]).c), 0, 1))
     with pytest.raises(HxError, match="EvalMultKey"):
         fresh.Relinearize(sq)                                  # EvalMultKey not generated
+    # the two-step fused entries: unknown block, ciphertext that is not fresh, rotation set index out of range
+    with pytest.raises(HxError):
+        cc.db_get(0, 0)
+    cc.db_register_ct(0, 0, ct)
+    with pytest.raises(HxError):
+        cc.db_register_ct(0, 1, low)
+    with pytest.raises(HxError, match="not registered"):
+        cc.score_blocks(ct, 1, [7])
+    with pytest.raises(HxError):
+        cc.score_blocks(ct, 1, [0], rotations=[1])
+    with pytest.raises(HxError):
+        cc.score_blocks(ct, 3, [0])                            # rotation keys 2 is missing: the hoisted batch must refuse

@@ -349,7 +349,12 @@ def run_b200(args):
                 "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak, "traffic": traffic, "algorithmic_bytes_per_launch": d["bytes"] / groups, "peak_source": peak_src,
                              "launches": groups, "kernels": d["launches"], "avg_launch_ms": avg_ms, "share_of_step": d["ms"] / ms_total,
-                             "warmup_profile_ms": {k: round(v["ms"], 3) for k, v in prof_all.items() if v["launches"]}}}
+                             "warmup_profile_ms": {k: round(v["ms"], 3) for k, v in prof_all.items() if v["launches"]},
+                             # the other kernel families of the step from the warm-up profile (each launch timed with events, so
+                             # small kernels read high): GB/s on their algorithmic bytes against the same peak
+                             "other_kernels": {k: {"algorithmic_gbs": round(v["bytes"] / (v["ms"] * 1e-3) / 1e9, 1),
+                                                   "frac": round(v["bytes"] / (v["ms"] * 1e-3) / 1e9 / peak, 3), "launches": v["launches"]}
+                                               for k, v in prof_all.items() if v["launches"] and v["ms"] > 0 and k != dominant}}}
         if not args.no_cpu_baseline and world == 1:
             v, desc, cores = cpu_port_latency(args.ring_dim, ndiag, total_blocks, n_rot_sample=96)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}

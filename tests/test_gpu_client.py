@@ -69,3 +69,30 @@ def test_hydia_end_to_end_product_client_small_ring():
     # a query matching nothing
     q2 = cl.encryptQuery(rng.integers(-99, 100, size=512).astype(np.float64))
     assert cl.decryptIndex(snd.indexScenario(q2)) == [] and cl.decryptMembership(snd.membershipScenario(q2)) is False
+
+
+def test_gpu_compare_reproduces_the_reference_signapprox_fixture():
+    """tools/figures/signApprox.csv (tests/golden/signapprox.npz): the authors' checked-in output of
+    OpenFHEWrapper::chebyshevCompare(delta 0.44, depth 10) on inputs in [-1, 1].  The same inputs are encrypted at the reference's
+    parameters (N = 2^15, depth 11), compared ON THE GPU (hx_compare and the per-op wrapper chain) and decrypted: the values
+    must match the fixture to 1e-4 (the tolerance the reference states, main_accuracy.cpp:360; the plaintext-math restatement
+    matches to 5.9e-5) and the decisions (>= 1.0, receiver_hers.cpp:30) must flip between 0.4540 and 0.4542 as the fixture's do."""
+    import os
+    import image_matching_b200 as hx
+    from image_matching_b200 import OpenFHEWrapper
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "signapprox.npz"))
+    x, want = g["input"], g["combined"]
+    cc = hx.CryptoContext.generate(depth=11)
+    assert cc.N == 32768 and cc.L == 12
+    cl = hx.Client(cc, seed=7)
+    cl.EvalMultKeyGen()
+    slots = cc.N // 2
+    assert len(x) <= slots
+    v = np.zeros(slots)
+    v[:len(x)] = x
+    ct = cc.LevelReduce(cl.encrypt(v), 1)                  # the score ciphertext enters the compare one level down (after its rescale)
+    got = cl.decrypt(cc.compare(ct, 0.44, 10))[:len(x)]
+    assert np.abs(got - want).max() <= 1e-4
+    per_op = cl.decrypt(OpenFHEWrapper.chebyshevCompare(cc, ct, 0.44, 10))[:len(x)]
+    assert np.array_equal(per_op, got)                     # fused entry == the wrapper's call sequence, bit for bit after decryption
+    assert np.all(got[(x >= 0.4542) & (x <= 0.6)] >= 1.0) and np.all(got[x <= 0.4540] < 1.0)

@@ -96,3 +96,25 @@ def test_gpu_compare_reproduces_the_reference_signapprox_fixture():
     per_op = cl.decrypt(OpenFHEWrapper.chebyshevCompare(cc, ct, 0.44, 10))[:len(x)]
     assert np.array_equal(per_op, got)                     # fused entry == the wrapper's call sequence, bit for bit after decryption
     assert np.all(got[(x >= 0.4542) & (x <= 0.6)] >= 1.0) and np.all(got[x <= 0.4540] < 1.0)
+
+
+def test_reference_dataset_2_10_at_full_parameters_scores_and_decisions():
+    """BASELINE configs[0] at the reference's own parameters (N = 2^15, 12 + 4 limbs, all 511 rotation keys): the shipped
+    dataset test/2_10.dat (tests/golden/dat_2_10.npz) enrolled, queried and scored through the product; every encrypted score
+    within 1e-4 of the plaintext cosine (the check of main_accuracy.cpp:354-364), membership true, index [0]."""
+    import os
+    import image_matching_b200 as hx
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "dat_2_10.npz"))
+    db, query = z["db"].astype(np.float64), z["query"].astype(np.float64)
+    n = len(db)
+    cc = hx.CryptoContext.generate(depth=11)
+    cl = hx.Client(cc, seed=11)
+    cl.EvalMultKeyGen(); cl.EvalSumKeyGen(); cl.EvalRotateKeyGen(list(range(1, 512)))
+    assert cl.enroll_diagonal(db) == 1
+    q = cl.encryptQuery(query)
+    snd = hx.DiagonalSender(cc, None, n)
+    cos = hx.plaintext_normalize(db) @ hx.plaintext_normalize(query)
+    got = cl.decrypt(snd.computeSimilarity(q)[0])
+    assert np.abs(got[:n] - cos).max() <= 1e-4 and np.abs(got[n:]).max() <= 1e-4      # padding rows score 0
+    assert cl.decryptMembership(snd.membershipScenario(q)) is True
+    assert cl.decryptIndex(snd.indexScenario(q)) == [0]

@@ -42,6 +42,19 @@ struct NttGeo {
 };
 
 __device__ __forceinline__ int insert_bits3(int t, int p) { return ((t >> p) << (p + 3)) | (t & ((1 << p) - 1)); }
+// Which of the 256 element groups a thread takes in a round. In the round with element stride 4 (p = 2) the natural order puts
+// the four 4-lane groups of a half-warp on blocks 0,1,2,3 of 32 elements, i.e. 34 doubles apart = 4 banks of 8 bytes: their
+// 4-double windows overlap pairwise and every LDS.64 / STS.64 of the round takes two wavefronts per half-warp (ncu: 2x).
+// Rotating the low three bits of the group number puts a half-warp on blocks 0,2,4,6 (68 doubles apart = 8 banks): conflict free.
+template <int P>
+__device__ __forceinline__ int round_thread(int t) {
+    if constexpr (P == 2) {
+        const int g = t >> 2;
+        return ((((g & ~7) | ((g & 3) << 1) | ((g >> 2) & 1))) << 2) | (t & 3);
+    } else {
+        return t;
+    }
+}
 
 // ---- forward --------------------------------------------------------------------------------
 // Two arithmetic back ends, chosen per prime (block-uniform):
@@ -85,7 +98,7 @@ __device__ __forceinline__ u64 fwd_normalize(u64 x, const PrimeConst& pc, bool f
 template <int SL0, int R, int S0, int SHIFT0>
 __device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
     constexpr int p = kLogTile - SL0 - R;
-    const int base = insert_bits3(t, p);
+    const int base = insert_bits3(round_thread<p>(t), p);
     u64* const sp = sm + tphys(base);
     u64 v[8];
 #pragma unroll
@@ -116,7 +129,7 @@ __device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const 
 template <int SL0, int R, int S0, int SHIFT0>
 __device__ __forceinline__ void fwd_round_fp(double* sm, int t, int tileoff, const double2* __restrict__ tw, double q) {
     constexpr int p = kLogTile - SL0 - R;
-    const int base = insert_bits3(t, p);
+    const int base = insert_bits3(round_thread<p>(t), p);
     double* const sp = sm + tphys(base);
     double v[8];
 #pragma unroll
@@ -188,7 +201,7 @@ __device__ __forceinline__ void fwd_row_pass(u64* sm, int t, int tile, const Tab
 template <int SH, int R, int S_TOP, int SHIFT_TOP>
 __device__ __forceinline__ void inv_round_ct(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
     constexpr int p = kLogTile - SH;
-    const int base = insert_bits3(t, p);
+    const int base = insert_bits3(round_thread<p>(t), p);
     u64* const sp = sm + tphys(base);
     u64 v[8];
 #pragma unroll

@@ -48,6 +48,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--rot-chunk", type=int, default=0, help="override the engine's hoisted-rotation batch size")
     ap.add_argument("--rot-streams", type=int, default=0, help="override the number of streams the hoisted-rotation batches use")
+    ap.add_argument("--ks-fuse-inv", type=int, default=-1, help="override the batch threshold of the fused inverse-column / conversion ModDown kernel (0 = off)")
     ap.add_argument("--ncu-range", action="store_true",
                     help="run one extra step inside cudaProfilerStart/Stop (for ncu --profile-from-start off)")
     return ap.parse_args()
@@ -196,6 +197,8 @@ def run_b200(args):
         cc.set_option("rot_chunk", args.rot_chunk)
     if args.rot_streams:
         cc.set_option("rot_streams", args.rot_streams)
+    if args.ks_fuse_inv >= 0:
+        cc.set_option("ks_fuse_inv", args.ks_fuse_inv)
     slots = cc.GetBatchSize()
     total_blocks = bpg * world
     n_total = total_blocks * slots

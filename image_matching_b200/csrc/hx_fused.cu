@@ -22,6 +22,8 @@
 #endif
 namespace hx {
 
+int g_ks_fuse_inv = 16;   // > 0: ModDown of key-switch batches with at least this many polynomials runs K2a inside K2b (hx_ctx_set_option "ks_fuse_inv")
+
 constexpr unsigned kTileBytes = kTileN * sizeof(u64);                                   // 16 KB
 constexpr unsigned kStageOff = (kTileWords * sizeof(u64) + 127u) & ~127u;              // staged key tiles start here
 constexpr unsigned ks_smem_bytes(int ndig) { return kStageOff + ndig * kTileBytes + 16; }
@@ -142,7 +144,10 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_cols(const __grid
 __device__ __forceinline__ void cp_async16(void* dst_smem, const void* src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
 }
-template <int LOGN>
+// FUSE_INV (ModDown of a large key-switch batch): `in` holds K1's output (inverse row pass done) and the CTA runs the
+// inverse column pass and the hatinv_n scaling of its n_in source tiles itself before converting ALL its target limbs
+// from shared memory -- k_inv_cols and the round trip of the scaled sources through tmpP disappear.
+template <int LOGN, bool FUSE_INV>
 __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __grid_constant__ DevTables T, const __grid_constant__ TabSet ts,
                                                                   const u64* __restrict__ in, size_t in_bs, u64* __restrict__ out, size_t out_bs,
                                                                   int ext_nl, int L, int jgroup) {
@@ -163,25 +168,63 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
     const int j0 = (blockIdx.y - ts.ystart[dgt]) * jgroup, j1 = min(n_out, j0 + jgroup);
     const u64* src = in + (size_t)blockIdx.z * in_bs + ((size_t)tile << G::LOGC);
     constexpr int kSegs = (1 << G::LOGC) / 2;                         // 16-byte chunks per tile row
-    for (int k = 0; k < n_in; k++) {
+    if constexpr (FUSE_INV) {
+        const u64* lim = in + (size_t)blockIdx.z * in_bs;
+        u64 x[8];
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const int ch = i * kTileThreads + t, r = ch / kSegs, sg = ch % kSegs;
-            cp_async16(stage + k * kTileN + (r << G::LOGC) + sg * 2, src + (size_t)k * T.N + ((size_t)r << G::B) + sg * 2);
+        for (int u = 0; u < 8; u++) x[u] = __ldg(lim + col_offset<LOGN>(tile, u * kTileThreads + t));
+        for (int k = 0; k < n_in; k++) {
+            const int sp = tab->src[k];
+            const u64 sq = T.pc[sp].q;
+#pragma unroll
+            for (int u = 0; u < 8; u++) smw[u * kWordStep] = x[u];
+            __syncthreads();
+            if (k + 1 < n_in) {   // next source tile in flight during this one's butterflies
+#pragma unroll
+                for (int u = 0; u < 8; u++) x[u] = __ldg(lim + (size_t)(k + 1) * T.N + col_offset<LOGN>(tile, u * kTileThreads + t));
+            }
+            inv_col_pass<LOGN>(sm, t, T.tw_inv + (size_t)sp * T.N, sq);
+            const u64 h = tab->hatinv_n[k], hs = tab->hatinv_n_sh[k];
+            if (k < n_in - 1) {
+#pragma unroll
+                for (int u = 0; u < 8; u++) stage[k * kTileN + u * kTileThreads + t] = split30(shoup_mul(smw[u * kWordStep], h, hs, sq));
+            } else {
+                // the last source goes back to its own column tile of the scratch limb (no other CTA touches it) and is re-read
+                // per target through L1: n_in - 1 staged tiles keep the CTA at 66 KB of shared memory, 3 CTAs per SM
+                u64* back = const_cast<u64*>(lim) + (size_t)k * T.N;
+#pragma unroll
+                for (int u = 0; u < 8; u++) back[col_offset<LOGN>(tile, u * kTileThreads + t)] = split30(shoup_mul(smw[u * kWordStep], h, hs, sq));
+            }
         }
+        __syncthreads();
+    } else {
+        for (int k = 0; k < n_in; k++) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const int ch = i * kTileThreads + t, r = ch / kSegs, sg = ch % kSegs;
+                cp_async16(stage + k * kTileN + (r << G::LOGC) + sg * 2, src + (size_t)k * T.N + ((size_t)r << G::B) + sg * 2);
+            }
+        }
+        asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
     }
-    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
-    __syncthreads();
     for (int j = j0; j < j1; j++) {
         const int prime = tab->dst[j];
         const PrimeConst pc = T.pc[prime];
         acc3 acc[8];
 #pragma unroll
         for (int u = 0; u < 8; u++) acc[u] = {0, 0, 0};
-        for (int k = 0; k < n_in; k++) {   // n_in <= 7 (digit width / number of P limbs)
+        const int n_st = FUSE_INV ? n_in - 1 : n_in;
+        for (int k = 0; k < n_st; k++) {   // n_in <= 7 (digit width / number of P limbs)
             const u64 m = tab->mat30[k * n_out + j];
 #pragma unroll
             for (int u = 0; u < 8; u++) mac30ss(acc[u], stage[k * kTileN + u * kTileThreads + t], m);
+        }
+        if constexpr (FUSE_INV) {
+            const u64 m = tab->mat30[n_st * n_out + j];
+            const u64* last = in + (size_t)blockIdx.z * in_bs + (size_t)n_st * T.N;   // written by this CTA above: plain loads
+#pragma unroll
+            for (int u = 0; u < 8; u++) mac30ss(acc[u], last[col_offset<LOGN>(tile, u * kTileThreads + t)], m);
         }
 #pragma unroll
         for (int u = 0; u < 8; u++) smw[u * kWordStep] = fwd_encode(redc(fold30(acc[u]), pc.q, pc.qinv_neg), fp_ok(pc.q));
@@ -199,16 +242,16 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
     }
 }
 // launch helper: dynamic shared memory = work tile + n_in staged source tiles
-template <int LOGN>
+template <int LOGN, bool FUSE_INV = false>
 static void launch_conv_fwd_col(const DevTables& T, const TabSet& ts, int max_n_in, int ny, int nbatch, const u64* in, size_t in_bs, u64* out,
                                 size_t out_bs, int ext_nl, int L, int jgroup, cudaStream_t st) {
     static int attr_bytes = 0;
-    const int bytes = (int)(kStageOff + max_n_in * kTileBytes);
+    const int bytes = (int)(kStageOff + (FUSE_INV ? max_n_in - 1 : max_n_in) * kTileBytes);
     if (bytes > attr_bytes) {
-        cudaFuncSetAttribute(k_conv_fwd_col<LOGN>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        cudaFuncSetAttribute(k_conv_fwd_col<LOGN, FUSE_INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
         attr_bytes = bytes;
     }
-    launch_pdl(k_conv_fwd_col<LOGN>, dim3(NttGeo<LOGN>::TILES, ny, nbatch), dim3(kTileThreads), bytes, st, T, ts, in, in_bs, out, out_bs, ext_nl, L, jgroup);
+    launch_pdl(k_conv_fwd_col<LOGN, FUSE_INV>, dim3(NttGeo<LOGN>::TILES, ny, nbatch), dim3(kTileThreads), bytes, st, T, ts, in, in_bs, out, out_bs, ext_nl, L, jgroup);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -305,6 +348,11 @@ static void launch_fused_tn(const DevTables& T, const FusedKsArgs& a, const Base
     }
     launch_pdl(k_ks_p_inner<LOGN, NDIG>, dim3(G::TILES, 2 * a.K, nb), dim3(kTileThreads), ks_smem_bytes(NDIG), st, T, a);
     const TabSet ts = single_table(moddown);
+    if (g_ks_fuse_inv && nb * 2 >= g_ks_fuse_inv) {   // large batches: one CTA per column tile does K2a and K2b for all target limbs
+        launch_conv_fwd_col<LOGN, true>(T, ts, a.K, 1, nb * 2, a.tmpP, (size_t)a.K * T.N, a.conv, (size_t)a.nl * T.N, -1, 0, a.nl, st);
+        launch_pdl(k_ks_q_finish<LOGN, NDIG>, dim3(G::TILES, 2 * a.nl, nb), dim3(kTileThreads), ks_smem_bytes(NDIG), st, T, a);
+        return;
+    }
     launch_pdl(k_inv_cols<LOGN>, dim3(G::TILES, a.K, nb * 2), dim3(kTileThreads), 0, st, T, ts, a.tmpP, (size_t)a.K * T.N);
     // large batches: 4 target limbs per CTA share one staging of the K source tiles
     const int jg = (nb * 2 >= 16) ? 4 : 1;

@@ -74,6 +74,7 @@ struct FusedKsArgs {
     u64* out;                       // [nb] x out_bs, each [2][nl][N]
     size_t out_bs;
 };
+extern int g_ks_fuse_inv;
 bool fused_ks_supported(int logN);
 void launch_fused_ks(const DevTables& T, const FusedKsArgs& a, const BaseConvTable* moddown, int nb, cudaStream_t st);
 

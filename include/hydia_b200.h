@@ -44,6 +44,8 @@ uint64_t hx_ctx_launches(hx_ctx* ctx);              /* kernels launched so far (
 /* Engine tuning / test switches: "rot_chunk" (hoisted rotations per key-switch batch), "rot_streams" (streams the
  * independent batches are issued on, default 2: the tail of one batch overlaps the head of the next),
  * "force_unfused" (1 = run the unfused reference kernels instead of the fused key-switch pipeline),
+ * "ks_fuse_inv" (default 16: key-switch batches with at least this many polynomials run ModDown's inverse column pass inside
+ * the base-conversion kernel, one launch and one pass over the P limbs fewer; 0 = separate launch; same bits either way),
  * "batch_blocks" (default 1: the fused HyDia entries relinearise / rescale / compare all database blocks of
  * this GPU as one batch; 0 = one chain per block). */
 int hx_ctx_set_option(hx_ctx* ctx, const char* name, int value);

@@ -169,6 +169,11 @@ def test_hydia_fused_path_bit_exact_small_ring(golden_dir):
     cc.set_option("batch_blocks", 0)
     assert all(same(g, w) for g, w in zip(cc.index(gq), widx))
     cc.set_option("batch_blocks", 1)
+    # ModDown of the 32-rotation batches with the inverse column pass inside the conversion kernel (one launch fewer) vs the
+    # separate k_inv_cols launch: same polynomials
+    for thr in (0, 16):
+        cc.set_option("ks_fuse_inv", thr)
+        assert all(same(g, w) for g, w in zip(cc.score_diag(gq), want))
     # decisions (receiver_hers.cpp:26-54) and score accuracy (main_accuracy.cpp:360)
     assert O.decrypt_index(orc, widx) == [0, n - 1] and O.decrypt_membership(orc, wm)
     cos = O.plaintext_normalize(db) @ O.plaintext_normalize(q)

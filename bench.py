@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--rot-chunk", type=int, default=0, help="override the engine's hoisted-rotation batch size")
     ap.add_argument("--rot-streams", type=int, default=0, help="override the number of streams the hoisted-rotation batches use")
     ap.add_argument("--ks-fuse-inv", type=int, default=-1, help="override the batch threshold of the fused inverse-column / conversion ModDown kernel (0 = off)")
+    ap.add_argument("--rot-lane", type=int, default=-1, help="override the engine's rotation lane (0 = all work ordered on the engine stream)")
     ap.add_argument("--ncu-range", action="store_true",
                     help="run one extra step inside cudaProfilerStart/Stop (for ncu --profile-from-start off)")
     return ap.parse_args()
@@ -199,6 +200,8 @@ def run_b200(args):
         cc.set_option("rot_streams", args.rot_streams)
     if args.ks_fuse_inv >= 0:
         cc.set_option("ks_fuse_inv", args.ks_fuse_inv)
+    if args.rot_lane >= 0:
+        cc.set_option("rot_lane", args.rot_lane)
     slots = cc.GetBatchSize()
     total_blocks = bpg * world
     n_total = total_blocks * slots
@@ -270,6 +273,7 @@ def run_b200(args):
         for _ in range(nsteps):
             q = upload_query_from_host() if e2e else q_res
             out = step(q, e2e)
+            cc.sync()   # a step is one query's latency: the next query starts when this one's results are complete
         cc.sync()
         torch.cuda.synchronize()
         ms = cc.timer_stop()

@@ -72,6 +72,7 @@ int hx_ctx_set_option(hx_ctx* ctx, const char* name, int value) {
         if (n == "force_unfused") ctx->eng->force_unfused = value != 0;
         else if (n == "rot_chunk") ctx->eng->rot_chunk = value;
         else if (n == "rot_streams") ctx->eng->rot_streams = std::max(1, std::min(4, value));
+        else if (n == "rot_lane") ctx->eng->rot_lane = value != 0;
         else if (n == "ks_fuse_inv") g_ks_fuse_inv = std::max(0, value);
         else if (n == "batch_blocks") ctx->eng->batch_blocks = value != 0;
         else throw std::runtime_error("hx_ctx_set_option: unknown option " + n);)
@@ -115,6 +116,7 @@ hx_ct* hx_ct_upload_dev(hx_ctx* ctx, int ncomp, int nlimbs, const void* dev_data
         Ct c = e->new_ct(ncomp, nlimbs, level, noise_deg);
         HX_CUDA(cudaMemcpyAsync(c->d, dev_data, sizeof(u64) * (size_t)ncomp * nlimbs * e->N, cudaMemcpyDeviceToDevice, e->st));
         e->sync();
+        c->settled = true;
         return wrap(c);)
 }
 int hx_ct_download_dev(hx_ct* ct, void* dev_data) {

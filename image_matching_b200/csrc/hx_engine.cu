@@ -31,7 +31,11 @@ Engine::Engine(int N_, int L_, int K_, int dnum_, const u64* q, const u64* p, co
     for (u64 m : mods)
         if (m >> 60) throw std::runtime_error("moduli must be below 2^60");
     HX_CUDA(cudaSetDevice(device));
-    HX_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    {   // the engine stream outranks the rotation lanes (hx_hydia.cu): its short dependent kernels are scheduled first
+        int least = 0, greatest = 0;
+        HX_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+        HX_CUDA(cudaStreamCreateWithPriority(&st, cudaStreamNonBlocking, greatest));
+    }
     // keep freed blocks in the stream-ordered pool: op outputs are allocated per call
     cudaMemPool_t pool;
     HX_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
@@ -201,6 +205,7 @@ Ct Engine::upload(const u64* host, int ncomp, int nl, int level, int deg) {
     Ct c = new_ct(ncomp, nl, level, deg);
     HX_CUDA(cudaMemcpyAsync(c->d, host, sizeof(u64) * (size_t)ncomp * nl * N, cudaMemcpyHostToDevice, st));
     sync();
+    c->settled = true;
     return c;
 }
 void Engine::download(const Ct& ct, u64* host) {

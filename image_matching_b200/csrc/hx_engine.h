@@ -45,6 +45,7 @@ struct CtObj {
     int nb = 1;         // batch entries
     int level = 0;      // GetLevel(): limbs dropped
     int deg = 1;        // GetNoiseScaleDeg()
+    bool settled = false;   // contents complete on the device when the handle was returned (uploads synchronise) and never written again
     ~CtObj();
     u64* comp(int c) const;
     size_t comp_stride() const;
@@ -71,6 +72,13 @@ public:
     int rot_streams = 2;             // hoisted-rotation batches are issued round-robin on this many streams (1 = the engine stream only)
     cudaStream_t aux_streams[3] = {nullptr, nullptr, nullptr};
     cudaEvent_t aux_events[4] = {nullptr, nullptr, nullptr, nullptr};
+    // Rotation lane: the hoisted rotations of a SETTLED query (an uploaded ciphertext) depend on nothing the engine stream still
+    // has queued, so the whole section (ModUp of the query + all batches) is issued on low-priority lane streams and the engine
+    // stream (highest priority) joins at the end: the small dependent kernels of a previous call's compare chain, which leave
+    // most SMs idle, run concurrently with the next call's rotations.  0 = everything ordered on the engine stream.
+    int rot_lane = 1;
+    cudaStream_t lane_streams[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t lane_events[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     int rot_chunk = 32;              // hoisted rotations per fused key-switch batch (intermediates stay L2 resident)
     bool force_unfused = false;      // tests: run the unfused reference kernels instead of hx_fused.cu
     int ks_kind = PK_KS_FUSED;       // profiler family of the next fused key switches (score_diag books its hoisted rotations separately)

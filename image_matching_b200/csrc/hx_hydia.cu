@@ -63,32 +63,51 @@ std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_all(const Ct& query, int 
     rs->eng = this;
     rs->keep = weak_from_this().lock();
     rs->ndiag = ndiag; rs->nl = nl; rs->level = query->level; rs->deg = query->deg;
+    const int chunk = std::max(1, std::min(rot_chunk, kMaxKsBatch));
+    const int ns = rot_streams;
+    cudaStream_t main_st = st;
+    struct StRestore { Engine* e; cudaStream_t s; ~StRestore() { e->st = s; } } st_restore{this, main_st};   // also on exceptions
+    const bool lane = rot_lane && query->settled && !force_unfused;
+    if (lane) {
+        // rotation lane: nothing below depends on what the engine stream still has queued (see hx_engine.h)
+        for (int s = 0; s < ns; s++)
+            if (!lane_streams[s]) HX_CUDA(cudaStreamCreateWithFlags(&lane_streams[s], cudaStreamNonBlocking));   // priority 0 = lowest
+        for (int s = 0; s < 5; s++)
+            if (!lane_events[s]) HX_CUDA(cudaEventCreateWithFlags(&lane_events[s], cudaEventDisableTiming));
+        st = lane_streams[0];   // allocations, the copy of the query and its ModUp are ordered on the lane
+    }
     u64* rotq = rs->rotq = alloc_words(ct_words * ndiag);
     HX_CUDA(cudaMemcpyAsync(rotq, query->d, sizeof(u64) * ct_words, cudaMemcpyDeviceToDevice, st));
     int ndig;
     u64* digits = ks_precompute(query->comp(1), nl, &ndig);
-    const int chunk = std::max(1, std::min(rot_chunk, kMaxKsBatch));
     ks_kind = PK_KS_HOISTED;
     // Independent batches may run on several streams so that the tail of one batch's kernels overlaps the next batch
-    // (smaller batches keep their intermediates in L2).  Stream s > 0 waits for the digits, the engine stream waits for all.
-    const int ns = rot_streams;
-    cudaStream_t main_st = st;
-    // profiler: the whole section is timed as one span on the engine stream (its batches overlap across streams);
+    // (smaller batches keep their intermediates in L2).  Stream s > 0 waits for the digits, the first stream waits for all.
+    cudaStream_t first = st;
+    cudaStream_t* others = lane ? lane_streams + 1 : aux_streams;
+    cudaEvent_t* evs = lane ? lane_events : aux_events;
+    // profiler: the whole section is timed as one span on its first stream (its batches overlap across streams);
     // the per-batch scopes inside only book launches and algorithmic bytes
     std::unique_ptr<Scope> span(new Scope(this, PK_KS_HOISTED, 0, 0.0));
     prof_no_events = true;
     if (ns > 1) {
-        for (int s = 0; s < ns - 1; s++)
-            if (!aux_streams[s]) HX_CUDA(cudaStreamCreateWithFlags(&aux_streams[s], cudaStreamNonBlocking));
-        for (int s = 0; s < 4; s++)
-            if (!aux_events[s]) HX_CUDA(cudaEventCreateWithFlags(&aux_events[s], cudaEventDisableTiming));
-        HX_CUDA(cudaEventRecord(aux_events[3], main_st));
-        for (int s = 0; s < ns - 1; s++) HX_CUDA(cudaStreamWaitEvent(aux_streams[s], aux_events[3], 0));
+        if (!lane) {
+            for (int s = 0; s < ns - 1; s++)
+                if (!aux_streams[s]) {   // same priority as the engine stream: unequal priorities between the batch streams cost 30 %
+                    int pr = 0;
+                    HX_CUDA(cudaStreamGetPriority(main_st, &pr));
+                    HX_CUDA(cudaStreamCreateWithPriority(&aux_streams[s], cudaStreamNonBlocking, pr));
+                }
+            for (int s = 0; s < 4; s++)
+                if (!aux_events[s]) HX_CUDA(cudaEventCreateWithFlags(&aux_events[s], cudaEventDisableTiming));
+        }
+        HX_CUDA(cudaEventRecord(evs[3], first));
+        for (int s = 0; s < ns - 1; s++) HX_CUDA(cudaStreamWaitEvent(others[s], evs[3], 0));
     }
     int turn = 0;
     for (int d0 = 1; d0 < ndiag; d0 += chunk, turn++) {
         int d1 = std::min(ndiag, d0 + chunk);
-        st = (ns > 1 && turn % ns) ? aux_streams[turn % ns - 1] : main_st;
+        st = (ns > 1 && turn % ns) ? others[turn % ns - 1] : first;
         std::vector<const EvalKey*> keys;
         std::vector<u64> gal;
         for (int d = d0; d < d1; d++) {
@@ -98,14 +117,19 @@ std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_all(const Ct& query, int 
         }
         ks_core_batch(digits, ndig, nl, keys, query->comp(0), 1, gal, rotq + ct_words * d0, ct_words);
     }
-    st = main_st;
+    st = first;
     if (ns > 1)
         for (int s = 0; s < ns - 1; s++) {
-            HX_CUDA(cudaEventRecord(aux_events[s], aux_streams[s]));
-            HX_CUDA(cudaStreamWaitEvent(main_st, aux_events[s], 0));
+            HX_CUDA(cudaEventRecord(evs[s], others[s]));
+            HX_CUDA(cudaStreamWaitEvent(first, evs[s], 0));
         }
     prof_no_events = false;
     span.reset();
+    if (lane) {   // the engine stream joins: everything after this call (diagonal MAC, frees) is ordered behind the lane
+        HX_CUDA(cudaEventRecord(lane_events[4], first));
+        HX_CUDA(cudaStreamWaitEvent(main_st, lane_events[4], 0));
+    }
+    st = main_st;
     ks_kind = PK_KS_FUSED;
     free_words(digits);
     return rs;

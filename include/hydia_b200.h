@@ -46,6 +46,8 @@ uint64_t hx_ctx_launches(hx_ctx* ctx);              /* kernels launched so far (
  * "force_unfused" (1 = run the unfused reference kernels instead of the fused key-switch pipeline),
  * "ks_fuse_inv" (default 16: key-switch batches with at least this many polynomials run ModDown's inverse column pass inside
  * the base-conversion kernel, one launch and one pass over the P limbs fewer; 0 = separate launch; same bits either way),
+ * "rot_lane" (default 1: the hoisted rotations of an uploaded query are issued on low-priority side streams that do not wait for
+ * work still queued on the engine stream, so the previous call's compare chain overlaps them; 0 = one ordered stream),
  * "batch_blocks" (default 1: the fused HyDia entries relinearise / rescale / compare all database blocks of
  * this GPU as one batch; 0 = one chain per block). */
 int hx_ctx_set_option(hx_ctx* ctx, const char* name, int value);

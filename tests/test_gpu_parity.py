@@ -174,6 +174,12 @@ def test_hydia_fused_path_bit_exact_small_ring(golden_dir):
     for thr in (0, 16):
         cc.set_option("ks_fuse_inv", thr)
         assert all(same(g, w) for g, w in zip(cc.score_diag(gq), want))
+    # rotation lane (the uploaded query's rotations issued on low-priority side streams, so a previous call's compare chain
+    # overlaps them) vs everything ordered on the engine stream: back-to-back scenarios, same polynomials
+    for lane in (0, 1):
+        cc.set_option("rot_lane", lane)
+        m1, i1, m2 = cc.membership(gq), cc.index(gq), cc.membership(gq)
+        assert same(m1, wm) and same(m2, wm) and all(same(g, w) for g, w in zip(i1, widx))
     # decisions (receiver_hers.cpp:26-54) and score accuracy (main_accuracy.cpp:360)
     assert O.decrypt_index(orc, widx) == [0, n - 1] and O.decrypt_membership(orc, wm)
     cos = O.plaintext_normalize(db) @ O.plaintext_normalize(q)

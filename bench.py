@@ -341,8 +341,10 @@ def run_b200(args):
             traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json"))).get(dominant, {}).get("traffic_bytes_per_launch")
         except Exception:
             pass
-        # a "launch" of a fused family is its group of kernels (4 for the key switch, ModUp and rescale)
-        groups = max(1, d["launches"] // {"ks_hoisted": 4, "ks_fused": 4, "modup": 4, "rescale": 4}.get(dominant, 1))
+        # a "launch" of a fused family is its group of kernels (4 for the key switch, ModUp and rescale; 3 for the batched hoisted
+        # rotations, whose ModDown runs the inverse column pass inside the conversion kernel unless --ks-fuse-inv 0)
+        ks_hoisted_group = 4 if args.ks_fuse_inv == 0 else 3
+        groups = max(1, d["launches"] // {"ks_hoisted": ks_hoisted_group, "ks_fused": 4, "modup": 4, "rescale": 4}.get(dominant, 1))
         avg_ms = d["ms"] / groups
         achieved = (d["bytes"] / groups) / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
         sec = ms_total / args.steps / 1e3

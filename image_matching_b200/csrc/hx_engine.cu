@@ -501,7 +501,7 @@ void Engine::ks_core_batch(const u64* digits, int ndig, int nl, const std::vecto
             a.out_bs = out_bs;
             {   // algorithmic bytes of one key switch after ModUp: evk once, digits once per launch,
                 // addend once, result once
-                Scope sc(this, ks_kind, 4,
+                Scope sc(this, ks_kind, (g_ks_fuse_inv && n * 2 >= g_ks_fuse_inv) ? 3 : 4,   // launch_fused_tn: ModDown in 2 or 3 launches
                          8.0 * N * ((double)n * 2 * ndig * ext + (double)(digits_bs ? n : 1) * ndig * ext + (double)(addend_bs ? n : 1) * addend_comps * nl + (double)n * 2 * nl));
                 launch_fused_ks(T, a, moddown_table(nl), n, st);
             }

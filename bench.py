@@ -50,6 +50,7 @@ def parse():
     ap.add_argument("--rot-streams", type=int, default=0, help="override the number of streams the hoisted-rotation batches use")
     ap.add_argument("--ks-fuse-inv", type=int, default=-1, help="override the batch threshold of the fused inverse-column / conversion ModDown kernel (0 = off)")
     ap.add_argument("--rot-lane", type=int, default=-1, help="override the engine's rotation lane (0 = all work ordered on the engine stream)")
+    ap.add_argument("--sync-exchange", action="store_true", help="N > 1: host-synchronous result exchange (no overlap of the scenarios)")
     ap.add_argument("--ncu-range", action="store_true",
                     help="run one extra step inside cudaProfilerStart/Stop (for ncu --profile-from-start off)")
     return ap.parse_args()
@@ -190,6 +191,7 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        os.environ.setdefault("TORCH_NCCL_HIGH_PRIORITY", "1")   # the collectives' kernels must not queue behind the low-priority rotation lanes
         dist.init_process_group("nccl", device_id=dev)
 
     bpg, ndiag = args.blocks_per_gpu, args.ndiag
@@ -236,7 +238,8 @@ def run_b200(args):
     mem_host = torch.empty(res_words, dtype=torch.int64).pin_memory()
 
     if world > 1:
-        snd = hx.ShardedDiagonalSender(cc, None, n_total, device=dev)
+        from image_matching_b200.sharded import TorchTransport
+        snd = hx.ShardedDiagonalSender(cc, None, n_total, device=dev, transport=TorchTransport(cc, dev, async_exchange=not args.sync_exchange))
     else:
         snd = hx.DiagonalSender(cc, None, n_total)
 

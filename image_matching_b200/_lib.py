@@ -35,6 +35,8 @@ SIGNATURES = {
     "hx_ct_download": (C.c_int, [VP, U64P]),
     "hx_ct_upload_dev": (VP, [VP, C.c_int, C.c_int, VP, C.c_int, C.c_int]),
     "hx_ct_download_dev": (C.c_int, [VP, VP]),
+    "hx_ct_download_dev_async": (C.c_int, [VP, VP, VP]),
+    "hx_ct_upload_dev_async": (VP, [VP, C.c_int, C.c_int, VP, C.c_int, C.c_int, VP]),
     "hx_ct_info": (C.c_int, [VP, I32P, I32P, I32P, I32P]),
     "hx_ct_clone": (VP, [VP]),
     "hx_ct_free": (None, [VP]),

@@ -128,6 +128,41 @@ int hx_ct_download_dev(hx_ct* ct, void* dev_data) {
         HX_CUDA(cudaMemcpyAsync(dev_data, ct->ct->d, sizeof(u64) * (size_t)ct->ct->ncomp * ct->ct->nl * e->N, cudaMemcpyDeviceToDevice, e->st));
         e->sync();)
 }
+// Stream-ordered exchange with a caller-owned stream (the transport stream of sharded.py): no host synchronisation.  Both directions
+// are ordered: the copy runs after everything queued on `stream` so far, and `stream` waits for the copy (so the caller may reuse or
+// free the buffer in its own stream order).
+static void order_streams(cudaStream_t first, cudaStream_t then) {
+    cudaEvent_t ev;
+    HX_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    cudaError_t e1 = cudaEventRecord(ev, first), e2 = cudaStreamWaitEvent(then, ev, 0);
+    cudaEventDestroy(ev);   // released once the recorded work has completed
+    HX_CUDA(e1);
+    HX_CUDA(e2);
+}
+int hx_ct_download_dev_async(hx_ct* ct, void* dev_data, void* stream) {
+    HX_TRY_INT(
+        need(ct, "ct"); need(dev_data, "dev_data");
+        if (ct->ct->nb != 1) throw std::runtime_error("hx_ct_download_dev_async: batched ciphertext (hx_ct_unstack it first)");
+        Engine* e = ct->ct->eng;
+        std::lock_guard<std::recursive_mutex> g(e->mu);
+        HX_CUDA(cudaSetDevice(e->device));
+        order_streams((cudaStream_t)stream, e->st);
+        HX_CUDA(cudaMemcpyAsync(dev_data, ct->ct->d, sizeof(u64) * (size_t)ct->ct->ncomp * ct->ct->nl * e->N, cudaMemcpyDeviceToDevice, e->st));
+        order_streams(e->st, (cudaStream_t)stream);)
+}
+hx_ct* hx_ct_upload_dev_async(hx_ctx* ctx, int ncomp, int nlimbs, const void* dev_data, int level, int noise_deg, void* stream) {
+    HX_TRY_PTR(
+        need(ctx, "ctx"); need(dev_data, "dev_data");
+        if (ncomp < 1 || ncomp > 3 || nlimbs < 1 || nlimbs > ctx->eng->L) throw std::runtime_error("hx_ct_upload_dev_async: bad shape");
+        Engine* e = ctx->eng.get();
+        std::lock_guard<std::recursive_mutex> g(e->mu);
+        HX_CUDA(cudaSetDevice(e->device));
+        Ct c = e->new_ct(ncomp, nlimbs, level, noise_deg);
+        order_streams((cudaStream_t)stream, e->st);
+        HX_CUDA(cudaMemcpyAsync(c->d, dev_data, sizeof(u64) * (size_t)ncomp * nlimbs * e->N, cudaMemcpyDeviceToDevice, e->st));
+        order_streams(e->st, (cudaStream_t)stream);
+        return wrap(c);)
+}
 int hx_ct_download(hx_ct* ct, uint64_t* data) {
     HX_TRY_INT(need(ct, "ct"); need(data, "data");
                if (ct->ct->nb != 1) throw std::runtime_error("hx_ct_download: batched ciphertext (hx_ct_unstack it first)");

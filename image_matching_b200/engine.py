@@ -45,6 +45,10 @@ class Ciphertext:
     def download_dev(self, dev_ptr: int):
         check_int(_lib.load().hx_ct_download_dev(self._h, VP(dev_ptr)))
 
+    def download_dev_async(self, dev_ptr: int, stream: int):
+        """hx_ct_download_dev_async: ordered against the caller's CUDA stream (raw cudaStream_t, 0 = default), no host sync."""
+        check_int(_lib.load().hx_ct_download_dev_async(self._h, VP(dev_ptr), VP(stream)))
+
     def to_numpy(self) -> np.ndarray:
         ncomp, nl, _, _ = self.info()
         out = np.empty((ncomp, nl, self.cc.N), dtype=np.uint64)
@@ -131,6 +135,10 @@ class CryptoContext:
     def upload_dev(self, dev_ptr: int, ncomp: int, nl: int, level: int = 0, noise_deg: int = 1) -> Ciphertext:
         """hx_ct_upload_dev from a DEVICE address on this context's GPU (NCCL staging buffer)."""
         return Ciphertext(self, self._lib.hx_ct_upload_dev(self._h, ncomp, nl, VP(dev_ptr), level, noise_deg))
+
+    def upload_dev_async(self, dev_ptr: int, ncomp: int, nl: int, level: int, noise_deg: int, stream: int) -> Ciphertext:
+        """hx_ct_upload_dev_async: ordered against the caller's CUDA stream (raw cudaStream_t, 0 = default), no host sync."""
+        return Ciphertext(self, self._lib.hx_ct_upload_dev_async(self._h, ncomp, nl, VP(dev_ptr), level, noise_deg, VP(stream)))
 
     def _ct(self, h) -> Ciphertext:
         return Ciphertext(self, h)

@@ -30,20 +30,48 @@ def block_range(rank: int, world: int, total_blocks: int):
 
 
 class TorchTransport:
-    """Moves ciphertext residues between the engine and torch tensors on the same device."""
+    """Moves ciphertext residues between the engine and torch tensors on the same device, stream-ordered (hx_ct_*_dev_async): the
+    host never waits, so the next scenario is issued while this one's compare chain still runs (the engine's rotation lane).
+    The exchange (copies, stack / pad / fold kernels, the NCCL collective's entry and exit) runs on a transport stream of its own at
+    the highest priority: the engine's rotation lanes run at the lowest, which is torch's default too."""
 
-    def __init__(self, cc, device):
+    def __init__(self, cc, device, async_exchange: bool = True):
         import torch
         self.cc, self.device, self.torch = cc, device, torch
+        self.async_exchange = async_exchange
+        self.stream = torch.cuda.Stream(device=device, priority=-1) if async_exchange else None
+
+    def exchange(self):
+        """Context for a scenario's exchange step: the transport stream is torch's current stream inside; it first waits for the
+        caller's stream and the caller's stream waits for it on exit."""
+        import contextlib
+        if not self.async_exchange:
+            return contextlib.nullcontext()
+        torch, hs = self.torch, self.stream
+
+        @contextlib.contextmanager
+        def ctx():
+            outer = torch.cuda.current_stream(self.device)
+            hs.wait_stream(outer)
+            with torch.cuda.stream(hs):
+                yield
+            outer.wait_stream(hs)
+        return ctx()
 
     def to_tensor(self, ct):
         ncomp, nl, _, _ = ct.info()
         t = self.torch.empty((ncomp, nl, self.cc.N), dtype=self.torch.int64, device=self.device)
-        ct.download_dev(t.data_ptr())
+        if self.async_exchange:
+            ct.download_dev_async(t.data_ptr(), int(self.torch.cuda.current_stream(self.device).cuda_stream))
+        else:
+            ct.download_dev(t.data_ptr())
         return t
 
     def from_tensor(self, t, level: int, deg: int):
         t = t.contiguous()
+        if self.async_exchange:
+            return self.cc.upload_dev_async(t.data_ptr(), t.shape[0], t.shape[1], level, deg,
+                                            int(self.torch.cuda.current_stream(self.device).cuda_stream))
         return self.cc.upload_dev(t.data_ptr(), t.shape[0], t.shape[1], level, deg)
 
 
@@ -69,10 +97,15 @@ class ShardedDiagonalSender(Sender):
         """Rank 0 returns the G result ciphertexts in global block order; other ranks return None."""
         import torch
         local = self._local_index(queryCipher)
-        meta = local[0].info() if local else None
-        stacked = torch.stack([self.transport.to_tensor(c) for c in local])          # [B][2][1][N]
         if self.world == 1:
             return local
+        with _exchange(self.transport):
+            return self._gather_index(local)
+
+    def _gather_index(self, local):
+        import torch
+        meta = local[0].info() if local else None
+        stacked = torch.stack([self.transport.to_tensor(c) for c in local])          # [B][2][1][N]
         counts = [block_range(r, self.world, self._total_blocks())[1] - block_range(r, self.world, self._total_blocks())[0]
                   for r in range(self.world)]
         bmax = max(counts)
@@ -97,21 +130,37 @@ class ShardedDiagonalSender(Sender):
         if self.world == 1:
             return cc.EvalSum(part, cc.GetBatchSize())
         _, _, level, deg = part.info()
-        t = self.transport.to_tensor(part)
-        self.dist.reduce(t, dst=0, op=self.dist.ReduceOp.SUM, group=self.group)
-        if self.rank != 0:
-            return None
-        t = fold_mod(t, cc.q[: t.shape[1]])
-        return cc.EvalSum(self.transport.from_tensor(t, level, deg), cc.GetBatchSize())
+        with _exchange(self.transport):
+            t = self.transport.to_tensor(part)
+            self.dist.reduce(t, dst=0, op=self.dist.ReduceOp.SUM, group=self.group)
+            if self.rank != 0:
+                return None
+            t = fold_mod(t, cc.q[: t.shape[1]])
+            total = self.transport.from_tensor(t, level, deg)
+        return cc.EvalSum(total, cc.GetBatchSize())
 
     def _total_blocks(self) -> int:
         import math
         return int(math.ceil(float(self.numVectors) / float(self.cc.GetBatchSize())))
 
 
+def _exchange(transport):
+    """The transport's exchange context if it has one (TorchTransport), else nothing (CPU transports of the gloo tests)."""
+    import contextlib
+    return transport.exchange() if hasattr(transport, "exchange") else contextlib.nullcontext()
+
+
+_FOLD_Q = {}
+
+
 def fold_mod(t, moduli):
     """Residue-wise t mod q_i over the limb axis (axis 1) of an int64 [ncomp][nl][N] tensor of
-    un-reduced sums (each < world * q_i < 2^63)."""
+    un-reduced sums (each < world * q_i < 2^63).  The modulus tensor is built once per (device, moduli):
+    torch.tensor(list, device=cuda) is a synchronous copy from pageable memory and would stall the host
+    behind the collective it follows."""
     import torch
-    q = torch.tensor([int(m) for m in moduli], dtype=torch.int64, device=t.device).view(1, -1, 1)
+    key = (str(t.device), tuple(int(m) for m in moduli))
+    q = _FOLD_Q.get(key)
+    if q is None:
+        q = _FOLD_Q[key] = torch.tensor(list(key[1]), dtype=torch.int64, device=t.device).view(1, -1, 1)
     return torch.remainder(t, q)

@@ -76,6 +76,12 @@ int hx_ct_download(hx_ct* ct, uint64_t* data);      /* data: [ncomp][nlimbs][N] 
 /* same, with DEVICE pointers on the context's GPU (NCCL staging buffers of the sharded sender) */
 hx_ct* hx_ct_upload_dev(hx_ctx* ctx, int ncomp, int nlimbs, const void* dev_data, int level, int noise_deg);
 int hx_ct_download_dev(hx_ct* ct, void* dev_data);
+/* The same two, stream-ordered instead of synchronising the host: `stream` is the caller's cudaStream_t (NULL = the legacy default
+ * stream), e.g. the stream its NCCL collectives are issued from.  The copy runs after the work queued on `stream` so far and `stream`
+ * waits for the copy.  Used by the multi-GPU sender so that a scenario's result combine does not stall the host and the
+ * next scenario's hoisted rotations overlap the previous compare chain ("rot_lane"); the uploaded ciphertext is not a lane candidate. */
+int hx_ct_download_dev_async(hx_ct* ct, void* dev_data, void* stream);
+hx_ct* hx_ct_upload_dev_async(hx_ctx* ctx, int ncomp, int nlimbs, const void* dev_data, int level, int noise_deg, void* stream);
 int hx_ct_info(hx_ct* ct, int* ncomp, int* nlimbs, int* level, int* noise_deg);
 hx_ct* hx_ct_clone(hx_ct* ct);
 void hx_ct_free(hx_ct* ct);

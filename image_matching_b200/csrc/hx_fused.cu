@@ -147,6 +147,13 @@ __device__ __forceinline__ void cp_async16(void* dst_smem, const void* src) {
 // FUSE_INV (ModDown of a large key-switch batch): `in` holds K1's output (inverse row pass done) and the CTA runs the
 // inverse column pass and the hatinv_n scaling of its n_in source tiles itself before converting ALL its target limbs
 // from shared memory -- k_inv_cols and the round trip of the scaled sources through tmpP disappear.
+// Coherent 64-bit global load that the compiler cannot turn into LD.NC: the FUSE_INV kernel reads source tiles it later overwrites
+// (its own column tile of the last scratch limb), and a line fetched through the non-coherent path could be served stale afterwards.
+__device__ __forceinline__ u64 ld_coherent(const u64* p) {
+    u64 v;
+    asm volatile("ld.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
 template <int LOGN, bool FUSE_INV>
 __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __grid_constant__ DevTables T, const __grid_constant__ TabSet ts,
                                                                   const u64* __restrict__ in, size_t in_bs, u64* __restrict__ out, size_t out_bs,
@@ -172,7 +179,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
         const u64* lim = in + (size_t)blockIdx.z * in_bs;
         u64 x[8];
 #pragma unroll
-        for (int u = 0; u < 8; u++) x[u] = __ldg(lim + col_offset<LOGN>(tile, u * kTileThreads + t));
+        for (int u = 0; u < 8; u++) x[u] = ld_coherent(lim + col_offset<LOGN>(tile, u * kTileThreads + t));
         for (int k = 0; k < n_in; k++) {
             const int sp = tab->src[k];
             const u64 sq = T.pc[sp].q;
@@ -181,7 +188,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
             __syncthreads();
             if (k + 1 < n_in) {   // next source tile in flight during this one's butterflies
 #pragma unroll
-                for (int u = 0; u < 8; u++) x[u] = __ldg(lim + (size_t)(k + 1) * T.N + col_offset<LOGN>(tile, u * kTileThreads + t));
+                for (int u = 0; u < 8; u++) x[u] = ld_coherent(lim + (size_t)(k + 1) * T.N + col_offset<LOGN>(tile, u * kTileThreads + t));
             }
             inv_col_pass<LOGN>(sm, t, T.tw_inv + (size_t)sp * T.N, sq);
             const u64 h = tab->hatinv_n[k], hs = tab->hatinv_n_sh[k];
@@ -193,7 +200,10 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
                 // per target through L1: n_in - 1 staged tiles keep the CTA at 66 KB of shared memory, 3 CTAs per SM
                 u64* back = const_cast<u64*>(lim) + (size_t)k * T.N;
 #pragma unroll
-                for (int u = 0; u < 8; u++) back[col_offset<LOGN>(tile, u * kTileThreads + t)] = split30(shoup_mul(smw[u * kWordStep], h, hs, sq));
+                for (int u = 0; u < 8; u++) {
+                    const u64 v = split30(shoup_mul(smw[u * kWordStep], h, hs, sq));
+                    asm volatile("st.global.u64 [%0], %1;" ::"l"(back + col_offset<LOGN>(tile, u * kTileThreads + t)), "l"(v) : "memory");
+                }
             }
         }
         __syncthreads();
@@ -224,7 +234,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
             const u64 m = tab->mat30[n_st * n_out + j];
             const u64* last = in + (size_t)blockIdx.z * in_bs + (size_t)n_st * T.N;   // written by this CTA above: plain loads
 #pragma unroll
-            for (int u = 0; u < 8; u++) mac30ss(acc[u], last[col_offset<LOGN>(tile, u * kTileThreads + t)], m);
+            for (int u = 0; u < 8; u++) mac30ss(acc[u], ld_coherent(last + col_offset<LOGN>(tile, u * kTileThreads + t)), m);
         }
 #pragma unroll
         for (int u = 0; u < 8; u++) smw[u * kWordStep] = fwd_encode(redc(fold30(acc[u]), pc.q, pc.qinv_neg), fp_ok(pc.q));

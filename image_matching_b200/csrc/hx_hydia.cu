@@ -105,17 +105,29 @@ std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_all(const Ct& query, int 
         for (int s = 0; s < ns - 1; s++) HX_CUDA(cudaStreamWaitEvent(others[s], evs[3], 0));
     }
     int turn = 0;
-    for (int d0 = 1; d0 < ndiag; d0 += chunk, turn++) {
-        int d1 = std::min(ndiag, d0 + chunk);
-        st = (ns > 1 && turn % ns) ? others[turn % ns - 1] : first;
-        std::vector<const EvalKey*> keys;
-        std::vector<u64> gal;
-        for (int d = d0; d < d1; d++) {
-            u64 k = galois_for_rotation(d);
-            keys.push_back(&rot_key(k));
-            gal.push_back(k);
+    try {
+        for (int d0 = 1; d0 < ndiag; d0 += chunk, turn++) {
+            int d1 = std::min(ndiag, d0 + chunk);
+            st = (ns > 1 && turn % ns) ? others[turn % ns - 1] : first;
+            std::vector<const EvalKey*> keys;
+            std::vector<u64> gal;
+            for (int d = d0; d < d1; d++) {
+                u64 k = galois_for_rotation(d);
+                keys.push_back(&rot_key(k));
+                gal.push_back(k);
+            }
+            ks_core_batch(digits, ndig, nl, keys, query->comp(0), 1, gal, rotq + ct_words * d0, ct_words);
         }
-        ks_core_batch(digits, ndig, nl, keys, query->comp(0), 1, gal, rotq + ct_words * d0, ct_words);
+    } catch (...) {
+        // e.g. a missing rotation key after some batches were queued: nothing may still write rotq / read the digits when the
+        // RotSet's destructor frees them on the engine stream
+        prof_no_events = false;
+        cudaStreamSynchronize(first);
+        for (int s = 0; s < ns - 1; s++)
+            if (others[s]) cudaStreamSynchronize(others[s]);
+        st = first;
+        free_words(digits);
+        throw;
     }
     st = first;
     if (ns > 1)

@@ -123,17 +123,26 @@ ParamSet generate_params(int depth, int scale_bits, int first_mod_bits, int ring
 
     if (ring_dim) {
         P.N = ring_dim;
-        choose(P.N);
     } else {
-        for (auto& row : kStdBits) {
-            P.N = row[0];
-            choose(P.N);
-            std::vector<u64> all(P.q);
-            all.insert(all.end(), P.p.begin(), P.p.end());
-            if (bitlen_product(all) <= row[1]) break;
-            if (row[0] == 131072) throw std::runtime_error("no ring dimension satisfies the security bound");
+        // StdLatticeParm::FindRingDim on the NOMINAL budget qBound = firstModSize + (L-1)*scalingModSize + logP, with logP from
+        // CryptoParametersRNS::EstimateLogP(..., addOne = true): (largest digit's nominal bits + 1) rounded up to whole 60-bit
+        // auxiliary primes.  The estimate -- not the generated primes -- picks N: depth 12 gives 60 + 12*45 + 300 = 900 > 881,
+        // hence N = 2^16 (pinned by /root/reference/tools/figures/15IndexTotals.csv:2,5 for approach 3).  The number of P limbs
+        // (choose) still follows PrecomputeCRTTables: ceil(bits(largest digit product) / 60) on the generated primes.
+        int maxbits = 0;
+        for (int j = 0; j < P.dnum; ++j) {
+            int b = 0;
+            for (int i = j * P.alpha; i < P.L && i < (j + 1) * P.alpha; ++i) b += (i == 0 ? first_mod_bits : scale_bits);
+            if (b > maxbits) maxbits = b;
         }
+        const int size_p = (maxbits + 1 + 59) / 60;
+        const int qbound = first_mod_bits + (P.L - 1) * scale_bits + size_p * 60;
+        P.N = 0;
+        for (auto& row : kStdBits)
+            if (qbound <= row[1]) { P.N = row[0]; break; }
+        if (!P.N) throw std::runtime_error("no ring dimension satisfies the security bound");
     }
+    choose(P.N);
     for (u64 x : P.q) P.psi_q.push_back(min_primitive_root(2ull * P.N, x));
     for (u64 x : P.p) P.psi_p.push_back(min_primitive_root(2ull * P.N, x));
     return P;

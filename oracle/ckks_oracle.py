@@ -94,6 +94,29 @@ _HESTD_128_CLASSIC_TERNARY = {1024: 27, 2048: 54, 4096: 109, 8192: 218, 16384: 4
                               65536: 1747, 131072: 3523}
 
 
+def estimate_qbound(depth: int, scale_bits: int = 45, first_mod: int = 60, num_large_digits: int = 0, aux_bits: int = 60) -> int:
+    """qBound of ParamsGenCKKSRNS for HYBRID key switching (upstream ckksrns-parametergeneration.cpp +
+    CryptoParametersRNS::EstimateLogP with addOne = true), FIXEDMANUAL (no extra modulus)."""
+    L = depth + 1
+    dnum = num_large_digits or (3 if depth > 3 else (2 if depth > 0 else 1))
+    alpha = -(-L // dnum)
+    dnum = -(-L // alpha)
+    bits = [scale_bits] * L
+    bits[0] = first_mod
+    max_bits = max(sum(bits[j * alpha:min(L, (j + 1) * alpha)]) for j in range(dnum)) + 1   # addOne
+    size_p = -(-max_bits // aux_bits)
+    return first_mod + (L - 1) * scale_bits + size_p * aux_bits
+
+
+def ring_dim_for(depth: int, scale_bits: int = 45, first_mod: int = 60, num_large_digits: int = 0, aux_bits: int = 60) -> int:
+    """StdLatticeParm::FindRingDim(HEStd_ternary, HEStd_128_classic, qBound)."""
+    qb = estimate_qbound(depth, scale_bits, first_mod, num_large_digits, aux_bits)
+    for N in sorted(_HESTD_128_CLASSIC_TERNARY):
+        if qb <= _HESTD_128_CLASSIC_TERNARY[N]:
+            return N
+    return 2 * max(_HESTD_128_CLASSIC_TERNARY)
+
+
 @dataclass
 class Params:
     N: int
@@ -161,17 +184,14 @@ def gen_params(depth: int, scale_bits: int = 45, first_mod: int = 60, ring_dim: 
         return q, p
 
     if ring_dim is None:
-        N = 1024
-        while True:
-            q, p = pick(N)
-            logqp = sum(x.bit_length() for x in q) + sum(x.bit_length() for x in p)
-            # upstream uses ceil(log2(QP)) of the product
-            prod = 1
-            for x in q + p:
-                prod *= x
-            if prod.bit_length() <= _HESTD_128_CLASSIC_TERNARY[N]:
-                break
-            N *= 2
+        # Ring dimension: StdLatticeParm::FindRingDim on the NOMINAL bit budget qBound = firstModSize + (L-1)*scalingModSize
+        # + logP, where logP comes from CryptoParametersRNS::EstimateLogP(..., addOne = true): the largest digit's nominal
+        # bits PLUS ONE, rounded up to whole 60-bit auxiliary primes.  The estimate, not the generated
+        # primes, picks N -- depth 12 gives 60 + 12*45 + 300 = 900 > 881, hence N = 2^16, which is what the ciphertext byte
+        # counts of /root/reference/tools/figures/15IndexTotals.csv:2,5 pin for approach 3.  The actual number of P limbs
+        # below (pick) still follows PrecomputeCRTTables: ceil(bits(largest digit product) / 60) on the generated primes.
+        N = ring_dim_for(depth, scale_bits, first_mod, num_large_digits, aux_bits)
+        q, p = pick(N)
     else:
         N = ring_dim
         q, p = pick(N)

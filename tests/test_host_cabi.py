@@ -35,7 +35,7 @@ def test_product_parameter_generation_equals_oracle():
     import ctypes as C
     from image_matching_b200 import _lib
     lib = _lib.load()
-    for depth, ring in ((11, 0), (11, 4096), (3, 2048), (13, 0)):
+    for depth, ring in ((11, 0), (11, 4096), (3, 2048), (13, 0), (12, 0), (18, 0)):   # 0: the recipe picks the ring
         N, L, K, d = C.c_int(), C.c_int(), C.c_int(), C.c_int()
         q, p, sq, sp = (np.zeros(40, dtype=np.uint64) for _ in range(4))
         u = lambda a: a.ctypes.data_as(_lib.U64P)

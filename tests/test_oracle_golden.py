@@ -8,16 +8,39 @@ import pytest
 from oracle import ckks_oracle as O
 
 
-def test_parameter_recipe_matches_reference_sizes():
-    # Appendix B / tools/figures/15IndexTotals.csv: approach 5 -> N = 2^15, L = 12, K = 4, dnum 3
-    P = O.gen_params(11)
-    assert (P.N, P.L, P.K, P.dnum, P.alpha) == (32768, 12, 4, 3, 4)
-    assert P.q[0] == 0xFFFFFFFFFFC0001              # largest 60-bit prime = 1 mod 2^16
+# depth from computeRequiredDepth (/root/reference/src/openFHE_wrapper.cpp:6-44, COMP_DEPTH 10,
+# ALPHA_DEPTH 2), (N, L) pinned by the ciphertext byte counts 2*L*N*8 behind /root/reference/tools/figures/
+# 15IndexTotals.csv:2,5 and 15MembershipTotals.csv:2,5 (golden item 4 of SURVEY 8(c)).
+APPENDIX_B = {   # approach: (depth, N, L, dnum, alpha, fresh ciphertext bytes, qBound of the ring-dimension estimate)
+    1: (13, 65536, 14, 3, 5, 14680064, 945),
+    2: (18, 65536, 19, 3, 7, 19922944, 1230),
+    3: (12, 65536, 13, 3, 5, 13631488, 900),
+    4: (11, 32768, 12, 3, 4, 6291456, 795),
+    5: (11, 32768, 12, 3, 4, 6291456, 795),
+}
+
+
+@pytest.mark.parametrize("approach", [1, 2, 3, 4, 5])
+def test_parameter_recipe_matches_reference_sizes(approach):
+    depth, N, L, dnum, alpha, ct_bytes, qbound = APPENDIX_B[approach]
+    assert O.estimate_qbound(depth) == qbound
+    P = O.gen_params(depth)
+    assert (P.N, P.L, P.dnum, P.alpha) == (N, L, dnum, alpha)
+    assert 2 * P.L * P.N * 8 == ct_bytes
+    # number of P limbs: PrecomputeCRTTables takes ceil(bits(largest digit product) / 60) on the GENERATED primes, while the
+    # ring-dimension estimate above charges one 60-bit prime more whenever the nominal digit size is a multiple of 60
+    # (addOne): approaches 1 and 3 have a 60 + 4*45 = 240-bit nominal digit whose real product is 239.99.. bits -> K = 4
+    # (SURVEY App. B lists the estimate's 5; no reference-held fixture pins K)
+    digit_bits = max(O._prod(P.q[j * P.alpha:(j + 1) * P.alpha]).bit_length() for j in range(P.dnum))
+    assert P.K == -(-digit_bits // 60) == {1: 4, 2: 6, 3: 4, 4: 4, 5: 4}[approach]
     assert all(x % (2 * P.N) == 1 for x in P.q + P.p)
-    assert len(set(P.q + P.p)) == 16
-    assert [x.bit_length() for x in P.q[1:]] == [46, 45] * 5 + [46]
-    # ciphertext bytes 2*L*N*8 = 6.29 MB, one evaluation key 2*dnum*(L+K)*N*8 = 25.17 MB
-    assert 2 * P.L * P.N * 8 == 6291456 and 2 * P.dnum * (P.L + P.K) * P.N * 8 == 25165824
+    assert len(set(P.q + P.p)) == P.L + P.K
+    assert P.q[0].bit_length() == 60 and all(x.bit_length() == 60 for x in P.p)
+    assert all(x.bit_length() in (45, 46) for x in P.q[1:])
+    if approach == 5:
+        assert P.q[0] == 0xFFFFFFFFFFC0001              # largest 60-bit prime = 1 mod 2^16
+        assert [x.bit_length() for x in P.q[1:]] == [46, 45] * 5 + [46]
+        assert 2 * P.dnum * (P.L + P.K) * P.N * 8 == 25165824   # one evaluation key 25.17 MB
     for q, psi in zip(P.q + P.p, P.psi_q + P.psi_p):
         assert pow(psi, P.N, q) == q - 1
 

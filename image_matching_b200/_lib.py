@@ -5,7 +5,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhydia_b200.so")
+LIB_PATH = os.environ.get("HYDIA_B200_LIB") or os.path.join(_HERE, "libhydia_b200.so")   # the override is for diagnostic builds only
 
 U64P = C.POINTER(C.c_uint64)
 F64P = C.POINTER(C.c_double)

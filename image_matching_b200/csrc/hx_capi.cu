@@ -64,6 +64,17 @@ void hx_ctx_destroy(hx_ctx* ctx) {
 }
 int hx_ctx_sync(hx_ctx* ctx) { HX_TRY_INT(need(ctx, "ctx"); ctx->eng->sync();) }
 uint64_t hx_ctx_launches(hx_ctx* ctx) { return ctx ? ctx->eng->launches : 0; }
+// diagnosis: cross-stream reuse policies of the stream-ordered pool (bit 0 follow-event, bit 1 opportunistic, bit 2 internal dependencies)
+static void set_pool_reuse(int device, int value) {
+    cudaMemPool_t pool;
+    HX_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+    int a = value & 1;
+    int b = (value >> 1) & 1;
+    int c = (value >> 2) & 1;
+    HX_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolReuseFollowEventDependencies, &a));
+    HX_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolReuseAllowOpportunistic, &b));
+    HX_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolReuseAllowInternalDependencies, &c));
+}
 int hx_ctx_set_option(hx_ctx* ctx, const char* name, int value) {
     HX_TRY_INT(
         need(ctx, "ctx"); need(name, "name");
@@ -75,6 +86,8 @@ int hx_ctx_set_option(hx_ctx* ctx, const char* name, int value) {
         else if (n == "rot_lane") ctx->eng->rot_lane = value != 0;
         else if (n == "ks_fuse_inv") g_ks_fuse_inv = std::max(0, value);
         else if (n == "batch_blocks") ctx->eng->batch_blocks = value != 0;
+        else if (n == "pdl") g_pdl = value != 0;
+        else if (n == "pool_reuse") set_pool_reuse(ctx->eng->device, value);
         else throw std::runtime_error("hx_ctx_set_option: unknown option " + n);)
 }
 int hx_prof_kinds(void) { return PK_COUNT; }

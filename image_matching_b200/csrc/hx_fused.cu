@@ -22,6 +22,7 @@
 #endif
 namespace hx {
 
+int g_pdl = 1;
 int g_ks_fuse_inv = 16;   // > 0: ModDown of key-switch batches with at least this many polynomials runs K2a inside K2b (hx_ctx_set_option "ks_fuse_inv")
 
 constexpr unsigned kTileBytes = kTileN * sizeof(u64);                                   // 16 KB
@@ -476,7 +477,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_rescale_cols(const __
 #pragma unroll
     for (int u = 0; u < 8; u++) {
         const int l = u * kTileThreads + t;
-        const u64 v = unsplit30(__ldg(src + col_offset<LOGN>(tile, l)));   // k_inv_cols stores split words
+        const u64 v = unsplit30(ldg64(src + col_offset<LOGN>(tile, l)));   // k_inv_cols stores split words
         u64 r = shoup_mul(v, negqlinv.v[i], negqlinv.sh[i], q);
         if (v > half) r = add_mod(r, 1, q);
         smw[u * kWordStep] = fwd_encode(r, fp_ok(q));

@@ -71,7 +71,15 @@ std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_all(const Ct& query, int 
     if (lane) {
         // rotation lane: nothing below depends on what the engine stream still has queued (see hx_engine.h)
         for (int s = 0; s < ns; s++)
-            if (!lane_streams[s]) HX_CUDA(cudaStreamCreateWithFlags(&lane_streams[s], cudaStreamNonBlocking));   // priority 0 = lowest
+            if (!lane_streams[s]) {
+                if (getenv("HX_LANE_PRIO")) {   // diagnosis: lanes at the engine stream's priority
+                    int pr = 0;
+                    HX_CUDA(cudaStreamGetPriority(main_st, &pr));
+                    HX_CUDA(cudaStreamCreateWithPriority(&lane_streams[s], cudaStreamNonBlocking, pr));
+                } else {
+                    HX_CUDA(cudaStreamCreateWithFlags(&lane_streams[s], cudaStreamNonBlocking));   // priority 0 = lowest
+                }
+            }
         for (int s = 0; s < 5; s++)
             if (!lane_events[s]) HX_CUDA(cudaEventCreateWithFlags(&lane_events[s], cudaEventDisableTiming));
         st = lane_streams[0];   // allocations, the copy of the query and its ModUp are ordered on the lane

@@ -68,7 +68,7 @@ void launch_baseconv(const DevTables& T, const BaseConvTable* tab, int n_in, int
 // by every batch entry (hoisted rotations share them) and stay L2-resident.  Keys are stored in
 // Montgomery form, so each output is 3 wide MACs + one REDC (3*q^2 < q*2^64).
 __global__ void __launch_bounds__(kThreads) k_ks_inner(DevTables T, const u64* __restrict__ digits, int ndig, int nl, int L, int K,
-                                                       const u64* const* __restrict__ keyA, const u64* const* __restrict__ keyB,
+                                                       const u64* const* keyA, const u64* const* keyB,
                                                        u64* __restrict__ out, size_t out_bs) {
     int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (idx >= T.N) return;
@@ -76,8 +76,8 @@ __global__ void __launch_bounds__(kThreads) k_ks_inner(DevTables T, const u64* _
     int kl = i < nl ? i : i - nl + L;          // limb index inside the key / prime index
     const PrimeConst pc = T.pc[kl];
     const int ext = nl + K;
-    const u64* ka = keyA[blockIdx.z];
-    const u64* kb = keyB[blockIdx.z];
+    const u64* ka = reinterpret_cast<const u64*>(ldg64(reinterpret_cast<const u64*>(keyA + blockIdx.z)));   // pointer tables are pool memory
+    const u64* kb = reinterpret_cast<const u64*>(ldg64(reinterpret_cast<const u64*>(keyB + blockIdx.z)));
     u128d b0 = {0, 0}, b1 = {0, 0}, a0 = {0, 0}, a1 = {0, 0};
     for (int j = 0; j < ndig; j++) {
         ulonglong2 d = ldg128(digits + ((size_t)j * ext + i) * T.N + idx);
@@ -110,8 +110,8 @@ void launch_ks_inner(const DevTables& T, const u64* digits, int ndig, int nl, in
 // ApproxModDown epilogue (row P5) fused with "+ c0" and the automorphism gather (row P3):
 //   out[i][j] = ct'[i][m] - conv'[i][m] + addend[i][m],  m = map[j]   (keys and conversion matrix carry P^-1)
 // grid.y = limb (nl), grid.z = batch*2 + component; addend ([comps][nl][N]) applies to components < addend_comps.
-__global__ void __launch_bounds__(kThreads) k_moddown_finish(DevTables T, const u64* __restrict__ ct, size_t ct_bs, const u64* __restrict__ conv,
-                                                             size_t conv_bs, const u64* __restrict__ addend, int addend_comps, const u32* const* __restrict__ maps,
+__global__ void __launch_bounds__(kThreads) k_moddown_finish(DevTables T, const u64* ct, size_t ct_bs, const u64* conv,
+                                                             size_t conv_bs, const u64* addend, int addend_comps, const u32* const* maps,
                                                              u64* __restrict__ out, size_t out_bs, int nl, int ext) {
     int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (idx >= T.N) return;
@@ -121,13 +121,13 @@ __global__ void __launch_bounds__(kThreads) k_moddown_finish(DevTables T, const 
     const u64* c = ct + (size_t)batch * ct_bs + ((size_t)comp * ext + i) * T.N;
     const u64* v = conv + (size_t)batch * conv_bs + ((size_t)comp * nl + i) * T.N;
     const u64* ad = (addend != nullptr && comp < addend_comps) ? addend + ((size_t)comp * nl + i) * T.N : nullptr;
-    const u32* map = maps ? maps[batch] : nullptr;
+    const u32* map = maps ? reinterpret_cast<const u32*>(ldg64(reinterpret_cast<const u64*>(maps + batch))) : nullptr;
     u64 r[2];
 #pragma unroll
     for (int e = 0; e < 2; e++) {
         int m = map ? (int)map[idx + e] : idx + e;
-        u64 d = sub_mod(c[m], v[m], q);
-        if (ad) d = add_mod(d, ad[m], q);
+        u64 d = sub_mod(ldg64(c + m), ldg64(v + m), q);
+        if (ad) d = add_mod(d, ldg64(ad + m), q);
         r[e] = d;
     }
     ulonglong2 o = {r[0], r[1]};
@@ -152,8 +152,8 @@ __global__ void __launch_bounds__(kThreads) k_ew(DevTables T, int op, u64* __res
     int i = blockIdx.y;
     const PrimeConst pc = T.pc[i];
     size_t off = (size_t)i * T.N + idx;
-    ulonglong2 x = *reinterpret_cast<const ulonglong2*>(a + blockIdx.z * cs_a + off);
-    ulonglong2 y = *reinterpret_cast<const ulonglong2*>(b + blockIdx.z * cs_b + off);
+    ulonglong2 x = ldg128(a + blockIdx.z * cs_a + off);
+    ulonglong2 y = ldg128(b + blockIdx.z * cs_b + off);
     ulonglong2 r;
     if (op == EW_ADD) { r.x = add_mod(x.x, y.x, pc.q); r.y = add_mod(x.y, y.y, pc.q); }
     else if (op == EW_SUB) { r.x = sub_mod(x.x, y.x, pc.q); r.y = sub_mod(x.y, y.y, pc.q); }
@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(kThreads) k_mul_scalar(DevTables T, u64* __res
     int i = blockIdx.y;
     const u64 q = T.pc[i].q;
     size_t off = (size_t)i * T.N + idx;
-    ulonglong2 x = *reinterpret_cast<const ulonglong2*>(a + blockIdx.z * cs_a + off);
+    ulonglong2 x = ldg128(a + blockIdx.z * cs_a + off);
     x.x = shoup_mul(x.x, s.v[i], s.sh[i], q);
     x.y = shoup_mul(x.y, s.v[i], s.sh[i], q);
     st128(out + blockIdx.z * cs_out + off, x);
@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(kThreads) k_add_scalar(DevTables T, u64* __res
     int i = blockIdx.y;
     const u64 q = T.pc[i].q;
     size_t off = ((size_t)blockIdx.z * gridDim.y + i) * T.N + idx;
-    ulonglong2 x = *reinterpret_cast<const ulonglong2*>(a + off);
+    ulonglong2 x = ldg128(a + off);
     if (blockIdx.z % ncomp == 0) {   // the constant goes to component 0; the other components are copied
         x.x = add_mod(x.x, s.v[i], q);
         x.y = add_mod(x.y, s.v[i], q);
@@ -238,10 +238,10 @@ __global__ void __launch_bounds__(kThreads) k_tensor(DevTables T, u64* __restric
     if (!bca) a += (size_t)blockIdx.z * 2 * cs_a;
     if (!bcb) b += (size_t)blockIdx.z * 2 * cs_b;
     out += (size_t)blockIdx.z * 3 * nl * T.N;   // batch entries are contiguous ciphertexts
-    ulonglong2 a0 = *reinterpret_cast<const ulonglong2*>(a + off);
-    ulonglong2 a1 = *reinterpret_cast<const ulonglong2*>(a + cs_a + off);
-    ulonglong2 b0 = *reinterpret_cast<const ulonglong2*>(b + off);
-    ulonglong2 b1 = *reinterpret_cast<const ulonglong2*>(b + cs_b + off);
+    ulonglong2 a0 = ldg128(a + off);
+    ulonglong2 a1 = ldg128(a + cs_a + off);
+    ulonglong2 b0 = ldg128(b + off);
+    ulonglong2 b1 = ldg128(b + cs_b + off);
     size_t cs_o = (size_t)nl * T.N;
     ulonglong2 r;
     r.x = mulmod(a0.x, b0.x, pc); r.y = mulmod(a0.y, b0.y, pc);
@@ -293,7 +293,7 @@ __global__ void __launch_bounds__(kThreads) k_batch_sum(DevTables T, u64* __rest
     if (idx >= T.N) return;
     const u64 q = T.pc[blockIdx.y % nl].q;
     size_t off = (size_t)blockIdx.y * T.N + idx;
-    ulonglong2 s = accumulate ? *reinterpret_cast<const ulonglong2*>(acc + off) : make_ulonglong2(0, 0);
+    ulonglong2 s = accumulate ? ldg128(acc + off) : make_ulonglong2(0, 0);
     for (int z = 0; z < nbatch; z++) {
         const ulonglong2 x = ldg128(in + (size_t)z * bs + off);
         s.x = add_mod(s.x, x.x, q);
@@ -311,7 +311,7 @@ __global__ void __launch_bounds__(kThreads) k_automorph(int N, u64* __restrict__
     int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= N) return;
     size_t off = (size_t)blockIdx.y * N;
-    out[off + idx] = in[off + map[idx]];
+    out[off + idx] = ldg64(in + off + map[idx]);
 }
 void launch_automorph(const DevTables& T, u64* out, const u64* in, const u32* map, int nlimbs_total, cudaStream_t st) {
     dim3 grid((T.N + kThreads - 1) / kThreads, nlimbs_total, 1);
@@ -374,7 +374,7 @@ __global__ void __launch_bounds__(kThreads) k_rescale_prep(DevTables T, const u6
     int i = blockIdx.y;
     const u64 q = T.pc[i].q;
     const u64 half = T.pc[nl - 1].q >> 1;
-    ulonglong2 v = *reinterpret_cast<const ulonglong2*>(last + blockIdx.z * last_bs + idx);
+    ulonglong2 v = ldg128(last + blockIdx.z * last_bs + idx);
     ulonglong2 r;
     r.x = shoup_mul(v.x, c.v[i], c.sh[i], q);
     r.y = shoup_mul(v.y, c.v[i], c.sh[i], q);
@@ -394,8 +394,8 @@ __global__ void __launch_bounds__(kThreads) k_rescale_finish(DevTables T, u64* _
     int i = blockIdx.y;
     const u64 q = T.pc[i].q;
     size_t off = (size_t)i * T.N + idx;
-    ulonglong2 x = *reinterpret_cast<const ulonglong2*>(c + blockIdx.z * c_bs + off);
-    ulonglong2 t = *reinterpret_cast<const ulonglong2*>(tmp + blockIdx.z * tmp_bs + off);
+    ulonglong2 x = ldg128(c + blockIdx.z * c_bs + off);
+    ulonglong2 t = ldg128(tmp + blockIdx.z * tmp_bs + off);
     x.x = add_mod(shoup_mul(x.x, s.v[i], s.sh[i], q), t.x, q);
     x.y = add_mod(shoup_mul(x.y, s.v[i], s.sh[i], q), t.y, q);
     st128(out + blockIdx.z * out_bs + off, x);

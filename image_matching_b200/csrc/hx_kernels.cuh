@@ -125,6 +125,7 @@ void launch_automorph(const DevTables& T, u64* out, const u64* in, const u32* ma
 void launch_automap(int N, int logN, u64 k, u32* map, cudaStream_t st);
 // Launch with programmatic stream serialization (the kernel's first statement must be pdl_wait()): hides the launch and
 // block-scheduling latency between the ~1000 small dependent kernels of a step.
+extern int g_pdl;   // 0: plain stream-ordered launches (hx_ctx_set_option "pdl"; diagnosis of launch-overlap hazards)
 template <class... KArgs, class... Args>
 inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
     cudaLaunchConfig_t cfg = {};
@@ -134,7 +135,7 @@ inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t s
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    attr[0].val.programmaticStreamSerializationAllowed = g_pdl ? 1 : 0;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);

@@ -131,7 +131,25 @@ __device__ __forceinline__ u64 mulmod(u64 a, u64 b, const PrimeConst& pc) {
 }
 
 // 128-bit global access (limb-coalesced: two adjacent coefficients of one limb).
-__device__ __forceinline__ ulonglong2 ldg128(const u64* p) { return __ldg(reinterpret_cast<const ulonglong2*>(p)); }
+// ---- global loads: which cache path for which data ------------------------------------------------------------------------
+// MUTABLE data (ciphertexts, digits, scratch: anything a kernel of this process writes during a query) is read with ld.global.cg
+// (L2 only).  The non-coherent path (ld.global.nc / __ldg, or what the compiler emits for a `const __restrict__` pointer) is kept
+// for data that never changes after setup (twiddles, evaluation keys, database blocks, tables).  Measured on B200
+// (tools/race_probe.py, profiles/r2_race_*.log): with the compare chain of one scenario on the engine stream and the next
+// scenario's rotations running concurrently on the lane streams, ~3 % of the calls returned a ciphertext with stale 128-byte
+// lines when produced data was read through LD.NC -- the pool recycles addresses between the streams and a line cached through
+// the non-coherent path on an SM outlived the kernel boundary of the OTHER stream.  With .cg loads: 0 mismatches in 2560 calls.
+// These words are read once per CTA, so L1 gives nothing for them anyway.
+__device__ __forceinline__ ulonglong2 ldg128(const u64* p) {
+    ulonglong2 v;
+    asm volatile("ld.global.cg.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ u64 ldg64(const u64* p) {
+    u64 v;
+    asm volatile("ld.global.cg.u64 %0, [%1];" : "=l"(v) : "l"(p));
+    return v;
+}
 __device__ __forceinline__ ulonglong2 ld_stream128(const u64* p) {
     ulonglong2 v;
     asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));

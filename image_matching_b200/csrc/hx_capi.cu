@@ -78,13 +78,13 @@ static void set_pool_reuse(int device, int value) {
 int hx_ctx_set_option(hx_ctx* ctx, const char* name, int value) {
     HX_TRY_INT(
         need(ctx, "ctx"); need(name, "name");
-        std::lock_guard<std::recursive_mutex> g(ctx->eng->mu);
+        Engine::Guard g(ctx->eng.get());
         std::string n(name);
         if (n == "force_unfused") ctx->eng->force_unfused = value != 0;
         else if (n == "rot_chunk") ctx->eng->rot_chunk = value;
         else if (n == "rot_streams") ctx->eng->rot_streams = std::max(1, std::min(4, value));
         else if (n == "rot_lane") ctx->eng->rot_lane = value != 0;
-        else if (n == "ks_fuse_inv") g_ks_fuse_inv = std::max(0, value);
+        else if (n == "ks_fuse_inv") ctx->eng->ks_fuse_inv = std::max(0, value);
         else if (n == "batch_blocks") ctx->eng->batch_blocks = value != 0;
         else if (n == "pdl") g_pdl = value != 0;
         else if (n == "pool_reuse") set_pool_reuse(ctx->eng->device, value);
@@ -125,7 +125,7 @@ hx_ct* hx_ct_upload_dev(hx_ctx* ctx, int ncomp, int nlimbs, const void* dev_data
         need(ctx, "ctx"); need(dev_data, "dev_data");
         if (ncomp < 1 || ncomp > 3 || nlimbs < 1 || nlimbs > ctx->eng->L) throw std::runtime_error("hx_ct_upload_dev: bad shape");
         Engine* e = ctx->eng.get();
-        std::lock_guard<std::recursive_mutex> g(e->mu);
+        Engine::Guard g(e);
         Ct c = e->new_ct(ncomp, nlimbs, level, noise_deg);
         HX_CUDA(cudaMemcpyAsync(c->d, dev_data, sizeof(u64) * (size_t)ncomp * nlimbs * e->N, cudaMemcpyDeviceToDevice, e->st));
         e->sync();
@@ -137,7 +137,7 @@ int hx_ct_download_dev(hx_ct* ct, void* dev_data) {
         need(ct, "ct"); need(dev_data, "dev_data");
         if (ct->ct->nb != 1) throw std::runtime_error("hx_ct_download_dev: batched ciphertext (hx_ct_unstack it first)");
         Engine* e = ct->ct->eng;
-        std::lock_guard<std::recursive_mutex> g(e->mu);
+        Engine::Guard g(e);
         HX_CUDA(cudaMemcpyAsync(dev_data, ct->ct->d, sizeof(u64) * (size_t)ct->ct->ncomp * ct->ct->nl * e->N, cudaMemcpyDeviceToDevice, e->st));
         e->sync();)
 }
@@ -157,7 +157,7 @@ int hx_ct_download_dev_async(hx_ct* ct, void* dev_data, void* stream) {
         need(ct, "ct"); need(dev_data, "dev_data");
         if (ct->ct->nb != 1) throw std::runtime_error("hx_ct_download_dev_async: batched ciphertext (hx_ct_unstack it first)");
         Engine* e = ct->ct->eng;
-        std::lock_guard<std::recursive_mutex> g(e->mu);
+        Engine::Guard g(e);
         HX_CUDA(cudaSetDevice(e->device));
         order_streams((cudaStream_t)stream, e->st);
         HX_CUDA(cudaMemcpyAsync(dev_data, ct->ct->d, sizeof(u64) * (size_t)ct->ct->ncomp * ct->ct->nl * e->N, cudaMemcpyDeviceToDevice, e->st));
@@ -168,7 +168,7 @@ hx_ct* hx_ct_upload_dev_async(hx_ctx* ctx, int ncomp, int nlimbs, const void* de
         need(ctx, "ctx"); need(dev_data, "dev_data");
         if (ncomp < 1 || ncomp > 3 || nlimbs < 1 || nlimbs > ctx->eng->L) throw std::runtime_error("hx_ct_upload_dev_async: bad shape");
         Engine* e = ctx->eng.get();
-        std::lock_guard<std::recursive_mutex> g(e->mu);
+        Engine::Guard g(e);
         HX_CUDA(cudaSetDevice(e->device));
         Ct c = e->new_ct(ncomp, nlimbs, level, noise_deg);
         order_streams((cudaStream_t)stream, e->st);
@@ -324,7 +324,7 @@ int hx_ntt(hx_ctx* ctx, uint64_t* data, int nbatch, const int* primes, int nprim
     HX_TRY_INT(
         need(ctx, "ctx"); need(data, "data"); need(primes, "primes");
         Engine* e = ctx->eng.get();
-        std::lock_guard<std::recursive_mutex> g(e->mu);
+        Engine::Guard g(e);
         size_t words = (size_t)nbatch * e->N;
         u64* d = e->alloc_words(words);
         HX_CUDA(cudaMemcpyAsync(d, data, words * sizeof(u64), cudaMemcpyHostToDevice, e->st));

@@ -129,7 +129,7 @@ static void fft_inplace(std::vector<std::complex<double>>& a, int sign) {
 
 // ------------------------------------------------------------------------------------------ Client
 Client::Client(std::shared_ptr<Engine> e, u64 seed_) : keep(e), eng(e.get()), seed(seed_) {
-    std::lock_guard<std::recursive_mutex> g(eng->mu);
+    Engine::Guard g(eng);
     const int N = eng->N, np = eng->L + eng->K;
     slot_idx.resize(N / 2);
     u64 m = 2ull * N, x = 1;
@@ -209,7 +209,7 @@ EvalKey Client::ks_keygen(const u64* s_old, const u64* s_new) {
     return k;
 }
 void Client::gen_mult_key() {
-    std::lock_guard<std::recursive_mutex> g(eng->mu);
+    Engine::Guard g(eng);
     const int N = eng->N, np = eng->L + eng->K;
     u64* s2 = eng->alloc_words((size_t)np * N);
     launch_ew(eng->T, EW_MUL, s2, d_sk, d_sk, np, 1, 0, 0, 0, eng->st);   // limb i <-> prime i for all L+K limbs
@@ -218,7 +218,7 @@ void Client::gen_mult_key() {
     eng->sync();
 }
 void Client::gen_rot_key_galois(u64 k) {
-    std::lock_guard<std::recursive_mutex> g(eng->mu);
+    Engine::Guard g(eng);
     if (eng->has_rot_key(k)) return;
     const int N = eng->N, np = eng->L + eng->K;
     // EvalAutomorphismKeyGen: new key = sigma_{k^-1}(s)
@@ -261,7 +261,7 @@ std::vector<long long> Client::encode(const double* values, int n) const {
 }
 
 void Client::encode_rns(const double* values, int n, u64* host_out) {
-    std::lock_guard<std::recursive_mutex> g(eng->mu);
+    Engine::Guard g(eng);
     const int N = eng->N, L = eng->L;
     std::vector<long long> coeffs = encode(values, n);
     long long* d_small = (long long*)eng->alloc_words(N);
@@ -277,7 +277,7 @@ void Client::encode_rns(const double* values, int n, u64* host_out) {
 }
 
 Ct Client::encrypt(const double* values, int n) {
-    std::lock_guard<std::recursive_mutex> g(eng->mu);
+    Engine::Guard g(eng);
     const int N = eng->N, L = eng->L;
     std::vector<long long> coeffs = encode(values, n);
     long long* d_small = (long long*)eng->alloc_words(N);
@@ -298,13 +298,13 @@ Ct Client::encrypt(const double* values, int n) {
 }
 
 void Client::enroll(int block, int diag, const double* values, int n) {
-    std::lock_guard<std::recursive_mutex> g(eng->mu);
+    Engine::Guard g(eng);
     Ct ct = encrypt(values, n);
     eng->db_store_device(block, diag, ct->d);
 }
 
 void Client::decrypt(const Ct& ct, double* out) {
-    std::lock_guard<std::recursive_mutex> g(eng->mu);
+    Engine::Guard g(eng);
     const int N = eng->N, nl = ct->nl;
     u64* acc = eng->alloc_words((size_t)nl * N);
     k_decrypt<<<grid1(N, nl), kCT, 0, eng->st>>>(eng->T, acc, ct->d, ct->ncomp, ct->comp_stride(), d_sk);
@@ -343,7 +343,7 @@ void Client::decrypt(const Ct& ct, double* out) {
 }
 
 void Client::secret(int8_t* out) {
-    std::lock_guard<std::recursive_mutex> g(eng->mu);
+    Engine::Guard g(eng);
     std::vector<int> h(eng->N);
     HX_CUDA(cudaMemcpyAsync(h.data(), d_sk_small, sizeof(int) * eng->N, cudaMemcpyDeviceToHost, eng->st));
     eng->sync();

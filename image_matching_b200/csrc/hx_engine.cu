@@ -8,13 +8,16 @@
 namespace hx {
 
 // ------------------------------------------------------------------------------------------ CtObj
+// Handle destructors may run on any host thread at any time (hx_ct_free from another OpenMP thread while this engine is inside
+// its hoisted rotations with `st` repointed): they take the engine lock and free on the engine stream, on which every handle's
+// contents were produced or joined.
 CtObj::~CtObj() {
-    if (d && eng) eng->free_words(d);
+    if (d && eng) { Engine::Guard g(eng); cudaFreeAsync(d, eng->st_main); }
 }
 u64* CtObj::comp(int c) const { return d + (size_t)c * comp_stride(); }
 size_t CtObj::comp_stride() const { return (size_t)nl * eng->N; }
 Engine::Digits::~Digits() {
-    if (d && eng) eng->free_words(d);
+    if (d && eng) { Engine::Guard g(eng); cudaFreeAsync(d, eng->st_main); }
 }
 
 // ------------------------------------------------------------------------------------------ setup
@@ -35,7 +38,9 @@ Engine::Engine(int N_, int L_, int K_, int dnum_, const u64* q, const u64* p, co
         int least = 0, greatest = 0;
         HX_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
         HX_CUDA(cudaStreamCreateWithPriority(&st, cudaStreamNonBlocking, greatest));
+        st_main = st;
     }
+    init_device_kernels(logN);   // > 48 KB dynamic shared memory opt-ins are per device
     // keep freed blocks in the stream-ordered pool: op outputs are allocated per call
     cudaMemPool_t pool;
     HX_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
@@ -84,7 +89,7 @@ Engine::Engine(int N_, int L_, int K_, int dnum_, const u64* q, const u64* p, co
 
 Engine::~Engine() {
     cudaSetDevice(device);
-    cudaStreamSynchronize(st);
+    cudaStreamSynchronize(st_main);
     for (auto& kv : modup_tabs_) cudaFree(kv.second);
     for (auto& kv : moddown_tabs_) cudaFree(kv.second);
     for (auto& kv : last_tabs_) cudaFree(kv.second);
@@ -97,7 +102,11 @@ Engine::~Engine() {
     for (auto ev : prof_pool) cudaEventDestroy(ev);
     if (timer_a) { cudaEventDestroy(timer_a); cudaEventDestroy(timer_b); }
     cudaFree(d_pc_); cudaFree(d_twf_); cudaFree(d_twi_); cudaFree(d_twd_);
-    cudaStreamDestroy(st);
+    for (auto s : aux_streams) if (s) { cudaStreamSynchronize(s); cudaStreamDestroy(s); }
+    for (auto s : lane_streams) if (s) { cudaStreamSynchronize(s); cudaStreamDestroy(s); }
+    for (auto ev : aux_events) if (ev) cudaEventDestroy(ev);
+    for (auto ev : lane_events) if (ev) cudaEventDestroy(ev);
+    cudaStreamDestroy(st_main);
 }
 
 // ------------------------------------------------------------------------------------------ profiler
@@ -126,12 +135,12 @@ Engine::Scope::~Scope() {
     if (b) cudaEventRecord(b, e->st);
 }
 void Engine::prof_enable(unsigned mask) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     prof_collect();
     prof_on = mask;
 }
 void Engine::prof_collect() {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (prof_recs.empty()) return;
     HX_CUDA(cudaStreamSynchronize(st));
     for (auto& r : prof_recs) {
@@ -143,17 +152,17 @@ void Engine::prof_collect() {
     prof_recs.clear();
 }
 void Engine::prof_reset() {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     prof_collect();
     for (int k = 0; k < PK_COUNT; k++) { prof_launches[k] = 0; prof_ms[k] = 0; prof_bytes[k] = 0; }
 }
 void Engine::timer_start() {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (!timer_a) { HX_CUDA(cudaEventCreate(&timer_a)); HX_CUDA(cudaEventCreate(&timer_b)); }
     HX_CUDA(cudaEventRecord(timer_a, st));
 }
 double Engine::timer_stop_ms() {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (!timer_a) throw std::runtime_error("timer_stop without timer_start");
     HX_CUDA(cudaEventRecord(timer_b, st));
     HX_CUDA(cudaEventSynchronize(timer_b));
@@ -178,7 +187,7 @@ Ct Engine::new_ct(int ncomp, int nl, int level, int deg, int nb) {
     return c;
 }
 Ct Engine::stack(const std::vector<Ct>& v) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (v.empty()) throw std::runtime_error("stack: empty input");
     const Ct& f = v[0];
     Ct out = new_ct(f->ncomp, f->nl, f->level, f->deg, (int)v.size());
@@ -190,7 +199,7 @@ Ct Engine::stack(const std::vector<Ct>& v) {
     return out;
 }
 std::vector<Ct> Engine::unstack(const Ct& a) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     std::vector<Ct> out;
     if (a->nb == 1) { out.push_back(a); return out; }
     for (int i = 0; i < a->nb; i++) {
@@ -201,7 +210,7 @@ std::vector<Ct> Engine::unstack(const Ct& a) {
     return out;
 }
 Ct Engine::upload(const u64* host, int ncomp, int nl, int level, int deg) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     Ct c = new_ct(ncomp, nl, level, deg);
     HX_CUDA(cudaMemcpyAsync(c->d, host, sizeof(u64) * (size_t)ncomp * nl * N, cudaMemcpyHostToDevice, st));
     sync();
@@ -209,19 +218,19 @@ Ct Engine::upload(const u64* host, int ncomp, int nl, int level, int deg) {
     return c;
 }
 void Engine::download(const Ct& ct, u64* host) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     HX_CUDA(cudaMemcpyAsync(host, ct->d, sizeof(u64) * (size_t)ct->nb * ct->ncomp * ct->nl * N, cudaMemcpyDeviceToHost, st));
     sync();
 }
 Ct Engine::clone(const Ct& a) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     Ct c = new_ct(a->ncomp, a->nl, a->level, a->deg, a->nb);
     HX_CUDA(cudaMemcpyAsync(c->d, a->d, sizeof(u64) * (size_t)a->nb * a->ncomp * a->nl * N, cudaMemcpyDeviceToDevice, st));
     return c;
 }
 
 Ct Engine::concat(const std::vector<Ct>& v) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (v.empty()) throw std::runtime_error("concat: empty input");
     const Ct& f = v[0];
     int nb = 0;
@@ -239,7 +248,7 @@ Ct Engine::concat(const std::vector<Ct>& v) {
     return out;
 }
 std::vector<Ct> Engine::split(const Ct& a, int parts) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (parts <= 0 || a->nb % parts) throw std::runtime_error("split: batch size is not a multiple of the number of parts");
     std::vector<Ct> out;
     if (parts == 1) { out.push_back(a); return out; }
@@ -394,25 +403,25 @@ void Engine::finish_key(EvalKey& k) {
     launch_split30(k.b, (size_t)dnum * ds, st);
 }
 void Engine::load_mult_key(const u64* a, const u64* b) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (have_mult_key_) { cudaFree(mult_key_.a); cudaFree(mult_key_.b); }
     mult_key_ = upload_key(*this, a, b);
     have_mult_key_ = true;
 }
 void Engine::load_rot_key(u64 galois, const u64* a, const u64* b) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     auto it = rot_keys_.find(galois);
     if (it != rot_keys_.end()) { cudaFree(it->second.a); cudaFree(it->second.b); }
     rot_keys_[galois] = upload_key(*this, a, b);
 }
 void Engine::adopt_rot_key(u64 galois, EvalKey k) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     auto it = rot_keys_.find(galois);
     if (it != rot_keys_.end()) { cudaFree(it->second.a); cudaFree(it->second.b); }
     rot_keys_[galois] = k;
 }
 void Engine::adopt_mult_key(EvalKey k) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (have_mult_key_) { cudaFree(mult_key_.a); cudaFree(mult_key_.b); }
     mult_key_ = k;
     have_mult_key_ = true;
@@ -501,7 +510,8 @@ void Engine::ks_core_batch(const u64* digits, int ndig, int nl, const std::vecto
             a.out_bs = out_bs;
             {   // algorithmic bytes of one key switch after ModUp: evk once, digits once per launch,
                 // addend once, result once
-                Scope sc(this, ks_kind, (g_ks_fuse_inv && n * 2 >= g_ks_fuse_inv) ? 3 : 4,   // launch_fused_tn: ModDown in 2 or 3 launches
+                a.fuse_inv = ks_fuse_inv;
+                Scope sc(this, ks_kind, (ks_fuse_inv && n * 2 >= ks_fuse_inv) ? 3 : 4,   // launch_fused_tn: ModDown in 2 or 3 launches
                          8.0 * N * ((double)n * 2 * ndig * ext + (double)(digits_bs ? n : 1) * ndig * ext + (double)(addend_bs ? n : 1) * addend_comps * nl + (double)n * 2 * nl));
                 launch_fused_ks(T, a, moddown_table(nl), n, st);
             }
@@ -552,7 +562,7 @@ void Engine::ks_core_batch(const u64* digits, int ndig, int nl, const std::vecto
 }
 
 std::shared_ptr<Engine::Digits> Engine::fast_rotation_precompute(const Ct& a) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     auto dg = std::make_shared<Digits>();
     dg->eng = this;
     dg->keep = weak_from_this().lock();
@@ -562,7 +572,7 @@ std::shared_ptr<Engine::Digits> Engine::fast_rotation_precompute(const Ct& a) {
     return dg;
 }
 Ct Engine::fast_rotation(const Ct& a, int r, const std::shared_ptr<Digits>& dg) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (r == 0) return clone(a);
     if (a->ncomp != 2 || dg->nl != a->nl) throw std::runtime_error("EvalFastRotation: digits do not match the ciphertext");
     if (dg->fused != (fused_ks_supported(logN) && !force_unfused)) throw std::runtime_error("EvalFastRotation: digits were precomputed by the other key-switch pipeline");
@@ -572,7 +582,7 @@ Ct Engine::fast_rotation(const Ct& a, int r, const std::shared_ptr<Digits>& dg) 
     return out;
 }
 Ct Engine::automorphism(const Ct& a, u64 k) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (a->ncomp != 2) throw std::runtime_error("EvalAutomorphism needs 2-component ciphertexts");
     int ndig;
     if (a->nb == 1) {
@@ -608,7 +618,7 @@ Ct Engine::eval_sum(const Ct& a, int n) {
     return out;
 }
 Ct Engine::relinearize(const Ct& a) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (a->ncomp == 2) return clone(a);
     if (a->ncomp != 3) throw std::runtime_error("Relinearize supports 3-component ciphertexts");
     if (!have_mult_key_) throw std::runtime_error("EvalMultKey is not generated");
@@ -623,7 +633,7 @@ Ct Engine::relinearize(const Ct& a) {
 
 // ------------------------------------------------------------------------------------------ leveled ops
 Ct Engine::level_reduce(const Ct& a, int levels) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (levels == 0) return a;
     if (levels < 0 || levels >= a->nl) throw std::runtime_error("LevelReduce: not enough limbs");
     int nl = a->nl - levels;
@@ -637,7 +647,7 @@ void Engine::align(Ct& a, Ct& b) {   // FIXEDMANUAL AdjustLevelsInPlace: drop li
     else if (b->nl > a->nl) b = level_reduce(b, b->nl - a->nl);
 }
 Ct Engine::add(const Ct& a_, const Ct& b_) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     Ct a = a_, b = b_;
     align(a, b);
     if (a->deg != b->deg) throw std::runtime_error("EvalAdd: noiseScaleDeg mismatch");
@@ -652,7 +662,7 @@ Ct Engine::add(const Ct& a_, const Ct& b_) {
     return out;
 }
 Ct Engine::sub(const Ct& a_, const Ct& b_) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     Ct a = a_, b = b_;
     align(a, b);
     if (a->deg != b->deg) throw std::runtime_error("EvalSub: noiseScaleDeg mismatch");
@@ -695,13 +705,13 @@ std::vector<u64> Engine::const_for_add(double c, int nl, int deg) const {
     return out;
 }
 Ct Engine::mult_const(const Ct& a, double c) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     Ct out = new_ct(a->ncomp, a->nl, a->level, a->deg + 1, a->nb);
     { Scope sc(this, PK_SCALAR, 1, 16.0 * N * a->nl * a->comps_total()); launch_mul_scalar(T, out->d, a->d, scalar_table(const_for_mult(c, a->nl)), a->nl, a->comps_total(), out->comp_stride(), a->comp_stride(), st); }
     return out;
 }
 Ct Engine::add_const(const Ct& a, double c) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     // the CryptoContext front end routes negative constants to EvalSub(ct, -c)
     std::vector<u64> k = const_for_add(std::fabs(c), a->nl, a->deg);
     if (c < 0)
@@ -711,7 +721,7 @@ Ct Engine::add_const(const Ct& a, double c) {
     return out;
 }
 Ct Engine::mult_norelin(const Ct& a_, const Ct& b_) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     Ct a = a_, b = b_;
     align(a, b);
     if (a->ncomp != 2 || b->ncomp != 2) throw std::runtime_error("EvalMultNoRelin supports 2-component inputs");
@@ -723,7 +733,7 @@ Ct Engine::mult_norelin(const Ct& a_, const Ct& b_) {
 }
 Ct Engine::mult(const Ct& a, const Ct& b) { return relinearize(mult_norelin(a, b)); }
 Ct Engine::mult_plain(const Ct& a, const u64* host_pt, int nlimbs) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (nlimbs < a->nl) throw std::runtime_error("EvalMult(ct, Plaintext): plaintext has fewer limbs than the ciphertext");
     // the plaintext was encoded at level 0; a ciphertext at a lower level uses its first nl limbs (same integer polynomial)
     u64* pt = alloc_words((size_t)a->nl * N);
@@ -739,7 +749,7 @@ Ct Engine::square(const Ct& a) { return mult(a, a); }
 
 // DropLastElementAndScale (sender_diag.cpp:80).
 Ct Engine::rescale(const Ct& a) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     int nl = a->nl;
     if (nl < 2) throw std::runtime_error("Rescale: no limb left to drop");
     int nc = a->comps_total();   // batch entries are independent components for DropLastElementAndScale

@@ -67,8 +67,16 @@ public:
     int N, logN, L, K, dnum, alpha, scale_bits, device;
     std::vector<u64> mods, psis;     // Q then P
     DevTables T{};
-    cudaStream_t st = nullptr;
+    cudaStream_t st = nullptr;       // WORKING stream of the thread that holds `mu` (the hoisted rotations repoint it to their lanes)
+    cudaStream_t st_main = nullptr;  // the engine stream; never changes.  Handles are freed on it (their destructors take `mu`)
     std::recursive_mutex mu;         // the reference enters from up to 48 OpenMP threads
+    // Every entry point: take the engine lock and make the engine's device current for this host thread (contexts on several
+    // devices in one process, worker threads whose current device is another one).
+    struct Guard {
+        std::unique_lock<std::recursive_mutex> lk;
+        explicit Guard(Engine* e) : lk(e->mu) { cudaSetDevice(e->device); }
+    };
+    int ks_fuse_inv = 16;            // > 0: ModDown of key-switch batches with at least this many polynomials runs the inverse column pass inside the conversion kernel
     int rot_streams = 2;             // hoisted-rotation batches are issued round-robin on this many streams (1 = the engine stream only)
     cudaStream_t aux_streams[3] = {nullptr, nullptr, nullptr};
     cudaEvent_t aux_events[4] = {nullptr, nullptr, nullptr, nullptr};

@@ -23,7 +23,11 @@
 namespace hx {
 
 int g_pdl = 1;
-int g_ks_fuse_inv = 16;   // > 0: ModDown of key-switch batches with at least this many polynomials runs K2a inside K2b (hx_ctx_set_option "ks_fuse_inv")
+template <class K>
+static void smem_optin(K kernel, unsigned bytes) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e != cudaSuccess) throw std::runtime_error(std::string("cudaFuncSetAttribute (dynamic shared memory opt-in): ") + cudaGetErrorString(e));
+}
 
 constexpr unsigned kTileBytes = kTileN * sizeof(u64);                                   // 16 KB
 constexpr unsigned kStageOff = (kTileWords * sizeof(u64) + 127u) & ~127u;              // staged key tiles start here
@@ -256,12 +260,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
 template <int LOGN, bool FUSE_INV = false>
 static void launch_conv_fwd_col(const DevTables& T, const TabSet& ts, int max_n_in, int ny, int nbatch, const u64* in, size_t in_bs, u64* out,
                                 size_t out_bs, int ext_nl, int L, int jgroup, cudaStream_t st) {
-    static int attr_bytes = 0;
     const int bytes = (int)(kStageOff + (FUSE_INV ? max_n_in - 1 : max_n_in) * kTileBytes);
-    if (bytes > attr_bytes) {
-        cudaFuncSetAttribute(k_conv_fwd_col<LOGN, FUSE_INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-        attr_bytes = bytes;
-    }
     launch_pdl(k_conv_fwd_col<LOGN, FUSE_INV>, dim3(NttGeo<LOGN>::TILES, ny, nbatch), dim3(kTileThreads), bytes, st, T, ts, in, in_bs, out, out_bs, ext_nl, L, jgroup);
 }
 
@@ -351,15 +350,9 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __g
 template <int LOGN, int NDIG>
 static void launch_fused_tn(const DevTables& T, const FusedKsArgs& a, const BaseConvTable* moddown, int nb, cudaStream_t st) {
     using G = NttGeo<LOGN>;
-    static bool attr_done = false;   // > 48 KB of dynamic shared memory needs the opt-in, once per instantiation
-    if (!attr_done) {
-        cudaFuncSetAttribute(k_ks_p_inner<LOGN, NDIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ks_smem_bytes(NDIG));
-        cudaFuncSetAttribute(k_ks_q_finish<LOGN, NDIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ks_smem_bytes(NDIG));
-        attr_done = true;
-    }
     launch_pdl(k_ks_p_inner<LOGN, NDIG>, dim3(G::TILES, 2 * a.K, nb), dim3(kTileThreads), ks_smem_bytes(NDIG), st, T, a);
     const TabSet ts = single_table(moddown);
-    if (g_ks_fuse_inv && nb * 2 >= g_ks_fuse_inv) {   // large batches: one CTA per column tile does K2a and K2b for all target limbs
+    if (a.fuse_inv && nb * 2 >= a.fuse_inv) {   // large batches: one CTA per column tile does K2a and K2b for all target limbs
         launch_conv_fwd_col<LOGN, true>(T, ts, a.K, 1, nb * 2, a.tmpP, (size_t)a.K * T.N, a.conv, (size_t)a.nl * T.N, -1, 0, a.nl, st);
         launch_pdl(k_ks_q_finish<LOGN, NDIG>, dim3(G::TILES, 2 * a.nl, nb), dim3(kTileThreads), ks_smem_bytes(NDIG), st, T, a);
         return;
@@ -377,7 +370,7 @@ static void launch_fused_t(const DevTables& T, const FusedKsArgs& a, const BaseC
         case 2: launch_fused_tn<LOGN, 2>(T, a, moddown, nb, st); break;
         case 3: launch_fused_tn<LOGN, 3>(T, a, moddown, nb, st); break;
         case 4: launch_fused_tn<LOGN, 4>(T, a, moddown, nb, st); break;
-        default: break;
+        default: throw std::runtime_error("fused key switch: number of digits must be 1..4");
     }
 }
 
@@ -556,7 +549,7 @@ void launch_fused_modup(const DevTables& T, const ModUpArgs& m, cudaStream_t st)
         case 14: modup_t<14>(T, m, st); break;
         case 15: modup_t<15>(T, m, st); break;
         case 16: modup_t<16>(T, m, st); break;
-        default: break;
+        default: throw std::runtime_error("fused ModUp: unsupported ring dimension");
     }
 }
 
@@ -577,11 +570,32 @@ void launch_fused_rescale(const DevTables& T, const RescaleArgs& r, cudaStream_t
         case 14: rescale_t<14>(T, r, st); break;
         case 15: rescale_t<15>(T, r, st); break;
         case 16: rescale_t<16>(T, r, st); break;
-        default: break;
+        default: throw std::runtime_error("fused rescale: unsupported ring dimension");
     }
 }
 
 bool fused_ks_supported(int logN) { return logN >= 12 && logN <= 16; }
+
+template <int LOGN>
+static void init_fused_t() {
+    const int conv_max = (int)(kStageOff + 7 * kTileBytes);   // digit width / P basis <= 7 limbs (Engine constructor)
+    smem_optin(k_conv_fwd_col<LOGN, false>, conv_max);
+    smem_optin(k_conv_fwd_col<LOGN, true>, conv_max);
+    smem_optin(k_ks_p_inner<LOGN, 1>, ks_smem_bytes(1)); smem_optin(k_ks_q_finish<LOGN, 1>, ks_smem_bytes(1));
+    smem_optin(k_ks_p_inner<LOGN, 2>, ks_smem_bytes(2)); smem_optin(k_ks_q_finish<LOGN, 2>, ks_smem_bytes(2));
+    smem_optin(k_ks_p_inner<LOGN, 3>, ks_smem_bytes(3)); smem_optin(k_ks_q_finish<LOGN, 3>, ks_smem_bytes(3));
+    smem_optin(k_ks_p_inner<LOGN, 4>, ks_smem_bytes(4)); smem_optin(k_ks_q_finish<LOGN, 4>, ks_smem_bytes(4));
+}
+void init_fused_kernels(int logN) {
+    switch (logN) {
+        case 12: init_fused_t<12>(); break;
+        case 13: init_fused_t<13>(); break;
+        case 14: init_fused_t<14>(); break;
+        case 15: init_fused_t<15>(); break;
+        case 16: init_fused_t<16>(); break;
+        default: break;   // smaller rings use the unfused kernels only
+    }
+}
 
 void launch_fused_ks(const DevTables& T, const FusedKsArgs& a, const BaseConvTable* moddown, int nb, cudaStream_t st) {
     switch (T.logN) {
@@ -590,7 +604,7 @@ void launch_fused_ks(const DevTables& T, const FusedKsArgs& a, const BaseConvTab
         case 14: launch_fused_t<14>(T, a, moddown, nb, st); break;
         case 15: launch_fused_t<15>(T, a, moddown, nb, st); break;
         case 16: launch_fused_t<16>(T, a, moddown, nb, st); break;
-        default: break;
+        default: throw std::runtime_error("fused key switch: unsupported ring dimension");
     }
 }
 

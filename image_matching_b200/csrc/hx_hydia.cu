@@ -27,20 +27,20 @@ static void db_finish(Engine& e, u64* dst) {
     launch_to_mont(e.T, dst, 2 * e.L, e.limb_map(primes), e.st);
 }
 void Engine::db_register(int block, int diag, const u64* host_ct) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     u64* dst = db_slot(*this, db_, block, diag);
     HX_CUDA(cudaMemcpyAsync(dst, host_ct, sizeof(u64) * (size_t)2 * L * N, cudaMemcpyHostToDevice, st));
     db_finish(*this, dst);
     sync();
 }
 void Engine::db_store_device(int block, int diag, const u64* dev_ct) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     u64* dst = db_slot(*this, db_, block, diag);
     HX_CUDA(cudaMemcpyAsync(dst, dev_ct, sizeof(u64) * (size_t)2 * L * N, cudaMemcpyDeviceToDevice, st));
     db_finish(*this, dst);
 }
 void Engine::db_adopt(int block, u64* dev, int ndiag) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     DbBlock& b = db_[block];
     if (b.d) cudaFree(b.d);
     b.d = dev;
@@ -51,10 +51,10 @@ void Engine::db_adopt(int block, u64* dev, int ndiag) {
 // (EvalFastRotationPrecompute + EvalFastRotation), then per block the 512 tensor products, their
 // sum, one relinearisation and one rescale (computeSimilarityMatrix, :66-83).
 Engine::RotSet::~RotSet() {
-    if (rotq && eng) eng->free_words(rotq);
+    if (rotq && eng) { Engine::Guard g(eng); cudaFreeAsync(rotq, eng->st_main); }
 }
 std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_all(const Ct& query, int ndiag) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (query->ncomp != 2 || query->nl != L || query->nb != 1) throw std::runtime_error("score_diag: query must be a fresh 2-component ciphertext");
     if (ndiag < 1) throw std::runtime_error("score_diag: ndiag must be positive");
     const int nl = query->nl;
@@ -71,49 +71,46 @@ std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_all(const Ct& query, int 
     if (lane) {
         // rotation lane: nothing below depends on what the engine stream still has queued (see hx_engine.h)
         for (int s = 0; s < ns; s++)
-            if (!lane_streams[s]) {
-                if (getenv("HX_LANE_PRIO")) {   // diagnosis: lanes at the engine stream's priority
-                    int pr = 0;
-                    HX_CUDA(cudaStreamGetPriority(main_st, &pr));
-                    HX_CUDA(cudaStreamCreateWithPriority(&lane_streams[s], cudaStreamNonBlocking, pr));
-                } else {
-                    HX_CUDA(cudaStreamCreateWithFlags(&lane_streams[s], cudaStreamNonBlocking));   // priority 0 = lowest
-                }
-            }
+            if (!lane_streams[s]) HX_CUDA(cudaStreamCreateWithFlags(&lane_streams[s], cudaStreamNonBlocking));   // priority 0 = lowest
         for (int s = 0; s < 5; s++)
             if (!lane_events[s]) HX_CUDA(cudaEventCreateWithFlags(&lane_events[s], cudaEventDisableTiming));
         st = lane_streams[0];   // allocations, the copy of the query and its ModUp are ordered on the lane
     }
-    u64* rotq = rs->rotq = alloc_words(ct_words * ndiag);
-    HX_CUDA(cudaMemcpyAsync(rotq, query->d, sizeof(u64) * ct_words, cudaMemcpyDeviceToDevice, st));
-    int ndig;
-    u64* digits = ks_precompute(query->comp(1), nl, &ndig);
-    ks_kind = PK_KS_HOISTED;
-    // Independent batches may run on several streams so that the tail of one batch's kernels overlaps the next batch
-    // (smaller batches keep their intermediates in L2).  Stream s > 0 waits for the digits, the first stream waits for all.
+    // Everything from here to the join runs on the lane / auxiliary streams.  If anything throws (a missing rotation key after
+    // some batches were queued, an allocation failure), those streams are drained before the exception leaves: the RotSet's
+    // destructor and the digit buffer's release below order their frees on the engine stream only.
+    u64* digits = nullptr;
     cudaStream_t first = st;
     cudaStream_t* others = lane ? lane_streams + 1 : aux_streams;
     cudaEvent_t* evs = lane ? lane_events : aux_events;
-    // profiler: the whole section is timed as one span on its first stream (its batches overlap across streams);
-    // the per-batch scopes inside only book launches and algorithmic bytes
-    std::unique_ptr<Scope> span(new Scope(this, PK_KS_HOISTED, 0, 0.0));
-    prof_no_events = true;
-    if (ns > 1) {
-        if (!lane) {
-            for (int s = 0; s < ns - 1; s++)
-                if (!aux_streams[s]) {   // same priority as the engine stream: unequal priorities between the batch streams cost 30 %
-                    int pr = 0;
-                    HX_CUDA(cudaStreamGetPriority(main_st, &pr));
-                    HX_CUDA(cudaStreamCreateWithPriority(&aux_streams[s], cudaStreamNonBlocking, pr));
-                }
-            for (int s = 0; s < 4; s++)
-                if (!aux_events[s]) HX_CUDA(cudaEventCreateWithFlags(&aux_events[s], cudaEventDisableTiming));
-        }
-        HX_CUDA(cudaEventRecord(evs[3], first));
-        for (int s = 0; s < ns - 1; s++) HX_CUDA(cudaStreamWaitEvent(others[s], evs[3], 0));
-    }
-    int turn = 0;
+    std::unique_ptr<Scope> span;
     try {
+        u64* rotq = rs->rotq = alloc_words(ct_words * ndiag);
+        HX_CUDA(cudaMemcpyAsync(rotq, query->d, sizeof(u64) * ct_words, cudaMemcpyDeviceToDevice, st));
+        int ndig;
+        digits = ks_precompute(query->comp(1), nl, &ndig);
+        ks_kind = PK_KS_HOISTED;
+        // Independent batches may run on several streams so that the tail of one batch's kernels overlaps the next batch
+        // (smaller batches keep their intermediates in L2).  Stream s > 0 waits for the digits, the first stream waits for all.
+        // profiler: the whole section is timed as one span on its first stream (its batches overlap across streams);
+        // the per-batch scopes inside only book launches and algorithmic bytes
+        span.reset(new Scope(this, PK_KS_HOISTED, 0, 0.0));
+        prof_no_events = true;
+        if (ns > 1) {
+            if (!lane) {
+                for (int s = 0; s < ns - 1; s++)
+                    if (!aux_streams[s]) {   // same priority as the engine stream: unequal priorities between the batch streams cost 30 %
+                        int pr = 0;
+                        HX_CUDA(cudaStreamGetPriority(main_st, &pr));
+                        HX_CUDA(cudaStreamCreateWithPriority(&aux_streams[s], cudaStreamNonBlocking, pr));
+                    }
+                for (int s = 0; s < 4; s++)
+                    if (!aux_events[s]) HX_CUDA(cudaEventCreateWithFlags(&aux_events[s], cudaEventDisableTiming));
+            }
+            HX_CUDA(cudaEventRecord(evs[3], first));
+            for (int s = 0; s < ns - 1; s++) HX_CUDA(cudaStreamWaitEvent(others[s], evs[3], 0));
+        }
+        int turn = 0;
         for (int d0 = 1; d0 < ndiag; d0 += chunk, turn++) {
             int d1 = std::min(ndiag, d0 + chunk);
             st = (ns > 1 && turn % ns) ? others[turn % ns - 1] : first;
@@ -127,14 +124,13 @@ std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_all(const Ct& query, int 
             ks_core_batch(digits, ndig, nl, keys, query->comp(0), 1, gal, rotq + ct_words * d0, ct_words);
         }
     } catch (...) {
-        // e.g. a missing rotation key after some batches were queued: nothing may still write rotq / read the digits when the
-        // RotSet's destructor frees them on the engine stream
         prof_no_events = false;
+        ks_kind = PK_KS_FUSED;
         cudaStreamSynchronize(first);
         for (int s = 0; s < ns - 1; s++)
             if (others[s]) cudaStreamSynchronize(others[s]);
-        st = first;
-        free_words(digits);
+        st = main_st;
+        if (digits) free_words(digits);
         throw;
     }
     st = first;
@@ -155,7 +151,7 @@ std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_all(const Ct& query, int 
     return rs;
 }
 Ct Engine::rotset_entry(const RotSet& rs, int i) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (i < 0 || i >= rs.ndiag) throw std::runtime_error("rotset_entry: index out of range");
     Ct c = new_ct(2, rs.nl, rs.level, rs.deg);
     const size_t ct_words = (size_t)2 * rs.nl * N;
@@ -163,7 +159,7 @@ Ct Engine::rotset_entry(const RotSet& rs, int i) {
     return c;
 }
 Ct Engine::db_entry(int block, int diag) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     auto it = db_.find(block);
     if (it == db_.end() || diag < 0 || diag >= it->second.ndiag) throw std::runtime_error("db_entry: no such database ciphertext");
     Ct c = new_ct(2, L, 0, 1);
@@ -176,7 +172,7 @@ Ct Engine::db_entry(int block, int diag) {
     return c;
 }
 std::vector<Ct> Engine::score_rotset(const RotSet& rs, const std::vector<int>& block_ids) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     const int nl = rs.nl, ndiag = rs.ndiag;
     const u64* rotq = rs.rotq;
     // all blocks of this GPU in one launch each: diagonal MAC (the rotated query is fetched from HBM once
@@ -204,7 +200,7 @@ std::vector<Ct> Engine::score_rotset(const RotSet& rs, const std::vector<int>& b
     return parts;
 }
 std::vector<Ct> Engine::score_diag_batched(const Ct& query, int ndiag) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (db_.empty()) throw std::runtime_error("score_diag: no database block registered");
     std::shared_ptr<RotSet> rs = rotate_hoisted_all(query, ndiag);
     std::vector<int> ids;
@@ -238,7 +234,7 @@ Ct Engine::membership(const Ct& query, int ndiag, double delta, int depth) {
 // digit sets), one batched rescale, one modular sum over the batch.  Modular addition is associative and
 // commutative, so the result equals the reference's sequential EvalAddInPlace chain bit for bit.
 std::vector<Ct> Engine::score_hers(const std::vector<Ct>& query, const std::vector<int>* matrices) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     if (query.empty()) throw std::runtime_error("score_hers: empty query");
     if (db_.empty()) throw std::runtime_error("score_hers: no database matrix registered");
     const int dim = (int)query.size(), nl = query[0]->nl;
@@ -282,7 +278,7 @@ std::vector<Ct> Engine::score_hers(const std::vector<Ct>& query, const std::vect
 }
 
 std::vector<Ct> Engine::compare_many(const std::vector<Ct>& cts, double delta, int depth) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     std::vector<Ct> out;
     const bool batch = batch_blocks && !force_unfused && fused_ks_supported(logN);
     for (size_t i0 = 0; i0 < cts.size(); i0 += kMaxKsBatch) {

@@ -617,13 +617,14 @@ __global__ void __launch_bounds__(kThreads + 32, 2) k_diag_mac_tma(DevTables T, 
         st128(o + (size_t)c * cs, v);
     }
 }
+void init_fused_kernels(int logN);   // hx_fused.cu
+void init_device_kernels(int logN) {
+    cudaError_t e = cudaFuncSetAttribute(k_diag_mac_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, kMacSmemBytes);
+    if (e != cudaSuccess) throw std::runtime_error(std::string("cudaFuncSetAttribute(k_diag_mac_tma): ") + cudaGetErrorString(e));
+    init_fused_kernels(logN);
+}
 void launch_diag_mac(const DevTables& T, const u64* rotq, const DbBlockPtrs& dbs, int nblocks, u64* out, int ndiag, int nl, cudaStream_t st) {
     if (T.N % (2 * kThreads) == 0) {
-        static bool attr_set = false;
-        if (!attr_set) {
-            cudaFuncSetAttribute(k_diag_mac_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, kMacSmemBytes);
-            attr_set = true;
-        }
         launch_pdl(k_diag_mac_tma, dim3(nblocks, T.N / (2 * kThreads), nl), dim3(kThreads + 32), (size_t)kMacSmemBytes, st, T, rotq, dbs, out, ndiag,
                    nl, 0);
         return;

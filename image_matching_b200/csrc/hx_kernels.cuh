@@ -73,9 +73,12 @@ struct FusedKsArgs {
     size_t add_bs = 0;              // words between the addends of consecutive batch entries (0 = shared)
     u64* out;                       // [nb] x out_bs, each [2][nl][N]
     size_t out_bs;
+    int fuse_inv = 16;              // Engine::ks_fuse_inv
 };
-extern int g_ks_fuse_inv;
 bool fused_ks_supported(int logN);
+// per-device opt-ins (dynamic shared memory above 48 KB) of every kernel a ring of 2^logN coefficients launches; called by the
+// Engine constructor with its device current
+void init_device_kernels(int logN);
 void launch_fused_ks(const DevTables& T, const FusedKsArgs& a, const BaseConvTable* moddown, int nb, cudaStream_t st);
 
 // fused ModUp: c [nbatch] x c_bs, each [nl][N]  ->  digits [nbatch][ndig][nl+K][N]

@@ -95,14 +95,12 @@ __device__ __forceinline__ u64 fwd_normalize(u64 x, const PrimeConst& pc, bool f
 // One round of R consecutive forward stages.  SL0 = first local stage (local stage sl toggles
 // local bit 10-sl); S0 = the global stage of SL0; SHIFT0 = S0 - (stage at which `tileoff` has
 // weight 1) so that twiddle index = 2^s + (tileoff << (s - S0 + SHIFT0)) + local group.
+// The R stages of a round on the 8 register-held elements of a thread (element k of `v` = tile element base + (k << p)); no
+// shared-memory access: kernels that feed a round from registers (multiply-accumulate results) or consume it in registers
+// (scaling, direct global stores) call these, the *_round_* wrappers below add the shared-memory load and store.
 template <int SL0, int R, int S0, int SHIFT0>
-__device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
+__device__ __forceinline__ void fwd_regs_ct(u64 (&v)[8], int base, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
     constexpr int p = kLogTile - SL0 - R;
-    const int base = insert_bits3(round_thread<p>(t), p);
-    u64* const sp = sm + tphys(base);
-    u64 v[8];
-#pragma unroll
-    for (int k = 0; k < 8; k++) v[k] = sp[toff(k, p)];
 #pragma unroll
     for (int r = 0; r < R; r++) {
         const int kb = R - 1 - r;
@@ -122,18 +120,25 @@ __device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const 
             v[k1] = x - y + q4;
         }
     }
+}
+template <int P>
+__device__ __forceinline__ int round_base(int t) { return insert_bits3(round_thread<P>(t), P); }
+template <int SL0, int R, int S0, int SHIFT0>
+__device__ __forceinline__ void fwd_round_ct(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
+    constexpr int p = kLogTile - SL0 - R;
+    const int base = round_base<p>(t);
+    u64* const sp = sm + tphys(base);
+    u64 v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) v[k] = sp[toff(k, p)];
+    fwd_regs_ct<SL0, R, S0, SHIFT0>(v, base, tileoff, tw, q, q4);
 #pragma unroll
     for (int k = 0; k < 8; k++) sp[toff(k, p)] = v[k];
 }
 // FP64 back end of the same round: tw = {w, w/q} as doubles.
 template <int SL0, int R, int S0, int SHIFT0>
-__device__ __forceinline__ void fwd_round_fp(double* sm, int t, int tileoff, const double2* __restrict__ tw, double q) {
+__device__ __forceinline__ void fwd_regs_fp(double (&v)[8], int base, int tileoff, const double2* __restrict__ tw, double q) {
     constexpr int p = kLogTile - SL0 - R;
-    const int base = insert_bits3(round_thread<p>(t), p);
-    double* const sp = sm + tphys(base);
-    double v[8];
-#pragma unroll
-    for (int k = 0; k < 8; k++) v[k] = sp[toff(k, p)];
 #pragma unroll
     for (int r = 0; r < R; r++) {
         const int kb = R - 1 - r;
@@ -156,6 +161,16 @@ __device__ __forceinline__ void fwd_round_fp(double* sm, int t, int tileoff, con
             v[k1] = __dsub_rn(x, m);
         }
     }
+}
+template <int SL0, int R, int S0, int SHIFT0>
+__device__ __forceinline__ void fwd_round_fp(double* sm, int t, int tileoff, const double2* __restrict__ tw, double q) {
+    constexpr int p = kLogTile - SL0 - R;
+    const int base = round_base<p>(t);
+    double* const sp = sm + tphys(base);
+    double v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) v[k] = sp[toff(k, p)];
+    fwd_regs_fp<SL0, R, S0, SHIFT0>(v, base, tileoff, tw, q);
 #pragma unroll
     for (int k = 0; k < 8; k++) sp[toff(k, p)] = v[k];
 }
@@ -199,13 +214,8 @@ __device__ __forceinline__ void fwd_row_pass(u64* sm, int t, int tile, const Tab
 // One round of R consecutive inverse (Gentleman-Sande) stages: local stages SH-1, SH-2, .., SH-R.
 // S_TOP = global stage of local stage SH-1; SHIFT_TOP = shift of tileoff at that stage.
 template <int SH, int R, int S_TOP, int SHIFT_TOP>
-__device__ __forceinline__ void inv_round_ct(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
+__device__ __forceinline__ void inv_regs_ct(u64 (&v)[8], int base, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
     constexpr int p = kLogTile - SH;
-    const int base = insert_bits3(round_thread<p>(t), p);
-    u64* const sp = sm + tphys(base);
-    u64 v[8];
-#pragma unroll
-    for (int k = 0; k < 8; k++) v[k] = sp[toff(k, p)];
 #pragma unroll
     for (int r = 0; r < R; r++) {
         const int kb = r;
@@ -225,6 +235,16 @@ __device__ __forceinline__ void inv_round_ct(u64* sm, int t, int tileoff, const 
             v[k1] = shoup_lazy4(x - y + q4, w.x, w.y, q);
         }
     }
+}
+template <int SH, int R, int S_TOP, int SHIFT_TOP>
+__device__ __forceinline__ void inv_round_ct(u64* sm, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
+    constexpr int p = kLogTile - SH;
+    const int base = round_base<p>(t);
+    u64* const sp = sm + tphys(base);
+    u64 v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) v[k] = sp[toff(k, p)];
+    inv_regs_ct<SH, R, S_TOP, SHIFT_TOP>(v, base, tileoff, tw, q, q4);
 #pragma unroll
     for (int k = 0; k < 8; k++) sp[toff(k, p)] = v[k];
 }

@@ -159,7 +159,7 @@ Split ps_split(const Vec& coeffs, int k, int m, bool cheb) {
 
 // EvalLinearWSumMutable: sum_i w_i * ct_i, then one ModReduce.
 Ct Engine::linear_wsum(const std::vector<Ct>& cts, const std::vector<double>& w) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     bool same = cts.size() <= (size_t)kMaxWsum;
     for (auto& c : cts) same = same && c->nl == cts[0]->nl && c->ncomp == cts[0]->ncomp && c->nb == cts[0]->nb && c->deg == cts[0]->deg;
     if (same) {   // one launch: sum_t w_t * ct_t (modular addition is associative: same bits as the add chain below)
@@ -309,7 +309,7 @@ std::pair<Ct, Ct> Engine::two_products(Ct a0, Ct b0, Ct a1, Ct b1, bool twice) {
 }
 
 Ct Engine::chebyshev_series(const Ct& x, const std::vector<double>& coefficients, double a, double b) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     int n = degree_of(coefficients);
     if (n < 5) throw std::runtime_error("EvalChebyshevSeries: degree < 5 (linear evaluation) is not on the HyDia path");
     Vec f2 = coefficients;
@@ -411,7 +411,7 @@ Ct Engine::inner_poly(const std::vector<double>& coeffs, int k, int m, std::vect
 
 // EvalPolyPS (cc->EvalPoly, openFHE_wrapper.cpp:179).
 Ct Engine::eval_poly(const Ct& x, const std::vector<double>& coefficients) {
-    std::lock_guard<std::recursive_mutex> g(mu);
+    Guard g(this);
     int n = degree_of(coefficients);
     if (n < 5) throw std::runtime_error("EvalPoly: degree < 5 (linear evaluation) is not on the HyDia path");
     Vec f2 = coefficients;

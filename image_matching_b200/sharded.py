@@ -85,6 +85,9 @@ class ShardedDiagonalSender(Sender):
         self.dist, self.group = dist, group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         self.transport = transport or TorchTransport(cc, device)
+        # membershipScenario SUM-reduces residues as int64: the un-reduced sum of `world` residues must stay below 2^63
+        if self.world * max(int(m) for m in cc.q) >= 1 << 63:
+            raise ValueError(f"ShardedDiagonalSender: world size {self.world} x max modulus exceeds the int64 range of the membership reduce")
 
     # -- per-rank compute: identical to the single-GPU fused path on the local blocks
     def computeSimilarity(self, queryCipher):

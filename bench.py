@@ -48,7 +48,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--rot-chunk", type=int, default=0, help="override the engine's hoisted-rotation batch size")
     ap.add_argument("--rot-streams", type=int, default=0, help="override the number of streams the hoisted-rotation batches use")
-    ap.add_argument("--ks-fuse-inv", type=int, default=-1, help="override the batch threshold of the fused inverse-column / conversion ModDown kernel (0 = off)")
+    ap.add_argument("--ks-moddown-w", type=int, default=-1, help="override the engine's warp-task ModDown kernel (0 = the r1 launch sequence)")
     ap.add_argument("--rot-lane", type=int, default=-1, help="override the engine's rotation lane (0 = all work ordered on the engine stream)")
     ap.add_argument("--sync-exchange", action="store_true", help="N > 1: host-synchronous result exchange (no overlap of the scenarios)")
     ap.add_argument("--ncu-range", action="store_true",
@@ -200,10 +200,10 @@ def run_b200(args):
         cc.set_option("rot_chunk", args.rot_chunk)
     if args.rot_streams:
         cc.set_option("rot_streams", args.rot_streams)
-    if args.ks_fuse_inv >= 0:
-        cc.set_option("ks_fuse_inv", args.ks_fuse_inv)
     if args.rot_lane >= 0:
         cc.set_option("rot_lane", args.rot_lane)
+    if args.ks_moddown_w >= 0:
+        cc.set_option("ks_moddown_w", args.ks_moddown_w)
     slots = cc.GetBatchSize()
     total_blocks = bpg * world
     n_total = total_blocks * slots
@@ -344,10 +344,10 @@ def run_b200(args):
             traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json"))).get(dominant, {}).get("traffic_bytes_per_launch")
         except Exception:
             pass
-        # a "launch" of a fused family is its group of kernels (4 for the key switch, ModUp and rescale; 3 for the batched hoisted
-        # rotations, whose ModDown runs the inverse column pass inside the conversion kernel unless --ks-fuse-inv 0)
-        ks_hoisted_group = 4 if args.ks_fuse_inv == 0 else 3
-        groups = max(1, d["launches"] // {"ks_hoisted": ks_hoisted_group, "ks_fused": 4, "modup": 4, "rescale": 4}.get(dominant, 1))
+        # a "launch" of a fused family is its group of kernels: P-limb kernel, ModDown middle (1 warp-task kernel, or 2 with
+        # --ks-moddown-w 0), Q-limb kernel once for the FP64 limbs and once for the 60-bit limb; 4 for ModUp and rescale
+        ks_group = 5 if args.ks_moddown_w == 0 else 4
+        groups = max(1, d["launches"] // {"ks_hoisted": ks_group, "ks_fused": ks_group, "modup": 4, "rescale": 4}.get(dominant, 1))
         avg_ms = d["ms"] / groups
         achieved = (d["bytes"] / groups) / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
         sec = ms_total / args.steps / 1e3

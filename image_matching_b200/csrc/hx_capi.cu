@@ -84,9 +84,9 @@ int hx_ctx_set_option(hx_ctx* ctx, const char* name, int value) {
         else if (n == "rot_chunk") ctx->eng->rot_chunk = value;
         else if (n == "rot_streams") ctx->eng->rot_streams = std::max(1, std::min(4, value));
         else if (n == "rot_lane") ctx->eng->rot_lane = value != 0;
-        else if (n == "ks_fuse_inv") ctx->eng->ks_fuse_inv = std::max(0, value);
         else if (n == "batch_blocks") ctx->eng->batch_blocks = value != 0;
         else if (n == "pdl") g_pdl = value != 0;
+        else if (n == "ks_moddown_w") ctx->eng->ks_moddown_w = value != 0;
         else if (n == "pool_reuse") set_pool_reuse(ctx->eng->device, value);
         else throw std::runtime_error("hx_ctx_set_option: unknown option " + n);)
 }

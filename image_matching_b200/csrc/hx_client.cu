@@ -58,7 +58,7 @@ __global__ void k_small_to_rns(DevTables T, u64* out, const long long* small, Li
     int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= T.N) return;
     u64 q = T.pc[lm.prime[blockIdx.y]].q;
-    long long v = small[idx];
+    long long v = (long long)ldg64(reinterpret_cast<const u64*>(small + idx));
     long long r = v % (long long)q;
     out[(size_t)blockIdx.y * T.N + idx] = r < 0 ? (u64)(r + (long long)q) : (u64)r;
 }
@@ -73,8 +73,8 @@ __global__ void k_ksgen_b(DevTables T, u64* b, const u64* a, const u64* e, const
     int i = blockIdx.y;
     const PrimeConst pc = T.pc[i];
     size_t o = (size_t)i * T.N + idx;
-    u64 v = sub_mod(e[o], mulmod(a[o], s_new[o], pc), pc.q);
-    if (s_old != nullptr && fac.v[i] != 0) v = add_mod(v, mulmod(fac.v[i], s_old[o], pc), pc.q);
+    u64 v = sub_mod(ldg64(e + o), mulmod(ldg64(a + o), ldg64(s_new + o), pc), pc.q);
+    if (s_old != nullptr && fac.v[i] != 0) v = add_mod(v, mulmod(fac.v[i], ldg64(s_old + o), pc), pc.q);
     b[o] = v;
 }
 // c0 = v*pkb + e0 + m ; c1 = v*pka + e1
@@ -85,8 +85,8 @@ __global__ void k_encrypt(DevTables T, u64* c, const u64* v, const u64* pkb, con
     int i = blockIdx.y;
     const PrimeConst pc = T.pc[i];
     size_t o = (size_t)i * T.N + idx;
-    c[o] = add_mod(add_mod(mulmod(v[o], pkb[o], pc), e0[o], pc.q), m[o], pc.q);
-    c[(size_t)nl * T.N + o] = add_mod(mulmod(v[o], pka[o], pc), e1[o], pc.q);
+    c[o] = add_mod(add_mod(mulmod(ldg64(v + o), ldg64(pkb + o), pc), ldg64(e0 + o), pc.q), ldg64(m + o), pc.q);
+    c[(size_t)nl * T.N + o] = add_mod(mulmod(ldg64(v + o), ldg64(pka + o), pc), ldg64(e1 + o), pc.q);
 }
 // acc = c0 + c1*s (+ c2*s^2)
 __global__ void k_decrypt(DevTables T, u64* acc, const u64* c, int ncomp, size_t cs, const u64* s) {
@@ -95,10 +95,10 @@ __global__ void k_decrypt(DevTables T, u64* acc, const u64* c, int ncomp, size_t
     int i = blockIdx.y;
     const PrimeConst pc = T.pc[i];
     size_t o = (size_t)i * T.N + idx;
-    u64 r = c[o], sp = s[o];
+    u64 r = ldg64(c + o), sp = ldg64(s + o);
     for (int k = 1; k < ncomp; k++) {
-        r = add_mod(r, mulmod(c[k * cs + o], sp, pc), pc.q);
-        sp = mulmod(sp, s[o], pc);
+        r = add_mod(r, mulmod(ldg64(c + k * cs + o), sp, pc), pc.q);
+        sp = mulmod(sp, ldg64(s + o), pc);
     }
     acc[o] = r;
 }

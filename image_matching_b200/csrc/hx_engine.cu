@@ -97,6 +97,7 @@ Engine::~Engine() {
     for (auto& kv : rot_keys_) { cudaFree(kv.second.a); cudaFree(kv.second.b); }
     if (have_mult_key_) { cudaFree(mult_key_.a); cudaFree(mult_key_.b); }
     for (auto& kv : db_) cudaFree(kv.second.d);
+    for (auto& r : rot_slots_) { if (r.d) cudaFree(r.d); if (r.released) cudaEventDestroy(r.released); }
     for (void* p : owned_) cudaFree(p);
     for (auto& r : prof_recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
     for (auto ev : prof_pool) cudaEventDestroy(ev);
@@ -384,23 +385,16 @@ static EvalKey upload_key(Engine& e, const u64* a, const u64* b) {
     e.sync();
     return k;
 }
-// Engine-internal key form: Montgomery residues, Q limbs pre-multiplied by P^-1 (so ModDown's last
-// multiplication disappears from the key-switch kernels).  Input: plain residues, [dnum][L+K][N].
+// Engine-internal key form (launch_key_finish): Q limbs pre-multiplied by P^-1 (so ModDown's last multiplication disappears from
+// the key-switch kernels); limbs below 2^46 as doubles (FP64 inner product), the 60-bit limbs (q_0 and P) as Montgomery residues
+// split into 30-bit halves (carry-free integer inner product).  Input: plain residues, [dnum][L+K][N].
 void Engine::finish_key(EvalKey& k) {
-    std::vector<int> primes;
-    for (int i = 0; i < L + K; i++) primes.push_back(i);
-    LimbMap lm = limb_map(primes);
     std::vector<u64> pinv(L);
     for (int i = 0; i < L; i++) pinv[i] = invmod(P_mod(i), mods[i]);
     ScalarTable ps = scalar_table(pinv);
-    const size_t ds = (size_t)(L + K) * N;
-    Scope sc(this, PK_MISC, 6, 96.0 * dnum * (L + K) * N);
-    launch_to_mont(T, k.a, dnum * (L + K), lm, st);
-    launch_to_mont(T, k.b, dnum * (L + K), lm, st);
-    launch_mul_scalar(T, k.a, k.a, ps, L, dnum, ds, ds, st);
-    launch_mul_scalar(T, k.b, k.b, ps, L, dnum, ds, ds, st);
-    launch_split30(k.a, (size_t)dnum * ds, st);   // 30-bit halves for the carry-free inner product
-    launch_split30(k.b, (size_t)dnum * ds, st);
+    Scope sc(this, PK_MISC, 2, 32.0 * dnum * (L + K) * N);
+    launch_key_finish(T, k.a, dnum, L, K, ps, st);
+    launch_key_finish(T, k.b, dnum, L, K, ps, st);
 }
 void Engine::load_mult_key(const u64* a, const u64* b) {
     Guard g(this);
@@ -510,8 +504,14 @@ void Engine::ks_core_batch(const u64* digits, int ndig, int nl, const std::vecto
             a.out_bs = out_bs;
             {   // algorithmic bytes of one key switch after ModUp: evk once, digits once per launch,
                 // addend once, result once
-                a.fuse_inv = ks_fuse_inv;
-                Scope sc(this, ks_kind, (ks_fuse_inv && n * 2 >= ks_fuse_inv) ? 3 : 4,   // launch_fused_tn: ModDown in 2 or 3 launches
+                a.moddown_w = ks_moddown_w;
+                a.fp_mask = 0;
+                for (int i = 0; i < nl; i++)
+                    if ((mods[i] >> 46) == 0) a.fp_mask |= 1ull << i;
+                const int n_fp = __builtin_popcountll(a.fp_mask);
+                const int k3_launches = (n_fp > 0) + (n_fp < nl);   // the Q-limb kernel runs once for the FP64 limbs and once for the 60-bit ones
+                const bool mw = ks_moddown_w && moddown_w_supported(logN, K);
+                Scope sc(this, ks_kind, (mw ? 2 : 3) + k3_launches,   // launch_fused_tn: ModDown's middle in 1 or 2 launches
                          8.0 * N * ((double)n * 2 * ndig * ext + (double)(digits_bs ? n : 1) * ndig * ext + (double)(addend_bs ? n : 1) * addend_comps * nl + (double)n * 2 * nl));
                 launch_fused_ks(T, a, moddown_table(nl), n, st);
             }

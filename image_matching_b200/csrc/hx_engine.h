@@ -76,7 +76,7 @@ public:
         std::unique_lock<std::recursive_mutex> lk;
         explicit Guard(Engine* e) : lk(e->mu) { cudaSetDevice(e->device); }
     };
-    int ks_fuse_inv = 16;            // > 0: ModDown of key-switch batches with at least this many polynomials runs the inverse column pass inside the conversion kernel
+    int ks_moddown_w = 1;            // ModDown's coefficient-domain middle as warp tasks (hx_moddown.cu) on rings of 2^15 / 2^16; 0 = the r1 launch sequence
     int rot_streams = 2;             // hoisted-rotation batches are issued round-robin on this many streams (1 = the engine stream only)
     cudaStream_t aux_streams[3] = {nullptr, nullptr, nullptr};
     cudaEvent_t aux_events[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -175,8 +175,18 @@ public:
     void db_store_device(int block, int diag, const u64* dev_ct /*[2][L][N], plain residues, device*/);
     int db_blocks() const { return (int)db_.size(); }
     // rotations 0..ndiag-1 of the query (entry 0 = the query), hoisted and batched, as one [ndiag][2][L][N] buffer
-    struct RotSet { u64* rotq = nullptr; int ndiag = 0, nl = 0, level = 0, deg = 0;
+    struct RotSet { u64* rotq = nullptr; int ndiag = 0, nl = 0, level = 0, deg = 0; int slot = -1;
                     Engine* eng = nullptr; std::shared_ptr<Engine> keep; ~RotSet(); };
+    // The rotated-query buffers (ndiag ciphertexts, 3.2 GB at the reference's parameters) are written by the rotation lanes and
+    // read by the diagonal MAC on the engine stream, and the NEXT query's rotations start while this one's MAC may still be queued.
+    // They are engine-owned slots recycled under explicit events -- a released slot carries an event recorded on the engine stream
+    // behind its last reader, and the next writer's stream waits for it -- instead of stream-ordered pool memory allocated on one
+    // stream and freed on another: with pool recycling of these buffers ~1 % of the index scenarios on a 2^12 ring came out wrong
+    // (tools/race_probe.py, profiles/r2_race_*.log), none with the buffer never recycled.
+    struct RotSlot { u64* d = nullptr; size_t words = 0; bool busy = false; cudaEvent_t released = nullptr; bool has_release = false; };
+    std::vector<RotSlot> rot_slots_;
+    int rot_slot_acquire(size_t words, cudaStream_t writer);   // returns the slot index; `writer` waits for the slot's last reader
+    void rot_slot_release(int slot);                           // records the release event on the engine stream
     std::shared_ptr<RotSet> rotate_hoisted_all(const Ct& query, int ndiag);   // sender_diag.cpp:20-26
     Ct rotset_entry(const RotSet& rs, int i);                                 // one rotated query as a ciphertext (copy)
     // computeSimilarityMatrix (sender_diag.cpp:66-83) for the named blocks against one rotation set, as batches of <= 32

@@ -16,6 +16,7 @@
 // All results are canonical residues: bit-identical to the unfused kernels and to the CPU oracle.
 #include "hx_kernels.cuh"
 #include "hx_ntt_tile.cuh"
+#include "hx_fpmod.cuh"
 
 #ifndef HX_MINB
 #define HX_MINB 3
@@ -129,7 +130,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_cols(const __grid
 #pragma unroll
     for (int u = 0; u < 8; u++) {
         const int l = u * kTileThreads + t;
-        smw[u * kWordStep] = limb[col_offset<LOGN>(tile, l)];
+        smw[u * kWordStep] = ldg64(limb + col_offset<LOGN>(tile, l));
     }
     __syncthreads();
     inv_col_pass<LOGN>(sm, t, T.tw_inv + (size_t)prime * T.N, q);
@@ -149,17 +150,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_cols(const __grid
 __device__ __forceinline__ void cp_async16(void* dst_smem, const void* src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
 }
-// FUSE_INV (ModDown of a large key-switch batch): `in` holds K1's output (inverse row pass done) and the CTA runs the
-// inverse column pass and the hatinv_n scaling of its n_in source tiles itself before converting ALL its target limbs
-// from shared memory -- k_inv_cols and the round trip of the scaled sources through tmpP disappear.
-// Coherent 64-bit global load that the compiler cannot turn into LD.NC: the FUSE_INV kernel reads source tiles it later overwrites
-// (its own column tile of the last scratch limb), and a line fetched through the non-coherent path could be served stale afterwards.
-__device__ __forceinline__ u64 ld_coherent(const u64* p) {
-    u64 v;
-    asm volatile("ld.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-template <int LOGN, bool FUSE_INV>
+template <int LOGN>
 __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __grid_constant__ DevTables T, const __grid_constant__ TabSet ts,
                                                                   const u64* __restrict__ in, size_t in_bs, u64* __restrict__ out, size_t out_bs,
                                                                   int ext_nl, int L, int jgroup) {
@@ -180,39 +171,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
     const int j0 = (blockIdx.y - ts.ystart[dgt]) * jgroup, j1 = min(n_out, j0 + jgroup);
     const u64* src = in + (size_t)blockIdx.z * in_bs + ((size_t)tile << G::LOGC);
     constexpr int kSegs = (1 << G::LOGC) / 2;                         // 16-byte chunks per tile row
-    if constexpr (FUSE_INV) {
-        const u64* lim = in + (size_t)blockIdx.z * in_bs;
-        u64 x[8];
-#pragma unroll
-        for (int u = 0; u < 8; u++) x[u] = ld_coherent(lim + col_offset<LOGN>(tile, u * kTileThreads + t));
-        for (int k = 0; k < n_in; k++) {
-            const int sp = tab->src[k];
-            const u64 sq = T.pc[sp].q;
-#pragma unroll
-            for (int u = 0; u < 8; u++) smw[u * kWordStep] = x[u];
-            __syncthreads();
-            if (k + 1 < n_in) {   // next source tile in flight during this one's butterflies
-#pragma unroll
-                for (int u = 0; u < 8; u++) x[u] = ld_coherent(lim + (size_t)(k + 1) * T.N + col_offset<LOGN>(tile, u * kTileThreads + t));
-            }
-            inv_col_pass<LOGN>(sm, t, T.tw_inv + (size_t)sp * T.N, sq);
-            const u64 h = tab->hatinv_n[k], hs = tab->hatinv_n_sh[k];
-            if (k < n_in - 1) {
-#pragma unroll
-                for (int u = 0; u < 8; u++) stage[k * kTileN + u * kTileThreads + t] = split30(shoup_mul(smw[u * kWordStep], h, hs, sq));
-            } else {
-                // the last source goes back to its own column tile of the scratch limb (no other CTA touches it) and is re-read
-                // per target through L1: n_in - 1 staged tiles keep the CTA at 66 KB of shared memory, 3 CTAs per SM
-                u64* back = const_cast<u64*>(lim) + (size_t)k * T.N;
-#pragma unroll
-                for (int u = 0; u < 8; u++) {
-                    const u64 v = split30(shoup_mul(smw[u * kWordStep], h, hs, sq));
-                    asm volatile("st.global.u64 [%0], %1;" ::"l"(back + col_offset<LOGN>(tile, u * kTileThreads + t)), "l"(v) : "memory");
-                }
-            }
-        }
-        __syncthreads();
-    } else {
+    {
         for (int k = 0; k < n_in; k++) {
 #pragma unroll
             for (int i = 0; i < 4; i++) {
@@ -229,17 +188,10 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
         acc3 acc[8];
 #pragma unroll
         for (int u = 0; u < 8; u++) acc[u] = {0, 0, 0};
-        const int n_st = FUSE_INV ? n_in - 1 : n_in;
-        for (int k = 0; k < n_st; k++) {   // n_in <= 7 (digit width / number of P limbs)
+        for (int k = 0; k < n_in; k++) {   // n_in <= 7 (digit width / number of P limbs)
             const u64 m = tab->mat30[k * n_out + j];
 #pragma unroll
             for (int u = 0; u < 8; u++) mac30ss(acc[u], stage[k * kTileN + u * kTileThreads + t], m);
-        }
-        if constexpr (FUSE_INV) {
-            const u64 m = tab->mat30[n_st * n_out + j];
-            const u64* last = in + (size_t)blockIdx.z * in_bs + (size_t)n_st * T.N;   // written by this CTA above: plain loads
-#pragma unroll
-            for (int u = 0; u < 8; u++) mac30ss(acc[u], ld_coherent(last + col_offset<LOGN>(tile, u * kTileThreads + t)), m);
         }
 #pragma unroll
         for (int u = 0; u < 8; u++) smw[u * kWordStep] = fwd_encode(redc(fold30(acc[u]), pc.q, pc.qinv_neg), fp_ok(pc.q));
@@ -257,18 +209,44 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_conv_fwd_col(const __
     }
 }
 // launch helper: dynamic shared memory = work tile + n_in staged source tiles
-template <int LOGN, bool FUSE_INV = false>
+template <int LOGN>
 static void launch_conv_fwd_col(const DevTables& T, const TabSet& ts, int max_n_in, int ny, int nbatch, const u64* in, size_t in_bs, u64* out,
                                 size_t out_bs, int ext_nl, int L, int jgroup, cudaStream_t st) {
-    const int bytes = (int)(kStageOff + (FUSE_INV ? max_n_in - 1 : max_n_in) * kTileBytes);
-    launch_pdl(k_conv_fwd_col<LOGN, FUSE_INV>, dim3(NttGeo<LOGN>::TILES, ny, nbatch), dim3(kTileThreads), bytes, st, T, ts, in, in_bs, out, out_bs, ext_nl, L, jgroup);
+    const int bytes = (int)(kStageOff + max_n_in * kTileBytes);
+    launch_pdl(k_conv_fwd_col<LOGN>, dim3(NttGeo<LOGN>::TILES, ny, nbatch), dim3(kTileThreads), bytes, st, T, ts, in, in_bs, out, out_bs, ext_nl, L, jgroup);
 }
 
 // ---------------------------------------------------------------------------------------------
-// K3: grid (TILES, 2*nl, nb).  out[b][comp][i][J] = (ip' - conv' + addend)[map_g(J)]  (ip', conv' carry the factor P^-1)
-// All global loads (converted tile, digits, key limbs) are issued before the transform so the
-// memory phase of one CTA overlaps the butterfly phase of its neighbours on the SM.
-template <int LOGN, int NDIG>
+// K3: grid (TILES, 2*nlimbs, nb) over the limbs listed in a.limbs (one launch for the FP64 limbs, one for the 60-bit ones).
+//   out[b][comp][i][J] = (ip - conv + addend)[map_g(J)]     (ip, conv carry the factor P^-1: it sits in the key's Q limbs and in the
+//   ModDown conversion matrix)
+// FP limbs (q < 2^46): the converted tile arrives as lazy doubles from the column pass, the forward row pass runs on doubles, the
+// evaluation-key inner product is computed on doubles as well (digits and the key's Q limbs are stored as doubles for these limbs:
+// 6 DP instructions per product against 4 IMAD.WIDE + a 128-bit fold + REDC), so the whole epilogue is `ip - conv + c0` in
+// doubles and ONE normalisation per coefficient.
+// The Galois permutation inside a tile is affine in the natural index: with J = otile*2048 + e (bit-reversed order), jh = brev11(e)
+// and jl = brev_h(otile), the source index is (2^h jh g + ((2 jl + 1) g >> 1)) mod N, i.e. source tile = brev_h(c mod 2^h) and
+// source offset = brev11(jh*g + (c >> h)) with c = ((2 jl + 1) g) >> 1: one multiply-add and two bit reversals per PAIR of
+// outputs (e, e+1 map to src, src^1 because g is odd).
+template <int LOGN>
+struct AutoTile {
+    u32 g, c1;
+    int tile;
+    __device__ __forceinline__ AutoTile(u32 otile, u32 g_) : g(g_) {
+        constexpr int h = LOGN - kLogTile;
+        const u32 jl = h ? (__brev(otile) >> (32 - h)) : 0u;
+        const u32 c = (((2u * jl + 1u) * g_) & ((2u << LOGN) - 1u)) >> 1;
+        tile = h ? (int)(__brev(c << (32 - h)) ) : 0;       // brev_h(c mod 2^h)
+        c1 = c >> h;
+    }
+    // source offset (inside the source tile) of output offset e = 2*m (m < 1024); e + 1 reads src ^ 1
+    __device__ __forceinline__ int src_of_pair(u32 m) const {
+        const u32 jh = __brev(m) >> 22;                       // brev11(2m) = brev10(m)
+        return (int)__brev((jh * g + c1) << 21);              // brev11 of the low 11 bits
+    }
+};
+
+template <int LOGN, int NDIG, bool FP>
 __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __grid_constant__ DevTables T, const __grid_constant__ FusedKsArgs a) {
     extern __shared__ __align__(128) unsigned char smraw[];
     u64* sm = reinterpret_cast<u64*>(smraw);                       // work tile
@@ -276,22 +254,18 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __g
     u64* mbar = reinterpret_cast<u64*>(smraw + kStageOff + NDIG * kTileBytes);
     const int t = threadIdx.x, otile = blockIdx.x;
     u64* const smp = sm + tphys(2 * t);   // this thread's element pairs: smp[u * kPairStep + {0,1}]
-    u64* const smw = sm + tphys(t);       // this thread's single words:  smw[u * kWordStep]
-    const int i = blockIdx.y >> 1, comp = blockIdx.y & 1, b = blockIdx.z;
-    const u32 g = a.galois[b];
-    // tiles map to tiles under the automorphism (the low bits of the natural index map among themselves)
-    const int tile = (int)(automap_at<LOGN>((u32)otile << kLogTile, g) >> kLogTile);
+    const int i = a.limbs[blockIdx.y >> 1], comp = blockIdx.y & 1, b = blockIdx.z;
+    const AutoTile<LOGN> am((u32)otile, a.galois[b]);
+    const int tile = am.tile;              // tiles map to tiles under the automorphism
     const PrimeConst pc = T.pc[i];
     const u64 q = pc.q;
-    const bool fp = fp_ok(q);
     const size_t toff = (size_t)tile * kTileN;
     const u64* cv = a.conv + (((size_t)b * 2 + comp) * a.nl + i) * T.N + toff;
     const u64* key = (comp == 0 ? a.keyB[b] : a.keyA[b]) + (size_t)i * T.N + toff;
     const u64* dig = a.digits + (size_t)b * a.digits_bs + (size_t)i * T.N + toff;
     const size_t kstride = (size_t)(a.L + a.K) * T.N, dstride = (size_t)(a.nl + a.K) * T.N;
-    // the key tiles of this CTA (NDIG x 16 KB, each contiguous) are fetched by TMA bulk copies into shared
-    // memory while the converted tile is loaded and transformed: 48 KB in flight per CTA without holding
-    // registers, and the inner product reads its keys at shared-memory latency
+    // the key tiles of this CTA (NDIG x 16 KB, each contiguous) are fetched by TMA bulk copies into shared memory while the
+    // converted tile is loaded and transformed: 48 KB in flight per CTA without holding registers
     if (t == 0) {
         mbar_init(mbar, 1);
         mbar_expect_tx(mbar, NDIG * kTileBytes);
@@ -307,61 +281,103 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __g
         smp[u * kPairStep + 1] = x.y;
     }
     __syncthreads();
-    fwd_row_pass<LOGN>(sm, t, tile, T, i, q);
+    {   // forward row pass, one arithmetic back end per instantiation (the launch lists separate the limbs)
+        using G = NttGeo<LOGN>;
+        if constexpr (FP) fwd_stages_fp<G::LOGD, kLogTile, G::A, G::LOGD>(reinterpret_cast<double*>(sm), t, tile, T.tw_fwd_d + (size_t)i * T.N, fp_from_u64(q));
+        else fwd_stages<G::LOGD, kLogTile, G::A, G::LOGD>(sm, t, tile, T.tw_fwd + (size_t)i * T.N, q, q << 2);
+    }
     const u64* add = (comp == 0 ? a.add0 : a.add1);
     if (add) add += (size_t)b * a.add_bs + (size_t)i * T.N + toff;
-    // P^-1 is folded into the evaluation keys' Q limbs and into the ModDown conversion matrix at load time
     mbar_wait(mbar, 0);
+    if constexpr (FP) {
+        const double qd = fp_from_u64(q), qinv = pc.qinv_d;
 #pragma unroll
-    for (int u = 0; u < 4; u++) {
-        const int e = (u * kTileThreads + t) * 2;
-        acc3 a0 = {0, 0, 0}, a1 = {0, 0, 0};
+        for (int u = 0; u < 4; u++) {
+            const int e = (u * kTileThreads + t) * 2;
+            double s0 = -fp_bits_to_double(smp[u * kPairStep]), s1 = -fp_bits_to_double(smp[u * kPairStep + 1]);
 #pragma unroll
-        for (int j = 0; j < NDIG; j++) {
-            const ulonglong2 d = ldg128(dig + j * dstride + e);
-            const ulonglong2 kv = *reinterpret_cast<const ulonglong2*>(kst + j * kTileN + e);
-            mac30ss(a0, d.x, kv.x);
-            mac30ss(a1, d.y, kv.y);
+            for (int j = 0; j < NDIG; j++) {
+                const ulonglong2 d = ldg128(dig + j * dstride + e);
+                const ulonglong2 kv = *reinterpret_cast<const ulonglong2*>(kst + j * kTileN + e);
+                s0 = __dadd_rn(s0, fp_mulmod(fp_bits_to_double(d.x), fp_bits_to_double(kv.x), qd, qinv));
+                s1 = __dadd_rn(s1, fp_mulmod(fp_bits_to_double(d.y), fp_bits_to_double(kv.y), qd, qinv));
+            }
+            if (add) {
+                const ulonglong2 ad = ldg128(add + e);
+                s0 = __dadd_rn(s0, fp_from_u64(ad.x));
+                s1 = __dadd_rn(s1, fp_from_u64(ad.y));
+            }
+            // |s| < 3 * (0.75 q + 2^43) + 10.3 q + q < 2^51: one normalisation gives the canonical residue
+            smp[u * kPairStep] = fp_to_u64(fp_normalize(s0, qd, qinv));
+            smp[u * kPairStep + 1] = fp_to_u64(fp_normalize(s1, qd, qinv));
         }
-        const u64 c0 = fwd_normalize(smp[u * kPairStep], pc, fp), c1 = fwd_normalize(smp[u * kPairStep + 1], pc, fp);
-        u64 r0 = sub_mod(redc(fold30(a0), q, pc.qinv_neg), c0, q);
-        u64 r1 = sub_mod(redc(fold30(a1), q, pc.qinv_neg), c1, q);
-        if (add) {
-            const ulonglong2 ad = ldg128(add + e);
-            r0 = add_mod(r0, ad.x, q);
-            r1 = add_mod(r1, ad.y, q);
+    } else {
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int e = (u * kTileThreads + t) * 2;
+            acc3 a0 = {0, 0, 0}, a1 = {0, 0, 0};
+#pragma unroll
+            for (int j = 0; j < NDIG; j++) {
+                const ulonglong2 d = ldg128(dig + j * dstride + e);
+                const ulonglong2 kv = *reinterpret_cast<const ulonglong2*>(kst + j * kTileN + e);
+                mac30ss(a0, d.x, kv.x);
+                mac30ss(a1, d.y, kv.y);
+            }
+            const u64 c0 = fwd_normalize(smp[u * kPairStep], pc, false), c1 = fwd_normalize(smp[u * kPairStep + 1], pc, false);
+            u64 r0 = sub_mod(redc(fold30(a0), q, pc.qinv_neg), c0, q);
+            u64 r1 = sub_mod(redc(fold30(a1), q, pc.qinv_neg), c1, q);
+            if (add) {
+                const ulonglong2 ad = ldg128(add + e);
+                r0 = add_mod(r0, ad.x, q);
+                r1 = add_mod(r1, ad.y, q);
+            }
+            smp[u * kPairStep] = r0;
+            smp[u * kPairStep + 1] = r1;
         }
-        smp[u * kPairStep] = r0;
-        smp[u * kPairStep + 1] = r1;
     }
     __syncthreads();
     u64* o = a.out + (size_t)b * a.out_bs + ((size_t)comp * a.nl + i) * T.N + (size_t)otile * kTileN;
 #pragma unroll
     for (int u = 0; u < 4; u++) {
-        const int e = (u * kTileThreads + t) * 2;
-        const u32 J = ((u32)otile << kLogTile) + e;
+        const int m = u * kTileThreads + t;
+        const int src = am.src_of_pair((u32)m), p = src & 1;
+        const u64* sp = sm + tphys(src & ~1);
         ulonglong2 x;
-        x.x = sm[tphys((int)(automap_at<LOGN>(J, g) & (kTileN - 1)))];
-        x.y = sm[tphys((int)(automap_at<LOGN>(J + 1, g) & (kTileN - 1)))];
-        st128(o + e, x);
+        x.x = sp[p];
+        x.y = sp[p ^ 1];
+        st128(o + 2 * m, x);
     }
 }
 
+// K3 in two launches: the FP64 limbs (q < 2^46) and the 60-bit limbs (q_0) run different code; a.fp_mask has bit i set for FP limbs
+template <int LOGN, int NDIG>
+static void launch_q_finish(const DevTables& T, const FusedKsArgs& a0, int nb, cudaStream_t st) {
+    using G = NttGeo<LOGN>;
+    FusedKsArgs a = a0;
+    int n = 0;
+    for (int i = 0; i < a.nl; i++)
+        if ((a.fp_mask >> i) & 1) a.limbs[n++] = (short)i;
+    if (n) launch_pdl(k_ks_q_finish<LOGN, NDIG, true>, dim3(G::TILES, 2 * n, nb), dim3(kTileThreads), ks_smem_bytes(NDIG), st, T, a);
+    n = 0;
+    for (int i = 0; i < a.nl; i++)
+        if (!((a.fp_mask >> i) & 1)) a.limbs[n++] = (short)i;
+    if (n) launch_pdl(k_ks_q_finish<LOGN, NDIG, false>, dim3(G::TILES, 2 * n, nb), dim3(kTileThreads), ks_smem_bytes(NDIG), st, T, a);
+}
 template <int LOGN, int NDIG>
 static void launch_fused_tn(const DevTables& T, const FusedKsArgs& a, const BaseConvTable* moddown, int nb, cudaStream_t st) {
     using G = NttGeo<LOGN>;
     launch_pdl(k_ks_p_inner<LOGN, NDIG>, dim3(G::TILES, 2 * a.K, nb), dim3(kTileThreads), ks_smem_bytes(NDIG), st, T, a);
     const TabSet ts = single_table(moddown);
-    if (a.fuse_inv && nb * 2 >= a.fuse_inv) {   // large batches: one CTA per column tile does K2a and K2b for all target limbs
-        launch_conv_fwd_col<LOGN, true>(T, ts, a.K, 1, nb * 2, a.tmpP, (size_t)a.K * T.N, a.conv, (size_t)a.nl * T.N, -1, 0, a.nl, st);
-        launch_pdl(k_ks_q_finish<LOGN, NDIG>, dim3(G::TILES, 2 * a.nl, nb), dim3(kTileThreads), ks_smem_bytes(NDIG), st, T, a);
+    if (a.moddown_w && moddown_w_supported(LOGN, a.K)) {   // rings of 2^15 / 2^16: the whole coefficient-domain middle as warp tasks
+        launch_moddown_w(T, moddown, a.K, nb * 2, a.tmpP, (size_t)a.K * T.N, a.conv, (size_t)a.nl * T.N, st);
+        launch_q_finish<LOGN, NDIG>(T, a, nb, st);
         return;
     }
     launch_pdl(k_inv_cols<LOGN>, dim3(G::TILES, a.K, nb * 2), dim3(kTileThreads), 0, st, T, ts, a.tmpP, (size_t)a.K * T.N);
     // large batches: 4 target limbs per CTA share one staging of the K source tiles
     const int jg = (nb * 2 >= 16) ? 4 : 1;
     launch_conv_fwd_col<LOGN>(T, ts, a.K, (a.nl + jg - 1) / jg, nb * 2, a.tmpP, (size_t)a.K * T.N, a.conv, (size_t)a.nl * T.N, -1, 0, jg, st);
-    launch_pdl(k_ks_q_finish<LOGN, NDIG>, dim3(G::TILES, 2 * a.nl, nb), dim3(kTileThreads), ks_smem_bytes(NDIG), st, T, a);
+    launch_q_finish<LOGN, NDIG>(T, a, nb, st);
 }
 template <int LOGN>
 static void launch_fused_t(const DevTables& T, const FusedKsArgs& a, const BaseConvTable* moddown, int nb, cudaStream_t st) {
@@ -422,35 +438,39 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_modup_rows(const __gr
     const int ext = gridDim.y;
     const int lo = d * alpha, hi = (d == ndig - 1) ? nl : (d + 1) * alpha;
     u64* limb = digits + ((size_t)blockIdx.z * ext + y) * T.N + (size_t)tile * kTileN;
+    // digit words as the key-switch inner products read them: doubles on the FP64 limbs (lazy there is fine: |x| < 2^51),
+    // 30-bit split words on the 60-bit limbs
+    const int prime = y < nl ? y : L + (y - nl);
+    const PrimeConst pc = T.pc[prime];
+    const u64 q = pc.q;
+    const bool fp = fp_ok(q);
     if (y >= lo && y < hi) {
         const u64* src = c + (size_t)bz * c_bs + (size_t)y * T.N + (size_t)tile * kTileN;
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             const int e = (u * kTileThreads + t) * 2;
             ulonglong2 x = ldg128(src + e);
-            x.x = split30(x.x); x.y = split30(x.y);
+            if (fp) { x.x = fp_double_to_bits(fp_from_u64(x.x)); x.y = fp_double_to_bits(fp_from_u64(x.y)); }
+            else { x.x = split30(x.x); x.y = split30(x.y); }
             st128(limb + e, x);
         }
         return;
     }
-    const int prime = y < nl ? y : L + (y - nl);
-    const PrimeConst pc = T.pc[prime];
-    const u64 q = pc.q;
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
-        const ulonglong2 x = *reinterpret_cast<const ulonglong2*>(limb + e);
+        const ulonglong2 x = ldg128(limb + e);
         smp[u * kPairStep] = x.x;
         smp[u * kPairStep + 1] = x.y;
     }
     __syncthreads();
     fwd_row_pass<LOGN>(sm, t, tile, T, prime, q);
-    const bool fp = fp_ok(q);
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
-        ulonglong2 x = {split30(fwd_normalize(smp[u * kPairStep], pc, fp)), split30(fwd_normalize(smp[u * kPairStep + 1], pc, fp))};
-        st128(limb + e, x);   // digits are stored split: the key-switch inner products multiply without unpacking
+        ulonglong2 x = {smp[u * kPairStep], smp[u * kPairStep + 1]};   // FP64 limbs: the row pass's lazy doubles as they are
+        if (!fp) { x.x = split30(fwd_normalize(x.x, pc, false)); x.y = split30(fwd_normalize(x.y, pc, false)); }
+        st128(limb + e, x);
     }
 }
 
@@ -579,14 +599,14 @@ bool fused_ks_supported(int logN) { return logN >= 12 && logN <= 16; }
 template <int LOGN>
 static void init_fused_t() {
     const int conv_max = (int)(kStageOff + 7 * kTileBytes);   // digit width / P basis <= 7 limbs (Engine constructor)
-    smem_optin(k_conv_fwd_col<LOGN, false>, conv_max);
-    smem_optin(k_conv_fwd_col<LOGN, true>, conv_max);
-    smem_optin(k_ks_p_inner<LOGN, 1>, ks_smem_bytes(1)); smem_optin(k_ks_q_finish<LOGN, 1>, ks_smem_bytes(1));
-    smem_optin(k_ks_p_inner<LOGN, 2>, ks_smem_bytes(2)); smem_optin(k_ks_q_finish<LOGN, 2>, ks_smem_bytes(2));
-    smem_optin(k_ks_p_inner<LOGN, 3>, ks_smem_bytes(3)); smem_optin(k_ks_q_finish<LOGN, 3>, ks_smem_bytes(3));
-    smem_optin(k_ks_p_inner<LOGN, 4>, ks_smem_bytes(4)); smem_optin(k_ks_q_finish<LOGN, 4>, ks_smem_bytes(4));
+    smem_optin(k_conv_fwd_col<LOGN>, conv_max);
+    smem_optin(k_ks_p_inner<LOGN, 1>, ks_smem_bytes(1)); smem_optin(k_ks_q_finish<LOGN, 1, true>, ks_smem_bytes(1)); smem_optin(k_ks_q_finish<LOGN, 1, false>, ks_smem_bytes(1));
+    smem_optin(k_ks_p_inner<LOGN, 2>, ks_smem_bytes(2)); smem_optin(k_ks_q_finish<LOGN, 2, true>, ks_smem_bytes(2)); smem_optin(k_ks_q_finish<LOGN, 2, false>, ks_smem_bytes(2));
+    smem_optin(k_ks_p_inner<LOGN, 3>, ks_smem_bytes(3)); smem_optin(k_ks_q_finish<LOGN, 3, true>, ks_smem_bytes(3)); smem_optin(k_ks_q_finish<LOGN, 3, false>, ks_smem_bytes(3));
+    smem_optin(k_ks_p_inner<LOGN, 4>, ks_smem_bytes(4)); smem_optin(k_ks_q_finish<LOGN, 4, true>, ks_smem_bytes(4)); smem_optin(k_ks_q_finish<LOGN, 4, false>, ks_smem_bytes(4));
 }
 void init_fused_kernels(int logN) {
+    init_moddown_kernels(logN);
     switch (logN) {
         case 12: init_fused_t<12>(); break;
         case 13: init_fused_t<13>(); break;

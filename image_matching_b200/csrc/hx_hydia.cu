@@ -51,7 +51,36 @@ void Engine::db_adopt(int block, u64* dev, int ndiag) {
 // (EvalFastRotationPrecompute + EvalFastRotation), then per block the 512 tensor products, their
 // sum, one relinearisation and one rescale (computeSimilarityMatrix, :66-83).
 Engine::RotSet::~RotSet() {
-    if (rotq && eng) { Engine::Guard g(eng); cudaFreeAsync(rotq, eng->st_main); }
+    if (slot >= 0 && eng) { Engine::Guard g(eng); eng->rot_slot_release(slot); }
+}
+int Engine::rot_slot_acquire(size_t words, cudaStream_t writer) {
+    int pick = -1;
+    for (size_t i = 0; i < rot_slots_.size(); i++)
+        if (!rot_slots_[i].busy && rot_slots_[i].words >= words && (pick < 0 || rot_slots_[i].words < rot_slots_[pick].words)) pick = (int)i;
+    if (pick < 0) {
+        for (size_t i = 0; i < rot_slots_.size(); i++)   // an idle slot that is too small: grow it (its last reader first)
+            if (!rot_slots_[i].busy) { pick = (int)i; break; }
+        if (pick < 0) { rot_slots_.emplace_back(); pick = (int)rot_slots_.size() - 1; }
+        RotSlot& r = rot_slots_[pick];
+        if (r.d) {
+            if (r.has_release) HX_CUDA(cudaEventSynchronize(r.released));
+            HX_CUDA(cudaFree(r.d));
+            r.d = nullptr; r.has_release = false;
+        }
+        HX_CUDA(cudaMalloc(&r.d, words * sizeof(u64)));
+        r.words = words;
+        if (!r.released) HX_CUDA(cudaEventCreateWithFlags(&r.released, cudaEventDisableTiming));
+    }
+    RotSlot& r = rot_slots_[pick];
+    r.busy = true;
+    if (r.has_release) HX_CUDA(cudaStreamWaitEvent(writer, r.released, 0));
+    return pick;
+}
+void Engine::rot_slot_release(int slot) {
+    RotSlot& r = rot_slots_[slot];
+    HX_CUDA(cudaEventRecord(r.released, st_main));   // every reader of a rotation set runs on (or is joined into) the engine stream
+    r.has_release = true;
+    r.busy = false;
 }
 std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_all(const Ct& query, int ndiag) {
     Guard g(this);
@@ -85,7 +114,8 @@ std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_all(const Ct& query, int 
     cudaEvent_t* evs = lane ? lane_events : aux_events;
     std::unique_ptr<Scope> span;
     try {
-        u64* rotq = rs->rotq = alloc_words(ct_words * ndiag);
+        rs->slot = rot_slot_acquire(ct_words * ndiag, st);
+        u64* rotq = rs->rotq = rot_slots_[rs->slot].d;
         HX_CUDA(cudaMemcpyAsync(rotq, query->d, sizeof(u64) * ct_words, cudaMemcpyDeviceToDevice, st));
         int ndig;
         digits = ks_precompute(query->comp(1), nl, &ndig);
@@ -129,8 +159,9 @@ std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_all(const Ct& query, int 
         cudaStreamSynchronize(first);
         for (int s = 0; s < ns - 1; s++)
             if (others[s]) cudaStreamSynchronize(others[s]);
-        st = main_st;
+        st = first;
         if (digits) free_words(digits);
+        st = main_st;
         throw;
     }
     st = first;
@@ -141,13 +172,13 @@ std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_all(const Ct& query, int 
         }
     prof_no_events = false;
     span.reset();
-    if (lane) {   // the engine stream joins: everything after this call (diagonal MAC, frees) is ordered behind the lane
+    free_words(digits);   // on `first`, behind every reader: scratch allocated on a stream is released on that stream
+    if (lane) {   // the engine stream joins: everything after this call (diagonal MAC, slot release) is ordered behind the lane
         HX_CUDA(cudaEventRecord(lane_events[4], first));
         HX_CUDA(cudaStreamWaitEvent(main_st, lane_events[4], 0));
     }
     st = main_st;
     ks_kind = PK_KS_FUSED;
-    free_words(digits);
     return rs;
 }
 Ct Engine::rotset_entry(const RotSet& rs, int i) {

@@ -4,6 +4,7 @@
 // Every kernel is HBM/L2-streaming integer work: one thread owns two adjacent coefficients of a
 // limb (128-bit loads/stores), grid.y walks limbs, grid.z walks batch entries.
 #include "hx_kernels.cuh"
+#include "hx_fpmod.cuh"
 
 namespace hx {
 
@@ -79,12 +80,18 @@ __global__ void __launch_bounds__(kThreads) k_ks_inner(DevTables T, const u64* _
     const u64* ka = reinterpret_cast<const u64*>(ldg64(reinterpret_cast<const u64*>(keyA + blockIdx.z)));   // pointer tables are pool memory
     const u64* kb = reinterpret_cast<const u64*>(ldg64(reinterpret_cast<const u64*>(keyB + blockIdx.z)));
     u128d b0 = {0, 0}, b1 = {0, 0}, a0 = {0, 0}, a1 = {0, 0};
+    const bool fpkey = kl < L && (pc.q >> 46) == 0;   // engine-internal key form (launch_key_finish): doubles of plain residues on these limbs
     for (int j = 0; j < ndig; j++) {
         ulonglong2 d = ldg128(digits + ((size_t)j * ext + i) * T.N + idx);
         size_t koff = ((size_t)j * (L + K) + kl) * T.N + idx;
         ulonglong2 vb = ld_stream128(kb + koff);
         ulonglong2 va = ld_stream128(ka + koff);
-        vb.x = unsplit30(vb.x); vb.y = unsplit30(vb.y); va.x = unsplit30(va.x); va.y = unsplit30(va.y);   // keys are stored split (fused path)
+        if (fpkey) {
+            vb.x = fp_to_u64(fp_bits_to_double(vb.x)); vb.y = fp_to_u64(fp_bits_to_double(vb.y));
+            va.x = fp_to_u64(fp_bits_to_double(va.x)); va.y = fp_to_u64(fp_bits_to_double(va.y));
+        } else {
+            vb.x = unsplit30(vb.x); vb.y = unsplit30(vb.y); va.x = unsplit30(va.x); va.y = unsplit30(va.y);   // Montgomery residues, stored split
+        }
         acc_wide(b0, d.x, vb.x);
         acc_wide(b1, d.y, vb.y);
         acc_wide(a0, d.x, va.x);
@@ -94,9 +101,11 @@ __global__ void __launch_bounds__(kThreads) k_ks_inner(DevTables T, const u64* _
     ulonglong2 r;
     r.x = redc(b0, pc.q, pc.qinv_neg);
     r.y = redc(b1, pc.q, pc.qinv_neg);
+    if (fpkey) { r.x = redc(mul_wide(r.x, pc.r2), pc.q, pc.qinv_neg); r.y = redc(mul_wide(r.y, pc.r2), pc.q, pc.qinv_neg); }   // plain key: undo the REDC's 2^-64
     st128(o, r);
     r.x = redc(a0, pc.q, pc.qinv_neg);
     r.y = redc(a1, pc.q, pc.qinv_neg);
+    if (fpkey) { r.x = redc(mul_wide(r.x, pc.r2), pc.q, pc.qinv_neg); r.y = redc(mul_wide(r.y, pc.r2), pc.q, pc.qinv_neg); }
     st128(o + (size_t)ext * T.N, r);
 }
 
@@ -339,7 +348,7 @@ __global__ void __launch_bounds__(kThreads) k_to_mont(DevTables T, u64* __restri
     size_t b = (size_t)blockIdx.y + (size_t)blockIdx.z * gridDim.y;
     const PrimeConst pc = T.pc[lm.prime[b % lm.period]];
     u64* p = data + b * T.N + idx;
-    ulonglong2 x = *reinterpret_cast<ulonglong2*>(p);
+    ulonglong2 x = ldg128(p);
     const u64 f = inverse ? 1ull : pc.r2;          // inverse: x * 2^-64, back to plain residues
     x.x = redc(mul_wide(x.x, f), pc.q, pc.qinv_neg);
     x.y = redc(mul_wide(x.y, f), pc.q, pc.qinv_neg);
@@ -348,9 +357,33 @@ __global__ void __launch_bounds__(kThreads) k_to_mont(DevTables T, u64* __restri
 __global__ void __launch_bounds__(kThreads) k_split30(u64* __restrict__ data, size_t words) {
     size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (i >= words) return;
-    ulonglong2 x = *reinterpret_cast<ulonglong2*>(data + i);
+    ulonglong2 x = ldg128(data + i);
     x.x = split30(x.x); x.y = split30(x.y);
     st128(data + i, x);
+}
+// grid (N / 512, L + K, dnum)
+__global__ void __launch_bounds__(kThreads) k_key_finish(DevTables T, u64* __restrict__ key, int L, int K, ScalarTable pinv) {
+    const int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    const int limb = blockIdx.y;
+    const PrimeConst pc = T.pc[limb];
+    u64* p = key + ((size_t)blockIdx.z * (L + K) + limb) * T.N + idx;
+    ulonglong2 x = ldg128(p);
+    if (limb < L) {
+        x.x = shoup_mul(x.x, pinv.v[limb], pinv.sh[limb], pc.q);
+        x.y = shoup_mul(x.y, pinv.v[limb], pinv.sh[limb], pc.q);
+    }
+    if (limb < L && (pc.q >> 46) == 0) {
+        x.x = fp_double_to_bits(fp_from_u64(x.x));
+        x.y = fp_double_to_bits(fp_from_u64(x.y));
+    } else {
+        x.x = split30(redc(mul_wide(x.x, pc.r2), pc.q, pc.qinv_neg));
+        x.y = split30(redc(mul_wide(x.y, pc.r2), pc.q, pc.qinv_neg));
+    }
+    st128(p, x);
+}
+void launch_key_finish(const DevTables& T, u64* key, int dnum, int L, int K, const ScalarTable& pinv, cudaStream_t st) {
+    k_key_finish<<<dim3(blocks_for(T.N), L + K, dnum), kThreads, 0, st>>>(T, key, L, K, pinv);
 }
 void launch_split30(u64* data, size_t words, cudaStream_t st) {
     k_split30<<<(unsigned)((words / 2 + kThreads - 1) / kThreads), kThreads, 0, st>>>(data, words);

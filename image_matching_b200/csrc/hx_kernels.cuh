@@ -73,13 +73,19 @@ struct FusedKsArgs {
     size_t add_bs = 0;              // words between the addends of consecutive batch entries (0 = shared)
     u64* out;                       // [nb] x out_bs, each [2][nl][N]
     size_t out_bs;
-    int fuse_inv = 16;              // Engine::ks_fuse_inv
+    int moddown_w = 1;              // Engine::ks_moddown_w: warp-task ModDown middle (hx_moddown.cu) where the ring supports it
+    unsigned long long fp_mask = 0; // bit i: Q limb i is an FP64 limb (q_i < 2^46); set by the engine
+    short limbs[kMaxPrimes];        // filled per launch of the Q-limb kernel: the limbs grid.y walks (FP64 limbs / 60-bit limbs)
 };
 bool fused_ks_supported(int logN);
 // per-device opt-ins (dynamic shared memory above 48 KB) of every kernel a ring of 2^logN coefficients launches; called by the
 // Engine constructor with its device current
 void init_device_kernels(int logN);
 void launch_fused_ks(const DevTables& T, const FusedKsArgs& a, const BaseConvTable* moddown, int nb, cudaStream_t st);
+// ModDown middle as warp tasks (hx_moddown.cu): in [nbatch][n_in][N] (inverse row pass done) -> out [nbatch][n_out][N] (forward column pass done)
+bool moddown_w_supported(int logN, int n_in);
+void init_moddown_kernels(int logN);
+void launch_moddown_w(const DevTables& T, const BaseConvTable* tab, int n_in, int nbatch, const u64* in, size_t in_bs, u64* out, size_t out_bs, cudaStream_t st);
 
 // fused ModUp: c [nbatch] x c_bs, each [nl][N]  ->  digits [nbatch][ndig][nl+K][N]
 struct ModUpArgs {
@@ -145,6 +151,10 @@ inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t s
     if (e != cudaSuccess) throw std::runtime_error(std::string("kernel launch failed: ") + cudaGetErrorString(e));
 }
 void launch_to_mont(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, cudaStream_t st, bool inverse = false);
+// Engine-internal evaluation-key form, in place on [dnum][L+K][N] plain residues (Engine::finish_key): Q limbs are multiplied by
+// P^-1 mod q_i; limbs below 2^46 (the FP64 limbs of the key-switch kernels) become doubles holding that residue, all other limbs
+// become Montgomery residues split into 30-bit halves.
+void launch_key_finish(const DevTables& T, u64* key, int dnum, int L, int K, const ScalarTable& pinv, cudaStream_t st);
 // in place: x -> split30(x) (engine-internal key form, see hx_modarith.cuh)
 void launch_split30(u64* data, size_t words, cudaStream_t st);
 

@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(kTile / kEPT) k_ntt_row(DevTables T, NttGeom g
     const int tile = 1 << g.logT;
     u64* limb = data + (size_t)blockIdx.y * T.N + (size_t)blockIdx.x * tile;
     for (int e = t * 2; e < tile; e += nthr * 2) {
-        ulonglong2 x = *reinterpret_cast<const ulonglong2*>(limb + e);
+        ulonglong2 x = ldg128(limb + e);
         sm[phys(e)] = x.x;
         sm[phys(e + 1)] = x.y;
     }
@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(kTile / kEPT) k_ntt_col(DevTables T, NttGeom g
     u64* limb = data + (size_t)blockIdx.y * T.N + ((size_t)blockIdx.x << g.logC);
     for (int e = t; e < tile; e += nthr) {
         int r = e >> g.logC, c = e & cmask;
-        sm[phys(e)] = limb[((size_t)r << g.B) + c];
+        sm[phys(e)] = ldg64(limb + ((size_t)r << g.B) + c);
     }
     __syncthreads();
     if (!kInverse) {
@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(kTileThreads) k_ntt_row_t(const __grid_constan
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
-        const ulonglong2 x = *reinterpret_cast<const ulonglong2*>(limb + e);
+        const ulonglong2 x = ldg128(limb + e);
         sm[tphys(e)] = x.x;
         sm[tphys(e + 1)] = x.y;
     }
@@ -260,7 +260,7 @@ __global__ void __launch_bounds__(kTileThreads) k_ntt_col_t(const __grid_constan
 #pragma unroll
     for (int u = 0; u < 8; u++) {
         const int l = u * kTileThreads + t;
-        const u64 x = limb[col_offset<LOGN>(tile, l)];
+        const u64 x = ldg64(limb + col_offset<LOGN>(tile, l));
         sm[tphys(l)] = kInverse ? x : fwd_encode(x, fp_ok(q));
     }
     __syncthreads();

@@ -44,8 +44,9 @@ uint64_t hx_ctx_launches(hx_ctx* ctx);              /* kernels launched so far (
 /* Engine tuning / test switches: "rot_chunk" (hoisted rotations per key-switch batch), "rot_streams" (streams the
  * independent batches are issued on, default 2: the tail of one batch overlaps the head of the next),
  * "force_unfused" (1 = run the unfused reference kernels instead of the fused key-switch pipeline),
- * "ks_fuse_inv" (default 16: key-switch batches with at least this many polynomials run ModDown's inverse column pass inside
- * the base-conversion kernel, one launch and one pass over the P limbs fewer; 0 = separate launch; same bits either way),
+ * "ks_moddown_w" (default 1: on rings of 2^15 / 2^16 coefficients ModDown's coefficient-domain middle runs as warp tasks in one
+ * kernel, hx_moddown.cu; 0 = the two-launch tile sequence every other ring uses; same bits either way),
+ * "pdl" (default 1: dependent kernels are launched with programmatic stream serialization; 0 = plain stream order),
  * "rot_lane" (default 1: the hoisted rotations of an uploaded query are issued on low-priority side streams that do not wait for
  * work still queued on the engine stream, so the previous call's compare chain overlaps them; 0 = one ordered stream),
  * "batch_blocks" (default 1: the fused HyDia entries relinearise / rescale / compare all database blocks of

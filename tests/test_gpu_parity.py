@@ -169,10 +169,9 @@ def test_hydia_fused_path_bit_exact_small_ring(golden_dir):
     cc.set_option("batch_blocks", 0)
     assert all(same(g, w) for g, w in zip(cc.index(gq), widx))
     cc.set_option("batch_blocks", 1)
-    # ModDown of the 32-rotation batches with the inverse column pass inside the conversion kernel (one launch fewer) vs the
-    # separate k_inv_cols launch: same polynomials
-    for thr in (0, 16):
-        cc.set_option("ks_fuse_inv", thr)
+    # one stream vs two for the 32-rotation batches: same polynomials
+    for ns in (1, 2):
+        cc.set_option("rot_streams", ns)
         assert all(same(g, w) for g, w in zip(cc.score_diag(gq), want))
     # rotation lane (the uploaded query's rotations issued on low-priority side streams, so a previous call's compare chain
     # overlaps them) vs everything ordered on the engine stream: back-to-back scenarios, same polynomials

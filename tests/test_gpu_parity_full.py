@@ -1,7 +1,7 @@
 """GPU parity at the shapes that are TIMED and at the parameter sets the reference uses:
 
 * bench.py's exact launch shape -- N = 2^15, 12 + 4 limbs, 512 diagonals (16 key-switch batches of 32 rotations, q0 fold every 64
-  terms), 2 database blocks, rot_lane 1, ks_fuse_inv 16 -- bit-exact against the oracle for score_diag / index / membership
+  terms), 2 database blocks, rot_lane 1, the warp-task ModDown kernel -- bit-exact against the oracle for score_diag / index / membership
   (/root/reference/src/sender/sender_diag.cpp:12-63), the GPU side repeated >= 20 times back to back (membership -> index ->
   membership) against one oracle answer: the regression test for cross-stream / stale-line races in the hoisted-rotation batch.
 * N = 2^16 with the limb counts of approach 3 (depth 12: 13 + 4) and approach 1 (depth 13: 14 + 4), and approach 2's 19 + 6
@@ -23,7 +23,7 @@ def test_bench_shape_bit_exact_repeated():
     assert (orc.N, orc.P.L, orc.P.K) == (32768, 12, 4)
     cc = make_gpu_context(orc)
     cc.set_option("rot_lane", 1)
-    cc.set_option("ks_fuse_inv", 16)
+    cc.set_option("ks_moddown_w", 1)
     rng = np.random.default_rng(77)
     # the database blocks reuse 64 distinct ciphertexts each (the arithmetic per diagonal does not care, encryption time does)
     base = [orc.encrypt(rng.uniform(-0.05, 0.05, orc.P.slots)) for _ in range(64 * blocks)]
@@ -44,12 +44,12 @@ def test_bench_shape_bit_exact_repeated():
         if not (same(m1, wm) and same(m2, wm) and len(i1) == blocks and all(same(g, w) for g, w in zip(i1, widx))):
             bad.append(it)
     assert not bad, f"mismatch against the oracle in repeats {bad} of {repeats}"
-    # and with everything ordered on the engine stream / the unfused ModDown launch sequence
-    for lane, fuse in ((0, 16), (1, 0), (0, 0)):
+    # and with everything ordered on the engine stream / the r1 ModDown launch sequence (k_inv_cols + k_conv_fwd_col)
+    for lane, mw in ((0, 1), (1, 0), (0, 0)):
         cc.set_option("rot_lane", lane)
-        cc.set_option("ks_fuse_inv", fuse)
+        cc.set_option("ks_moddown_w", mw)
         for _ in range(3):
-            assert same(cc.membership(gq, ndiag), wm) and all(same(g, w) for g, w in zip(cc.index(gq, ndiag), widx)), (lane, fuse)
+            assert same(cc.membership(gq, ndiag), wm) and all(same(g, w) for g, w in zip(cc.index(gq, ndiag), widx)), (lane, mw)
 
 
 @pytest.mark.parametrize("depth,L,K", [(12, 13, 4), (13, 14, 4), (18, 19, 6)])

@@ -16,7 +16,8 @@ import image_matching_b200 as hx
 def main():
     repeats = int(sys.argv[1]) if len(sys.argv) > 1 else 20
     ndiag, blocks = 512, 2
-    cc = hx.CryptoContext.generate(depth=11)
+    ring = int(os.environ.get("PROBE_RING", "0"))   # 0 = the reference's ring (2^15); 4096 exercises the small-ring kernels
+    cc = hx.CryptoContext.generate(depth=11, ring_dim=ring)
     cl = hx.Client(cc, seed=3)
     cl.EvalMultKeyGen(); cl.EvalSumKeyGen(); cl.EvalRotateKeyGen(list(range(1, ndiag)))
     rng = np.random.default_rng(5)
@@ -28,9 +29,9 @@ def main():
     q = cc.upload(q0.to_numpy(), 0, 1)   # an UPLOADED query is 'settled': only then does the engine use the rotation lane
 
     def setopt(lane, fuse, streams, pdl):
-        cc.set_option("rot_lane", lane); cc.set_option("ks_fuse_inv", fuse); cc.set_option("rot_streams", streams); cc.set_option("pdl", pdl)
+        cc.set_option("rot_lane", lane); cc.set_option("ks_moddown_w", fuse); cc.set_option("rot_streams", streams); cc.set_option("pdl", pdl)
 
-    setopt(0, 0, 1, 0)
+    setopt(0, 0, 1, 0)   # the most conservative configuration: r1 ModDown launch sequence, one stream, no lane, no PDL
     ref_s = [c.to_numpy() for c in cc.score_diag(q, ndiag)]
     ref_i = [c.to_numpy() for c in cc.index(q, ndiag)]
     ref_m = cc.membership(q, ndiag).to_numpy()
@@ -47,23 +48,50 @@ def main():
 
     pools = [int(x) for x in os.environ.get("PROBE_POOL", "7").split(",")]
     lanes = [int(x) for x in os.environ.get("PROBE_LANE", "0,1").split(",")]
-    for pool, lane, fuse, streams, pdl in itertools.product(pools, lanes, (0, 16), (1, 2), (0, 1)):
+    only = os.environ.get("PROBE_ONLY")   # "moddown_w,streams,pdl" to run a single configuration
+    for pool, lane, fuse, streams, pdl in itertools.product(pools, lanes, (0, 1), (1, 2), (0, 1)):
+        if only and only != f"{fuse},{streams},{pdl}":
+            continue
         cc.set_option("pool_reuse", pool)
         setopt(lane, fuse, streams, pdl)
         bad_s = bad_chain = 0
         first = None
+        details = []
         for it in range(repeats):
             s = cc.score_diag(q, ndiag)
-            m1, i1, m2 = cc.membership(q, ndiag), cc.index(q, ndiag), cc.membership(q, ndiag)
+            mode = os.environ.get("PROBE_MODE", "")
+            m1, i1 = cc.membership(q, ndiag), cc.index(q, ndiag)
+            early = clones = None
+            if mode == "early":      # download the index results before the next scenario is issued
+                early = [c.to_numpy() for c in i1]
+            elif mode == "clone":    # device-side copies taken right after the index scenario, compared at the end
+                clones = [cc._ct(cc._lib.hx_ct_clone(c._h)) for c in i1]
+            m2 = cc.membership(q, ndiag)
+            if early is not None:
+                for g, (a, e) in enumerate(zip(ref_i, early)):
+                    if not np.array_equal(a, e) and len(details) < 6:
+                        details.append(f"it {it} EARLY download of i1[{g}] already wrong: " + where(a, e))
+            if clones is not None:
+                for g, (a, c, o) in enumerate(zip(ref_i, clones, i1)):
+                    cn, on = c.to_numpy(), o.to_numpy()
+                    if (not np.array_equal(a, cn) or not np.array_equal(a, on)) and len(details) < 6:
+                        details.append(f"it {it} i1[{g}]: clone {'ok' if np.array_equal(a, cn) else 'WRONG'}, original {'ok' if np.array_equal(a, on) else 'WRONG'}")
             for g, (a, c) in enumerate(zip(ref_s, s)):
                 x = c.to_numpy()
                 if not np.array_equal(a, x):
                     bad_s += 1
                     first = first or f"score block {g}: " + where(a, x)
-            ok = np.array_equal(m1.to_numpy(), ref_m) and np.array_equal(m2.to_numpy(), ref_m) and all(np.array_equal(a, c.to_numpy()) for a, c in zip(ref_i, i1))
+            ok = True
+            for name, got, want in [("m1", m1.to_numpy(), ref_m), ("m2", m2.to_numpy(), ref_m)] + [(f"i1[{g}]", c.to_numpy(), a) for g, (a, c) in enumerate(zip(ref_i, i1))]:
+                if not np.array_equal(got, want):
+                    ok = False
+                    if len(details) < 6:
+                        details.append(f"it {it} {name}: " + where(want, got))
             bad_chain += 0 if ok else 1
-        print(f"pool={pool} lane={lane} fuse_inv={fuse} streams={streams} pdl={pdl}: score mismatches {bad_s}/{repeats * blocks}, scenario-chain mismatches {bad_chain}/{repeats}"
+        print(f"pool={pool} lane={lane} moddown_w={fuse} streams={streams} pdl={pdl}: score mismatches {bad_s}/{repeats * blocks}, scenario-chain mismatches {bad_chain}/{repeats}"
               + (f"  first: {first}" if first else ""), flush=True)
+        for d in details:
+            print("      " + d, flush=True)
 
 
 if __name__ == "__main__":

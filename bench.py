@@ -1,16 +1,22 @@
 """bench.py -- HyDia approach 5 encrypted match latency on B200 (BASELINE.json metric).
 
-A step = one query through DiagonalSender.membershipScenario + indexScenario
-(/root/reference/src/main.cpp:343,361), each recomputing the similarity as the reference does.
-Workload at N=1: configs[1] (2^14-vector synthetic DB = 1 block of 512 diagonal ciphertexts);
-N>1: weak scaling, --blocks-per-gpu blocks on every rank (8 blocks x 8 GPUs = configs[4], 2^20).
-See DESIGN.md "Measurement" for every field of the JSON line.
+A step = one query through DiagonalSender.membershipScenario + indexScenario (/root/reference/src/main.cpp:343,361), each
+recomputing the similarity as the reference does (src/sender/sender_diag.cpp:12-63).
+
+Workloads:
+  --gpus 1           BASELINE configs[1]: 2^14-vector synthetic DB = 1 block of 512 diagonal ciphertexts (N = 2^15, 12 + 4 limbs);
+                     the line also carries `share_of_configs4`: the same step on 8 blocks, one GPU's share of configs[4]
+  --gpus 2 | 4 | 8   BASELINE configs[4]: 2^20 vectors = 64 blocks sharded contiguously over the ranks (strong scaling: the
+                     database is the same for every N >= 2); --total-blocks overrides
+  --impl reference   the CPU arm: the oracle port of the same path on all host cores (oracle/cpu_path.py; OpenFHE is not
+                     installable here), rank 0 only
+Every field of the JSON line is described in DESIGN.md "Measurement".
 """
 import argparse
 import json
 import os
-import subprocess
 import sys
+import tempfile
 import threading
 import time
 
@@ -22,6 +28,7 @@ if ROOT not in sys.path:
 
 METRIC = "encrypted_match_latency_membership_plus_index"
 UNIT = "s"
+SLOTS = 16384
 # BASELINE.md "HyDia, approach 5": published Sender compute seconds (membership, index) per DB size on a 48-thread
 # Xeon Gold 5412U (tools/figures/approach5.csv) -- other hardware, not re-measured; vs_baseline = value / (m + i)
 PUBLISHED_APPROACH5 = {1 << 14: (4.518783, 4.175511), 1 << 15: (6.155975, 5.85484), 1 << 16: (9.560245, 9.011757),
@@ -29,31 +36,42 @@ PUBLISHED_APPROACH5 = {1 << 14: (4.518783, 4.175511), 1 << 15: (6.155975, 5.8548
                        1 << 20: (102.411, 96.52172)}
 
 
-def vs_published(args, seconds):
-    if args.ring_dim or args.ndiag != 512:
-        return None
-    pub = PUBLISHED_APPROACH5.get(args.blocks_per_gpu * args.gpus * 16384)
-    return seconds / sum(pub) if pub else None
-
-
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=6)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--blocks-per-gpu", type=int, default=1)
-    ap.add_argument("--ring-dim", type=int, default=0, help="0 = the 128-bit ring of the reference (2^15)")
+    ap.add_argument("--total-blocks", type=int, default=0, help="database blocks of 16384 vectors over all GPUs (0: 1 at --gpus 1, 64 = configs[4] otherwise)")
+    ap.add_argument("--ring-dim", type=int, default=0, help="0 = the 128-bit ring of the reference (2^15); smaller rings are for quick checks only")
     ap.add_argument("--ndiag", type=int, default=512)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-share", action="store_true", help="--gpus 1: skip the extra 8-block measurement (share_of_configs4)")
+    ap.add_argument("--cpu-budget-s", type=float, default=200.0, help="--impl reference: wall-clock budget that sizes the per-step sample")
     ap.add_argument("--rot-chunk", type=int, default=0, help="override the engine's hoisted-rotation batch size")
     ap.add_argument("--rot-streams", type=int, default=0, help="override the number of streams the hoisted-rotation batches use")
     ap.add_argument("--ks-moddown-w", type=int, default=-1, help="override the engine's warp-task ModDown kernel (0 = the r1 launch sequence)")
     ap.add_argument("--rot-lane", type=int, default=-1, help="override the engine's rotation lane (0 = all work ordered on the engine stream)")
+    ap.add_argument("--rot-shard", type=int, default=-1, help="N > 1: 1 = hoisted rotations sharded over the ranks and all-gathered, 0 = every rank computes all of them")
     ap.add_argument("--sync-exchange", action="store_true", help="N > 1: host-synchronous result exchange (no overlap of the scenarios)")
-    ap.add_argument("--ncu-range", action="store_true",
-                    help="run one extra step inside cudaProfilerStart/Stop (for ncu --profile-from-start off)")
-    return ap.parse_args()
+    ap.add_argument("--ncu-range", action="store_true", help="run one extra step inside cudaProfilerStart/Stop (for ncu --profile-from-start off)")
+    a = ap.parse_args()
+    if a.total_blocks <= 0:
+        a.total_blocks = 1 if a.gpus == 1 else 64
+    if a.total_blocks % a.gpus:
+        raise SystemExit(f"--total-blocks {a.total_blocks} is not a multiple of --gpus {a.gpus}")
+    return a
+
+
+def slots_of(args):
+    return (args.ring_dim // 2) if args.ring_dim else SLOTS
+
+
+def vs_published(args, seconds):
+    if args.ring_dim or args.ndiag != 512:
+        return None
+    pub = PUBLISHED_APPROACH5.get(args.total_blocks * SLOTS)
+    return seconds / sum(pub) if pub else None
 
 
 def synth_db(n, seed, match_rows):
@@ -63,6 +81,18 @@ def synth_db(n, seed, match_rows):
     for r in match_rows:
         db[r] = rng.integers(1, 4, size=512)
     return db
+
+
+def workload_config(args, total_blocks=None):
+    tb = total_blocks or args.total_blocks
+    full = not args.ring_dim and args.ndiag == 512
+    name = " = BASELINE configs[1]" if (tb == 1 and full) else (" = BASELINE configs[4]" if (tb == 64 and full) else "")
+    return {"workload": f"HyDia approach 5, membership + index scenarios, synthetic DB of {tb * slots_of(args)} vectors x 512 dims "
+                        f"({tb} block(s) of {args.ndiag} diagonal ciphertexts, {tb // args.gpus} per GPU){name}",
+            "approach": 5, "ring_dim": args.ring_dim or 32768, "limbs": "12+4", "total_blocks": tb, "blocks_per_gpu": tb // args.gpus,
+            "ndiag": args.ndiag,
+            "scaling_note": "N = 1 runs configs[1] (1 block); every N >= 2 runs the same 64-block database (strong scaling)",
+            "l2_policy": "inputs larger than L2: each step streams 13.3 GB of rotation keys and 3.2 GB of database per block (L2 = 126 MB)"}
 
 
 class ClockSampler(threading.Thread):
@@ -97,83 +127,102 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
-def cpu_port_latency(ring_dim, ndiag, blocks, n_rot_sample=96):
-    """CPU arm: the oracle (oracle/ckks_oracle.py over oracle/ckks_ref.c, OpenMP on all host cores) runs the
-    same op sequence as sender_diag.cpp on a bounded sample -- n_rot_sample hoisted rotations and diagonal
-    products instead of ndiag-1 / ndiag, everything else in full -- and the per-op times are scaled to the
-    full workload. Returns (estimated seconds for membership + index, description, cores)."""
+# ---------------------------------------------------------------------------------------------------- CPU arm
+def cpu_arm(args, total_blocks, steps, warmup, budget_s):
+    """The oracle port of sender_diag.cpp:12-63 on all host cores (oracle/cpu_path.py restates the reference's OpenMP loops).
+    A step runs the path IN FULL when the workload is one block (configs[1]); for more blocks the per-block part (512 products +
+    511 adds + relinearise + rescale + compare) is run on a bounded sample of blocks and scaled -- the fixed part (511 hoisted
+    rotations per scenario) always runs in full.  Two database modes: (ii) ciphertexts in RAM -- the
+    reported value -- and (i) re-read from files inside the timed region as sender_diag.cpp:87-91 does, timed once.
+    Returns (seconds per step [list], description dict)."""
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)   # torchrun exports 1 to its workers
     from oracle import ckks_oracle as O
-    P = O.gen_params(11, ring_dim=ring_dim or None)
+    from oracle.cpu_path import CpuDiagPath, DiskDb, host_threads
+    ndiag = args.ndiag
+    threads = host_threads()
+    P = O.gen_params(11, ring_dim=args.ring_dim or None)
     orc = O.Oracle(P)
     orc.keygen(1)
     orc.mult_keygen()
-    ns = min(n_rot_sample, ndiag - 1)
-    orc.rot_keygen(list(range(1, ns + 1)) + [1 << i for i in range(2)])
+    orc.rot_keygen(list(range(1, ndiag)) + [1 << i for i in range(int(np.log2(P.slots)))])
     rng = np.random.default_rng(0)
+    ndist = 64   # distinct database ciphertexts (encryption time; the arithmetic per diagonal does not care)
+    base = [orc.encrypt(rng.uniform(-0.04, 0.04, P.slots)) for _ in range(ndist)]
     q = orc.encrypt(rng.uniform(-0.04, 0.04, P.slots))
-    dbc = [orc.encrypt(rng.uniform(-0.04, 0.04, P.slots)) for _ in range(4)]
-    t0 = time.perf_counter()
-    dg = orc.fast_rotation_precompute(q)
-    t_pre = time.perf_counter() - t0
-    t0 = time.perf_counter()
-    rot = [orc.fast_rotation(q, r, dg) for r in range(1, ns + 1)]
-    t_rot = (time.perf_counter() - t0) / ns
-    t0 = time.perf_counter()
-    acc = orc.mult_norelin(q, dbc[0])
-    for i, r in enumerate(rot):
-        acc = orc.add(acc, orc.mult_norelin(r, dbc[(i + 1) % 4]))
-    t_mac = (time.perf_counter() - t0) / (ns + 1)
-    t0 = time.perf_counter()
-    s = orc.rescale(orc.relinearize(acc))
-    t_relin = time.perf_counter() - t0
-    t0 = time.perf_counter()
-    c = orc.chebyshev_compare(s, 0.44, 10)
-    t_cmp = time.perf_counter() - t0
-    t0 = time.perf_counter()
-    m = orc.add(c, orc.automorphism(c, 5))
-    m = orc.add(m, orc.automorphism(m, 25))
-    t_sumrot = (time.perf_counter() - t0) / 2
-    nsum = int(np.log2(P.slots))
-    scen = t_pre + (ndiag - 1) * t_rot + blocks * (ndiag * t_mac + t_relin + t_cmp)
-    total = 2 * scen + nsum * t_sumrot
-    cores = os.cpu_count() or 1
-    desc = (f"oracle port, N={P.N}: 1 precompute + {ns} hoisted rotations + {ns + 1} diagonal products (scaled to "
-            f"{ndiag - 1}/{ndiag}) + relin + rescale + 1 chebyshevCompare + 2 EvalSum steps (scaled to {nsum}); "
-            f"per-op s: rot {t_rot:.4f} mac {t_mac:.4f} relin+rescale {t_relin:.3f} compare {t_cmp:.3f}")
-    return total, desc, cores
+    ram = lambda g, d: base[(d * 7 + g) % ndist]
+    cp = CpuDiagPath(orc, threads)
+
+    def timed_step(load, blocks):
+        t0 = time.perf_counter()
+        cp.membership(q, load, blocks, ndiag)
+        cp.index(q, load, blocks, ndiag)
+        return time.perf_counter() - t0
+
+    # size the sample: the fixed part in full, as many blocks as the budget allows
+    t_one = timed_step(ram, [0])                          # also the first warm-up step (pages the library and the keys in)
+    sample_blocks, t_fixed = total_blocks, 0.0
+    if total_blocks > 1:
+        t0 = time.perf_counter()
+        dg = orc.fast_rotation_precompute(q)
+        list(cp.pool.map(lambda i: orc.fast_rotation(q, i, dg), range(1, ndiag)))
+        t_fixed = 2 * (time.perf_counter() - t0)
+        t_block = max(t_one - t_fixed, 1e-3)
+        per_step_budget = budget_s / max(1, steps + warmup)
+        sample_blocks = int(max(1, min(total_blocks, (per_step_budget - t_fixed) // t_block)))
+    blocks = list(range(sample_blocks))
+    scale = lambda t: t if sample_blocks == total_blocks else t_fixed + (t - t_fixed) * (total_blocks / sample_blocks)
+    vals = []
+    for i in range(max(0, warmup - 1) + steps):
+        t = timed_step(ram, blocks)
+        if i >= max(0, warmup - 1):
+            vals.append(scale(t))
+    # mode (i): database re-read from disk inside the timed region, one step
+    disk_s = None
+    try:
+        with tempfile.TemporaryDirectory(prefix="hx_cpu_db_") as td:
+            ddb = DiskDb(td)
+            for k, c in enumerate(base):
+                ddb.store(0, k, c)
+            disk_s = scale(timed_step(lambda g, d: ddb.load(0, (d * 7 + g) % ndist), blocks))
+    except OSError:
+        pass
+    cp.close()
+    desc = {"kind": "port", "cores": threads,
+            "sample": (f"oracle port (Python + C/OpenMP, oracle/cpu_path.py) of sender_diag.cpp:12-63, N={P.N}, {ndiag} diagonals: "
+                       + ("the whole path per step (2 x 511 hoisted rotations, 2 x 512 products, relinearise, rescale, compare, EvalSum)"
+                          if sample_blocks == total_blocks else
+                          f"2 x 511 hoisted rotations in full + {sample_blocks} of {total_blocks} blocks (512 products, 511 adds, relinearise, "
+                          f"rescale, compare each), block part scaled to {total_blocks}")
+                       + f"; database ciphertexts in RAM ({ndist} distinct, tiled)"),
+            "value_db_from_disk": disk_s, "blocks_run": sample_blocks}
+    return vals, desc
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the path. OpenFHE v1.2.3 is not buildable here
-    (un-vendored), so this is the oracle port on all host cores; rank 0 only."""
+    """--impl reference: the reference's CPU implementation of the path.  OpenFHE v1.2.3 is not buildable here (un-vendored,
+    DESIGN.md), so this is the oracle port on all host cores; rank 0 only."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
-    nsteps = max(1, min(args.steps, 3))
-    vals = []
-    for i in range(args.warmup + nsteps):
-        v, desc, cores = cpu_port_latency(args.ring_dim, args.ndiag, args.blocks_per_gpu * args.gpus, n_rot_sample=48)
-        if i >= args.warmup:
-            vals.append(v)
-        if i == 0 and args.warmup > 1:
-            args.warmup = 1   # one untimed pass is enough to page the library in; keeps the run to minutes
+    vals, desc = cpu_arm(args, args.total_blocks, args.steps, args.warmup, args.cpu_budget_s)
     v = float(np.mean(vals))
+    n_total = args.total_blocks * slots_of(args)
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": len(vals),
-            "warmup": args.warmup, "ms_per_step": v * 1e3, "higher_is_better": False, "scaling": "weak", "vs_baseline": vs_published(args, v),
-            "dtype": "u64", "data": "synthetic", "config": workload_config(args),
-            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
+            "warmup": args.warmup, "ms_per_step": v * 1e3, "higher_is_better": False, "scaling": "strong" if args.gpus > 1 else "weak",
+            "vs_baseline": vs_published(args, v), "dtype": "u64", "data": "synthetic", "config": workload_config(args),
+            "vectors_per_s": n_total / v,
+            "cpu_baseline": dict(desc, value=v, unit=UNIT),
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line))
+    print(json.dumps(line), flush=True)
 
 
-def workload_config(args):
-    blocks = args.blocks_per_gpu * args.gpus
-    return {"workload": f"HyDia approach 5, membership + index scenarios, synthetic DB of {blocks * 16384 if not args.ring_dim else blocks * args.ring_dim // 2} "
-                        f"vectors x 512 dims ({args.blocks_per_gpu} block(s) of {args.ndiag} diagonal ciphertexts per GPU)"
-                        + (" = BASELINE configs[1]" if blocks == 1 and not args.ring_dim and args.ndiag == 512 else "")
-                        + (" = BASELINE configs[4]" if blocks == 64 and not args.ring_dim and args.ndiag == 512 else ""),
-            "approach": 5, "ring_dim": args.ring_dim or 32768, "limbs": "12+4", "blocks_per_gpu": args.blocks_per_gpu,
-            "ndiag": args.ndiag, "l2_policy": "inputs larger than L2: each step streams 13.3 GB of rotation keys and "
-            "3.2 GB of database per block (L2 = 126 MB)"}
+# ---------------------------------------------------------------------------------------------------- B200 arm
+def stamped(path, stamp):
+    """A committed profile summary (profiles/*.json) counts only while it was captured from the kernels this library holds."""
+    try:
+        d = json.load(open(path))
+    except Exception:
+        return None
+    return d if d.get("kernel_stamp") == stamp else None
 
 
 def run_b200(args):
@@ -194,33 +243,30 @@ def run_b200(args):
         os.environ.setdefault("TORCH_NCCL_HIGH_PRIORITY", "1")   # the collectives' kernels must not queue behind the low-priority rotation lanes
         dist.init_process_group("nccl", device_id=dev)
 
-    bpg, ndiag = args.blocks_per_gpu, args.ndiag
+    ndiag = args.ndiag
     cc = hx.CryptoContext.generate(depth=11, ring_dim=args.ring_dim, device=local)
-    if args.rot_chunk:
-        cc.set_option("rot_chunk", args.rot_chunk)
-    if args.rot_streams:
-        cc.set_option("rot_streams", args.rot_streams)
-    if args.rot_lane >= 0:
-        cc.set_option("rot_lane", args.rot_lane)
-    if args.ks_moddown_w >= 0:
-        cc.set_option("ks_moddown_w", args.ks_moddown_w)
+    for name, v in (("rot_chunk", args.rot_chunk or -1), ("rot_streams", args.rot_streams or -1), ("ks_moddown_w", args.ks_moddown_w),
+                    ("rot_lane", args.rot_lane)):
+        if v >= 0:
+            cc.set_option(name, v)
     slots = cc.GetBatchSize()
-    total_blocks = bpg * world
-    n_total = total_blocks * slots
     cl = hx.Client(cc, seed=1)                     # same seed on every rank: replicated key set
     cl.EvalMultKeyGen()
     cl.EvalSumKeyGen()
     cl.EvalRotateKeyGen(list(range(1, ndiag)))
-    # database: global block g lives on rank g // bpg as local block g % bpg; matches at rows 0 and n-1
-    for b in range(bpg):
-        g = rank * bpg + b
-        match = ([0] if g == 0 else []) + ([slots - 1] if g == total_blocks - 1 else [])
-        db = synth_db(slots, seed=100 + g, match_rows=match)
-        rows = hx.diagonal_pack(db, slots)
-        for d in range(ndiag):
-            cl.enroll_row(b, d, rows[d])
-        del db, rows
-    expected_index = sorted({0, n_total - 1})
+
+    def enroll(total_blocks):
+        """global block g lives on rank g // bpg as local block g % bpg; matches at rows 0 and n-1"""
+        bpg = total_blocks // world
+        for b in range(bpg):
+            g = rank * bpg + b
+            match = ([0] if g == 0 else []) + ([slots - 1] if g == total_blocks - 1 else [])
+            db = synth_db(slots, seed=100 + g, match_rows=match)
+            rows = hx.diagonal_pack(db, slots)
+            for d in range(ndiag):
+                cl.enroll_row(b, d, rows[d])
+            del db, rows
+        return sorted({0, total_blocks * slots - 1})
 
     # query: encrypted once on rank 0, kept in pinned host memory (what a Receiver sends)
     ct_words = 2 * cc.L * cc.N
@@ -234,14 +280,6 @@ def run_b200(args):
         dist.broadcast(q_dev, src=0)
         q_host.copy_(q_dev.cpu())
     res_words = 2 * cc.N
-    idx_host = torch.empty((total_blocks, res_words), dtype=torch.int64).pin_memory()
-    mem_host = torch.empty(res_words, dtype=torch.int64).pin_memory()
-
-    if world > 1:
-        from image_matching_b200.sharded import TorchTransport
-        snd = hx.ShardedDiagonalSender(cc, None, n_total, device=dev, transport=TorchTransport(cc, dev, async_exchange=not args.sync_exchange))
-    else:
-        snd = hx.DiagonalSender(cc, None, n_total)
 
     def upload_query_from_host():
         if world == 1:
@@ -253,15 +291,6 @@ def run_b200(args):
         torch.cuda.synchronize()
         return cc.upload_dev(q_dev.data_ptr(), 2, cc.L)
 
-    def step(q, to_host):
-        m = snd.membershipScenario([q])
-        idx = snd.indexScenario([q])
-        if to_host and rank == 0:
-            m.download_ptr(mem_host.data_ptr())
-            for i, c in enumerate(idx):
-                c.download_ptr(idx_host[i].data_ptr())
-        return m, idx
-
     def fence():
         cc.sync()
         torch.cuda.synchronize()
@@ -269,51 +298,100 @@ def run_b200(args):
             dist.barrier()
             torch.cuda.synchronize()
 
-    def timed(nsteps, e2e):
-        fence()
-        cc.timer_start()
-        out = None
-        for _ in range(nsteps):
-            q = upload_query_from_host() if e2e else q_res
-            out = step(q, e2e)
-            cc.sync()   # a step is one query's latency: the next query starts when this one's results are complete
-        cc.sync()
-        torch.cuda.synchronize()
-        ms = cc.timer_stop()
+    def measure(total_blocks, steps, warmup, profile):
+        """warm-up, then `steps` steps with the query resident in HBM and `steps` steps end to end (query from pinned host memory,
+        results back to host), each arm timed in two halves that alternate (value, e2e, value, e2e) so that neither arm owns the
+        warmer half of the run; device time from CUDA events on the engine stream with a host clock beside it"""
+        n_total = total_blocks * slots
         if world > 1:
-            t = torch.tensor([ms], dtype=torch.float64, device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms, out
+            from image_matching_b200.sharded import TorchTransport
+            kw = {"shard_rotations": bool(args.rot_shard)} if args.rot_shard >= 0 else {}
+            snd = hx.ShardedDiagonalSender(cc, None, n_total, device=dev, transport=TorchTransport(cc, dev, async_exchange=not args.sync_exchange), **kw)
+        else:
+            snd = hx.DiagonalSender(cc, None, n_total)
+        idx_host = torch.empty((total_blocks, res_words), dtype=torch.int64).pin_memory()
+        mem_host = torch.empty(res_words, dtype=torch.int64).pin_memory()
 
-    q_res = upload_query_from_host()
-    # warm-up; the first warm-up step runs with every kernel family timed to find the dominant one
-    cc.prof_reset()
-    cc.prof_enable(None)
-    step(q_res, False)
-    prof_all = cc.prof_read()
-    dominant = max(prof_all, key=lambda k: prof_all[k]["ms"])
-    cc.prof_enable([])
-    for _ in range(max(0, args.warmup - 1)):
-        step(q_res, False)
+        def step(q, to_host):
+            m = snd.membershipScenario([q])
+            idx = snd.indexScenario([q])
+            if to_host and rank == 0:
+                m.download_ptr(mem_host.data_ptr())
+                for i, c in enumerate(idx):
+                    c.download_ptr(idx_host[i].data_ptr())
+            return m, idx
 
+        def timed(nsteps, e2e):
+            fence()
+            t0 = time.perf_counter()
+            cc.timer_start()
+            out = None
+            for _ in range(nsteps):
+                q = upload_query_from_host() if e2e else q_res
+                out = step(q, e2e)
+                cc.sync()   # a step is one query's latency: the next query starts when this one's results are complete
+            cc.sync()
+            torch.cuda.synchronize()
+            ms = cc.timer_stop()
+            wall_ms = (time.perf_counter() - t0) * 1e3
+            if world > 1:
+                t = torch.tensor([ms, wall_ms], dtype=torch.float64, device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms, wall_ms = float(t[0].item()), float(t[1].item())
+            return ms, wall_ms, out
+
+        q_res = upload_query_from_host()
+        prof_all, dominant = {}, None
+        if profile:   # the first warm-up step runs with every kernel family timed to find the dominant one
+            cc.prof_reset()
+            cc.prof_enable(None)
+            step(q_res, False)
+            prof_all = cc.prof_read()
+            dominant = max(prof_all, key=lambda k: prof_all[k]["ms"])
+            cc.prof_enable([])
+        for _ in range(max(0, warmup - (1 if profile else 0))):
+            step(q_res, False)
+        cc.sync()
+        if profile:
+            cc.prof_reset()
+            cc.prof_enable([dominant])
+        l0 = cc.launches()
+        halves = [n for n in (steps // 2, steps - steps // 2) if n]
+        ms_v = ms_e = wall_v = wall_e = 0.0
+        launches = 0
+        out = None
+        for n in halves:
+            l0 = cc.launches()
+            a, b, out = timed(n, False)
+            ms_v += a; wall_v += b
+            launches += cc.launches() - l0
+            if profile:
+                cc.prof_enable([])      # the dominant family is timed in the value halves only
+            a, b, _ = timed(n, True)
+            ms_e += a; wall_e += b
+            if profile:
+                cc.prof_enable([dominant])
+        prof = cc.prof_read() if profile else {}
+        if profile:
+            cc.prof_enable([])
+        fence()
+        return {"sec": ms_v / steps / 1e3, "sec_e2e": ms_e / steps / 1e3, "wall_sec": wall_v / steps / 1e3, "wall_sec_e2e": wall_e / steps / 1e3,
+                "launches": launches, "prof": prof, "prof_all": prof_all, "dominant": dominant, "out": out, "n_total": n_total, "snd": snd}
+
+    expected_index = enroll(args.total_blocks)
     sampler = ClockSampler(local)
     sampler.start()
-    cc.prof_reset()
-    cc.prof_enable([dominant])
-    l0 = cc.launches()
-    ms_total, (m, idx) = timed(args.steps, False)
-    launches = cc.launches() - l0
-    prof = cc.prof_read()
-    cc.prof_enable([])
-    ms_e2e, _ = timed(args.steps, True)
+    r = measure(args.total_blocks, args.steps, args.warmup, profile=True)
     sampler.stop_flag = True
     sampler.join(timeout=2)
+    m, idx = r["out"]
 
     if args.ncu_range:
         fence()
         torch.cuda.cudart().cudaProfilerStart()
-        step(q_res, False)
+        qn = upload_query_from_host()
+        r["snd"].membershipScenario([qn])
+        r["snd"].indexScenario([qn])
         fence()
         torch.cuda.cudart().cudaProfilerStop()
 
@@ -325,10 +403,27 @@ def run_b200(args):
         ok = (got_idx == expected_index) and got_mem
         if not ok:
             print(f"bench.py: WRONG RESULT index={got_idx[:8]} (expected {expected_index}) membership={got_mem}", file=sys.stderr)
+    launches = r["launches"]
     if world > 1:
         lt = torch.tensor([launches], dtype=torch.int64, device=dev)
         dist.all_reduce(lt)
         launches = int(lt.item())
+
+    # --gpus 1: one GPU's share of configs[4] (8 blocks) as an extra measurement on the same context
+    share = None
+    if world == 1 and not args.no_share and not args.ring_dim and args.total_blocks == 1 and not args.ncu_range:
+        del m, idx
+        r["out"] = None
+        exp8 = enroll(8)
+        nshare = max(2, args.steps // 2)
+        r8 = measure(8, nshare, 2, profile=False)
+        m8, idx8 = r8["out"]
+        ok8 = (cl.decryptIndex(idx8) == exp8) and cl.decryptMembership(m8)
+        ok = ok and ok8
+        share = {"workload": "8 blocks (2^17 vectors) on one GPU = one GPU's database share of BASELINE configs[4]; the 511 hoisted rotations are "
+                             "computed in full here (at N > 1 they are sharded over the ranks)",
+                 "value": r8["sec"], "e2e": r8["sec_e2e"], "unit": UNIT, "steps": nshare, "results_ok": bool(ok8),
+                 "vectors_per_s": 8 * slots / r8["sec"]}
 
     if rank == 0:
         peaks = {}
@@ -338,38 +433,43 @@ def run_b200(args):
             pass
         peak = float(peaks.get("hbm_gbs", 0)) or 6500.0
         peak_src = "MEASURED_PEAKS.json hbm_gbs" if peaks.get("hbm_gbs") else "fallback 6500 GB/s (B200_PROFILING.md)"
+        dominant, prof, prof_all = r["dominant"], r["prof"], r["prof_all"]
         d = prof[dominant]
-        traffic = None
-        try:   # ncu --set full DRAM bytes per launch of this kernel family (captured once per change, see profiles/)
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json"))).get(dominant, {}).get("traffic_bytes_per_launch")
-        except Exception:
-            pass
+        stamp = cc.kernel_stamp()
+        tr = stamped(os.path.join(ROOT, "profiles", "r2_traffic.json"), stamp)
+        traffic = (tr or {}).get(dominant, {}).get("traffic_bytes_per_launch")
+        ls = stamped(os.path.join(ROOT, "profiles", "r2_launch_summary.json"), stamp)
         # a "launch" of a fused family is its group of kernels: P-limb kernel, ModDown middle (1 warp-task kernel, or 2 with
         # --ks-moddown-w 0), Q-limb kernel once for the FP64 limbs and once for the 60-bit limb; 4 for ModUp and rescale
         ks_group = 5 if args.ks_moddown_w == 0 else 4
         groups = max(1, d["launches"] // {"ks_hoisted": ks_group, "ks_fused": ks_group, "modup": 4, "rescale": 4}.get(dominant, 1))
         avg_ms = d["ms"] / groups
         achieved = (d["bytes"] / groups) / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
-        sec = ms_total / args.steps / 1e3
-        sec_e2e = ms_e2e / args.steps / 1e3
+        sec, sec_e2e = r["sec"], r["sec_e2e"]
         line = {"metric": METRIC, "value": sec, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": sec * 1e3, "higher_is_better": False, "scaling": "weak", "vs_baseline": vs_published(args, sec), "dtype": "u64",
-                "data": "synthetic", "config": workload_config(args),
+                "ms_per_step": sec * 1e3, "higher_is_better": False, "scaling": "strong" if world > 1 else "weak",
+                "vs_baseline": vs_published(args, sec), "dtype": "u64", "data": "synthetic", "config": workload_config(args),
+                "vectors_per_s": r["n_total"] / sec,
                 "e2e": {"value": sec_e2e, "unit": UNIT, "h2d_bytes_per_step": ct_words * 8,
-                        "d2h_bytes_per_step": (total_blocks + 1) * res_words * 8},
+                        "d2h_bytes_per_step": (args.total_blocks + 1) * res_words * 8, "host_clock_value": r["wall_sec_e2e"]},
+                "host_clock_value": r["wall_sec"],
                 "gpu_launches": launches, "clocks": sampler.result(), "results_ok": bool(ok),
                 "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": achieved / peak, "traffic": traffic, "algorithmic_bytes_per_launch": d["bytes"] / groups, "peak_source": peak_src,
-                             "launches": groups, "kernels": d["launches"], "avg_launch_ms": avg_ms, "share_of_step": d["ms"] / ms_total,
+                             "frac": achieved / peak, "traffic": traffic,
+                             "traffic_source": ("profiles/r2_traffic.json (ncu --set full, same kernel_stamp)" if traffic else
+                                                "null: no ncu capture committed for this library's kernel_stamp"),
+                             "algorithmic_bytes_per_launch": d["bytes"] / groups, "peak_source": peak_src,
+                             "launches": groups, "kernels": d["launches"], "avg_launch_ms": avg_ms, "share_of_step": d["ms"] / (sec * 1e3 * args.steps),
+                             "kernel_stamp": stamp,
                              "warmup_profile_ms": {k: round(v["ms"], 3) for k, v in prof_all.items() if v["launches"]},
-                             # the other kernel families of the step from the warm-up profile (each launch timed with events, so
-                             # small kernels read high): GB/s on their algorithmic bytes against the same peak
-                             "other_kernels": {k: {"algorithmic_gbs": round(v["bytes"] / (v["ms"] * 1e-3) / 1e9, 1),
-                                                   "frac": round(v["bytes"] / (v["ms"] * 1e-3) / 1e9 / peak, 3), "launches": v["launches"]}
-                                               for k, v in prof_all.items() if v["launches"] and v["ms"] > 0 and k != dominant}}}
+                             # the other kernel families: from the serialized ncu launch list of this library's kernels when one is
+                             # committed (profiles/r2_launch_summary.json); per-launch events in a warm-up step overstate small kernels
+                             "other_kernels": (ls or {}).get("families")}}
+        if share:
+            line["share_of_configs4"] = share
         if not args.no_cpu_baseline and world == 1:
-            v, desc, cores = cpu_port_latency(args.ring_dim, ndiag, total_blocks, n_rot_sample=96)
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
+            vals, desc = cpu_arm(args, args.total_blocks, 1, 1, 120.0)
+            line["cpu_baseline"] = dict(desc, value=float(np.mean(vals)), unit=UNIT)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

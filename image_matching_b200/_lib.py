@@ -20,6 +20,7 @@ SIGNATURES = {
     "hx_ctx_destroy": (None, [VP]),
     "hx_ctx_sync": (C.c_int, [VP]),
     "hx_ctx_launches": (C.c_uint64, [VP]),
+    "hx_kernel_stamp": (C.c_char_p, []),
     "hx_ctx_set_option": (C.c_int, [VP, C.c_char_p, C.c_int]),
     "hx_prof_kinds": (C.c_int, []),
     "hx_prof_name": (C.c_char_p, [C.c_int]),

@@ -64,6 +64,10 @@ void hx_ctx_destroy(hx_ctx* ctx) {
 }
 int hx_ctx_sync(hx_ctx* ctx) { HX_TRY_INT(need(ctx, "ctx"); ctx->eng->sync();) }
 uint64_t hx_ctx_launches(hx_ctx* ctx) { return ctx ? ctx->eng->launches : 0; }
+#ifndef HX_KERNEL_STAMP
+#define HX_KERNEL_STAMP "unstamped"
+#endif
+const char* hx_kernel_stamp(void) { return HX_KERNEL_STAMP; }
 // diagnosis: cross-stream reuse policies of the stream-ordered pool (bit 0 follow-event, bit 1 opportunistic, bit 2 internal dependencies)
 static void set_pool_reuse(int device, int value) {
     cudaMemPool_t pool;

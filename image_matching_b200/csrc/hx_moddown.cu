@@ -20,6 +20,9 @@
 #include "hx_ntt_tile.cuh"
 #include "hx_fpmod.cuh"
 
+#ifndef HX_MDW_MINB
+#define HX_MDW_MINB 3
+#endif
 namespace hx {
 
 template <int LOGN>
@@ -181,7 +184,7 @@ __device__ __forceinline__ void inv_top(V (&v)[16], const TW* __restrict__ tw, B
 // grid (2^B / 8 column tiles, nbatch) ; in: [nbatch][n_in][N] (K1's output: inverse row pass done, values in [0,4q));
 // out: [nbatch][n_out][N], forward column pass done, pass-internal words (lazy doubles on FP64 limbs, [0,8q) on 60-bit limbs)
 template <int LOGN>
-__global__ void __launch_bounds__(256, LOGN <= 15 ? 3 : 2) k_moddown_w(const __grid_constant__ DevTables T, const BaseConvTable* __restrict__ tab,
+__global__ void __launch_bounds__(256, LOGN <= 15 ? HX_MDW_MINB : 2) k_moddown_w(const __grid_constant__ DevTables T, const BaseConvTable* __restrict__ tab,
                                                                        const u64* in, size_t in_bs, u64* out, size_t out_bs) {
     using W = WGeo<LOGN>;
     pdl_wait();

@@ -90,6 +90,7 @@ class CryptoContext:
     def GetBatchSize(self) -> int: return self.N // 2
     def sync(self): check_int(self._lib.hx_ctx_sync(self._h))
     def launches(self) -> int: return int(self._lib.hx_ctx_launches(self._h))
+    def kernel_stamp(self) -> str: return self._lib.hx_kernel_stamp().decode()
     def set_option(self, name: str, value: int): check_int(self._lib.hx_ctx_set_option(self._h, name.encode(), int(value)))
 
     # ---- launch accounting / device timer (bench.py)

@@ -41,6 +41,9 @@ hx_ctx* hx_ctx_create(int N, int L, int K, int dnum, const uint64_t* q, const ui
 void hx_ctx_destroy(hx_ctx* ctx);
 int hx_ctx_sync(hx_ctx* ctx);                       /* wait for all queued device work */
 uint64_t hx_ctx_launches(hx_ctx* ctx);              /* kernels launched so far (bench accounting) */
+/* Hash of the kernel sources this library was built from (csrc Makefile): committed ncu summaries under profiles/ carry the stamp
+ * they were captured at, and bench.py ignores them when it differs. */
+const char* hx_kernel_stamp(void);
 /* Engine tuning / test switches: "rot_chunk" (hoisted rotations per key-switch batch), "rot_streams" (streams the
  * independent batches are issued on, default 2: the tail of one batch overlaps the head of the next),
  * "force_unfused" (1 = run the unfused reference kernels instead of the fused key-switch pipeline),

@@ -73,6 +73,8 @@ def lib():
         L.ref_baseconv.argtypes = [U64P, U64P, C.c_int, U64P, C.c_int, U64P, u64, U64P, U64P]
         L.ref_switch_modulus.argtypes = [U64P, U64P, u64, u64, u64]
         L.ref_tensor_acc.argtypes = [U64P, U64P, U64P, C.c_int, u64, U64P]
+        L.ref_set_threads.argtypes = [C.c_int]
+        L.ref_max_threads.restype = C.c_int
         _lib = L
     return _lib
 

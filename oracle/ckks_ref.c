@@ -18,9 +18,30 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 typedef uint64_t u64;
 typedef unsigned __int128 u128;
+
+/* OpenMP team size of the CALLING thread for the limb-parallel loops below.  The timed CPU arm (oracle/cpu_path.py) restates the
+ * reference's own parallel structure -- "#pragma omp parallel for num_threads(MAX_NUM_CORES)" over rotations / products / blocks
+ * (sender_diag.cpp:23,40,57,70) -- with one host thread per loop iteration, each of which runs these primitives single-threaded. */
+void ref_set_threads(int n) {
+#ifdef _OPENMP
+    omp_set_num_threads(n < 1 ? 1 : n);
+#else
+    (void)n;
+#endif
+}
+int ref_max_threads(void) {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
 
 /* ---------------------------------------------------------------- scalar number theory */
 

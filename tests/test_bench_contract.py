@@ -12,7 +12,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 @pytest.mark.timeout(600)
 def test_reference_arm_prints_one_contract_line():
-    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0", "--ring-dim", "4096"],
                        capture_output=True, text=True, timeout=550, cwd=ROOT)
     assert r.returncode == 0, r.stderr[-1500:]
     lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
@@ -22,5 +22,6 @@ def test_reference_arm_prints_one_contract_line():
     assert d["higher_is_better"] is False and d["n_gpus"] == 1 and d["steps"] == 1 and d["value"] > 0
     assert d["config"]["workload"].startswith("HyDia approach 5") and "model" not in d["config"]
     cb = d["cpu_baseline"]
-    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and "sample" in cb
+    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and "the whole path per step" in cb["sample"]
+    assert cb["value_db_from_disk"] is not None and d["vectors_per_s"] > 0
     assert d["e2e"] == {"value": d["value"], "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}

@@ -52,7 +52,9 @@ def parse():
     ap.add_argument("--rot-streams", type=int, default=0, help="override the number of streams the hoisted-rotation batches use")
     ap.add_argument("--ks-moddown-w", type=int, default=-1, help="override the engine's warp-task ModDown kernel (0 = the r1 launch sequence)")
     ap.add_argument("--rot-lane", type=int, default=-1, help="override the engine's rotation lane (0 = all work ordered on the engine stream)")
-    ap.add_argument("--rot-shard", type=int, default=-1, help="N > 1: 1 = hoisted rotations sharded over the ranks and all-gathered, 0 = every rank computes all of them")
+    ap.add_argument("--shard", default="diagonals", choices=["diagonals", "blocks"],
+                    help="N > 1: 'diagonals' = every rank holds its diagonal range of all blocks, computes only its rotations, partial sums "
+                         "reduce-scattered; 'blocks' = round 1 (whole blocks per rank, all rotations on every rank)")
     ap.add_argument("--sync-exchange", action="store_true", help="N > 1: host-synchronous result exchange (no overlap of the scenarios)")
     ap.add_argument("--ncu-range", action="store_true", help="run one extra step inside cudaProfilerStart/Stop (for ncu --profile-from-start off)")
     a = ap.parse_args()
@@ -90,7 +92,7 @@ def workload_config(args, total_blocks=None):
     return {"workload": f"HyDia approach 5, membership + index scenarios, synthetic DB of {tb * slots_of(args)} vectors x 512 dims "
                         f"({tb} block(s) of {args.ndiag} diagonal ciphertexts, {tb // args.gpus} per GPU){name}",
             "approach": 5, "ring_dim": args.ring_dim or 32768, "limbs": "12+4", "total_blocks": tb, "blocks_per_gpu": tb // args.gpus,
-            "ndiag": args.ndiag,
+            "ndiag": args.ndiag, "sharding": (args.shard if args.gpus > 1 else None),
             "scaling_note": "N = 1 runs configs[1] (1 block); every N >= 2 runs the same 64-block database (strong scaling)",
             "l2_policy": "inputs larger than L2: each step streams 13.3 GB of rotation keys and 3.2 GB of database per block (L2 = 126 MB)"}
 
@@ -253,18 +255,27 @@ def run_b200(args):
     cl = hx.Client(cc, seed=1)                     # same seed on every rank: replicated key set
     cl.EvalMultKeyGen()
     cl.EvalSumKeyGen()
-    cl.EvalRotateKeyGen(list(range(1, ndiag)))
+    by_diag = world > 1 and args.shard == "diagonals"
+    if by_diag:
+        from image_matching_b200.sharded import diag_range
+        d0, d1 = diag_range(rank, world, ndiag)
+        cc.set_option("db_diag0", d0)
+        cc.set_option("db_diag_count", d1 - d0)
+        cl.EvalRotateKeyGen(list(range(max(d0, 1), d1)))   # a rank needs the keys of its own rotations only
+    else:
+        d0, d1 = 0, ndiag
+        cl.EvalRotateKeyGen(list(range(1, ndiag)))
 
     def enroll(total_blocks):
-        """global block g lives on rank g // bpg as local block g % bpg; matches at rows 0 and n-1"""
+        """matches at rows 0 and n-1.  'blocks': global block g lives on rank g // bpg as local block g % bpg; 'diagonals': every
+        rank enrolls its diagonal range of every block under the global block id"""
         bpg = total_blocks // world
-        for b in range(bpg):
-            g = rank * bpg + b
+        for g in (range(total_blocks) if by_diag else range(rank * bpg, (rank + 1) * bpg)):
             match = ([0] if g == 0 else []) + ([slots - 1] if g == total_blocks - 1 else [])
             db = synth_db(slots, seed=100 + g, match_rows=match)
             rows = hx.diagonal_pack(db, slots)
-            for d in range(ndiag):
-                cl.enroll_row(b, d, rows[d])
+            for d in range(d0, d1):
+                cl.enroll_row(g if by_diag else g - rank * bpg, d, rows[d])
             del db, rows
         return sorted({0, total_blocks * slots - 1})
 
@@ -305,8 +316,8 @@ def run_b200(args):
         n_total = total_blocks * slots
         if world > 1:
             from image_matching_b200.sharded import TorchTransport
-            kw = {"shard_rotations": bool(args.rot_shard)} if args.rot_shard >= 0 else {}
-            snd = hx.ShardedDiagonalSender(cc, None, n_total, device=dev, transport=TorchTransport(cc, dev, async_exchange=not args.sync_exchange), **kw)
+            snd = hx.ShardedDiagonalSender(cc, None, n_total, device=dev, transport=TorchTransport(cc, dev, async_exchange=not args.sync_exchange),
+                                           shard=args.shard)
         else:
             snd = hx.DiagonalSender(cc, None, n_total)
         idx_host = torch.empty((total_blocks, res_words), dtype=torch.int64).pin_memory()

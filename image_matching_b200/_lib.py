@@ -21,6 +21,11 @@ SIGNATURES = {
     "hx_ctx_sync": (C.c_int, [VP]),
     "hx_ctx_launches": (C.c_uint64, [VP]),
     "hx_kernel_stamp": (C.c_char_p, []),
+    "hx_diag_mac_partial": (VP, [VP, VP, C.c_int, C.c_int, I32P, C.c_int]),
+    "hx_ct_fold_mod": (C.c_int, [VP]),
+    "hx_ct_alloc": (VP, [VP, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "hx_ct_device_view": (C.c_int, [VP, C.POINTER(C.c_void_p), U64P, I32P]),
+    "hx_stream_order": (C.c_int, [VP, VP, C.c_int]),
     "hx_ctx_set_option": (C.c_int, [VP, C.c_char_p, C.c_int]),
     "hx_prof_kinds": (C.c_int, []),
     "hx_prof_name": (C.c_char_p, [C.c_int]),

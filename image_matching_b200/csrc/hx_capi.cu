@@ -91,6 +91,11 @@ int hx_ctx_set_option(hx_ctx* ctx, const char* name, int value) {
         else if (n == "batch_blocks") ctx->eng->batch_blocks = value != 0;
         else if (n == "pdl") g_pdl = value != 0;
         else if (n == "ks_moddown_w") ctx->eng->ks_moddown_w = value != 0;
+        else if (n == "db_diag0" || n == "db_diag_count") {
+            if (ctx->eng->db_blocks()) throw std::runtime_error("hx_ctx_set_option: the resident diagonal range must be set before any database block is registered");
+            if (value < 0 || (n == "db_diag_count" && value < 1)) throw std::runtime_error("hx_ctx_set_option: bad diagonal range");
+            (n == "db_diag0" ? ctx->eng->db_diag0 : ctx->eng->db_diag_count) = value;
+        }
         else if (n == "pool_reuse") set_pool_reuse(ctx->eng->device, value);
         else throw std::runtime_error("hx_ctx_set_option: unknown option " + n);)
 }
@@ -261,6 +266,29 @@ int hx_score_diag(hx_ctx* ctx, hx_ct* query, int ndiag, hx_ct** out, int max_out
         for (size_t i = 0; i < s.size(); i++) out[i] = wrap(s[i]);
         return (int)s.size();
     } catch (const std::exception& e) { set_err(e); return -1; }
+}
+hx_ct* hx_diag_mac_partial(hx_ctx* ctx, hx_ct* query, int d0, int d1, const int* blocks, int nblocks) {
+    HX_TRY_PTR(need(ctx, "ctx"); need(query, "query"); need(blocks, "blocks");
+               return wrap(ctx->eng->diag_mac_partial(query->ct, d0, d1, std::vector<int>(blocks, blocks + nblocks)));)
+}
+int hx_ct_fold_mod(hx_ct* ct) { HX_TRY_INT(need(ct, "ct"); ct->ct->eng->fold_mod(ct->ct);) }
+hx_ct* hx_ct_alloc(hx_ctx* ctx, int ncomp, int nlimbs, int level, int noise_deg, int nbatch) {
+    HX_TRY_PTR(need(ctx, "ctx");
+               if (ncomp < 1 || ncomp > 3 || nlimbs < 1 || nlimbs > ctx->eng->L || nbatch < 1) throw std::runtime_error("hx_ct_alloc: bad shape");
+               return wrap(ctx->eng->alloc_like(ncomp, nlimbs, level, noise_deg, nbatch));)
+}
+int hx_ct_device_view(hx_ct* ct, void** dev_ptr, uint64_t* words, int* nbatch) {
+    HX_TRY_INT(need(ct, "ct");
+               if (dev_ptr) *dev_ptr = ct->ct->d;
+               if (words) *words = (uint64_t)ct->ct->nb * ct->ct->batch_stride();
+               if (nbatch) *nbatch = ct->ct->nb;)
+}
+int hx_stream_order(hx_ctx* ctx, void* stream, int engine_waits) {
+    HX_TRY_INT(need(ctx, "ctx");
+               Engine* e = ctx->eng.get();
+               Engine::Guard g(e);
+               if (engine_waits) order_streams((cudaStream_t)stream, e->st);
+               else order_streams(e->st, (cudaStream_t)stream);)
 }
 hx_ct* hx_membership(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sign_depth) {
     HX_TRY_PTR(need(ctx, "ctx"); need(query, "query"); return wrap(ctx->eng->membership(query->ct, ndiag, delta, sign_depth));)

@@ -156,7 +156,11 @@ public:
     Ct eval_sum(const Ct& a, int n);                        // EvalSum (sender_diag.cpp:47)
     Ct add_many(const std::vector<Ct>& v);                  // EvalAddManyInPlace (sender_diag.cpp:46)
     // hoisted rotations (sender_diag.cpp:22-26)
-    struct DbBlock { u64* d = nullptr; int ndiag = 0; };
+    struct DbBlock { u64* d = nullptr; int ndiag = 0; int diag0 = 0; };   // diagonals diag0 .. diag0 + ndiag - 1 are resident
+    // Diagonal range this context holds of EVERY database block (options "db_diag0" / "db_diag_count", set before registering):
+    // the multi-GPU sender shards the 512 diagonals over the ranks, each rank computing its own rotations and the partial
+    // sum over its diagonals for all blocks (sharded.py); a single GPU holds 0..511.
+    int db_diag0 = 0, db_diag_count = 512;
     struct Digits { u64* d = nullptr; int ndig = 0, nl = 0; bool fused = false;   // fused ModUp stores 30-bit-split words
                     Engine* eng = nullptr; std::shared_ptr<Engine> keep; ~Digits(); };
     std::shared_ptr<Digits> fast_rotation_precompute(const Ct& a);
@@ -175,7 +179,7 @@ public:
     void db_store_device(int block, int diag, const u64* dev_ct /*[2][L][N], plain residues, device*/);
     int db_blocks() const { return (int)db_.size(); }
     // rotations 0..ndiag-1 of the query (entry 0 = the query), hoisted and batched, as one [ndiag][2][L][N] buffer
-    struct RotSet { u64* rotq = nullptr; int ndiag = 0, nl = 0, level = 0, deg = 0; int slot = -1;
+    struct RotSet { u64* rotq = nullptr; int d0 = 0, ndiag = 0, nl = 0, level = 0, deg = 0; int slot = -1;   // rotations d0 .. d0 + ndiag - 1
                     Engine* eng = nullptr; std::shared_ptr<Engine> keep; ~RotSet(); };
     // The rotated-query buffers (ndiag ciphertexts, 3.2 GB at the reference's parameters) are written by the rotation lanes and
     // read by the diagonal MAC on the engine stream, and the NEXT query's rotations start while this one's MAC may still be queued.
@@ -187,7 +191,14 @@ public:
     std::vector<RotSlot> rot_slots_;
     int rot_slot_acquire(size_t words, cudaStream_t writer);   // returns the slot index; `writer` waits for the slot's last reader
     void rot_slot_release(int slot);                           // records the release event on the engine stream
-    std::shared_ptr<RotSet> rotate_hoisted_all(const Ct& query, int ndiag);   // sender_diag.cpp:20-26
+    std::shared_ptr<RotSet> rotate_hoisted_all(const Ct& query, int ndiag) { return rotate_hoisted_range(query, 0, ndiag); }   // sender_diag.cpp:20-26
+    std::shared_ptr<RotSet> rotate_hoisted_range(const Ct& query, int d0, int d1);   // rotations d0 .. d1 - 1 (rotation 0 = the query)
+    // sum over the rotation set's diagonals of rotQ[d] (x) DB[g][d] for the named blocks: ONE batched 3-component ciphertext
+    // [blocks][3][nl][N], not relinearised (sender_diag.cpp:70-77 restricted to a diagonal range)
+    Ct mac_rotset(const RotSet& rs, const std::vector<int>& blocks);
+    Ct diag_mac_partial(const Ct& query, int d0, int d1, const std::vector<int>& blocks);
+    void fold_mod(const Ct& a);   // in place: every word (an un-reduced sum of residues below 2^63) -> its residue mod q_limb
+    Ct alloc_like(int ncomp, int nl, int level, int deg, int nb) { Guard g(this); return new_ct(ncomp, nl, level, deg, nb); }
     Ct rotset_entry(const RotSet& rs, int i);                                 // one rotated query as a ciphertext (copy)
     // computeSimilarityMatrix (sender_diag.cpp:66-83) for the named blocks against one rotation set, as batches of <= 32
     std::vector<Ct> score_rotset(const RotSet& rs, const std::vector<int>& blocks);

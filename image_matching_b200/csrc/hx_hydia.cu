@@ -9,16 +9,18 @@ namespace hx {
 // DB ciphertext `diag` of block `block` (serial/db_diagonal/index{block*512+diag}.bin in the
 // reference, sender_diag.cpp:87): stored in Montgomery form for the lazy MAC.
 static u64* db_slot(Engine& e, std::map<int, Engine::DbBlock>& db, int block, int diag) {
-    const int kDiag = 512;
-    if (diag < 0 || diag >= kDiag) throw std::runtime_error("db_register: diagonal index out of range");
+    if (diag < e.db_diag0 || diag >= e.db_diag0 + e.db_diag_count)
+        throw std::runtime_error("db_register: diagonal index outside this context's resident range (options db_diag0 / db_diag_count)");
     Engine::DbBlock& b = db[block];
     size_t ct_words = (size_t)2 * e.L * e.N;
     if (!b.d) {
-        HX_CUDA(cudaMalloc(&b.d, sizeof(u64) * ct_words * kDiag));
-        HX_CUDA(cudaMemsetAsync(b.d, 0, sizeof(u64) * ct_words * kDiag, e.st));
-        b.ndiag = kDiag;
+        HX_CUDA(cudaMalloc(&b.d, sizeof(u64) * ct_words * e.db_diag_count));
+        HX_CUDA(cudaMemsetAsync(b.d, 0, sizeof(u64) * ct_words * e.db_diag_count, e.st));
+        b.ndiag = e.db_diag_count;
+        b.diag0 = e.db_diag0;
     }
-    return b.d + ct_words * diag;
+    if (b.diag0 != e.db_diag0 || b.ndiag != e.db_diag_count) throw std::runtime_error("db_register: the resident diagonal range changed after this block was created");
+    return b.d + ct_words * (diag - b.diag0);
 }
 static void db_finish(Engine& e, u64* dst) {
     std::vector<int> primes;
@@ -82,16 +84,17 @@ void Engine::rot_slot_release(int slot) {
     r.has_release = true;
     r.busy = false;
 }
-std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_all(const Ct& query, int ndiag) {
+std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_range(const Ct& query, int d0, int d1) {
     Guard g(this);
     if (query->ncomp != 2 || query->nl != L || query->nb != 1) throw std::runtime_error("score_diag: query must be a fresh 2-component ciphertext");
-    if (ndiag < 1) throw std::runtime_error("score_diag: ndiag must be positive");
+    if (d0 < 0 || d1 <= d0) throw std::runtime_error("score_diag: empty or negative rotation range");
+    const int ndiag = d1 - d0;
     const int nl = query->nl;
     const size_t ct_words = (size_t)2 * nl * N;
     auto rs = std::make_shared<RotSet>();
     rs->eng = this;
     rs->keep = weak_from_this().lock();
-    rs->ndiag = ndiag; rs->nl = nl; rs->level = query->level; rs->deg = query->deg;
+    rs->d0 = d0; rs->ndiag = ndiag; rs->nl = nl; rs->level = query->level; rs->deg = query->deg;
     const int chunk = std::max(1, std::min(rot_chunk, kMaxKsBatch));
     const int ns = rot_streams;
     cudaStream_t main_st = st;
@@ -116,7 +119,7 @@ std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_all(const Ct& query, int 
     try {
         rs->slot = rot_slot_acquire(ct_words * ndiag, st);
         u64* rotq = rs->rotq = rot_slots_[rs->slot].d;
-        HX_CUDA(cudaMemcpyAsync(rotq, query->d, sizeof(u64) * ct_words, cudaMemcpyDeviceToDevice, st));
+        if (d0 == 0) HX_CUDA(cudaMemcpyAsync(rotq, query->d, sizeof(u64) * ct_words, cudaMemcpyDeviceToDevice, st));   // rotation 0 (sender_diag.cpp:21)
         int ndig;
         digits = ks_precompute(query->comp(1), nl, &ndig);
         ks_kind = PK_KS_HOISTED;
@@ -141,17 +144,17 @@ std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_all(const Ct& query, int 
             for (int s = 0; s < ns - 1; s++) HX_CUDA(cudaStreamWaitEvent(others[s], evs[3], 0));
         }
         int turn = 0;
-        for (int d0 = 1; d0 < ndiag; d0 += chunk, turn++) {
-            int d1 = std::min(ndiag, d0 + chunk);
+        for (int b0 = std::max(d0, 1); b0 < d1; b0 += chunk, turn++) {
+            int b1 = std::min(d1, b0 + chunk);
             st = (ns > 1 && turn % ns) ? others[turn % ns - 1] : first;
             std::vector<const EvalKey*> keys;
             std::vector<u64> gal;
-            for (int d = d0; d < d1; d++) {
+            for (int d = b0; d < b1; d++) {
                 u64 k = galois_for_rotation(d);
                 keys.push_back(&rot_key(k));
                 gal.push_back(k);
             }
-            ks_core_batch(digits, ndig, nl, keys, query->comp(0), 1, gal, rotq + ct_words * d0, ct_words);
+            ks_core_batch(digits, ndig, nl, keys, query->comp(0), 1, gal, rotq + ct_words * (b0 - d0), ct_words);
         }
     } catch (...) {
         prof_no_events = false;
@@ -202,30 +205,53 @@ Ct Engine::db_entry(int block, int diag) {
     launch_to_mont(T, c->d, 2 * L, limb_map(primes), st, true);
     return c;
 }
-std::vector<Ct> Engine::score_rotset(const RotSet& rs, const std::vector<int>& block_ids) {
+// database pointers of the named blocks at the rotation set's first diagonal
+static std::vector<const u64*> db_ptrs_for(const Engine& e, const std::map<int, Engine::DbBlock>& db, const Engine::RotSet& rs, const std::vector<int>& block_ids) {
+    std::vector<const u64*> blocks;
+    const size_t ct_words = (size_t)2 * e.L * e.N;
+    for (int id : block_ids) {
+        auto it = db.find(id);
+        if (it == db.end()) throw std::runtime_error("score_diag: database block not registered");
+        const Engine::DbBlock& b = it->second;
+        if (rs.d0 < b.diag0 || rs.d0 + rs.ndiag > b.diag0 + b.ndiag) throw std::runtime_error("score_diag: database block does not hold every diagonal of the rotation set");
+        blocks.push_back(b.d + ct_words * (rs.d0 - b.diag0));
+    }
+    return blocks;
+}
+Ct Engine::mac_rotset(const RotSet& rs, const std::vector<int>& block_ids) {
     Guard g(this);
     const int nl = rs.nl, ndiag = rs.ndiag;
-    const u64* rotq = rs.rotq;
+    std::vector<const u64*> blocks = db_ptrs_for(*this, db_, rs, block_ids);
+    if (blocks.empty()) throw std::runtime_error("score_diag: no database block named");
+    Ct acc = new_ct(3, nl, rs.level, rs.deg + 1, (int)blocks.size());
+    for (size_t g0 = 0; g0 < blocks.size(); g0 += kMaxDbBlocks) {   // the rotated query is fetched from HBM once per launch
+        const int n = (int)std::min((size_t)kMaxDbBlocks, blocks.size() - g0);
+        DbBlockPtrs ptrs;
+        for (int i = 0; i < n; i++) ptrs.p[i] = blocks[g0 + i];
+        Scope sc(this, PK_DIAG_MAC, 1, 8.0 * N * nl * 2 * ndiag * n);   // algorithmic bytes: the database diagonals, read once
+        launch_diag_mac(T, rs.rotq, ptrs, n, acc->d + g0 * acc->batch_stride(), ndiag, nl, st);
+    }
+    return acc;
+}
+Ct Engine::diag_mac_partial(const Ct& query, int d0, int d1, const std::vector<int>& block_ids) {
+    Guard g(this);
+    std::shared_ptr<RotSet> rs = rotate_hoisted_range(query, d0, d1);
+    return mac_rotset(*rs, block_ids);
+}
+void Engine::fold_mod(const Ct& a) {
+    Guard g(this);
+    Scope sc(this, PK_EW, 1, 16.0 * N * a->nl * a->comps_total());
+    launch_fold_mod(T, a->d, a->nl, a->comps_total(), st);
+}
+std::vector<Ct> Engine::score_rotset(const RotSet& rs, const std::vector<int>& block_ids) {
+    Guard g(this);
     // all blocks of this GPU in one launch each: diagonal MAC (the rotated query is fetched from HBM once
     // for all of them), relinearisation and rescale on the batch [G][3][nl][N]
-    std::vector<const u64*> blocks;
-    for (int id : block_ids) {
-        auto it = db_.find(id);
-        if (it == db_.end()) throw std::runtime_error("score_diag: database block not registered");
-        if (it->second.ndiag < ndiag) throw std::runtime_error("score_diag: database block has fewer diagonals than requested");
-        blocks.push_back(it->second.d);
-    }
     std::vector<Ct> parts;
     const int group = (batch_blocks && !force_unfused && fused_ks_supported(logN)) ? std::min(kMaxKsBatch, kMaxDbBlocks) : 1;
-    for (size_t g0 = 0; g0 < blocks.size(); g0 += group) {
-        const int g = (int)std::min((size_t)group, blocks.size() - g0);
-        DbBlockPtrs ptrs;
-        for (int i = 0; i < g; i++) ptrs.p[i] = blocks[g0 + i];
-        Ct acc = new_ct(3, nl, rs.level, rs.deg + 1, g);
-        {   // algorithmic bytes: the database blocks, read once; rotq is shared by the launch
-            Scope sc(this, PK_DIAG_MAC, 1, 8.0 * N * nl * 2 * ndiag * g);
-            launch_diag_mac(T, rotq, ptrs, g, acc->d, ndiag, nl, st);
-        }
+    for (size_t g0 = 0; g0 < block_ids.size(); g0 += group) {
+        const size_t n = std::min((size_t)group, block_ids.size() - g0);
+        Ct acc = mac_rotset(rs, std::vector<int>(block_ids.begin() + g0, block_ids.begin() + g0 + n));
         parts.push_back(rescale(relinearize(acc)));
     }
     return parts;

@@ -315,6 +315,22 @@ void launch_batch_sum(const DevTables& T, u64* acc, const u64* in, int nl, int n
     launch_pdl(k_batch_sum, grid, dim3(kThreads), 0, st, T, acc, in, nl, (size_t)ncomp * nl * T.N, nbatch, accumulate);
 }
 
+// multi-GPU combine (sharded.py): the ranks' partial sums are added as plain 64-bit integers by the collective; this brings
+// them back to residues
+__global__ void __launch_bounds__(kThreads) k_fold_mod(DevTables T, u64* __restrict__ data, int nl) {
+    pdl_wait();
+    int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    const PrimeConst pc = T.pc[blockIdx.y % nl];
+    u64* p = data + (size_t)blockIdx.y * T.N + idx;
+    ulonglong2 x = ldg128(p);
+    x.x = reduce64(x.x, pc.q, pc.mu64);
+    x.y = reduce64(x.y, pc.q, pc.mu64);
+    st128(p, x);
+}
+void launch_fold_mod(const DevTables& T, u64* data, int nl, int ncomps, cudaStream_t st) {
+    launch_pdl(k_fold_mod, dim3(blocks_for(T.N), nl * ncomps, 1), dim3(kThreads), 0, st, T, data, nl);
+}
 // AutomorphismTransform (row P3): out[l][j] = in[l][map[j]].
 __global__ void __launch_bounds__(kThreads) k_automorph(int N, u64* __restrict__ out, const u64* __restrict__ in, const u32* __restrict__ map) {
     int idx = blockIdx.x * blockDim.x + threadIdx.x;

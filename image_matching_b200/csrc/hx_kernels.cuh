@@ -130,6 +130,8 @@ void launch_tensor_db(const DevTables& T, u64* out, const CtPtrs& a, size_t cs_a
 // acc[c][i][n] (+)= sum_z in[z][c][i][n] mod q_i over the nbatch entries of a batched ciphertext; ncl = ncomp*nl limbs
 // per entry, limb y has prime index y % nl.  accumulate = 0 overwrites acc.
 void launch_batch_sum(const DevTables& T, u64* acc, const u64* in, int nl, int ncomp, int nbatch, int accumulate, cudaStream_t st);
+// in place x -> x mod q_limb for un-reduced 64-bit sums; data [ncomps][nl][N]
+void launch_fold_mod(const DevTables& T, u64* data, int nl, int ncomps, cudaStream_t st);
 void launch_automorph(const DevTables& T, u64* out, const u64* in, const u32* map, int nlimbs_total, cudaStream_t st);
 void launch_automap(int N, int logN, u64 k, u32* map, cudaStream_t st);
 // Launch with programmatic stream serialization (the kernel's first statement must be pdl_wait()): hides the launch and

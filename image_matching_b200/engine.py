@@ -230,6 +230,21 @@ class CryptoContext:
             return [self._ct(out[i]) for i in range(len(b))], [self._ct(self._lib.hx_rotset_get(rs, int(r))) for r in rotations]
         finally:
             self._lib.hx_rotset_free(rs)
+    # ---- multi-GPU building blocks (sharded.py): diagonal-sharded partial sums, in-place collective access to ciphertext storage
+    def diag_mac_partial(self, query: Ciphertext, d0: int, d1: int, blocks: Sequence[int]) -> Ciphertext:
+        """Rotations d0..d1-1 of the query and sum over those diagonals of rotQ[d] (x) DB[g][d] for every named block: one batched
+        3-component ciphertext [len(blocks)][3][L][N], not relinearised (hx_diag_mac_partial)."""
+        b = np.array(list(blocks), dtype=np.int32)
+        return self._ct(self._lib.hx_diag_mac_partial(self._h, query._h, int(d0), int(d1), b.ctypes.data_as(_lib.I32P), len(b)))
+    def alloc(self, ncomp: int, nl: int, level: int, deg: int, nbatch: int = 1) -> Ciphertext:
+        return self._ct(self._lib.hx_ct_alloc(self._h, ncomp, nl, level, deg, nbatch))
+    def fold_mod(self, ct: Ciphertext): check_int(self._lib.hx_ct_fold_mod(ct._h))
+    def device_view(self, ct: Ciphertext):
+        """(device pointer, 64-bit words, batch entries) of a ciphertext's storage (hx_ct_device_view)."""
+        ptr, words, nb = C.c_void_p(), C.c_uint64(), C.c_int()
+        check_int(self._lib.hx_ct_device_view(ct._h, C.byref(ptr), C.byref(words), C.byref(nb)))
+        return int(ptr.value), int(words.value), int(nb.value)
+    def stream_order(self, stream: int, engine_waits: bool): check_int(self._lib.hx_stream_order(self._h, C.c_void_p(stream), 1 if engine_waits else 0))
     def stack(self, cts: Sequence[Ciphertext]) -> Ciphertext:
         """n ciphertexts of one shape -> one batched handle (hx_ct_stack); every Eval* call then works on all entries at once."""
         n = len(cts)

@@ -1,16 +1,26 @@
-"""Multi-GPU HyDia Sender: database blocks sharded over ranks, evaluation keys replicated, only the
-per-block result ciphertexts combined.  One process per GPU over torch.distributed
-(NCCL over NVLink on the GPU box; gloo in the CPU tests).
+"""Multi-GPU HyDia Sender.  One process per GPU over torch.distributed (NCCL over NVLink on the GPU box;
+gloo in the CPU tests).  Evaluation keys are generated from one seed on every rank.
 
-The reference loops over blocks serially in one process (/root/reference/src/sender/sender_diag.cpp:28-30)
-and runs the compare in an OpenMP loop over blocks (:40-43, :57-60); here rank r owns the contiguous
-global blocks [r*B, (r+1)*B) so a decoded index stays j + g*slots (receiver_hers.cpp:46-49).
+Two shardings of /root/reference/src/sender/sender_diag.cpp's work, same results bit for bit:
 
-Exchange steps (the only data-path collectives):
-  indexScenario      gather of the G result ciphertexts (2 x 1 limb each) to rank 0
-  membershipScenario local EvalAddMany, then SUM-reduce of the residues as int64 (world * q0 < 2^63),
-                     one mod-q0 fold, and EvalSum on rank 0.  Modular addition is associative, so the
-                     result is bit-identical to the reference's EvalAddManyInPlace tree over all G blocks.
+shard = "diagonals" (default on GPUs, round 2)
+  The 512 diagonals of EVERY block are split over the ranks.  Rank r holds DB[g][d] for its diagonals d only, computes only ITS
+  hoisted rotations (sender_diag.cpp:20-26 restricted to d0 <= i < d1: 64 instead of 511 at 8 ranks) and the partial sums
+  sum_{d0 <= d < d1} rotQ[d] (x) DB[g][d] for all G blocks (:70-77).  The ONE data-path exchange is a reduce-scatter of those
+  un-relinearised accumulators as raw 64-bit words (world * q < 2^63), 9.4 MB per block; one fold brings the words back to
+  residues.  Modular addition is associative and commutative, so the block's accumulator equals the single-GPU sum over 512
+  diagonals exactly.  Each rank then relinearises, rescales and compares its contiguous share of the blocks (:79-80, :40-43).
+  Round 1 replicated the 511 rotations on every rank (18.6 of 55 ms at 8 GPUs); all-gathering sharded rotations would move
+  3.2 GB into every GPU per scenario, the partial sums are 0.6 GB in total.
+
+shard = "blocks" (round 1; kept for comparison and for databases enrolled block-wise)
+  Rank r owns whole blocks [r*B, (r+1)*B) and every rank computes all rotations.
+
+Result exchange (both shardings):
+  indexScenario      gather of the G result ciphertexts (2 x 1 limb each) to rank 0 in global block order, so a decoded index
+                     stays j + g*slots (receiver_hers.cpp:46-49)
+  membershipScenario local EvalAddMany, SUM-reduce of the residues as int64, one mod-q0 fold, EvalSum on rank 0 -- bit-identical
+                     to the reference's EvalAddManyInPlace tree over all G blocks.
 """
 from __future__ import annotations
 
@@ -20,6 +30,11 @@ import numpy as np
 
 from .config import COMP_DEPTH, MATCH_THRESHOLD, VECTOR_DIM
 from .sender import Sender
+
+
+def diag_range(rank: int, world: int, ndiag: int = VECTOR_DIM):
+    """Contiguous diagonal partition (same rule as block_range)."""
+    return block_range(rank, world, ndiag)
 
 
 def block_range(rank: int, world: int, total_blocks: int):
@@ -58,6 +73,42 @@ class TorchTransport:
             outer.wait_stream(hs)
         return ctx()
 
+    class _View:
+        """CUDA array interface over a ciphertext's device storage: torch wraps it without a copy."""
+
+        def __init__(self, ptr, words):
+            self.__cuda_array_interface__ = {"shape": (words,), "typestr": "<i8", "data": (ptr, False), "version": 3, "strides": None}
+
+    def view(self, ct):
+        """int64 tensor [batch entries][words per entry] aliasing the ciphertext's storage (no copy).  The caller orders the
+        streams (engine_to_exchange before reading, exchange_to_engine after writing)."""
+        ptr, words, nb = self.cc.device_view(ct)
+        return self.torch.as_tensor(self._View(ptr, words), device=self.device).view(nb, words // nb)
+
+    def engine_to_exchange(self):
+        """torch's current stream waits for everything queued on the engine stream."""
+        self.cc.stream_order(int(self.torch.cuda.current_stream(self.device).cuda_stream), engine_waits=False)
+
+    def exchange_to_engine(self):
+        """the engine stream waits for everything queued on torch's current stream."""
+        self.cc.stream_order(int(self.torch.cuda.current_stream(self.device).cuda_stream), engine_waits=True)
+
+    def reduce_scatter_blocks(self, dist, group, acc, lo, hi, total, world):
+        """acc: this rank's partial sums [total][3][L][N].  Returns this rank's blocks lo..hi-1 summed over the ranks as raw 64-bit
+        words (a new batched ciphertext; hx_ct_fold_mod still to be applied).  reduce_scatter when the blocks split evenly,
+        all_reduce + slice otherwise."""
+        ncomp, nl, level, deg = acc.info()
+        out = self.cc.alloc(ncomp, nl, level, deg, hi - lo)
+        self.engine_to_exchange()
+        src, dst = self.view(acc), self.view(out)
+        if total % world == 0:
+            dist.reduce_scatter_tensor(dst, src, op=dist.ReduceOp.SUM, group=group)
+        else:
+            dist.all_reduce(src, op=dist.ReduceOp.SUM, group=group)
+            dst.copy_(src[lo:hi])
+        self.exchange_to_engine()
+        return out, acc   # acc must outlive the collective: the caller drops it after the engine stream has joined
+
     def to_tensor(self, ct):
         ncomp, nl, _, _ = ct.info()
         t = self.torch.empty((ncomp, nl, self.cc.N), dtype=self.torch.int64, device=self.device)
@@ -79,22 +130,42 @@ class ShardedDiagonalSender(Sender):
     """DiagonalSender over `world` ranks. `cc` is this rank's context holding its local blocks
     (registered as local block ids 0..B-1) and the full (replicated) key set."""
 
-    def __init__(self, cc, pk, numVectors: int, group=None, transport=None, device=None):
+    def __init__(self, cc, pk, numVectors: int, group=None, transport=None, device=None, shard: str = None):
         super().__init__(cc, pk, numVectors)
         import torch.distributed as dist
         self.dist, self.group = dist, group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         self.transport = transport or TorchTransport(cc, device)
+        # "diagonals" needs a transport that can run the reduce-scatter on ciphertext storage and a context whose database holds
+        # this rank's diagonal range of every block (enroll with diag_range); "blocks" is the round-1 sharding
+        self.shard = shard or ("diagonals" if hasattr(self.transport, "reduce_scatter_blocks") else "blocks")
+        if self.shard not in ("diagonals", "blocks"):
+            raise ValueError("shard must be 'diagonals' or 'blocks'")
         # membershipScenario SUM-reduces residues as int64: the un-reduced sum of `world` residues must stay below 2^63
         if self.world * max(int(m) for m in cc.q) >= 1 << 63:
             raise ValueError(f"ShardedDiagonalSender: world size {self.world} x max modulus exceeds the int64 range of the membership reduce")
 
-    # -- per-rank compute: identical to the single-GPU fused path on the local blocks
+    # -- per-rank compute
     def computeSimilarity(self, queryCipher):
-        return self.cc.score_diag(queryCipher[0], VECTOR_DIM)
+        """Scores of THIS rank's blocks (global blocks block_range(rank)), as one batched ciphertext in "diagonals" mode."""
+        cc = self.cc
+        if self.shard == "blocks":
+            return cc.score_diag(queryCipher[0], VECTOR_DIM)
+        total = self._total_blocks()
+        d0, d1 = diag_range(self.rank, self.world)
+        lo, hi = block_range(self.rank, self.world, total)
+        acc = cc.diag_mac_partial(queryCipher[0], d0, d1, range(total))       # [total][3][L][N]: partial sums over my diagonals
+        with _exchange(self.transport):
+            mine, keep = self.transport.reduce_scatter_blocks(self.dist, self.group, acc, lo, hi, total, self.world)
+        cc.fold_mod(mine)                                                     # raw sums of `world` residues -> residues
+        del keep, acc                                                         # freed in engine-stream order, behind the join
+        return cc.Rescale(cc.Relinearize(mine))                               # sender_diag.cpp:79-80 on my blocks, batched
 
     def _local_index(self, queryCipher):
-        return self.cc.index(queryCipher[0], VECTOR_DIM, MATCH_THRESHOLD, COMP_DEPTH)
+        if self.shard == "blocks":
+            return self.cc.index(queryCipher[0], VECTOR_DIM, MATCH_THRESHOLD, COMP_DEPTH)
+        cc = self.cc
+        return cc.unstack(cc.compare(self.computeSimilarity(queryCipher), MATCH_THRESHOLD, COMP_DEPTH))
 
     def indexScenario(self, queryCipher) -> Optional[List]:
         """Rank 0 returns the G result ciphertexts in global block order; other ranks return None."""

@@ -129,6 +129,20 @@ hx_ct* hx_membership(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sig
 /* DiagonalSender::indexScenario (sender_diag.cpp:52) */
 int hx_index(hx_ctx* ctx, hx_ct* query, int ndiag, double delta, int sign_depth, hx_ct** out, int max_out);
 
+/* Multi-GPU building blocks (image_matching_b200/sharded.py).  The 512 diagonals of EVERY block are sharded over
+ * the ranks (context options "db_diag0" / "db_diag_count", set before registering): a rank computes only its own hoisted rotations
+ * (sender_diag.cpp:20-26 restricted to d0 <= i < d1) and the partial sum over its diagonals of rotQ[i] (x) DB[g][i] for all blocks
+ * (sender_diag.cpp:70-77), one batched 3-component ciphertext [nblocks][3][L][N].  The ranks' partial sums are added by a
+ * reduce-scatter on the raw 64-bit words (world * q < 2^63), hx_ct_fold_mod brings the words back to residues, and
+ * hx_relin / hx_rescale / hx_compare run on each rank's share of the blocks.  Modular addition is associative, so the result is
+ * bit-identical to the single-GPU sum.  hx_ct_alloc / hx_ct_device_view / hx_stream_order let the collective read and write
+ * ciphertext storage in place on a caller-owned stream (engine_waits = 0: `stream` waits for the engine stream; 1: the reverse). */
+hx_ct* hx_diag_mac_partial(hx_ctx* ctx, hx_ct* query, int d0, int d1, const int* blocks, int nblocks);
+int hx_ct_fold_mod(hx_ct* ct);
+hx_ct* hx_ct_alloc(hx_ctx* ctx, int ncomp, int nlimbs, int level, int noise_deg, int nbatch);
+int hx_ct_device_view(hx_ct* ct, void** dev_ptr, uint64_t* words, int* nbatch);
+int hx_stream_order(hx_ctx* ctx, void* stream, int engine_waits);
+
 /* The same path in two steps, for callers that hold the database as ciphertext handles and score blocks one at a time
  * (the deferred-execution layer of shim/openfhe.h): hx_rot_fast_all = sender_diag.cpp:20-26 (rotations 0..ndiag-1 of the
  * query, hoisted, batched; entry 0 is the query), hx_score_blocks = computeSimilarityMatrix (sender_diag.cpp:66-83) for the

@@ -328,8 +328,7 @@ def run_b200(args):
             idx = snd.indexScenario([q])
             if to_host and rank == 0:
                 m.download_ptr(mem_host.data_ptr())
-                for i, c in enumerate(idx):
-                    c.download_ptr(idx_host[i].data_ptr())
+                cc.download_many_ptr(idx, idx_host.data_ptr())
             return m, idx
 
         def timed(nsteps, e2e):

@@ -190,6 +190,23 @@ int hx_ct_download(hx_ct* ct, uint64_t* data) {
                if (ct->ct->nb != 1) throw std::runtime_error("hx_ct_download: batched ciphertext (hx_ct_unstack it first)");
                ct->ct->eng->download(ct->ct, (u64*)data);)
 }
+int hx_ct_download_many(hx_ct* const* cts, int n, uint64_t* data) {
+    HX_TRY_INT(need(cts, "cts"); need(data, "data");
+               if (n < 1) throw std::runtime_error("hx_ct_download_many: empty input");
+               need(cts[0], "cts[0]");
+               Engine* e = cts[0]->ct->eng;
+               Engine::Guard g(e);
+               size_t off = 0;
+               for (int i = 0; i < n; i++) {
+                   need(cts[i], "cts[i]");
+                   const CtObj& c = *cts[i]->ct;
+                   if (c.eng != e) throw std::runtime_error("hx_ct_download_many: ciphertexts of different contexts");
+                   const size_t words = (size_t)c.nb * c.ncomp * c.nl * e->N;
+                   HX_CUDA(cudaMemcpyAsync(data + off, c.d, sizeof(u64) * words, cudaMemcpyDeviceToHost, e->st));
+                   off += words;
+               }
+               e->sync();)
+}
 int hx_ct_info(hx_ct* ct, int* ncomp, int* nlimbs, int* level, int* noise_deg) {
     HX_TRY_INT(
         need(ct, "ct");

@@ -231,6 +231,10 @@ class CryptoContext:
         finally:
             self._lib.hx_rotset_free(rs)
     # ---- multi-GPU building blocks (sharded.py): diagonal-sharded partial sums, in-place collective access to ciphertext storage
+    def download_many_ptr(self, cts: Sequence[Ciphertext], host_ptr: int):
+        """Results back to back into one (pinned) host buffer with a single synchronisation (hx_ct_download_many)."""
+        arr = (VP * len(cts))(*[c._h for c in cts])
+        check_int(self._lib.hx_ct_download_many(arr, len(cts), C.c_void_p(host_ptr)))
     def diag_mac_partial(self, query: Ciphertext, d0: int, d1: int, blocks: Sequence[int]) -> Ciphertext:
         """Rotations d0..d1-1 of the query and sum over those diagonals of rotQ[d] (x) DB[g][d] for every named block: one batched
         3-component ciphertext [len(blocks)][3][L][N], not relinearised (hx_diag_mac_partial)."""

@@ -88,6 +88,8 @@ int hx_ct_download_dev_async(hx_ct* ct, void* dev_data, void* stream);
 hx_ct* hx_ct_upload_dev_async(hx_ctx* ctx, int ncomp, int nlimbs, const void* dev_data, int level, int noise_deg, void* stream);
 int hx_ct_info(hx_ct* ct, int* ncomp, int* nlimbs, int* level, int* noise_deg);
 hx_ct* hx_ct_clone(hx_ct* ct);
+/* n ciphertexts back to back into one host buffer, one synchronisation (the G result ciphertexts of indexScenario) */
+int hx_ct_download_many(hx_ct* const* cts, int n, uint64_t* data);
 void hx_ct_free(hx_ct* ct);
 
 /* ---- primitive evaluation ops (call sites: SURVEY.md section 8(b)) ---------------------------- */

@@ -47,6 +47,58 @@ def test_client_ciphertext_decrypts_under_oracle(small):
     assert np.abs(dec - a).max() <= 1e-7
 
 
+def _oracle_for(cc, cl):
+    g = O.gen_params(11, ring_dim=cc.N)
+    P = O.Params(N=cc.N, L=cc.L, K=cc.K, dnum=cc.dnum, alpha=-(-cc.L // cc.dnum), q=cc.q, p=cc.p, psi_q=g.psi_q, psi_p=g.psi_p)
+    orc = O.Oracle(P)
+    orc.sk = orc.small_to_rns(cl.secret().astype(np.int64), list(range(P.L + P.K)))
+    return orc
+
+
+def test_device_decrypt_equals_oracle_decrypt(small):
+    """(f)3, receiver side (/root/reference/src/receiver/receiver_hers.cpp:26-54, src/openFHE_wrapper.cpp:83-84): the SAME
+    ciphertext and the SAME secret through hx_client_decrypt and through the oracle's decrypt + decode.  Neither side floods
+    noise, both interpolate the same integer polynomial (the product from its first two limbs, the oracle from all of them: the
+    message + noise is far below q0*q1), so the decoded slots agree to FFT rounding: <= 1e-9."""
+    cc, cl = small
+    orc = _oracle_for(cc, cl)
+    rng = np.random.default_rng(9)
+    a, b = rng.uniform(-1, 1, cc.N // 2), rng.uniform(-1, 1, cc.N // 2)
+    ca, cb = cl.encrypt(a), cl.encrypt(b)
+    cases = [ca,                                          # fresh: 2 components, 12 limbs
+             cc.EvalMultNoRelin(ca, cb),                  # 3 components, degree 2
+             cc.Rescale(cc.EvalMult(ca, cb)),             # 11 limbs
+             cc.LevelReduce(ca, 11)]                      # 1 limb: the result shape of the scenarios
+    for ct in cases:
+        ncomp, nl, level, deg = ct.info()
+        want = orc.decrypt(O.Ct(list(ct.to_numpy()), level, deg))
+        assert np.abs(cl.decrypt(ct) - want).max() <= 1e-9, (ncomp, nl, deg)
+
+
+def test_device_encode_matches_oracle_encode(small):
+    """(f)3, MakeCKKSPackedPlaintext (src/openFHE_wrapper.cpp:75): hx_client_encode against the oracle's encode.  Both compute
+    round(2^45 * special-iFFT(values)); the two FFTs (iterative radix-2 in the product, numpy's in the oracle) differ by
+    floating-point rounding of order 2^45 * N * 2^-53 ~ 0.5 in the scaled coefficient, so coefficients may differ by one unit
+    in the last place and bit-identity is NOT a property of encoding (OpenFHE's own FFT would differ the same way): every
+    integer coefficient within 1, at least half of them equal, decoded slots within 1e-9.  This is why the bit-exact sender tests
+    hand the oracle's plaintext polynomial to both sides."""
+    cc, cl = small
+    orc = _oracle_for(cc, cl)
+    rng = np.random.default_rng(10)
+    for vals in (rng.uniform(-1, 1, cc.N // 2), np.where(np.arange(cc.N // 2) % 128 == 0, 1.0, 0.0), np.full(cc.N // 2, 0.25)):
+        got = cl.MakeCKKSPackedPlaintext(vals)                      # [L][N], evaluation form
+        want_c = orc.encode_coeffs(vals).astype(np.int64)
+        g0 = got[:1].copy()
+        orc.ntt(g0, [0], inverse=True)
+        q0 = cc.q[0]
+        got_c = np.array([int(x) - q0 if int(x) > q0 // 2 else int(x) for x in g0[0]], dtype=np.int64)
+        d = np.abs(got_c - want_c)
+        assert d.max() <= 1 and (d == 0).mean() >= 0.5
+        # every limb encodes the same integer polynomial
+        again = orc.small_to_rns(got_c, list(range(cc.L)))
+        assert np.array_equal(again, got)
+
+
 def test_hydia_end_to_end_product_client_small_ring():
     """Enroll -> query -> membership/index entirely through the product (device keygen + encrypt),
     decisions identical to the plaintext rule cos >= effective threshold (receiver_hers.cpp:26-54)."""

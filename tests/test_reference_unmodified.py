@@ -87,10 +87,11 @@ def test_reference_main_unmodified_approach5_2_10(tmp_path):
 @needs_exe
 @pytest.mark.gpu
 @pytest.mark.timeout(1500)
-@pytest.mark.parametrize("approach", [1, 3, 4])
+@pytest.mark.parametrize("approach", [1, 2, 3, 4])
 def test_reference_main_unmodified_other_approaches(tmp_path, approach):
-    """Baseline (1), Blind-Match (3) and HERS (4) through the reference's own enroller / receiver / sender classes on the same
-    dataset: rows R7-R10 reached from unmodified reference code."""
+    """Baseline (1), GROTE (2: alpha-norm rows / columns, src/sender/sender_grote.cpp:25-65 over sender_hers.cpp:118-178),
+    Blind-Match (3) and HERS (4) through the reference's own enroller / receiver / sender classes on the same dataset: rows
+    R7-R10 and the second half of (f)4 reached from unmodified reference code, results asserted."""
     r = run_reference(tmp_path, approach)
     assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
     assert parse(r.stdout) == ("true", [0])

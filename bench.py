@@ -367,25 +367,39 @@ def run_b200(args):
             cc.prof_enable([dominant])
         l0 = cc.launches()
         halves = [n for n in (steps // 2, steps - steps // 2) if n]
-        ms_v = ms_e = wall_v = wall_e = 0.0
-        launches = 0
-        out = None
-        for n in halves:
-            l0 = cc.launches()
-            a, b, out = timed(n, False)
-            ms_v += a; wall_v += b
-            launches += cc.launches() - l0
+        remeasured = False
+        while True:
+            ms_v = ms_e = wall_v = wall_e = 0.0
+            launches = 0
+            out = None
+            per_half = []
+            for n in halves:
+                l0 = cc.launches()
+                a, b, out = timed(n, False)
+                ms_v += a; wall_v += b
+                launches += cc.launches() - l0
+                if profile:
+                    cc.prof_enable([])      # the dominant family is timed in the value halves only
+                a2, b2, _ = timed(n, True)
+                ms_e += a2; wall_e += b2
+                per_half.append((a / n, a2 / n))
+                if profile:
+                    cc.prof_enable([dominant])
+            # the two halves of an arm time the same work: a gap above 25 % is a disturbance (first-touch allocation, a clock
+            # transition), not a property of the path -- measure once more and say so
+            spread = max(max(h[i] for h in per_half) / min(h[i] for h in per_half) for i in (0, 1))
+            if spread <= 1.25 or remeasured:
+                break
+            remeasured = True
             if profile:
-                cc.prof_enable([])      # the dominant family is timed in the value halves only
-            a, b, _ = timed(n, True)
-            ms_e += a; wall_e += b
-            if profile:
+                cc.prof_reset()
                 cc.prof_enable([dominant])
         prof = cc.prof_read() if profile else {}
         if profile:
             cc.prof_enable([])
         fence()
         return {"sec": ms_v / steps / 1e3, "sec_e2e": ms_e / steps / 1e3, "wall_sec": wall_v / steps / 1e3, "wall_sec_e2e": wall_e / steps / 1e3,
+                "halves_ms": [[round(x, 3) for x in h] for h in per_half], "remeasured": remeasured,
                 "launches": launches, "prof": prof, "prof_all": prof_all, "dominant": dominant, "out": out, "n_total": n_total, "snd": snd}
 
     expected_index = enroll(args.total_blocks)
@@ -462,7 +476,7 @@ def run_b200(args):
                 "vectors_per_s": r["n_total"] / sec,
                 "e2e": {"value": sec_e2e, "unit": UNIT, "h2d_bytes_per_step": ct_words * 8,
                         "d2h_bytes_per_step": (args.total_blocks + 1) * res_words * 8, "host_clock_value": r["wall_sec_e2e"]},
-                "host_clock_value": r["wall_sec"],
+                "host_clock_value": r["wall_sec"], "halves_ms_per_step_value_e2e": r["halves_ms"], "remeasured_after_disturbance": r["remeasured"],
                 "gpu_launches": launches, "clocks": sampler.result(), "results_ok": bool(ok),
                 "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak, "traffic": traffic,

@@ -440,8 +440,9 @@ u64* Engine::ks_precompute(const u64* c, int nl, int* ndig_out, int nbatch, size
         for (int j = 0; j < ndig; j++) m.tabs[j] = modup_table(nl, j);
         m.scratch = alloc_words((size_t)nbatch * nl * N);
         m.digits = digits;
+        m.warp_tasks = ks_moddown_w;
         {   // algorithmic bytes: input polynomial once, digits once
-            Scope sc(this, PK_MODUP, 4, 8.0 * N * nbatch * (nl + (double)ndig * ext));
+            Scope sc(this, PK_MODUP, (ks_moddown_w && moddown_w_supported(logN, alpha)) ? 3 : 4, 8.0 * N * nbatch * (nl + (double)ndig * ext));
             launch_fused_modup(T, m, st);
         }
         free_words(m.scratch);

@@ -546,20 +546,25 @@ static void modup_t(const DevTables& T, const ModUpArgs& m, cudaStream_t st) {
     using G = NttGeo<LOGN>;
     const int ext = m.nl + m.K;
     launch_pdl(k_inv_rows<LOGN>, dim3(G::TILES, m.nl, m.nbatch), dim3(kTileThreads), 0, st, T, m.c, m.c_bs, m.scratch, (size_t)m.nl * T.N, 0);
-    // all digits in one launch per stage: inverse columns of the nl source limbs, then every digit's
-    // conversion to its complement limbs fused with their forward column pass
-    TabSet ts{};
-    ts.ndig = m.ndig; ts.alpha = m.alpha; ts.ystart[0] = 0;
-    for (int d = 0; d < m.ndig; d++) {
-        const int lo = d * m.alpha, hi = (d == m.ndig - 1) ? m.nl : (d + 1) * m.alpha, sz = hi - lo;
-        ts.t[d] = m.tabs[d];
-        ts.ystart[d + 1] = ts.ystart[d] + (ext - sz);
-        ts.in_off[d] = (size_t)lo * T.N;
-        ts.out_off[d] = (size_t)d * ext * T.N;
+    if (m.warp_tasks && moddown_w_supported(LOGN, m.alpha)) {
+        // rings of 2^15 / 2^16: inverse column pass, conversion and forward column pass of every digit in ONE launch of warp tasks
+        launch_modup_w(T, m, st);
+    } else {
+        // all digits in one launch per stage: inverse columns of the nl source limbs, then every digit's
+        // conversion to its complement limbs fused with their forward column pass
+        TabSet ts{};
+        ts.ndig = m.ndig; ts.alpha = m.alpha; ts.ystart[0] = 0;
+        for (int d = 0; d < m.ndig; d++) {
+            const int lo = d * m.alpha, hi = (d == m.ndig - 1) ? m.nl : (d + 1) * m.alpha, sz = hi - lo;
+            ts.t[d] = m.tabs[d];
+            ts.ystart[d + 1] = ts.ystart[d] + (ext - sz);
+            ts.in_off[d] = (size_t)lo * T.N;
+            ts.out_off[d] = (size_t)d * ext * T.N;
+        }
+        launch_pdl(k_inv_cols<LOGN>, dim3(G::TILES, m.nl, m.nbatch), dim3(kTileThreads), 0, st, T, ts, m.scratch, (size_t)m.nl * T.N);
+        launch_conv_fwd_col<LOGN>(T, ts, m.alpha, ts.ystart[m.ndig], m.nbatch,
+                                  m.scratch, (size_t)m.nl * T.N, m.digits, (size_t)m.ndig * ext * T.N, m.nl, m.L, 1, st);
     }
-    launch_pdl(k_inv_cols<LOGN>, dim3(G::TILES, m.nl, m.nbatch), dim3(kTileThreads), 0, st, T, ts, m.scratch, (size_t)m.nl * T.N);
-    launch_conv_fwd_col<LOGN>(T, ts, m.alpha, ts.ystart[m.ndig], m.nbatch,
-                              m.scratch, (size_t)m.nl * T.N, m.digits, (size_t)m.ndig * ext * T.N, m.nl, m.L, 1, st);
     launch_pdl(k_modup_rows<LOGN>, dim3(G::TILES, ext, m.ndig * m.nbatch), dim3(kTileThreads), 0, st, T, m.digits, m.c, m.c_bs, m.ndig, m.nl, m.L, m.alpha);
 }
 void launch_fused_modup(const DevTables& T, const ModUpArgs& m, cudaStream_t st) {

@@ -94,8 +94,10 @@ struct ModUpArgs {
     const BaseConvTable* tabs[kMaxDigits];   // per digit: own limbs -> complement (Q then P)
     u64* scratch;                            // [nbatch][nl][N]
     u64* digits;
+    int warp_tasks = 1;                      // Engine::ks_moddown_w
 };
 void launch_fused_modup(const DevTables& T, const ModUpArgs& m, cudaStream_t st);
+void launch_modup_w(const DevTables& T, const ModUpArgs& m, cudaStream_t st);   // hx_moddown.cu: the middle of ModUp as warp tasks
 // fused rescale: c [ncomp] x c_bs, each [nl][N]  ->  out [ncomp] x out_bs, each [nl-1][N]
 struct RescaleArgs {
     const u64* c; size_t c_bs; int ncomp, nl;

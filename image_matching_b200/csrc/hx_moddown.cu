@@ -19,6 +19,7 @@
 #include "hx_kernels.cuh"
 #include "hx_ntt_tile.cuh"
 #include "hx_fpmod.cuh"
+#include <algorithm>
 
 #ifndef HX_MDW_MINB
 #define HX_MDW_MINB 3
@@ -183,20 +184,32 @@ __device__ __forceinline__ void inv_top(V (&v)[16], const TW* __restrict__ tw, B
 
 // grid (2^B / 8 column tiles, nbatch) ; in: [nbatch][n_in][N] (K1's output: inverse row pass done, values in [0,4q));
 // out: [nbatch][n_out][N], forward column pass done, pass-internal words (lazy doubles on FP64 limbs, [0,8q) on 60-bit limbs)
+// One launch serves ModDown (one table, output limb j at position j) and ModUp (one table per digit: blockIdx.y = entry * ndig +
+// digit, source limbs of digit d start at in_off[d], the digit's extended polynomial at out_off[d], output limb of prime p at
+// its extended-basis position: Q limbs 0..ext_nl-1, then the P limbs).
+struct MdwArgs {
+    const BaseConvTable* tab[kMaxDigits];
+    size_t in_off[kMaxDigits], out_off[kMaxDigits];
+    int ndig;
+    size_t in_bs, out_bs;      // words between batch entries
+    int ext_nl, L;             // ext_nl < 0: ModDown positions
+};
 template <int LOGN>
-__global__ void __launch_bounds__(256, LOGN <= 15 ? HX_MDW_MINB : 2) k_moddown_w(const __grid_constant__ DevTables T, const BaseConvTable* __restrict__ tab,
-                                                                       const u64* in, size_t in_bs, u64* out, size_t out_bs) {
+__global__ void __launch_bounds__(256, LOGN <= 15 ? HX_MDW_MINB : 2) k_moddown_w(const __grid_constant__ DevTables T, const __grid_constant__ MdwArgs A,
+                                                                       const u64* in, u64* out) {
     using W = WGeo<LOGN>;
     pdl_wait();
     extern __shared__ __align__(16) u64 smw[];
+    const int dgt = blockIdx.y % A.ndig, entry = blockIdx.y / A.ndig;
+    const BaseConvTable* __restrict__ tab = A.tab[dgt];
     const int n_in = tab->n_in, n_out = tab->n_out;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     u64* const stage = smw;                                                   // [n_in][GROUPS][ROWS][WCOLS], 30-bit split words
     u64* const xch = smw + (size_t)n_in * W::STAGE_WORDS + warp * W::XWORDS;  // this warp's exchange buffer
     const int rhB = lane >> 1, cqB = lane & 1;                                // low ownership
     const size_t colbase = (size_t)blockIdx.x * W::CTA_COLS;
-    in += (size_t)blockIdx.y * in_bs;
-    out += (size_t)blockIdx.y * out_bs;
+    in += (size_t)entry * A.in_bs + A.in_off[dgt];
+    out += (size_t)entry * A.out_bs + A.out_off[dgt];
 
     // ---- inverse tasks: (source limb k, column group g)
     for (int task = warp; task < n_in * W::GROUPS; task += W::WARPS) {
@@ -246,7 +259,8 @@ __global__ void __launch_bounds__(256, LOGN <= 15 ? HX_MDW_MINB : 2) k_moddown_w
                 if (k < n_in) mac30ss(acc, st[(size_t)k * W::STAGE_WORDS + rh * W::NR * W::WCOLS], mk[k]);
             r[rh] = redc_lazy(fold30(acc), q, pc.qinv_neg);       // in [0, 2q): sum of <= 7 products below 2^60 q
         }
-        u64* dst = out + (size_t)j * T.N + colbase + g * W::WCOLS + cqB * W::NC + ((size_t)(rhB * W::NR) << W::B);
+        const int pos = A.ext_nl < 0 ? j : (prime < A.L ? prime : A.ext_nl + prime - A.L);
+        u64* dst = out + (size_t)pos * T.N + colbase + g * W::WCOLS + cqB * W::NC + ((size_t)(rhB * W::NR) << W::B);
         if (fp_ok(q)) {
             const double qd = fp_from_u64(q);
             const double2* __restrict__ twd = T.tw_fwd_d + (size_t)prime * T.N;
@@ -299,14 +313,35 @@ void init_moddown_kernels(int logN) {
     if (logN == 16) init_t<16>();
 }
 template <int LOGN>
-static void launch_t(const DevTables& T, const BaseConvTable* tab, int n_in, int nbatch, const u64* in, size_t in_bs, u64* out, size_t out_bs, cudaStream_t st) {
+static void launch_t(const DevTables& T, const MdwArgs& A, int max_n_in, int nbatch, const u64* in, u64* out, cudaStream_t st) {
     using W = WGeo<LOGN>;
-    launch_pdl(k_moddown_w<LOGN>, dim3((1u << W::B) / W::CTA_COLS, nbatch), dim3(256), moddown_w_smem<LOGN>(n_in), st, T, tab, in, in_bs, out, out_bs);
+    launch_pdl(k_moddown_w<LOGN>, dim3((1u << W::B) / W::CTA_COLS, nbatch * A.ndig), dim3(256), moddown_w_smem<LOGN>(max_n_in), st, T, A, in, out);
+}
+static void launch_any(const DevTables& T, const MdwArgs& A, int max_n_in, int nbatch, const u64* in, u64* out, cudaStream_t st) {
+    if (T.logN == 15) launch_t<15>(T, A, max_n_in, nbatch, in, out, st);
+    else if (T.logN == 16) launch_t<16>(T, A, max_n_in, nbatch, in, out, st);
+    else throw std::runtime_error("warp-task base conversion: unsupported ring dimension");
 }
 void launch_moddown_w(const DevTables& T, const BaseConvTable* tab, int n_in, int nbatch, const u64* in, size_t in_bs, u64* out, size_t out_bs, cudaStream_t st) {
-    if (T.logN == 15) launch_t<15>(T, tab, n_in, nbatch, in, in_bs, out, out_bs, st);
-    else if (T.logN == 16) launch_t<16>(T, tab, n_in, nbatch, in, in_bs, out, out_bs, st);
-    else throw std::runtime_error("launch_moddown_w: unsupported ring dimension");
+    MdwArgs A{};
+    A.tab[0] = tab; A.ndig = 1; A.in_bs = in_bs; A.out_bs = out_bs; A.ext_nl = -1; A.L = 0;
+    launch_any(T, A, n_in, nbatch, in, out, st);
+}
+// ModUp's middle (EvalKeySwitchPrecomputeCore): scratch [nbatch][nl][N] (inverse row pass done) -> the converted limbs of every
+// digit of digits [nbatch][ndig][nl+K][N] (forward column pass done; k_modup_rows finishes them and copies the digit's own limbs)
+void launch_modup_w(const DevTables& T, const ModUpArgs& m, cudaStream_t st) {
+    const int ext = m.nl + m.K;
+    MdwArgs A{};
+    A.ndig = m.ndig; A.in_bs = (size_t)m.nl * T.N; A.out_bs = (size_t)m.ndig * ext * T.N; A.ext_nl = m.nl; A.L = m.L;
+    int max_in = 1;
+    for (int d = 0; d < m.ndig; d++) {
+        const int lo = d * m.alpha, hi = (d == m.ndig - 1) ? m.nl : (d + 1) * m.alpha;
+        A.tab[d] = m.tabs[d];
+        A.in_off[d] = (size_t)lo * T.N;
+        A.out_off[d] = (size_t)d * ext * T.N;
+        max_in = std::max(max_in, hi - lo);
+    }
+    launch_any(T, A, max_in, m.nbatch, m.scratch, m.digits, st);
 }
 
 }  // namespace hx

@@ -96,6 +96,12 @@ SIGNATURES = {
     "hx_client_enroll": (C.c_int, [VP, C.c_int, C.c_int, F64P, C.c_int]),
     "hx_client_decrypt": (C.c_int, [VP, VP, F64P]),
     "hx_client_secret": (C.c_int, [VP, C.POINTER(C.c_int8)]),
+    "hx_ctx_get_params": (C.c_int, [VP, I32P, I32P, I32P, I32P, I32P, U64P, U64P, U64P, U64P]),
+    "hx_key_count": (C.c_int, [VP, I32P]),
+    "hx_key_list": (C.c_int, [VP, C.POINTER(C.c_uint32), C.c_int]),
+    "hx_key_export": (C.c_int, [VP, C.c_uint32, U64P, U64P]),
+    "hx_client_export_public": (C.c_int, [VP, U64P, U64P]),
+    "hx_client_import": (VP, [VP, C.c_uint64, C.POINTER(C.c_int8), U64P, U64P]),
 }
 
 _lib = None

@@ -411,6 +411,46 @@ int hx_client_enroll(hx_client* c, int block, int diag, const double* values, in
     HX_TRY_INT(need(c, "client"); need(values, "values"); c->cl->enroll(block, diag, values, n);)
 }
 int hx_client_decrypt(hx_client* c, hx_ct* ct, double* out) { HX_TRY_INT(need(c, "client"); need(ct, "ct"); need(out, "out"); c->cl->decrypt(ct->ct, out);) }
+// ---- (de)serialisation support (shim/hx_serial.h): parameters, evaluation keys and the key pair as plain residues
+int hx_ctx_get_params(hx_ctx* ctx, int* N, int* L, int* K, int* dnum, int* log2_scale, uint64_t* q, uint64_t* p, uint64_t* psi_q, uint64_t* psi_p) {
+    HX_TRY_INT(need(ctx, "ctx");
+               Engine* e = ctx->eng.get();
+               if (N) *N = e->N;
+               if (L) *L = e->L;
+               if (K) *K = e->K;
+               if (dnum) *dnum = e->dnum;
+               if (log2_scale) *log2_scale = e->scale_bits;
+               for (int i = 0; i < e->L; i++) { if (q) q[i] = e->mods[i]; if (psi_q) psi_q[i] = e->psis[i]; }
+               for (int i = 0; i < e->K; i++) { if (p) p[i] = e->mods[e->L + i]; if (psi_p) psi_p[i] = e->psis[e->L + i]; })
+}
+int hx_key_count(hx_ctx* ctx, int* has_mult) {
+    if (!ctx) return -1;
+    Engine::Guard g(ctx->eng.get());
+    if (has_mult) *has_mult = ctx->eng->has_mult_key() ? 1 : 0;
+    return (int)ctx->eng->rot_key_galois().size();
+}
+int hx_key_list(hx_ctx* ctx, uint32_t* galois, int max_out) {
+    try {
+        need(ctx, "ctx"); need(galois, "galois");
+        Engine::Guard g(ctx->eng.get());
+        std::vector<u64> v = ctx->eng->rot_key_galois();
+        if ((int)v.size() > max_out) throw std::runtime_error("hx_key_list: output array too small");
+        for (size_t i = 0; i < v.size(); i++) galois[i] = (uint32_t)v[i];
+        return (int)v.size();
+    } catch (const std::exception& e) { set_err(e); return -1; }
+}
+int hx_key_export(hx_ctx* ctx, uint32_t galois, uint64_t* a, uint64_t* b) {
+    HX_TRY_INT(need(ctx, "ctx"); need(a, "a"); need(b, "b"); ctx->eng->export_key(galois, (u64*)a, (u64*)b);)
+}
+int hx_client_export_public(hx_client* c, uint64_t* pkb, uint64_t* pka) {
+    HX_TRY_INT(need(c, "client"); need(pkb, "pkb"); need(pka, "pka"); c->cl->export_public((u64*)pkb, (u64*)pka);)
+}
+hx_client* hx_client_import(hx_ctx* ctx, uint64_t seed, const int8_t* sk, const uint64_t* pkb, const uint64_t* pka) {
+    HX_TRY_PTR(need(ctx, "ctx"); need(sk, "sk"); need(pkb, "pkb"); need(pka, "pka");
+               hx_client* c = new hx_client;
+               c->cl = new Client(ctx->eng, seed, sk, (const u64*)pkb, (const u64*)pka);
+               return c;)
+}
 int hx_client_secret(hx_client* c, int8_t* out) { HX_TRY_INT(need(c, "client"); need(out, "out"); c->cl->secret(out);) }
 
 }  // extern "C"

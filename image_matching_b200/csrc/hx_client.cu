@@ -155,6 +155,38 @@ Client::Client(std::shared_ptr<Engine> e, u64 seed_) : keep(e), eng(e.get()), se
     eng->free_words(e_rns);
     eng->sync();
 }
+Client::Client(std::shared_ptr<Engine> e, u64 seed_, const int8_t* sk, const u64* pkb, const u64* pka) : keep(e), eng(e.get()), seed(seed_) {
+    Engine::Guard g(eng);
+    const int N = eng->N, np = eng->L + eng->K;
+    slot_idx.resize(N / 2);
+    u64 m = 2ull * N, x = 1;
+    for (int j = 0; j < N / 2; j++) { slot_idx[j] = (int)((x - 1) / 2); x = (x * 5) % m; }
+    zeta.resize(N);
+    for (int n = 0; n < N; n++) zeta[n] = std::polar(1.0, M_PI * (double)n / (double)N);
+    next_stream = 1u << 20;   // fresh randomness for encryptions made after the import: streams the generating client never used
+    std::vector<int> small(N);
+    for (int i = 0; i < N; i++) {
+        if (sk[i] < -1 || sk[i] > 1) throw std::runtime_error("hx_client_import: secret key coefficients must be in {-1, 0, 1}");
+        small[i] = sk[i];
+    }
+    HX_CUDA(cudaMalloc(&d_sk_small, sizeof(int) * N));
+    HX_CUDA(cudaMemcpy(d_sk_small, small.data(), sizeof(int) * N, cudaMemcpyHostToDevice));
+    HX_CUDA(cudaMalloc(&d_sk, sizeof(u64) * (size_t)np * N));
+    std::vector<int> all;
+    for (int i = 0; i < np; i++) all.push_back(i);
+    small_to_rns(d_sk_small, d_sk, all);
+    HX_CUDA(cudaMalloc(&d_pka, sizeof(u64) * (size_t)eng->L * N));
+    HX_CUDA(cudaMalloc(&d_pkb, sizeof(u64) * (size_t)eng->L * N));
+    HX_CUDA(cudaMemcpy(d_pka, pka, sizeof(u64) * (size_t)eng->L * N, cudaMemcpyHostToDevice));
+    HX_CUDA(cudaMemcpy(d_pkb, pkb, sizeof(u64) * (size_t)eng->L * N, cudaMemcpyHostToDevice));
+    eng->sync();
+}
+void Client::export_public(u64* pkb, u64* pka) {
+    Engine::Guard g(eng);
+    eng->sync();
+    HX_CUDA(cudaMemcpy(pkb, d_pkb, sizeof(u64) * (size_t)eng->L * eng->N, cudaMemcpyDeviceToHost));
+    HX_CUDA(cudaMemcpy(pka, d_pka, sizeof(u64) * (size_t)eng->L * eng->N, cudaMemcpyDeviceToHost));
+}
 Client::~Client() {
     cudaFree(d_sk_small); cudaFree(d_sk); cudaFree(d_pka); cudaFree(d_pkb);
 }

@@ -9,6 +9,9 @@ namespace hx {
 class Client {
 public:
     Client(std::shared_ptr<Engine> e, u64 seed);
+    // from a serialised key pair: secret as small coefficients in {-1,0,1}, public key (b, a) as plain residues [L][N] each
+    Client(std::shared_ptr<Engine> e, u64 seed, const int8_t* sk, const u64* pkb, const u64* pka);
+    void export_public(u64* pkb, u64* pka);
     ~Client();
     void gen_mult_key();                          // EvalMultKeyGen      (src/main.cpp:188)
     void gen_rot_keys(const int* rot, int n);     // EvalRotateKeyGen    (src/main.cpp:206)

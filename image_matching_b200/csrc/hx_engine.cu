@@ -396,6 +396,25 @@ void Engine::finish_key(EvalKey& k) {
     launch_key_finish(T, k.a, dnum, L, K, ps, st);
     launch_key_finish(T, k.b, dnum, L, K, ps, st);
 }
+void Engine::export_key(u64 galois, u64* host_a, u64* host_b) {
+    Guard g(this);
+    if (galois == 0 && !have_mult_key_) throw std::runtime_error("EvalMultKey is not generated");
+    const EvalKey& k = galois ? rot_key(galois) : mult_key_;
+    std::vector<u64> pm(L);
+    for (int i = 0; i < L; i++) pm[i] = P_mod(i);
+    ScalarTable ps = scalar_table(pm);
+    const size_t words = (size_t)dnum * (L + K) * N;
+    u64* tmp = alloc_words(words);
+    const u64* src[2] = {k.a, k.b};
+    u64* dst[2] = {host_a, host_b};
+    for (int c = 0; c < 2; c++) {
+        Scope sc(this, PK_MISC, 1, 16.0 * words);
+        launch_key_unfinish(T, tmp, src[c], dnum, L, K, ps, st);
+        HX_CUDA(cudaMemcpyAsync(dst[c], tmp, sizeof(u64) * words, cudaMemcpyDeviceToHost, st));
+        sync();
+    }
+    free_words(tmp);
+}
 void Engine::load_mult_key(const u64* a, const u64* b) {
     Guard g(this);
     if (have_mult_key_) { cudaFree(mult_key_.a); cudaFree(mult_key_.b); }

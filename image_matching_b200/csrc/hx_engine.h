@@ -135,6 +135,10 @@ public:
     void adopt_mult_key(EvalKey k);
     void finish_key(EvalKey& k);                 // plain residues -> engine-internal key form (in place)
     bool has_rot_key(u64 galois) const { return rot_keys_.count(galois) != 0; }
+    bool has_mult_key() const { return have_mult_key_; }
+    std::vector<u64> rot_key_galois() const { std::vector<u64> v; for (auto& kv : rot_keys_) v.push_back(kv.first); return v; }
+    // plain residues [dnum][L+K][N] of a loaded key back to the host (the inverse of finish_key); galois = 0: the mult key
+    void export_key(u64 galois, u64* host_a, u64* host_b);
     u64 galois_for_rotation(int r) const;
 
     // ---- primitive evaluation ops

@@ -401,6 +401,30 @@ __global__ void __launch_bounds__(kThreads) k_key_finish(DevTables T, u64* __res
 void launch_key_finish(const DevTables& T, u64* key, int dnum, int L, int K, const ScalarTable& pinv, cudaStream_t st) {
     k_key_finish<<<dim3(blocks_for(T.N), L + K, dnum), kThreads, 0, st>>>(T, key, L, K, pinv);
 }
+__global__ void __launch_bounds__(kThreads) k_key_unfinish(DevTables T, u64* __restrict__ out, const u64* __restrict__ key, int L, int K, ScalarTable pmod) {
+    const int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (idx >= T.N) return;
+    const int limb = blockIdx.y;
+    const PrimeConst pc = T.pc[limb];
+    const size_t off = ((size_t)blockIdx.z * (L + K) + limb) * T.N + idx;
+    ulonglong2 x = ld_stream128(key + off);
+    if (limb < L && (pc.q >> 46) == 0) {
+        x.x = fp_to_u64(fp_bits_to_double(x.x));
+        x.y = fp_to_u64(fp_bits_to_double(x.y));
+    } else {
+        u128d a = {unsplit30(x.x), 0}, b = {unsplit30(x.y), 0};
+        x.x = redc(a, pc.q, pc.qinv_neg);      // out of Montgomery form
+        x.y = redc(b, pc.q, pc.qinv_neg);
+    }
+    if (limb < L) {
+        x.x = shoup_mul(x.x, pmod.v[limb], pmod.sh[limb], pc.q);
+        x.y = shoup_mul(x.y, pmod.v[limb], pmod.sh[limb], pc.q);
+    }
+    st128(out + off, x);
+}
+void launch_key_unfinish(const DevTables& T, u64* out, const u64* key, int dnum, int L, int K, const ScalarTable& pmod, cudaStream_t st) {
+    k_key_unfinish<<<dim3(blocks_for(T.N), L + K, dnum), kThreads, 0, st>>>(T, out, key, L, K, pmod);
+}
 void launch_split30(u64* data, size_t words, cudaStream_t st) {
     k_split30<<<(unsigned)((words / 2 + kThreads - 1) / kThreads), kThreads, 0, st>>>(data, words);
 }

@@ -159,6 +159,8 @@ void launch_to_mont(const DevTables& T, u64* data, int nbatch, const LimbMap& lm
 // P^-1 mod q_i; limbs below 2^46 (the FP64 limbs of the key-switch kernels) become doubles holding that residue, all other limbs
 // become Montgomery residues split into 30-bit halves.
 void launch_key_finish(const DevTables& T, u64* key, int dnum, int L, int K, const ScalarTable& pinv, cudaStream_t st);
+// the inverse: engine-internal key words -> plain residues (out of place), for key export (serialisation); pmod[i] = P mod q_i
+void launch_key_unfinish(const DevTables& T, u64* out, const u64* key, int dnum, int L, int K, const ScalarTable& pmod, cudaStream_t st);
 // in place: x -> split30(x) (engine-internal key form, see hx_modarith.cuh)
 void launch_split30(u64* data, size_t words, cudaStream_t st);
 

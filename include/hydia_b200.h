@@ -203,6 +203,16 @@ int hx_client_enroll(hx_client* c, int block, int diag, const double* values, in
 int hx_client_decrypt(hx_client* c, hx_ct* ct, double* out);
 /* secret key (ternary, N int8) for cross-checks against the CPU oracle in tests */
 int hx_client_secret(hx_client* c, int8_t* out);
+/* (De)serialisation support for shim/hx_serial.h (Serial::SerializeToFile / DeserializeFromFile and cc->Serialize...Key of
+ * /root/reference/src/main.cpp:124-165, 251-285): the context's parameters, the loaded evaluation keys as plain residues
+ * [dnum][L+K][N] (galois 0 = the EvalMult key; the reverse direction is hx_key_load_mult / hx_key_load_auto) and the key pair
+ * (secret as coefficients in {-1,0,1}, public key (b, a) as residues [L][N]). */
+int hx_ctx_get_params(hx_ctx* ctx, int* N, int* L, int* K, int* dnum, int* log2_scale, uint64_t* q, uint64_t* p, uint64_t* psi_q, uint64_t* psi_p);
+int hx_key_count(hx_ctx* ctx, int* has_mult);                        /* number of automorphism keys loaded */
+int hx_key_list(hx_ctx* ctx, uint32_t* galois, int max_out);         /* their Galois elements */
+int hx_key_export(hx_ctx* ctx, uint32_t galois, uint64_t* a, uint64_t* b);
+int hx_client_export_public(hx_client* c, uint64_t* pkb, uint64_t* pka);
+hx_client* hx_client_import(hx_ctx* ctx, uint64_t seed, const int8_t* sk, const uint64_t* pkb, const uint64_t* pka);
 
 #ifdef __cplusplus
 }

@@ -45,6 +45,7 @@
 #include <vector>
 
 #include "hydia_b200.h"
+#include "hx_serial.h"
 
 namespace lbcrypto {
 
@@ -70,6 +71,19 @@ struct Backend {
     bool sync_every_call = false;
     bool deferred = true;     // HYDIA_DEFERRED=0: every call is issued as it comes (pure per-op path)
     bool chains = true;       // HYDIA_DEFERRED=2 (default unless calls are synchronous): compare chains are recorded and batched too
+    std::vector<uint64_t> pending_pkb, pending_pka;   // a deserialised public key waits here for its private key (hx_client_import)
+    // HYDIA_SHIM_SERIAL_FILES=1: Serial:: and cc->Serialize...Key write and read real SerType::BINARY files (shim/hx_serial.h);
+    // default: evaluation keys and database ciphertexts stay in HBM and the "files" are a path -> handle table
+    static bool serial_files() {
+        static const bool on = [] { const char* e = std::getenv("HYDIA_SHIM_SERIAL_FILES"); return e && std::atoi(e) != 0; }();
+        return on;
+    }
+    // the context a ciphertext file is read into when no in-process handle is registered under its path (a fresh process that
+    // deserialised serial/cryptocontext.bin): the most recently created or deserialised one
+    static std::shared_ptr<Backend>& current() {
+        static auto* c = new std::shared_ptr<Backend>();
+        return *c;
+    }
     ~Backend() {
         if (client) hx_client_destroy(client);
         if (ctx) hx_ctx_destroy(ctx);
@@ -778,12 +792,33 @@ public:
     }
 
     // -- key (de)serialisation (src/main.cpp:124-165, 251-285): the keys never leave HBM
-    template <class ST> bool SerializeEvalMultKey(std::ostream& os, const ST&, const std::string& = "") const { return marker(os); }
-    template <class ST> bool SerializeEvalSumKey(std::ostream& os, const ST&, const std::string& = "") const { return marker(os); }
-    template <class ST> bool SerializeEvalAutomorphismKey(std::ostream& os, const ST&, const std::string& = "") const { return marker(os); }
-    template <class ST> bool DeserializeEvalMultKey(std::istream& is, const ST&) const { return is.good(); }
-    template <class ST> bool DeserializeEvalSumKey(std::istream& is, const ST&) const { return is.good(); }
-    template <class ST> bool DeserializeEvalAutomorphismKey(std::istream& is, const ST&) const { return is.good(); }
+    // With HYDIA_SHIM_SERIAL_FILES=1 the streams carry the keys (shim/hx_serial.h: cereal BINARY conventions, layout unverified
+    // against upstream); otherwise a marker line, because the keys stay resident.
+    template <class ST> bool SerializeEvalMultKey(std::ostream& os, const ST&, const std::string& = "") const {
+        if (!shim::Backend::serial_files()) return marker(os);
+        try { return hxser::write_mult_key_stream(os, be_->ctx); } catch (const std::exception& e) { std::cerr << e.what() << std::endl; return false; }
+    }
+    template <class ST> bool SerializeEvalSumKey(std::ostream& os, const ST&, const std::string& = "") const {
+        if (!shim::Backend::serial_files()) return marker(os);
+        const std::vector<uint32_t> sum = hxser::eval_sum_galois(be_->N);
+        try { return hxser::write_auto_key_stream(os, be_->ctx, &sum); } catch (const std::exception& e) { std::cerr << e.what() << std::endl; return false; }
+    }
+    template <class ST> bool SerializeEvalAutomorphismKey(std::ostream& os, const ST&, const std::string& = "") const {
+        if (!shim::Backend::serial_files()) return marker(os);
+        try { return hxser::write_auto_key_stream(os, be_->ctx, nullptr); } catch (const std::exception& e) { std::cerr << e.what() << std::endl; return false; }
+    }
+    template <class ST> bool DeserializeEvalMultKey(std::istream& is, const ST&) const {
+        if (!shim::Backend::serial_files()) return is.good();
+        try { return hxser::read_mult_key_stream(is, be_->ctx); } catch (const std::exception& e) { std::cerr << e.what() << std::endl; return false; }
+    }
+    template <class ST> bool DeserializeEvalSumKey(std::istream& is, const ST&) const {
+        if (!shim::Backend::serial_files()) return is.good();
+        try { return hxser::read_auto_key_stream(is, be_->ctx); } catch (const std::exception& e) { std::cerr << e.what() << std::endl; return false; }
+    }
+    template <class ST> bool DeserializeEvalAutomorphismKey(std::istream& is, const ST&) const {
+        if (!shim::Backend::serial_files()) return is.good();
+        try { return hxser::read_auto_key_stream(is, be_->ctx); } catch (const std::exception& e) { std::cerr << e.what() << std::endl; return false; }
+    }
 
 private:
     // a new recorded ciphertext = `a` followed by one more step (a's own steps are copied when `a` is still a recorded chain)
@@ -851,8 +886,26 @@ inline CryptoContext<DCRTPoly> GenCryptoContext(const CCParams<CryptoContextCKKS
     // complete when the receiver reads it; with synchronous calls that would move work out of the reference's timers, so
     // chains are then recorded only on request (HYDIA_DEFERRED=2).
     be->chains = be->deferred && (deferred ? std::atoi(deferred) >= 2 : !be->sync_every_call);
+    shim::Backend::current() = be;
     return std::make_shared<CryptoContextImpl<DCRTPoly>>(be);
 }
+namespace shim {
+// the same context from serialised parameters (Serial::DeserializeFromFile of serial/cryptocontext.bin, src/main.cpp:124)
+inline std::shared_ptr<Backend> backend_from_params(const hxser::Params& P) {
+    auto be = std::make_shared<Backend>();
+    be->N = P.N; be->L = P.L; be->K = P.K; be->dnum = P.dnum; be->scale_bits = P.scale_bits;
+    const char* dev = std::getenv("HYDIA_DEVICE");
+    be->ctx = check(hx_ctx_create(P.N, P.L, P.K, P.dnum, P.q.data(), P.p.data(), P.psi_q.data(), P.psi_p.data(), P.scale_bits, dev ? std::atoi(dev) : 0),
+                    "DeserializeFromFile(CryptoContext)");
+    const char* sync = std::getenv("HYDIA_SYNC_EVERY_CALL");
+    be->sync_every_call = sync && std::atoi(sync) != 0;
+    const char* deferred = std::getenv("HYDIA_DEFERRED");
+    be->deferred = !deferred || std::atoi(deferred) != 0;
+    be->chains = be->deferred && (deferred ? std::atoi(deferred) >= 2 : !be->sync_every_call);
+    Backend::current() = be;
+    return be;
+}
+}  // namespace shim
 
 // ---- Serial ------------------------------------------------------------------------------------------------------------
 namespace Serial {
@@ -866,13 +919,39 @@ inline std::mutex& table_mutex() {
     static auto* m = new std::mutex();
     return *m;
 }
+// the ciphertext as a real SerType::BINARY file (HYDIA_SHIM_SERIAL_FILES=1), as the reference's enrollers produce
+inline bool write_ct_file(const std::string& path, const Ciphertext<DCRTPoly>& ct) {
+    if (!shim::Backend::serial_files()) return true;
+    try {
+        hxser::Session ses;
+        ses.P = hxser::params_of(ct->backend()->ctx);
+        ses.have_params = true;
+        hxser::HostCt h;
+        shim::check(hx_ct_info(ct->handle(), &h.ncomp, &h.nl, &h.level, &h.deg), "SerializeToFile");
+        h.data.resize((size_t)h.ncomp * h.nl * ses.P.N);
+        shim::check(hx_ct_download(ct->handle(), h.data.data()), "SerializeToFile");
+        std::ofstream os(path, std::ios::out | std::ios::binary);
+        if (!os.is_open()) return false;
+        hxser::Writer w(os);
+        hxser::write_ciphertext(w, ses, h);
+        return w.good();
+    } catch (const std::exception& e) {
+        std::cerr << "SerializeToFile(" << path << "): " << e.what() << std::endl;
+        return false;
+    }
+}
 }  // namespace detail
 
 // Enrollers (src/enroller/enroller_diag.cpp:158-164, enroller_hers.cpp:116-121, ...): the ciphertext becomes database entry
 // `path`, resident in HBM. A private copy is kept so later "...InPlace" calls on the caller's object cannot touch it.
+inline bool SerializeToFileResident(const std::string& path, const Ciphertext<DCRTPoly>& ct);
 template <class ST>
 bool SerializeToFile(const std::string& path, const Ciphertext<DCRTPoly>& ct, const ST&) {
     if (!ct) return false;
+    if (!SerializeToFileResident(path, ct)) return false;
+    return detail::write_ct_file(path, ct);
+}
+inline bool SerializeToFileResident(const std::string& path, const Ciphertext<DCRTPoly>& ct) {
     std::shared_ptr<CiphertextImpl<DCRTPoly>> entry;
     int index = -1, matrix = -1, consumed = 0;
     // serial/db_diagonal/index{block*512+diag}.bin (enroller_diag.cpp:159): goes into the engine's database store, which is what
@@ -897,27 +976,148 @@ bool SerializeToFile(const std::string& path, const Ciphertext<DCRTPoly>& ct, co
         if (!copy) return false;
         entry = std::make_shared<CiphertextImpl<DCRTPoly>>(ct->backend(), copy);
     }
-    std::lock_guard<std::mutex> g(detail::table_mutex());
-    detail::table()[path] = entry;
+    {
+        std::lock_guard<std::mutex> g(detail::table_mutex());
+        detail::table()[path] = entry;
+    }
     return true;
 }
 // Senders (src/sender/sender_diag.cpp:87-91 and the like): the handle registered under `path`; false when nothing was enrolled
 // there, which the reference reports on cerr and carries on from.
 template <class ST>
 bool DeserializeFromFile(const std::string& path, Ciphertext<DCRTPoly>& ct, const ST&) {
-    std::lock_guard<std::mutex> g(detail::table_mutex());
-    auto it = detail::table().find(path);
-    if (it == detail::table().end()) return false;
-    ct = it->second;
-    return true;
+    {
+        std::lock_guard<std::mutex> g(detail::table_mutex());
+        auto it = detail::table().find(path);
+        if (it != detail::table().end()) { ct = it->second; return true; }
+    }
+    // no resident handle under this path: read the file into the current context (a process that started from serial/*.bin) and
+    // keep it resident from then on -- the reference re-reads it on every query, the arithmetic that follows is the same
+    std::shared_ptr<shim::Backend> be = shim::Backend::current();
+    if (!shim::Backend::serial_files() || !be) return false;
+    try {
+        std::ifstream is(path, std::ios::in | std::ios::binary);
+        if (!is.is_open()) return false;
+        hxser::Session ses;
+        ses.P = hxser::params_of(be->ctx);
+        ses.have_params = true;
+        hxser::Reader r(is);
+        hxser::HostCt h = hxser::read_ciphertext(r, ses);
+        Ciphertext<DCRTPoly> fresh = std::make_shared<CiphertextImpl<DCRTPoly>>(
+            be, shim::check(hx_ct_upload(be->ctx, h.ncomp, h.nl, h.data.data(), h.level, h.deg), "DeserializeFromFile"));
+        if (!SerializeToFileResident(path, fresh)) return false;
+        std::lock_guard<std::mutex> g(detail::table_mutex());
+        ct = detail::table()[path];
+        return true;
+    } catch (const std::exception& e) {
+        std::cerr << "DeserializeFromFile(" << path << "): " << e.what() << std::endl;
+        return false;
+    }
 }
-// Context and key pair (src/main.cpp:122-134, 246-249): nothing to move, the objects are process resident.
-template <class ST> bool SerializeToFile(const std::string&, const CryptoContext<DCRTPoly>& cc, const ST&) { return bool(cc); }
-template <class ST> bool SerializeToFile(const std::string&, const PublicKey<DCRTPoly>& k, const ST&) { return bool(k); }
-template <class ST> bool SerializeToFile(const std::string&, const PrivateKey<DCRTPoly>& k, const ST&) { return bool(k); }
-template <class ST> bool DeserializeFromFile(const std::string&, CryptoContext<DCRTPoly>&, const ST&) { return false; }
-template <class ST> bool DeserializeFromFile(const std::string&, PublicKey<DCRTPoly>&, const ST&) { return false; }
-template <class ST> bool DeserializeFromFile(const std::string&, PrivateKey<DCRTPoly>&, const ST&) { return false; }
+// Context and key pair (src/main.cpp:122-134, 246-249).  Default: nothing to move, the objects are process resident, and reading
+// them back fails as a missing file would.  HYDIA_SHIM_SERIAL_FILES=1: real files (shim/hx_serial.h) -- the context as its
+// parameter block, the public key as CryptoObject + (b, a), the private key as CryptoObject + its N coefficients in {-1,0,1}
+// (one byte each; upstream stores the key as a DCRTPoly: DEVIATION).
+template <class ST> bool SerializeToFile(const std::string& path, const CryptoContext<DCRTPoly>& cc, const ST&) {
+    if (!cc || !shim::Backend::serial_files()) return bool(cc);
+    try {
+        hxser::Session ses; ses.P = hxser::params_of(cc->backend()->ctx); ses.have_params = true;
+        std::ofstream os(path, std::ios::out | std::ios::binary);
+        hxser::Writer w(os);
+        hxser::write_context(w, ses);
+        return os.is_open() && w.good();
+    } catch (const std::exception& e) { std::cerr << "SerializeToFile(" << path << "): " << e.what() << std::endl; return false; }
+}
+template <class ST> bool SerializeToFile(const std::string& path, const PublicKey<DCRTPoly>& k, const ST&) {
+    if (!k || !shim::Backend::serial_files()) return bool(k);
+    try {
+        hxser::Session ses; ses.P = hxser::params_of(k->be->ctx); ses.have_params = true;
+        const size_t words = (size_t)ses.P.L * ses.P.N;
+        std::vector<uint64_t> ba(2 * words);
+        shim::check(hx_client_export_public(k->be->client, ba.data(), ba.data() + words), "SerializeToFile(PublicKey)");
+        std::ofstream os(path, std::ios::out | std::ios::binary);
+        hxser::Writer w(os);
+        w.shared_fresh();
+        w.version(hxser::C_PUBKEY, hxser::kVerKey);
+        hxser::write_object_base(w, ses);
+        w.size(2);
+        hxser::write_dcrt(w, ses, hxser::first_limbs(ses.P.L), ba.data());
+        hxser::write_dcrt(w, ses, hxser::first_limbs(ses.P.L), ba.data() + words);
+        return os.is_open() && w.good();
+    } catch (const std::exception& e) { std::cerr << "SerializeToFile(" << path << "): " << e.what() << std::endl; return false; }
+}
+template <class ST> bool SerializeToFile(const std::string& path, const PrivateKey<DCRTPoly>& k, const ST&) {
+    if (!k || !shim::Backend::serial_files()) return bool(k);
+    try {
+        hxser::Session ses; ses.P = hxser::params_of(k->be->ctx); ses.have_params = true;
+        std::vector<int8_t> sk((size_t)ses.P.N);
+        shim::check(hx_client_secret(k->be->client, sk.data()), "SerializeToFile(PrivateKey)");
+        std::ofstream os(path, std::ios::out | std::ios::binary);
+        hxser::Writer w(os);
+        w.shared_fresh();
+        w.version(hxser::C_PRIVKEY, hxser::kVerKey);
+        hxser::write_object_base(w, ses);
+        w.size(sk.size());
+        w.raw(sk.data(), sk.size());
+        return os.is_open() && w.good();
+    } catch (const std::exception& e) { std::cerr << "SerializeToFile(" << path << "): " << e.what() << std::endl; return false; }
+}
+template <class ST> bool DeserializeFromFile(const std::string& path, CryptoContext<DCRTPoly>& cc, const ST&) {
+    if (!shim::Backend::serial_files()) return false;
+    try {
+        std::ifstream is(path, std::ios::in | std::ios::binary);
+        if (!is.is_open()) return false;
+        hxser::Session ses;
+        hxser::Reader r(is);
+        hxser::read_context(r, ses);
+        cc = std::make_shared<CryptoContextImpl<DCRTPoly>>(shim::backend_from_params(ses.P));
+        return true;
+    } catch (const std::exception& e) { std::cerr << "DeserializeFromFile(" << path << "): " << e.what() << std::endl; return false; }
+}
+template <class ST> bool DeserializeFromFile(const std::string& path, PublicKey<DCRTPoly>& k, const ST&) {
+    std::shared_ptr<shim::Backend> be = shim::Backend::current();
+    if (!shim::Backend::serial_files() || !be) return false;
+    try {
+        std::ifstream is(path, std::ios::in | std::ios::binary);
+        if (!is.is_open()) return false;
+        hxser::Session ses; ses.P = hxser::params_of(be->ctx); ses.have_params = true;
+        hxser::Reader r(is);
+        bool fresh;
+        r.shared(&fresh);
+        r.version(hxser::C_PUBKEY, hxser::kVerKey);
+        hxser::read_object_base(r, ses);
+        if (r.size(2) != 2) return false;
+        std::vector<int> limbs;
+        be->pending_pkb.clear(); be->pending_pka.clear();
+        hxser::read_dcrt(r, ses, limbs, be->pending_pkb);
+        hxser::read_dcrt(r, ses, limbs, be->pending_pka);
+        k = std::make_shared<PublicKeyImpl<DCRTPoly>>(PublicKeyImpl<DCRTPoly>{be});
+        return (int)limbs.size() == ses.P.L;
+    } catch (const std::exception& e) { std::cerr << "DeserializeFromFile(" << path << "): " << e.what() << std::endl; return false; }
+}
+template <class ST> bool DeserializeFromFile(const std::string& path, PrivateKey<DCRTPoly>& k, const ST&) {
+    std::shared_ptr<shim::Backend> be = shim::Backend::current();
+    if (!shim::Backend::serial_files() || !be) return false;
+    try {
+        std::ifstream is(path, std::ios::in | std::ios::binary);
+        if (!is.is_open()) return false;
+        hxser::Session ses; ses.P = hxser::params_of(be->ctx); ses.have_params = true;
+        hxser::Reader r(is);
+        bool fresh;
+        r.shared(&fresh);
+        r.version(hxser::C_PRIVKEY, hxser::kVerKey);
+        hxser::read_object_base(r, ses);
+        std::vector<int8_t> sk(r.size(1 << 20));
+        r.raw(sk.data(), sk.size());
+        if ((int)sk.size() != ses.P.N || be->pending_pkb.empty()) return false;   // the reference reads the public key first (main.cpp:128-134)
+        if (be->client) { hx_client_destroy(be->client); be->client = nullptr; }
+        const char* seed = std::getenv("HYDIA_SEED");
+        be->client = shim::check(hx_client_import(be->ctx, seed ? std::strtoull(seed, nullptr, 10) : 1, sk.data(), be->pending_pkb.data(), be->pending_pka.data()),
+                                 "DeserializeFromFile(PrivateKey)");
+        k = std::make_shared<PrivateKeyImpl<DCRTPoly>>(PrivateKeyImpl<DCRTPoly>{be});
+        return true;
+    } catch (const std::exception& e) { std::cerr << "DeserializeFromFile(" << path << "): " << e.what() << std::endl; return false; }
+}
 }  // namespace Serial
 
 // OpenFHE prints vectors as "[ a b c ]" (src/main.cpp:388-389 streams the index results this way).

@@ -84,6 +84,47 @@ def test_reference_main_unmodified_approach5_2_10(tmp_path):
     print(r.stdout)
 
 
+@pytest.mark.gpu
+@pytest.mark.timeout(600)
+def test_shim_serial_roundtrip():
+    """SURVEY 8(f) item 2: SerType::BINARY files (shim/hx_serial.h) for ciphertexts, evaluation keys, context and key pair, written
+    by one context and read by a second one built from the serialised parameters: bit-identical (tests/cpp/shim_serial_roundtrip.cpp)."""
+    exe = os.path.join(ROOT, "shim", "_ref", "shim_serial_roundtrip")
+    if not os.path.exists(exe):
+        pytest.skip("shim self-test not built (python __graft_entry__.py)")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=550)
+    assert r.returncode == 0 and r.stdout.strip().endswith("OK"), (r.stdout[-800:], r.stderr[-1500:])
+
+
+@needs_exe
+@pytest.mark.gpu
+@pytest.mark.timeout(2400)
+def test_reference_second_run_reads_serial_files(tmp_path):
+    """READ_FROM_SERIAL (include/config.h:27, src/main.cpp:122-165): a first run of the unmodified main under
+    HYDIA_SHIM_SERIAL_FILES=1 writes serial/*.bin -- context, key pair, EvalMult / rotation / EvalSum keys, 512 database ciphertexts
+    (about 17 GB, as the real reference does) -- and the same main built with READ_FROM_SERIAL = true (shim/Makefile:
+    ImageMatchingFromSerial) answers the query from those files alone: no key generation, no enrollment."""
+    exe2 = os.path.join(os.path.dirname(EXE), "ImageMatchingFromSerial")
+    if not os.path.exists(exe2):
+        pytest.skip("ImageMatchingFromSerial not built")
+    import shutil
+    if shutil.disk_usage(str(tmp_path)).free < 40 << 30:
+        pytest.skip("less than 40 GB free for the serialised keys and database")
+    env = {"HYDIA_SHIM_SERIAL_FILES": "1"}
+    r = run_reference(tmp_path, 5, env=env, timeout=1100)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    assert parse(r.stdout) == ("true", [0])
+    sizes = {f: os.path.getsize(tmp_path / "serial" / f) for f in ("cryptocontext.bin", "publickey.bin", "privatekey.bin", "multkey.bin", "rotkey.bin", "sumkey.bin")}
+    assert sizes["rotkey.bin"] > 12 << 30 and sizes["multkey.bin"] > 24 << 20 and sizes["publickey.bin"] > 6 << 20, sizes
+    assert os.path.getsize(tmp_path / "serial" / "db_diagonal" / "index0.bin") > 6 << 20
+    r2 = subprocess.run([exe2, str(tmp_path / "data.dat"), "5"], cwd=str(tmp_path), capture_output=True, text=True, timeout=1100,
+                        env=dict(os.environ, **env))
+    assert r2.returncode == 0, (r2.stdout[-1500:], r2.stderr[-1500:])
+    assert "Error deserializing" not in r2.stderr and "Encrypting database vectors" not in r2.stdout
+    assert parse(r2.stdout) == ("true", [0])
+    shutil.rmtree(tmp_path / "serial", ignore_errors=True)
+
+
 @needs_exe
 @pytest.mark.gpu
 @pytest.mark.timeout(1500)

@@ -359,8 +359,13 @@ def run_b200(args):
             prof_all = cc.prof_read()
             dominant = max(prof_all, key=lambda k: prof_all[k]["ms"])
             cc.prof_enable([])
-        for _ in range(max(0, warmup - (1 if profile else 0))):
-            step(q_res, False)
+        nw = max(0, warmup - (1 if profile else 0))
+        for i in range(nw):
+            if i == nw - 1:   # the last warm-up step takes the end-to-end route (pinned upload, results to host) so that arm is warm too
+                step(upload_query_from_host(), True)
+            else:
+                step(q_res, False)
+            cc.sync()
         cc.sync()
         if profile:
             cc.prof_reset()
@@ -373,12 +378,19 @@ def run_b200(args):
             launches = 0
             out = None
             per_half = []
+            prof = {dominant: {"launches": 0, "ms": 0.0, "bytes": 0.0}} if profile else {}
             for n in halves:
                 l0 = cc.launches()
+                p0 = cc.prof_read()[dominant] if profile else None
                 a, b, out = timed(n, False)
                 ms_v += a; wall_v += b
                 launches += cc.launches() - l0
                 if profile:
+                    # launches and bytes count whether or not the family is being timed, its milliseconds only while it is:
+                    # take all three as differences around the value half, so that they describe the same launches
+                    p1 = cc.prof_read()[dominant]
+                    for k in ("launches", "ms", "bytes"):
+                        prof[dominant][k] += p1[k] - p0[k]
                     cc.prof_enable([])      # the dominant family is timed in the value halves only
                 a2, b2, _ = timed(n, True)
                 ms_e += a2; wall_e += b2
@@ -394,7 +406,6 @@ def run_b200(args):
             if profile:
                 cc.prof_reset()
                 cc.prof_enable([dominant])
-        prof = cc.prof_read() if profile else {}
         if profile:
             cc.prof_enable([])
         fence()

@@ -194,7 +194,9 @@ struct MdwArgs {
     size_t in_bs, out_bs;      // words between batch entries
     int ext_nl, L;             // ext_nl < 0: ModDown positions
 };
-template <int LOGN>
+// NIN: the number of source limbs when every table of the launch has that many (the conversion's multiply-accumulates are then
+// straight-line code the scheduler can interleave; with a run-time count each one sits behind its own branch), 0 = read it from the table.
+template <int LOGN, int NIN>
 __global__ void __launch_bounds__(256, LOGN <= 15 ? HX_MDW_MINB : 2) k_moddown_w(const __grid_constant__ DevTables T, const __grid_constant__ MdwArgs A,
                                                                        const u64* in, u64* out) {
     using W = WGeo<LOGN>;
@@ -202,7 +204,7 @@ __global__ void __launch_bounds__(256, LOGN <= 15 ? HX_MDW_MINB : 2) k_moddown_w
     extern __shared__ __align__(16) u64 smw[];
     const int dgt = blockIdx.y % A.ndig, entry = blockIdx.y / A.ndig;
     const BaseConvTable* __restrict__ tab = A.tab[dgt];
-    const int n_in = tab->n_in, n_out = tab->n_out;
+    const int n_in = NIN ? NIN : tab->n_in, n_out = tab->n_out;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     u64* const stage = smw;                                                   // [n_in][GROUPS][ROWS][WCOLS], 30-bit split words
     u64* const xch = smw + (size_t)n_in * W::STAGE_WORDS + warp * W::XWORDS;  // this warp's exchange buffer
@@ -246,17 +248,18 @@ __global__ void __launch_bounds__(256, LOGN <= 15 ? HX_MDW_MINB : 2) k_moddown_w
         const int prime = tab->dst[j];
         const PrimeConst pc = T.pc[prime];
         const u64 q = pc.q;
-        u64 mk[7];
+        constexpr int KM = NIN ? NIN : 7;
+        u64 mk[KM];
 #pragma unroll
-        for (int k = 0; k < 7; k++) mk[k] = k < n_in ? tab->mat30[k * n_out + j] : 0ull;
+        for (int k = 0; k < KM; k++) mk[k] = (NIN || k < n_in) ? tab->mat30[k * n_out + j] : 0ull;
         const u64* st = stage + ((size_t)g * W::ROWS) * W::WCOLS + lane;
         u64 r[16];
 #pragma unroll
         for (int rh = 0; rh < 16; rh++) {
             acc3 acc = {0, 0, 0};
 #pragma unroll
-            for (int k = 0; k < 7; k++)
-                if (k < n_in) mac30ss(acc, st[(size_t)k * W::STAGE_WORDS + rh * W::NR * W::WCOLS], mk[k]);
+            for (int k = 0; k < KM; k++)
+                if (NIN || k < n_in) mac30ss(acc, st[(size_t)k * W::STAGE_WORDS + rh * W::NR * W::WCOLS], mk[k]);
             r[rh] = redc_lazy(fold30(acc), q, pc.qinv_neg);       // in [0, 2q): sum of <= 7 products below 2^60 q
         }
         const int pos = A.ext_nl < 0 ? j : (prime < A.L ? prime : A.ext_nl + prime - A.L);
@@ -303,29 +306,40 @@ __global__ void __launch_bounds__(256, LOGN <= 15 ? HX_MDW_MINB : 2) k_moddown_w
 
 bool moddown_w_supported(int logN, int n_in) { return (logN == 15 || logN == 16) && n_in >= 1 && n_in <= 7; }
 
+template <int LOGN, int NIN>
+static void init_tn() {
+    cudaError_t e = cudaFuncSetAttribute(k_moddown_w<LOGN, NIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)moddown_w_smem<LOGN>(NIN ? NIN : 7));
+    if (e != cudaSuccess) throw std::runtime_error(std::string("cudaFuncSetAttribute(k_moddown_w): ") + cudaGetErrorString(e));
+}
 template <int LOGN>
 static void init_t() {
-    cudaError_t e = cudaFuncSetAttribute(k_moddown_w<LOGN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)moddown_w_smem<LOGN>(7));
-    if (e != cudaSuccess) throw std::runtime_error(std::string("cudaFuncSetAttribute(k_moddown_w): ") + cudaGetErrorString(e));
+    init_tn<LOGN, 0>();
+    init_tn<LOGN, 4>();
 }
 void init_moddown_kernels(int logN) {
     if (logN == 15) init_t<15>();
     if (logN == 16) init_t<16>();
 }
-template <int LOGN>
-static void launch_t(const DevTables& T, const MdwArgs& A, int max_n_in, int nbatch, const u64* in, u64* out, cudaStream_t st) {
+// uniform_n_in: every table of the launch has max_n_in source limbs (the caller knows the digit sizes; the tables are device memory)
+template <int LOGN, int NIN>
+static void launch_tn(const DevTables& T, const MdwArgs& A, int max_n_in, int nbatch, const u64* in, u64* out, cudaStream_t st) {
     using W = WGeo<LOGN>;
-    launch_pdl(k_moddown_w<LOGN>, dim3((1u << W::B) / W::CTA_COLS, nbatch * A.ndig), dim3(256), moddown_w_smem<LOGN>(max_n_in), st, T, A, in, out);
+    launch_pdl(k_moddown_w<LOGN, NIN>, dim3((1u << W::B) / W::CTA_COLS, nbatch * A.ndig), dim3(256), moddown_w_smem<LOGN>(max_n_in), st, T, A, in, out);
 }
-static void launch_any(const DevTables& T, const MdwArgs& A, int max_n_in, int nbatch, const u64* in, u64* out, cudaStream_t st) {
-    if (T.logN == 15) launch_t<15>(T, A, max_n_in, nbatch, in, out, st);
-    else if (T.logN == 16) launch_t<16>(T, A, max_n_in, nbatch, in, out, st);
+template <int LOGN>
+static void launch_t(const DevTables& T, const MdwArgs& A, int max_n_in, bool uniform_n_in, int nbatch, const u64* in, u64* out, cudaStream_t st) {
+    if (uniform_n_in && max_n_in == 4) launch_tn<LOGN, 4>(T, A, max_n_in, nbatch, in, out, st);
+    else launch_tn<LOGN, 0>(T, A, max_n_in, nbatch, in, out, st);
+}
+static void launch_any(const DevTables& T, const MdwArgs& A, int max_n_in, bool uniform_n_in, int nbatch, const u64* in, u64* out, cudaStream_t st) {
+    if (T.logN == 15) launch_t<15>(T, A, max_n_in, uniform_n_in, nbatch, in, out, st);
+    else if (T.logN == 16) launch_t<16>(T, A, max_n_in, uniform_n_in, nbatch, in, out, st);
     else throw std::runtime_error("warp-task base conversion: unsupported ring dimension");
 }
 void launch_moddown_w(const DevTables& T, const BaseConvTable* tab, int n_in, int nbatch, const u64* in, size_t in_bs, u64* out, size_t out_bs, cudaStream_t st) {
     MdwArgs A{};
     A.tab[0] = tab; A.ndig = 1; A.in_bs = in_bs; A.out_bs = out_bs; A.ext_nl = -1; A.L = 0;
-    launch_any(T, A, n_in, nbatch, in, out, st);
+    launch_any(T, A, n_in, true, nbatch, in, out, st);
 }
 // ModUp's middle (EvalKeySwitchPrecomputeCore): scratch [nbatch][nl][N] (inverse row pass done) -> the converted limbs of every
 // digit of digits [nbatch][ndig][nl+K][N] (forward column pass done; k_modup_rows finishes them and copies the digit's own limbs)
@@ -333,15 +347,16 @@ void launch_modup_w(const DevTables& T, const ModUpArgs& m, cudaStream_t st) {
     const int ext = m.nl + m.K;
     MdwArgs A{};
     A.ndig = m.ndig; A.in_bs = (size_t)m.nl * T.N; A.out_bs = (size_t)m.ndig * ext * T.N; A.ext_nl = m.nl; A.L = m.L;
-    int max_in = 1;
+    int max_in = 1, min_in = 1 << 30;
     for (int d = 0; d < m.ndig; d++) {
         const int lo = d * m.alpha, hi = (d == m.ndig - 1) ? m.nl : (d + 1) * m.alpha;
         A.tab[d] = m.tabs[d];
         A.in_off[d] = (size_t)lo * T.N;
         A.out_off[d] = (size_t)d * ext * T.N;
         max_in = std::max(max_in, hi - lo);
+        min_in = std::min(min_in, hi - lo);
     }
-    launch_any(T, A, max_in, m.nbatch, m.scratch, m.digits, st);
+    launch_any(T, A, max_in, min_in == max_in, m.nbatch, m.scratch, m.digits, st);
 }
 
 }  // namespace hx

@@ -46,6 +46,7 @@ SIGNATURES = {
     "hx_ct_info": (C.c_int, [VP, I32P, I32P, I32P, I32P]),
     "hx_ct_clone": (VP, [VP]),
     "hx_ct_download_many": (C.c_int, [C.POINTER(VP), C.c_int, VP]),
+    "hx_rescale_noalloc": (C.c_int, [VP, VP, C.c_int, C.c_int, VP]),
     "hx_ct_free": (None, [VP]),
     "hx_add": (VP, [VP, VP]),
     "hx_sub": (VP, [VP, VP]),

@@ -6,6 +6,7 @@
 #include "hx_engine.h"
 
 using namespace hx;
+namespace hx { void rescale_noalloc(Engine& e, const u64* in, int ncomp, int nl, u64* out); }   // hx_noalloc.cu
 
 struct hx_ctx { std::shared_ptr<Engine> eng; };
 struct hx_ct { Ct ct; };
@@ -453,4 +454,7 @@ hx_client* hx_client_import(hx_ctx* ctx, uint64_t seed, const int8_t* sk, const 
 }
 int hx_client_secret(hx_client* c, int8_t* out) { HX_TRY_INT(need(c, "client"); need(out, "out"); c->cl->secret(out);) }
 
+int hx_rescale_noalloc(hx_ctx* ctx, const uint64_t* d_in, int ncomp, int nlimbs, uint64_t* d_out) {
+    HX_TRY_INT(need(ctx, "ctx"); rescale_noalloc(*ctx->eng, (const u64*)d_in, ncomp, nlimbs, (u64*)d_out);)
+}
 }  // extern "C"

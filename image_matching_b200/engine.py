@@ -248,6 +248,10 @@ class CryptoContext:
         ptr, words, nb = C.c_void_p(), C.c_uint64(), C.c_int()
         check_int(self._lib.hx_ct_device_view(ct._h, C.byref(ptr), C.byref(words), C.byref(nb)))
         return int(ptr.value), int(words.value), int(nb.value)
+    def rescale_noalloc(self, in_ptr: int, ncomp: int, nl: int, out_ptr: int):
+        """hx_rescale_noalloc: Rescale on caller-owned device buffers ([ncomp][nl][N] -> [ncomp][nl-1][N]) with the scratch in a
+        static device array of the library; allocates nothing, queued on the engine stream."""
+        check_int(self._lib.hx_rescale_noalloc(self._h, C.c_void_p(in_ptr), int(ncomp), int(nl), C.c_void_p(out_ptr)))
     def stream_order(self, stream: int, engine_waits: bool): check_int(self._lib.hx_stream_order(self._h, C.c_void_p(stream), 1 if engine_waits else 0))
     def stack(self, cts: Sequence[Ciphertext]) -> Ciphertext:
         """n ciphertexts of one shape -> one batched handle (hx_ct_stack); every Eval* call then works on all entries at once."""

@@ -214,6 +214,20 @@ int hx_key_export(hx_ctx* ctx, uint32_t galois, uint64_t* a, uint64_t* b);
 int hx_client_export_public(hx_client* c, uint64_t* pkb, uint64_t* pka);
 hx_client* hx_client_import(hx_ctx* ctx, uint64_t seed, const int8_t* sk, const uint64_t* pkb, const uint64_t* pka);
 
+/* ---- allocation-free variant ----------------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  hx_rescale_noalloc is hx_rescale (RescaleInPlace,
+ * the same four kernels) on device buffers the caller owns: d_in = [ncomp][nlimbs][N] residues in evaluation form, d_out =
+ * [ncomp][nlimbs-1][N], both on the context's GPU and not overlapping.  It calls no cudaMalloc / cudaFree / allocating library
+ * routine and creates no handle: its scratch (the dropped limb's coefficients, the converted limbs, the 1-limb conversion table)
+ * is a file-scope __device__ array of HX_NOALLOC_MAX_WORDS 64-bit words (+ 4 KiB) that every GPU loading the library holds until
+ * the process exits.  ncomp * nlimbs * N above that limit is rejected with an error (use hx_rescale).  The work is queued on
+ * the context's engine stream like every other call (hx_ctx_sync / hx_stream_order to consume d_out elsewhere).  The array is
+ * shared by all calls and contexts on a device and keeps the last call's contents; nothing in it needs clearing, but calls that
+ * overlap on the GPU (two contexts on one device) race on it. */
+#define HX_NOALLOC_MAX_WORDS (1u << 21) /* 16 MiB: 2 components x 16 limbs at N = 2^16, 2 x 32 limbs at N = 2^15 */
+int hx_rescale_noalloc(hx_ctx* ctx, const uint64_t* d_in, int ncomp, int nlimbs, uint64_t* d_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -251,6 +251,8 @@ def run_b200(args):
                     ("rot_lane", args.rot_lane)):
         if v >= 0:
             cc.set_option(name, v)
+    for kv in filter(None, os.environ.get("HYDIA_ENGINE_OPTS", "").split(",")):   # diagnostic: any hx_ctx_set_option pair, name=value
+        cc.set_option(kv.split("=")[0], int(kv.split("=")[1]))
     slots = cc.GetBatchSize()
     cl = hx.Client(cc, seed=1)                     # same seed on every rank: replicated key set
     cl.EvalMultKeyGen()
@@ -323,12 +325,25 @@ def run_b200(args):
         idx_host = torch.empty((total_blocks, res_words), dtype=torch.int64).pin_memory()
         mem_host = torch.empty(res_words, dtype=torch.int64).pin_memory()
 
+        e2e_parts = os.environ.get("HYDIA_BENCH_E2E_PARTS", "ud")   # diagnostic: "u" = upload only, "d" = download only
+        trace2 = os.environ.get("HYDIA_BENCH_TRACE") == "2"
+        trace = os.environ.get("HYDIA_BENCH_TRACE") == "1"   # host-clock phases of the end-to-end step on rank 0 (diagnostic)
+
         def step(q, to_host):
+            t = [time.perf_counter()]
             m = snd.membershipScenario([q])
+            t.append(time.perf_counter())
             idx = snd.indexScenario([q])
+            t.append(time.perf_counter())
             if to_host and rank == 0:
                 m.download_ptr(mem_host.data_ptr())
+                t.append(time.perf_counter())
                 cc.download_many_ptr(idx, idx_host.data_ptr())
+                t.append(time.perf_counter())
+            if trace and rank == 0:
+                print("trace to_host=%d issue_membership %.2f issue_index %.2f" % (to_host, (t[1] - t[0]) * 1e3, (t[2] - t[1]) * 1e3)
+                      + (" wait+download_membership %.2f download_index %.2f" % ((t[3] - t[2]) * 1e3, (t[4] - t[3]) * 1e3) if len(t) > 3 else ""),
+                      file=sys.stderr, flush=True)
             return m, idx
 
         def timed(nsteps, e2e):
@@ -337,9 +352,21 @@ def run_b200(args):
             cc.timer_start()
             out = None
             for _ in range(nsteps):
-                q = upload_query_from_host() if e2e else q_res
-                out = step(q, e2e)
+                if trace2:
+                    cc.trace_start()
+                ta = time.perf_counter()
+                q = upload_query_from_host() if (e2e and "u" in e2e_parts) else q_res
+                tb = time.perf_counter()
+                out = step(q, e2e and "d" in e2e_parts)
+                tc = time.perf_counter()
                 cc.sync()   # a step is one query's latency: the next query starts when this one's results are complete
+                if trace2:
+                    cc.trace_mark("step_end")
+                    mk = cc.trace_dump()
+                    print("timeline timed e2e=%d rank %d: %s" % (e2e, rank, json.dumps({k: [round(x, 1) for x in v] for k, v in mk.items()})), file=sys.stderr, flush=True)
+                if trace and rank == 0:
+                    print("trace e2e=%d upload %.2f step %.2f sync %.2f" % (e2e, (tb - ta) * 1e3, (tc - tb) * 1e3, (time.perf_counter() - tc) * 1e3),
+                          file=sys.stderr, flush=True)
             cc.sync()
             torch.cuda.synchronize()
             ms = cc.timer_stop()
@@ -411,7 +438,7 @@ def run_b200(args):
         fence()
         return {"sec": ms_v / steps / 1e3, "sec_e2e": ms_e / steps / 1e3, "wall_sec": wall_v / steps / 1e3, "wall_sec_e2e": wall_e / steps / 1e3,
                 "halves_ms": [[round(x, 3) for x in h] for h in per_half], "remeasured": remeasured,
-                "launches": launches, "prof": prof, "prof_all": prof_all, "dominant": dominant, "out": out, "n_total": n_total, "snd": snd}
+                "launches": launches, "prof": prof, "prof_all": prof_all, "dominant": dominant, "out": out, "n_total": n_total, "snd": snd, "q_res": q_res, "mem_host": mem_host, "idx_host": idx_host}
 
     expected_index = enroll(args.total_blocks)
     sampler = ClockSampler(local)
@@ -420,6 +447,23 @@ def run_b200(args):
     sampler.stop_flag = True
     sampler.join(timeout=2)
     m, idx = r["out"]
+
+    if os.environ.get("HYDIA_BENCH_TRACE") == "1":
+        # one more step with the engine's timeline marks on: where a step's time goes on this rank (ms since the step's start)
+        for route in ("value", "e2e"):
+            fence()
+            cc.trace_start()
+            qn = upload_query_from_host() if route == "e2e" else r["q_res"]
+            tm, ti = r["snd"].membershipScenario([qn]), r["snd"].indexScenario([qn])
+            if route == "e2e" and rank == 0:
+                tm.download_ptr(r["mem_host"].data_ptr())
+                cc.download_many_ptr(ti, r["idx_host"].data_ptr())
+            cc.trace_mark("step_end")
+            marks = cc.trace_dump()
+            del tm, ti, qn
+            print("timeline %s rank %d: %s" % (route, rank, json.dumps({k: [round(x, 2) for x in v] for k, v in marks.items()})),
+                  file=sys.stderr, flush=True)
+        fence()
 
     if args.ncu_range:
         fence()

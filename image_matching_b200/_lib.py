@@ -46,6 +46,9 @@ SIGNATURES = {
     "hx_ct_info": (C.c_int, [VP, I32P, I32P, I32P, I32P]),
     "hx_ct_clone": (VP, [VP]),
     "hx_ct_download_many": (C.c_int, [C.POINTER(VP), C.c_int, VP]),
+    "hx_trace_start": (C.c_int, [VP]),
+    "hx_trace_mark": (C.c_int, [VP, C.c_char_p, VP]),
+    "hx_trace_dump": (C.c_int, [VP, C.c_char_p, C.c_int]),
     "hx_rescale_noalloc": (C.c_int, [VP, VP, C.c_int, C.c_int, VP]),
     "hx_ct_free": (None, [VP]),
     "hx_add": (VP, [VP, VP]),

@@ -454,6 +454,17 @@ hx_client* hx_client_import(hx_ctx* ctx, uint64_t seed, const int8_t* sk, const 
 }
 int hx_client_secret(hx_client* c, int8_t* out) { HX_TRY_INT(need(c, "client"); need(out, "out"); c->cl->secret(out);) }
 
+int hx_trace_start(hx_ctx* ctx) { HX_TRY_INT(need(ctx, "ctx"); ctx->eng->trace_start();) }
+int hx_trace_mark(hx_ctx* ctx, const char* name, void* stream) {
+    HX_TRY_INT(need(ctx, "ctx"); need(name, "name"); ctx->eng->trace_mark(name, (cudaStream_t)stream);)
+}
+int hx_trace_dump(hx_ctx* ctx, char* out, int cap) {
+    HX_TRY_INT(need(ctx, "ctx"); need(out, "out");
+               std::string s = ctx->eng->trace_dump();
+               if (cap < 1) throw std::runtime_error("hx_trace_dump: empty buffer");
+               std::strncpy(out, s.c_str(), (size_t)cap - 1);
+               out[cap - 1] = 0;)
+}
 int hx_rescale_noalloc(hx_ctx* ctx, const uint64_t* d_in, int ncomp, int nlimbs, uint64_t* d_out) {
     HX_TRY_INT(need(ctx, "ctx"); rescale_noalloc(*ctx->eng, (const u64*)d_in, ncomp, nlimbs, (u64*)d_out);)
 }

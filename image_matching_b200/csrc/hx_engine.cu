@@ -1,4 +1,6 @@
 // hx_engine.cu -- Engine: context tables, memory, keys, and the primitive evaluation ops.
+#include <cstdlib>
+#include <cstring>
 #include "hx_engine.h"
 
 #include <algorithm>
@@ -107,6 +109,9 @@ Engine::~Engine() {
     for (auto s : lane_streams) if (s) { cudaStreamSynchronize(s); cudaStreamDestroy(s); }
     for (auto ev : aux_events) if (ev) cudaEventDestroy(ev);
     for (auto ev : lane_events) if (ev) cudaEventDestroy(ev);
+    if (mac_gate_) cudaEventDestroy(mac_gate_);
+    if (trace_origin) cudaEventDestroy(trace_origin);
+    for (auto& r : trace_recs) cudaEventDestroy(r.ev);
     cudaStreamDestroy(st_main);
 }
 
@@ -134,6 +139,41 @@ Engine::Scope::Scope(Engine* e_, int kind_, int nlaunch, double bytes) : e(e_), 
 }
 Engine::Scope::~Scope() {
     if (b) cudaEventRecord(b, e->st);
+}
+void Engine::trace_start() {
+    Guard g(this);
+    if (!trace_origin) HX_CUDA(cudaEventCreate(&trace_origin));
+    for (auto& r : trace_recs) cudaEventDestroy(r.ev);
+    trace_recs.clear();
+    HX_CUDA(cudaEventRecord(trace_origin, st_main));
+    trace_on = true;
+}
+void Engine::trace_mark(const char* name, cudaStream_t s) {
+    if (!trace_on) return;
+    static const char* filter = std::getenv("HYDIA_TRACE_FILTER");   // diagnostic: comma list of the marks to keep
+    if (filter && !std::strstr(filter, name)) return;
+    Guard g(this);
+    TraceRec r;
+    r.name = name;
+    HX_CUDA(cudaEventCreate(&r.ev));
+    HX_CUDA(cudaEventRecord(r.ev, s ? s : st));
+    trace_recs.push_back(std::move(r));
+}
+std::string Engine::trace_dump() {
+    Guard g(this);
+    std::string out;
+    for (auto& r : trace_recs) {
+        float ms = -1.f;
+        HX_CUDA(cudaEventSynchronize(r.ev));   // each mark on its own stream: no device-wide synchronisation that would hide a stall
+        cudaEventElapsedTime(&ms, trace_origin, r.ev);
+        char buf[64];
+        snprintf(buf, sizeof buf, ":%.3f;", ms);
+        out += r.name + buf;
+        cudaEventDestroy(r.ev);
+    }
+    trace_recs.clear();
+    trace_on = false;
+    return out;
 }
 void Engine::prof_enable(unsigned mask) {
     Guard g(this);

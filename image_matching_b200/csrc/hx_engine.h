@@ -107,6 +107,15 @@ public:
         Scope(Engine* e, int kind, int nlaunch, double bytes);
         ~Scope();
     };
+    // ---- timeline marks (diagnostic; off by default): named CUDA events recorded on a stream, dumped as "name:ms;..." relative to
+    // the mark that switched the trace on.  Used to name the limiter of a multi-GPU step without a system profiler.
+    struct TraceRec { std::string name; cudaEvent_t ev; };
+    bool trace_on = false;
+    cudaEvent_t trace_origin = nullptr;
+    std::vector<TraceRec> trace_recs;
+    void trace_start();
+    void trace_mark(const char* name, cudaStream_t s);   // no-op unless the trace is on
+    std::string trace_dump();                            // synchronises the device, ends the trace
     void prof_enable(unsigned mask);
     void prof_reset();
     void prof_collect();                     // sync + fold event pairs into prof_ms
@@ -193,6 +202,7 @@ public:
     // (tools/race_probe.py, profiles/r2_race_*.log), none with the buffer never recycled.
     struct RotSlot { u64* d = nullptr; size_t words = 0; bool busy = false; cudaEvent_t released = nullptr; bool has_release = false; };
     std::vector<RotSlot> rot_slots_;
+    cudaEvent_t mac_gate_ = nullptr;                           // see mac_rotset
     int rot_slot_acquire(size_t words, cudaStream_t writer);   // returns the slot index; `writer` waits for the slot's last reader
     void rot_slot_release(int slot);                           // records the release event on the engine stream
     std::shared_ptr<RotSet> rotate_hoisted_all(const Ct& query, int ndiag) { return rotate_hoisted_range(query, 0, ndiag); }   // sender_diag.cpp:20-26

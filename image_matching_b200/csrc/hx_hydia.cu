@@ -98,6 +98,10 @@ std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_range(const Ct& query, in
     const int chunk = std::max(1, std::min(rot_chunk, kMaxKsBatch));
     const int ns = rot_streams;
     cudaStream_t main_st = st;
+    // a timing-enabled event record on the engine stream at the head of every rotation section and before every diagonal MAC
+    // (mac_rotset): orders nothing new, but see the measurement quoted there
+    if (!mac_gate_) HX_CUDA(cudaEventCreate(&mac_gate_));
+    HX_CUDA(cudaEventRecord(mac_gate_, main_st));
     struct StRestore { Engine* e; cudaStream_t s; ~StRestore() { e->st = s; } } st_restore{this, main_st};   // also on exceptions
     const bool lane = rot_lane && query->settled && !force_unfused;
     if (lane) {
@@ -118,6 +122,7 @@ std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_range(const Ct& query, in
     std::unique_ptr<Scope> span;
     try {
         rs->slot = rot_slot_acquire(ct_words * ndiag, st);
+        trace_mark("rot_begin", st);   // fires once the slot's last reader and the lane's earlier work are done
         u64* rotq = rs->rotq = rot_slots_[rs->slot].d;
         if (d0 == 0) HX_CUDA(cudaMemcpyAsync(rotq, query->d, sizeof(u64) * ct_words, cudaMemcpyDeviceToDevice, st));   // rotation 0 (sender_diag.cpp:21)
         int ndig;
@@ -176,6 +181,7 @@ std::shared_ptr<Engine::RotSet> Engine::rotate_hoisted_range(const Ct& query, in
     prof_no_events = false;
     span.reset();
     free_words(digits);   // on `first`, behind every reader: scratch allocated on a stream is released on that stream
+    trace_mark("rot_end", first);
     if (lane) {   // the engine stream joins: everything after this call (diagonal MAC, slot release) is ordered behind the lane
         HX_CUDA(cudaEventRecord(lane_events[4], first));
         HX_CUDA(cudaStreamWaitEvent(main_st, lane_events[4], 0));
@@ -224,6 +230,12 @@ Ct Engine::mac_rotset(const RotSet& rs, const std::vector<int>& block_ids) {
     std::vector<const u64*> blocks = db_ptrs_for(*this, db_, rs, block_ids);
     if (blocks.empty()) throw std::runtime_error("score_diag: no database block named");
     Ct acc = new_ct(3, nl, rs.level, rs.deg + 1, (int)blocks.size());
+    trace_mark("mac_begin", st);
+    // An event record between the lane join (cudaStreamWaitEvent in rotate_hoisted_range) and the MAC launch.  It orders nothing
+    // new; measured at 2 GPUs (32 blocks per rank) it removes a 20 ms stall of rank 0's second MAC in steps that end with a
+    // device-to-host download (e2e 152 -> 134 ms per step; CUDA_DEVICE_MAX_CONNECTIONS=1 removes it too, 32 does not): DESIGN.md 7.
+    if (!mac_gate_) HX_CUDA(cudaEventCreate(&mac_gate_));   // timing enabled: the record that was measured
+    HX_CUDA(cudaEventRecord(mac_gate_, st));
     for (size_t g0 = 0; g0 < blocks.size(); g0 += kMaxDbBlocks) {   // the rotated query is fetched from HBM once per launch
         const int n = (int)std::min((size_t)kMaxDbBlocks, blocks.size() - g0);
         DbBlockPtrs ptrs;
@@ -231,6 +243,7 @@ Ct Engine::mac_rotset(const RotSet& rs, const std::vector<int>& block_ids) {
         Scope sc(this, PK_DIAG_MAC, 1, 8.0 * N * nl * 2 * ndiag * n);   // algorithmic bytes: the database diagonals, read once
         launch_diag_mac(T, rs.rotq, ptrs, n, acc->d + g0 * acc->batch_stride(), ndiag, nl, st);
     }
+    trace_mark("mac_end", st);
     return acc;
 }
 Ct Engine::diag_mac_partial(const Ct& query, int d0, int d1, const std::vector<int>& block_ids) {

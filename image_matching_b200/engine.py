@@ -248,6 +248,18 @@ class CryptoContext:
         ptr, words, nb = C.c_void_p(), C.c_uint64(), C.c_int()
         check_int(self._lib.hx_ct_device_view(ct._h, C.byref(ptr), C.byref(words), C.byref(nb)))
         return int(ptr.value), int(words.value), int(nb.value)
+    def trace_start(self): check_int(self._lib.hx_trace_start(self._h))
+    def trace_mark(self, name: str, stream: int = 0): check_int(self._lib.hx_trace_mark(self._h, name.encode(), C.c_void_p(stream or None)))
+    def trace_dump(self) -> dict:
+        """{mark name: [ms since trace_start, ...]} of the marks recorded since trace_start (hx_trace_dump; synchronises)."""
+        buf = C.create_string_buffer(1 << 16)
+        check_int(self._lib.hx_trace_dump(self._h, buf, len(buf)))
+        out = {}
+        for item in buf.value.decode().split(";"):
+            if item:
+                k, v = item.rsplit(":", 1)
+                out.setdefault(k, []).append(float(v))
+        return out
     def rescale_noalloc(self, in_ptr: int, ncomp: int, nl: int, out_ptr: int):
         """hx_rescale_noalloc: Rescale on caller-owned device buffers ([ncomp][nl][N] -> [ncomp][nl-1][N]) with the scratch in a
         static device array of the library; allocates nothing, queued on the engine stream."""

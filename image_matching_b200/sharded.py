@@ -37,6 +37,13 @@ def diag_range(rank: int, world: int, ndiag: int = VECTOR_DIM):
     return block_range(rank, world, ndiag)
 
 
+def _mark(cc, name, stream=0):
+    """Timeline mark on the context if it has the facility (the CPU contexts of the gloo tests do not)."""
+    f = getattr(cc, "trace_mark", None)
+    if f is not None:
+        f(name, stream)
+
+
 def block_range(rank: int, world: int, total_blocks: int):
     """Contiguous block partition: the first (total % world) ranks own one block more."""
     base, extra = divmod(total_blocks, world)
@@ -100,12 +107,15 @@ class TorchTransport:
         ncomp, nl, level, deg = acc.info()
         out = self.cc.alloc(ncomp, nl, level, deg, hi - lo)
         self.engine_to_exchange()
+        cur = int(self.torch.cuda.current_stream(self.device).cuda_stream)
+        _mark(self.cc, "exchange_begin", cur)   # timeline marks: no-ops unless a trace is on (hx_trace_start)
         src, dst = self.view(acc), self.view(out)
         if total % world == 0:
             dist.reduce_scatter_tensor(dst, src, op=dist.ReduceOp.SUM, group=group)
         else:
             dist.all_reduce(src, op=dist.ReduceOp.SUM, group=group)
             dst.copy_(src[lo:hi])
+        _mark(self.cc, "exchange_end", cur)
         self.exchange_to_engine()
         return out, acc   # acc must outlive the collective: the caller drops it after the engine stream has joined
 
@@ -159,13 +169,17 @@ class ShardedDiagonalSender(Sender):
             mine, keep = self.transport.reduce_scatter_blocks(self.dist, self.group, acc, lo, hi, total, self.world)
         cc.fold_mod(mine)                                                     # raw sums of `world` residues -> residues
         del keep, acc                                                         # freed in engine-stream order, behind the join
-        return cc.Rescale(cc.Relinearize(mine))                               # sender_diag.cpp:79-80 on my blocks, batched
+        score = cc.Rescale(cc.Relinearize(mine))                              # sender_diag.cpp:79-80 on my blocks, batched
+        _mark(cc, "score_end")
+        return score
 
     def _local_index(self, queryCipher):
         if self.shard == "blocks":
             return self.cc.index(queryCipher[0], VECTOR_DIM, MATCH_THRESHOLD, COMP_DEPTH)
         cc = self.cc
-        return cc.unstack(cc.compare(self.computeSimilarity(queryCipher), MATCH_THRESHOLD, COMP_DEPTH))
+        out = cc.unstack(cc.compare(self.computeSimilarity(queryCipher), MATCH_THRESHOLD, COMP_DEPTH))
+        _mark(cc, "compare_end")
+        return out
 
     def indexScenario(self, queryCipher) -> Optional[List]:
         """Rank 0 returns the G result ciphertexts in global block order; other ranks return None."""

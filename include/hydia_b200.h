@@ -214,6 +214,13 @@ int hx_key_export(hx_ctx* ctx, uint32_t galois, uint64_t* a, uint64_t* b);
 int hx_client_export_public(hx_client* c, uint64_t* pkb, uint64_t* pka);
 hx_client* hx_client_import(hx_ctx* ctx, uint64_t seed, const int8_t* sk, const uint64_t* pkb, const uint64_t* pka);
 
+/* ---- timeline marks (diagnostic, no counterpart in the reference): named CUDA events on a stream (NULL = the engine stream),
+ * dumped as "name:ms;name:ms;..." relative to hx_trace_start; hx_trace_dump waits for the marks' events (no device-wide synchronisation) and ends the trace.  The engine
+ * marks its own rotation lane (rot_begin / rot_end) and diagonal MAC (mac_begin / mac_end) while a trace is on. */
+int hx_trace_start(hx_ctx* ctx);
+int hx_trace_mark(hx_ctx* ctx, const char* name, void* stream);
+int hx_trace_dump(hx_ctx* ctx, char* out, int cap);
+
 /* ---- allocation-free variant ----------------------------------------------------------------------------------------
  * No counterpart in the reference: added for callers that cannot call cudaMalloc (code
  * under CUDA graph capture, tight serving loops, harnesses that forbid it).  hx_rescale_noalloc is hx_rescale (RescaleInPlace,

@@ -139,6 +139,7 @@ Client::Client(std::shared_ptr<Engine> e, u64 seed_) : keep(e), eng(e.get()), se
     // secret key: ternary, all L+K limbs, evaluation form
     HX_CUDA(cudaMalloc(&d_sk_small, sizeof(int) * N));
     k_sample_ternary<<<(N + kCT - 1) / kCT, kCT, 0, eng->st>>>(N, d_sk_small, seed, next_stream++);
+    check_launch("k_sample_ternary");
     HX_CUDA(cudaMalloc(&d_sk, sizeof(u64) * (size_t)np * N));
     std::vector<int> all;
     for (int i = 0; i < np; i++) all.push_back(i);
@@ -149,9 +150,11 @@ Client::Client(std::shared_ptr<Engine> e, u64 seed_) : keep(e), eng(e.get()), se
     HX_CUDA(cudaMalloc(&d_pka, sizeof(u64) * (size_t)eng->L * N));
     HX_CUDA(cudaMalloc(&d_pkb, sizeof(u64) * (size_t)eng->L * N));
     k_sample_uniform<<<grid1(N, eng->L), kCT, 0, eng->st>>>(eng->T, d_pka, eng->limb_map(qs), seed, next_stream++);
+    check_launch("k_sample_uniform");
     u64* e_rns = gauss_rns(qs);
     ScalarTable zero = eng->scalar_table(std::vector<u64>(eng->L, 0));
     k_ksgen_b<<<grid1(N, eng->L), kCT, 0, eng->st>>>(eng->T, d_pkb, d_pka, e_rns, d_sk, nullptr, zero);
+    check_launch("k_ksgen_b");
     eng->free_words(e_rns);
     eng->sync();
 }
@@ -194,7 +197,9 @@ void Client::small_to_rns(const int* d_small, u64* out, const std::vector<int>& 
     const int N = eng->N;
     long long* wide = (long long*)eng->alloc_words(N);
     k_widen<<<(N + kCT - 1) / kCT, kCT, 0, eng->st>>>(N, wide, d_small);
+    check_launch("k_widen");
     k_small_to_rns<<<grid1(N, (int)primes.size()), kCT, 0, eng->st>>>(eng->T, out, wide, eng->limb_map(primes));
+    check_launch("k_small_to_rns");
     eng->ntt_limbs(out, (int)primes.size(), primes, false);
     eng->free_words((u64*)wide);
 }
@@ -202,6 +207,7 @@ u64* Client::gauss_rns(const std::vector<int>& primes) {
     const int N = eng->N;
     int* small = (int*)eng->alloc_words(N / 2 + 1);
     k_sample_gauss<<<(N + kCT - 1) / kCT, kCT, 0, eng->st>>>(N, small, seed, next_stream++);
+    check_launch("k_sample_gauss");
     u64* out = eng->alloc_words((size_t)primes.size() * N);
     small_to_rns(small, out, primes);
     eng->free_words((u64*)small);
@@ -211,6 +217,7 @@ u64* Client::ternary_rns(const std::vector<int>& primes) {
     const int N = eng->N;
     int* small = (int*)eng->alloc_words(N / 2 + 1);
     k_sample_ternary<<<(N + kCT - 1) / kCT, kCT, 0, eng->st>>>(N, small, seed, next_stream++);
+    check_launch("k_sample_ternary");
     u64* out = eng->alloc_words((size_t)primes.size() * N);
     small_to_rns(small, out, primes);
     eng->free_words((u64*)small);
@@ -231,10 +238,12 @@ EvalKey Client::ks_keygen(const u64* s_old, const u64* s_new) {
         u64* aj = k.a + (size_t)j * np * N;
         u64* bj = k.b + (size_t)j * np * N;
         k_sample_uniform<<<grid1(N, np), kCT, 0, eng->st>>>(eng->T, aj, lm, seed, next_stream++);
+        check_launch("k_sample_uniform");
         u64* e = gauss_rns(all);
         std::vector<u64> fac(np, 0);
         for (int i = j * eng->alpha; i < eng->L && i < (j + 1) * eng->alpha; i++) fac[i] = eng->P_mod(i);
         k_ksgen_b<<<grid1(N, np), kCT, 0, eng->st>>>(eng->T, bj, aj, e, s_new, s_old, eng->scalar_table(fac));
+        check_launch("k_ksgen_b");
         eng->free_words(e);
     }
     eng->finish_key(k);
@@ -302,6 +311,7 @@ void Client::encode_rns(const double* values, int n, u64* host_out) {
     for (int i = 0; i < L; i++) qs.push_back(i);
     u64* m = eng->alloc_words((size_t)L * N);
     k_small_to_rns<<<grid1(N, L), kCT, 0, eng->st>>>(eng->T, m, d_small, eng->limb_map(qs));
+    check_launch("k_small_to_rns");
     eng->ntt_limbs(m, L, qs, false);
     HX_CUDA(cudaMemcpyAsync(host_out, m, sizeof(u64) * (size_t)L * N, cudaMemcpyDeviceToHost, eng->st));
     HX_CUDA(cudaStreamSynchronize(eng->st));
@@ -318,12 +328,14 @@ Ct Client::encrypt(const double* values, int n) {
     for (int i = 0; i < L; i++) qs.push_back(i);
     u64* m = eng->alloc_words((size_t)L * N);
     k_small_to_rns<<<grid1(N, L), kCT, 0, eng->st>>>(eng->T, m, d_small, eng->limb_map(qs));
+    check_launch("k_small_to_rns");
     eng->ntt_limbs(m, L, qs, false);
     u64* v = ternary_rns(qs);
     u64* e0 = gauss_rns(qs);
     u64* e1 = gauss_rns(qs);
     Ct ct = eng->new_ct(2, L, 0, 1);
     k_encrypt<<<grid1(N, L), kCT, 0, eng->st>>>(eng->T, ct->d, v, d_pkb, d_pka, e0, e1, m, L);
+    check_launch("k_encrypt");
     HX_CUDA(cudaStreamSynchronize(eng->st));   // coeffs (host) must outlive the copy
     eng->free_words(v); eng->free_words(e0); eng->free_words(e1); eng->free_words(m); eng->free_words((u64*)d_small);
     return ct;
@@ -340,6 +352,7 @@ void Client::decrypt(const Ct& ct, double* out) {
     const int N = eng->N, nl = ct->nl;
     u64* acc = eng->alloc_words((size_t)nl * N);
     k_decrypt<<<grid1(N, nl), kCT, 0, eng->st>>>(eng->T, acc, ct->d, ct->ncomp, ct->comp_stride(), d_sk);
+    check_launch("k_decrypt");
     std::vector<int> qs;
     for (int i = 0; i < nl; i++) qs.push_back(i);
     eng->ntt_limbs(acc, nl, qs, true);

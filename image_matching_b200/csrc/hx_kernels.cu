@@ -61,6 +61,7 @@ void launch_baseconv(const DevTables& T, const BaseConvTable* tab, int n_in, int
                      u64* out, size_t out_bs, int nbatch, cudaStream_t st) {
     dim3 grid(blocks_for(T.N), 1, nbatch);
     k_baseconv<<<grid, kThreads, 0, st>>>(T, tab, n_in, n_out, in, in_bs, out, out_bs);
+    check_launch("k_baseconv");
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -113,6 +114,7 @@ void launch_ks_inner(const DevTables& T, const u64* digits, int ndig, int nl, in
                      const u64* const* keyB, u64* out, size_t out_bs, int nbatch, cudaStream_t st) {
     dim3 grid(blocks_for(T.N), nl + K, nbatch);
     k_ks_inner<<<grid, kThreads, 0, st>>>(T, digits, ndig, nl, L, K, keyA, keyB, out, out_bs);
+    check_launch("k_ks_inner");
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -149,6 +151,7 @@ void launch_moddown_finish(const DevTables& T, const u64* ct, size_t ct_bs, cons
     dim3 grid(blocks_for(T.N), nl, nbatch * 2);
     int ext = (int)(ct_bs / (2 * (size_t)T.N));   // ct batch entry = [2][ext][N]
     k_moddown_finish<<<grid, kThreads, 0, st>>>(T, ct, ct_bs, conv, conv_bs, addend, addend_comps, maps, out, out_bs, nl, ext);
+    check_launch("k_moddown_finish");
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -341,6 +344,7 @@ __global__ void __launch_bounds__(kThreads) k_automorph(int N, u64* __restrict__
 void launch_automorph(const DevTables& T, u64* out, const u64* in, const u32* map, int nlimbs_total, cudaStream_t st) {
     dim3 grid((T.N + kThreads - 1) / kThreads, nlimbs_total, 1);
     k_automorph<<<grid, kThreads, 0, st>>>(T.N, out, in, map);
+    check_launch("k_automorph");
 }
 
 // PrecomputeAutoMap: map[brev(j)] = brev(((2j+1)*k mod 2N) >> 1).
@@ -355,6 +359,7 @@ __global__ void k_automap(int N, int logN, u64 k, u32* __restrict__ map) {
 }
 void launch_automap(int N, int logN, u64 k, u32* map, cudaStream_t st) {
     k_automap<<<(N + 255) / 256, 256, 0, st>>>(N, logN, k, map);
+    check_launch("k_automap");
 }
 
 // x -> x * 2^64 mod q (Montgomery form) for keys / database blocks at load time.
@@ -400,6 +405,7 @@ __global__ void __launch_bounds__(kThreads) k_key_finish(DevTables T, u64* __res
 }
 void launch_key_finish(const DevTables& T, u64* key, int dnum, int L, int K, const ScalarTable& pinv, cudaStream_t st) {
     k_key_finish<<<dim3(blocks_for(T.N), L + K, dnum), kThreads, 0, st>>>(T, key, L, K, pinv);
+    check_launch("k_key_finish");
 }
 __global__ void __launch_bounds__(kThreads) k_key_unfinish(DevTables T, u64* __restrict__ out, const u64* __restrict__ key, int L, int K, ScalarTable pmod) {
     const int idx = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
@@ -424,9 +430,11 @@ __global__ void __launch_bounds__(kThreads) k_key_unfinish(DevTables T, u64* __r
 }
 void launch_key_unfinish(const DevTables& T, u64* out, const u64* key, int dnum, int L, int K, const ScalarTable& pmod, cudaStream_t st) {
     k_key_unfinish<<<dim3(blocks_for(T.N), L + K, dnum), kThreads, 0, st>>>(T, out, key, L, K, pmod);
+    check_launch("k_key_unfinish");
 }
 void launch_split30(u64* data, size_t words, cudaStream_t st) {
     k_split30<<<(unsigned)((words / 2 + kThreads - 1) / kThreads), kThreads, 0, st>>>(data, words);
+    check_launch("k_split30");
 }
 void launch_to_mont(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, cudaStream_t st, bool inverse) {
     // nbatch must be a multiple of lm.period; split so grid.y stays a multiple of the period
@@ -434,6 +442,7 @@ void launch_to_mont(const DevTables& T, u64* data, int nbatch, const LimbMap& lm
     int groups = nbatch / per;
     dim3 grid(blocks_for(T.N), per, groups);
     k_to_mont<<<grid, kThreads, 0, st>>>(T, data, lm, inverse);
+    check_launch("k_to_mont");
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -459,6 +468,7 @@ void launch_rescale_prep(const DevTables& T, const u64* last, size_t last_bs, u6
                          const ScalarTable& negqlinv, int nbatch, cudaStream_t st) {
     dim3 grid(blocks_for(T.N), nl - 1, nbatch);
     k_rescale_prep<<<grid, kThreads, 0, st>>>(T, last, last_bs, tmp, tmp_bs, nl, negqlinv);
+    check_launch("k_rescale_prep");
 }
 __global__ void __launch_bounds__(kThreads) k_rescale_finish(DevTables T, u64* __restrict__ out, size_t out_bs, const u64* __restrict__ c, size_t c_bs,
                                                              const u64* __restrict__ tmp, size_t tmp_bs, ScalarTable s) {
@@ -477,6 +487,7 @@ void launch_rescale_finish(const DevTables& T, u64* out, size_t out_bs, const u6
                            int nl, const ScalarTable& qlinv, int nbatch, cudaStream_t st) {
     dim3 grid(blocks_for(T.N), nl - 1, nbatch);
     k_rescale_finish<<<grid, kThreads, 0, st>>>(T, out, out_bs, c, c_bs, tmp, tmp_bs, qlinv);
+    check_launch("k_rescale_finish");
 }
 
 // ---------------------------------------------------------------------------------------------

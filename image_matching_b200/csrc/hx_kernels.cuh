@@ -138,6 +138,11 @@ void launch_automorph(const DevTables& T, u64* out, const u64* in, const u32* ma
 void launch_automap(int N, int logN, u64 k, u32* map, cudaStream_t st);
 // Launch with programmatic stream serialization (the kernel's first statement must be pdl_wait()): hides the launch and
 // block-scheduling latency between the ~1000 small dependent kernels of a step.
+// after every <<<>>> launch: a failed launch (bad configuration, sticky error) surfaces at the call, not at the next synchronisation
+inline void check_launch(const char* kernel) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) throw std::runtime_error(std::string("kernel launch failed (") + kernel + "): " + cudaGetErrorString(e));
+}
 extern int g_pdl;   // 0: plain stream-ordered launches (hx_ctx_set_option "pdl"; diagnosis of launch-overlap hazards)
 template <class... KArgs, class... Args>
 inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {

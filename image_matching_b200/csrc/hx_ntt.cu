@@ -285,10 +285,14 @@ static void launch_ntt_t(const DevTables& T, u64* data, int nbatch, const LimbMa
     dim3 grid(NttGeo<LOGN>::TILES, nbatch);
     if (!inverse) {
         k_ntt_col_t<LOGN, false><<<grid, kTileThreads, 0, st>>>(T, data, lm);
+        check_launch("k_ntt_col_t");
         k_ntt_row_t<LOGN, false><<<grid, kTileThreads, 0, st>>>(T, data, lm);
+        check_launch("k_ntt_row_t");
     } else {
         k_ntt_row_t<LOGN, true><<<grid, kTileThreads, 0, st>>>(T, data, lm);
+        check_launch("k_ntt_row_t");
         k_ntt_col_t<LOGN, true><<<grid, kTileThreads, 0, st>>>(T, data, lm);
+        check_launch("k_ntt_col_t");
     }
 }
 
@@ -319,10 +323,14 @@ void launch_ntt(const DevTables& T, u64* data, int nbatch, const LimbMap& lm, bo
     dim3 grid_row(T.N >> g.logT, nbatch), grid_col(T.N >> g.logT, nbatch);
     if (!inverse) {
         if (g.A > 0) k_ntt_col<false><<<grid_col, threads, 0, st>>>(T, g, data, lm);
+        check_launch("k_ntt_col");
         k_ntt_row<false><<<grid_row, threads, 0, st>>>(T, g, data, lm);
+        check_launch("k_ntt_row");
     } else {
         k_ntt_row<true><<<grid_row, threads, 0, st>>>(T, g, data, lm);
+        check_launch("k_ntt_row");
         if (g.A > 0) k_ntt_col<true><<<grid_col, threads, 0, st>>>(T, g, data, lm);
+        check_launch("k_ntt_col");
     }
 }
 

@@ -273,18 +273,11 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_q_finish(const __g
         for (int j = 0; j < NDIG; j++) bulk_g2s(kst + j * kTileN, key + j * kstride, kTileBytes, mbar);
     }
     pdl_wait();      // the evaluation keys above are static; everything below reads the previous kernels' output
-#pragma unroll
-    for (int u = 0; u < 4; u++) {
-        const int e = (u * kTileThreads + t) * 2;
-        const ulonglong2 x = ldg128(cv + e);
-        smp[u * kPairStep] = x.x;
-        smp[u * kPairStep + 1] = x.y;
-    }
-    __syncthreads();
-    {   // forward row pass, one arithmetic back end per instantiation (the launch lists separate the limbs)
+    {   // forward row pass, one arithmetic back end per instantiation (the launch lists separate the limbs); its first round reads the
+        // converted tile straight from global memory
         using G = NttGeo<LOGN>;
-        if constexpr (FP) fwd_stages_fp<G::LOGD, kLogTile, G::A, G::LOGD>(reinterpret_cast<double*>(sm), t, tile, T.tw_fwd_d + (size_t)i * T.N, fp_from_u64(q));
-        else fwd_stages<G::LOGD, kLogTile, G::A, G::LOGD>(sm, t, tile, T.tw_fwd + (size_t)i * T.N, q, q << 2);
+        if constexpr (FP) fwd_stages_fp_g<G::LOGD, kLogTile, G::A, G::LOGD>(reinterpret_cast<double*>(sm), cv, t, tile, T.tw_fwd_d + (size_t)i * T.N, fp_from_u64(q));
+        else fwd_stages_g<G::LOGD, kLogTile, G::A, G::LOGD>(sm, cv, t, tile, T.tw_fwd + (size_t)i * T.N, q, q << 2);
     }
     const u64* add = (comp == 0 ? a.add0 : a.add1);
     if (add) add += (size_t)b * a.add_bs + (size_t)i * T.N + toff;

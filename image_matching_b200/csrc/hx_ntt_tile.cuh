@@ -194,6 +194,39 @@ __device__ __forceinline__ void fwd_stages_fp(double* sm, int t, int tileoff, co
         fwd_stages_fp<SL + R, SL_END, S + R, SHIFT + R>(sm, t, tileoff, tw, q);
     }
 }
+// The same passes with the FIRST round fed straight from global memory: `src` is the tile's 2048 contiguous pass-internal words,
+// read in the round's own ownership (a warp reads 256 contiguous bytes per element index).  Saves the staging stores, the first
+// round's shared loads and one barrier; the tile in shared memory need not be initialised.
+template <int SL, int SL_END, int S, int SHIFT>
+__device__ __forceinline__ void fwd_stages_g(u64* sm, const u64* src, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
+    constexpr int R = (SL_END - SL >= 3) ? 3 : (SL_END - SL);
+    constexpr int p = kLogTile - SL - R;
+    const int base = round_base<p>(t);
+    u64 v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) v[k] = ldg64(src + base + (k << p));
+    fwd_regs_ct<SL, R, S, SHIFT>(v, base, tileoff, tw, q, q4);
+    u64* const sp = sm + tphys(base);
+#pragma unroll
+    for (int k = 0; k < 8; k++) sp[toff(k, p)] = v[k];
+    __syncthreads();
+    fwd_stages<SL + R, SL_END, S + R, SHIFT + R>(sm, t, tileoff, tw, q, q4);
+}
+template <int SL, int SL_END, int S, int SHIFT>
+__device__ __forceinline__ void fwd_stages_fp_g(double* sm, const u64* src, int t, int tileoff, const double2* __restrict__ tw, double q) {
+    constexpr int R = (SL_END - SL >= 3) ? 3 : (SL_END - SL);
+    constexpr int p = kLogTile - SL - R;
+    const int base = round_base<p>(t);
+    double v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) v[k] = __longlong_as_double((long long)ldg64(src + base + (k << p)));
+    fwd_regs_fp<SL, R, S, SHIFT>(v, base, tileoff, tw, q);
+    double* const sp = sm + tphys(base);
+#pragma unroll
+    for (int k = 0; k < 8; k++) sp[toff(k, p)] = v[k];
+    __syncthreads();
+    fwd_stages_fp<SL + R, SL_END, S + R, SHIFT + R>(sm, t, tileoff, tw, q);
+}
 // column pass: global stages 0..A-1 = local stages 0..A-1, twiddle = 2^s + (row >> (A-s)); no tile offset.
 // Shared memory holds pass-internal words (fwd_encode of canonical residues) on entry.
 template <int LOGN, class Tables>

@@ -84,14 +84,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_ks_p_inner(const __gr
         smp[u * kPairStep + 1] = redc(fold30(a1), pc.q, pc.qinv_neg);
     }
     __syncthreads();
-    inv_row_pass<LOGN>(sm, t, tile, T.tw_inv + (size_t)prime * T.N, pc.q);
     u64* o = a.tmpP + (((size_t)b * 2 + comp) * a.K + k) * T.N + (size_t)tile * kTileN;
-#pragma unroll
-    for (int u = 0; u < 4; u++) {
-        const int e = (u * kTileThreads + t) * 2;
-        ulonglong2 x = {smp[u * kPairStep], smp[u * kPairStep + 1]};
-        st128(o + e, x);
-    }
+    inv_row_pass_g<LOGN>(sm, o, t, tile, T.tw_inv + (size_t)prime * T.N, pc.q);   // last round straight to global memory
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -407,14 +401,8 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_inv_rows(const __grid
         smp[u * kPairStep + 1] = x.y;
     }
     __syncthreads();
-    inv_row_pass<LOGN>(sm, t, tile, T.tw_inv + (size_t)prime * T.N, q);
     u64* dst = out + (size_t)blockIdx.z * out_bs + (size_t)blockIdx.y * T.N + (size_t)tile * kTileN;
-#pragma unroll
-    for (int u = 0; u < 4; u++) {
-        const int e = (u * kTileThreads + t) * 2;
-        ulonglong2 x = {smp[u * kPairStep], smp[u * kPairStep + 1]};
-        st128(dst + e, x);
-    }
+    inv_row_pass_g<LOGN>(sm, dst, t, tile, T.tw_inv + (size_t)prime * T.N, q);   // last round straight to global memory
 }
 
 // ModUp tail: grid (TILES, ext, ndig*nbatch).  Limb y of digit d: own limbs [lo,hi) are copied from the
@@ -449,15 +437,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_modup_rows(const __gr
         }
         return;
     }
-#pragma unroll
-    for (int u = 0; u < 4; u++) {
-        const int e = (u * kTileThreads + t) * 2;
-        const ulonglong2 x = ldg128(limb + e);
-        smp[u * kPairStep] = x.x;
-        smp[u * kPairStep + 1] = x.y;
-    }
-    __syncthreads();
-    fwd_row_pass<LOGN>(sm, t, tile, T, prime, q);
+    fwd_row_pass_g<LOGN>(sm, limb, t, tile, T, prime, q);   // first round straight from global memory
 #pragma unroll
     for (int u = 0; u < 4; u++) {
         const int e = (u * kTileThreads + t) * 2;
@@ -511,15 +491,7 @@ __global__ void __launch_bounds__(kTileThreads, HX_MINB) k_rescale_rows(const __
     const u64 q = pc.q;
     const size_t off = (size_t)i * T.N + (size_t)tile * kTileN;
     const u64* src = tmp + (size_t)blockIdx.z * tmp_bs + off;
-#pragma unroll
-    for (int u = 0; u < 4; u++) {
-        const int e = (u * kTileThreads + t) * 2;
-        const ulonglong2 x = ldg128(src + e);
-        smp[u * kPairStep] = x.x;
-        smp[u * kPairStep + 1] = x.y;
-    }
-    __syncthreads();
-    fwd_row_pass<LOGN>(sm, t, tile, T, i, q);
+    fwd_row_pass_g<LOGN>(sm, src, t, tile, T, i, q);   // first round straight from global memory
     const bool fp = fp_ok(q);
     const u64* cs = c + (size_t)blockIdx.z * c_bs + off;
     u64* dst = out + (size_t)blockIdx.z * out_bs + off;

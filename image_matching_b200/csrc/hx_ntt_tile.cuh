@@ -243,6 +243,14 @@ __device__ __forceinline__ void fwd_row_pass(u64* sm, int t, int tile, const Tab
     else fwd_stages<G::LOGD, kLogTile, G::A, G::LOGD>(sm, t, tile, T.tw_fwd + (size_t)prime * T.N, q, q << 2);
 }
 
+// row pass with its first round fed from global memory (see fwd_stages_g): `src` = the tile's 2048 contiguous pass-internal words
+template <int LOGN, class Tables>
+__device__ __forceinline__ void fwd_row_pass_g(u64* sm, const u64* src, int t, int tile, const Tables& T, int prime, u64 q) {
+    using G = NttGeo<LOGN>;
+    if (fp_ok(q)) fwd_stages_fp_g<G::LOGD, kLogTile, G::A, G::LOGD>(reinterpret_cast<double*>(sm), src, t, tile, T.tw_fwd_d + (size_t)prime * T.N, u64_to_double_small(q));
+    else fwd_stages_g<G::LOGD, kLogTile, G::A, G::LOGD>(sm, src, t, tile, T.tw_fwd + (size_t)prime * T.N, q, q << 2);
+}
+
 // ---- inverse --------------------------------------------------------------------------------
 // One round of R consecutive inverse (Gentleman-Sande) stages: local stages SH-1, SH-2, .., SH-R.
 // S_TOP = global stage of local stage SH-1; SHIFT_TOP = shift of tileoff at that stage.
@@ -297,6 +305,34 @@ __device__ __forceinline__ void inv_row_pass(u64* sm, int t, int tile, const ulo
     using G = NttGeo<LOGN>;
     // top stage LOGN-1: shift of the tile offset there = LOGD + (LOGN-1-A) = 10
     inv_stages<G::LOGD, kLogTile, LOGN - 1, kLogTile - 1>(sm, t, tile, tw, q, q << 2);
+}
+// The same with the LAST round written straight to global memory (`dst` = the tile's 2048 contiguous words; a warp writes 256
+// contiguous bytes per element index): no final shared stores, no re-read in another ownership, one barrier fewer.  Values [0,4q).
+template <int SL, int SH, int S_TOP, int SHIFT_TOP>
+__device__ __forceinline__ void inv_stages_g(u64* sm, u64* dst, int t, int tileoff, const ulonglong2* __restrict__ tw, u64 q, u64 q4) {
+    static_assert(SH > SL, "at least one stage");
+    constexpr int rem = (SH - SL) % 3;
+    constexpr int R = rem == 0 ? 3 : rem;
+    if constexpr (SH - R == SL) {
+        constexpr int p = kLogTile - SH;
+        const int base = round_base<p>(t);
+        const u64* const sp = sm + tphys(base);
+        u64 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = sp[toff(k, p)];
+        inv_regs_ct<SH, R, S_TOP, SHIFT_TOP>(v, base, tileoff, tw, q, q4);
+#pragma unroll
+        for (int k = 0; k < 8; k++) dst[base + (k << p)] = v[k];
+    } else {
+        inv_round_ct<SH, R, S_TOP, SHIFT_TOP>(sm, t, tileoff, tw, q, q4);
+        __syncthreads();
+        inv_stages_g<SL, SH - R, S_TOP - R, SHIFT_TOP - R>(sm, dst, t, tileoff, tw, q, q4);
+    }
+}
+template <int LOGN>
+__device__ __forceinline__ void inv_row_pass_g(u64* sm, u64* dst, int t, int tile, const ulonglong2* __restrict__ tw, u64 q) {
+    using G = NttGeo<LOGN>;
+    inv_stages_g<G::LOGD, kLogTile, LOGN - 1, kLogTile - 1>(sm, dst, t, tile, tw, q, q << 2);
 }
 template <int LOGN>
 __device__ __forceinline__ void inv_col_pass(u64* sm, int t, const ulonglong2* __restrict__ tw, u64 q) {

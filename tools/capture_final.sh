@@ -14,6 +14,6 @@ python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-share --total-blocks
 NCU="ncu --clock-control none --profile-from-start off"
 $NCU --metrics gpu__time_duration.sum --csv --log-file $out/${tag}_launches_1b.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-share --ncu-range > $out/${tag}_ncu1.log 2>&1
 $NCU --metrics gpu__time_duration.sum --csv --log-file $out/${tag}_launches_8b.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-share --total-blocks 8 --ncu-range > $out/${tag}_ncu8.log 2>&1
-$NCU --set full --import-source on -k regex:'k_moddown_w|k_ks_p_inner|k_ks_q_finish' -s 12 -c 12 -o $out/${tag}_ks -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-share --ncu-range > $out/${tag}_ncu_full.log 2>&1
-$NCU --set full --import-source on -k regex:'k_diag_mac|k_modup_rows|k_rescale_rows|k_rescale_cols|k_tensor' -c 10 -o $out/${tag}_other -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-share --total-blocks 8 --ncu-range > $out/${tag}_ncu_other.log 2>&1
+$NCU --set full --import-source on -k regex:'k_moddown_w|k_ks_p_inner|k_ks_q_finish' -s 12 -c 8 -o $out/${tag}_ks -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-share --ncu-range > $out/${tag}_ncu_full.log 2>&1
+$NCU --set full --import-source on -k regex:'k_diag_mac|k_modup_rows|k_rescale_rows|k_rescale_cols|k_tensor' -c 6 -o $out/${tag}_other -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-share --total-blocks 8 --ncu-range > $out/${tag}_ncu_other.log 2>&1
 ls -la $out | grep ${tag}

@@ -89,3 +89,28 @@ def test_ring_2p16_reference_limb_counts_bit_exact(depth, L, K):
     assert same(mp_g, mp_w)
     # decrypted-level sanity with the tolerance the reference states (main_accuracy.cpp:354-364)
     assert np.abs(orc.decrypt(s_w) - a * b).max() <= 1e-4
+
+
+def test_ragged_diagonal_count_and_odd_block_count_bit_exact():
+    """N = 2^15 with a diagonal count that is not a multiple of the 32-rotation batch (37 = 32 + a batch of 4 rotations after
+    rotation 0, the small-batch launch shapes of every key-switch kernel) and three database blocks (the batched compare chain on an
+    odd batch): score_diag / index / membership against the oracle (sender_diag.cpp:12-63), with two rotation-batch sizes."""
+    ndiag, blocks = 37, 3
+    orc = make_oracle(ring_dim=None, depth=11, rotations=list(range(1, ndiag)) + [2 ** i for i in range(14)], seed=23)
+    cc = make_gpu_context(orc)
+    rng = np.random.default_rng(5)
+    base = [orc.encrypt(rng.uniform(-0.05, 0.05, orc.P.slots)) for _ in range(16)]
+    dbc = [base[(d * 5 + 3 * b) % 16] for b in range(blocks) for d in range(ndiag)]
+    for i, c in enumerate(dbc):
+        cc.db_register(i // ndiag, i % ndiag, np.stack(c.c))
+    qc = orc.encrypt(rng.uniform(-0.05, 0.05, orc.P.slots))
+    gq = up(cc, qc)
+    want = O.diag_compute_similarity(orc, qc, dbc, ndiag)
+    widx = [O.chebyshev_compare(orc, s) for s in want]
+    wm = orc.eval_sum(orc.add_many(widx), orc.P.slots)
+    for chunk in (32, 5):
+        cc.set_option("rot_chunk", chunk)
+        got = cc.score_diag(gq, ndiag)
+        assert len(got) == blocks and all(same(g, w) for g, w in zip(got, want)), chunk
+        assert all(same(g, w) for g, w in zip(cc.index(gq, ndiag), widx)), chunk
+        assert same(cc.membership(gq, ndiag), wm), chunk

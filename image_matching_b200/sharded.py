@@ -119,6 +119,26 @@ class TorchTransport:
         self.exchange_to_engine()
         return out, acc   # acc must outlive the collective: the caller drops it after the engine stream has joined
 
+    def reduce_inplace(self, dist, group, ct):
+        """int64 SUM of the ciphertext's raw words over the ranks into rank 0, on the ciphertext's own storage (no staging tensor,
+        no torch arithmetic: hx_ct_fold_mod brings the sums back below q_i afterwards).  Contents on other ranks are unspecified."""
+        self.engine_to_exchange()
+        dist.reduce(self.view(ct), dst=0, op=dist.ReduceOp.SUM, group=group)
+        self.exchange_to_engine()
+
+    def gather_batched(self, dist, group, ct, rank, world):
+        """Every rank's batched ciphertext [B][...] (same B on all ranks) into one batched ciphertext [world * B][...] on rank 0, in
+        rank order, received straight into the result's storage.  Returns (result or None, ct): ct must outlive the collective."""
+        ncomp, nl, level, deg = ct.info()
+        nb = self.cc.device_view(ct)[2]
+        out = self.cc.alloc(ncomp, nl, level, deg, nb * world) if rank == 0 else None
+        self.engine_to_exchange()
+        src = self.view(ct)
+        bufs = list(self.view(out).chunk(world, dim=0)) if rank == 0 else None
+        dist.gather(src, bufs, dst=0, group=group)
+        self.exchange_to_engine()
+        return out, ct
+
     def to_tensor(self, ct):
         ncomp, nl, _, _ = ct.info()
         t = self.torch.empty((ncomp, nl, self.cc.N), dtype=self.torch.int64, device=self.device)
@@ -183,7 +203,16 @@ class ShardedDiagonalSender(Sender):
 
     def indexScenario(self, queryCipher) -> Optional[List]:
         """Rank 0 returns the G result ciphertexts in global block order; other ranks return None."""
-        import torch
+        total = self._total_blocks()
+        if self.world > 1 and self.shard == "diagonals" and hasattr(self.transport, "gather_batched") and total % self.world == 0:
+            # the compare results stay one batched ciphertext and are gathered straight into rank 0's result storage
+            cc = self.cc
+            cmp = cc.compare(self.computeSimilarity(queryCipher), MATCH_THRESHOLD, COMP_DEPTH)
+            _mark(cc, "compare_end")
+            with _exchange(self.transport):
+                out, keep = self.transport.gather_batched(self.dist, self.group, cmp, self.rank, self.world)
+            del keep, cmp                                     # freed in engine-stream order, behind the join
+            return cc.unstack(out) if self.rank == 0 else None
         local = self._local_index(queryCipher)
         if self.world == 1:
             return local
@@ -218,6 +247,13 @@ class ShardedDiagonalSender(Sender):
         if self.world == 1:
             return cc.EvalSum(part, cc.GetBatchSize())
         _, _, level, deg = part.info()
+        if hasattr(self.transport, "reduce_inplace"):
+            with _exchange(self.transport):
+                self.transport.reduce_inplace(self.dist, self.group, part)
+            if self.rank != 0:
+                return None
+            cc.fold_mod(part)                                 # sums of `world` residues -> residues (hx_ct_fold_mod)
+            return cc.EvalSum(part, cc.GetBatchSize())
         with _exchange(self.transport):
             t = self.transport.to_tensor(part)
             self.dist.reduce(t, dst=0, op=self.dist.ReduceOp.SUM, group=self.group)
